@@ -1,0 +1,172 @@
+// curve.cuh — short-Weierstrass (a = 0) group law in XYZZ coordinates.
+//
+// Replaces, on the device, libff's GroupT::mixed_add / add / dbl / operator- for
+//   alt_bn128 G1/G2 (alt_bn128_g1.cpp:149-326, alt_bn128_g2.cpp:166-349),
+//   bls12_377 G1/G2 (bls12_377_g1.cpp:190-352, bls12_377_g2.cpp:209-368),
+//   bw6_761  G1/G2 (bw6_761_g1.cpp:206-358,  bw6_761_g2.cpp:211-...).
+// All six curves' groups have a = 0, so one formula set serves them. The reference
+// uses Jacobian (or, for bw6_761, homogeneous projective) coordinates; group
+// elements are only canonical after normalisation, so the device is
+// free to use XYZZ (x = X/ZZ, y = Y/ZZZ, ZZ^3 = ZZZ^2): mixed add 8M+2S, add 12M+2S,
+// no inversions. Results are normalised to affine before they leave the device and
+// are then bit-identical to the reference's to_affine_coordinates().
+//
+// Exceptional cases follow libff's test list (test_groups.cpp:24-57): O+P, P+O,
+// P+P (-> dbl), P+(-P) (-> O).
+#pragma once
+#include "fp.cuh"
+
+namespace b200
+{
+
+template<class F> struct Affine {
+    F x, y;
+};
+
+template<class F> struct XYZZ {
+    F x, y, zz, zzz;
+
+    HD static XYZZ inf()
+    {
+        XYZZ r;
+        r.x = F::zero();
+        r.y = F::zero();
+        r.zz = F::zero();
+        r.zzz = F::zero();
+        return r;
+    }
+    HD bool is_inf() const { return zz.is_zero(); }
+    HD static XYZZ from_affine(const Affine<F> &p)
+    {
+        XYZZ r;
+        r.x = p.x;
+        r.y = p.y;
+        r.zz = F::one();
+        r.zzz = F::one();
+        return r;
+    }
+};
+
+// 2 * (affine p)   — EFD dbl-2008-s-1 with ZZ = ZZZ = 1, a = 0.
+template<class F> HD XYZZ<F> dbl_affine(const Affine<F> &p)
+{
+    const F u = p.y.dbl();
+    const F v = u.sqr();
+    const F w = u * v;
+    const F s = p.x * v;
+    const F x2 = p.x.sqr();
+    const F m = x2.dbl() + x2;
+    XYZZ<F> r;
+    r.x = m.sqr() - s.dbl();
+    r.y = m * (s - r.x) - w * p.y;
+    r.zz = v;
+    r.zzz = w;
+    return r;
+}
+
+// acc = 2 * acc   — EFD dbl-2008-s-1, a = 0. (y == 0 cannot occur on these prime-order groups,
+// but is handled: U = 0 gives ZZ = 0 = infinity, which is the right answer for a 2-torsion point.)
+template<class F> HD void dbl(XYZZ<F> &a)
+{
+    const F u = a.y.dbl();
+    const F v = u.sqr();
+    const F w = u * v;
+    const F s = a.x * v;
+    const F x2 = a.x.sqr();
+    const F m = x2.dbl() + x2;
+    const F x3 = m.sqr() - s.dbl();
+    a.y = m * (s - x3) - w * a.y;
+    a.x = x3;
+    a.zz = v * a.zz;
+    a.zzz = w * a.zzz;
+}
+
+// acc += p (p affine, never infinity)   — EFD madd-2008-s.
+// Counterpart of libff mixed_add (alt_bn128_g1.cpp:208-283).
+template<class F> HD void madd(XYZZ<F> &a, const Affine<F> &p)
+{
+    if (a.is_inf()) {
+        a = XYZZ<F>::from_affine(p);
+        return;
+    }
+    const F u2 = p.x * a.zz;
+    const F s2 = p.y * a.zzz;
+    const F pd = u2 - a.x;
+    const F rd = s2 - a.y;
+    if (pd.is_zero()) {
+        if (rd.is_zero()) {
+            a = dbl_affine(p);
+        } else {
+            a = XYZZ<F>::inf();
+        }
+        return;
+    }
+    const F pp = pd.sqr();
+    const F ppp = pd * pp;
+    const F q = a.x * pp;
+    const F x3 = rd.sqr() - ppp - q.dbl();
+    a.y = rd * (q - x3) - a.y * ppp;
+    a.x = x3;
+    a.zz = a.zz * pp;
+    a.zzz = a.zzz * ppp;
+}
+
+// acc += b   — EFD add-2008-s. Counterpart of libff add / operator+ (alt_bn128_g1.cpp:97-206).
+template<class F> HD void add(XYZZ<F> &a, const XYZZ<F> &b)
+{
+    if (b.is_inf()) {
+        return;
+    }
+    if (a.is_inf()) {
+        a = b;
+        return;
+    }
+    const F u1 = a.x * b.zz;
+    const F u2 = b.x * a.zz;
+    const F s1 = a.y * b.zzz;
+    const F s2 = b.y * a.zzz;
+    const F pd = u2 - u1;
+    const F rd = s2 - s1;
+    if (pd.is_zero()) {
+        if (rd.is_zero()) {
+            dbl(a);
+        } else {
+            a = XYZZ<F>::inf();
+        }
+        return;
+    }
+    const F pp = pd.sqr();
+    const F ppp = pd * pp;
+    const F q = u1 * pp;
+    const F x3 = rd.sqr() - ppp - q.dbl();
+    a.y = rd * (q - x3) - s1 * ppp;
+    a.x = x3;
+    a.zz = a.zz * b.zz * pp;
+    a.zzz = a.zzz * b.zzz * ppp;
+}
+
+template<class F> HD XYZZ<F> neg(const XYZZ<F> &a)
+{
+    XYZZ<F> r = a;
+    r.y = a.y.neg();
+    return r;
+}
+
+// Normalise: returns false for infinity, else writes affine (x, y).
+// x = X/ZZ, y = Y/ZZZ: one inversion of ZZ*ZZZ... kept simple: inv(ZZZ), then
+// 1/ZZ = ZZZ^-1 * (ZZZ/ZZ) is not available without Z, so two products off one inverse:
+//   t = (ZZ*ZZZ)^-1;  1/ZZ = t*ZZZ;  1/ZZZ = t*ZZ.
+template<class F> HD bool to_affine(const XYZZ<F> &a, Affine<F> &out)
+{
+    if (a.is_inf()) {
+        out.x = F::zero();
+        out.y = F::zero();
+        return false;
+    }
+    const F t = (a.zz * a.zzz).inverse();
+    out.x = a.x * (t * a.zzz);
+    out.y = a.y * (t * a.zz);
+    return true;
+}
+
+} // namespace b200

@@ -1,0 +1,317 @@
+// fp.cuh — Montgomery-form prime-field arithmetic on 32-bit limbs.
+//
+// Replaces libff's Fp_model<n, modulus> (depends/libff/libff/algebra/fields/fp.hpp:38-160,
+// mul_reduce fp.tcc:51-228, operator+= :350-465, operator-= :467-547, invert :679-727)
+// on the device. Memory layout is bit-identical to libff: bigint<n>'s n little-endian
+// u64 limbs (bigint.hpp:33) read as 2n little-endian u32 limbs; values are Montgomery
+// residues a*R mod p with R = 2^(64n) = 2^(32N), always fully reduced (< p), exactly as
+// Fp_model keeps them. So a device result can be memcmp'ed with the reference's mont_repr.
+//
+// Multiplication is an operand-scanning Montgomery product on two interleaved
+// accumulators ("even"/"odd" 64-bit columns): every 32x32->64 product lands on a
+// 64-bit aligned column of one of the two accumulators, so each row is one carry
+// chain of mad.lo.cc/madc.hi.cc pairs (-> IMAD.WIDE.U32 + carry in SASS) and no
+// product ever needs its own carry fix-up. Cost: 2*N^2 wide multiply-adds + N low
+// multiplies (the quotient digits) — the MM(n32) of SURVEY.md §8(d).
+#pragma once
+#include "prims.cuh"
+
+namespace b200
+{
+
+template<class P> struct Fp {
+    static constexpr int N = P::N;
+    typedef P params;
+    uint32_t v[N];
+
+    HD static Fp zero()
+    {
+        Fp r;
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            r.v[i] = 0;
+        }
+        return r;
+    }
+    // Montgomery form of 1 (= R mod p), libff's Fp_model::one().
+    HD static Fp one()
+    {
+        Fp r;
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            r.v[i] = P::one(i);
+        }
+        return r;
+    }
+    HD static Fp r2()
+    {
+        Fp r;
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            r.v[i] = P::r2(i);
+        }
+        return r;
+    }
+
+    HD bool is_zero() const
+    {
+        uint32_t acc = 0;
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            acc |= v[i];
+        }
+        return acc == 0;
+    }
+    HD bool operator==(const Fp &o) const
+    {
+        uint32_t acc = 0;
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            acc |= v[i] ^ o.v[i];
+        }
+        return acc == 0;
+    }
+    HD bool operator!=(const Fp &o) const { return !(*this == o); }
+
+    // r = (borrow of x - p) ? x : x - p, for x < 2p.
+    HD static void final_sub(uint32_t *x)
+    {
+        uint32_t t[N];
+        t[0] = prim::sub_cc(x[0], P::mod(0));
+#pragma unroll
+        for (int i = 1; i < N; ++i) {
+            t[i] = prim::subc_cc(x[i], P::mod(i));
+        }
+        const uint32_t borrow = prim::subc(0, 0); // 0 or 0xffffffff
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            x[i] = borrow ? x[i] : t[i];
+        }
+    }
+
+    HD friend Fp operator+(const Fp &a, const Fp &b)
+    {
+        Fp r;
+        r.v[0] = prim::add_cc(a.v[0], b.v[0]);
+#pragma unroll
+        for (int i = 1; i < N - 1; ++i) {
+            r.v[i] = prim::addc_cc(a.v[i], b.v[i]);
+        }
+        r.v[N - 1] = prim::addc(a.v[N - 1], b.v[N - 1]); // p has a spare top bit: a+b < 2p < 2^(32N)
+        final_sub(r.v);
+        return r;
+    }
+
+    HD friend Fp operator-(const Fp &a, const Fp &b)
+    {
+        Fp r;
+        r.v[0] = prim::sub_cc(a.v[0], b.v[0]);
+#pragma unroll
+        for (int i = 1; i < N; ++i) {
+            r.v[i] = prim::subc_cc(a.v[i], b.v[i]);
+        }
+        const uint32_t borrow = prim::subc(0, 0); // all-ones iff a < b
+        r.v[0] = prim::add_cc(r.v[0], P::mod(0) & borrow);
+#pragma unroll
+        for (int i = 1; i < N - 1; ++i) {
+            r.v[i] = prim::addc_cc(r.v[i], P::mod(i) & borrow);
+        }
+        r.v[N - 1] = prim::addc(r.v[N - 1], P::mod(N - 1) & borrow);
+        return r;
+    }
+
+    HD Fp neg() const
+    {
+        // libff Fp_model::operator- (fp.tcc:616-630): 0 stays 0, else p - a.
+        Fp r;
+        r.v[0] = prim::sub_cc(P::mod(0), v[0]);
+#pragma unroll
+        for (int i = 1; i < N - 1; ++i) {
+            r.v[i] = prim::subc_cc(P::mod(i), v[i]);
+        }
+        r.v[N - 1] = prim::subc(P::mod(N - 1), v[N - 1]);
+        const bool z = is_zero();
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            r.v[i] = z ? 0u : r.v[i];
+        }
+        return r;
+    }
+    HD Fp cneg(bool flag) const
+    {
+        const Fp n = neg();
+        Fp r;
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            r.v[i] = flag ? n.v[i] : v[i];
+        }
+        return r;
+    }
+
+    HD Fp dbl() const { return *this + *this; }
+
+    // One Montgomery round on the two interleaved accumulators (see header).
+    //   ev has weight 2^0 per limb index, od has weight 2^32: V = ev + 2^32 * od.
+    // first: ev/od are written; else the previous round's (ev, od) arrive swapped
+    // and shifted: new ev = old od (+ old ev[1]), new od = old ev >> 64.
+    template<bool FIRST> HD static void mont_round(uint32_t *ev, uint32_t *od, const uint32_t *a, uint32_t bi)
+    {
+        if (FIRST) {
+#pragma unroll
+            for (int j = 0; j < N; j += 2) {
+                ev[j] = prim::mul_lo(a[j], bi);
+                ev[j + 1] = prim::mul_hi(a[j], bi);
+                od[j] = prim::mul_lo(a[j + 1], bi);
+                od[j + 1] = prim::mul_hi(a[j + 1], bi);
+            }
+        } else {
+            // ev[0] (old od[0]) += old ev[1]; its carry has weight 2^32 = od[0]'s.
+            ev[0] = prim::add_cc(ev[0], od[1]);
+            // od[k] = old_ev[k+2] + (odd-limb products of a*bi), shifted down by 64 bits.
+#pragma unroll
+            for (int j = 1; j < N; j += 2) {
+                const int k = j - 1;
+                const uint32_t in0 = (k + 2 < N) ? od[k + 2] : 0u;
+                const uint32_t in1 = (k + 3 < N) ? od[k + 3] : 0u;
+                od[k] = prim::madc_lo_cc(a[j], bi, in0);
+                if (k + 1 < N - 1) {
+                    od[k + 1] = prim::madc_hi_cc(a[j], bi, in1);
+                } else {
+                    od[k + 1] = prim::madc_hi(a[j], bi, in1);
+                }
+            }
+            ev[0] = prim::mad_lo_cc(a[0], bi, ev[0]);
+            ev[1] = prim::madc_hi_cc(a[0], bi, ev[1]);
+#pragma unroll
+            for (int j = 2; j < N; j += 2) {
+                ev[j] = prim::madc_lo_cc(a[j], bi, ev[j]);
+                ev[j + 1] = prim::madc_hi_cc(a[j], bi, ev[j + 1]);
+            }
+            od[N - 1] = prim::addc(od[N - 1], 0);
+        }
+        const uint32_t m = prim::mul_lo(ev[0], P::INV);
+        od[0] = prim::mad_lo_cc(P::mod(1), m, od[0]);
+        if (N > 2) {
+            od[1] = prim::madc_hi_cc(P::mod(1), m, od[1]);
+        } else {
+            od[1] = prim::madc_hi(P::mod(1), m, od[1]);
+        }
+#pragma unroll
+        for (int j = 3; j < N; j += 2) {
+            od[j - 1] = prim::madc_lo_cc(P::mod(j), m, od[j - 1]);
+            if (j < N - 1) {
+                od[j] = prim::madc_hi_cc(P::mod(j), m, od[j]);
+            } else {
+                od[j] = prim::madc_hi(P::mod(j), m, od[j]);
+            }
+        }
+        ev[0] = prim::mad_lo_cc(P::mod(0), m, ev[0]);
+        ev[1] = prim::madc_hi_cc(P::mod(0), m, ev[1]);
+#pragma unroll
+        for (int j = 2; j < N; j += 2) {
+            ev[j] = prim::madc_lo_cc(P::mod(j), m, ev[j]);
+            ev[j + 1] = prim::madc_hi_cc(P::mod(j), m, ev[j + 1]);
+        }
+        od[N - 1] = prim::addc(od[N - 1], 0);
+    }
+
+    // a * b * R^-1 mod p, fully reduced. (libff: Fp_model::mul_reduce, fp.tcc:51-228.)
+    HD friend Fp operator*(const Fp &a, const Fp &b)
+    {
+        static_assert(N % 2 == 0, "even limb count");
+        uint32_t acc[2][N];
+        mont_round<true>(acc[0], acc[1], a.v, b.v[0]);
+#pragma unroll
+        for (int i = 1; i < N; ++i) {
+            mont_round<false>(acc[i & 1], acc[(i & 1) ^ 1], a.v, b.v[i]);
+        }
+        // after the last round (i = N-1, odd): ev = acc[1], od = acc[0], ev[0] == 0.
+        const uint32_t *ev = acc[1];
+        const uint32_t *od = acc[0];
+        Fp r;
+        r.v[0] = prim::add_cc(ev[1], od[0]);
+#pragma unroll
+        for (int k = 1; k < N - 1; ++k) {
+            r.v[k] = prim::addc_cc(ev[k + 1], od[k]);
+        }
+        r.v[N - 1] = prim::addc(od[N - 1], 0);
+        final_sub(r.v);
+        return r;
+    }
+
+    HD Fp sqr() const { return (*this) * (*this); }
+
+    // Montgomery -> standard representation (libff as_bigint, fp.tcc:270-281): multiply by 1.
+    HD Fp from_mont() const
+    {
+        Fp o = zero();
+        o.v[0] = 1;
+        return (*this) * o;
+    }
+    // standard -> Montgomery (libff Fp_model(bigint) ctor, fp.tcc:230-235): multiply by R^2.
+    HD Fp to_mont() const { return (*this) * r2(); }
+
+    // a^(p-2) (libff's invert uses mpn_gcdext, fp.tcc:679-727; the value is the same).
+    HD Fp inverse() const
+    {
+        Fp result = one();
+        bool started = false;
+        for (int i = N - 1; i >= 0; --i) {
+            const uint32_t w = P::pm2(i);
+            for (int b = 31; b >= 0; --b) {
+                if (started) {
+                    result = result.sqr();
+                }
+                if ((w >> b) & 1u) {
+                    result = started ? result * (*this) : *this;
+                    started = true;
+                }
+            }
+        }
+        return result;
+    }
+};
+
+// Fp2 = Fp[u] / (u^2 - nr).  libff Fp2_model (fp2.hpp; mul fp2.tcc:102-114 Karatsuba,
+// squared fp2.tcc:142-151 complex squaring). In-memory layout c0 | c1 as in libff.
+// P2 supplies: typedef Fp<...> base;  static base mul_by_nr(const base&).
+template<class P2> struct Fp2 {
+    typedef typename P2::base F;
+    typedef P2 params;
+    F c0, c1;
+
+    HD static Fp2 zero() { return Fp2{F::zero(), F::zero()}; }
+    HD static Fp2 one() { return Fp2{F::one(), F::zero()}; }
+    HD bool is_zero() const { return c0.is_zero() && c1.is_zero(); }
+    HD bool operator==(const Fp2 &o) const { return c0 == o.c0 && c1 == o.c1; }
+    HD bool operator!=(const Fp2 &o) const { return !(*this == o); }
+    HD friend Fp2 operator+(const Fp2 &a, const Fp2 &b) { return Fp2{a.c0 + b.c0, a.c1 + b.c1}; }
+    HD friend Fp2 operator-(const Fp2 &a, const Fp2 &b) { return Fp2{a.c0 - b.c0, a.c1 - b.c1}; }
+    HD Fp2 neg() const { return Fp2{c0.neg(), c1.neg()}; }
+    HD Fp2 cneg(bool f) const { return Fp2{c0.cneg(f), c1.cneg(f)}; }
+    HD Fp2 dbl() const { return Fp2{c0.dbl(), c1.dbl()}; }
+    HD friend Fp2 operator*(const Fp2 &a, const Fp2 &b)
+    {
+        const F aA = a.c0 * b.c0;
+        const F bB = a.c1 * b.c1;
+        const F s = (a.c0 + a.c1) * (b.c0 + b.c1);
+        return Fp2{aA + P2::mul_by_nr(bB), s - aA - bB};
+    }
+    HD Fp2 sqr() const
+    {
+        const F ab = c0 * c1;
+        const F t = (c0 + c1) * (c0 + P2::mul_by_nr(c1));
+        return Fp2{t - ab - P2::mul_by_nr(ab), ab + ab};
+    }
+    HD Fp2 inverse() const
+    {
+        // fp2.tcc:153-167: (c0 - c1 u) / (c0^2 - nr c1^2)
+        const F t0 = c0.sqr();
+        const F t1 = c1.sqr();
+        const F t2 = t0 - P2::mul_by_nr(t1);
+        const F t3 = t2.inverse();
+        return Fp2{c0 * t3, (c1 * t3).neg()};
+    }
+};
+
+} // namespace b200

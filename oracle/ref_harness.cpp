@@ -67,6 +67,28 @@ template<typename ppT> struct groth16_fixture {
     }
 };
 
+// SHA512_rng<FieldT> (rng.tcc:26-69) asserts size_in_bits <= 512; bw6_761's Fq is 761 bits.
+// For such fields derive a full-width element from three 64-byte draws with the
+// reference's own field arithmetic: lo + hi * 2^384-ish mix (x*y + z).
+template<typename FieldT, bool BIG = (FieldT::num_limbs > 8)> struct det_rng {
+    static FieldT get(uint64_t idx) { return SHA512_rng<FieldT>(idx); }
+};
+template<typename FieldT> struct det_rng<FieldT, true> {
+    static FieldT get(uint64_t idx)
+    {
+        typedef Fp_model<6, bls12_377_modulus_q> SmallT; // 377-bit draws
+        bigint<FieldT::num_limbs> b[3];
+        for (int k = 0; k < 3; ++k) {
+            const auto v = SHA512_rng<SmallT>(idx * 3 + k).as_bigint();
+            b[k].clear();
+            for (int i = 0; i < 6; ++i) {
+                b[k].data[i] = v.data[i];
+            }
+        }
+        return FieldT(b[0]) * FieldT(b[1]) + FieldT(b[2]);
+    }
+};
+
 template<typename GroupT> void make_distinct_special(std::vector<GroupT> &v, size_t n, uint64_t seed)
 {
     // n distinct affine points: P_0 = [h]G, P_i = P_{i-1} + [h']G, then one
@@ -125,7 +147,7 @@ template<typename ppT> struct H {
 #pragma omp parallel for
 #endif
         for (size_t i = 0; i < n; ++i) {
-            o[i] = SHA512_rng<FieldT>(idx0 + i);
+            o[i] = det_rng<FieldT>::get(idx0 + i);
         }
         return 0;
     }
