@@ -1,0 +1,152 @@
+/* libsnark_b200.h — C-ABI of the B200 drop-in for libsnark's Groth16 proving hot path.
+ *
+ * The reference (clearmatics/libsnark + libff + libfqfft) has no FFI on this path: the
+ * operators are C++ templates. This header is the boundary a maintainer
+ * binds them to; libsnark_b200/overlay/libsnark_b200_overlay.hpp is that binding
+ * (template specialisations that forward to these entry points). Conventions follow the
+ * in-tree precedent depends/libff/ffi/ffi.h:19-95: extern "C", (const void*, size_t)
+ * buffers in the reference's own in-memory layouts, status return, exact-size checks.
+ *
+ * Layouts (all little-endian u64 limbs, Montgomery form, value < modulus — exactly
+ * Fp_model::mont_repr.data, fp.hpp:43 / bigint.hpp:33):
+ *   Fr / Fq element      : n limbs                      (alt_bn128 4/4, bls12_377 4/6, bw6_761 6/12)
+ *   G1 point             : X | Y | Z                    (3 * nq limbs; alt_bn128_g1.hpp)
+ *   G2 point             : X.c0 X.c1 | Y.c0 Y.c1 | Z.c0 Z.c1   (6 * nq limbs; bw6_761: X | Y | Z over Fq)
+ *   "special" base       : Z == one (affine) or Z == 0 (infinity)        (alt_bn128_g1.cpp:68-91)
+ * MSM results are returned normalised: (x, y, one) or the reference's zero() encoding
+ * (0, one, 0), so they memcmp-equal the reference's result after to_affine_coordinates().
+ *
+ * Every call is synchronous from the caller's view and returns B200_OK (0) or a negative
+ * status; b200_last_error() describes the last failure on the calling thread. There is no
+ * CPU fallback: without a CUDA device every compute entry point returns B200_ERR_CUDA.
+ */
+#ifndef LIBSNARK_B200_H_
+#define LIBSNARK_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default) /* the library itself is built with -fvisibility=hidden */
+#endif
+
+enum b200_curve { B200_ALT_BN128 = 0, B200_BLS12_377 = 1, B200_BW6_761 = 2 };
+enum b200_group { B200_G1 = 1, B200_G2 = 2 };
+enum b200_status {
+    B200_OK = 0,
+    B200_ERR_ARG = -1,    /* bad curve / group / size / null pointer */
+    B200_ERR_CUDA = -2,   /* CUDA runtime failure (incl. no device) */
+    B200_ERR_DOMAIN = -3, /* libfqfft DomainSizeException analogue: size not a power of two <= 2^s */
+    B200_ERR_HANDLE = -4  /* unknown handle */
+};
+/* evaluation_domain operations (libfqfft/evaluation_domain/evaluation_domain.hpp:63-78) */
+enum b200_ntt_op { B200_FFT = 0, B200_IFFT = 1, B200_COSET_FFT = 2, B200_ICOSET_FFT = 3 };
+
+/* ---- runtime ------------------------------------------------------------------------ */
+int b200_version(void);
+/* Binds the calling process to CUDA device `device` (one process per GPU) and creates the
+ * library's streams. Idempotent for the same device. */
+int b200_init(int device);
+int b200_device_count(void);
+const char *b200_last_error(void);
+/* sizes in bytes of the reference's types for `curve` */
+size_t b200_sizeof_fr(int curve);
+size_t b200_sizeof_group(int curve, int group);
+
+/* ---- device memory (for callers that keep data resident between calls) -------------- */
+int b200_dev_alloc(size_t bytes, void **dev_ptr);
+int b200_dev_free(void *dev_ptr);
+int b200_memcpy_h2d(void *dev_dst, const void *host_src, size_t bytes);
+int b200_memcpy_d2h(void *host_dst, const void *dev_src, size_t bytes);
+int b200_sync(void);
+
+/* ---- MSM: libff::multi_exp<GroupT, FieldT, multi_exp_method_BDLO12_signed,
+ *           multi_exp_base_form_special>  (multiexp.hpp:63-73, multiexp.tcc:643-688) ------
+ * bases   : n points in the reference layout, `base_stride` bytes apart (sizeof(GroupT) for
+ *           a std::vector<GroupT>; sizeof(knowledge_commitment<G2,G1>) for a B_query).
+ * scalars : n Fr elements, Montgomery form, contiguous.
+ * out     : one point, reference layout, normalised.
+ * The reference's `chunks` argument has no meaning here (one GPU pass) and is dropped. */
+int b200_msm(int curve, int group, const void *bases, size_t base_stride, size_t n,
+             const void *scalars, void *out);
+
+/* Device-resident base sets (proving-key queries are uploaded once; SURVEY.md §8b "Ownership"). */
+typedef uint64_t b200_bases_t;
+int b200_bases_upload(int curve, int group, const void *bases, size_t base_stride, size_t n,
+                      b200_bases_t *handle);
+int b200_bases_free(b200_bases_t handle);
+size_t b200_bases_size(b200_bases_t handle);
+
+/* MSM over bases[first, first+n) of a resident set.
+ * scalars_on_device != 0: `scalars` is a device pointer (e.g. the H coefficients left on
+ * the device by b200_witness_map_h_dev). */
+int b200_msm_resident(b200_bases_t handle, size_t first, size_t n, const void *scalars,
+                      int scalars_on_device, void *out);
+
+/* Per-window partial sums instead of the folded point: for multi-GPU sharding by base range
+ * (SURVEY.md §8e). out_windows receives b200_msm_num_windows() points of
+ * b200_msm_window_bytes() each in the library's extended-Jacobian form
+ * (X | Y | ZZ | ZZZ, Montgomery limbs; x = X/ZZ, y = Y/ZZZ) — an opaque blob to gather
+ * between ranks. b200_msm_fold_windows folds `num_shards` such arrays (concatenated,
+ * all from shards of the same size class n_per_shard) into the final normalised point. */
+int b200_msm_num_windows(int curve, size_t n);
+size_t b200_msm_window_bytes(int curve, int group);
+int b200_msm_resident_windows(b200_bases_t handle, size_t first, size_t n, const void *scalars,
+                              int scalars_on_device, void *out_windows);
+int b200_msm_fold_windows(int curve, int group, size_t n_per_shard, const void *windows,
+                          size_t num_shards, void *out);
+
+/* libff::multi_exp_filter_one_zero (multiexp.hpp:83-88, multiexp.tcc:690-757; upstream name
+ * multi_exp_with_mixed_addition). Same value as b200_msm: scalars 0 and 1 need no host
+ * pre-pass on the device path; the counts the reference prints are returned for log parity
+ * (stats[0] = zeros skipped, stats[1] = ones added, stats[2] = the rest; may be NULL). */
+int b200_msm_filter_one_zero(int curve, int group, const void *bases, size_t base_stride,
+                             size_t n, const void *scalars, void *out, size_t *stats);
+
+/* libsnark::kc_multi_exp_with_mixed_addition<G2, G1, Fr, BDLO12_signed, special>
+ * (kc_multiexp.hpp:32-44, kc_multiexp.tcc:31-113) over a sparse_vector of
+ * knowledge_commitment<G2,G1> (sparse_vector.hpp:33-74): indices[nnz] (size_t, ascending),
+ * values[nnz] (G2 | G1 per entry). Entries with min_idx <= index < max_idx use
+ * scalars[index - min_idx]. Returns the pair (out_g2, out_g1), normalised. */
+int b200_kc_msm(int curve, const size_t *indices, const void *values, size_t nnz,
+                size_t min_idx, size_t max_idx, const void *scalars, size_t num_scalars,
+                void *out_g2, void *out_g1, size_t *stats);
+
+/* ---- NTT: libfqfft::basic_radix2_domain<Fr>::{FFT,iFFT,cosetFFT,icosetFFT}
+ *      (basic_radix2_domain.tcc:54-88), in place on m = 2^k Fr elements, natural order in
+ *      and out. `g` = coset generator (Fr, Montgomery) for the coset ops, else ignored/NULL.
+ *      m not a power of two, m < 2 or log2(m) > Fr::s  ->  B200_ERR_DOMAIN. ----------------- */
+int b200_ntt(int curve, int op, void *data, size_t m, const void *g);
+int b200_ntt_dev(int curve, int op, void *dev_data, size_t m, const void *g);
+/* basic_radix2_domain::divide_by_Z_on_coset (basic_radix2_domain.tcc:117-126) with
+ * coset generator Fr::multiplicative_generator. */
+int b200_divide_by_Z_on_coset(int curve, void *data, size_t m);
+
+/* The NTT chain of libsnark::r1cs_to_qap_witness_map (r1cs_to_qap.tcc:252-330) for the
+ * Groth16 case d1 = d2 = d3 = 0: in = the evaluations aA, aB, aC (m each, host);
+ * out_H = coefficients_for_H, m + 1 elements.  All seven transforms and the pointwise
+ * (A*B - C) / Z run on the device without intermediate copies. */
+int b200_witness_map_h(int curve, const void *aA, const void *aB, const void *aC, size_t m,
+                       void *out_H);
+/* Same with device buffers; dA, dB, dC are clobbered, dH (m + 1 elements) may alias none. */
+int b200_witness_map_h_dev(int curve, void *dA, void *dB, void *dC, size_t m, void *dH);
+
+/* ---- measurement helpers (used by bench.py; not part of the reference surface) ------- */
+/* Runs `iters` launches of a dependent-free IMAD.WIDE loop and returns multiply-adds/s. */
+int b200_imad_peak(int iters, double *wide_mads_per_s, double *lo_mads_per_s);
+/* Time (ms, CUDA events on the library stream) of the last MSM's kernels:
+ * [0] scalar prep+sort, [1] bucket accumulation, [2] bucket reduction, [3] fold, [4] total */
+int b200_last_msm_timing(double *ms5);
+/* Number of kernels this library has launched since b200_init (bench.py's gpu_launches). */
+uint64_t b200_launch_count(void);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* LIBSNARK_B200_H_ */

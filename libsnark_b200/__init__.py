@@ -1,0 +1,301 @@
+"""libsnark_b200 — B200-native drop-in for the Groth16 proving hot path of clearmatics/libsnark.
+
+This package is a thin ctypes binding of the C-ABI in include/libsnark_b200.h (implemented by
+libsnark_b200/libsnark_b200.so: hand-written CUDA for sm_100a). The function and class names
+mirror the reference operators they replace:
+
+  multi_exp / multi_exp_filter_one_zero   libff/algebra/scalar_multiplication/multiexp.hpp:63-88
+  kc_multi_exp_with_mixed_addition        libsnark/knowledge_commitment/kc_multiexp.hpp:32-44
+  evaluation_domain (basic radix-2)       libfqfft/evaluation_domain/evaluation_domain.hpp:37-105
+  r1cs_to_qap_witness_map_h               libsnark/reductions/r1cs_to_qap/r1cs_to_qap.tcc:252-330
+
+Arrays are numpy uint64 views of the reference's in-memory layouts (Montgomery limbs). There
+is no CPU fallback: a missing shared library or CUDA device raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libsnark_b200.so")
+
+ALT_BN128, BLS12_377, BW6_761 = 0, 1, 2
+CURVES = {"alt_bn128": ALT_BN128, "bls12_377": BLS12_377, "bw6_761": BW6_761}
+G1, G2 = 1, 2
+FFT, IFFT, COSET_FFT, ICOSET_FFT = 0, 1, 2, 3
+OK, ERR_ARG, ERR_CUDA, ERR_DOMAIN, ERR_HANDLE = 0, -1, -2, -3, -4
+
+# every symbol include/libsnark_b200.h declares (tests check the .so exports all of them)
+EXPORTS = [
+    "b200_version", "b200_init", "b200_device_count", "b200_last_error", "b200_sizeof_fr", "b200_sizeof_group",
+    "b200_dev_alloc", "b200_dev_free", "b200_memcpy_h2d", "b200_memcpy_d2h", "b200_sync",
+    "b200_msm", "b200_bases_upload", "b200_bases_free", "b200_bases_size", "b200_msm_resident",
+    "b200_msm_num_windows", "b200_msm_window_bytes", "b200_msm_resident_windows", "b200_msm_fold_windows",
+    "b200_msm_filter_one_zero", "b200_kc_msm",
+    "b200_ntt", "b200_ntt_dev", "b200_divide_by_Z_on_coset", "b200_witness_map_h", "b200_witness_map_h_dev",
+    "b200_imad_peak", "b200_last_msm_timing", "b200_launch_count",
+]
+
+
+class B200Error(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"libsnark_b200 status {code}: {msg}")
+        self.code = code
+
+
+class DomainSizeException(B200Error):
+    """libfqfft::DomainSizeException (libfqfft/tools/exceptions.hpp:21-31)."""
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            raise FileNotFoundError(
+                f"{_LIB_PATH} is missing: build it with `make -C libsnark_b200/csrc` "
+                "(or __graft_entry__.build()); there is no CPU fallback")
+        L = C.CDLL(_LIB_PATH)
+        vp, sz, i, u64 = C.c_void_p, C.c_size_t, C.c_int, C.c_uint64
+        L.b200_last_error.restype = C.c_char_p
+        L.b200_sizeof_fr.restype = sz
+        L.b200_sizeof_fr.argtypes = [i]
+        L.b200_sizeof_group.restype = sz
+        L.b200_sizeof_group.argtypes = [i, i]
+        L.b200_init.argtypes = [i]
+        L.b200_dev_alloc.argtypes = [sz, C.POINTER(vp)]
+        L.b200_dev_free.argtypes = [vp]
+        L.b200_memcpy_h2d.argtypes = [vp, vp, sz]
+        L.b200_memcpy_d2h.argtypes = [vp, vp, sz]
+        L.b200_msm.argtypes = [i, i, vp, sz, sz, vp, vp]
+        L.b200_bases_upload.argtypes = [i, i, vp, sz, sz, C.POINTER(u64)]
+        L.b200_bases_free.argtypes = [u64]
+        L.b200_bases_size.restype = sz
+        L.b200_bases_size.argtypes = [u64]
+        L.b200_msm_resident.argtypes = [u64, sz, sz, vp, i, vp]
+        L.b200_msm_num_windows.argtypes = [i, sz]
+        L.b200_msm_window_bytes.restype = sz
+        L.b200_msm_window_bytes.argtypes = [i, i]
+        L.b200_msm_resident_windows.argtypes = [u64, sz, sz, vp, i, vp]
+        L.b200_msm_fold_windows.argtypes = [i, i, sz, vp, sz, vp]
+        L.b200_msm_filter_one_zero.argtypes = [i, i, vp, sz, sz, vp, vp, vp]
+        L.b200_kc_msm.argtypes = [i, vp, vp, sz, sz, sz, vp, sz, vp, vp, vp]
+        L.b200_ntt.argtypes = [i, i, vp, sz, vp]
+        L.b200_ntt_dev.argtypes = [i, i, vp, sz, vp]
+        L.b200_divide_by_Z_on_coset.argtypes = [i, vp, sz]
+        L.b200_witness_map_h.argtypes = [i, vp, vp, vp, sz, vp]
+        L.b200_witness_map_h_dev.argtypes = [i, vp, vp, vp, sz, vp]
+        L.b200_imad_peak.argtypes = [i, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        L.b200_last_msm_timing.argtypes = [C.POINTER(C.c_double)]
+        L.b200_launch_count.restype = u64
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != OK:
+        msg = lib().b200_last_error().decode(errors="replace")
+        if rc == ERR_DOMAIN:
+            raise DomainSizeException(rc, msg)
+        raise B200Error(rc, msg)
+
+
+def _cid(curve):
+    return CURVES[curve] if isinstance(curve, str) else int(curve)
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _u64(a):
+    return np.ascontiguousarray(a, dtype=np.uint64)
+
+
+def init(device=0):
+    _check(lib().b200_init(int(device)))
+
+
+def device_count():
+    return lib().b200_device_count()
+
+
+def launch_count():
+    return int(lib().b200_launch_count())
+
+
+def sizeof_fr(curve):
+    return lib().b200_sizeof_fr(_cid(curve))
+
+
+def sizeof_group(curve, group):
+    return lib().b200_sizeof_group(_cid(curve), group)
+
+
+# ---- MSM -------------------------------------------------------------------------------------
+
+def multi_exp(curve, group, bases, scalars, base_stride=None):
+    """libff::multi_exp<GroupT, Fr, BDLO12_signed, special> -> one normalised point (u64 limbs)."""
+    c = _cid(curve)
+    bases, scalars = _u64(bases), _u64(scalars)
+    n = scalars.shape[0]
+    stride = base_stride if base_stride is not None else (bases.strides[0] if bases.ndim == 2 else 0)
+    out = np.zeros(sizeof_group(c, group) // 8, dtype=np.uint64)
+    _check(lib().b200_msm(c, group, _p(bases), stride, n, _p(scalars), _p(out)))
+    return out
+
+
+def multi_exp_filter_one_zero(curve, group, bases, scalars, base_stride=None, return_stats=False):
+    """libff::multi_exp_filter_one_zero (upstream: multi_exp_with_mixed_addition)."""
+    c = _cid(curve)
+    bases, scalars = _u64(bases), _u64(scalars)
+    n = scalars.shape[0]
+    stride = base_stride if base_stride is not None else (bases.strides[0] if bases.ndim == 2 else 0)
+    out = np.zeros(sizeof_group(c, group) // 8, dtype=np.uint64)
+    stats = np.zeros(3, dtype=np.uint64)
+    _check(lib().b200_msm_filter_one_zero(c, group, _p(bases), stride, n, _p(scalars), _p(out), _p(stats)))
+    return (out, stats) if return_stats else out
+
+
+def kc_multi_exp_with_mixed_addition(curve, indices, values, min_idx, max_idx, scalars):
+    """libsnark::kc_multi_exp_with_mixed_addition over a sparse vector of (G2, G1) pairs -> (g2, g1)."""
+    c = _cid(curve)
+    indices, values, scalars = _u64(indices), _u64(values), _u64(scalars)
+    g2 = np.zeros(sizeof_group(c, G2) // 8, dtype=np.uint64)
+    g1 = np.zeros(sizeof_group(c, G1) // 8, dtype=np.uint64)
+    _check(lib().b200_kc_msm(c, _p(indices), _p(values), indices.shape[0], min_idx, max_idx, _p(scalars),
+                             scalars.shape[0], _p(g2), _p(g1), None))
+    return g2, g1
+
+
+class ResidentBases:
+    """A proving-key query kept on the device (b200_bases_upload)."""
+
+    def __init__(self, curve, group, bases, base_stride=None):
+        self.curve, self.group = _cid(curve), group
+        bases = _u64(bases)
+        n = bases.shape[0]
+        stride = base_stride if base_stride is not None else bases.strides[0]
+        h = C.c_uint64(0)
+        _check(lib().b200_bases_upload(self.curve, group, _p(bases), stride, n, C.byref(h)))
+        self.handle, self.n = h.value, n
+
+    def multi_exp(self, scalars, first=0, n=None, device_ptr=None):
+        n = self.n - first if n is None else n
+        out = np.zeros(sizeof_group(self.curve, self.group) // 8, dtype=np.uint64)
+        if device_ptr is not None:
+            _check(lib().b200_msm_resident(self.handle, first, n, C.c_void_p(device_ptr), 1, _p(out)))
+        else:
+            scalars = _u64(scalars)
+            _check(lib().b200_msm_resident(self.handle, first, n, _p(scalars), 0, _p(out)))
+        return out
+
+    def window_sums(self, scalars, first=0, n=None, device_ptr=None):
+        n = self.n - first if n is None else n
+        W = lib().b200_msm_num_windows(self.curve, n)
+        wb = lib().b200_msm_window_bytes(self.curve, self.group)
+        out = np.zeros(W * wb // 8, dtype=np.uint64)
+        if device_ptr is not None:
+            _check(lib().b200_msm_resident_windows(self.handle, first, n, C.c_void_p(device_ptr), 1, _p(out)))
+        else:
+            scalars = _u64(scalars)
+            _check(lib().b200_msm_resident_windows(self.handle, first, n, _p(scalars), 0, _p(out)))
+        return out
+
+    def free(self):
+        if self.handle:
+            _check(lib().b200_bases_free(self.handle))
+            self.handle = 0
+
+
+def fold_windows(curve, group, n_per_shard, windows, num_shards):
+    c = _cid(curve)
+    windows = _u64(windows)
+    out = np.zeros(sizeof_group(c, group) // 8, dtype=np.uint64)
+    _check(lib().b200_msm_fold_windows(c, group, n_per_shard, _p(windows), num_shards, _p(out)))
+    return out
+
+
+def last_msm_timing():
+    ms = (C.c_double * 5)()
+    _check(lib().b200_last_msm_timing(ms))
+    return dict(zip(["sort", "accumulate", "reduce", "fold", "total"], list(ms)))
+
+
+def imad_peak(iters=4096):
+    w, lo = C.c_double(0), C.c_double(0)
+    _check(lib().b200_imad_peak(iters, C.byref(w), C.byref(lo)))
+    return w.value, lo.value
+
+
+# ---- NTT -------------------------------------------------------------------------------------
+
+class evaluation_domain:
+    """libfqfft::basic_radix2_domain<Fr> (what get_evaluation_domain returns for m = 2^k)."""
+
+    def __init__(self, curve, m):
+        self.curve, self.m = _cid(curve), int(m)
+
+    def _run(self, op, a, g=None):
+        a = np.array(a, dtype=np.uint64, order="C", copy=True)
+        if a.shape[0] != self.m:
+            raise DomainSizeException(ERR_DOMAIN, "expected a.size() == m")  # basic_radix2_domain.tcc:57
+        g_ = None if g is None else _u64(g)
+        _check(lib().b200_ntt(self.curve, op, _p(a), self.m, _p(g_)))
+        return a
+
+    def FFT(self, a):
+        return self._run(FFT, a)
+
+    def iFFT(self, a):
+        return self._run(IFFT, a)
+
+    def cosetFFT(self, a, g):
+        return self._run(COSET_FFT, a, g)
+
+    def icosetFFT(self, a, g):
+        return self._run(ICOSET_FFT, a, g)
+
+    def divide_by_Z_on_coset(self, a):
+        a = np.array(a, dtype=np.uint64, order="C", copy=True)
+        _check(lib().b200_divide_by_Z_on_coset(self.curve, _p(a), self.m))
+        return a
+
+
+def get_evaluation_domain(curve, min_size):
+    """libfqfft::get_evaluation_domain (get_evaluation_domain.tcc:32-70), power-of-two sizes only."""
+    return evaluation_domain(curve, min_size)
+
+
+def r1cs_to_qap_witness_map_h(curve, aA, aB, aC):
+    """The NTT chain of r1cs_to_qap_witness_map: evaluations aA, aB, aC -> coefficients_for_H (m + 1)."""
+    c = _cid(curve)
+    aA, aB, aC = _u64(aA), _u64(aB), _u64(aC)
+    m = aA.shape[0]
+    out = np.zeros((m + 1, aA.shape[1]), dtype=np.uint64)
+    _check(lib().b200_witness_map_h(c, _p(aA), _p(aB), _p(aC), m, _p(out)))
+    return out
+
+
+class DeviceBuffer:
+    def __init__(self, nbytes):
+        p = C.c_void_p(0)
+        _check(lib().b200_dev_alloc(nbytes, C.byref(p)))
+        self.ptr, self.nbytes = p.value, nbytes
+
+    def upload(self, a):
+        a = np.ascontiguousarray(a)
+        _check(lib().b200_memcpy_h2d(C.c_void_p(self.ptr), _p(a), a.nbytes))
+
+    def download(self, shape, dtype=np.uint64):
+        out = np.zeros(shape, dtype=dtype)
+        _check(lib().b200_memcpy_d2h(_p(out), C.c_void_p(self.ptr), out.nbytes))
+        return out
+
+    def free(self):
+        if self.ptr:
+            _check(lib().b200_dev_free(C.c_void_p(self.ptr)))
+            self.ptr = 0

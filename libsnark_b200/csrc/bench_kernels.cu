@@ -1,0 +1,117 @@
+// bench_kernels.cu — integer-pipe peak microbenchmark (the MSM roofline denominator,
+// "peak_imad measured on the box by a dependent-free IMAD microbenchmark").
+#include "runtime.hpp"
+
+namespace
+{
+
+// 8 independent 64-bit accumulators per thread, each advanced by IMAD.WIDE.U32
+// (mad.wide.u32: 32x32+64 -> 64). No carries between chains, so the FMA-heavy pipe is the
+// only limiter once enough warps are resident.
+template<int UNROLL> __global__ void __launch_bounds__(256) k_imad_wide(uint64_t *out, uint32_t a, uint32_t b, int iters)
+{
+    uint64_t acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        acc[k] = threadIdx.x + k;
+    }
+    uint32_t x = a + threadIdx.x, y = b + blockIdx.x;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[k]) : "r"(x), "r"(y));
+            }
+        }
+    }
+    uint64_t r = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        r ^= acc[k];
+    }
+    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = r;
+}
+
+template<int UNROLL> __global__ void __launch_bounds__(256) k_imad_lo(uint32_t *out, uint32_t a, uint32_t b, int iters)
+{
+    uint32_t acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        acc[k] = threadIdx.x + k;
+    }
+    uint32_t x = a + threadIdx.x, y = b + blockIdx.x;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                asm volatile("mad.lo.u32 %0, %1, %2, %0;" : "+r"(acc[k]) : "r"(x), "r"(y));
+            }
+        }
+    }
+    uint32_t r = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        r ^= acc[k];
+    }
+    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = r;
+}
+
+b200::rt::DevBuf g_buf;
+
+} // namespace
+
+extern "C" int b200_imad_peak(int iters, double *wide_mads_per_s, double *lo_mads_per_s)
+{
+    using namespace b200;
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    if (iters <= 0) {
+        iters = 4096;
+    }
+    cudaDeviceProp prop;
+    int dev = 0;
+    B200_CUDA_CHECK(cudaGetDevice(&dev));
+    B200_CUDA_CHECK(cudaGetDeviceProperties(&prop, dev));
+    const int blocks = prop.multiProcessorCount * 8, threads = 256;
+    constexpr int UNROLL = 4;
+    if (g_buf.reserve((size_t)blocks * threads * 8)) {
+        return B200_ERR_CUDA;
+    }
+    cudaStream_t s = rt::stream();
+    cudaEvent_t e0, e1;
+    B200_CUDA_CHECK(cudaEventCreate(&e0));
+    B200_CUDA_CHECK(cudaEventCreate(&e1));
+    const double ops = (double)blocks * threads * (double)iters * UNROLL * 8;
+    for (int which = 0; which < 2; ++which) {
+        float best = 1e30f;
+        for (int rep = 0; rep < 4; ++rep) {
+            B200_CUDA_CHECK(cudaEventRecord(e0, s));
+            if (which == 0) {
+                k_imad_wide<UNROLL><<<blocks, threads, 0, s>>>(g_buf.as<uint64_t>(), 12345u, 6789u, iters);
+            } else {
+                k_imad_lo<UNROLL><<<blocks, threads, 0, s>>>(g_buf.as<uint32_t>(), 12345u, 6789u, iters);
+            }
+            B200_LAUNCH_CHECK();
+            B200_CUDA_CHECK(cudaEventRecord(e1, s));
+            B200_CUDA_CHECK(cudaEventSynchronize(e1));
+            float ms = 0;
+            B200_CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+            if (rep > 0 && ms < best) {
+                best = ms;
+            }
+        }
+        const double rate = ops / (best * 1e-3);
+        if (which == 0 && wide_mads_per_s) {
+            *wide_mads_per_s = rate;
+        }
+        if (which == 1 && lo_mads_per_s) {
+            *lo_mads_per_s = rate;
+        }
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return B200_OK;
+}

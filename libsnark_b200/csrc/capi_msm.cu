@@ -1,0 +1,378 @@
+// capi_msm.cu — C-ABI entry points for the MSM operators (include/libsnark_b200.h).
+#include <algorithm>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <vector>
+
+#include "curve_params.cuh"
+#include "msm_geometry.hpp"
+#include "runtime.hpp"
+
+using namespace b200;
+
+namespace
+{
+
+struct GroupVt {
+    int (*bases_upload)(int, int, const void *, size_t, size_t, rt::BaseSet *);
+    int (*msm_windows)(const rt::BaseSet &, size_t, size_t, const void *, void *, int *, int *);
+    int (*msm_fold)(const void *, int, int, size_t, void *);
+    size_t (*window_point_bytes)();
+    int (*scalar_bits)();
+};
+#define GROUP_VT(name) {name##_bases_upload, name##_msm_windows, name##_msm_fold, name##_window_point_bytes, name##_scalar_bits}
+
+struct CurveVt {
+    GroupVt g[2]; // [0] = G1, [1] = G2
+    size_t fr_bytes, fq_bytes;
+    bool g2_is_fq2;
+    const GroupVt &grp(int group) const { return g[group == B200_G2 ? 1 : 0]; }
+    int scalar_bits() const { return g[0].scalar_bits(); }
+    size_t window_point_bytes(int group) const { return grp(group).window_point_bytes(); }
+};
+
+const CurveVt *vt(int curve)
+{
+    static const CurveVt tbl[3] = {
+        {{GROUP_VT(alt_bn128_g1), GROUP_VT(alt_bn128_g2)}, 32, 32, true},
+        {{GROUP_VT(bls12_377_g1), GROUP_VT(bls12_377_g2)}, 32, 48, true},
+        {{GROUP_VT(bw6_761_g1), GROUP_VT(bw6_761_g1)}, 48, 96, false},
+    };
+    if (curve < 0 || curve > 2) {
+        rt::set_error(B200_ERR_ARG, "unknown curve %d", curve);
+        return nullptr;
+    }
+    return &tbl[curve];
+}
+
+size_t group_bytes(const CurveVt *v, int group) { return 3 * v->fq_bytes * ((group == B200_G2 && v->g2_is_fq2) ? 2 : 1); }
+
+std::mutex g_mu;
+std::map<uint64_t, rt::BaseSet> g_sets;
+uint64_t g_next_handle = 1;
+
+rt::DevBuf g_scalars, g_windows, g_out;
+
+// The reference's zero(): (0, one, 0).
+void write_zero_point(int curve, int group, void *out)
+{
+    const CurveVt *v = vt(curve);
+    const size_t fq = v->fq_bytes;
+    const size_t coord = group_bytes(v, group) / 3;
+    memset(out, 0, 3 * coord);
+    uint32_t *y = reinterpret_cast<uint32_t *>(static_cast<uint8_t *>(out) + coord);
+    for (size_t i = 0; i < fq / 4; ++i) {
+        switch (curve) {
+        case B200_ALT_BN128: y[i] = alt_bn128_fq_params::one((int)i); break;
+        case B200_BLS12_377: y[i] = bls12_377_fq_params::one((int)i); break;
+        default: y[i] = bw6_761_fq_params::one((int)i); break;
+        }
+    }
+}
+
+int msm_resident_impl(const rt::BaseSet &bs, size_t first, size_t n, const void *scalars, int on_device,
+                      void *out, void *out_windows)
+{
+    const CurveVt *v = vt(bs.curve);
+    if (first + n > bs.n) {
+        return rt::set_error(B200_ERR_ARG, "range [%zu, %zu) exceeds the %zu resident bases", first, first + n, bs.n);
+    }
+    const int bits = v->scalar_bits();
+    if (n == 0) {
+        if (out) {
+            write_zero_point(bs.curve, bs.group, out);
+        }
+        if (out_windows) {
+            return rt::set_error(B200_ERR_ARG, "windows of an empty MSM are undefined");
+        }
+        return B200_OK;
+    }
+    (void)bits;
+    cudaStream_t s = rt::stream();
+    const void *sdev = scalars;
+    if (!on_device) {
+        if (g_scalars.reserve(n * v->fr_bytes)) {
+            return B200_ERR_CUDA;
+        }
+        B200_CUDA_CHECK(cudaMemcpyAsync(g_scalars.p, scalars, n * v->fr_bytes, cudaMemcpyHostToDevice, s));
+        sdev = g_scalars.p;
+    }
+    const size_t wbytes = v->window_point_bytes(bs.group);
+    if (g_windows.reserve(64 * wbytes * 2) || g_out.reserve(1024)) {
+        return B200_ERR_CUDA;
+    }
+    int W = 0, c = 0;
+    int rc = v->grp(bs.group).msm_windows(bs, first, n, sdev, g_windows.p, &W, &c);
+    if (rc) {
+        return rc;
+    }
+    if (out_windows) {
+        B200_CUDA_CHECK(cudaMemcpyAsync(out_windows, g_windows.p, (size_t)W * wbytes, cudaMemcpyDeviceToHost, s));
+    }
+    if (out) {
+        rc = v->grp(bs.group).msm_fold(g_windows.p, W, c, 1, g_out.p);
+        if (rc) {
+            return rc;
+        }
+        B200_CUDA_CHECK(cudaMemcpyAsync(out, g_out.p, group_bytes(v, bs.group), cudaMemcpyDeviceToHost, s));
+    }
+    B200_CUDA_CHECK(cudaStreamSynchronize(s));
+    return B200_OK;
+}
+
+void free_set(rt::BaseSet &bs)
+{
+    if (bs.pts) {
+        cudaFree(bs.pts);
+    }
+    if (bs.inf) {
+        cudaFree(bs.inf);
+    }
+    bs = rt::BaseSet();
+}
+
+template<int N> bool limbs_equal_one(const uint32_t *s, uint32_t (*one)(int))
+{
+    for (int i = 0; i < N; ++i) {
+        if (s[i] != one(i)) {
+            return false;
+        }
+    }
+    return true;
+}
+
+void scalar_stats(int curve, const void *scalars, size_t n, size_t *stats)
+{
+    const CurveVt *v = vt(curve);
+    const size_t nl = v->fr_bytes / 4;
+    uint32_t one[12];
+    for (size_t i = 0; i < nl; ++i) {
+        one[i] = curve == B200_ALT_BN128   ? alt_bn128_fr_params::one((int)i)
+                 : curve == B200_BLS12_377 ? bls12_377_fr_params::one((int)i)
+                                           : bw6_761_fr_params::one((int)i);
+    }
+    size_t zeros = 0, ones = 0;
+    const uint32_t *s = static_cast<const uint32_t *>(scalars);
+    for (size_t i = 0; i < n; ++i, s += nl) {
+        uint32_t orr = 0, diff = 0;
+        for (size_t j = 0; j < nl; ++j) {
+            orr |= s[j];
+            diff |= s[j] ^ one[j];
+        }
+        zeros += orr == 0;
+        ones += diff == 0;
+    }
+    stats[0] = zeros;
+    stats[1] = ones;
+    stats[2] = n - zeros - ones;
+}
+
+} // namespace
+
+extern "C" {
+
+size_t b200_sizeof_fr(int curve)
+{
+    const CurveVt *v = vt(curve);
+    return v ? v->fr_bytes : 0;
+}
+
+size_t b200_sizeof_group(int curve, int group)
+{
+    const CurveVt *v = vt(curve);
+    if (!v || (group != B200_G1 && group != B200_G2)) {
+        return 0;
+    }
+    return group_bytes(v, group);
+}
+
+int b200_bases_upload(int curve, int group, const void *bases, size_t base_stride, size_t n, b200_bases_t *handle)
+{
+    const CurveVt *v = vt(curve);
+    if (!v) {
+        return B200_ERR_ARG;
+    }
+    if ((group != B200_G1 && group != B200_G2) || !handle || (n && !bases)) {
+        return rt::set_error(B200_ERR_ARG, "bad group / null pointer");
+    }
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    rt::BaseSet bs;
+    const int rc = v->grp(group).bases_upload(curve, group, bases, base_stride, n, &bs);
+    if (rc) {
+        return rc;
+    }
+    *handle = g_next_handle++;
+    g_sets[*handle] = bs;
+    return B200_OK;
+}
+
+int b200_bases_free(b200_bases_t handle)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_sets.find(handle);
+    if (it == g_sets.end()) {
+        return rt::set_error(B200_ERR_HANDLE, "unknown base-set handle %llu", (unsigned long long)handle);
+    }
+    cudaStreamSynchronize(rt::stream());
+    free_set(it->second);
+    g_sets.erase(it);
+    return B200_OK;
+}
+
+size_t b200_bases_size(b200_bases_t handle)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_sets.find(handle);
+    return it == g_sets.end() ? 0 : it->second.n;
+}
+
+int b200_msm_resident(b200_bases_t handle, size_t first, size_t n, const void *scalars, int scalars_on_device,
+                      void *out)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_sets.find(handle);
+    if (it == g_sets.end()) {
+        return rt::set_error(B200_ERR_HANDLE, "unknown base-set handle %llu", (unsigned long long)handle);
+    }
+    if (!out || (n && !scalars)) {
+        return rt::set_error(B200_ERR_ARG, "null pointer");
+    }
+    return msm_resident_impl(it->second, first, n, scalars, scalars_on_device, out, nullptr);
+}
+
+int b200_msm_num_windows(int curve, size_t n)
+{
+    const CurveVt *v = vt(curve);
+    if (!v) {
+        return B200_ERR_ARG;
+    }
+    return msm::make_geometry(n, v->scalar_bits()).W;
+}
+
+size_t b200_msm_window_bytes(int curve, int group)
+{
+    const CurveVt *v = vt(curve);
+    return v ? v->window_point_bytes(group) : 0;
+}
+
+int b200_msm_resident_windows(b200_bases_t handle, size_t first, size_t n, const void *scalars,
+                              int scalars_on_device, void *out_windows)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_sets.find(handle);
+    if (it == g_sets.end()) {
+        return rt::set_error(B200_ERR_HANDLE, "unknown base-set handle %llu", (unsigned long long)handle);
+    }
+    if (!out_windows || !scalars || n == 0) {
+        return rt::set_error(B200_ERR_ARG, "null pointer or empty range");
+    }
+    return msm_resident_impl(it->second, first, n, scalars, scalars_on_device, nullptr, out_windows);
+}
+
+int b200_msm_fold_windows(int curve, int group, size_t n_per_shard, const void *windows, size_t num_shards, void *out)
+{
+    const CurveVt *v = vt(curve);
+    if (!v) {
+        return B200_ERR_ARG;
+    }
+    if (!windows || !out || num_shards == 0 || (group != B200_G1 && group != B200_G2)) {
+        return rt::set_error(B200_ERR_ARG, "bad argument");
+    }
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    const msm::Geometry geo = msm::make_geometry(n_per_shard, v->scalar_bits());
+    const int W = geo.W, c = geo.c;
+    const size_t bytes = (size_t)W * num_shards * v->window_point_bytes(group);
+    cudaStream_t s = rt::stream();
+    if (g_windows.reserve(bytes) || g_out.reserve(1024)) {
+        return B200_ERR_CUDA;
+    }
+    B200_CUDA_CHECK(cudaMemcpyAsync(g_windows.p, windows, bytes, cudaMemcpyHostToDevice, s));
+    const int rc = v->grp(group).msm_fold(g_windows.p, W, c, num_shards, g_out.p);
+    if (rc) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaMemcpyAsync(out, g_out.p, group_bytes(v, group), cudaMemcpyDeviceToHost, s));
+    B200_CUDA_CHECK(cudaStreamSynchronize(s));
+    return B200_OK;
+}
+
+int b200_msm(int curve, int group, const void *bases, size_t base_stride, size_t n, const void *scalars, void *out)
+{
+    const CurveVt *v = vt(curve);
+    if (!v) {
+        return B200_ERR_ARG;
+    }
+    if ((group != B200_G1 && group != B200_G2) || !out || (n && (!bases || !scalars))) {
+        return rt::set_error(B200_ERR_ARG, "bad group / null pointer");
+    }
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    if (n == 0) {
+        write_zero_point(curve, group, out);
+        return B200_OK;
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    rt::BaseSet bs;
+    int rc = v->grp(group).bases_upload(curve, group, bases, base_stride, n, &bs);
+    if (rc) {
+        return rc;
+    }
+    rc = msm_resident_impl(bs, 0, n, scalars, 0, out, nullptr);
+    cudaStreamSynchronize(rt::stream());
+    free_set(bs);
+    return rc;
+}
+
+int b200_msm_filter_one_zero(int curve, int group, const void *bases, size_t base_stride, size_t n,
+                             const void *scalars, void *out, size_t *stats)
+{
+    if (stats && vt(curve) && scalars) {
+        scalar_stats(curve, scalars, n, stats);
+    }
+    return b200_msm(curve, group, bases, base_stride, n, scalars, out);
+}
+
+int b200_kc_msm(int curve, const size_t *indices, const void *values, size_t nnz, size_t min_idx, size_t max_idx,
+                const void *scalars, size_t num_scalars, void *out_g2, void *out_g1, size_t *stats)
+{
+    const CurveVt *v = vt(curve);
+    if (!v) {
+        return B200_ERR_ARG;
+    }
+    if (!out_g2 || !out_g1 || (nnz && (!indices || !values)) || max_idx < min_idx ||
+        max_idx - min_idx > num_scalars || (num_scalars && !scalars)) {
+        return rt::set_error(B200_ERR_ARG, "bad argument");
+    }
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    // kc_multiexp.tcc:40-44 / :63: entries with min_idx <= index < max_idx
+    const size_t *lo = std::lower_bound(indices, indices + nnz, min_idx);
+    const size_t *hi = std::lower_bound(lo, indices + nnz, max_idx);
+    const size_t first = (size_t)(lo - indices), cnt = (size_t)(hi - lo);
+    const size_t g2b = group_bytes(v, B200_G2), g1b = group_bytes(v, B200_G1), stride = g2b + g1b;
+    std::vector<uint8_t> gathered(cnt * v->fr_bytes);
+    const uint8_t *sc = static_cast<const uint8_t *>(scalars);
+    for (size_t k = 0; k < cnt; ++k) {
+        memcpy(gathered.data() + k * v->fr_bytes, sc + (indices[first + k] - min_idx) * v->fr_bytes, v->fr_bytes);
+    }
+    if (stats) {
+        scalar_stats(curve, gathered.data(), cnt, stats);
+    }
+    const uint8_t *vals = static_cast<const uint8_t *>(values) + first * stride;
+    int rc = b200_msm(curve, B200_G2, vals, stride, cnt, gathered.data(), out_g2);
+    if (rc) {
+        return rc;
+    }
+    return b200_msm(curve, B200_G1, vals + g2b, stride, cnt, gathered.data(), out_g1);
+}
+
+} // extern "C"

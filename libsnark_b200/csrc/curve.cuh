@@ -81,6 +81,20 @@ template<class F> HD void dbl(XYZZ<F> &a)
     a.zzz = w * a.zzz;
 }
 
+#if defined(__CUDACC__)
+template<class F> __device__ __noinline__ void dbl_affine_outlined(XYZZ<F> &r, const Affine<F> &p) { r = dbl_affine(p); }
+#endif
+template<class F> HD XYZZ<F> dbl_affine_cold(const Affine<F> &p)
+{
+#if defined(__CUDA_ARCH__)
+    XYZZ<F> r;
+    dbl_affine_outlined(r, p);
+    return r;
+#else
+    return dbl_affine(p);
+#endif
+}
+
 // acc += p (p affine, never infinity)   — EFD madd-2008-s.
 // Counterpart of libff mixed_add (alt_bn128_g1.cpp:208-283).
 template<class F> HD void madd(XYZZ<F> &a, const Affine<F> &p)
@@ -95,7 +109,7 @@ template<class F> HD void madd(XYZZ<F> &a, const Affine<F> &p)
     const F rd = s2 - a.y;
     if (pd.is_zero()) {
         if (rd.is_zero()) {
-            a = dbl_affine(p);
+            a = dbl_affine_cold(p); // rare: out of line, keeps the hot loop small
         } else {
             a = XYZZ<F>::inf();
         }
@@ -143,6 +157,29 @@ template<class F> HD void add(XYZZ<F> &a, const XYZZ<F> &b)
     a.x = x3;
     a.zz = a.zz * b.zz * pp;
     a.zzz = a.zzz * b.zzz * ppp;
+}
+
+// Out-of-line copies for kernels where the group law is not the inner loop (bucket
+// reduction, window sums, fold): one instance per translation unit instead of one per call site.
+#if defined(__CUDACC__)
+template<class F> __device__ __noinline__ void add_outlined(XYZZ<F> &a, const XYZZ<F> &b) { add(a, b); }
+template<class F> __device__ __noinline__ void dbl_outlined(XYZZ<F> &a) { dbl(a); }
+#endif
+template<class F> HD void add_cold(XYZZ<F> &a, const XYZZ<F> &b)
+{
+#if defined(__CUDA_ARCH__)
+    add_outlined(a, b);
+#else
+    add(a, b);
+#endif
+}
+template<class F> HD void dbl_cold(XYZZ<F> &a)
+{
+#if defined(__CUDA_ARCH__)
+    dbl_outlined(a);
+#else
+    dbl(a);
+#endif
 }
 
 template<class F> HD XYZZ<F> neg(const XYZZ<F> &a)

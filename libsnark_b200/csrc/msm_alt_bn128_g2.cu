@@ -1,0 +1,7 @@
+// msm_alt_bn128_g2.cu — instantiates the MSM pipeline (msm.cuh / msm_host.cuh) for alt_bn128 G2.
+#include "msm_host.cuh"
+
+namespace b200
+{
+B200_DEFINE_GROUP_ENTRY(alt_bn128_g2, CURVE_ALT_BN128, GROUP_G2)
+} // namespace b200

@@ -1,0 +1,173 @@
+// msm_host.cuh — host-side driver of the MSM pipeline in msm.cuh (stream-ordered launches,
+// no host synchronisation between the stages; the only device->host transfer is the result).
+#pragma once
+#include "msm.cuh"
+#include "runtime.hpp"
+
+namespace b200
+{
+namespace msm
+{
+
+struct Workspace {
+    rt::DevBuf t, counts, offsets, cursor, task_off, tile_sums, entries, tasks, partial, chunk_out, staging, any_inf;
+};
+inline Workspace &workspace()
+{
+    static Workspace ws;
+    return ws;
+}
+
+inline unsigned grid_for(size_t n, unsigned block) { return (unsigned)((n + block - 1) / block); }
+
+template<class F>
+int bases_upload(int curve, int group, const void *host, size_t stride, size_t n, rt::BaseSet *out)
+{
+    if (stride < sizeof(RefPoint<F>) || stride % 16 != 0) {
+        return rt::set_error(B200_ERR_ARG, "base stride %zu invalid for a %zu-byte point", stride, sizeof(RefPoint<F>));
+    }
+    Workspace &ws = workspace();
+    cudaStream_t s = rt::stream();
+    const size_t bytes = n ? (n - 1) * stride + sizeof(RefPoint<F>) : 0;
+    void *pts = nullptr;
+    uint8_t *inf = nullptr;
+    if (n) {
+        if (ws.staging.reserve(bytes) || ws.any_inf.reserve(16)) {
+            return B200_ERR_CUDA;
+        }
+        B200_CUDA_CHECK(cudaMalloc(&pts, n * sizeof(Affine<F>)));
+        B200_CUDA_CHECK(cudaMalloc((void **)&inf, n));
+        B200_CUDA_CHECK(cudaMemcpyAsync(ws.staging.p, host, bytes, cudaMemcpyHostToDevice, s));
+        B200_CUDA_CHECK(cudaMemsetAsync(ws.any_inf.p, 0, 4, s));
+        k_convert_bases<F><<<grid_for(n, 256), 256, 0, s>>>(
+            ws.staging.as<uint8_t>(), stride, n, static_cast<Affine<F> *>(pts), inf, ws.any_inf.as<uint32_t>());
+        B200_LAUNCH_CHECK();
+        uint32_t any = 0;
+        B200_CUDA_CHECK(cudaMemcpyAsync(&any, ws.any_inf.p, 4, cudaMemcpyDeviceToHost, s));
+        B200_CUDA_CHECK(cudaStreamSynchronize(s));
+        if (!any) {
+            cudaFree(inf);
+            inf = nullptr;
+        }
+    }
+    out->curve = curve;
+    out->group = group;
+    out->n = n;
+    out->point_bytes = sizeof(Affine<F>);
+    out->pts = pts;
+    out->inf = inf;
+    return B200_OK;
+}
+
+// Runs stages 1-7; leaves W window sums (XYZZ<F>) at windows_dev.
+template<class Fr, class F>
+int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scalars_dev, void *windows_dev, int *W_out, int *c_out)
+{
+    constexpr int NL = Fr::N;
+    const Geometry g = make_geometry(n, Fr::params::BITS);
+    *W_out = g.W;
+    *c_out = g.c;
+    Workspace &ws = workspace();
+    cudaStream_t s = rt::stream();
+    rt::MsmTiming &tm = rt::msm_timing();
+
+    const size_t max_entries = (size_t)g.W * n;
+    const size_t max_tasks = (size_t)g.NB + max_entries / SEG + 1;
+    const uint32_t ntiles = grid_for(g.NB, SCAN_TILE);
+    const size_t nchunks = (size_t)g.W * g.cpw;
+    if (max_entries >= 0x7fffffffull || max_tasks >= 0xffffffffull) {
+        return rt::set_error(B200_ERR_ARG, "MSM of %zu points exceeds the 32-bit entry index", n);
+    }
+    if (ws.t.reserve(n * NL * 4 + 16) || ws.counts.reserve(((size_t)g.NB + 1) * 4) ||
+        ws.offsets.reserve(((size_t)g.NB + 1) * 4) || ws.cursor.reserve(((size_t)g.NB + 1) * 4) ||
+        ws.task_off.reserve(((size_t)g.NB + 1) * 4) || ws.tile_sums.reserve((size_t)ntiles * 8 + 8) ||
+        ws.entries.reserve(max_entries * 4 + 16) || ws.tasks.reserve(max_tasks * sizeof(Task)) ||
+        ws.partial.reserve(max_tasks * sizeof(XYZZ<F>)) || ws.chunk_out.reserve(nchunks * sizeof(XYZZ<F>))) {
+        return B200_ERR_CUDA;
+    }
+    const Affine<F> *bases = static_cast<const Affine<F> *>(bs.pts) + first;
+    const uint8_t *inf = bs.inf ? bs.inf + first : nullptr;
+    uint32_t *t = ws.t.as<uint32_t>();
+    uint32_t *counts = ws.counts.as<uint32_t>();
+    uint32_t *offsets = ws.offsets.as<uint32_t>();
+    uint32_t *cursor = ws.cursor.as<uint32_t>();
+    uint32_t *task_off = ws.task_off.as<uint32_t>();
+    uint2 *tile_sums = ws.tile_sums.as<uint2>();
+    uint32_t *entries = ws.entries.as<uint32_t>();
+    Task *tasks = ws.tasks.as<Task>();
+    XYZZ<F> *partial = ws.partial.as<XYZZ<F>>();
+    XYZZ<F> *chunk_out = ws.chunk_out.as<XYZZ<F>>();
+
+    B200_CUDA_CHECK(cudaEventRecord(tm.ev[0], s));
+    // 1-4: digits and counting sort
+    B200_CUDA_CHECK(cudaMemsetAsync(counts, 0, ((size_t)g.NB + 1) * 4, s));
+    const Limbs<NL> K = make_offset_constant<NL>(g);
+    k_prepare<Fr><<<grid_for(n, 256), 256, 0, s>>>(static_cast<const Fr *>(scalars_dev), t, n, K, inf);
+    B200_LAUNCH_CHECK();
+    k_histogram<<<grid_for(n, 256), 256, 0, s>>>(t, NL, g, counts);
+    B200_LAUNCH_CHECK();
+    k_scan_tiles<<<ntiles, SCAN_THREADS, 0, s>>>(counts, g.NB, tile_sums);
+    B200_LAUNCH_CHECK();
+    k_scan_tile_sums<<<1, SCAN_THREADS, 0, s>>>(tile_sums, ntiles);
+    B200_LAUNCH_CHECK();
+    k_scan_finish<<<ntiles, SCAN_THREADS, 0, s>>>(counts, g.NB, tile_sums, offsets, cursor, task_off);
+    B200_LAUNCH_CHECK();
+    k_scatter<<<grid_for(n, 256), 256, 0, s>>>(t, NL, g, cursor, entries);
+    B200_LAUNCH_CHECK();
+    k_build_tasks<<<grid_for(g.NB, 256), 256, 0, s>>>(counts, offsets, task_off, g.NB, tasks);
+    B200_LAUNCH_CHECK();
+    B200_CUDA_CHECK(cudaEventRecord(tm.ev[1], s));
+    // 5: bucket accumulation (grid sized for the task upper bound; surplus CTAs exit at once)
+    k_accumulate<F><<<grid_for(max_tasks, ACC_THREADS), ACC_THREADS, 0, s>>>(
+        tasks, task_off + g.NB, entries, bases, partial);
+    B200_LAUNCH_CHECK();
+    B200_CUDA_CHECK(cudaEventRecord(tm.ev[2], s));
+    // 6-7: bucket reduction
+    k_reduce_chunks<F><<<grid_for(nchunks, 128), 128, 0, s>>>(g, task_off, partial, chunk_out);
+    B200_LAUNCH_CHECK();
+    const size_t wsum_smem = (size_t)WSUM_THREADS * sizeof(XYZZ<F>);
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200_CUDA_CHECK(cudaFuncSetAttribute(
+            k_window_sum<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsum_smem));
+        attr_set = true;
+    }
+    k_window_sum<F><<<g.W, WSUM_THREADS, wsum_smem, s>>>(g, chunk_out, static_cast<XYZZ<F> *>(windows_dev));
+    B200_LAUNCH_CHECK();
+    B200_CUDA_CHECK(cudaEventRecord(tm.ev[3], s));
+    return B200_OK;
+}
+
+template<class F> int msm_fold(const void *windows_dev, int W, int c, size_t shards, void *out_dev)
+{
+    cudaStream_t s = rt::stream();
+    k_fold<F><<<1, 32, 0, s>>>(static_cast<const XYZZ<F> *>(windows_dev), W, c, shards, static_cast<RefPoint<F> *>(out_dev));
+    B200_LAUNCH_CHECK();
+    rt::MsmTiming &tm = rt::msm_timing();
+    B200_CUDA_CHECK(cudaEventRecord(tm.ev[4], s));
+    tm.valid = true;
+    return B200_OK;
+}
+
+} // namespace msm
+
+#define B200_DEFINE_GROUP_ENTRY(name, CURVE, GROUP)                                                            \
+    int name##_bases_upload(int curve, int group, const void *host, size_t stride, size_t n,                  \
+                            rt::BaseSet *out)                                                                  \
+    {                                                                                                          \
+        return msm::bases_upload<group_traits<CURVE, GROUP>::F>(curve, group, host, stride, n, out);           \
+    }                                                                                                          \
+    int name##_msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scalars_dev,            \
+                           void *windows_dev, int *W, int *c)                                                  \
+    {                                                                                                          \
+        return msm::msm_windows<group_traits<CURVE, GROUP>::Fr, group_traits<CURVE, GROUP>::F>(                \
+            bs, first, n, scalars_dev, windows_dev, W, c);                                                     \
+    }                                                                                                          \
+    int name##_msm_fold(const void *windows_dev, int W, int c, size_t shards, void *out_dev)                  \
+    {                                                                                                          \
+        return msm::msm_fold<group_traits<CURVE, GROUP>::F>(windows_dev, W, c, shards, out_dev);               \
+    }                                                                                                          \
+    size_t name##_window_point_bytes() { return sizeof(XYZZ<group_traits<CURVE, GROUP>::F>); }                 \
+    int name##_scalar_bits() { return group_traits<CURVE, GROUP>::Fr::params::BITS; }
+
+} // namespace b200

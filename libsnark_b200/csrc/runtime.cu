@@ -1,0 +1,185 @@
+// runtime.cu — device binding, stream, error string, workspace buffers, device-memory C-ABI.
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+
+#include "runtime.hpp"
+
+namespace b200
+{
+namespace rt
+{
+
+namespace
+{
+thread_local char g_err[512] = "";
+int g_device = -1;
+cudaStream_t g_stream = nullptr;
+std::atomic<uint64_t> g_launches{0};
+MsmTiming g_timing;
+} // namespace
+
+int set_error(int code, const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+const char *last_error() { return g_err; }
+
+static int do_init(int device)
+{
+    if (g_device == device && g_stream) {
+        return B200_OK;
+    }
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        return set_error(B200_ERR_CUDA, "no CUDA device: %s (this library has no CPU fallback)",
+                         e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    }
+    if (device < 0 || device >= count) {
+        return set_error(B200_ERR_ARG, "device %d out of range [0, %d)", device, count);
+    }
+    B200_CUDA_CHECK(cudaSetDevice(device));
+    if (!g_stream) {
+        B200_CUDA_CHECK(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < 5; ++i) {
+            B200_CUDA_CHECK(cudaEventCreate(&g_timing.ev[i]));
+        }
+    }
+    g_device = device;
+    return B200_OK;
+}
+
+bool ensure_init() { return (g_stream && g_device >= 0) || do_init(0) == B200_OK; }
+cudaStream_t stream() { return g_stream; }
+void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+MsmTiming &msm_timing() { return g_timing; }
+
+int DevBuf::reserve(size_t bytes)
+{
+    if (bytes <= cap) {
+        return B200_OK;
+    }
+    if (p) {
+        // stream-ordered users of the old buffer must be done before it is freed
+        cudaStreamSynchronize(g_stream);
+        cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    const size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) {
+        p = nullptr;
+        return set_error(B200_ERR_CUDA, "cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e));
+    }
+    cap = want;
+    return B200_OK;
+}
+void DevBuf::release()
+{
+    if (p) {
+        cudaFree(p);
+    }
+    p = nullptr;
+    cap = 0;
+}
+
+} // namespace rt
+} // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+int b200_version(void) { return 100; }
+
+int b200_init(int device) { return rt::do_init(device); }
+
+int b200_device_count(void)
+{
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess) {
+        return 0;
+    }
+    return count;
+}
+
+const char *b200_last_error(void) { return rt::last_error(); }
+
+int b200_dev_alloc(size_t bytes, void **dev_ptr)
+{
+    if (!dev_ptr) {
+        return rt::set_error(B200_ERR_ARG, "null dev_ptr");
+    }
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    B200_CUDA_CHECK(cudaMalloc(dev_ptr, bytes ? bytes : 16));
+    return B200_OK;
+}
+
+int b200_dev_free(void *dev_ptr)
+{
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
+    B200_CUDA_CHECK(cudaFree(dev_ptr));
+    return B200_OK;
+}
+
+int b200_memcpy_h2d(void *dev_dst, const void *host_src, size_t bytes)
+{
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    B200_CUDA_CHECK(cudaMemcpyAsync(dev_dst, host_src, bytes, cudaMemcpyHostToDevice, rt::stream()));
+    B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
+    return B200_OK;
+}
+
+int b200_memcpy_d2h(void *host_dst, const void *dev_src, size_t bytes)
+{
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    B200_CUDA_CHECK(cudaMemcpyAsync(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost, rt::stream()));
+    B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
+    return B200_OK;
+}
+
+int b200_sync(void)
+{
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
+    return B200_OK;
+}
+
+uint64_t b200_launch_count(void) { return rt::g_launches.load(); }
+
+int b200_last_msm_timing(double *ms5)
+{
+    rt::MsmTiming &tm = rt::msm_timing();
+    if (!ms5 || !tm.valid) {
+        return rt::set_error(B200_ERR_ARG, "no MSM has run yet");
+    }
+    B200_CUDA_CHECK(cudaEventSynchronize(tm.ev[4]));
+    for (int i = 0; i < 4; ++i) {
+        float ms = 0;
+        B200_CUDA_CHECK(cudaEventElapsedTime(&ms, tm.ev[i], tm.ev[i + 1]));
+        ms5[i] = ms;
+    }
+    float tot = 0;
+    B200_CUDA_CHECK(cudaEventElapsedTime(&tot, tm.ev[0], tm.ev[4]));
+    ms5[4] = tot;
+    return B200_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,85 @@
+// runtime.hpp — process-wide state of the library (one process per GPU): the bound device,
+// the compute stream, the last-error string, the launch counter and grow-only device buffers.
+#pragma once
+#include <cstdarg>
+#include <cstddef>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/libsnark_b200.h"
+
+namespace b200
+{
+namespace rt
+{
+
+int set_error(int code, const char *fmt, ...);
+const char *last_error();
+bool ensure_init();         // true when a device is bound (b200_init called or lazily device 0)
+cudaStream_t stream();      // the library's compute stream
+void count_launch(int n = 1);
+
+#define B200_CUDA_CHECK(expr)                                                                      \
+    do {                                                                                           \
+        cudaError_t e__ = (expr);                                                                  \
+        if (e__ != cudaSuccess) {                                                                  \
+            return b200::rt::set_error(B200_ERR_CUDA, "%s failed: %s (%s:%d)", #expr,             \
+                                       cudaGetErrorString(e__), __FILE__, __LINE__);               \
+        }                                                                                          \
+    } while (0)
+
+#define B200_LAUNCH_CHECK()                                                                        \
+    do {                                                                                           \
+        b200::rt::count_launch();                                                                  \
+        cudaError_t e__ = cudaGetLastError();                                                      \
+        if (e__ != cudaSuccess) {                                                                  \
+            return b200::rt::set_error(B200_ERR_CUDA, "kernel launch failed: %s (%s:%d)",          \
+                                       cudaGetErrorString(e__), __FILE__, __LINE__);               \
+        }                                                                                          \
+    } while (0)
+
+// Grow-only device buffer (cudaMalloc is a synchronising, millisecond-scale call: workspaces
+// are kept between calls).
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes);
+    void release();
+    template<class T> T *as() { return static_cast<T *>(p); }
+};
+
+// A device-resident base set (proving-key query) in device affine form.
+struct BaseSet {
+    int curve = -1, group = 0;
+    size_t n = 0;
+    size_t point_bytes = 0; // sizeof(Affine<F>)
+    void *pts = nullptr;    // Affine<F>[n]
+    uint8_t *inf = nullptr; // n flags, or nullptr when no base is the point at infinity
+};
+
+struct MsmTiming {
+    cudaEvent_t ev[5];
+    bool valid = false;
+};
+MsmTiming &msm_timing();
+
+} // namespace rt
+
+// Implemented once per (curve, group) in msm_<curve>_<group>.cu. bw6_761's G2 is over Fq
+// like its G1 (bw6_761_g2.hpp), so both groups share the g1 instance.
+#define B200_DECLARE_GROUP_ENTRY(name)                                                             \
+    int name##_bases_upload(int curve, int group, const void *host, size_t stride, size_t n,      \
+                            rt::BaseSet *out);                                                     \
+    int name##_msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scalars_dev, \
+                           void *windows_dev, int *W, int *c);                                     \
+    int name##_msm_fold(const void *windows_dev, int W, int c, size_t shards, void *out_dev);     \
+    size_t name##_window_point_bytes();                                                            \
+    int name##_scalar_bits();
+
+B200_DECLARE_GROUP_ENTRY(alt_bn128_g1)
+B200_DECLARE_GROUP_ENTRY(alt_bn128_g2)
+B200_DECLARE_GROUP_ENTRY(bls12_377_g1)
+B200_DECLARE_GROUP_ENTRY(bls12_377_g2)
+B200_DECLARE_GROUP_ENTRY(bw6_761_g1)
+
+} // namespace b200
