@@ -1,2 +1,438 @@
+// ntt.cu — host driver and C-ABI of the NTT operators (ntt.cuh): cached per-size domains
+// (twiddle and coset tables in HBM), pass planning, the evaluation_domain entry points and
+// the fused witness-map chain of r1cs_to_qap_witness_map (r1cs_to_qap.tcc:252-330).
+#include <cstring>
+#include <map>
+#include <memory>
+#include <mutex>
+
+#include "ntt.cuh"
 #include "runtime.hpp"
-extern "C" int b200_ntt(int, int, void *, size_t, const void *) { return b200::rt::set_error(B200_ERR_ARG, "ntt: not built yet"); }
+
+using namespace b200;
+
+namespace
+{
+
+constexpr int MAX_DEG = 8;
+
+inline unsigned grid_for(uint64_t n, unsigned block) { return (unsigned)((n + block - 1) / block); }
+
+template<class Fr> struct Domain {
+    int lgn = 0;
+    rt::DevBuf twiddles, consts, pows, g_dev;
+    rt::DevBuf gpow, ginv_minv, gpow_minv; // coset tables for the generator in g_host
+    uint32_t g_host[Fr::N];
+    bool has_g = false;
+    const Fr *c(int i) { return consts.template as<Fr>() + i; }
+    const Fr *pows_w() { return pows.template as<Fr>(); }
+    const Fr *pows_g() { return pows.template as<Fr>() + 64; }
+    const Fr *pows_gi() { return pows.template as<Fr>() + 128; }
+};
+
+template<class Fr> std::map<int, std::unique_ptr<Domain<Fr>>> &domains()
+{
+    static std::map<int, std::unique_ptr<Domain<Fr>>> m;
+    return m;
+}
+
+// (Re)computes the domain constants for generator g (host pointer to Fr::N u32) and drops
+// stale coset tables.
+template<class Fr> int domain_set_generator(Domain<Fr> &d, const uint32_t *g)
+{
+    cudaStream_t s = rt::stream();
+    if (d.consts.reserve(8 * sizeof(Fr)) || d.pows.reserve(192 * sizeof(Fr)) || d.g_dev.reserve(sizeof(Fr))) {
+        return B200_ERR_CUDA;
+    }
+    memcpy(d.g_host, g, sizeof(d.g_host));
+    B200_CUDA_CHECK(cudaMemcpyAsync(d.g_dev.p, d.g_host, sizeof(Fr), cudaMemcpyHostToDevice, s));
+    ntt::k_domain_consts<Fr><<<1, 32, 0, s>>>(d.lgn, d.g_dev.template as<Fr>(), d.consts.template as<Fr>(), d.pows.template as<Fr>(),
+                                              d.pows.template as<Fr>() + 64, d.pows.template as<Fr>() + 128);
+    B200_LAUNCH_CHECK();
+    d.gpow.release();
+    d.ginv_minv.release();
+    d.gpow_minv.release();
+    d.has_g = true;
+    return B200_OK;
+}
+
+template<class Fr> int get_domain(int lgn, const uint32_t *g, Domain<Fr> **out)
+{
+    auto &m = domains<Fr>();
+    auto it = m.find(lgn);
+    if (it == m.end()) {
+        std::unique_ptr<Domain<Fr>> d(new Domain<Fr>());
+        d->lgn = lgn;
+        uint32_t gen[Fr::N];
+        for (int i = 0; i < Fr::N; ++i) {
+            gen[i] = Fr::params::generator(i);
+        }
+        int rc = domain_set_generator(*d, g ? g : gen);
+        if (rc) {
+            return rc;
+        }
+        const uint64_t half = 1ull << (lgn - 1);
+        if (d->twiddles.reserve(half * sizeof(Fr))) {
+            return B200_ERR_CUDA;
+        }
+        ntt::k_pow_table<Fr><<<grid_for(half, 256), 256, 0, rt::stream()>>>(
+            half, d->pows_w(), lgn - 1, nullptr, d->twiddles.template as<Fr>());
+        B200_LAUNCH_CHECK();
+        it = m.emplace(lgn, std::move(d)).first;
+    } else if (g && memcmp(g, it->second->g_host, sizeof(uint32_t) * Fr::N) != 0) {
+        int rc = domain_set_generator(*it->second, g);
+        if (rc) {
+            return rc;
+        }
+    }
+    *out = it->second.get();
+    return B200_OK;
+}
+
+enum CosetTable { T_GPOW, T_GINV_MINV, T_GPOW_MINV };
+template<class Fr> int coset_table(Domain<Fr> &d, CosetTable which, const Fr **out)
+{
+    rt::DevBuf &buf = which == T_GPOW ? d.gpow : which == T_GINV_MINV ? d.ginv_minv : d.gpow_minv;
+    const uint64_t n = 1ull << d.lgn;
+    if (!buf.p) {
+        if (buf.reserve(n * sizeof(Fr))) {
+            return B200_ERR_CUDA;
+        }
+        const Fr *pows = which == T_GINV_MINV ? d.pows_gi() : d.pows_g();
+        const Fr *scale = which == T_GPOW ? nullptr : d.c(1);
+        ntt::k_pow_table<Fr><<<grid_for(n, 256), 256, 0, rt::stream()>>>(n, pows, d.lgn, scale, buf.template as<Fr>());
+        B200_LAUNCH_CHECK();
+    }
+    *out = buf.template as<Fr>();
+    return B200_OK;
+}
+
+// Runs one transform. Passes ping-pong between `in` and `tmp`; the last pass writes `out`.
+// out may equal in (then an odd pass count ends with one device copy from tmp).
+template<class Fr>
+int run_transform(Domain<Fr> &d, int inverse, Fr *in, Fr *tmp, Fr *out, const Fr *pre_table, const Fr *post_table,
+                  const Fr *post_const)
+{
+    const int lgn = d.lgn;
+    const int P = (lgn + MAX_DEG - 1) / MAX_DEG;
+    cudaStream_t s = rt::stream();
+    Fr *cur = in;
+    int lgp = 0;
+    for (int i = 0; i < P; ++i) {
+        ntt::PassParams pp;
+        pp.lgn = lgn;
+        pp.lgp = lgp;
+        pp.deg = lgn / P + (i < lgn % P ? 1 : 0);
+        pp.lgc = lgn - pp.deg < 3 ? lgn - pp.deg : 3;
+        pp.inverse = inverse;
+        pp.nsteps = 0;
+        for (int rem = pp.deg; rem > 0;) {
+            const int q = rem == 4 ? 2 : (rem >= 3 ? 3 : rem);
+            pp.step_q[pp.nsteps++] = q;
+            rem -= q;
+        }
+        const bool last = (i == P - 1);
+        Fr *dst = last ? out : (cur == in ? tmp : in);
+        bool copy_back = false;
+        if (dst == cur) { // in-place request with an odd number of passes
+            dst = tmp;
+            copy_back = true;
+        }
+        const uint64_t tile_elems = 1ull << (pp.deg + pp.lgc);
+        unsigned threads = (unsigned)(tile_elems / 8);
+        if (threads < 32) {
+            threads = 32;
+        }
+        const unsigned blocks = (unsigned)(1ull << (lgn - pp.deg - pp.lgc));
+        const size_t smem = (size_t)(Fr::N / 4) * 16 * ((size_t)1 << pp.deg) * ((1u << pp.lgc) + 1);
+        static size_t smem_attr = 0;
+        if (smem > smem_attr) {
+            B200_CUDA_CHECK(cudaFuncSetAttribute(ntt::k_ntt_pass<Fr>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 (int)(smem > 48 * 1024 ? smem : 48 * 1024)));
+            smem_attr = smem;
+        }
+        ntt::k_ntt_pass<Fr><<<blocks, threads, smem, s>>>(pp, cur, dst, d.twiddles.template as<Fr>(),
+                                                        i == 0 ? pre_table : nullptr, last ? post_table : nullptr,
+                                                        last ? post_const : nullptr);
+        B200_LAUNCH_CHECK();
+        if (copy_back) {
+            B200_CUDA_CHECK(cudaMemcpyAsync(out, tmp, sizeof(Fr) << lgn, cudaMemcpyDeviceToDevice, s));
+        }
+        cur = dst;
+        lgp += pp.deg;
+    }
+    return B200_OK;
+}
+
+int log2_exact(size_t m)
+{
+    if (m < 2 || (m & (m - 1))) {
+        return -1;
+    }
+    int k = 0;
+    while ((1ull << k) < m) {
+        ++k;
+    }
+    return k;
+}
+
+rt::DevBuf g_bufA, g_bufB, g_bufC, g_bufS, g_bufH;
+std::mutex g_mu;
+
+template<class Fr> int ntt_op_dev(int op, Fr *data, Fr *tmp, Fr *out, size_t m, const void *g)
+{
+    const int lgn = log2_exact(m);
+    if (lgn < 0 || lgn > Fr::params::S) {
+        // get_evaluation_domain / basic_radix2_domain ctor (basic_radix2_domain.tcc:25-52)
+        return rt::set_error(B200_ERR_DOMAIN, "basic_radix2_domain: size %zu is not a power of two in [2, 2^%d]", m,
+                             Fr::params::S);
+    }
+    const bool coset = (op == B200_COSET_FFT || op == B200_ICOSET_FFT);
+    if (coset && !g) {
+        return rt::set_error(B200_ERR_ARG, "coset transform needs a generator");
+    }
+    Domain<Fr> *d = nullptr;
+    int rc = get_domain<Fr>(lgn, coset ? static_cast<const uint32_t *>(g) : nullptr, &d);
+    if (rc) {
+        return rc;
+    }
+    const Fr *tbl = nullptr;
+    switch (op) {
+    case B200_FFT: return run_transform<Fr>(*d, 0, data, tmp, out, nullptr, nullptr, nullptr);
+    case B200_IFFT: return run_transform<Fr>(*d, 1, data, tmp, out, nullptr, nullptr, d->c(1));
+    case B200_COSET_FFT:
+        if ((rc = coset_table(*d, T_GPOW, &tbl))) {
+            return rc;
+        }
+        return run_transform<Fr>(*d, 0, data, tmp, out, tbl, nullptr, nullptr);
+    case B200_ICOSET_FFT:
+        if ((rc = coset_table(*d, T_GINV_MINV, &tbl))) {
+            return rc;
+        }
+        return run_transform<Fr>(*d, 1, data, tmp, out, nullptr, tbl, nullptr);
+    }
+    return rt::set_error(B200_ERR_ARG, "unknown NTT op %d", op);
+}
+
+template<class Fr> int ntt_host(int op, void *data, size_t m, const void *g)
+{
+    const size_t bytes = m * sizeof(Fr);
+    if (g_bufA.reserve(bytes) || g_bufS.reserve(bytes)) {
+        return B200_ERR_CUDA;
+    }
+    cudaStream_t s = rt::stream();
+    B200_CUDA_CHECK(cudaMemcpyAsync(g_bufA.p, data, bytes, cudaMemcpyHostToDevice, s));
+    int rc = ntt_op_dev<Fr>(op, g_bufA.as<Fr>(), g_bufS.as<Fr>(), g_bufA.as<Fr>(), m, g);
+    if (rc) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaMemcpyAsync(data, g_bufA.p, bytes, cudaMemcpyDeviceToHost, s));
+    B200_CUDA_CHECK(cudaStreamSynchronize(s));
+    return B200_OK;
+}
+
+template<class Fr> int ntt_dev(int op, void *dev_data, size_t m, const void *g)
+{
+    if (g_bufS.reserve(m * sizeof(Fr))) {
+        return B200_ERR_CUDA;
+    }
+    int rc = ntt_op_dev<Fr>(op, static_cast<Fr *>(dev_data), g_bufS.as<Fr>(), static_cast<Fr *>(dev_data), m, g);
+    if (rc) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
+    return B200_OK;
+}
+
+template<class Fr> int divide_by_z(void *data, size_t m)
+{
+    const int lgn = log2_exact(m);
+    if (lgn < 0 || lgn > Fr::params::S) {
+        return rt::set_error(B200_ERR_DOMAIN, "basic_radix2_domain: bad size %zu", m);
+    }
+    Domain<Fr> *d = nullptr;
+    uint32_t gen[Fr::N];
+    for (int i = 0; i < Fr::N; ++i) {
+        gen[i] = Fr::params::generator(i);
+    }
+    int rc = get_domain<Fr>(lgn, gen, &d);
+    if (rc) {
+        return rc;
+    }
+    const size_t bytes = m * sizeof(Fr);
+    if (g_bufA.reserve(bytes)) {
+        return B200_ERR_CUDA;
+    }
+    cudaStream_t s = rt::stream();
+    B200_CUDA_CHECK(cudaMemcpyAsync(g_bufA.p, data, bytes, cudaMemcpyHostToDevice, s));
+    ntt::k_scale<Fr><<<grid_for(m, 256), 256, 0, s>>>(m, g_bufA.as<Fr>(), d->c(4));
+    B200_LAUNCH_CHECK();
+    B200_CUDA_CHECK(cudaMemcpyAsync(data, g_bufA.p, bytes, cudaMemcpyDeviceToHost, s));
+    B200_CUDA_CHECK(cudaStreamSynchronize(s));
+    return B200_OK;
+}
+
+// r1cs_to_qap.tcc:252-330 with d1 = d2 = d3 = 0. dA, dB, dC clobbered; dH gets m + 1 elements.
+template<class Fr> int witness_map_dev(Fr *dA, Fr *dB, Fr *dC, size_t m, Fr *dH)
+{
+    const int lgn = log2_exact(m);
+    if (lgn < 0 || lgn > Fr::params::S) {
+        return rt::set_error(B200_ERR_DOMAIN, "basic_radix2_domain: bad size %zu", m);
+    }
+    uint32_t gen[Fr::N];
+    for (int i = 0; i < Fr::N; ++i) {
+        gen[i] = Fr::params::generator(i); // g = FieldT::multiplicative_generator (r1cs_to_qap.tcc:273)
+    }
+    Domain<Fr> *d = nullptr;
+    int rc = get_domain<Fr>(lgn, gen, &d);
+    if (rc) {
+        return rc;
+    }
+    if (g_bufS.reserve(m * sizeof(Fr))) {
+        return B200_ERR_CUDA;
+    }
+    Fr *S = g_bufS.as<Fr>();
+    const Fr *gpow_minv = nullptr, *ginv_minv = nullptr;
+    if ((rc = coset_table(*d, T_GPOW_MINV, &gpow_minv)) || (rc = coset_table(*d, T_GINV_MINV, &ginv_minv))) {
+        return rc;
+    }
+    cudaStream_t s = rt::stream();
+    Fr *vecs[3] = {dA, dB, dC};
+    const bool odd = ((lgn + MAX_DEG - 1) / MAX_DEG) & 1;
+    for (int v = 0; v < 3; ++v) {
+        // iFFT then cosetFFT: the 1/m of the inverse and the g^i of the coset are one table
+        // multiplication fused into the inverse's last pass. With an odd pass count the
+        // inverse lands in S and the forward transform brings it back: no device copies.
+        Fr *X = vecs[v], *mid = odd ? S : X, *other = odd ? X : S;
+        if ((rc = run_transform<Fr>(*d, 1, X, S, mid, nullptr, gpow_minv, nullptr)) ||
+            (rc = run_transform<Fr>(*d, 0, mid, other, X, nullptr, nullptr, nullptr))) {
+            return rc;
+        }
+    }
+    ntt::k_pointwise_h<Fr><<<grid_for(m, 256), 256, 0, s>>>(m, dA, dB, dC, d->c(4), dA);
+    B200_LAUNCH_CHECK();
+    if ((rc = run_transform<Fr>(*d, 1, dA, S, dH, nullptr, ginv_minv, nullptr))) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaMemsetAsync(dH + m, 0, sizeof(Fr), s)); // coefficients_for_H[m] = 0
+    return B200_OK;
+}
+
+template<class Fr> int witness_map_host(const void *aA, const void *aB, const void *aC, size_t m, void *out_H)
+{
+    const size_t bytes = m * sizeof(Fr);
+    if (g_bufA.reserve(bytes) || g_bufB.reserve(bytes) || g_bufC.reserve(bytes) || g_bufH.reserve(bytes + sizeof(Fr))) {
+        return B200_ERR_CUDA;
+    }
+    cudaStream_t s = rt::stream();
+    B200_CUDA_CHECK(cudaMemcpyAsync(g_bufA.p, aA, bytes, cudaMemcpyHostToDevice, s));
+    B200_CUDA_CHECK(cudaMemcpyAsync(g_bufB.p, aB, bytes, cudaMemcpyHostToDevice, s));
+    B200_CUDA_CHECK(cudaMemcpyAsync(g_bufC.p, aC, bytes, cudaMemcpyHostToDevice, s));
+    int rc = witness_map_dev<Fr>(g_bufA.as<Fr>(), g_bufB.as<Fr>(), g_bufC.as<Fr>(), m, g_bufH.as<Fr>());
+    if (rc) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaMemcpyAsync(out_H, g_bufH.p, bytes + sizeof(Fr), cudaMemcpyDeviceToHost, s));
+    B200_CUDA_CHECK(cudaStreamSynchronize(s));
+    return B200_OK;
+}
+
+#define DISPATCH_FR(curve, call)                                                                   \
+    switch (curve) {                                                                               \
+    case B200_ALT_BN128: {                                                                         \
+        typedef alt_bn128_fr Fr;                                                                   \
+        return call;                                                                               \
+    }                                                                                              \
+    case B200_BLS12_377: {                                                                         \
+        typedef bls12_377_fr Fr;                                                                   \
+        return call;                                                                               \
+    }                                                                                              \
+    case B200_BW6_761: {                                                                           \
+        typedef bw6_761_fr Fr;                                                                     \
+        return call;                                                                               \
+    }                                                                                              \
+    default: return rt::set_error(B200_ERR_ARG, "unknown curve %d", curve);                        \
+    }
+
+} // namespace
+
+extern "C" {
+
+int b200_ntt(int curve, int op, void *data, size_t m, const void *g)
+{
+    if (!data) {
+        return rt::set_error(B200_ERR_ARG, "null data");
+    }
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    DISPATCH_FR(curve, ntt_host<Fr>(op, data, m, g));
+}
+
+int b200_ntt_dev(int curve, int op, void *dev_data, size_t m, const void *g)
+{
+    if (!dev_data) {
+        return rt::set_error(B200_ERR_ARG, "null data");
+    }
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    DISPATCH_FR(curve, ntt_dev<Fr>(op, dev_data, m, g));
+}
+
+int b200_divide_by_Z_on_coset(int curve, void *data, size_t m)
+{
+    if (!data) {
+        return rt::set_error(B200_ERR_ARG, "null data");
+    }
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    DISPATCH_FR(curve, divide_by_z<Fr>(data, m));
+}
+
+int b200_witness_map_h(int curve, const void *aA, const void *aB, const void *aC, size_t m, void *out_H)
+{
+    if (!aA || !aB || !aC || !out_H) {
+        return rt::set_error(B200_ERR_ARG, "null pointer");
+    }
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    DISPATCH_FR(curve, witness_map_host<Fr>(aA, aB, aC, m, out_H));
+}
+
+int b200_witness_map_h_dev(int curve, void *dA, void *dB, void *dC, size_t m, void *dH)
+{
+    if (!dA || !dB || !dC || !dH) {
+        return rt::set_error(B200_ERR_ARG, "null pointer");
+    }
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    int rc;
+    switch (curve) {
+    case B200_ALT_BN128:
+        rc = witness_map_dev<alt_bn128_fr>((alt_bn128_fr *)dA, (alt_bn128_fr *)dB, (alt_bn128_fr *)dC, m, (alt_bn128_fr *)dH);
+        break;
+    case B200_BLS12_377:
+        rc = witness_map_dev<bls12_377_fr>((bls12_377_fr *)dA, (bls12_377_fr *)dB, (bls12_377_fr *)dC, m, (bls12_377_fr *)dH);
+        break;
+    case B200_BW6_761:
+        rc = witness_map_dev<bw6_761_fr>((bw6_761_fr *)dA, (bw6_761_fr *)dB, (bw6_761_fr *)dC, m, (bw6_761_fr *)dH);
+        break;
+    default: return rt::set_error(B200_ERR_ARG, "unknown curve %d", curve);
+    }
+    if (rc) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
+    return B200_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,350 @@
+// ntt.cuh — radix-2 NTT over Fr, device side.
+//
+// Replaces libfqfft::basic_radix2_domain<FieldT>::{FFT, iFFT, cosetFFT, icosetFFT}
+// (basic_radix2_domain.tcc:54-88) and the kernels under them, _basic_serial_radix2_FFT /
+// _basic_parallel_radix2_FFT (basic_radix2_domain_aux.tcc:44-172) and _multiply_by_coset
+// (:174-183). Natural order in, natural order out, same values (the transform is a
+// function of its input, so any correct algorithm is bit-identical).
+//
+// Algorithm: a size-n = 2^lgn transform is cut into passes of DEG <= 9 stage bits
+// (Stockham autosort: no bit-reversal pass). With p = 2^lgp the product of the radices of the
+// earlier passes, R = 2^DEG and t = n / R, pass input x and output y:
+//     for index in [0, t), k = index mod p:
+//         U[j] = sum_i x[index + i t] * w^i * omega_R^(i j),   w = omega_(pR)^k
+//         y[(index - k) R + k + j p] = U[j]
+// The inter-pass twiddle w^i is merged into the butterfly twiddles: loading x[index + i t]
+// at local row bitrev(i) and running DEG decimation-in-time stages, the butterfly of stage
+// s (half-size 2^s) at local offset j < 2^s uses the *global* twiddle
+//     omega_(p 2^(s+1))^(k + j p) = omega_n^e,   e = (k + j p) << (lgn - lgp - s - 1) < n/2,
+// so a transform costs exactly (n/2) lgn field multiplications and reads one table
+// T[e] = omega_n^e, e < n/2 (precomputed in HBM). The inverse uses omega^-e = -T[n/2 - e].
+//
+// One CTA owns C consecutive `index` values (columns; C * sizeof(Fr) contiguous bytes per
+// row on both the gather and the scatter side) and keeps the R x C tile in shared memory.
+// Each thread holds 8 elements in registers and runs up to 3 stages (radix-8) between
+// shared-memory exchanges. Coset scaling (a[i] *= g^i) and the 1/m of the inverse are
+// fused into the first pass's loads / the last pass's stores from precomputed tables.
+#pragma once
+#include "curves.cuh"
+
+namespace b200
+{
+namespace ntt
+{
+
+struct alignas(16) Vec4 {
+    uint32_t x, y, z, w;
+};
+
+struct PassParams {
+    int lgn;      // log2 of the transform size
+    int lgp;      // log2 of the product of the earlier passes' radices
+    int deg;      // stage bits of this pass
+    int lgc;      // log2 of the columns per CTA
+    int inverse;  // 0: omega, 1: omega^-1
+    int nsteps;   // register steps
+    int step_q[4];
+};
+
+HD uint32_t bitrev(uint32_t v, int bits)
+{
+    uint32_t r = 0;
+    for (int i = 0; i < bits; ++i) {
+        r |= ((v >> i) & 1u) << (bits - 1 - i);
+    }
+    return r;
+}
+
+// shared-memory tile: NPL planes of 16-byte quarter-elements, row stride C + 1 (bank spreading)
+template<class Fr> struct Tile {
+    static constexpr int NPL = Fr::N / 4;
+    Vec4 *base;
+    uint32_t row_stride; // C + 1
+    uint32_t plane;      // R * (C + 1)
+    HD Fr load(uint32_t row, uint32_t col) const
+    {
+        Fr r;
+        const uint32_t o = row * row_stride + col;
+#pragma unroll
+        for (int p = 0; p < NPL; ++p) {
+            const Vec4 q = base[p * plane + o];
+            r.v[4 * p + 0] = q.x;
+            r.v[4 * p + 1] = q.y;
+            r.v[4 * p + 2] = q.z;
+            r.v[4 * p + 3] = q.w;
+        }
+        return r;
+    }
+    HD void store(uint32_t row, uint32_t col, const Fr &v) const
+    {
+        const uint32_t o = row * row_stride + col;
+#pragma unroll
+        for (int p = 0; p < NPL; ++p) {
+            Vec4 q;
+            q.x = v.v[4 * p + 0];
+            q.y = v.v[4 * p + 1];
+            q.z = v.v[4 * p + 2];
+            q.w = v.v[4 * p + 3];
+            base[p * plane + o] = q;
+        }
+    }
+};
+
+template<class Fr> HD Fr gload(const Fr *p)
+{
+    Fr r;
+    const Vec4 *s = reinterpret_cast<const Vec4 *>(p);
+#pragma unroll
+    for (int k = 0; k < Fr::N / 4; ++k) {
+        const Vec4 q = s[k];
+        r.v[4 * k + 0] = q.x;
+        r.v[4 * k + 1] = q.y;
+        r.v[4 * k + 2] = q.z;
+        r.v[4 * k + 3] = q.w;
+    }
+    return r;
+}
+template<class Fr> HD void gstore(Fr *p, const Fr &v)
+{
+    Vec4 *d = reinterpret_cast<Vec4 *>(p);
+#pragma unroll
+    for (int k = 0; k < Fr::N / 4; ++k) {
+        Vec4 q;
+        q.x = v.v[4 * k + 0];
+        q.y = v.v[4 * k + 1];
+        q.z = v.v[4 * k + 2];
+        q.w = v.v[4 * k + 3];
+        d[k] = q;
+    }
+}
+
+// ---- phase A: gather the tile (rows land bit-reversed) ---------------------------------------
+template<class Fr>
+HD void load_phase(uint32_t tid, uint32_t nthreads, const PassParams &pp, uint64_t index0, const Fr *in,
+                   const Fr *pre_table, const Tile<Fr> &tile)
+{
+    const uint32_t C = 1u << pp.lgc, R = 1u << pp.deg;
+    const uint64_t t = 1ull << (pp.lgn - pp.deg);
+    for (uint32_t idx = tid; idx < R * C; idx += nthreads) {
+        const uint32_t col = idx & (C - 1), i = idx >> pp.lgc;
+        const uint64_t gpos = index0 + col + (uint64_t)i * t;
+        Fr x = gload(in + gpos);
+        if (pre_table != nullptr) {
+            x = x * gload(pre_table + gpos);
+        }
+        tile.store(bitrev(i, pp.deg), col, x);
+    }
+}
+
+// ---- phase B: Q stages on 2^Q rows {base + a 2^r} held in registers -----------------------------
+template<class Fr, int Q>
+HD void radix_group(Fr *v, const PassParams &pp, int r, uint32_t lo, uint64_t k, const Fr *twiddles)
+{
+    const uint64_t half_n = 1ull << (pp.lgn - 1);
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+        const int sh = pp.lgn - pp.lgp - (r + q) - 1;
+        const uint64_t e0 = (k + ((uint64_t)lo << pp.lgp)) << sh;
+#pragma unroll
+        for (int jq = 0; jq < (1 << q); ++jq) {
+            const uint64_t e = e0 + ((uint64_t)jq << (pp.lgn - q - 1));
+            const bool trivial = (e == 0);
+            Fr tw;
+            if (!trivial) {
+                tw = gload(twiddles + (pp.inverse ? half_n - e : e));
+            }
+#pragma unroll
+            for (int h = 0; h < (1 << (Q - q - 1)); ++h) {
+                const int a = (h << (q + 1)) | jq;
+                const int b = a | (1 << q);
+                const Fr y = trivial ? v[b] : v[b] * tw;
+                const Fr x = v[a];
+                if (pp.inverse && !trivial) { // omega^-e = -T[n/2 - e]
+                    v[a] = x - y;
+                    v[b] = x + y;
+                } else {
+                    v[a] = x + y;
+                    v[b] = x - y;
+                }
+            }
+        }
+    }
+}
+
+template<class Fr, int Q>
+HD void step_phase(uint32_t tid, uint32_t nthreads, const PassParams &pp, int r, uint64_t index0, const Fr *twiddles,
+                   const Tile<Fr> &tile)
+{
+    const uint32_t C = 1u << pp.lgc, R = 1u << pp.deg;
+    const uint32_t ngroups = (R >> Q) << pp.lgc;
+    const uint64_t pmask = (1ull << pp.lgp) - 1;
+    for (uint32_t gam = tid; gam < ngroups; gam += nthreads) {
+        const uint32_t col = gam & (C - 1), gi = gam >> pp.lgc;
+        const uint32_t lo = gi & ((1u << r) - 1), hi = gi >> r;
+        const uint32_t base = (hi << (r + Q)) | lo;
+        Fr v[1 << Q];
+#pragma unroll
+        for (int a = 0; a < (1 << Q); ++a) {
+            v[a] = tile.load(base + ((uint32_t)a << r), col);
+        }
+        radix_group<Fr, Q>(v, pp, r, lo, (index0 + col) & pmask, twiddles);
+#pragma unroll
+        for (int a = 0; a < (1 << Q); ++a) {
+            tile.store(base + ((uint32_t)a << r), col, v[a]);
+        }
+    }
+}
+
+// ---- phase C: scatter ---------------------------------------------------------------------------
+template<class Fr>
+HD void store_phase(uint32_t tid, uint32_t nthreads, const PassParams &pp, uint64_t index0, Fr *out,
+                    const Fr *post_table, const Fr *post_const, const Tile<Fr> &tile)
+{
+    const uint32_t C = 1u << pp.lgc, R = 1u << pp.deg;
+    const uint64_t p = 1ull << pp.lgp;
+    for (uint32_t idx = tid; idx < R * C; idx += nthreads) {
+        uint32_t col, j;
+        uint64_t dst;
+        if (pp.lgp >= pp.lgc) {
+            col = idx & (C - 1);
+            j = idx >> pp.lgc;
+            const uint64_t k = (index0 + col) & (p - 1);
+            dst = ((index0 + col - k) << pp.deg) + k + ((uint64_t)j << pp.lgp);
+        } else { // p < C: runs of R * p contiguous outputs per block of p columns
+            const uint32_t kk = idx & (uint32_t)(p - 1);
+            j = (idx >> pp.lgp) & (R - 1);
+            const uint32_t chi = idx >> (pp.lgp + pp.deg);
+            col = (chi << pp.lgp) + kk;
+            dst = ((index0 + ((uint64_t)chi << pp.lgp)) << pp.deg) + ((uint64_t)j << pp.lgp) + kk;
+        }
+        Fr x = tile.load(j, col);
+        if (post_table != nullptr) {
+            x = x * gload(post_table + dst);
+        } else if (post_const != nullptr) {
+            x = x * gload(post_const);
+        }
+        gstore(out + dst, x);
+    }
+}
+
+// out[e] = scale * prod_{b : bit b of e} pows[b]   (pows[b] = base^(2^b)); used for the twiddle
+// table (base = omega_n) and the coset tables (base = g or g^-1, scale = 1 or m^-1).
+template<class Fr> HD void pow_table_body(uint64_t e, const Fr *pows, int nbits, const Fr *scale, Fr *out)
+{
+    Fr acc = scale ? gload(scale) : Fr::one();
+    for (int b = 0; b < nbits; ++b) {
+        if ((e >> b) & 1ull) {
+            acc = acc * gload(pows + b);
+        }
+    }
+    gstore(out + e, acc);
+}
+
+// Domain constants, computed by one thread: consts layout (Fr each):
+//   [0] omega_n  [1] m^-1  [2] g  [3] g^-1  [4] (g^m - 1)^-1  [5] one
+//   pows_w[b] = omega^(2^b), pows_g[b] = g^(2^b), pows_gi[b] = g^-(2^b),  b < lgn
+template<class Fr> HD void domain_consts_body(int lgn, const Fr *g_in, Fr *consts, Fr *pows_w, Fr *pows_g, Fr *pows_gi)
+{
+    Fr w;
+#pragma unroll
+    for (int i = 0; i < Fr::N; ++i) {
+        w.v[i] = Fr::params::root_of_unity(i);
+    }
+    for (int i = Fr::params::S; i > lgn; --i) { // get_root_of_unity, field_utils.tcc:190-206
+        w = w.sqr();
+    }
+    Fr m = Fr::zero();
+    m.v[lgn >> 5] = 1u << (lgn & 31);
+    const Fr minv = m.to_mont().inverse();
+    const Fr g = gload(g_in);
+    const Fr gi = g.is_zero() ? g : g.inverse();
+    Fr pw = w, pg = g, pgi = gi;
+    for (int b = 0; b < lgn; ++b) {
+        gstore(pows_w + b, pw);
+        gstore(pows_g + b, pg);
+        gstore(pows_gi + b, pgi);
+        pw = pw.sqr();
+        pg = pg.sqr();
+        pgi = pgi.sqr();
+    }
+    // after lgn squarings pg = g^m: Z(g x) = g^m - 1 on the coset (basic_radix2_domain.tcc:117-126)
+    const Fr z = pg - Fr::one();
+    gstore(consts + 0, w);
+    gstore(consts + 1, minv);
+    gstore(consts + 2, g);
+    gstore(consts + 3, gi);
+    gstore(consts + 4, z.is_zero() ? z : z.inverse());
+    gstore(consts + 5, Fr::one());
+}
+
+#if defined(__CUDACC__)
+
+template<class Fr>
+__global__ void __launch_bounds__(512) k_ntt_pass(PassParams pp, const Fr *in, Fr *out, const Fr *twiddles,
+                                                  const Fr *pre_table, const Fr *post_table, const Fr *post_const)
+{
+    extern __shared__ uint4 ntt_smem[];
+    Tile<Fr> tile;
+    tile.base = reinterpret_cast<Vec4 *>(ntt_smem);
+    tile.row_stride = (1u << pp.lgc) + 1;
+    tile.plane = (1u << pp.deg) * tile.row_stride;
+    const uint32_t tid = threadIdx.x, nth = blockDim.x;
+    const uint64_t index0 = (uint64_t)blockIdx.x << pp.lgc;
+    load_phase<Fr>(tid, nth, pp, index0, in, pre_table, tile);
+    __syncthreads();
+    int r = 0;
+    for (int s = 0; s < pp.nsteps; ++s) {
+        const int q = pp.step_q[s];
+        if (q == 3) {
+            step_phase<Fr, 3>(tid, nth, pp, r, index0, twiddles, tile);
+        } else if (q == 2) {
+            step_phase<Fr, 2>(tid, nth, pp, r, index0, twiddles, tile);
+        } else {
+            step_phase<Fr, 1>(tid, nth, pp, r, index0, twiddles, tile);
+        }
+        r += q;
+        __syncthreads();
+    }
+    store_phase<Fr>(tid, nth, pp, index0, out, post_table, post_const, tile);
+}
+
+template<class Fr>
+__global__ void k_pow_table(uint64_t count, const Fr *pows, int nbits, const Fr *scale, Fr *out)
+{
+    const uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < count) {
+        pow_table_body<Fr>(e, pows, nbits, scale, out);
+    }
+}
+
+template<class Fr> __global__ void k_domain_consts(int lgn, const Fr *g_in, Fr *consts, Fr *pows_w, Fr *pows_g, Fr *pows_gi)
+{
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        domain_consts_body<Fr>(lgn, g_in, consts, pows_w, pows_g, pows_gi);
+    }
+}
+
+// h[i] = (a[i] * b[i] - c[i]) * zinv      (r1cs_to_qap.tcc:286-288, :310-312, :315)
+template<class Fr> __global__ void k_pointwise_h(uint64_t m, const Fr *a, const Fr *b, const Fr *c, const Fr *zinv, Fr *h)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < m) {
+        const Fr z = gload(zinv);
+        const Fr v = (gload(a + i) * gload(b + i) - gload(c + i)) * z;
+        gstore(h + i, v);
+    }
+}
+
+// a[i] *= c   (divide_by_Z_on_coset, basic_radix2_domain.tcc:117-126)
+template<class Fr> __global__ void k_scale(uint64_t m, Fr *a, const Fr *c)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < m) {
+        gstore(a + i, gload(a + i) * gload(c));
+    }
+}
+
+#endif // __CUDACC__
+
+} // namespace ntt
+} // namespace b200

@@ -458,6 +458,33 @@ template<typename ppT> struct H {
         return 0;
     }
 
+    // The evaluations aA, aB, aC that r1cs_to_qap_witness_map feeds its first iFFTs
+    // (r1cs_to_qap.tcc:236-248 and :293-296), computed with the reference's own
+    // linear_combination::evaluate. m elements each.
+    static int abc_evaluations(const groth16_fixture<ppT> *f, void *oA, void *oB, void *oC)
+    {
+        const auto &cs = f->example.constraint_system;
+        const size_t m = libfqfft::get_evaluation_domain<FrT>(cs.num_constraints() + cs.num_inputs() + 1)->m;
+        r1cs_variable_assignment<FrT> full = f->example.primary_input;
+        full.insert(full.end(), f->example.auxiliary_input.begin(), f->example.auxiliary_input.end());
+        std::vector<FrT> aA(m, FrT::zero()), aB(m, FrT::zero()), aC(m, FrT::zero());
+        for (size_t i = 0; i <= cs.num_inputs(); ++i) {
+            aA[i + cs.num_constraints()] = (i > 0 ? full[i - 1] : FrT::one());
+        }
+#ifdef MULTICORE
+#pragma omp parallel for
+#endif
+        for (size_t i = 0; i < cs.num_constraints(); ++i) {
+            aA[i] += cs.constraints[i].a.evaluate(full);
+            aB[i] += cs.constraints[i].b.evaluate(full);
+            aC[i] += cs.constraints[i].c.evaluate(full);
+        }
+        memcpy(oA, aA.data(), m * sizeof(FrT));
+        memcpy(oB, aB.data(), m * sizeof(FrT));
+        memcpy(oC, aC.data(), m * sizeof(FrT));
+        return 0;
+    }
+
     // Restates r1cs_gg_ppzksnark.tcc:477-598 with caller-supplied r, s (the
     // reference draws them from std::random_device). Every
     // operator called is the reference's (or, in the overlay build, whatever
@@ -934,6 +961,13 @@ API int ref_groth16_witness_map(void *h_, void *out_H, double *ms)
 {
     fixture_handle *h = static_cast<fixture_handle *>(h_);
     DISPATCH_FIXTURE(h, witness_map, out_H, ms);
+    return -100;
+}
+
+API int ref_groth16_abc_evaluations(void *h_, void *oA, void *oB, void *oC)
+{
+    fixture_handle *h = static_cast<fixture_handle *>(h_);
+    DISPATCH_FIXTURE(h, abc_evaluations, oA, oB, oC);
     return -100;
 }
 

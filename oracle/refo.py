@@ -50,6 +50,7 @@ class RefOracle:
         L.ref_groth16_sizes.argtypes = [C.c_void_p, C.c_void_p]
         L.ref_groth16_witness_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.ref_groth16_prove.argtypes = [C.c_void_p] * 5
+        L.ref_groth16_abc_evaluations.argtypes = [C.c_void_p] * 4
         L.ref_groth16_prove_stock.argtypes = [C.c_void_p] * 3
         L.ref_groth16_verify.argtypes = [C.c_void_p, C.c_void_p]
         L.ref_bdlo12_signed_optimal_c.restype = C.c_uint64
@@ -277,6 +278,13 @@ class Groth16Fixture:
         ms = C.c_double(0)
         assert self.ref.lib.ref_groth16_witness_map(self.h, _p(out), C.byref(ms)) == 0
         return out, ms.value
+
+    def abc_evaluations(self):
+        """aA, aB, aC of r1cs_to_qap.tcc:236-248/:293-296 (the inputs of the NTT chain)."""
+        shape = (self.sizes["m"], self.i["nr"])
+        a, b, c = (np.zeros(shape, dtype=np.uint64) for _ in range(3))
+        assert self.ref.lib.ref_groth16_abc_evaluations(self.h, _p(a), _p(b), _p(c)) == 0
+        return a, b, c
 
     def proof_limbs(self):
         return 2 * self.i["g1_limbs"] + self.i["g2_limbs"]

@@ -1,0 +1,93 @@
+"""GPU parity: b200_ntt / b200_witness_map_h (through the C-ABI) vs libfqfft's basic_radix2_domain
+and libsnark's r1cs_to_qap_witness_map run by the unmodified reference. Bit-exact."""
+import numpy as np
+import pytest
+
+from oracle import refo
+
+pytestmark = pytest.mark.gpu
+
+CURVES = ["alt_bn128", "bls12_377", "bw6_761"]
+
+
+def _gen(ref, curve):
+    return ref.field_consts(curve, refo.FR)["generator"]
+
+
+@pytest.mark.parametrize("curve", CURVES)
+@pytest.mark.parametrize("log_m", [1, 2, 3, 4, 5, 8, 9, 10, 13, 16])
+def test_fft_ops_match_reference(ref, b200, curve, log_m):
+    if curve != "alt_bn128" and log_m in (5, 9, 13):
+        pytest.skip("covered on alt_bn128")
+    m = 1 << log_m
+    a = ref.field_random(curve, refo.FR, 7 * m, m)
+    g = _gen(ref, curve)
+    dom = b200.get_evaluation_domain(curve, m)
+    assert np.array_equal(dom.FFT(a), ref.fft(curve, refo.FFT, a))
+    assert np.array_equal(dom.iFFT(a), ref.fft(curve, refo.IFFT, a))
+    assert np.array_equal(dom.cosetFFT(a, g), ref.fft(curve, refo.COSET_FFT, a, g))
+    assert np.array_equal(dom.icosetFFT(a, g), ref.fft(curve, refo.ICOSET_FFT, a, g))
+    assert np.array_equal(dom.divide_by_Z_on_coset(a), ref.fft(curve, refo.DIV_Z_COSET, a))
+
+
+def test_fft_other_coset_generator(ref, b200):
+    curve, m = "alt_bn128", 1 << 10
+    a = ref.field_random(curve, refo.FR, 1, m)
+    g = ref.field_random(curve, refo.FR, 424242, 1)[0]
+    dom = b200.get_evaluation_domain(curve, m)
+    assert np.array_equal(dom.cosetFFT(a, g), ref.fft(curve, refo.COSET_FFT, a, g))
+    assert np.array_equal(dom.icosetFFT(a, g), ref.fft(curve, refo.ICOSET_FFT, a, g))
+    g2 = _gen(ref, curve)  # back to the default: tables are rebuilt
+    assert np.array_equal(dom.cosetFFT(a, g2), ref.fft(curve, refo.COSET_FFT, a, g2))
+
+
+def test_fft_small_known_vector(ref, b200):
+    """libfqfft evaluation_domain_test.cpp:40-80: f = {2, 5, 3, 8}, FFT(f)[i] == f(omega^i)."""
+    curve = "alt_bn128"
+    f = np.zeros((4, 4), dtype=np.uint64)
+    f[:, 0] = [2, 5, 3, 8]
+    fm = ref.to_mont(curve, refo.FR, f)
+    got = b200.get_evaluation_domain(curve, 4).FFT(fm)
+    want = ref.poly_eval_at_domain(curve, fm, np.arange(4, dtype=np.uint64))
+    assert np.array_equal(got, want)
+
+
+def test_domain_size_exception(b200):
+    """basic_radix2_domain.tcc:57,65: a.size() != m throws DomainSizeException; non powers of two have no basic domain."""
+    a = np.zeros((6, 4), dtype=np.uint64)
+    with pytest.raises(b200.DomainSizeException):
+        b200.get_evaluation_domain("alt_bn128", 6).FFT(a)
+    with pytest.raises(b200.DomainSizeException):
+        b200.get_evaluation_domain("alt_bn128", 8).FFT(a)
+
+
+@pytest.mark.parametrize("log_m", [20])
+def test_fft_large_roundtrip_and_spot_check(ref, b200, log_m):
+    """Size-independent properties at scale: iFFT(FFT(a)) == a, icosetFFT(cosetFFT(a)) == a, and
+    naive Horner evaluation at a few domain points."""
+    curve, m = "alt_bn128", 1 << log_m
+    a = ref.field_random(curve, refo.FR, 5, m)
+    g = _gen(ref, curve)
+    dom = b200.get_evaluation_domain(curve, m)
+    fa = dom.FFT(a)
+    assert np.array_equal(dom.iFFT(fa), a)
+    assert np.array_equal(dom.icosetFFT(dom.cosetFFT(a, g), g), a)
+    idx = np.array([0, 1, 2, m // 2, m - 1, 12345, 777777 % m], dtype=np.uint64)
+    assert np.array_equal(fa[idx.astype(np.int64)], ref.poly_eval_at_domain(curve, a, idx))
+    assert np.array_equal(fa, ref.fft(curve, refo.FFT, a))
+
+
+@pytest.mark.parametrize("curve,log_m", [("alt_bn128", 4), ("alt_bn128", 10), ("alt_bn128", 16), ("bls12_377", 12),
+                                         ("bw6_761", 11)])
+def test_witness_map_h(ref, b200, curve, log_m):
+    """coefficients_for_H of r1cs_to_qap_witness_map: the reference's own H vs the device chain fed with
+    the reference's aA, aB, aC evaluations (recovered from its H? no: recomputed here from the R1CS)."""
+    m = 1 << log_m
+    ni = 2 if log_m < 6 else 10
+    fx = ref.groth16_setup(curve, m - ni - 1, ni, real_keys=False)
+    assert fx.sizes["m"] == m
+    want, _ = fx.witness_map()
+    aA, aB, aC = fx.abc_evaluations()
+    got = b200.r1cs_to_qap_witness_map_h(curve, aA, aB, aC)
+    assert np.array_equal(got, want)
+    fx.close()
