@@ -91,6 +91,9 @@ def lib():
         L.b200_imad_peak.argtypes = [i, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.b200_last_msm_timing.argtypes = [C.POINTER(C.c_double)]
         L.b200_launch_count.restype = u64
+        L.b200_test_field_op.argtypes = [i, i, i, vp, vp, vp, sz]
+        L.b200_test_fp_convert.argtypes = [i, i, i, vp, vp, sz]
+        L.b200_test_group_op.argtypes = [i, i, i, vp, vp, vp, sz]
         _lib = L
     return _lib
 
@@ -226,9 +229,11 @@ def last_msm_timing():
 
 
 def imad_peak(iters=4096):
+    """(IMAD.WIDE no carry, IMAD lo, IMAD.WIDE.X carry chains) multiply-adds per second."""
     w, lo = C.c_double(0), C.c_double(0)
     _check(lib().b200_imad_peak(iters, C.byref(w), C.byref(lo)))
-    return w.value, lo.value
+    lib().b200_imad_carry_peak.restype = C.c_double
+    return w.value, lo.value, lib().b200_imad_carry_peak()
 
 
 # ---- NTT -------------------------------------------------------------------------------------
@@ -299,3 +304,30 @@ class DeviceBuffer:
         if self.ptr:
             _check(lib().b200_dev_free(C.c_void_p(self.ptr)))
             self.ptr = 0
+
+
+# ---- device unit-test hooks (selftest.cu) ------------------------------------------------------
+
+def test_field_op(curve, field, op, a, b=None):
+    a = _u64(a)
+    b = a if b is None else _u64(b)
+    out = np.zeros_like(a)
+    _check(lib().b200_test_field_op(_cid(curve), field, op, _p(a), _p(b), _p(out), a.shape[0]))
+    return out
+
+
+def test_fp_convert(curve, field, to_mont, a):
+    a = _u64(a)
+    out = np.zeros_like(a)
+    _check(lib().b200_test_fp_convert(_cid(curve), field, int(to_mont), _p(a), _p(out), a.shape[0]))
+    return out
+
+
+def test_group_op(curve, group, op, a, b):
+    a, b = _u64(a), _u64(b)
+    out = np.zeros_like(a)
+    _check(lib().b200_test_group_op(_cid(curve), group, op, _p(a), _p(b), _p(out), a.shape[0]))
+    return out
+
+
+test_field_op.__test__ = test_fp_convert.__test__ = test_group_op.__test__ = False

@@ -17,7 +17,7 @@ namespace
 struct GroupVt {
     int (*bases_upload)(int, int, const void *, size_t, size_t, rt::BaseSet *);
     int (*msm_windows)(const rt::BaseSet &, size_t, size_t, const void *, void *, int *, int *);
-    int (*msm_fold)(const void *, int, int, size_t, void *);
+    int (*msm_fold)(const void *, int, int, int, size_t, void *);
     size_t (*window_point_bytes)();
     int (*scalar_bits)();
 };
@@ -111,11 +111,10 @@ int msm_resident_impl(const rt::BaseSet &bs, size_t first, size_t n, const void 
         B200_CUDA_CHECK(cudaMemcpyAsync(out_windows, g_windows.p, (size_t)W * wbytes, cudaMemcpyDeviceToHost, s));
     }
     if (out) {
-        rc = v->grp(bs.group).msm_fold(g_windows.p, W, c, 1, g_out.p);
+        rc = v->grp(bs.group).msm_fold(g_windows.p, 1, W, c, 1, out);
         if (rc) {
             return rc;
         }
-        B200_CUDA_CHECK(cudaMemcpyAsync(out, g_out.p, group_bytes(v, bs.group), cudaMemcpyDeviceToHost, s));
     }
     B200_CUDA_CHECK(cudaStreamSynchronize(s));
     return B200_OK;
@@ -282,25 +281,8 @@ int b200_msm_fold_windows(int curve, int group, size_t n_per_shard, const void *
     if (!windows || !out || num_shards == 0 || (group != B200_G1 && group != B200_G2)) {
         return rt::set_error(B200_ERR_ARG, "bad argument");
     }
-    if (!rt::ensure_init()) {
-        return B200_ERR_CUDA;
-    }
-    std::lock_guard<std::mutex> lk(g_mu);
     const msm::Geometry geo = msm::make_geometry(n_per_shard, v->scalar_bits());
-    const int W = geo.W, c = geo.c;
-    const size_t bytes = (size_t)W * num_shards * v->window_point_bytes(group);
-    cudaStream_t s = rt::stream();
-    if (g_windows.reserve(bytes) || g_out.reserve(1024)) {
-        return B200_ERR_CUDA;
-    }
-    B200_CUDA_CHECK(cudaMemcpyAsync(g_windows.p, windows, bytes, cudaMemcpyHostToDevice, s));
-    const int rc = v->grp(group).msm_fold(g_windows.p, W, c, num_shards, g_out.p);
-    if (rc) {
-        return rc;
-    }
-    B200_CUDA_CHECK(cudaMemcpyAsync(out, g_out.p, group_bytes(v, group), cudaMemcpyDeviceToHost, s));
-    B200_CUDA_CHECK(cudaStreamSynchronize(s));
-    return B200_OK;
+    return v->grp(group).msm_fold(windows, 0, geo.W, geo.c, num_shards, out);
 }
 
 int b200_msm(int curve, int group, const void *bases, size_t base_stride, size_t n, const void *scalars, void *out)

@@ -95,68 +95,70 @@ template<class F> HD XYZZ<F> dbl_affine_cold(const Affine<F> &p)
 #endif
 }
 
+// Branch-free selection between two points (per-limb selects; keeps the warp converged).
+template<class F> HD XYZZ<F> select(bool take_b, const XYZZ<F> &a, const XYZZ<F> &b)
+{
+    XYZZ<F> r;
+    const uint32_t *pa = reinterpret_cast<const uint32_t *>(&a);
+    const uint32_t *pb = reinterpret_cast<const uint32_t *>(&b);
+    uint32_t *pr = reinterpret_cast<uint32_t *>(&r);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(XYZZ<F>) / 4); ++i) {
+        pr[i] = take_b ? pb[i] : pa[i];
+    }
+    return r;
+}
+
 // acc += p (p affine, never infinity)   — EFD madd-2008-s.
-// Counterpart of libff mixed_add (alt_bn128_g1.cpp:208-283).
+// Counterpart of libff mixed_add (alt_bn128_g1.cpp:208-283). Written without early exits:
+// the general formula is always evaluated (P + (-P) falls out of it as ZZ = 0), an infinite
+// accumulator is patched by a select, and only P + P takes a (rare, out-of-line) branch.
 template<class F> HD void madd(XYZZ<F> &a, const Affine<F> &p)
 {
-    if (a.is_inf()) {
-        a = XYZZ<F>::from_affine(p);
-        return;
-    }
+    const bool a_inf = a.is_inf();
     const F u2 = p.x * a.zz;
     const F s2 = p.y * a.zzz;
     const F pd = u2 - a.x;
     const F rd = s2 - a.y;
-    if (pd.is_zero()) {
-        if (rd.is_zero()) {
-            a = dbl_affine_cold(p); // rare: out of line, keeps the hot loop small
-        } else {
-            a = XYZZ<F>::inf();
-        }
-        return;
-    }
     const F pp = pd.sqr();
     const F ppp = pd * pp;
     const F q = a.x * pp;
-    const F x3 = rd.sqr() - ppp - q.dbl();
-    a.y = rd * (q - x3) - a.y * ppp;
-    a.x = x3;
-    a.zz = a.zz * pp;
-    a.zzz = a.zzz * ppp;
+    XYZZ<F> r;
+    r.x = rd.sqr() - ppp - q.dbl();
+    r.y = rd * (q - r.x) - a.y * ppp;
+    r.zz = a.zz * pp;
+    r.zzz = a.zzz * ppp;
+    if (!a_inf && pd.is_zero() && rd.is_zero()) {
+        r = dbl_affine_cold(p); // P + P
+    }
+    a = select(a_inf, r, XYZZ<F>::from_affine(p));
 }
 
 // acc += b   — EFD add-2008-s. Counterpart of libff add / operator+ (alt_bn128_g1.cpp:97-206).
+// Same structure as madd: no early exits, selects for the infinity cases.
 template<class F> HD void add(XYZZ<F> &a, const XYZZ<F> &b)
 {
-    if (b.is_inf()) {
-        return;
-    }
-    if (a.is_inf()) {
-        a = b;
-        return;
-    }
+    const bool a_inf = a.is_inf(), b_inf = b.is_inf();
     const F u1 = a.x * b.zz;
     const F u2 = b.x * a.zz;
     const F s1 = a.y * b.zzz;
     const F s2 = b.y * a.zzz;
     const F pd = u2 - u1;
     const F rd = s2 - s1;
-    if (pd.is_zero()) {
-        if (rd.is_zero()) {
-            dbl(a);
-        } else {
-            a = XYZZ<F>::inf();
-        }
-        return;
-    }
     const F pp = pd.sqr();
     const F ppp = pd * pp;
     const F q = u1 * pp;
-    const F x3 = rd.sqr() - ppp - q.dbl();
-    a.y = rd * (q - x3) - s1 * ppp;
-    a.x = x3;
-    a.zz = a.zz * b.zz * pp;
-    a.zzz = a.zzz * b.zzz * ppp;
+    XYZZ<F> r;
+    r.x = rd.sqr() - ppp - q.dbl();
+    r.y = rd * (q - r.x) - s1 * ppp;
+    r.zz = a.zz * b.zz * pp;
+    r.zzz = a.zzz * b.zzz * ppp;
+    if (!a_inf && !b_inf && pd.is_zero() && rd.is_zero()) {
+        r = a;
+        dbl(r); // P + P
+    }
+    r = select(a_inf, r, b);
+    a = select(b_inf, r, a);
 }
 
 // Out-of-line copies for kernels where the group law is not the inner loop (bucket

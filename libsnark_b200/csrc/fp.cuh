@@ -19,7 +19,27 @@
 namespace b200
 {
 
-template<class P> struct Fp {
+// Host code (the MSM's final O(scalar bits) window fold, host_fold.hpp) uses a plain 64-bit-limb
+// CIOS instead of the device carry chains; tests/host_emu defines B200_HOST_EMULATE_PRIMS to run
+// the device formulation itself on the CPU through the prims.cuh emulation.
+#if !defined(__CUDA_ARCH__) && !defined(B200_HOST_EMULATE_PRIMS)
+#define B200_HOST_FAST 1
+#else
+#define B200_HOST_FAST 0
+#endif
+
+// Translation units whose kernels are latency-bound chains of group operations run by few warps
+// (bucket reduction, window sums, test hooks) are compiled with -DB200_OUTLINE_MUL: every field
+// product then calls one shared out-of-line copy, so the code a warp walks through stays inside
+// the instruction cache. (Measured: with inlined products those kernels were instruction-fetch
+// bound at ~45 cycles per instruction; profiles/r1_reduce_icache.md.)
+#if defined(B200_OUTLINE_MUL)
+#define B200_OUTLINE_MUL_ALWAYS 1
+#else
+#define B200_OUTLINE_MUL_ALWAYS 0
+#endif
+
+template<class P> struct alignas(16) Fp {
     static constexpr int N = P::N;
     typedef P params;
     uint32_t v[N];
@@ -89,8 +109,124 @@ template<class P> struct Fp {
         }
     }
 
+#if B200_HOST_FAST
+    static inline uint64_t limb64(const uint32_t *v, int i) { return (uint64_t)v[2 * i] | ((uint64_t)v[2 * i + 1] << 32); }
+    static inline uint64_t mod64(int i) { return (uint64_t)P::mod(2 * i) | ((uint64_t)P::mod(2 * i + 1) << 32); }
+    static inline void put64(uint32_t *v, int i, uint64_t x)
+    {
+        v[2 * i] = (uint32_t)x;
+        v[2 * i + 1] = (uint32_t)(x >> 32);
+    }
+    // r = x - p if x >= p (x < 2p given as M limbs)
+    static inline void host_final_sub(uint64_t *x)
+    {
+        constexpr int M = N / 2;
+        uint64_t t[M];
+        unsigned __int128 borrow = 0;
+        for (int i = 0; i < M; ++i) {
+            const unsigned __int128 d = (unsigned __int128)x[i] - mod64(i) - (uint64_t)borrow;
+            t[i] = (uint64_t)d;
+            borrow = (d >> 64) & 1;
+        }
+        if (!borrow) {
+            for (int i = 0; i < M; ++i) {
+                x[i] = t[i];
+            }
+        }
+    }
+    static inline Fp host_add(const Fp &a, const Fp &b)
+    {
+        constexpr int M = N / 2;
+        uint64_t x[M];
+        unsigned __int128 c = 0;
+        for (int i = 0; i < M; ++i) {
+            c += (unsigned __int128)limb64(a.v, i) + limb64(b.v, i);
+            x[i] = (uint64_t)c;
+            c >>= 64;
+        }
+        host_final_sub(x);
+        Fp r;
+        for (int i = 0; i < M; ++i) {
+            put64(r.v, i, x[i]);
+        }
+        return r;
+    }
+    static inline Fp host_sub(const Fp &a, const Fp &b)
+    {
+        constexpr int M = N / 2;
+        uint64_t x[M];
+        unsigned __int128 borrow = 0;
+        for (int i = 0; i < M; ++i) {
+            const unsigned __int128 d = (unsigned __int128)limb64(a.v, i) - limb64(b.v, i) - (uint64_t)borrow;
+            x[i] = (uint64_t)d;
+            borrow = (d >> 64) & 1;
+        }
+        if (borrow) {
+            unsigned __int128 c = 0;
+            for (int i = 0; i < M; ++i) {
+                c += (unsigned __int128)x[i] + mod64(i);
+                x[i] = (uint64_t)c;
+                c >>= 64;
+            }
+        }
+        Fp r;
+        for (int i = 0; i < M; ++i) {
+            put64(r.v, i, x[i]);
+        }
+        return r;
+    }
+    static inline Fp host_mul(const Fp &a, const Fp &b)
+    {
+        constexpr int M = N / 2;
+        uint64_t A[M], B[M], Q[M], t[M + 2];
+        for (int i = 0; i < M; ++i) {
+            A[i] = limb64(a.v, i);
+            B[i] = limb64(b.v, i);
+            Q[i] = mod64(i);
+            t[i] = 0;
+        }
+        t[M] = t[M + 1] = 0;
+        uint64_t y = 1; // p^-1 mod 2^64 by Newton iteration, then negate
+        for (int k = 0; k < 6; ++k) {
+            y *= 2 - Q[0] * y;
+        }
+        const uint64_t inv64 = 0 - y;
+        for (int i = 0; i < M; ++i) {
+            unsigned __int128 cur, carry = 0;
+            for (int j = 0; j < M; ++j) {
+                cur = (unsigned __int128)A[j] * B[i] + t[j] + (uint64_t)carry;
+                t[j] = (uint64_t)cur;
+                carry = cur >> 64;
+            }
+            cur = (unsigned __int128)t[M] + (uint64_t)carry;
+            t[M] = (uint64_t)cur;
+            t[M + 1] = (uint64_t)(cur >> 64);
+            const uint64_t m = t[0] * inv64;
+            cur = (unsigned __int128)m * Q[0] + t[0];
+            carry = cur >> 64;
+            for (int j = 1; j < M; ++j) {
+                cur = (unsigned __int128)m * Q[j] + t[j] + (uint64_t)carry;
+                t[j - 1] = (uint64_t)cur;
+                carry = cur >> 64;
+            }
+            cur = (unsigned __int128)t[M] + (uint64_t)carry;
+            t[M - 1] = (uint64_t)cur;
+            t[M] = t[M + 1] + (uint64_t)(cur >> 64);
+        }
+        host_final_sub(t);
+        Fp r;
+        for (int i = 0; i < M; ++i) {
+            put64(r.v, i, t[i]);
+        }
+        return r;
+    }
+#endif
+
     HD friend Fp operator+(const Fp &a, const Fp &b)
     {
+#if B200_HOST_FAST
+        return host_add(a, b);
+#endif
         Fp r;
         r.v[0] = prim::add_cc(a.v[0], b.v[0]);
 #pragma unroll
@@ -104,6 +240,9 @@ template<class P> struct Fp {
 
     HD friend Fp operator-(const Fp &a, const Fp &b)
     {
+#if B200_HOST_FAST
+        return host_sub(a, b);
+#endif
         Fp r;
         r.v[0] = prim::sub_cc(a.v[0], b.v[0]);
 #pragma unroll
@@ -221,7 +360,7 @@ template<class P> struct Fp {
     HD friend Fp operator*(const Fp &a, const Fp &b)
     {
 #if defined(__CUDA_ARCH__)
-        if (N >= 16) {
+        if (N >= 16 || B200_OUTLINE_MUL_ALWAYS) {
             Fp r;
             mul_outlined(r.v, a.v, b.v);
             return r;
@@ -248,6 +387,9 @@ template<class P> struct Fp {
     HD static Fp mul_inline(const Fp &a, const Fp &b)
     {
         static_assert(N % 2 == 0, "even limb count");
+#if B200_HOST_FAST
+        return host_mul(a, b);
+#endif
         uint32_t acc[2][N];
         mont_round<true>(acc[0], acc[1], a.v, b.v[0]);
 #pragma unroll

@@ -21,8 +21,8 @@
 //                  multiexp_accumulate_buckets, multiexp.tcc:91-125, cut into chunks) plus
 //                  a short double-and-add for the chunk's weight offset
 //   7. window sum  tree sum of the chunk results of each window
-//   8. fold        Horner over the windows (2^c * acc + R_w, multiexp.tcc:602-629) and
-//                  normalisation to affine.
+//   8. fold        (host, host_fold.hpp) Horner over the windows (2^c * acc + R_w,
+//                  multiexp.tcc:602-629) and normalisation to affine.
 //
 // Kernel bodies are written as HD functions of a flat thread index so that
 // tests/host_emu can execute the same index logic on the CPU (test infrastructure only;
@@ -184,7 +184,8 @@ struct Task {
 };
 
 HD void build_tasks_body(
-    size_t b, const uint32_t *counts, const uint32_t *offsets, const uint32_t *task_off, Task *tasks)
+    size_t b, const uint32_t *counts, const uint32_t *offsets, const uint32_t *task_off, Task *tasks,
+    uint32_t *multi_count, uint32_t *multi_list)
 {
     const uint32_t cnt = counts[b];
     const uint32_t first = task_off[b];
@@ -194,6 +195,13 @@ HD void build_tasks_body(
         tk.start = off + done;
         tk.len = (cnt - done) < (uint32_t)SEG ? (cnt - done) : (uint32_t)SEG;
         tasks[first + s] = tk;
+    }
+    if (cnt > (uint32_t)(COLLAPSE_TASKS * SEG)) { // many tasks: their partial sums are merged by k_collapse
+#if defined(__CUDA_ARCH__)
+        multi_list[atomicAdd(multi_count, 1u)] = (uint32_t)b;
+#else
+        multi_list[(*multi_count)++] = (uint32_t)b;
+#endif
     }
 }
 
@@ -225,13 +233,17 @@ template<class F>
 HD void reduce_chunk_body(
     size_t gidx, const Geometry &g, const uint32_t *task_off, const XYZZ<F> *partial, XYZZ<F> *chunk_out)
 {
+    // chunk_out: where this thread's weighted sum goes (a register/local struct in the kernel)
     XYZZ<F> run = XYZZ<F>::inf();
     XYZZ<F> sum = XYZZ<F>::inf();
     const size_t b0 = gidx * CHUNK;
     for (int k = CHUNK - 1; k >= 0; --k) {
         const uint32_t t0 = task_off[b0 + k];
         const uint32_t t1 = task_off[b0 + k + 1];
-        for (uint32_t t = t0; t < t1; ++t) {
+        // up to COLLAPSE_TASKS partial sums are added here; beyond that k_collapse has already
+        // left the bucket's total in its first task slot
+        const uint32_t tend = (t1 - t0 > (uint32_t)COLLAPSE_TASKS) ? t0 + 1 : t1;
+        for (uint32_t t = t0; t < tend; ++t) {
             const XYZZ<F> s = load_vec(partial + t);
             add_cold(run, s);
         }
@@ -253,26 +265,7 @@ HD void reduce_chunk_body(
         }
         add_cold(sum, acc);
     }
-    store_vec(chunk_out + gidx, sum);
-}
-
-// ---- 8. fold ------------------------------------------------------------------------------------
-// windows: num_shards arrays of W points (shard-major). result = sum_w 2^(c w) sum_shards R_{s,w}.
-template<class F> HD XYZZ<F> fold_windows(const XYZZ<F> *windows, int W, int c, size_t num_shards)
-{
-    XYZZ<F> acc = XYZZ<F>::inf();
-    for (int w = W - 1; w >= 0; --w) {
-        if (!acc.is_inf()) {
-            for (int k = 0; k < c; ++k) {
-                dbl_cold(acc);
-            }
-        }
-        for (size_t s = 0; s < num_shards; ++s) {
-            const XYZZ<F> r = load_vec(windows + s * W + w);
-            add_cold(acc, r);
-        }
-    }
-    return acc;
+    *chunk_out = sum;
 }
 
 // Reference layout of a normalised point: (x, y, one) or zero() = (0, one, 0)
@@ -460,11 +453,12 @@ static __global__ void k_scan_finish(
 }
 
 static __global__ void k_build_tasks(
-    const uint32_t *counts, const uint32_t *offsets, const uint32_t *task_off, uint32_t nb, Task *tasks)
+    const uint32_t *counts, const uint32_t *offsets, const uint32_t *task_off, uint32_t nb, Task *tasks,
+    uint32_t *multi_count, uint32_t *multi_list)
 {
     const size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (b < nb) {
-        build_tasks_body(b, counts, offsets, task_off, tasks);
+        build_tasks_body(b, counts, offsets, task_off, tasks, multi_count, multi_list);
     }
 }
 
@@ -515,55 +509,6 @@ __global__ void __launch_bounds__(ACC_THREADS) k_accumulate(
         const uint32_t id = base + order[tid];
         const Task tk = tasks[id];
         accumulate_task<F>(tk, entries, bases, partial + id);
-    }
-}
-
-template<class F>
-__global__ void __launch_bounds__(128) k_reduce_chunks(
-    Geometry g, const uint32_t *task_off, const XYZZ<F> *partial, XYZZ<F> *chunk_out)
-{
-    const size_t gidx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (gidx < (size_t)g.W * g.cpw) {
-        reduce_chunk_body<F>(gidx, g, task_off, partial, chunk_out);
-    }
-}
-
-// One CTA per window: each thread sums a strided subset of the window's chunk results, then
-// a shared-memory tree.
-constexpr int WSUM_THREADS = 64;
-template<class F>
-__global__ void __launch_bounds__(WSUM_THREADS) k_window_sum(Geometry g, const XYZZ<F> *chunk_out, XYZZ<F> *windows)
-{
-    extern __shared__ uint4 wsum_smem[];
-    XYZZ<F> *sh = reinterpret_cast<XYZZ<F> *>(wsum_smem);
-    const int w = blockIdx.x;
-    XYZZ<F> acc = XYZZ<F>::inf();
-    for (uint32_t i = threadIdx.x; i < g.cpw; i += WSUM_THREADS) {
-        const XYZZ<F> s = load_vec(chunk_out + (size_t)w * g.cpw + i);
-        add_cold(acc, s);
-    }
-    store_vec(sh + threadIdx.x, acc);
-    __syncthreads();
-    for (int stride = WSUM_THREADS / 2; stride >= 1; stride >>= 1) {
-        if ((int)threadIdx.x < stride) {
-            XYZZ<F> a = load_vec(sh + threadIdx.x);
-            const XYZZ<F> b = load_vec(sh + threadIdx.x + stride);
-            add_cold(a, b);
-            store_vec(sh + threadIdx.x, a);
-        }
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-        store_vec(windows + w, load_vec(sh));
-    }
-}
-
-template<class F>
-__global__ void k_fold(const XYZZ<F> *windows, int W, int c, size_t num_shards, RefPoint<F> *out)
-{
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        const XYZZ<F> r = fold_windows<F>(windows, W, c, num_shards);
-        store_vec(out, normalise(r));
     }
 }
 

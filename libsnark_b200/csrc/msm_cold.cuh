@@ -1,0 +1,126 @@
+// msm_cold.cuh — stages 6-7 of the MSM (bucket reduction, window sums): kernels and their
+// launcher. Included only by msm_cold_<curve>_<group>.cu, which are compiled with
+// -DB200_OUTLINE_MUL (see fp.cuh): these kernels are chains of full group additions executed by
+// comparatively few warps, so compact code beats inlined code.
+#pragma once
+#include "msm.cuh"
+#include "runtime.hpp"
+
+namespace b200
+{
+namespace msm
+{
+
+// Warp-level exchange of a point (32-bit shuffles of every limb).
+template<class F> __device__ __forceinline__ XYZZ<F> shfl_down_point(const XYZZ<F> &p, int delta)
+{
+    XYZZ<F> r;
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(&p);
+    uint32_t *dst = reinterpret_cast<uint32_t *>(&r);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(XYZZ<F>) / 4); ++i) {
+        dst[i] = __shfl_down_sync(0xffffffffu, src[i], delta);
+    }
+    return r;
+}
+
+// 5c. Buckets that were cut into several tasks (more than SEG entries: heavy buckets of skewed
+// scalar sets, and the narrow top window) get their partial sums merged here, one warp per
+// bucket: lanes stride over the partials, then a shuffle tree. The total lands in the bucket's
+// first task slot, which is the only one the reduction reads.
+template<class F>
+__global__ void __launch_bounds__(128) k_collapse(const uint32_t *multi_count, const uint32_t *multi_list,
+                                                  const uint32_t *task_off, XYZZ<F> *partial)
+{
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t nmulti = *multi_count;
+    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < nmulti; i += warps) {
+        const uint32_t b = multi_list[i];
+        const uint32_t t0 = task_off[b], t1 = task_off[b + 1];
+        XYZZ<F> acc = XYZZ<F>::inf();
+        for (uint32_t t = t0 + lane; t < t1; t += 32) {
+            const XYZZ<F> s = load_vec(partial + t);
+            add_cold(acc, s);
+        }
+        for (int delta = 16; delta >= 1; delta >>= 1) {
+            const XYZZ<F> other = shfl_down_point(acc, delta);
+            add_cold(acc, other);
+        }
+        if (lane == 0) {
+            store_vec(partial + t0, acc);
+        }
+    }
+}
+
+// 6. One thread per CHUNK buckets (reduce_chunk_body), then a shared-memory tree over the CTA:
+// block_out[blockIdx] = sum of the CTA's weighted chunk sums. g.rb threads, all in one window.
+template<class F>
+__global__ void __launch_bounds__(REDUCE_BLOCK) k_reduce_chunks(
+    Geometry g, const uint32_t *task_off, const XYZZ<F> *partial, XYZZ<F> *block_out)
+{
+    extern __shared__ uint4 reduce_smem[];
+    XYZZ<F> *sh = reinterpret_cast<XYZZ<F> *>(reduce_smem);
+    const size_t gidx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    XYZZ<F> mine;
+    reduce_chunk_body<F>(gidx, g, task_off, partial, &mine);
+    store_vec(sh + threadIdx.x, mine);
+    __syncthreads();
+    for (int stride = (int)blockDim.x / 2; stride >= 1; stride >>= 1) {
+        if ((int)threadIdx.x < stride) {
+            XYZZ<F> a = load_vec(sh + threadIdx.x);
+            const XYZZ<F> b = load_vec(sh + threadIdx.x + stride);
+            add_cold(a, b);
+            store_vec(sh + threadIdx.x, a);
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        store_vec(block_out + blockIdx.x, load_vec(sh));
+    }
+}
+
+// 7. One CTA per window sums the window's g.opw block results.
+constexpr int WSUM_THREADS = 32;
+template<class F>
+__global__ void __launch_bounds__(WSUM_THREADS) k_window_sum(Geometry g, const XYZZ<F> *block_out, XYZZ<F> *windows)
+{
+    const int w = blockIdx.x;
+    XYZZ<F> acc = XYZZ<F>::inf();
+    for (uint32_t i = threadIdx.x; i < g.opw; i += WSUM_THREADS) {
+        const XYZZ<F> s = load_vec(block_out + (size_t)w * g.opw + i);
+        add_cold(acc, s);
+    }
+    for (int delta = 16; delta >= 1; delta >>= 1) {
+        const XYZZ<F> other = shfl_down_point(acc, delta);
+        add_cold(acc, other);
+    }
+    if (threadIdx.x == 0) {
+        store_vec(windows + w, acc);
+    }
+}
+
+template<class F>
+int reduce_launch(const Geometry &g, const uint32_t *task_off, const uint32_t *multi_count,
+                  const uint32_t *multi_list, XYZZ<F> *partial, XYZZ<F> *block_out, XYZZ<F> *windows_dev)
+{
+    cudaStream_t s = rt::stream();
+    k_collapse<F><<<148 * 4, 128, 0, s>>>(multi_count, multi_list, task_off, partial);
+    B200_LAUNCH_CHECK();
+    const size_t nchunks = (size_t)g.W * g.cpw;
+    const size_t smem = (size_t)g.rb * sizeof(XYZZ<F>);
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200_CUDA_CHECK(cudaFuncSetAttribute(k_reduce_chunks<F>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)(REDUCE_BLOCK * sizeof(XYZZ<F>))));
+        attr_set = true;
+    }
+    k_reduce_chunks<F><<<(unsigned)(nchunks / g.rb), g.rb, smem, s>>>(g, task_off, partial, block_out);
+    B200_LAUNCH_CHECK();
+    k_window_sum<F><<<g.W, WSUM_THREADS, 0, s>>>(g, block_out, windows_dev);
+    B200_LAUNCH_CHECK();
+    return B200_OK;
+}
+
+} // namespace msm
+} // namespace b200

@@ -1,0 +1,13 @@
+// msm_cold_alt_bn128_g2.cu — bucket reduction / window sums for alt_bn128 G2 (compiled with
+// -DB200_OUTLINE_MUL, see msm_cold.cuh).
+#include "msm_cold.cuh"
+
+namespace b200
+{
+namespace msm
+{
+typedef group_traits<CURVE_ALT_BN128, GROUP_G2>::F F_;
+template int reduce_launch<F_>(const Geometry &, const uint32_t *, const uint32_t *, const uint32_t *, XYZZ<F_> *,
+                               XYZZ<F_> *, XYZZ<F_> *);
+} // namespace msm
+} // namespace b200

@@ -1,0 +1,13 @@
+// msm_cold_bw6_761_g1.cu — bucket reduction / window sums for bw6_761 G1 (compiled with
+// -DB200_OUTLINE_MUL, see msm_cold.cuh).
+#include "msm_cold.cuh"
+
+namespace b200
+{
+namespace msm
+{
+typedef group_traits<CURVE_BW6_761, GROUP_G1>::F F_;
+template int reduce_launch<F_>(const Geometry &, const uint32_t *, const uint32_t *, const uint32_t *, XYZZ<F_> *,
+                               XYZZ<F_> *, XYZZ<F_> *);
+} // namespace msm
+} // namespace b200

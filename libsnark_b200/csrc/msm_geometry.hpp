@@ -9,7 +9,9 @@ namespace msm
 {
 
 constexpr int SEG = 64;   // max entries per accumulation task
-constexpr int CHUNK = 16; // buckets per reduce thread
+constexpr int COLLAPSE_TASKS = 4; // buckets with more tasks than this are pre-merged by k_collapse
+constexpr int CHUNK = 8;  // buckets per reduce thread
+constexpr int REDUCE_BLOCK = 128; // reduce threads per CTA (all in one window)
 
 struct Geometry {
     uint32_t n;   // points
@@ -18,10 +20,12 @@ struct Geometry {
     uint32_t B;   // buckets per window = 2^(c-1)
     uint32_t NB;  // W * B
     uint32_t cpw; // chunks per window = B / CHUNK
+    uint32_t rb;  // reduce CTA size = min(REDUCE_BLOCK, cpw)
+    uint32_t opw; // reduce CTAs (= partial window sums) per window = cpw / rb
 };
 
-// Window width: minimise  W(c) * (10 n + 42 * 2^(c-1))  field mults (10 per mixed add,
-// ~42 per bucket in the reduction), c in [5, 20].
+// Window width: minimise  W(c) * (10 n + 100 * 2^(c-1))  field mults (10 per mixed add,
+// ~100 per bucket in the reduction as measured: the reduction runs at low occupancy), c in [5, 20].
 inline Geometry make_geometry(uint64_t n, int scalar_bits, int force_c = 0)
 {
     Geometry g;
@@ -30,7 +34,7 @@ inline Geometry make_geometry(uint64_t n, int scalar_bits, int force_c = 0)
     double best = 1e300;
     for (int c = 5; c <= 20; ++c) {
         const int W = (scalar_bits + 1 + c - 1) / c;
-        const double cost = (double)W * (10.0 * (double)n + 42.0 * (double)(1u << (c - 1)));
+        const double cost = (double)W * (10.0 * (double)n + 100.0 * (double)(1u << (c - 1)));
         if (cost < best) {
             best = cost;
             best_c = c;
@@ -41,6 +45,8 @@ inline Geometry make_geometry(uint64_t n, int scalar_bits, int force_c = 0)
     g.B = 1u << (g.c - 1);
     g.NB = (uint32_t)g.W * g.B;
     g.cpw = g.B / CHUNK;
+    g.rb = g.cpw < (uint32_t)REDUCE_BLOCK ? g.cpw : (uint32_t)REDUCE_BLOCK;
+    g.opw = g.cpw / g.rb;
     return g;
 }
 

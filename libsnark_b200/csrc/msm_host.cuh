@@ -1,6 +1,11 @@
 // msm_host.cuh — host-side driver of the MSM pipeline in msm.cuh (stream-ordered launches,
 // no host synchronisation between the stages; the only device->host transfer is the result).
 #pragma once
+#include <chrono>
+#include <cstring>
+#include <vector>
+
+#include "host_fold.hpp"
 #include "msm.cuh"
 #include "runtime.hpp"
 
@@ -10,13 +15,18 @@ namespace msm
 {
 
 struct Workspace {
-    rt::DevBuf t, counts, offsets, cursor, task_off, tile_sums, entries, tasks, partial, chunk_out, staging, any_inf;
+    rt::DevBuf t, counts, offsets, cursor, task_off, tile_sums, entries, tasks, partial, chunk_out, staging, any_inf, multi;
 };
 inline Workspace &workspace()
 {
     static Workspace ws;
     return ws;
 }
+
+// Stages 6-7; defined in msm_cold.cuh and instantiated in msm_cold_<curve>_<group>.cu.
+template<class F>
+int reduce_launch(const Geometry &g, const uint32_t *task_off, const uint32_t *multi_count,
+                  const uint32_t *multi_list, XYZZ<F> *partial, XYZZ<F> *block_out, XYZZ<F> *windows_dev);
 
 inline unsigned grid_for(size_t n, unsigned block) { return (unsigned)((n + block - 1) / block); }
 
@@ -74,7 +84,6 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
     const size_t max_entries = (size_t)g.W * n;
     const size_t max_tasks = (size_t)g.NB + max_entries / SEG + 1;
     const uint32_t ntiles = grid_for(g.NB, SCAN_TILE);
-    const size_t nchunks = (size_t)g.W * g.cpw;
     if (max_entries >= 0x7fffffffull || max_tasks >= 0xffffffffull) {
         return rt::set_error(B200_ERR_ARG, "MSM of %zu points exceeds the 32-bit entry index", n);
     }
@@ -82,7 +91,8 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
         ws.offsets.reserve(((size_t)g.NB + 1) * 4) || ws.cursor.reserve(((size_t)g.NB + 1) * 4) ||
         ws.task_off.reserve(((size_t)g.NB + 1) * 4) || ws.tile_sums.reserve((size_t)ntiles * 8 + 8) ||
         ws.entries.reserve(max_entries * 4 + 16) || ws.tasks.reserve(max_tasks * sizeof(Task)) ||
-        ws.partial.reserve(max_tasks * sizeof(XYZZ<F>)) || ws.chunk_out.reserve(nchunks * sizeof(XYZZ<F>))) {
+        ws.partial.reserve(max_tasks * sizeof(XYZZ<F>)) ||
+        ws.chunk_out.reserve(((size_t)g.W * g.opw) * sizeof(XYZZ<F>)) || ws.multi.reserve(((size_t)g.NB + 4) * 4)) {
         return B200_ERR_CUDA;
     }
     const Affine<F> *bases = static_cast<const Affine<F> *>(bs.pts) + first;
@@ -97,10 +107,13 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
     Task *tasks = ws.tasks.as<Task>();
     XYZZ<F> *partial = ws.partial.as<XYZZ<F>>();
     XYZZ<F> *chunk_out = ws.chunk_out.as<XYZZ<F>>();
+    uint32_t *multi_count = ws.multi.as<uint32_t>();
+    uint32_t *multi_list = multi_count + 4;
 
     B200_CUDA_CHECK(cudaEventRecord(tm.ev[0], s));
     // 1-4: digits and counting sort
     B200_CUDA_CHECK(cudaMemsetAsync(counts, 0, ((size_t)g.NB + 1) * 4, s));
+    B200_CUDA_CHECK(cudaMemsetAsync(multi_count, 0, 16, s));
     const Limbs<NL> K = make_offset_constant<NL>(g);
     k_prepare<Fr><<<grid_for(n, 256), 256, 0, s>>>(static_cast<const Fr *>(scalars_dev), t, n, K, inf);
     B200_LAUNCH_CHECK();
@@ -114,7 +127,7 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
     B200_LAUNCH_CHECK();
     k_scatter<<<grid_for(n, 256), 256, 0, s>>>(t, NL, g, cursor, entries);
     B200_LAUNCH_CHECK();
-    k_build_tasks<<<grid_for(g.NB, 256), 256, 0, s>>>(counts, offsets, task_off, g.NB, tasks);
+    k_build_tasks<<<grid_for(g.NB, 256), 256, 0, s>>>(counts, offsets, task_off, g.NB, tasks, multi_count, multi_list);
     B200_LAUNCH_CHECK();
     B200_CUDA_CHECK(cudaEventRecord(tm.ev[1], s));
     // 5: bucket accumulation (grid sized for the task upper bound; surplus CTAs exit at once)
@@ -123,29 +136,37 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
     B200_LAUNCH_CHECK();
     B200_CUDA_CHECK(cudaEventRecord(tm.ev[2], s));
     // 6-7: bucket reduction
-    k_reduce_chunks<F><<<grid_for(nchunks, 128), 128, 0, s>>>(g, task_off, partial, chunk_out);
-    B200_LAUNCH_CHECK();
-    const size_t wsum_smem = (size_t)WSUM_THREADS * sizeof(XYZZ<F>);
-    static bool attr_set = false;
-    if (!attr_set) {
-        B200_CUDA_CHECK(cudaFuncSetAttribute(
-            k_window_sum<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsum_smem));
-        attr_set = true;
+    {
+        const int rc = reduce_launch<F>(g, task_off, multi_count, multi_list, partial, chunk_out,
+                                         static_cast<XYZZ<F> *>(windows_dev));
+        if (rc) {
+            return rc;
+        }
     }
-    k_window_sum<F><<<g.W, WSUM_THREADS, wsum_smem, s>>>(g, chunk_out, static_cast<XYZZ<F> *>(windows_dev));
-    B200_LAUNCH_CHECK();
     B200_CUDA_CHECK(cudaEventRecord(tm.ev[3], s));
     return B200_OK;
 }
 
-template<class F> int msm_fold(const void *windows_dev, int W, int c, size_t shards, void *out_dev)
+// Stage 8 on the host (host_fold.hpp). `windows` holds shards * W points; when on_device it is
+// first copied back (2 KB for alt_bn128 G1). out: one normalised point, host memory.
+template<class F> int msm_fold(const void *windows, int on_device, int W, int c, size_t shards, void *out)
 {
-    cudaStream_t s = rt::stream();
-    k_fold<F><<<1, 32, 0, s>>>(static_cast<const XYZZ<F> *>(windows_dev), W, c, shards, static_cast<RefPoint<F> *>(out_dev));
-    B200_LAUNCH_CHECK();
+    const size_t count = (size_t)W * shards;
+    std::vector<XYZZ<F>> host(count);
     rt::MsmTiming &tm = rt::msm_timing();
-    B200_CUDA_CHECK(cudaEventRecord(tm.ev[4], s));
-    tm.valid = true;
+    if (on_device) {
+        cudaStream_t s = rt::stream();
+        B200_CUDA_CHECK(cudaMemcpyAsync(host.data(), windows, count * sizeof(XYZZ<F>), cudaMemcpyDeviceToHost, s));
+        B200_CUDA_CHECK(cudaEventRecord(tm.ev[4], s));
+        B200_CUDA_CHECK(cudaStreamSynchronize(s));
+        tm.valid = true;
+    } else {
+        memcpy(host.data(), windows, count * sizeof(XYZZ<F>));
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    const RefPoint<F> r = host_fold<F>(host.data(), W, c, shards);
+    tm.host_fold_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    memcpy(out, &r, sizeof(r));
     return B200_OK;
 }
 
@@ -163,9 +184,9 @@ template<class F> int msm_fold(const void *windows_dev, int W, int c, size_t sha
         return msm::msm_windows<group_traits<CURVE, GROUP>::Fr, group_traits<CURVE, GROUP>::F>(                \
             bs, first, n, scalars_dev, windows_dev, W, c);                                                     \
     }                                                                                                          \
-    int name##_msm_fold(const void *windows_dev, int W, int c, size_t shards, void *out_dev)                  \
+    int name##_msm_fold(const void *windows, int on_device, int W, int c, size_t shards, void *out)           \
     {                                                                                                          \
-        return msm::msm_fold<group_traits<CURVE, GROUP>::F>(windows_dev, W, c, shards, out_dev);               \
+        return msm::msm_fold<group_traits<CURVE, GROUP>::F>(windows, on_device, W, c, shards, out);            \
     }                                                                                                          \
     size_t name##_window_point_bytes() { return sizeof(XYZZ<group_traits<CURVE, GROUP>::F>); }                 \
     int name##_scalar_bits() { return group_traits<CURVE, GROUP>::Fr::params::BITS; }

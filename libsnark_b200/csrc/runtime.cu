@@ -171,14 +171,15 @@ int b200_last_msm_timing(double *ms5)
         return rt::set_error(B200_ERR_ARG, "no MSM has run yet");
     }
     B200_CUDA_CHECK(cudaEventSynchronize(tm.ev[4]));
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < 3; ++i) {
         float ms = 0;
         B200_CUDA_CHECK(cudaEventElapsedTime(&ms, tm.ev[i], tm.ev[i + 1]));
         ms5[i] = ms;
     }
     float tot = 0;
     B200_CUDA_CHECK(cudaEventElapsedTime(&tot, tm.ev[0], tm.ev[4]));
-    ms5[4] = tot;
+    ms5[3] = tm.host_fold_ms;
+    ms5[4] = tot + tm.host_fold_ms;
     return B200_OK;
 }
 

@@ -58,7 +58,8 @@ struct BaseSet {
 };
 
 struct MsmTiming {
-    cudaEvent_t ev[5];
+    cudaEvent_t ev[5]; // start | sorted | accumulated | reduced | windows on host
+    double host_fold_ms = 0;
     bool valid = false;
 };
 MsmTiming &msm_timing();
@@ -72,7 +73,7 @@ MsmTiming &msm_timing();
                             rt::BaseSet *out);                                                     \
     int name##_msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scalars_dev, \
                            void *windows_dev, int *W, int *c);                                     \
-    int name##_msm_fold(const void *windows_dev, int W, int c, size_t shards, void *out_dev);     \
+    int name##_msm_fold(const void *windows, int on_device, int W, int c, size_t shards, void *out); \
     size_t name##_window_point_bytes();                                                            \
     int name##_scalar_bits();
 
