@@ -93,9 +93,13 @@ int b200_msm_resident(b200_bases_t handle, size_t first, size_t n, const void *s
  * between ranks. b200_msm_fold_windows folds `num_shards` such arrays (concatenated,
  * all from shards of the same size class n_per_shard) into the final normalised point. */
 int b200_msm_num_windows(int curve, size_t n);
+int b200_msm_window_bits(int curve, size_t n);
 size_t b200_msm_window_bytes(int curve, int group);
 int b200_msm_resident_windows(b200_bases_t handle, size_t first, size_t n, const void *scalars,
                               int scalars_on_device, void *out_windows);
+/* Same, leaving the window sums in device memory (e.g. a torch CUDA tensor that NCCL gathers). */
+int b200_msm_resident_windows_dev(b200_bases_t handle, size_t first, size_t n, const void *scalars,
+                                  int scalars_on_device, void *dev_out_windows);
 int b200_msm_fold_windows(int curve, int group, size_t n_per_shard, const void *windows,
                           size_t num_shards, void *out);
 
@@ -140,6 +144,14 @@ int b200_imad_peak(int iters, double *wide_mads_per_s, double *lo_mads_per_s);
 /* Time (ms, CUDA events on the library stream) of the last MSM's kernels:
  * [0] scalar prep+sort, [1] bucket accumulation, [2] bucket reduction, [3] fold, [4] total */
 int b200_last_msm_timing(double *ms5);
+/* CUDA-event stopwatch on the library's stream (device time of everything launched between). */
+int b200_timer_start(void);
+int b200_timer_stop(double *ms);
+/* Synthetic bases for benchmarks: out_host[i] = [k0 + i] * generator, i < n (k0 >= 1), affine,
+ * reference layout; computed on the device. */
+int b200_make_bases(int curve, int group, uint64_t k0, size_t n, void *out_host);
+/* Wide multiply-adds per second of carry-chained IMAD.WIDE.X (valid after b200_imad_peak). */
+double b200_imad_carry_peak(void);
 /* Number of kernels this library has launched since b200_init (bench.py's gpu_launches). */
 uint64_t b200_launch_count(void);
 

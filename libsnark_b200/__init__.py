@@ -31,10 +31,11 @@ EXPORTS = [
     "b200_version", "b200_init", "b200_device_count", "b200_last_error", "b200_sizeof_fr", "b200_sizeof_group",
     "b200_dev_alloc", "b200_dev_free", "b200_memcpy_h2d", "b200_memcpy_d2h", "b200_sync",
     "b200_msm", "b200_bases_upload", "b200_bases_free", "b200_bases_size", "b200_msm_resident",
-    "b200_msm_num_windows", "b200_msm_window_bytes", "b200_msm_resident_windows", "b200_msm_fold_windows",
+    "b200_msm_num_windows", "b200_msm_window_bits", "b200_msm_window_bytes", "b200_msm_resident_windows", "b200_msm_fold_windows",
     "b200_msm_filter_one_zero", "b200_kc_msm",
     "b200_ntt", "b200_ntt_dev", "b200_divide_by_Z_on_coset", "b200_witness_map_h", "b200_witness_map_h_dev",
-    "b200_imad_peak", "b200_last_msm_timing", "b200_launch_count",
+    "b200_msm_resident_windows_dev", "b200_timer_start", "b200_timer_stop", "b200_make_bases",
+    "b200_imad_carry_peak", "b200_imad_peak", "b200_last_msm_timing", "b200_launch_count",
 ]
 
 
@@ -77,6 +78,7 @@ def lib():
         L.b200_bases_size.argtypes = [u64]
         L.b200_msm_resident.argtypes = [u64, sz, sz, vp, i, vp]
         L.b200_msm_num_windows.argtypes = [i, sz]
+        L.b200_msm_window_bits.argtypes = [i, sz]
         L.b200_msm_window_bytes.restype = sz
         L.b200_msm_window_bytes.argtypes = [i, i]
         L.b200_msm_resident_windows.argtypes = [u64, sz, sz, vp, i, vp]
@@ -91,6 +93,10 @@ def lib():
         L.b200_imad_peak.argtypes = [i, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.b200_last_msm_timing.argtypes = [C.POINTER(C.c_double)]
         L.b200_launch_count.restype = u64
+        L.b200_msm_resident_windows_dev.argtypes = [u64, sz, sz, vp, i, vp]
+        L.b200_timer_stop.argtypes = [C.POINTER(C.c_double)]
+        L.b200_make_bases.argtypes = [i, i, u64, sz, vp]
+        L.b200_imad_carry_peak.restype = C.c_double
         L.b200_test_field_op.argtypes = [i, i, i, vp, vp, vp, sz]
         L.b200_test_fp_convert.argtypes = [i, i, i, vp, vp, sz]
         L.b200_test_group_op.argtypes = [i, i, i, vp, vp, vp, sz]
@@ -208,6 +214,16 @@ class ResidentBases:
             _check(lib().b200_msm_resident_windows(self.handle, first, n, _p(scalars), 0, _p(out)))
         return out
 
+    def window_sums_dev(self, dev_out, scalars=None, first=0, n=None, device_ptr=None):
+        """Window sums left in device memory at address dev_out (e.g. a torch CUDA tensor)."""
+        n = self.n - first if n is None else n
+        if device_ptr is not None:
+            _check(lib().b200_msm_resident_windows_dev(self.handle, first, n, C.c_void_p(device_ptr), 1,
+                                                       C.c_void_p(dev_out)))
+        else:
+            scalars = _u64(scalars)
+            _check(lib().b200_msm_resident_windows_dev(self.handle, first, n, _p(scalars), 0, C.c_void_p(dev_out)))
+
     def free(self):
         if self.handle:
             _check(lib().b200_bases_free(self.handle))
@@ -228,11 +244,42 @@ def last_msm_timing():
     return dict(zip(["sort", "accumulate", "reduce", "fold", "total"], list(ms)))
 
 
+def timer_start():
+    _check(lib().b200_timer_start())
+
+
+def timer_stop():
+    ms = C.c_double(0)
+    _check(lib().b200_timer_stop(C.byref(ms)))
+    return ms.value
+
+
+def make_bases(curve, group, n, k0=1):
+    """n distinct affine points [k0 + i] * generator in the reference layout, generated on the device."""
+    c = _cid(curve)
+    out = np.zeros((n, sizeof_group(c, group) // 8), dtype=np.uint64)
+    _check(lib().b200_make_bases(c, group, k0, n, _p(out)))
+    return out
+
+
+def random_scalars(curve, n, seed=0):
+    """n uniformly random Fr residues (any value < r is a valid Montgomery representative)."""
+    c = _cid(curve)
+    r = {ALT_BN128: 0x30644e72e131a029b85045b68181585d2833e84879b9709143e1f593f0000001,
+         BLS12_377: 0x12ab655e9a2ca55660b44d1e5c37b00159aa76fed00000010a11800000000001,
+         BW6_761: 0x1ae3a4617c510eac63b05c06ca1493b1a22d9f300f5138f1ef3622fba094800170b5d44300000008508c00000000001}[c]
+    L = sizeof_fr(c) // 8
+    rng = np.random.default_rng(seed)
+    a = rng.integers(0, 1 << 64, size=(n, L), dtype=np.uint64)
+    top = r >> (64 * (L - 1))
+    a[:, L - 1] %= np.uint64(top)  # top limb strictly below r's top limb -> value < r
+    return a
+
+
 def imad_peak(iters=4096):
     """(IMAD.WIDE no carry, IMAD lo, IMAD.WIDE.X carry chains) multiply-adds per second."""
     w, lo = C.c_double(0), C.c_double(0)
     _check(lib().b200_imad_peak(iters, C.byref(w), C.byref(lo)))
-    lib().b200_imad_carry_peak.restype = C.c_double
     return w.value, lo.value, lib().b200_imad_carry_peak()
 
 

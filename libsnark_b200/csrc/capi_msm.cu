@@ -72,7 +72,7 @@ void write_zero_point(int curve, int group, void *out)
 }
 
 int msm_resident_impl(const rt::BaseSet &bs, size_t first, size_t n, const void *scalars, int on_device,
-                      void *out, void *out_windows)
+                      void *out, void *out_windows, void *dev_out_windows = nullptr)
 {
     const CurveVt *v = vt(bs.curve);
     if (first + n > bs.n) {
@@ -109,6 +109,9 @@ int msm_resident_impl(const rt::BaseSet &bs, size_t first, size_t n, const void 
     }
     if (out_windows) {
         B200_CUDA_CHECK(cudaMemcpyAsync(out_windows, g_windows.p, (size_t)W * wbytes, cudaMemcpyDeviceToHost, s));
+    }
+    if (dev_out_windows) {
+        B200_CUDA_CHECK(cudaMemcpyAsync(dev_out_windows, g_windows.p, (size_t)W * wbytes, cudaMemcpyDeviceToDevice, s));
     }
     if (out) {
         rc = v->grp(bs.group).msm_fold(g_windows.p, 1, W, c, 1, out);
@@ -252,6 +255,15 @@ int b200_msm_num_windows(int curve, size_t n)
     return msm::make_geometry(n, v->scalar_bits()).W;
 }
 
+int b200_msm_window_bits(int curve, size_t n)
+{
+    const CurveVt *v = vt(curve);
+    if (!v) {
+        return B200_ERR_ARG;
+    }
+    return msm::make_geometry(n, v->scalar_bits()).c;
+}
+
 size_t b200_msm_window_bytes(int curve, int group)
 {
     const CurveVt *v = vt(curve);
@@ -270,6 +282,20 @@ int b200_msm_resident_windows(b200_bases_t handle, size_t first, size_t n, const
         return rt::set_error(B200_ERR_ARG, "null pointer or empty range");
     }
     return msm_resident_impl(it->second, first, n, scalars, scalars_on_device, nullptr, out_windows);
+}
+
+int b200_msm_resident_windows_dev(b200_bases_t handle, size_t first, size_t n, const void *scalars,
+                                  int scalars_on_device, void *dev_out_windows)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_sets.find(handle);
+    if (it == g_sets.end()) {
+        return rt::set_error(B200_ERR_HANDLE, "unknown base-set handle %llu", (unsigned long long)handle);
+    }
+    if (!dev_out_windows || !scalars || n == 0) {
+        return rt::set_error(B200_ERR_ARG, "null pointer or empty range");
+    }
+    return msm_resident_impl(it->second, first, n, scalars, scalars_on_device, nullptr, nullptr, dev_out_windows);
 }
 
 int b200_msm_fold_windows(int curve, int group, size_t n_per_shard, const void *windows, size_t num_shards, void *out)

@@ -17,6 +17,7 @@ int g_device = -1;
 cudaStream_t g_stream = nullptr;
 std::atomic<uint64_t> g_launches{0};
 MsmTiming g_timing;
+cudaEvent_t g_timer[2] = {nullptr, nullptr};
 } // namespace
 
 int set_error(int code, const char *fmt, ...)
@@ -159,6 +160,33 @@ int b200_sync(void)
         return B200_ERR_CUDA;
     }
     B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
+    return B200_OK;
+}
+
+int b200_timer_start(void)
+{
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    if (!rt::g_timer[0]) {
+        B200_CUDA_CHECK(cudaEventCreate(&rt::g_timer[0]));
+        B200_CUDA_CHECK(cudaEventCreate(&rt::g_timer[1]));
+    }
+    B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
+    B200_CUDA_CHECK(cudaEventRecord(rt::g_timer[0], rt::stream()));
+    return B200_OK;
+}
+
+int b200_timer_stop(double *ms)
+{
+    if (!ms || !rt::g_timer[0]) {
+        return rt::set_error(B200_ERR_ARG, "timer not started");
+    }
+    B200_CUDA_CHECK(cudaEventRecord(rt::g_timer[1], rt::stream()));
+    B200_CUDA_CHECK(cudaEventSynchronize(rt::g_timer[1]));
+    float f = 0;
+    B200_CUDA_CHECK(cudaEventElapsedTime(&f, rt::g_timer[0], rt::g_timer[1]));
+    *ms = f;
     return B200_OK;
 }
 
