@@ -1,0 +1,102 @@
+"""ctypes binding of oracle/liboracle_port.so (oracle_port.c: the plain-C restatement of the
+reference's algorithms) — TEST INFRASTRUCTURE ONLY. Same array conventions as oracle/refo.py."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+CURVES = {"alt_bn128": 0, "bls12_377": 1, "bw6_761": 2}
+NR = {0: 4, 1: 4, 2: 6}
+NQ = {0: 4, 1: 6, 2: 12}
+G2_FQ2 = {0: True, 1: True, 2: False}
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _cid(curve):
+    return CURVES[curve] if isinstance(curve, str) else int(curve)
+
+
+class OraclePort:
+    def __init__(self, path=None):
+        path = path or os.path.join(_HERE, "liboracle_port.so")
+        if not os.path.exists(path):
+            subprocess.run(["make", "-C", _HERE, "port"], check=True, stdout=subprocess.DEVNULL)
+        self.lib = L = C.CDLL(path)
+        vp, sz, i = C.c_void_p, C.c_size_t, C.c_int
+        L.port_msm.argtypes = [i, i, i, vp, sz, sz, vp, vp]
+        L.port_kc_msm.argtypes = [i, vp, vp, sz, sz, sz, vp, vp, vp]
+        L.port_signed_digits.argtypes = [i, vp, sz, sz, sz, vp]
+        L.port_bdlo12_signed_optimal_c.restype = C.c_uint64
+        L.port_bdlo12_signed_optimal_c.argtypes = [C.c_uint64]
+        L.port_fft.argtypes = [i, i, vp, sz, vp]
+        L.port_witness_map_h.argtypes = [i, vp, vp, vp, sz, vp]
+        L.port_field_op.argtypes = [i, i, i, vp, vp, vp, sz]
+        L.port_group_op.argtypes = [i, i, i, vp, vp, vp, sz]
+
+    def group_limbs(self, curve, group):
+        c = _cid(curve)
+        return 3 * NQ[c] * (2 if (group == 2 and G2_FQ2[c]) else 1)
+
+    def msm(self, curve, group, bases, scalars, method=0, stride=None):
+        c = _cid(curve)
+        bases = np.ascontiguousarray(bases, dtype=np.uint64)
+        scalars = np.ascontiguousarray(scalars, dtype=np.uint64)
+        n = scalars.shape[0]
+        out = np.zeros(self.group_limbs(c, group), dtype=np.uint64)
+        stride = stride if stride is not None else (bases.strides[0] if bases.ndim == 2 else 0)
+        assert self.lib.port_msm(c, group, method, _p(bases), stride, n, _p(scalars), _p(out)) == 0
+        return out
+
+    def kc_msm(self, curve, indices, values, min_idx, max_idx, scalars):
+        c = _cid(curve)
+        indices = np.ascontiguousarray(indices, dtype=np.uint64)
+        values = np.ascontiguousarray(values, dtype=np.uint64)
+        scalars = np.ascontiguousarray(scalars, dtype=np.uint64)
+        g2 = np.zeros(self.group_limbs(c, 2), dtype=np.uint64)
+        g1 = np.zeros(self.group_limbs(c, 1), dtype=np.uint64)
+        assert self.lib.port_kc_msm(c, _p(indices), _p(values), indices.shape[0], min_idx, max_idx, _p(scalars),
+                                    _p(g2), _p(g1)) == 0
+        return g2, g1
+
+    def signed_digits(self, curve, scalars, c, num_digits):
+        scalars = np.ascontiguousarray(scalars, dtype=np.uint64)
+        out = np.zeros((scalars.shape[0], num_digits), dtype=np.int64)
+        assert self.lib.port_signed_digits(_cid(curve), _p(scalars), scalars.shape[0], c, num_digits, _p(out)) == 0
+        return out
+
+    def optimal_c(self, n):
+        return int(self.lib.port_bdlo12_signed_optimal_c(n))
+
+    def fft(self, curve, op, data, g=None):
+        a = np.array(data, dtype=np.uint64, order="C", copy=True)
+        g_ = None if g is None else np.ascontiguousarray(g, dtype=np.uint64)
+        rc = self.lib.port_fft(_cid(curve), op, _p(a), a.shape[0], _p(g_))
+        if rc:
+            raise RuntimeError(f"port_fft rc={rc}")
+        return a
+
+    def witness_map_h(self, curve, aA, aB, aC):
+        aA, aB, aC = (np.ascontiguousarray(x, dtype=np.uint64) for x in (aA, aB, aC))
+        m = aA.shape[0]
+        out = np.zeros((m + 1, aA.shape[1]), dtype=np.uint64)
+        assert self.lib.port_witness_map_h(_cid(curve), _p(aA), _p(aB), _p(aC), m, _p(out)) == 0
+        return out
+
+    def field_op(self, curve, field, op, a, b=None):
+        a = np.ascontiguousarray(a, dtype=np.uint64)
+        b = a if b is None else np.ascontiguousarray(b, dtype=np.uint64)
+        out = np.zeros_like(a)
+        assert self.lib.port_field_op(_cid(curve), field, op, _p(a), _p(b), _p(out), a.shape[0]) == 0
+        return out
+
+    def group_op(self, curve, group, op, a, b=None):
+        a = np.ascontiguousarray(a, dtype=np.uint64)
+        b = a if b is None else np.ascontiguousarray(b, dtype=np.uint64)
+        out = np.zeros_like(a)
+        assert self.lib.port_group_op(_cid(curve), group, op, _p(a), _p(b), _p(out), a.shape[0]) == 0
+        return out

@@ -4,8 +4,11 @@
 // against the reference on a machine without a GPU. Not linked into the product library.
 #include <cstdint>
 #include <cstring>
+#include <vector>
 
 #include "curves.cuh"
+#include "host_fold.hpp"
+#include "msm.cuh"
 
 using namespace b200;
 
@@ -131,6 +134,109 @@ extern "C" int emu_group_op(int curve, int group, int op, const void *a, const v
     case 6: return group_op<bls12_377_fq2>(op, a, b, o, n);
     case 9: return group_op<bw6_761_fq>(op, a, b, o, n);
     case 10: return group_op<bw6_761_fq>(op, a, b, o, n);
+    }
+    return -100;
+}
+
+
+// ---- MSM index logic (msm.cuh bodies) on the host -------------------------------------------
+// Signed window digits as the device computes them (prepare_body: from_mont + offset constant K,
+// then window_digit), for comparison with libff's field_get_signed_digit.
+template<class Fr> static int signed_digits(const void *scalars, size_t n, int c, int64_t *out, int *W_out)
+{
+    msm::Geometry g = msm::make_geometry(n, Fr::params::BITS, c);
+    *W_out = g.W;
+    const msm::Limbs<Fr::N> K = msm::make_offset_constant<Fr::N>(g);
+    std::vector<uint32_t> t(n * Fr::N);
+    for (size_t i = 0; i < n; ++i) {
+        msm::prepare_body<Fr>(i, (const Fr *)scalars, t.data(), K, nullptr);
+        for (int w = 0; w < g.W; ++w) {
+            out[i * g.W + w] = msm::window_digit(t.data() + i * Fr::N, Fr::N, g, w);
+        }
+    }
+    return 0;
+}
+
+extern "C" int emu_signed_digits(int curve, const void *scalars, size_t n, int c, int64_t *out, int *W_out)
+{
+    switch (curve) {
+    case 0: return signed_digits<alt_bn128_fr>(scalars, n, c, out, W_out);
+    case 1: return signed_digits<bls12_377_fr>(scalars, n, c, out, W_out);
+    case 2: return signed_digits<bw6_761_fr>(scalars, n, c, out, W_out);
+    }
+    return -100;
+}
+
+// The whole MSM pipeline of msm.cuh executed sequentially on the host (same bodies, same index
+// logic: histogram -> scan -> scatter -> tasks -> accumulate -> reduce -> fold).
+template<class Fr, class F> static int msm_emulated(const void *bases_ref, size_t n, const void *scalars, int force_c, void *out)
+{
+    using namespace msm;
+    Geometry g = make_geometry(n, Fr::params::BITS, force_c);
+    const Limbs<Fr::N> K = make_offset_constant<Fr::N>(g);
+    std::vector<Affine<F>> bases(n);
+    std::vector<uint8_t> inf(n);
+    uint32_t any = 0;
+    for (size_t i = 0; i < n; ++i) {
+        convert_base_body<F>(i, (const uint8_t *)bases_ref, sizeof(RefPoint<F>), bases.data(), inf.data(), &any);
+    }
+    std::vector<uint32_t> t(n * Fr::N), counts(g.NB + 1, 0), offsets(g.NB + 1), cursor(g.NB + 1), task_off(g.NB + 1);
+    for (size_t i = 0; i < n; ++i) {
+        prepare_body<Fr>(i, (const Fr *)scalars, t.data(), K, any ? inf.data() : nullptr);
+    }
+    for (size_t i = 0; i < n; ++i) {
+        histogram_body(i, t.data(), Fr::N, g, counts.data());
+    }
+    uint32_t off = 0, toff = 0;
+    for (uint32_t b = 0; b < g.NB; ++b) {
+        offsets[b] = cursor[b] = off;
+        task_off[b] = toff;
+        off += counts[b];
+        toff += (counts[b] + SEG - 1) / SEG;
+    }
+    offsets[g.NB] = off;
+    task_off[g.NB] = toff;
+    std::vector<uint32_t> entries(off + 1), multi_list(g.NB + 1);
+    uint32_t multi_count = 0;
+    for (size_t i = 0; i < n; ++i) {
+        scatter_body(i, t.data(), Fr::N, g, cursor.data(), entries.data());
+    }
+    std::vector<Task> tasks(toff + 1);
+    for (size_t b = 0; b < g.NB; ++b) {
+        build_tasks_body(b, counts.data(), offsets.data(), task_off.data(), tasks.data(), &multi_count, multi_list.data());
+    }
+    std::vector<XYZZ<F>> partial(toff + 1);
+    for (uint32_t k = 0; k < toff; ++k) {
+        accumulate_task<F>(tasks[k], entries.data(), bases.data(), &partial[k]);
+    }
+    for (uint32_t k = 0; k < multi_count; ++k) { // k_collapse
+        const uint32_t b = multi_list[k];
+        XYZZ<F> acc = XYZZ<F>::inf();
+        for (uint32_t q = task_off[b]; q < task_off[b + 1]; ++q) {
+            add(acc, partial[q]);
+        }
+        partial[task_off[b]] = acc;
+    }
+    std::vector<XYZZ<F>> windows(g.W, XYZZ<F>::inf());
+    for (size_t gidx = 0; gidx < (size_t)g.W * g.cpw; ++gidx) {
+        XYZZ<F> s;
+        reduce_chunk_body<F>(gidx, g, task_off.data(), partial.data(), &s);
+        add(windows[gidx / g.cpw], s);
+    }
+    const RefPoint<F> r = host_fold<F>(windows.data(), g.W, g.c, 1);
+    memcpy(out, &r, sizeof(r));
+    return 0;
+}
+
+extern "C" int emu_msm(int curve, int group, const void *bases, size_t n, const void *scalars, int force_c, void *out)
+{
+    switch (curve * 4 + group) {
+    case 1: return msm_emulated<alt_bn128_fr, alt_bn128_fq>(bases, n, scalars, force_c, out);
+    case 2: return msm_emulated<alt_bn128_fr, alt_bn128_fq2>(bases, n, scalars, force_c, out);
+    case 5: return msm_emulated<bls12_377_fr, bls12_377_fq>(bases, n, scalars, force_c, out);
+    case 6: return msm_emulated<bls12_377_fr, bls12_377_fq2>(bases, n, scalars, force_c, out);
+    case 9:
+    case 10: return msm_emulated<bw6_761_fr, bw6_761_fq>(bases, n, scalars, force_c, out);
     }
     return -100;
 }

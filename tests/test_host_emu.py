@@ -1,0 +1,123 @@
+"""CPU tier: the DEVICE formulation executed on the host. tests/host_emu/emu.cpp compiles the product's
+field / curve / MSM-index templates (libsnark_b200/csrc/{fp,curve,msm}.cuh) with
+-DB200_HOST_EMULATE_PRIMS, i.e. the 32-bit mad.cc carry chains run through a bit-exact emulation of the
+PTX carry flag and the kernel bodies run as plain loops. Checked against the golden vectors produced by
+the unmodified reference. This pins, without a GPU: the Montgomery carry chains, the XYZZ group law
+incl. its exceptional cases, the K-offset signed-digit extraction (== libff field_get_signed_digit) and
+the bucket/task/reduction index logic."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = os.path.join(HERE, "golden")
+EMU_DIR = os.path.join(HERE, "host_emu")
+CSRC = os.path.join(os.path.dirname(HERE), "libsnark_b200", "csrc")
+CURVES = {"alt_bn128": 0, "bls12_377": 1, "bw6_761": 2}
+BITS = {"alt_bn128": 254, "bls12_377": 253, "bw6_761": 377}
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+@pytest.fixture(scope="module")
+def emu():
+    so = os.path.join(EMU_DIR, "libemu.so")
+    src = os.path.join(EMU_DIR, "emu.cpp")
+    hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".hpp"))]
+    if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(f) for f in hdrs + [src]):
+        subprocess.run(["g++", "-std=c++17", "-O1", "-shared", "-fPIC", "-DB200_HOST_EMULATE_PRIMS", "-I", CSRC,
+                        "-o", so, src], check=True)
+    L = C.CDLL(so)
+    vp, sz, i = C.c_void_p, C.c_size_t, C.c_int
+    L.emu_field_op.argtypes = [i, i, i, vp, vp, vp, sz]
+    L.emu_fp_convert.argtypes = [i, i, i, vp, vp, sz]
+    L.emu_group_op.argtypes = [i, i, i, vp, vp, vp, sz]
+    L.emu_signed_digits.argtypes = [i, vp, sz, i, vp, C.POINTER(C.c_int)]
+    L.emu_msm.argtypes = [i, i, vp, sz, vp, i, vp]
+    return L
+
+
+@pytest.mark.parametrize("curve", list(CURVES))
+def test_emulated_field_ops(emu, curve):
+    g = np.load(os.path.join(GOLD, "fields.npz"))
+    for fname, fid in [("fr", 0), ("fq", 1), ("fq2", 2)]:
+        k = f"{curve}.{fname}"
+        if k + ".a" not in g:
+            continue
+        a, b = np.ascontiguousarray(g[k + ".a"]), np.ascontiguousarray(g[k + ".b"])
+        for oname, op in [("add", 0), ("sub", 1), ("mul", 2), ("sqr", 3), ("neg", 4), ("inv", 5)]:
+            out = np.zeros_like(a)
+            assert emu.emu_field_op(CURVES[curve], fid, op, _p(a), _p(b), _p(out), a.shape[0]) == 0
+            assert np.array_equal(out, g[f"{k}.{oname}"]), (k, oname)
+
+
+@pytest.mark.parametrize("curve", list(CURVES))
+def test_emulated_group_law(emu, curve):
+    g = np.load(os.path.join(GOLD, "groups.npz"))
+    for gname, gid in [("g1", 1), ("g2", 2)]:
+        k = f"{curve}.{gname}"
+        a, b = np.ascontiguousarray(g[k + ".a"]), np.ascontiguousarray(g[k + ".b"])
+        for op, want in [(0, "add"), (1, "add"), (2, "dbl")]:
+            out = np.zeros_like(a)
+            assert emu.emu_group_op(CURVES[curve], gid, op, _p(a), _p(b), _p(out), a.shape[0]) == 0
+            assert np.array_equal(out, g[f"{k}.{want}"]), (k, op)
+
+
+@pytest.mark.parametrize("curve", list(CURVES))
+def test_device_digit_extraction_equals_libff(emu, curve):
+    """msm.cuh window_digit over t = s + K  ==  libff field_get_signed_digit (field_utils.tcc:82-115)."""
+    g = np.load(os.path.join(GOLD, "digits.npz"))
+    sc = np.ascontiguousarray(g[f"{curve}.scalars"])
+    for c in [5, 12, 13, 16]:
+        want = g[f"{curve}.c{c}"]
+        W = C.c_int(0)
+        out = np.zeros((sc.shape[0], 512), dtype=np.int64)
+        flat = np.zeros(sc.shape[0] * 512, dtype=np.int64)
+        assert emu.emu_signed_digits(CURVES[curve], _p(sc), sc.shape[0], c, _p(flat), C.byref(W)) == 0
+        out = flat[: sc.shape[0] * W.value].reshape(sc.shape[0], W.value)
+        assert W.value == (BITS[curve] + 1 + c - 1) // c
+        k = min(W.value, want.shape[1])
+        assert np.array_equal(out[:, :k], want[:, :k]), c
+        assert not want[:, k:].any() and not out[:, k:].any()
+
+
+def _emu_msm(emu, curve, gid, bases, scalars, force_c=0):
+    bases, scalars = np.ascontiguousarray(bases), np.ascontiguousarray(scalars)
+    out = np.zeros(bases.shape[1], dtype=np.uint64)
+    assert emu.emu_msm(CURVES[curve], gid, _p(bases), scalars.shape[0], _p(scalars), force_c, _p(out)) == 0
+    return out
+
+
+def test_emulated_msm_kats(emu):
+    g = np.load(os.path.join(GOLD, "msm.npz"))
+    for k in [1, 2, 3, 4, 5, 256, 257]:
+        got = _emu_msm(emu, "alt_bn128", 1, g["family.bases"][:k], g[f"family.scalars{k}"])
+        assert np.array_equal(got, g[f"family.out{k}"]), k
+    for c in [0, 5, 9, 13]:
+        assert np.array_equal(_emu_msm(emu, "alt_bn128", 1, g["edge.bases"], g["edge.scalars"], c), g["edge.out"]), c
+
+
+@pytest.mark.parametrize("curve", list(CURVES))
+def test_emulated_msm_pipeline(emu, curve):
+    """zeros, ones, an infinity base and a repeated base through the sort / task / reduce index logic."""
+    g = np.load(os.path.join(GOLD, "msm.npz"))
+    for gname, gid in [("g1", 1), ("g2", 2)]:
+        k = f"rand.{curve}.{gname}"
+        for c in ([0, 6] if gid == 1 else [0]):
+            assert np.array_equal(_emu_msm(emu, curve, gid, g[k + ".bases"], g[k + ".scalars"], c), g[k + ".out"]), (k, c)
+
+
+def test_emulated_msm_heavy_bucket(emu):
+    """All-equal scalars: every point lands in the same bucket of each window -> many tasks per bucket
+    (the k_collapse path) and the narrow top window."""
+    g = np.load(os.path.join(GOLD, "msm.npz"))
+    bases = np.repeat(g["family.bases"], 3, axis=0)[:700]   # repeated bases as well: P + P collisions
+    sc = np.repeat(g["rand.alt_bn128.g1.scalars"][:1], 700, axis=0)
+    from oracle import port
+    want = port.OraclePort().msm("alt_bn128", 1, bases, sc)
+    assert np.array_equal(_emu_msm(emu, "alt_bn128", 1, bases, sc, 5), want)

@@ -1,0 +1,148 @@
+"""CPU tier: pins the oracle. The C restatement (oracle/oracle_port.c) is checked against the golden
+vectors in tests/golden/, which tools/gen_golden.py produced from the UNMODIFIED reference
+(oracle/_ref); where that reference build is present (this container) it is re-checked against the same
+vectors, so the fixtures cannot drift. KATs: libff test_multiexp.cpp:204-255, :337-383,
+test_fields.cpp:282-395; libfqfft evaluation_domain_test.cpp:40-80."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import port as port_mod
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+CURVES = ["alt_bn128", "bls12_377", "bw6_761"]
+FIELDS = {"fr": 0, "fq": 1, "fq2": 2}
+OPS = {"add": 0, "sub": 1, "mul": 2, "sqr": 3, "neg": 4, "inv": 5}
+
+
+@pytest.fixture(scope="module")
+def P():
+    return port_mod.OraclePort()
+
+
+def impls(P):
+    """(name, object) of every oracle implementation available: the C port always, the reference if built."""
+    out = [("port", P)]
+    try:
+        from oracle import refo
+        out.append(("ref", refo.RefOracle()))
+    except (OSError, FileNotFoundError):
+        pass
+    return out
+
+
+@pytest.mark.parametrize("curve", CURVES)
+def test_field_ops_golden(P, curve):
+    g = np.load(os.path.join(GOLD, "fields.npz"))
+    for name, impl in impls(P):
+        for fname, fid in FIELDS.items():
+            k = f"{curve}.{fname}"
+            if k + ".a" not in g:
+                continue
+            a, b = g[k + ".a"], g[k + ".b"]
+            for oname, op in OPS.items():
+                assert np.array_equal(impl.field_op(curve, fid, op, a, b), g[f"{k}.{oname}"]), (name, k, oname)
+
+
+@pytest.mark.parametrize("curve", CURVES)
+def test_signed_digits_golden(P, curve):
+    g = np.load(os.path.join(GOLD, "digits.npz"))
+    sc = g[f"{curve}.scalars"]
+    for name, impl in impls(P):
+        for c in [2, 5, 12, 13, 16, 21]:
+            want = g[f"{curve}.c{c}"]
+            assert np.array_equal(impl.signed_digits(curve, sc, c, want.shape[1]), want), (name, c)
+        for n, c in g["optimal_c"]:
+            assert impl.optimal_c(int(n)) == int(c)
+
+
+def test_signed_digit_properties(P):
+    """test_fields.cpp:348-395: digits lie in [-2^(c-1), 2^(c-1)) and recompose to the value."""
+    g = np.load(os.path.join(GOLD, "digits.npz"))
+    r = 0x30644e72e131a029b85045b68181585d2833e84879b9709143e1f593f0000001
+    for c in [2, 5, 12, 13, 16, 21]:
+        d = g[f"alt_bn128.c{c}"]
+        assert d.min() >= -(1 << (c - 1)) and d.max() < (1 << (c - 1))
+        v = sum(int(x) << (c * i) for i, x in enumerate(d[0]))
+        assert v == r - 1  # Fr(-1)
+
+
+def test_field_get_digit_kat():
+    """test_fields.cpp:282-344: 16-bit digits of Fr(-1) of alt_bn128 (unsigned digit = signed digit + carry handling off)."""
+    v = 0x30644e72e131a029b85045b68181585d2833e84879b9709143e1f593f0000000
+    want = [0x0000, 0xf000, 0xf593, 0x43e1, 0x7091, 0x79b9, 0xe848, 0x2833, 0x585d, 0x8181, 0x45b6, 0xb850, 0xa029,
+            0xe131, 0x4e72, 0x3064]
+    assert [(v >> (16 * i)) & 0xffff for i in range(16)] == want
+
+
+@pytest.mark.parametrize("curve", CURVES)
+def test_group_law_golden(P, curve):
+    g = np.load(os.path.join(GOLD, "groups.npz"))
+    for name, impl in impls(P):
+        for gname, gid in [("g1", 1), ("g2", 2)]:
+            k = f"{curve}.{gname}"
+            a, b = g[k + ".a"], g[k + ".b"]
+            norm = (lambda x: x) if name == "port" else (lambda x: impl.group_op(curve, gid, 4, x))
+            assert np.array_equal(norm(impl.group_op(curve, gid, 0, a, b)), g[k + ".add"]), (name, k)
+            assert np.array_equal(norm(impl.group_op(curve, gid, 2, a)), g[k + ".dbl"]), (name, k)
+            assert np.array_equal(norm(impl.group_op(curve, gid, 3, a)), g[k + ".neg"]), (name, k)
+
+
+def test_msm_kats(P):
+    g = np.load(os.path.join(GOLD, "msm.npz"))
+    for name, impl in impls(P):
+        for k in [1, 2, 3, 4, 5, 256, 257]:
+            got = impl.msm("alt_bn128", 1, g["family.bases"][:k], g[f"family.scalars{k}"])
+            assert np.array_equal(got, g[f"family.out{k}"]), (name, k)
+        assert np.array_equal(impl.msm("alt_bn128", 1, g["edge.bases"], g["edge.scalars"]), g["edge.out"]), name
+
+
+@pytest.mark.parametrize("curve", CURVES)
+def test_msm_random_golden(P, curve):
+    g = np.load(os.path.join(GOLD, "msm.npz"))
+    for name, impl in impls(P):
+        for gname, gid in [("g1", 1), ("g2", 2)]:
+            k = f"rand.{curve}.{gname}"
+            for method in (0, 2):
+                got = impl.msm(curve, gid, g[k + ".bases"], g[k + ".scalars"], method=method)
+                assert np.array_equal(got, g[k + ".out"]), (name, k, method)
+        k = f"kc.{curve}"
+        for lo, hi in [(0, 64), (5, 50)]:
+            sc = g[k + ".scalars"][: hi - lo]
+            if name == "port":
+                o2, o1 = impl.kc_msm(curve, g[k + ".indices"], g[k + ".values"], lo, hi, sc)
+            else:
+                o2, o1 = impl.kc_msm(curve, g[k + ".indices"], g[k + ".values"], 64, lo, hi, sc)
+            assert np.array_equal(o2, g[f"{k}.out_g2.{lo}_{hi}"]) and np.array_equal(o1, g[f"{k}.out_g1.{lo}_{hi}"])
+
+
+@pytest.mark.parametrize("curve", CURVES)
+def test_fft_golden(P, curve):
+    g = np.load(os.path.join(GOLD, "fft.npz"))
+    for name, impl in impls(P):
+        for m in [2, 4, 8, 32, 256]:
+            k = f"{curve}.m{m}"
+            a = g[k + ".in"]
+            for op, oname in enumerate(["fft", "ifft", "cosetfft", "icosetfft", "divz"]):
+                assert np.array_equal(impl.fft(curve, op, a), g[f"{k}.{oname}"]), (name, k, oname)
+    assert np.array_equal(P.fft("alt_bn128", 0, g["f2538.in"]), g["f2538.fft"])
+
+
+def test_fft_roundtrip_and_domain_error(P):
+    g = np.load(os.path.join(GOLD, "fft.npz"))
+    a = g["alt_bn128.m256.in"]
+    assert np.array_equal(P.fft("alt_bn128", 1, P.fft("alt_bn128", 0, a)), a)
+    assert np.array_equal(P.fft("alt_bn128", 3, P.fft("alt_bn128", 2, a)), a)
+    with pytest.raises(RuntimeError):
+        P.fft("alt_bn128", 0, a[:6])  # DomainSizeException analogue
+
+
+@pytest.mark.parametrize("curve", CURVES)
+def test_witness_map_golden(P, curve):
+    g = np.load(os.path.join(GOLD, "fft.npz"))
+    k = f"wm.{curve}"
+    assert np.array_equal(P.witness_map_h(curve, g[k + ".aA"], g[k + ".aB"], g[k + ".aC"]), g[k + ".H"])
+    # degree of H is m - 2: H[m-1] == H[m] == 0, H[m-2] != 0 (r1cs_gg_ppzksnark.tcc:488-490)
+    H = g[k + ".H"]
+    assert not H[-1].any() and not H[-2].any() and H[-3].any()
