@@ -1,0 +1,319 @@
+// libsnark_b200_overlay.hpp — the reference-side binding of the B200 drop-in.
+//
+// clearmatics/libsnark has no plugin mechanism on the Groth16 proving hot path: the operators are
+// C++ templates instantiated in the caller's translation unit. This header is what a
+// maintainer adds to interpose the CUDA library WITHOUT editing the reference: compile the
+// translation units that instantiate the prover with
+//
+//     -include libsnark_b200/overlay/libsnark_b200_overlay.hpp  -Iinclude  -lsnark_b200
+//
+// (it must be seen before the first implicit instantiation of the templates below). It provides
+// explicit specialisations that forward to the C-ABI of include/libsnark_b200.h for
+//   libff::multi_exp<G, Fr, multi_exp_method_BDLO12_signed, multi_exp_base_form_special>
+//                                       (libff/algebra/scalar_multiplication/multiexp.hpp:63-73)
+//   libff::multi_exp_filter_one_zero<...same...>                       (multiexp.hpp:83-88)
+//   libsnark::kc_multi_exp_with_mixed_addition<G2, G1, Fr, BDLO12_signed, special>
+//                                       (libsnark/knowledge_commitment/kc_multiexp.hpp:32-44)
+//   libfqfft::basic_radix2_domain<Fr>::{FFT, iFFT, cosetFFT, icosetFFT, divide_by_Z_on_coset}
+//                                       (libfqfft/evaluation_domain/domains/basic_radix2_domain.hpp)
+// for G in {G1, G2} of alt_bn128, bls12_377 and bw6_761. Every other instantiation (other methods,
+// base forms, curves, domains) keeps the reference's CPU template. There is no CPU fallback inside
+// the specialisations: a failing C-ABI call throws (std::runtime_error, or
+// libfqfft::DomainSizeException for a size the basic radix-2 domain does not have).
+//
+// Proving-key residency: the reference passes host iterators on every call and gives no lifetime
+// signal, so base vectors are cached on the device keyed by (host pointer, stride, count, a
+// fingerprint of the first and last point). libsnark_b200::release_cached_bases() drops the cache
+// (call it before freeing or mutating a proving key).
+#ifndef LIBSNARK_B200_OVERLAY_HPP_
+#define LIBSNARK_B200_OVERLAY_HPP_
+
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <stdexcept>
+#include <string>
+#include <tuple>
+#include <vector>
+
+#include <libff/algebra/curves/alt_bn128/alt_bn128_pp.hpp>
+#include <libff/algebra/curves/bls12_377/bls12_377_pp.hpp>
+#include <libff/algebra/curves/bw6_761/bw6_761_pp.hpp>
+#include <libff/algebra/scalar_multiplication/multiexp.hpp>
+#include <libff/common/profiling.hpp>
+#include <libfqfft/evaluation_domain/domains/basic_radix2_domain.hpp>
+#include <libfqfft/evaluation_domain/get_evaluation_domain.hpp>
+#include <libfqfft/tools/exceptions.hpp>
+#include <libsnark/knowledge_commitment/kc_multiexp.hpp>
+#include <libsnark/reductions/r1cs_to_qap/r1cs_to_qap.hpp>
+
+#include "libsnark_b200.h"
+
+namespace libsnark_b200
+{
+
+template<typename T> struct curve_of;
+#define B200_OVERLAY_TRAIT(TYPE, CURVE, GROUP)                                                     \
+    template<> struct curve_of<TYPE> {                                                             \
+        static constexpr int curve = CURVE;                                                        \
+        static constexpr int group = GROUP;                                                        \
+    };
+B200_OVERLAY_TRAIT(libff::alt_bn128_G1, B200_ALT_BN128, B200_G1)
+B200_OVERLAY_TRAIT(libff::alt_bn128_G2, B200_ALT_BN128, B200_G2)
+B200_OVERLAY_TRAIT(libff::bls12_377_G1, B200_BLS12_377, B200_G1)
+B200_OVERLAY_TRAIT(libff::bls12_377_G2, B200_BLS12_377, B200_G2)
+B200_OVERLAY_TRAIT(libff::bw6_761_G1, B200_BW6_761, B200_G1)
+B200_OVERLAY_TRAIT(libff::bw6_761_G2, B200_BW6_761, B200_G2)
+B200_OVERLAY_TRAIT(libff::alt_bn128_Fr, B200_ALT_BN128, 0)
+B200_OVERLAY_TRAIT(libff::bls12_377_Fr, B200_BLS12_377, 0)
+B200_OVERLAY_TRAIT(libff::bw6_761_Fr, B200_BW6_761, 0)
+#undef B200_OVERLAY_TRAIT
+
+inline void check(int rc, const char *what)
+{
+    if (rc == B200_OK) {
+        return;
+    }
+    const std::string msg = std::string("libsnark_b200: ") + what + ": " + b200_last_error();
+    if (rc == B200_ERR_DOMAIN) {
+        throw libfqfft::DomainSizeException(msg);
+    }
+    throw std::runtime_error(msg);
+}
+
+struct bases_cache {
+    typedef std::tuple<const void *, size_t, size_t, int, int, unsigned long long> key_t;
+    std::map<key_t, b200_bases_t> sets;
+    static bases_cache &get()
+    {
+        static bases_cache c;
+        return c;
+    }
+    static unsigned long long fingerprint(const void *p, size_t stride, size_t n, size_t point_bytes)
+    {
+        unsigned long long h = 1469598103934665603ull; // FNV-1a over the first and the last point
+        const unsigned char *b = static_cast<const unsigned char *>(p);
+        const size_t offs[2] = {0, n ? (n - 1) * stride : 0};
+        for (size_t k = 0; k < 2 && n; ++k) {
+            for (size_t i = 0; i < point_bytes; ++i) {
+                h = (h ^ b[offs[k] + i]) * 1099511628211ull;
+            }
+        }
+        return h;
+    }
+    b200_bases_t lookup(int curve, int group, const void *p, size_t stride, size_t n, size_t point_bytes)
+    {
+        const key_t key(p, stride, n, curve, group, fingerprint(p, stride, n, point_bytes));
+        auto it = sets.find(key);
+        if (it != sets.end()) {
+            return it->second;
+        }
+        b200_bases_t h = 0;
+        check(b200_bases_upload(curve, group, p, stride, n, &h), "b200_bases_upload");
+        sets[key] = h;
+        return h;
+    }
+    void clear()
+    {
+        for (auto &kv : sets) {
+            b200_bases_free(kv.second);
+        }
+        sets.clear();
+    }
+};
+inline void release_cached_bases() { bases_cache::get().clear(); }
+
+// sum_i scalar[i] * base[i] over contiguous host ranges (the reference's iterator pairs).
+template<typename GroupT, typename FieldT>
+GroupT msm_contiguous(const GroupT *bases, size_t n, const FieldT *scalars)
+{
+    GroupT out = GroupT::zero();
+    if (n == 0) {
+        return out;
+    }
+    typedef curve_of<GroupT> tr;
+    const b200_bases_t h = bases_cache::get().lookup(tr::curve, tr::group, bases, sizeof(GroupT), n, sizeof(GroupT));
+    check(b200_msm_resident(h, 0, n, scalars, 0, &out), "b200_msm_resident");
+    return out;
+}
+
+// The three statistics lines of multi_exp_filter_one_zero (multiexp.tcc:737-751) / kc (kc_multiexp.tcc:91-105).
+template<typename FieldT> void print_filter_stats(const FieldT *scalars, size_t n)
+{
+    if (libff::inhibit_profiling_info) {
+        return;
+    }
+    size_t num_skip = 0, num_add = 0;
+    const FieldT zero = FieldT::zero(), one = FieldT::one();
+    for (size_t i = 0; i < n; ++i) {
+        num_skip += scalars[i] == zero;
+        num_add += scalars[i] == one;
+    }
+    const size_t num_other = n - num_skip - num_add;
+    libff::print_indent();
+    printf("* Elements of w skipped: %zu (%0.2f%%)\n", num_skip, 100. * num_skip / (n ? n : 1));
+    libff::print_indent();
+    printf("* Elements of w processed with special addition: %zu (%0.2f%%)\n", num_add, 100. * num_add / (n ? n : 1));
+    libff::print_indent();
+    printf("* Elements of w remaining: %zu (%0.2f%%)\n", num_other, 100. * num_other / (n ? n : 1));
+}
+
+template<typename T1, typename T2, typename FieldT>
+libsnark::knowledge_commitment<T1, T2> kc_msm(
+    const libsnark::knowledge_commitment_vector<T1, T2> &vec, const size_t min_idx, const size_t max_idx,
+    typename std::vector<FieldT>::const_iterator scalar_start, typename std::vector<FieldT>::const_iterator scalar_end)
+{
+    typedef libsnark::knowledge_commitment<T1, T2> KC;
+    (void)scalar_end;
+    // kc_multiexp.tcc:40-44, :63: the stored entries with min_idx <= index < max_idx
+    const auto lo = std::lower_bound(vec.indices.begin(), vec.indices.end(), min_idx);
+    const auto hi = std::lower_bound(lo, vec.indices.end(), max_idx);
+    const size_t first = lo - vec.indices.begin(), cnt = hi - lo;
+    KC out(T1::zero(), T2::zero());
+    if (cnt == 0) {
+        return out;
+    }
+    std::vector<FieldT> gathered(cnt);
+    for (size_t k = 0; k < cnt; ++k) {
+        gathered[k] = *(scalar_start + (vec.indices[first + k] - min_idx));
+    }
+    print_filter_stats(gathered.data(), cnt);
+    const unsigned char *vals = reinterpret_cast<const unsigned char *>(vec.values.data());
+    const size_t n = vec.values.size();
+    const size_t off2 = reinterpret_cast<const unsigned char *>(&vec.values[0].h) - vals;
+    bases_cache &c = bases_cache::get();
+    const b200_bases_t hg = c.lookup(curve_of<T1>::curve, curve_of<T1>::group, vals, sizeof(KC), n, sizeof(T1));
+    const b200_bases_t hh = c.lookup(curve_of<T2>::curve, curve_of<T2>::group, vals + off2, sizeof(KC), n, sizeof(T2));
+    check(b200_msm_resident(hg, first, cnt, gathered.data(), 0, &out.g), "b200_msm_resident (kc.g)");
+    check(b200_msm_resident(hh, first, cnt, gathered.data(), 0, &out.h), "b200_msm_resident (kc.h)");
+    return out;
+}
+
+template<typename FieldT> void ntt(std::vector<FieldT> &a, size_t m, int op, const FieldT *g)
+{
+    if (a.size() != m) { // basic_radix2_domain.tcc:57, :65
+        throw libfqfft::DomainSizeException("basic_radix2: expected a.size() == this->m");
+    }
+    check(b200_ntt(curve_of<FieldT>::curve, op, a.data(), m, g), "b200_ntt");
+}
+
+// The NTT chain of r1cs_to_qap_witness_map (r1cs_to_qap.tcc:252-330) as ONE device pipeline, for
+// callers that can change one line of the prover: evaluations stay on the device between the seven
+// transforms. Written against the reference's types; Groth16 case (d1 = d2 = d3 = 0).
+template<typename FieldT>
+libsnark::qap_witness<FieldT> r1cs_to_qap_witness_map_fused(
+    const libsnark::r1cs_constraint_system<FieldT> &cs, const libsnark::r1cs_primary_input<FieldT> &primary_input,
+    const libsnark::r1cs_auxiliary_input<FieldT> &auxiliary_input)
+{
+    const size_t m = libfqfft::get_evaluation_domain<FieldT>(cs.num_constraints() + cs.num_inputs() + 1)->m;
+    libsnark::r1cs_variable_assignment<FieldT> full = primary_input;
+    full.insert(full.end(), auxiliary_input.begin(), auxiliary_input.end());
+    std::vector<FieldT> aA(m, FieldT::zero()), aB(m, FieldT::zero()), aC(m, FieldT::zero());
+    for (size_t i = 0; i <= cs.num_inputs(); ++i) {
+        aA[i + cs.num_constraints()] = (i > 0 ? full[i - 1] : FieldT::one());
+    }
+#ifdef MULTICORE
+#pragma omp parallel for
+#endif
+    for (size_t i = 0; i < cs.num_constraints(); ++i) {
+        aA[i] += cs.constraints[i].a.evaluate(full);
+        aB[i] += cs.constraints[i].b.evaluate(full);
+        aC[i] += cs.constraints[i].c.evaluate(full);
+    }
+    std::vector<FieldT> H(m + 1, FieldT::zero());
+    check(b200_witness_map_h(curve_of<FieldT>::curve, aA.data(), aB.data(), aC.data(), m, H.data()),
+          "b200_witness_map_h");
+    return libsnark::qap_witness<FieldT>(
+        cs.num_variables(), m, cs.num_inputs(), FieldT::zero(), FieldT::zero(), FieldT::zero(), full, std::move(H));
+}
+
+} // namespace libsnark_b200
+
+// ---------------------------------------------------------------------------------------------------
+// explicit specialisations
+// ---------------------------------------------------------------------------------------------------
+#define B200_OVERLAY_MSM(G, FR)                                                                                        \
+    namespace libff                                                                                                    \
+    {                                                                                                                  \
+    template<>                                                                                                         \
+    inline G multi_exp<G, FR, multi_exp_method_BDLO12_signed, multi_exp_base_form_special>(                            \
+        std::vector<G>::const_iterator vec_start, std::vector<G>::const_iterator vec_end,                              \
+        std::vector<FR>::const_iterator scalar_start, std::vector<FR>::const_iterator scalar_end, const size_t chunks) \
+    {                                                                                                                  \
+        (void)chunks;                                                                                                  \
+        (void)scalar_end;                                                                                              \
+        const size_t n = vec_end - vec_start;                                                                          \
+        return libsnark_b200::msm_contiguous<G, FR>(n ? &*vec_start : nullptr, n, n ? &*scalar_start : nullptr);       \
+    }                                                                                                                  \
+    template<>                                                                                                         \
+    inline G multi_exp_filter_one_zero<G, FR, multi_exp_method_BDLO12_signed, multi_exp_base_form_special>(            \
+        std::vector<G>::const_iterator vec_start, std::vector<G>::const_iterator vec_end,                              \
+        std::vector<FR>::const_iterator scalar_start, std::vector<FR>::const_iterator scalar_end, const size_t chunks) \
+    {                                                                                                                  \
+        (void)chunks;                                                                                                  \
+        (void)scalar_end;                                                                                              \
+        const size_t n = vec_end - vec_start;                                                                          \
+        if (n) {                                                                                                       \
+            libsnark_b200::print_filter_stats<FR>(&*scalar_start, n);                                                  \
+        }                                                                                                              \
+        return libsnark_b200::msm_contiguous<G, FR>(n ? &*vec_start : nullptr, n, n ? &*scalar_start : nullptr);       \
+    }                                                                                                                  \
+    }
+
+#define B200_OVERLAY_KC(G2T, G1T, FR)                                                                                  \
+    namespace libsnark                                                                                                 \
+    {                                                                                                                  \
+    template<>                                                                                                         \
+    inline knowledge_commitment<G2T, G1T> kc_multi_exp_with_mixed_addition<                                            \
+        G2T, G1T, FR, libff::multi_exp_method_BDLO12_signed, libff::multi_exp_base_form_special>(                      \
+        const knowledge_commitment_vector<G2T, G1T> &vec, const size_t min_idx, const size_t max_idx,                  \
+        std::vector<FR>::const_iterator scalar_start, std::vector<FR>::const_iterator scalar_end, const size_t chunks) \
+    {                                                                                                                  \
+        (void)chunks;                                                                                                  \
+        return libsnark_b200::kc_msm<G2T, G1T, FR>(vec, min_idx, max_idx, scalar_start, scalar_end);                   \
+    }                                                                                                                  \
+    }
+
+#define B200_OVERLAY_NTT(FR)                                                                                           \
+    namespace libfqfft                                                                                                 \
+    {                                                                                                                  \
+    template<> inline void basic_radix2_domain<FR>::FFT(std::vector<FR> &a)                                            \
+    {                                                                                                                  \
+        libsnark_b200::ntt<FR>(a, this->m, B200_FFT, nullptr);                                                         \
+    }                                                                                                                  \
+    template<> inline void basic_radix2_domain<FR>::iFFT(std::vector<FR> &a)                                           \
+    {                                                                                                                  \
+        libsnark_b200::ntt<FR>(a, this->m, B200_IFFT, nullptr);                                                        \
+    }                                                                                                                  \
+    template<> inline void basic_radix2_domain<FR>::cosetFFT(std::vector<FR> &a, const FR &g)                          \
+    {                                                                                                                  \
+        libsnark_b200::ntt<FR>(a, this->m, B200_COSET_FFT, &g);                                                        \
+    }                                                                                                                  \
+    template<> inline void basic_radix2_domain<FR>::icosetFFT(std::vector<FR> &a, const FR &g)                         \
+    {                                                                                                                  \
+        libsnark_b200::ntt<FR>(a, this->m, B200_ICOSET_FFT, &g);                                                       \
+    }                                                                                                                  \
+    template<> inline void basic_radix2_domain<FR>::divide_by_Z_on_coset(std::vector<FR> &P)                           \
+    {                                                                                                                  \
+        libsnark_b200::check(                                                                                          \
+            b200_divide_by_Z_on_coset(libsnark_b200::curve_of<FR>::curve, P.data(), this->m),                          \
+            "b200_divide_by_Z_on_coset");                                                                              \
+    }                                                                                                                  \
+    }
+
+B200_OVERLAY_MSM(libff::alt_bn128_G1, libff::alt_bn128_Fr)
+B200_OVERLAY_MSM(libff::alt_bn128_G2, libff::alt_bn128_Fr)
+B200_OVERLAY_KC(libff::alt_bn128_G2, libff::alt_bn128_G1, libff::alt_bn128_Fr)
+B200_OVERLAY_NTT(libff::alt_bn128_Fr)
+
+B200_OVERLAY_MSM(libff::bls12_377_G1, libff::bls12_377_Fr)
+B200_OVERLAY_MSM(libff::bls12_377_G2, libff::bls12_377_Fr)
+B200_OVERLAY_KC(libff::bls12_377_G2, libff::bls12_377_G1, libff::bls12_377_Fr)
+B200_OVERLAY_NTT(libff::bls12_377_Fr)
+
+B200_OVERLAY_MSM(libff::bw6_761_G1, libff::bw6_761_Fr)
+B200_OVERLAY_MSM(libff::bw6_761_G2, libff::bw6_761_Fr)
+B200_OVERLAY_KC(libff::bw6_761_G2, libff::bw6_761_G1, libff::bw6_761_Fr)
+B200_OVERLAY_NTT(libff::bw6_761_Fr)
+
+#endif // LIBSNARK_B200_OVERLAY_HPP_

@@ -28,7 +28,20 @@
 #include <libff/algebra/curves/bls12_377/bls12_377_pp.hpp>
 #include <libff/algebra/curves/bw6_761/bw6_761_pp.hpp>
 #include <libff/algebra/fields/field_utils.hpp>
+// multiexp.tcc's ordered_exponent::operator< (bos_coster, used only by the verifier's input
+// accumulation) has an x86 asm compare with no "memory" clobber; gcc 13 -O2 moves the heap
+// swaps across it and the verifier then rejects valid proofs for some thread counts. Including
+// the header with USE_ASM off selects its own mpn_cmp branch; the field arithmetic headers were
+// already included above with USE_ASM on, so nothing on the timed path changes.
+#ifdef USE_ASM
+#undef USE_ASM
+#define REF_HARNESS_RESTORE_USE_ASM
+#endif
 #include <libff/algebra/scalar_multiplication/multiexp.hpp>
+#ifdef REF_HARNESS_RESTORE_USE_ASM
+#define USE_ASM
+#undef REF_HARNESS_RESTORE_USE_ASM
+#endif
 #include <libff/common/profiling.hpp>
 #include <libff/common/rng.hpp>
 #include <libfqfft/evaluation_domain/domains/basic_radix2_domain.hpp>
@@ -346,8 +359,12 @@ template<typename ppT> struct H {
             case 4: dom->divide_by_Z_on_coset(a); break;
             default: return -1;
             }
-        } catch (const std::exception &e) {
+        } catch (const libfqfft::DomainSizeException &) { // not derived from std::exception
             return -2;
+        } catch (const libfqfft::InvalidSizeException &) {
+            return -2;
+        } catch (const std::exception &) {
+            return -3;
         }
         memcpy(d, a.data(), m * sizeof(FrT));
         return 0;
@@ -502,6 +519,11 @@ template<typename ppT> struct H {
             stage_ms = dummy;
         }
 
+#ifdef B200_OVERLAY
+        // overlay build: the seven transforms run as one device pipeline (b200_witness_map_h)
+        const qap_witness<FrT> qap_wit = libsnark_b200::r1cs_to_qap_witness_map_fused(
+            pk.constraint_system, f->example.primary_input, f->example.auxiliary_input);
+#else
         const qap_witness<FrT> qap_wit = r1cs_to_qap_witness_map(
             pk.constraint_system,
             f->example.primary_input,
@@ -510,6 +532,7 @@ template<typename ppT> struct H {
             FrT::zero(),
             FrT::zero(),
             false);
+#endif
         t1 = get_nsec_time();
         stage_ms[0] = (t1 - t) * 1e-6;
         t = t1;

@@ -289,19 +289,22 @@ class Groth16Fixture:
     def proof_limbs(self):
         return 2 * self.i["g1_limbs"] + self.i["g2_limbs"]
 
-    def prove(self, r, s):
+    def prove(self, r, s, via=None):
+        """Proof (g_A | g_B | g_C, normalised) with caller-supplied r, s. via = another RefOracle (the
+        overlay build) runs ITS prover on this fixture: the C++ objects are layout-identical."""
         r = np.ascontiguousarray(r, dtype=np.uint64)
         s = np.ascontiguousarray(s, dtype=np.uint64)
         out = np.zeros(self.proof_limbs(), dtype=np.uint64)
         ms = np.zeros(6, dtype=np.float64)
-        assert self.ref.lib.ref_groth16_prove(self.h, _p(r), _p(s), _p(out), _p(ms)) == 0
+        lib = (via or self.ref).lib
+        assert lib.ref_groth16_prove(self.h, _p(r), _p(s), _p(out), _p(ms)) == 0
         stages = dict(zip(["witness_map", "A", "B", "H", "L", "total"], ms.tolist()))
         return out, stages
 
-    def prove_stock(self):
+    def prove_stock(self, via=None):
         out = np.zeros(self.proof_limbs(), dtype=np.uint64)
         ms = C.c_double(0)
-        assert self.ref.lib.ref_groth16_prove_stock(self.h, _p(out), C.byref(ms)) == 0
+        assert (via or self.ref).lib.ref_groth16_prove_stock(self.h, _p(out), C.byref(ms)) == 0
         return out, ms.value
 
     def verify(self, proof):
