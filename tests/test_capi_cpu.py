@@ -133,3 +133,17 @@ def test_sharded_fold_gloo_world2(b, tmp_path):
     wins = [_fake_windows(P, "alt_bn128", 1, W, s, 12)[0] for s in range(2)]
     want = b.fold_windows("alt_bn128", b.G1, n, np.concatenate(wins), 2)
     assert np.array_equal(np.load(out), want)
+
+
+def test_product_does_not_touch_the_oracle():
+    """The shipped path (package + shared library) never imports, links or opens anything under oracle/."""
+    import subprocess
+    pkg = os.path.join(ROOT, "libsnark_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".hpp", ".h")) and "overlay" not in dirpath:
+                text = open(os.path.join(dirpath, f), errors="ignore").read()
+                for needle in ("import oracle", "from oracle", "oracle/", "libref_", "oracle_port", "refo"):
+                    assert needle not in text, f"{f} refers to {needle}"
+    needed = subprocess.run(["readelf", "-d", os.path.join(pkg, "libsnark_b200.so")], capture_output=True, text=True).stdout
+    assert "libref" not in needed and "oracle" not in needed

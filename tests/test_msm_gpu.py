@@ -35,7 +35,7 @@ def test_msm_empty(b200, ref):
     assert np.array_equal(got, zero[0])
 
 
-@pytest.mark.parametrize("log_n", [16, 18])
+@pytest.mark.parametrize("log_n", [16, 18, 20])
 def test_msm_alt_bn128_g1_large(ref, b200, log_n):
     n = 1 << log_n
     bases, scalars = _inputs(ref, "alt_bn128", refo.G1, n, seed=3)
@@ -127,3 +127,29 @@ def test_resident_and_sharded(ref, b200):
     ws = np.concatenate([rb.window_sums(scalars[k * q:(k + 1) * q], first=k * q, n=q) for k in range(4)])
     assert np.array_equal(b200.fold_windows(curve, group, q, ws, 4), want)
     rb.free()
+
+
+@pytest.mark.parametrize("curve,group,log_n", [("bls12_377", refo.G1, 18), ("bw6_761", refo.G1, 16),
+                                               ("alt_bn128", refo.G2, 18)])
+def test_msm_full_size_linearity(ref, b200, curve, group, log_n):
+    """BASELINE config 5 sizes through a size-independent property: one device MSM over
+    the whole range equals the group sum of reference MSMs over disjoint quarters, and
+    MSM(bases, s1 + s2) == MSM(bases, s1) + MSM(bases, s2) on the device."""
+    n = 1 << log_n
+    bases, scalars = _inputs(ref, curve, group, n, seed=11)
+    got = b200.multi_exp(curve, group, bases, scalars)
+    q = n // 4
+    parts = [ref.msm(curve, group, bases[i * q:(i + 1) * q], scalars[i * q:(i + 1) * q], chunks=ref.num_threads())
+             for i in range(4)]
+    acc = parts[0]
+    for p_ in parts[1:]:
+        acc = ref.group_op(curve, group, refo.GOP_ADD, acc[None, :], p_[None, :])[0]
+    acc = ref.group_op(curve, group, refo.GOP_TO_AFFINE, acc[None, :])[0]
+    assert np.array_equal(got, acc)
+    s2 = ref.field_random(curve, refo.FR, 991, n)
+    ssum = ref.field_op(curve, refo.FR, 0, scalars, s2)   # op 0 = add
+    lhs = b200.multi_exp(curve, group, bases, ssum)
+    r2 = b200.multi_exp(curve, group, bases, s2)
+    rhs = ref.group_op(curve, group, refo.GOP_ADD, got[None, :], r2[None, :])
+    rhs = ref.group_op(curve, group, refo.GOP_TO_AFFINE, rhs)[0]
+    assert np.array_equal(lhs, rhs)

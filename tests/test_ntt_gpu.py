@@ -61,7 +61,7 @@ def test_domain_size_exception(b200):
         b200.get_evaluation_domain("alt_bn128", 8).FFT(a)
 
 
-@pytest.mark.parametrize("log_m", [20])
+@pytest.mark.parametrize("log_m", [20, 24])
 def test_fft_large_roundtrip_and_spot_check(ref, b200, log_m):
     """Size-independent properties at scale: iFFT(FFT(a)) == a, icosetFFT(cosetFFT(a)) == a, and
     naive Horner evaluation at a few domain points."""
@@ -74,7 +74,8 @@ def test_fft_large_roundtrip_and_spot_check(ref, b200, log_m):
     assert np.array_equal(dom.icosetFFT(dom.cosetFFT(a, g), g), a)
     idx = np.array([0, 1, 2, m // 2, m - 1, 12345, 777777 % m], dtype=np.uint64)
     assert np.array_equal(fa[idx.astype(np.int64)], ref.poly_eval_at_domain(curve, a, idx))
-    assert np.array_equal(fa, ref.fft(curve, refo.FFT, a))
+    if log_m <= 20:     # the reference's own FFT at 2^24 takes minutes on the host; properties cover it
+        assert np.array_equal(fa, ref.fft(curve, refo.FFT, a))
 
 
 @pytest.mark.parametrize("curve,log_m", [("alt_bn128", 4), ("alt_bn128", 10), ("alt_bn128", 16), ("bls12_377", 12),
