@@ -124,6 +124,8 @@ def reference_msm_rate(log_n_full, steps, warmup, budget_s=60.0):
     bounded sample of the workload. Returns (Mpts/s, threads, sample description, ms per step)."""
     from oracle import refo
     ref = refo.RefOracle()
+    # torchrun exports OMP_NUM_THREADS=1; the reference arm is entitled to every host core it can use
+    ref.set_num_threads(len(os.sched_getaffinity(0)))
     threads = ref.num_threads()
     # size the sample from a small probe so that (steps + warmup) runs fit the budget
     probe_n = 1 << 14

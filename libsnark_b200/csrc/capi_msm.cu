@@ -118,6 +118,12 @@ int msm_resident_impl(const rt::BaseSet &bs, size_t first, size_t n, const void 
         if (rc) {
             return rc;
         }
+    } else {
+        // window sums only (sharded callers fold later): close the timing record here
+        rt::MsmTiming &tm = rt::msm_timing();
+        B200_CUDA_CHECK(cudaEventRecord(tm.ev[4], s));
+        tm.host_fold_ms = 0;
+        tm.valid = true;
     }
     B200_CUDA_CHECK(cudaStreamSynchronize(s));
     return B200_OK;
