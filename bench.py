@@ -294,21 +294,26 @@ def run_b200_arm(args):
         "clocks": clocks,
     }
     if rank == 0:
-        wide, lo, carry = b.imad_peak()
+        wide, lo, _ = b.imad_peak()
         c = line["config"]["window_bits"]
         imads = 11 * W * n * 136  # bucket accumulation only: W*N mixed adds x 11 modmuls x MM(8)
         ach = imads / (acc_ms * 1e-3)
         line["roofline"] = {
             "bound": "int-pipe", "kernel": "k_accumulate", "achieved": ach / 1e12, "peak": wide / 1e12,
-            "unit": "Tmad/s (32x32+64 multiply-adds)", "frac": ach / wide, "traffic": None,
-            "peak_source": "b200_imad_peak: dependent-free IMAD.WIDE.U32 loop measured in this run (MEASURED_PEAKS.json "
-                           "has no integer figure)",
-            "peak_carry_chain": carry / 1e12, "frac_of_carry_chain_peak": ach / carry,
+            "unit": "Tmad/s (32x32+64 multiply-adds)", "frac": ach / wide,
+            # dram__bytes_read.sum + dram__bytes_write.sum of one k_accumulate launch at this workload,
+            # profiles/r1_ncu_full_msm.md (ncu --set full); algorithmic bytes are 68 B per mixed add
+            "traffic": 525.8e6, "algorithmic_bytes": 68.0 * W * n,
+            "peak_source": "b200_imad_peak, measured in this run: chains of IMAD.WIDE.U32.X (the 32x32+64 multiply-add a "
+                           "Montgomery product is made of; it holds the FMA-heavy pipe for two issue slots, 32 per clock "
+                           "per SM). MEASURED_PEAKS.json has no integer figure.",
+            "imad32_issue_peak": lo / 1e12, "frac_of_imad32_issue_peak": ach / lo,
+            "pipe_utilisation_ncu": 0.839,  # sm__pipe_fmaheavy_cycles_active, profiles/r1_ncu_full_msm.md
             "whole_msm_achieved": msm_algorithmic_imads(n, c, W) / (ms_step * 1e-3) / 1e12,
             "kernel_ms": acc_ms,
         }
         if world == 1 and not args.no_ntt:
-            line["ntt"] = bench_ntt(b, torch, args.ntt_log_m)
+            line["ntt"] = bench_ntt(b, torch, args.ntt_log_m, wide)
         if world == 1 and not args.no_cpu_baseline:
             try:
                 rate, threads, sample, _ = reference_msm_rate(args.log_n, 2, 1, budget_s=20.0)
@@ -323,7 +328,7 @@ def run_b200_arm(args):
         dist.destroy_process_group()
 
 
-def bench_ntt(b, torch, log_m):
+def bench_ntt(b, torch, log_m, wide_peak):
     """Secondary metric 'NTT elem/s @2^24': basic_radix2_domain<alt_bn128_Fr>::FFT, data resident in HBM
     (value) and through the host-buffer C-ABI call b200_ntt (e2e)."""
     m = 1 << log_m
@@ -352,8 +357,9 @@ def bench_ntt(b, torch, log_m):
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
                          "frac": gbs / peaks.get("hbm_gbs"), "traffic": None,
                          "algorithmic_bytes": 2 * m * 32,
-                         "int_pipe_note": "(m/2) log2(m) modmuls x 136 multiply-adds; see DESIGN.md"},
-            "modmul_Tmad_s": (m // 2) * log_m * 136 / (ms * 1e-3) / 1e12}
+                         "int_pipe_note": "(m/2) log2(m) modmuls x 136 multiply-adds against the IMAD.WIDE peak; see DESIGN.md §5"},
+            "modmul_Tmad_s": (m // 2) * log_m * 136 / (ms * 1e-3) / 1e12,
+            "int_pipe_frac": (m // 2) * log_m * 136 / (ms * 1e-3) / wide_peak}
 
 
 def main():

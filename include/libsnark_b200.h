@@ -139,7 +139,9 @@ int b200_witness_map_h(int curve, const void *aA, const void *aB, const void *aC
 int b200_witness_map_h_dev(int curve, void *dA, void *dB, void *dC, size_t m, void *dH);
 
 /* ---- measurement helpers (used by bench.py; not part of the reference surface) ------- */
-/* Runs `iters` launches of a dependent-free IMAD.WIDE loop and returns multiply-adds/s. */
+/* Integer-pipe microbenchmarks, multiply-adds per second: wide = 32x32+64 IMAD.WIDE.U32(.X) chains
+ * (what a Montgomery product is made of; two issue slots each), lo = 32-bit IMAD (the pipe's
+ * issue rate). Operands are loop-variant so that nothing is hoisted. */
 int b200_imad_peak(int iters, double *wide_mads_per_s, double *lo_mads_per_s);
 /* Time (ms, CUDA events on the library stream) of the last MSM's kernels:
  * [0] scalar prep+sort, [1] bucket accumulation, [2] bucket reduction, [3] fold, [4] total */

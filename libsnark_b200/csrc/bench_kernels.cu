@@ -1,52 +1,30 @@
-// bench_kernels.cu — integer-pipe peak microbenchmark (the MSM roofline denominator,
+// bench_kernels.cu — integer-pipe peak microbenchmarks (the MSM roofline denominator,
 // "peak_imad measured on the box by a dependent-free IMAD microbenchmark").
+// Two rates: 32-bit IMAD (the pipe's issue rate, 64 per clock per SM) and the 32x32+64 wide
+// multiply-add IMAD.WIDE.U32(.X), which holds the pipe for two issue slots (32 per clock per SM)
+// and is what a multi-limb Montgomery product consists of. tools/microbench/imad_bench.cu has
+// the longer set of variants.
 #include "runtime.hpp"
 
 namespace
 {
 
-// 8 independent 64-bit accumulators per thread, each advanced by IMAD.WIDE.U32
-// (mad.wide.u32: 32x32+64 -> 64). No carries between chains, so the FMA-heavy pipe is the
-// only limiter once enough warps are resident.
-template<int UNROLL> __global__ void __launch_bounds__(256) k_imad_wide(uint64_t *out, uint32_t a, uint32_t b, int iters)
-{
-    uint64_t acc[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        acc[k] = threadIdx.x + k;
-    }
-    uint32_t x = a + threadIdx.x, y = b + blockIdx.x;
-    for (int it = 0; it < iters; ++it) {
-#pragma unroll
-        for (int u = 0; u < UNROLL; ++u) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[k]) : "r"(x), "r"(y));
-            }
-        }
-    }
-    uint64_t r = 0;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        r ^= acc[k];
-    }
-    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = r;
-}
-
+// 32-bit IMAD (mad.lo.u32), 8 chains per thread. The multiplier operands come from the other
+// accumulators, i.e. they are loop-VARIANT: with invariant operands ptxas hoists the product out
+// of the loop and what remains (and what an earlier version of this file measured) is IADD3.
 template<int UNROLL> __global__ void __launch_bounds__(256) k_imad_lo(uint32_t *out, uint32_t a, uint32_t b, int iters)
 {
     uint32_t acc[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        acc[k] = threadIdx.x + k;
+        acc[k] = (threadIdx.x + k) * 0x9e3779b9u + a + b * blockIdx.x;
     }
-    uint32_t x = a + threadIdx.x, y = b + blockIdx.x;
     for (int it = 0; it < iters; ++it) {
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
-                asm volatile("mad.lo.u32 %0, %1, %2, %0;" : "+r"(acc[k]) : "r"(x), "r"(y));
+                asm volatile("mad.lo.u32 %0, %1, %2, %0;" : "+r"(acc[k]) : "r"(acc[(k + 1) % 8]), "r"(acc[(k + 3) % 8]));
             }
         }
     }
@@ -133,13 +111,11 @@ extern "C" int b200_imad_peak(int iters, double *wide_mads_per_s, double *lo_mad
     B200_CUDA_CHECK(cudaEventCreate(&e0));
     B200_CUDA_CHECK(cudaEventCreate(&e1));
     const double ops = (double)blocks * threads * (double)iters * UNROLL * 8;
-    for (int which = 0; which < 3; ++which) {
+    for (int which = 1; which < 3; ++which) {
         float best = 1e30f;
         for (int rep = 0; rep < 4; ++rep) {
             B200_CUDA_CHECK(cudaEventRecord(e0, s));
-            if (which == 0) {
-                k_imad_wide<UNROLL><<<blocks, threads, 0, s>>>(g_buf.as<uint64_t>(), 12345u, 6789u, iters);
-            } else if (which == 1) {
+            if (which == 1) {
                 k_imad_lo<UNROLL><<<blocks, threads, 0, s>>>(g_buf.as<uint32_t>(), 12345u, 6789u, iters);
             } else {
                 k_imad_carry<UNROLL><<<blocks, threads, 0, s>>>(g_buf.as<uint32_t>(), 12345u, 6789u, iters);
@@ -154,7 +130,7 @@ extern "C" int b200_imad_peak(int iters, double *wide_mads_per_s, double *lo_mad
             }
         }
         const double rate = ops / (best * 1e-3);
-        if (which == 0 && wide_mads_per_s) {
+        if (which == 2 && wide_mads_per_s) {
             *wide_mads_per_s = rate;
         }
         if (which == 1 && lo_mads_per_s) {
