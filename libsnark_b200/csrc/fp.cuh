@@ -361,28 +361,14 @@ template<class P> struct alignas(16) Fp {
     {
 #if defined(__CUDA_ARCH__)
         if (N >= 16 || B200_OUTLINE_MUL_ALWAYS) {
-            Fp r;
-            mul_outlined(r.v, a.v, b.v);
-            return r;
+            return mul_outlined(a, b);
         }
 #endif
         return mul_inline(a, b);
     }
 #if defined(__CUDACC__)
-    static __device__ __noinline__ void mul_outlined(uint32_t *r, const uint32_t *a, const uint32_t *b)
-    {
-        Fp x, y;
-#pragma unroll
-        for (int i = 0; i < N; ++i) {
-            x.v[i] = a[i];
-            y.v[i] = b[i];
-        }
-        const Fp z = mul_inline(x, y);
-#pragma unroll
-        for (int i = 0; i < N; ++i) {
-            r[i] = z.v[i];
-        }
-    }
+    // by value: operands and result travel in registers (pointers would force them through local memory)
+    static __device__ __noinline__ Fp mul_outlined(Fp a, Fp b) { return mul_inline(a, b); }
 #endif
     HD static Fp mul_inline(const Fp &a, const Fp &b)
     {
@@ -461,18 +447,53 @@ template<class P2> struct Fp2 {
     HD Fp2 neg() const { return Fp2{c0.neg(), c1.neg()}; }
     HD Fp2 cneg(bool f) const { return Fp2{c0.cneg(f), c1.cneg(f)}; }
     HD Fp2 dbl() const { return Fp2{c0.dbl(), c1.dbl()}; }
-    HD friend Fp2 operator*(const Fp2 &a, const Fp2 &b)
+    // Karatsuba product / complex squaring (fp2.tcc:102-151). With B200_OUTLINE_FP2 the whole Fp2
+    // operation is ONE out-of-line body whose base-field products are inlined side by side: the
+    // three (two) independent carry chains give the scheduler latency cover that a kernel running
+    // one or two warps per scheduler (255 registers) does not get from other warps.
+    HD static Fp2 mul_body(const Fp2 &a, const Fp2 &b)
     {
+#if defined(__CUDA_ARCH__) && defined(B200_OUTLINE_FP2)
+        const F aA = F::mul_inline(a.c0, b.c0);
+        const F bB = F::mul_inline(a.c1, b.c1);
+        const F s = F::mul_inline(a.c0 + a.c1, b.c0 + b.c1);
+#else
         const F aA = a.c0 * b.c0;
         const F bB = a.c1 * b.c1;
         const F s = (a.c0 + a.c1) * (b.c0 + b.c1);
+#endif
         return Fp2{aA + P2::mul_by_nr(bB), s - aA - bB};
+    }
+    HD static Fp2 sqr_body(const Fp2 &a)
+    {
+#if defined(__CUDA_ARCH__) && defined(B200_OUTLINE_FP2)
+        const F ab = F::mul_inline(a.c0, a.c1);
+        const F t = F::mul_inline(a.c0 + a.c1, a.c0 + P2::mul_by_nr(a.c1));
+#else
+        const F ab = a.c0 * a.c1;
+        const F t = (a.c0 + a.c1) * (a.c0 + P2::mul_by_nr(a.c1));
+#endif
+        return Fp2{t - ab - P2::mul_by_nr(ab), ab + ab};
+    }
+#if defined(__CUDACC__) && defined(B200_OUTLINE_FP2)
+    static __device__ __noinline__ Fp2 mul_outlined(Fp2 a, Fp2 b) { return mul_body(a, b); }
+    static __device__ __noinline__ Fp2 sqr_outlined(Fp2 a) { return sqr_body(a); }
+#endif
+    HD friend Fp2 operator*(const Fp2 &a, const Fp2 &b)
+    {
+#if defined(__CUDA_ARCH__) && defined(B200_OUTLINE_FP2)
+        return mul_outlined(a, b);
+#else
+        return mul_body(a, b);
+#endif
     }
     HD Fp2 sqr() const
     {
-        const F ab = c0 * c1;
-        const F t = (c0 + c1) * (c0 + P2::mul_by_nr(c1));
-        return Fp2{t - ab - P2::mul_by_nr(ab), ab + ab};
+#if defined(__CUDA_ARCH__) && defined(B200_OUTLINE_FP2)
+        return sqr_outlined(*this);
+#else
+        return sqr_body(*this);
+#endif
     }
     HD Fp2 inverse() const
     {

@@ -12,8 +12,11 @@ from oracle import refo  # noqa: E402
 b.init(0)
 print("imad peak (wide, lo) mads/s:", b.imad_peak())
 ref = refo.RefOracle()
-for curve, group, logn in [("alt_bn128", refo.G1, 20), ("alt_bn128", refo.G2, 18), ("bls12_377", refo.G1, 18),
-                           ("bw6_761", refo.G1, 16)]:
+CASES = [("alt_bn128", refo.G1, 20), ("alt_bn128", refo.G2, 18), ("alt_bn128", refo.G2, 20), ("bls12_377", refo.G1, 18),
+         ("bls12_377", refo.G1, 20), ("bls12_377", refo.G2, 18), ("bw6_761", refo.G1, 16), ("bw6_761", refo.G1, 18)]
+if len(sys.argv) > 1:
+    CASES = [c for c in CASES if c[0] in sys.argv[1:] or f"{c[0]}:{c[1]}" in sys.argv[1:]]
+for curve, group, logn in CASES:
     n = 1 << logn
     t0 = time.time()
     bases = ref.make_bases(curve, group, n, 1)
