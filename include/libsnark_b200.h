@@ -138,6 +138,29 @@ int b200_witness_map_h(int curve, const void *aA, const void *aB, const void *aC
 /* Same with device buffers; dA, dB, dC are clobbered, dH (m + 1 elements) may alias none. */
 int b200_witness_map_h_dev(int curve, void *dA, void *dB, void *dC, size_t m, void *dH);
 
+/* ---- R1CS on the device (r1cs_to_qap.tcc:236-248, :293-296) -------- */
+/* The constraint system as ONE CSR over Fr: rows [0, nc) are the a-combinations of the constraints,
+ * [nc, 2nc) the b-, [2nc, 3nc) the c-combinations (libsnark::r1cs_constraint, r1cs.hpp:53-70).
+ * row_ptr has 3*nc + 1 entries; col[e] = linear_term::index (0 is the constant ONE, k the k-th
+ * variable, variable.hpp:96-117); val[e] = linear_term::coeff, Montgomery Fr. Uploaded once per
+ * proving key. */
+typedef uint64_t b200_r1cs_t;
+int b200_r1cs_upload(int curve, size_t num_constraints, size_t num_inputs, size_t num_variables,
+                     const uint32_t *row_ptr, const uint32_t *col, const void *val,
+                     b200_r1cs_t *handle);
+int b200_r1cs_free(b200_r1cs_t handle);
+/* aA, aB, aC (m elements each, host) as r1cs_to_qap_witness_map builds them before its first
+ * transform (r1cs_to_qap.tcc:236-248): w = (1 | primary | auxiliary), num_variables + 1 elements,
+ * host. Includes the input-consistency rows aA[nc + i] = w[i], i <= num_inputs. */
+int b200_r1cs_evaluate(b200_r1cs_t handle, const void *w, size_t m, void *aA, void *aB, void *aC);
+/* The whole of r1cs_to_qap_witness_map for d1 = d2 = d3 = 0 on the device: d_w (device,
+ * num_variables + 1 elements) -> dH = coefficients_for_H (device, m + 1 elements). The MSMs can
+ * then consume d_w and dH in place (b200_msm_resident with scalars_on_device = 1). */
+int b200_witness_map_r1cs_dev(b200_r1cs_t handle, const void *d_w, size_t m, void *dH);
+/* d_dst[i] = d_src[d_idx[i]], Fr elements, all pointers device (the scalars of a sparse
+ * knowledge-commitment query, kc_multiexp.tcc:52-89). */
+int b200_gather_dev(int curve, const void *d_src, const uint32_t *d_idx, size_t n, void *d_dst);
+
 /* ---- measurement helpers (used by bench.py; not part of the reference surface) ------- */
 /* Integer-pipe microbenchmarks, multiply-adds per second: wide = 32x32+64 IMAD.WIDE.U32(.X) chains
  * (what a Montgomery product is made of; two issue slots each), lo = 32-bit IMAD (the pipe's

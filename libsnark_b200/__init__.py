@@ -36,6 +36,7 @@ EXPORTS = [
     "b200_ntt", "b200_ntt_dev", "b200_divide_by_Z_on_coset", "b200_witness_map_h", "b200_witness_map_h_dev",
     "b200_msm_resident_windows_dev", "b200_timer_start", "b200_timer_stop", "b200_make_bases",
     "b200_imad_carry_peak", "b200_imad_peak", "b200_last_msm_timing", "b200_launch_count",
+    "b200_r1cs_upload", "b200_r1cs_free", "b200_r1cs_evaluate", "b200_witness_map_r1cs_dev", "b200_gather_dev",
 ]
 
 
@@ -91,6 +92,11 @@ def lib():
         L.b200_witness_map_h.argtypes = [i, vp, vp, vp, sz, vp]
         L.b200_witness_map_h_dev.argtypes = [i, vp, vp, vp, sz, vp]
         L.b200_imad_peak.argtypes = [i, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        L.b200_r1cs_upload.argtypes = [i, sz, sz, sz, vp, vp, vp, C.POINTER(u64)]
+        L.b200_r1cs_free.argtypes = [u64]
+        L.b200_r1cs_evaluate.argtypes = [u64, vp, sz, vp, vp, vp]
+        L.b200_witness_map_r1cs_dev.argtypes = [u64, vp, sz, vp]
+        L.b200_gather_dev.argtypes = [i, vp, vp, sz, vp]
         L.b200_last_msm_timing.argtypes = [C.POINTER(C.c_double)]
         L.b200_launch_count.restype = u64
         L.b200_msm_resident_windows_dev.argtypes = [u64, sz, sz, vp, i, vp]
@@ -330,6 +336,50 @@ def r1cs_to_qap_witness_map_h(curve, aA, aB, aC):
     out = np.zeros((m + 1, aA.shape[1]), dtype=np.uint64)
     _check(lib().b200_witness_map_h(c, _p(aA), _p(aB), _p(aC), m, _p(out)))
     return out
+
+
+class R1CS:
+    """A constraint system resident on the device as one CSR (rows: a-, b-, c-combinations of the constraints;
+    column 0 = the constant ONE, column k = variable k). Mirrors what libsnark::r1cs_to_qap_witness_map reads from
+    r1cs_constraint_system (r1cs_to_qap.tcc:236-248)."""
+
+    def __init__(self, curve, num_constraints, num_inputs, num_variables, row_ptr, col, val):
+        self.curve, self.nc, self.ni, self.nv = curve, num_constraints, num_inputs, num_variables
+        row_ptr = np.ascontiguousarray(row_ptr, dtype=np.uint32)
+        col = np.ascontiguousarray(col, dtype=np.uint32)
+        val = _u64(val)
+        assert row_ptr.shape[0] == 3 * num_constraints + 1
+        h = C.c_uint64(0)
+        _check(lib().b200_r1cs_upload(_cid(curve), num_constraints, num_inputs, num_variables, _p(row_ptr), _p(col),
+                                      _p(val), C.byref(h)))
+        self.handle = h.value
+        self._limbs = sizeof_fr(curve) // 8
+
+    def evaluate(self, w, m):
+        """(aA, aB, aC), m rows each, from w = (1 | primary | auxiliary)."""
+        w = _u64(w)
+        assert w.shape[0] == self.nv + 1
+        out = [np.zeros((m, self._limbs), dtype=np.uint64) for _ in range(3)]
+        _check(lib().b200_r1cs_evaluate(self.handle, _p(w), m, _p(out[0]), _p(out[1]), _p(out[2])))
+        return out
+
+    def witness_map_h(self, w, m):
+        """coefficients_for_H (m + 1 rows) straight from the witness; everything stays on the device in between."""
+        w = _u64(w)
+        assert w.shape[0] == self.nv + 1
+        dw, dh = DeviceBuffer(w.nbytes), DeviceBuffer((m + 1) * self._limbs * 8)
+        try:
+            dw.upload(w)
+            _check(lib().b200_witness_map_r1cs_dev(self.handle, C.c_void_p(dw.ptr), m, C.c_void_p(dh.ptr)))
+            return dh.download((m + 1, self._limbs))
+        finally:
+            dw.free()
+            dh.free()
+
+    def free(self):
+        if self.handle:
+            _check(lib().b200_r1cs_free(self.handle))
+            self.handle = 0
 
 
 class DeviceBuffer:

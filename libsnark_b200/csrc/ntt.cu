@@ -5,6 +5,7 @@
 #include <map>
 #include <memory>
 #include <mutex>
+#include <vector>
 
 #include "ntt.cuh"
 #include "runtime.hpp"
@@ -337,6 +338,111 @@ template<class Fr> int witness_map_host(const void *aA, const void *aB, const vo
     return B200_OK;
 }
 
+// ---- R1CS on the device -------------------------------------------------------------------------
+struct R1csSet {
+    int curve = -1;
+    size_t nc = 0, ni = 0, nv = 0, nnz = 0, num_long = 0;
+    uint32_t *row_ptr = nullptr, *col = nullptr, *long_rows = nullptr;
+    void *val = nullptr;
+};
+std::map<uint64_t, R1csSet> g_r1cs;
+uint64_t g_next_r1cs = 1;
+
+void free_r1cs(R1csSet &r)
+{
+    cudaFree(r.row_ptr);
+    cudaFree(r.long_rows);
+    cudaFree(r.col);
+    cudaFree(r.val);
+    r = R1csSet();
+}
+
+template<class Fr>
+int r1cs_upload(R1csSet &r, const uint32_t *row_ptr, const uint32_t *col, const void *val)
+{
+    cudaStream_t s = rt::stream();
+    const size_t rows = 3 * r.nc + 1;
+    B200_CUDA_CHECK(cudaMalloc((void **)&r.row_ptr, rows * 4));
+    B200_CUDA_CHECK(cudaMalloc((void **)&r.col, (r.nnz ? r.nnz : 1) * 4));
+    B200_CUDA_CHECK(cudaMalloc(&r.val, (r.nnz ? r.nnz : 1) * sizeof(Fr)));
+    B200_CUDA_CHECK(cudaMemcpyAsync(r.row_ptr, row_ptr, rows * 4, cudaMemcpyHostToDevice, s));
+    std::vector<uint32_t> long_rows;
+    for (size_t i = 0; i + 1 < rows; ++i) {
+        if (row_ptr[i + 1] - row_ptr[i] > ntt::R1CS_LONG_ROW) {
+            long_rows.push_back((uint32_t)i);
+        }
+    }
+    r.num_long = long_rows.size();
+    if (r.num_long) {
+        B200_CUDA_CHECK(cudaMalloc((void **)&r.long_rows, r.num_long * 4));
+        B200_CUDA_CHECK(cudaMemcpyAsync(r.long_rows, long_rows.data(), r.num_long * 4, cudaMemcpyHostToDevice, s));
+    }
+    if (r.nnz) {
+        B200_CUDA_CHECK(cudaMemcpyAsync(r.col, col, r.nnz * 4, cudaMemcpyHostToDevice, s));
+        B200_CUDA_CHECK(cudaMemcpyAsync(r.val, val, r.nnz * sizeof(Fr), cudaMemcpyHostToDevice, s));
+    }
+    B200_CUDA_CHECK(cudaStreamSynchronize(s));
+    return B200_OK;
+}
+
+template<class Fr> int r1cs_eval_launch(const R1csSet &r, const Fr *d_w, size_t m, Fr *aA, Fr *aB, Fr *aC)
+{
+    cudaStream_t s = rt::stream();
+    ntt::k_r1cs_eval<Fr><<<grid_for(3 * m, 256), 256, 0, s>>>(
+        r.nc, r.ni, m, r.row_ptr, r.col, static_cast<const Fr *>(r.val), d_w, aA, aB, aC);
+    B200_LAUNCH_CHECK();
+    if (r.num_long) {
+        ntt::k_r1cs_eval_long<Fr><<<(unsigned)r.num_long, ntt::R1CS_LONG_THREADS, 0, s>>>(
+            r.nc, r.long_rows, r.row_ptr, r.col, static_cast<const Fr *>(r.val), d_w, aA, aB, aC);
+        B200_LAUNCH_CHECK();
+    }
+    return B200_OK;
+}
+
+// d_w: (1 | primary | auxiliary), nv + 1 elements on the device. dH: m + 1 elements on the device.
+template<class Fr> int witness_map_r1cs_dev(const R1csSet &r, const void *d_w, size_t m, void *dH)
+{
+    if (m < r.nc + r.ni + 1) {
+        return rt::set_error(B200_ERR_DOMAIN, "domain size %zu < num_constraints + num_inputs + 1 = %zu", m,
+                             r.nc + r.ni + 1);
+    }
+    const size_t bytes = m * sizeof(Fr);
+    if (g_bufA.reserve(bytes) || g_bufB.reserve(bytes) || g_bufC.reserve(bytes)) {
+        return B200_ERR_CUDA;
+    }
+    if (int rc = r1cs_eval_launch<Fr>(r, static_cast<const Fr *>(d_w), m, g_bufA.as<Fr>(), g_bufB.as<Fr>(), g_bufC.as<Fr>())) {
+        return rc;
+    }
+    return witness_map_dev<Fr>(g_bufA.as<Fr>(), g_bufB.as<Fr>(), g_bufC.as<Fr>(), m, static_cast<Fr *>(dH));
+}
+
+template<class Fr> int r1cs_eval_host(const R1csSet &r, const void *w_host, size_t m, void *aA, void *aB, void *aC)
+{
+    const size_t bytes = m * sizeof(Fr);
+    if (g_bufA.reserve(bytes) || g_bufB.reserve(bytes) || g_bufC.reserve(bytes) || g_bufH.reserve((r.nv + 1) * sizeof(Fr))) {
+        return B200_ERR_CUDA;
+    }
+    cudaStream_t s = rt::stream();
+    B200_CUDA_CHECK(cudaMemcpyAsync(g_bufH.p, w_host, (r.nv + 1) * sizeof(Fr), cudaMemcpyHostToDevice, s));
+    if (int rc = r1cs_eval_launch<Fr>(r, g_bufH.as<Fr>(), m, g_bufA.as<Fr>(), g_bufB.as<Fr>(), g_bufC.as<Fr>())) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaMemcpyAsync(aA, g_bufA.p, bytes, cudaMemcpyDeviceToHost, s));
+    B200_CUDA_CHECK(cudaMemcpyAsync(aB, g_bufB.p, bytes, cudaMemcpyDeviceToHost, s));
+    B200_CUDA_CHECK(cudaMemcpyAsync(aC, g_bufC.p, bytes, cudaMemcpyDeviceToHost, s));
+    B200_CUDA_CHECK(cudaStreamSynchronize(s));
+    return B200_OK;
+}
+
+template<class Fr> int gather_dev(const void *d_src, const uint32_t *d_idx, size_t n, void *d_dst)
+{
+    ntt::k_gather<Fr><<<grid_for(n ? n : 1, 256), 256, 0, rt::stream()>>>(
+        n, static_cast<const Fr *>(d_src), d_idx, static_cast<Fr *>(d_dst));
+    B200_LAUNCH_CHECK();
+    B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
+    return B200_OK;
+}
+
 #define DISPATCH_FR(curve, call)                                                                   \
     switch (curve) {                                                                               \
     case B200_ALT_BN128: {                                                                         \
@@ -433,6 +539,118 @@ int b200_witness_map_h_dev(int curve, void *dA, void *dB, void *dC, size_t m, vo
     }
     B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
     return B200_OK;
+}
+
+int b200_r1cs_upload(int curve, size_t num_constraints, size_t num_inputs, size_t num_variables,
+                     const uint32_t *row_ptr, const uint32_t *col, const void *val, b200_r1cs_t *handle)
+{
+    if (!row_ptr || !handle || num_inputs > num_variables) {
+        return rt::set_error(B200_ERR_ARG, "bad R1CS arguments");
+    }
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    const size_t nnz = row_ptr[3 * num_constraints];
+    if (row_ptr[0] != 0 || (nnz && (!col || !val)) || 3 * (num_constraints + num_inputs + 1) >= 0xffffffffull) {
+        return rt::set_error(B200_ERR_ARG, "bad R1CS CSR");
+    }
+    for (size_t i = 0; i < 3 * num_constraints; ++i) {
+        if (row_ptr[i] > row_ptr[i + 1]) {
+            return rt::set_error(B200_ERR_ARG, "row_ptr not monotone at %zu", i);
+        }
+    }
+    for (size_t e = 0; e < nnz; ++e) {
+        if (col[e] > num_variables) {
+            return rt::set_error(B200_ERR_ARG, "column %u > num_variables %zu", col[e], num_variables);
+        }
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    R1csSet r;
+    r.curve = curve;
+    r.nc = num_constraints;
+    r.ni = num_inputs;
+    r.nv = num_variables;
+    r.nnz = nnz;
+    int rc;
+    switch (curve) {
+    case B200_ALT_BN128: rc = r1cs_upload<alt_bn128_fr>(r, row_ptr, col, val); break;
+    case B200_BLS12_377: rc = r1cs_upload<bls12_377_fr>(r, row_ptr, col, val); break;
+    case B200_BW6_761: rc = r1cs_upload<bw6_761_fr>(r, row_ptr, col, val); break;
+    default: return rt::set_error(B200_ERR_ARG, "unknown curve %d", curve);
+    }
+    if (rc) {
+        free_r1cs(r);
+        return rc;
+    }
+    *handle = g_next_r1cs++;
+    g_r1cs[*handle] = r;
+    return B200_OK;
+}
+
+int b200_r1cs_free(b200_r1cs_t handle)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_r1cs.find(handle);
+    if (it == g_r1cs.end()) {
+        return rt::set_error(B200_ERR_HANDLE, "unknown R1CS handle %llu", (unsigned long long)handle);
+    }
+    cudaStreamSynchronize(rt::stream());
+    free_r1cs(it->second);
+    g_r1cs.erase(it);
+    return B200_OK;
+}
+
+int b200_r1cs_evaluate(b200_r1cs_t handle, const void *w, size_t m, void *aA, void *aB, void *aC)
+{
+    if (!w || !aA || !aB || !aC) {
+        return rt::set_error(B200_ERR_ARG, "null pointer");
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_r1cs.find(handle);
+    if (it == g_r1cs.end()) {
+        return rt::set_error(B200_ERR_HANDLE, "unknown R1CS handle %llu", (unsigned long long)handle);
+    }
+    const R1csSet &r = it->second;
+    if (m < r.nc + r.ni + 1) {
+        return rt::set_error(B200_ERR_DOMAIN, "m = %zu < num_constraints + num_inputs + 1", m);
+    }
+    DISPATCH_FR(r.curve, r1cs_eval_host<Fr>(r, w, m, aA, aB, aC));
+}
+
+int b200_witness_map_r1cs_dev(b200_r1cs_t handle, const void *d_w, size_t m, void *dH)
+{
+    if (!d_w || !dH) {
+        return rt::set_error(B200_ERR_ARG, "null pointer");
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_r1cs.find(handle);
+    if (it == g_r1cs.end()) {
+        return rt::set_error(B200_ERR_HANDLE, "unknown R1CS handle %llu", (unsigned long long)handle);
+    }
+    const R1csSet &r = it->second;
+    int rc;
+    switch (r.curve) {
+    case B200_ALT_BN128: rc = witness_map_r1cs_dev<alt_bn128_fr>(r, d_w, m, dH); break;
+    case B200_BLS12_377: rc = witness_map_r1cs_dev<bls12_377_fr>(r, d_w, m, dH); break;
+    default: rc = witness_map_r1cs_dev<bw6_761_fr>(r, d_w, m, dH); break;
+    }
+    if (rc) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
+    return B200_OK;
+}
+
+int b200_gather_dev(int curve, const void *d_src, const uint32_t *d_idx, size_t n, void *d_dst)
+{
+    if (n && (!d_src || !d_idx || !d_dst)) {
+        return rt::set_error(B200_ERR_ARG, "null pointer");
+    }
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    DISPATCH_FR(curve, gather_dev<Fr>(d_src, d_idx, n, d_dst));
 }
 
 } // extern "C"

@@ -344,6 +344,78 @@ template<class Fr> __global__ void k_scale(uint64_t m, Fr *a, const Fr *c)
     }
 }
 
+constexpr uint32_t R1CS_LONG_ROW = 64;
+constexpr int R1CS_LONG_THREADS = 256;
+
+// Sparse R1CS evaluation (r1cs_to_qap.tcc:236-248, :293-296; linear_combination::evaluate,
+// variable.tcc:288-299): rows [0, nc) of A, [nc, 2nc) of B, [2nc, 3nc) of C in one CSR.
+// Column 0 is the constant 1, column k the k-th variable, so w = (1 | primary | auxiliary) is indexed
+// directly. One thread per row; rows of R1CS matrices hold a handful of terms. Also writes the
+// input-consistency rows aA[nc + i] = w[i], i <= num_inputs (:240-243) and zeroes the padding up to m.
+template<class Fr>
+__global__ void k_r1cs_eval(uint64_t nc, uint64_t ni, uint64_t m, const uint32_t *row_ptr, const uint32_t *col,
+                            const Fr *val, const Fr *w, Fr *aA, Fr *aB, Fr *aC)
+{
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= 3 * m) {
+        return;
+    }
+    const uint64_t mat = t / m, i = t - mat * m;
+    Fr *dst = mat == 0 ? aA : (mat == 1 ? aB : aC);
+    Fr acc = Fr::zero();
+    if (i < nc) {
+        const uint64_t row = mat * nc + i;
+        const uint32_t e0 = row_ptr[row], e1 = row_ptr[row + 1];
+        if (e1 - e0 > R1CS_LONG_ROW) {
+            return; // k_r1cs_eval_long owns this row
+        }
+        for (uint32_t e = e0; e < e1; ++e) {
+            acc = acc + gload(val + e) * gload(w + col[e]);
+        }
+    } else if (mat == 0 && i - nc <= ni) {
+        acc = gload(w + (i - nc));
+    }
+    gstore(dst + i, acc);
+}
+
+// Rows with more than R1CS_LONG_ROW terms (a sum over all variables is a common last constraint):
+// one CTA per row, strided partial sums, shared-memory tree.
+template<class Fr>
+__global__ void __launch_bounds__(R1CS_LONG_THREADS)
+    k_r1cs_eval_long(uint64_t nc, const uint32_t *long_rows, const uint32_t *row_ptr, const uint32_t *col, const Fr *val,
+                     const Fr *w, Fr *aA, Fr *aB, Fr *aC)
+{
+    __shared__ Fr part[R1CS_LONG_THREADS];
+    const uint64_t row = long_rows[blockIdx.x];
+    const uint32_t e0 = row_ptr[row], e1 = row_ptr[row + 1];
+    Fr acc = Fr::zero();
+    for (uint32_t e = e0 + threadIdx.x; e < e1; e += R1CS_LONG_THREADS) {
+        acc = acc + gload(val + e) * gload(w + col[e]);
+    }
+    part[threadIdx.x] = acc;
+    __syncthreads();
+    for (int half = R1CS_LONG_THREADS / 2; half > 0; half >>= 1) {
+        if ((int)threadIdx.x < half) {
+            part[threadIdx.x] = part[threadIdx.x] + part[threadIdx.x + half];
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const uint64_t mat = row / nc, i = row - mat * nc;
+        Fr *dst = mat == 0 ? aA : (mat == 1 ? aB : aC);
+        gstore(dst + i, part[0]);
+    }
+}
+
+// dst[i] = src[idx[i]]
+template<class Fr> __global__ void k_gather(uint64_t n, const Fr *src, const uint32_t *idx, Fr *dst)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        gstore(dst + i, gload(src + idx[i]));
+    }
+}
+
 #endif // __CUDACC__
 
 } // namespace ntt

@@ -28,7 +28,9 @@
 #ifndef LIBSNARK_B200_OVERLAY_HPP_
 #define LIBSNARK_B200_OVERLAY_HPP_
 
+#include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <stdexcept>
@@ -46,6 +48,7 @@
 #include <libfqfft/tools/exceptions.hpp>
 #include <libsnark/knowledge_commitment/kc_multiexp.hpp>
 #include <libsnark/reductions/r1cs_to_qap/r1cs_to_qap.hpp>
+#include <libsnark/zk_proof_systems/ppzksnark/r1cs_gg_ppzksnark/r1cs_gg_ppzksnark.hpp>
 
 #include "libsnark_b200.h"
 
@@ -225,6 +228,242 @@ libsnark::qap_witness<FieldT> r1cs_to_qap_witness_map_fused(
           "b200_witness_map_h");
     return libsnark::qap_witness<FieldT>(
         cs.num_variables(), m, cs.num_inputs(), FieldT::zero(), FieldT::zero(), FieldT::zero(), full, std::move(H));
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Device-resident prover (SURVEY.md §8f N1 + N2): the orchestration of r1cs_gg_ppzksnark_prover
+// (r1cs_gg_ppzksnark.tcc:460-603) with the witness uploaded ONCE and everything between the witness
+// and the five MSM results kept on the device: sparse R1CS evaluation, the seven transforms, and the
+// scalars of all MSMs (the witness itself and coefficients_for_H) never return to the host.
+// The operator-level specialisations above stay available; this is the one-call alternative for
+// callers that can change the line that invokes the prover.
+struct device_buffer {
+    void *p = nullptr;
+    size_t cap = 0;
+    void reserve(size_t bytes)
+    {
+        if (bytes <= cap) {
+            return;
+        }
+        if (p) {
+            b200_dev_free(p);
+            p = nullptr;
+        }
+        check(b200_dev_alloc(bytes, &p), "b200_dev_alloc");
+        cap = bytes;
+    }
+    ~device_buffer()
+    {
+        // process exit: the CUDA context may already be gone; leak rather than call into it
+    }
+};
+
+struct r1cs_cache {
+    struct entry {
+        b200_r1cs_t handle = 0;
+        size_t nc = 0, nv = 0;
+    };
+    std::map<const void *, entry> sets;
+    static r1cs_cache &get()
+    {
+        static r1cs_cache c;
+        return c;
+    }
+    template<typename FieldT> b200_r1cs_t lookup(const libsnark::r1cs_constraint_system<FieldT> &cs)
+    {
+        auto it = sets.find(&cs);
+        if (it != sets.end() && it->second.nc == cs.num_constraints() && it->second.nv == cs.num_variables()) {
+            return it->second.handle;
+        }
+        const size_t nc = cs.num_constraints();
+        std::vector<uint32_t> row_ptr(3 * nc + 1, 0);
+        size_t nnz = 0;
+        for (size_t i = 0; i < nc; ++i) {
+            nnz += cs.constraints[i].a.terms.size() + cs.constraints[i].b.terms.size() + cs.constraints[i].c.terms.size();
+        }
+        std::vector<uint32_t> col(nnz);
+        std::vector<FieldT> val(nnz);
+        size_t e = 0;
+        for (int mat = 0; mat < 3; ++mat) {
+            for (size_t i = 0; i < nc; ++i) {
+                const libsnark::linear_combination<FieldT> &lc =
+                    mat == 0 ? cs.constraints[i].a : (mat == 1 ? cs.constraints[i].b : cs.constraints[i].c);
+                row_ptr[mat * nc + i] = (uint32_t)e;
+                for (const auto &t : lc.terms) {
+                    col[e] = (uint32_t)t.index;
+                    val[e] = t.coeff;
+                    ++e;
+                }
+            }
+        }
+        row_ptr[3 * nc] = (uint32_t)e;
+        entry en;
+        en.nc = nc;
+        en.nv = cs.num_variables();
+        check(b200_r1cs_upload(curve_of<FieldT>::curve, nc, cs.num_inputs(), cs.num_variables(), row_ptr.data(),
+                               col.data(), val.data(), &en.handle),
+              "b200_r1cs_upload");
+        sets[&cs] = en;
+        return en.handle;
+    }
+    void clear()
+    {
+        for (auto &kv : sets) {
+            b200_r1cs_free(kv.second.handle);
+        }
+        sets.clear();
+    }
+};
+inline void release_cached_r1cs() { r1cs_cache::get().clear(); }
+
+// device copy of a sparse query's index list (or nothing when the query is dense)
+struct index_cache {
+    struct entry {
+        void *d_idx = nullptr;
+        bool dense = true;
+        size_t n = 0;
+    };
+    std::map<const void *, entry> sets;
+    static index_cache &get()
+    {
+        static index_cache c;
+        return c;
+    }
+    const entry &lookup(const std::vector<size_t> &indices)
+    {
+        auto it = sets.find(indices.data());
+        if (it != sets.end() && it->second.n == indices.size()) {
+            return it->second;
+        }
+        entry en;
+        en.n = indices.size();
+        std::vector<uint32_t> idx(indices.size());
+        for (size_t k = 0; k < indices.size(); ++k) {
+            idx[k] = (uint32_t)indices[k];
+            en.dense = en.dense && indices[k] == k;
+        }
+        if (!en.dense) {
+            check(b200_dev_alloc(idx.size() * 4, &en.d_idx), "b200_dev_alloc");
+            check(b200_memcpy_h2d(en.d_idx, idx.data(), idx.size() * 4), "b200_memcpy_h2d");
+        }
+        return sets[indices.data()] = en;
+    }
+};
+
+template<typename ppT>
+libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
+    const libsnark::r1cs_gg_ppzksnark_proving_key<ppT> &pk,
+    const libsnark::r1cs_gg_ppzksnark_primary_input<ppT> &primary_input,
+    const libsnark::r1cs_gg_ppzksnark_auxiliary_input<ppT> &auxiliary_input, const libff::Fr<ppT> &r,
+    const libff::Fr<ppT> &s)
+{
+    typedef libff::Fr<ppT> FrT;
+    typedef libff::G1<ppT> G1T;
+    typedef libff::G2<ppT> G2T;
+    typedef libsnark::knowledge_commitment<G2T, G1T> KC;
+    const int curve = curve_of<FrT>::curve;
+    const auto &cs = pk.constraint_system;
+    const size_t nv = cs.num_variables(), ni = cs.num_inputs();
+    if (primary_input.size() != ni || primary_input.size() + auxiliary_input.size() != nv) {
+        throw std::runtime_error("libsnark_b200: witness size does not match the constraint system");
+    }
+    const size_t m = libfqfft::get_evaluation_domain<FrT>(cs.num_constraints() + ni + 1)->m;
+    static const bool trace = getenv("B200_OVERLAY_TRACE") != nullptr;
+    long long t_prev = libff::get_nsec_time();
+    auto lap = [&](const char *what) {
+        if (trace) {
+            const long long now = libff::get_nsec_time();
+            fprintf(stderr, "[b200 fused prover] %-28s %9.3f ms\n", what, (now - t_prev) * 1e-6);
+            t_prev = now;
+        }
+    };
+
+    // (1 | primary | auxiliary): const_padded_assignment of r1cs_gg_ppzksnark.tcc:525-529
+    static std::vector<FrT> w;
+    w.resize(nv + 1);
+    w[0] = FrT::one();
+    std::copy(primary_input.begin(), primary_input.end(), w.begin() + 1);
+    std::copy(auxiliary_input.begin(), auxiliary_input.end(), w.begin() + 1 + ni);
+
+    static device_buffer d_w, d_h, d_g;
+    d_w.reserve((nv + 1) * sizeof(FrT));
+    d_h.reserve((m + 1) * sizeof(FrT));
+    lap("assemble witness");
+    check(b200_memcpy_h2d(d_w.p, w.data(), (nv + 1) * sizeof(FrT)), "b200_memcpy_h2d (witness)");
+    lap("witness H2D");
+
+    // r1cs_to_qap_witness_map with d1 = d2 = d3 = 0 (:497): coefficients_for_H stays on the device
+    const b200_r1cs_t hr = r1cs_cache::get().lookup(cs);
+    lap("R1CS lookup");
+    check(b200_witness_map_r1cs_dev(hr, d_w.p, m, d_h.p), "b200_witness_map_r1cs_dev");
+    lap("witness map (device)");
+
+    bases_cache &bc = bases_cache::get();
+    const FrT *dw = static_cast<const FrT *>(d_w.p);
+    // A (:531-541): A_query[0 .. nv] x w
+    G1T evaluation_At = G1T::zero();
+    {
+        const b200_bases_t h = bc.lookup(curve, B200_G1, pk.A_query.data(), sizeof(G1T), pk.A_query.size(), sizeof(G1T));
+        lap("A lookup");
+        check(b200_msm_resident(h, 0, nv + 1, dw, 1, &evaluation_At), "b200_msm_resident (A)");
+        lap("A msm");
+    }
+    // B (:545-555): sparse knowledge-commitment query, entries with index in [0, nv]
+    KC evaluation_Bt(G2T::zero(), G1T::zero());
+    {
+        const auto &vec = pk.B_query;
+        const size_t cnt = std::lower_bound(vec.indices.begin(), vec.indices.end(), nv + 1) - vec.indices.begin();
+        if (cnt) {
+            const unsigned char *vals = reinterpret_cast<const unsigned char *>(vec.values.data());
+            const size_t off2 = reinterpret_cast<const unsigned char *>(&vec.values[0].h) - vals;
+            const b200_bases_t hg = bc.lookup(curve, B200_G2, vals, sizeof(KC), vec.values.size(), sizeof(G2T));
+            const b200_bases_t hh = bc.lookup(curve, B200_G1, vals + off2, sizeof(KC), vec.values.size(), sizeof(G1T));
+            const index_cache::entry &ix = index_cache::get().lookup(vec.indices);
+            const void *sc = dw;
+            if (!ix.dense) {
+                d_g.reserve(cnt * sizeof(FrT));
+                check(b200_gather_dev(curve, dw, static_cast<const uint32_t *>(ix.d_idx), cnt, d_g.p), "b200_gather_dev");
+                sc = d_g.p;
+            }
+            lap("B lookup + gather");
+            check(b200_msm_resident(hg, 0, cnt, sc, 1, &evaluation_Bt.g), "b200_msm_resident (B.g)");
+            lap("B.g msm (G2)");
+            check(b200_msm_resident(hh, 0, cnt, sc, 1, &evaluation_Bt.h), "b200_msm_resident (B.h)");
+            lap("B.h msm (G1)");
+        }
+    }
+    // H (:561-567): H_query[0 .. m-2] x coefficients_for_H
+    G1T evaluation_Ht = G1T::zero();
+    {
+        const b200_bases_t h = bc.lookup(curve, B200_G1, pk.H_query.data(), sizeof(G1T), pk.H_query.size(), sizeof(G1T));
+        check(b200_msm_resident(h, 0, m - 1, d_h.p, 1, &evaluation_Ht), "b200_msm_resident (H)");
+        lap("H lookup + msm");
+    }
+    // L (:570-580): L_query x w[ni+1 .. nv]
+    G1T evaluation_Lt = G1T::zero();
+    {
+        const b200_bases_t h = bc.lookup(curve, B200_G1, pk.L_query.data(), sizeof(G1T), pk.L_query.size(), sizeof(G1T));
+        check(b200_msm_resident(h, 0, pk.L_query.size(), dw + ni + 1, 1, &evaluation_Lt), "b200_msm_resident (L)");
+        lap("L lookup + msm");
+    }
+    // :583-595, unchanged
+    const G1T g1_A = pk.alpha_g1 + evaluation_At + r * pk.delta_g1;
+    const G1T g1_B = pk.beta_g1 + evaluation_Bt.h + s * pk.delta_g1;
+    const G2T g2_B = pk.beta_g2 + evaluation_Bt.g + s * pk.delta_g2;
+    const G1T g1_C = evaluation_Ht + evaluation_Lt + s * g1_A + r * g1_B - (r * s) * pk.delta_g1;
+    lap("proof assembly");
+    return libsnark::r1cs_gg_ppzksnark_proof<ppT>(G1T(g1_A), G2T(g2_B), G1T(g1_C));
+}
+
+// Drop-in for r1cs_gg_ppzksnark_prover(pk, primary, auxiliary): r, s drawn as the reference draws them (:499-500).
+template<typename ppT>
+libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
+    const libsnark::r1cs_gg_ppzksnark_proving_key<ppT> &pk,
+    const libsnark::r1cs_gg_ppzksnark_primary_input<ppT> &primary_input,
+    const libsnark::r1cs_gg_ppzksnark_auxiliary_input<ppT> &auxiliary_input)
+{
+    return r1cs_gg_ppzksnark_prover_fused<ppT>(
+        pk, primary_input, auxiliary_input, libff::Fr<ppT>::random_element(), libff::Fr<ppT>::random_element());
 }
 
 } // namespace libsnark_b200

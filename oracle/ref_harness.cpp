@@ -605,6 +605,65 @@ template<typename ppT> struct H {
         return 0;
     }
 
+    // Overlay build only: the device-resident prover of libsnark_b200_overlay.hpp, same output layout.
+    static int prove_fused(const groth16_fixture<ppT> *f, const void *r_, const void *s_, void *out, double *ms)
+    {
+#ifdef B200_OVERLAY
+        const FrT r = *static_cast<const FrT *>(r_);
+        const FrT s = *static_cast<const FrT *>(s_);
+        const long long t0 = get_nsec_time();
+        r1cs_gg_ppzksnark_proof<ppT> p = libsnark_b200::r1cs_gg_ppzksnark_prover_fused<ppT>(
+            f->keypair.pk, f->example.primary_input, f->example.auxiliary_input, r, s);
+        if (ms) {
+            *ms = (get_nsec_time() - t0) * 1e-6;
+        }
+        G1T a = p.g_A, c = p.g_C;
+        G2T b = p.g_B;
+        a.to_affine_coordinates();
+        b.to_affine_coordinates();
+        c.to_affine_coordinates();
+        char *o = static_cast<char *>(out);
+        memcpy(o, &a, sizeof(G1T));
+        memcpy(o + sizeof(G1T), &b, sizeof(G2T));
+        memcpy(o + sizeof(G1T) + sizeof(G2T), &c, sizeof(G1T));
+        return 0;
+#else
+        (void)f; (void)r_; (void)s_; (void)out; (void)ms;
+        return -7; // the stock build has no device prover
+#endif
+    }
+
+    // The constraint system as one CSR (rows: a-, b-, c-combinations; col 0 = ONE), for feeding
+    // b200_r1cs_upload in tests. Call with null arrays to get nnz.
+    static int r1cs_csr(const groth16_fixture<ppT> *f, uint32_t *row_ptr, uint32_t *col, void *val, uint64_t *nnz_out)
+    {
+        const auto &cs = f->example.constraint_system;
+        const size_t nc = cs.num_constraints();
+        FrT *v = static_cast<FrT *>(val);
+        size_t e = 0;
+        for (int mat = 0; mat < 3; ++mat) {
+            for (size_t i = 0; i < nc; ++i) {
+                const linear_combination<FrT> &lc =
+                    mat == 0 ? cs.constraints[i].a : (mat == 1 ? cs.constraints[i].b : cs.constraints[i].c);
+                if (row_ptr) {
+                    row_ptr[mat * nc + i] = (uint32_t)e;
+                }
+                for (const auto &t : lc.terms) {
+                    if (col) {
+                        col[e] = (uint32_t)t.index;
+                        v[e] = t.coeff;
+                    }
+                    ++e;
+                }
+            }
+        }
+        if (row_ptr) {
+            row_ptr[3 * nc] = (uint32_t)e;
+        }
+        *nnz_out = e;
+        return 0;
+    }
+
     // The reference's own prover entry point (random r, s); returns the proof
     // the same way. Used to show the overlay is a drop-in for the unmodified
     // r1cs_gg_ppzksnark_prover.
@@ -998,6 +1057,20 @@ API int ref_groth16_prove(void *h_, const void *r, const void *s, void *out, dou
 {
     fixture_handle *h = static_cast<fixture_handle *>(h_);
     DISPATCH_FIXTURE(h, prove, r, s, out, stage_ms);
+    return -100;
+}
+
+API int ref_groth16_prove_fused(void *h_, const void *r, const void *s, void *out, double *ms)
+{
+    fixture_handle *h = static_cast<fixture_handle *>(h_);
+    DISPATCH_FIXTURE(h, prove_fused, r, s, out, ms);
+    return -100;
+}
+
+API int ref_groth16_r1cs_csr(void *h_, uint32_t *row_ptr, uint32_t *col, void *val, uint64_t *nnz)
+{
+    fixture_handle *h = static_cast<fixture_handle *>(h_);
+    DISPATCH_FIXTURE(h, r1cs_csr, row_ptr, col, val, nnz);
     return -100;
 }
 

@@ -52,6 +52,8 @@ class RefOracle:
         L.ref_groth16_prove.argtypes = [C.c_void_p] * 5
         L.ref_groth16_abc_evaluations.argtypes = [C.c_void_p] * 4
         L.ref_groth16_prove_stock.argtypes = [C.c_void_p] * 3
+        L.ref_groth16_prove_fused.argtypes = [C.c_void_p] * 5
+        L.ref_groth16_r1cs_csr.argtypes = [C.c_void_p] * 5
         L.ref_groth16_verify.argtypes = [C.c_void_p, C.c_void_p]
         L.ref_bdlo12_signed_optimal_c.restype = C.c_uint64
         L.ref_bdlo12_signed_optimal_c.argtypes = [C.c_uint64]
@@ -300,6 +302,31 @@ class Groth16Fixture:
         assert lib.ref_groth16_prove(self.h, _p(r), _p(s), _p(out), _p(ms)) == 0
         stages = dict(zip(["witness_map", "A", "B", "H", "L", "total"], ms.tolist()))
         return out, stages
+
+    def prove_fused(self, r, s, via):
+        """The overlay's device-resident prover (libsnark_b200::r1cs_gg_ppzksnark_prover_fused) on this fixture."""
+        r = np.ascontiguousarray(r, dtype=np.uint64)
+        s = np.ascontiguousarray(s, dtype=np.uint64)
+        out = np.zeros(self.proof_limbs(), dtype=np.uint64)
+        ms = C.c_double(0)
+        rc = via.lib.ref_groth16_prove_fused(self.h, _p(r), _p(s), _p(out), C.byref(ms))
+        assert rc == 0, rc
+        return out, ms.value
+
+    def r1cs_csr(self):
+        """(row_ptr, col, val): the constraint system as one CSR over Fr, rows = a | b | c combinations."""
+        nnz = C.c_uint64(0)
+        assert self.ref.lib.ref_groth16_r1cs_csr(self.h, None, None, None, C.byref(nnz)) == 0
+        row_ptr = np.zeros(3 * self.sizes["num_constraints"] + 1, dtype=np.uint32)
+        col = np.zeros(max(1, nnz.value), dtype=np.uint32)
+        val = np.zeros((max(1, nnz.value), self.i["nr"]), dtype=np.uint64)
+        assert self.ref.lib.ref_groth16_r1cs_csr(self.h, _p(row_ptr), _p(col), _p(val), C.byref(nnz)) == 0
+        return row_ptr, col[:nnz.value], val[:nnz.value]
+
+    def full_assignment(self):
+        """w = (1 | primary | auxiliary), Montgomery Fr."""
+        one = self.ref.field_consts(self.curve, FR)["one"]
+        return np.concatenate([np.asarray(one, dtype=np.uint64)[None, :], self.primary_input, self.auxiliary_input])
 
     def prove_stock(self, via=None):
         out = np.zeros(self.proof_limbs(), dtype=np.uint64)

@@ -68,3 +68,46 @@ def test_overlay_operators_match_reference(ref, overlay):
         assert np.array_equal(overlay.fft(curve, op, a, g, via_factory=True), ref.fft(curve, op, a, g))
     with pytest.raises(RuntimeError):
         overlay.fft(curve, refo.FFT, a[:100], via_factory=False)
+
+
+@pytest.mark.parametrize("curve,nc,ni", [("alt_bn128", 1000, 10), ("alt_bn128", (1 << 14) - 11, 10), ("bls12_377", 500, 3),
+                                         ("bw6_761", 200, 5)])
+def test_r1cs_evaluation_and_witness_map_on_device(ref, b200, curve, nc, ni):
+    """b200_r1cs_evaluate == the aA/aB/aC the reference builds (r1cs_to_qap.tcc:236-248) and
+    b200_witness_map_r1cs_dev == every coefficient of H (r1cs_to_qap.tcc:252-330), straight from the witness."""
+    fx = ref.groth16_setup(curve, nc, ni, real_keys=False)
+    try:
+        row_ptr, col, val = fx.r1cs_csr()
+        w = fx.full_assignment()
+        m = fx.sizes["m"]
+        cs = b200.R1CS(curve, fx.sizes["num_constraints"], fx.sizes["num_inputs"], fx.sizes["num_variables"], row_ptr, col, val)
+        try:
+            for got, want in zip(cs.evaluate(w, m), fx.abc_evaluations()):
+                assert np.array_equal(got, want)
+            assert np.array_equal(cs.witness_map_h(w, m), fx.witness_map()[0])
+            with pytest.raises(b200.DomainSizeException):
+                cs.evaluate(w, 4)
+        finally:
+            cs.free()
+    finally:
+        fx.close()
+
+
+@pytest.mark.parametrize("curve,log_m,real_keys", [("alt_bn128", 10, True), ("alt_bn128", 16, False), ("bls12_377", 10, True),
+                                                   ("bw6_761", 8, True)])
+def test_device_resident_prover_bit_exact(ref, overlay, curve, log_m, real_keys):
+    """libsnark_b200::r1cs_gg_ppzksnark_prover_fused (witness uploaded once, R1CS evaluation + transforms + MSM scalars
+    all on the device) gives the reference's proof bit for bit, and the reference verifier accepts it."""
+    ni = 10
+    fx = ref.groth16_setup(curve, (1 << log_m) - ni - 1, ni, real_keys=real_keys)
+    try:
+        rs = ref.field_random(curve, refo.FR, 0x5EED, 2)
+        want, _ = fx.prove(rs[0], rs[1])
+        got, _ = fx.prove_fused(rs[0], rs[1], via=overlay)
+        assert np.array_equal(got, want)
+        got2, _ = fx.prove_fused(rs[0], rs[1], via=overlay)      # second call: cached key and CSR
+        assert np.array_equal(got2, want)
+        if real_keys:
+            assert fx.verify(got) == 1
+    finally:
+        fx.close()
