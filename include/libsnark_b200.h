@@ -161,6 +161,30 @@ int b200_witness_map_r1cs_dev(b200_r1cs_t handle, const void *d_w, size_t m, voi
  * knowledge-commitment query, kc_multiexp.tcc:52-89). */
 int b200_gather_dev(int curve, const void *d_src, const uint32_t *d_idx, size_t n, void *d_dst);
 
+/* ---- the prover in one call (r1cs_gg_ppzksnark_prover, r1cs_gg_ppzksnark.tcc:460-603) ---------- */
+/* A proving key assembled from handles that are already on the device: the four queries
+ * (r1cs_gg_ppzksnark_proving_key, r1cs_gg_ppzksnark.hpp:74-170; B_query split into its G2 and G1
+ * halves, B_indices = sparse_vector::indices or NULL when every index 0..num_variables is
+ * present), the constraint system, and the five single points in the reference's layout.
+ * The handle does not own the queries or the R1CS. domain_size = the m of
+ * get_evaluation_domain(num_constraints + num_inputs + 1), a power of two. */
+typedef uint64_t b200_groth16_pk_t;
+int b200_groth16_pk_create(int curve, const void *alpha_g1, const void *beta_g1, const void *beta_g2,
+                           const void *delta_g1, const void *delta_g2, b200_bases_t A_query,
+                           b200_bases_t B_query_g2, b200_bases_t B_query_g1, const uint32_t *B_indices,
+                           b200_bases_t H_query, b200_bases_t L_query, b200_r1cs_t r1cs,
+                           size_t num_constraints, size_t num_inputs, size_t num_variables,
+                           size_t domain_size, b200_groth16_pk_t *handle);
+int b200_groth16_pk_free(b200_groth16_pk_t handle);
+/* One proof. primary_input (num_inputs) and auxiliary_input (num_variables - num_inputs) are host
+ * arrays of Montgomery Fr, r and s the zero-knowledge randomness (the reference draws them at
+ * .tcc:499-500; the caller supplies them here so that proofs are reproducible). proof_out =
+ * g_A (G1) | g_B (G2) | g_C (G1), normalised, reference layouts. stage_ms (nullable, 7 doubles):
+ * witness upload, witness map, A, B, H, L, total. */
+int b200_groth16_prove(b200_groth16_pk_t handle, const void *primary_input,
+                       const void *auxiliary_input, const void *r, const void *s, void *proof_out,
+                       double *stage_ms);
+
 /* ---- measurement helpers (used by bench.py; not part of the reference surface) ------- */
 /* Integer-pipe microbenchmarks, multiply-adds per second: wide = 32x32+64 IMAD.WIDE.U32(.X) chains
  * (what a Montgomery product is made of; two issue slots each), lo = 32-bit IMAD (the pipe's

@@ -37,6 +37,7 @@ EXPORTS = [
     "b200_msm_resident_windows_dev", "b200_timer_start", "b200_timer_stop", "b200_make_bases",
     "b200_imad_carry_peak", "b200_imad_peak", "b200_last_msm_timing", "b200_launch_count",
     "b200_r1cs_upload", "b200_r1cs_free", "b200_r1cs_evaluate", "b200_witness_map_r1cs_dev", "b200_gather_dev",
+    "b200_groth16_pk_create", "b200_groth16_pk_free", "b200_groth16_prove",
 ]
 
 
@@ -97,6 +98,10 @@ def lib():
         L.b200_r1cs_evaluate.argtypes = [u64, vp, sz, vp, vp, vp]
         L.b200_witness_map_r1cs_dev.argtypes = [u64, vp, sz, vp]
         L.b200_gather_dev.argtypes = [i, vp, vp, sz, vp]
+        L.b200_groth16_pk_create.argtypes = [i, vp, vp, vp, vp, vp, u64, u64, u64, vp, u64, u64, u64, sz, sz, sz, sz,
+                                             C.POINTER(u64)]
+        L.b200_groth16_pk_free.argtypes = [u64]
+        L.b200_groth16_prove.argtypes = [u64, vp, vp, vp, vp, vp, C.POINTER(C.c_double)]
         L.b200_last_msm_timing.argtypes = [C.POINTER(C.c_double)]
         L.b200_launch_count.restype = u64
         L.b200_msm_resident_windows_dev.argtypes = [u64, sz, sz, vp, i, vp]
@@ -380,6 +385,42 @@ class R1CS:
         if self.handle:
             _check(lib().b200_r1cs_free(self.handle))
             self.handle = 0
+
+
+class Groth16ProvingKey:
+    """r1cs_gg_ppzksnark_proving_key resident on the device; prove() mirrors r1cs_gg_ppzksnark_prover
+    (r1cs_gg_ppzksnark.tcc:460-603) with caller-supplied r, s."""
+
+    def __init__(self, curve, alpha_g1, beta_g1, beta_g2, delta_g1, delta_g2, A_query, B_query_g2, B_query_g1,
+                 B_indices, H_query, L_query, r1cs, domain_size):
+        self.curve, self.r1cs = curve, r1cs
+        self.sets = [ResidentBases(curve, G1, A_query), ResidentBases(curve, G2, B_query_g2),
+                     ResidentBases(curve, G1, B_query_g1), ResidentBases(curve, G1, H_query),
+                     ResidentBases(curve, G1, L_query)]
+        pts = [_u64(x) for x in (alpha_g1, beta_g1, beta_g2, delta_g1, delta_g2)]
+        idx = None if B_indices is None else np.ascontiguousarray(B_indices, dtype=np.uint32)
+        h = C.c_uint64(0)
+        _check(lib().b200_groth16_pk_create(
+            _cid(curve), *[_p(x) for x in pts], self.sets[0].handle, self.sets[1].handle, self.sets[2].handle,
+            None if idx is None else _p(idx), self.sets[3].handle, self.sets[4].handle, r1cs.handle, r1cs.nc, r1cs.ni,
+            r1cs.nv, domain_size, C.byref(h)))
+        self.handle = h.value
+        self._proof_limbs = (2 * sizeof_group(curve, G1) + sizeof_group(curve, G2)) // 8
+
+    def prove(self, primary_input, auxiliary_input, r, s):
+        """(proof, stages): proof = g_A | g_B | g_C normalised (reference layouts), stages in ms."""
+        pi, ai, r, s = _u64(primary_input), _u64(auxiliary_input), _u64(r), _u64(s)
+        out = np.zeros(self._proof_limbs, dtype=np.uint64)
+        ms = (C.c_double * 7)()
+        _check(lib().b200_groth16_prove(self.handle, _p(pi), _p(ai), _p(r), _p(s), _p(out), ms))
+        return out, dict(zip(["upload", "witness_map", "A", "B", "H", "L", "total"], list(ms)))
+
+    def free(self):
+        if self.handle:
+            _check(lib().b200_groth16_pk_free(self.handle))
+            self.handle = 0
+            for rb in self.sets:
+                rb.free()
 
 
 class DeviceBuffer:

@@ -441,7 +441,8 @@ template<typename ppT> struct H {
     }
 
     // which: 0 A_query, 1 B_query.values, 2 B_query.indices, 3 H_query, 4 L_query,
-    //        5 primary_input, 6 auxiliary_input
+    //        5 primary_input, 6 auxiliary_input, 7 alpha_g1, 8 beta_g1, 9 beta_g2, 10 delta_g1, 11 delta_g2
+    //        (single points, any projective representative)
     static const void *ptr(const groth16_fixture<ppT> *f, int which)
     {
         const auto &pk = f->keypair.pk;
@@ -453,6 +454,11 @@ template<typename ppT> struct H {
         case 4: return pk.L_query.data();
         case 5: return f->example.primary_input.data();
         case 6: return f->example.auxiliary_input.data();
+        case 7: return &pk.alpha_g1;
+        case 8: return &pk.beta_g1;
+        case 9: return &pk.beta_g2;
+        case 10: return &pk.delta_g1;
+        case 11: return &pk.delta_g2;
         }
         return nullptr;
     }
@@ -461,7 +467,7 @@ template<typename ppT> struct H {
     {
         const long long t0 = get_nsec_time();
         const qap_witness<FrT> w = r1cs_to_qap_witness_map(
-            f->example.constraint_system,
+            f->keypair.pk.constraint_system,
             f->example.primary_input,
             f->example.auxiliary_input,
             FrT::zero(),
@@ -480,7 +486,7 @@ template<typename ppT> struct H {
     // linear_combination::evaluate. m elements each.
     static int abc_evaluations(const groth16_fixture<ppT> *f, void *oA, void *oB, void *oC)
     {
-        const auto &cs = f->example.constraint_system;
+        const auto &cs = f->keypair.pk.constraint_system;
         const size_t m = libfqfft::get_evaluation_domain<FrT>(cs.num_constraints() + cs.num_inputs() + 1)->m;
         r1cs_variable_assignment<FrT> full = f->example.primary_input;
         full.insert(full.end(), f->example.auxiliary_input.begin(), f->example.auxiliary_input.end());
@@ -637,7 +643,7 @@ template<typename ppT> struct H {
     // b200_r1cs_upload in tests. Call with null arrays to get nnz.
     static int r1cs_csr(const groth16_fixture<ppT> *f, uint32_t *row_ptr, uint32_t *col, void *val, uint64_t *nnz_out)
     {
-        const auto &cs = f->example.constraint_system;
+        const auto &cs = f->keypair.pk.constraint_system;
         const size_t nc = cs.num_constraints();
         FrT *v = static_cast<FrT *>(val);
         size_t e = 0;

@@ -275,6 +275,15 @@ class Groth16Fixture:
     def auxiliary_input(self):
         return self._view(6, self.sizes["num_variables"] - self.sizes["num_inputs"], self.i["nr"])
 
+    def pk_points(self):
+        """alpha_g1, beta_g1, beta_g2, delta_g1, delta_g2 normalised to the special (affine) form."""
+        out = []
+        for which, grp, key in [(7, G1, "g1_limbs"), (8, G1, "g1_limbs"), (9, G2, "g2_limbs"), (10, G1, "g1_limbs"),
+                                (11, G2, "g2_limbs")]:
+            v = self._view(which, 1, self.i[key]).copy()
+            out.append(self.ref.group_op(self.curve, grp, GOP_TO_AFFINE, v)[0])
+        return out
+
     def witness_map(self):
         out = np.zeros((self.sizes["m"] + 1, self.i["nr"]), dtype=np.uint64)
         ms = C.c_double(0)
