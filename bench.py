@@ -48,6 +48,8 @@ def parse_args():
     ap.add_argument("--no-ntt", action="store_true", help="skip the secondary NTT 2^24 measurement")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ntt-log-m", type=int, default=24)
+    ap.add_argument("--no-prove", action="store_true", help="skip the Groth16 prove measurement")
+    ap.add_argument("--prove-log-m", type=int, default=20)
     return ap.parse_args()
 
 
@@ -314,6 +316,8 @@ def run_b200_arm(args):
         }
         if world == 1 and not args.no_ntt:
             line["ntt"] = bench_ntt(b, torch, args.ntt_log_m, wide)
+        if world == 1 and not args.no_prove:
+            line["groth16_prove"] = bench_groth16(b, args.prove_log_m, max(3, min(args.steps, 10)), max(3, args.warmup))
         if world == 1 and not args.no_cpu_baseline:
             try:
                 rate, threads, sample, _ = reference_msm_rate(args.log_n, 2, 1, budget_s=20.0)
@@ -326,6 +330,56 @@ def run_b200_arm(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def bench_groth16(b, log_m, steps, warmup):
+    """BASELINE.json metric 'Groth16 prove ms @2^20 BN254': b200_groth16_prove (witness on the host in, proof on the host
+    out) on a synthetic satisfiable R1CS of the shape of generate_r1cs_example_with_field_input with num_inputs = 10 and
+    num_constraints = 2^log_m - 11, proving key = distinct device-generated points of the right
+    sizes, resident on the device. Parity of this entry point with the reference prover (fixed r, s) is what
+    tests/test_groth16_gpu.py::test_c_abi_prover_bit_exact checks; profiles/r1_groth16_prove.jsonl has the reference's time."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import synth_r1cs
+    ni, m = 10, 1 << log_m
+    t0 = time.time()
+    sy = synth_r1cs.make(CURVE, m - ni - 1, ni)
+    nv = sy["nv"]
+    cs = b.R1CS(CURVE, sy["nc"], ni, nv, sy["row_ptr"], sy["col"], sy["val"])
+    k = 1
+    qs = []
+    for grp, n in [(b.G1, nv + 1), (b.G2, nv + 1), (b.G1, nv + 1), (b.G1, m - 1), (b.G1, nv - ni)]:
+        qs.append(b.make_bases(CURVE, grp, n, k0=k))
+        k += n
+    p1 = b.make_bases(CURVE, b.G1, 3, k0=k)
+    p2 = b.make_bases(CURVE, b.G2, 2, k0=k + 3)
+    pk = b.Groth16ProvingKey(CURVE, p1[0], p1[1], p2[0], p1[2], p2[1], qs[0], qs[1], qs[2], None, qs[3], qs[4], cs, m)
+    setup_s = time.time() - t0
+    rs = b.random_scalars(CURVE, 2, seed=99)
+    proof = None
+    for _ in range(warmup):
+        proof, _ = pk.prove(sy["primary"], sy["auxiliary"], rs[0], rs[1])
+    times, stages = [], []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        p, st = pk.prove(sy["primary"], sy["auxiliary"], rs[0], rs[1])
+        times.append((time.perf_counter() - t0) * 1e3)
+        stages.append(st)
+        assert np.array_equal(p, proof), "prover is not deterministic for fixed r, s"
+    ms = float(np.mean(times))
+    keys = stages[0].keys()
+    out = {"metric": f"Groth16 prove ms @2^{log_m} BN254", "value": ms, "unit": "ms", "higher_is_better": False,
+           "steps": steps, "warmup": warmup, "min_ms": float(np.min(times)),
+           "stage_ms": {kk: float(np.mean([s_[kk] for s_ in stages])) for kk in keys},
+           "sizes": {"num_constraints": sy["nc"], "num_inputs": ni, "num_variables": nv, "domain": m,
+                     "r1cs_nnz": int(sy["col"].shape[0])},
+           "h2d_bytes_per_step": int((nv + 1) * 32), "d2h_bytes_per_step": int(5 * 17 * 128 + 17 * 256),
+           "setup_s": setup_s,
+           "note": "wall clock around b200_groth16_prove: witness (host) -> H2D -> sparse R1CS evaluation -> 7 NTTs -> "
+                   "A, B(G2+G1), H, L MSMs on device-resident scalars -> window sums D2H -> host fold and proof assembly; "
+                   "proving key and constraint system resident on the device (uploaded once, outside the timed region)"}
+    pk.free()
+    cs.free()
+    return out
 
 
 def bench_ntt(b, torch, log_m, wide_peak):

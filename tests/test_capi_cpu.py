@@ -147,3 +147,19 @@ def test_product_does_not_touch_the_oracle():
                     assert needle not in text, f"{f} refers to {needle}"
     needed = subprocess.run(["readelf", "-d", os.path.join(pkg, "libsnark_b200.so")], capture_output=True, text=True).stdout
     assert "libref" not in needed and "oracle" not in needed
+
+
+def test_synthetic_r1cs_is_satisfied():
+    """tools/synth_r1cs.py (the bench's stand-in for generate_r1cs_example_with_field_input): <a,w> * <b,w> = <c,w>."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import synth_r1cs
+    for curve in ("alt_bn128", "bw6_761"):
+        s = synth_r1cs.make(curve, 50, 4)
+        p, Rinv = s["modulus"], pow(s["R"], -1, s["modulus"])
+        w = np.concatenate([s["one"][None, :], s["primary"], s["auxiliary"]])
+        ints = [sum(int(x) << (64 * i) for i, x in enumerate(row)) * Rinv % p for row in w]
+        assert ints[0] == 1 and len(ints) == s["nv"] + 1
+        nc, rp, col = s["nc"], s["row_ptr"], s["col"]
+        ev = [sum(ints[c] for c in col[rp[r]:rp[r + 1]]) % p for r in range(3 * nc)]
+        for i in range(nc):
+            assert ev[i] * ev[nc + i] % p == ev[2 * nc + i], (curve, i)
