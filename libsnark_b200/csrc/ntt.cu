@@ -1,6 +1,7 @@
 // ntt.cu — host driver and C-ABI of the NTT operators (ntt.cuh): cached per-size domains
 // (twiddle and coset tables in HBM), pass planning, the evaluation_domain entry points and
 // the fused witness-map chain of r1cs_to_qap_witness_map (r1cs_to_qap.tcc:252-330).
+#include <algorithm>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -341,8 +342,10 @@ template<class Fr> int witness_map_host(const void *aA, const void *aB, const vo
 // ---- R1CS on the device -------------------------------------------------------------------------
 struct R1csSet {
     int curve = -1;
-    size_t nc = 0, ni = 0, nv = 0, nnz = 0, num_long = 0;
-    uint32_t *row_ptr = nullptr, *col = nullptr, *long_rows = nullptr;
+    size_t nc = 0, ni = 0, nv = 0, nnz = 0, num_long = 0, num_segs = 0;
+    uint32_t *row_ptr = nullptr, *col = nullptr, *long_rows = nullptr, *seg_ptr = nullptr;
+    ntt::LongSeg *segs = nullptr;
+    void *partials = nullptr;
     void *val = nullptr;
 };
 std::map<uint64_t, R1csSet> g_r1cs;
@@ -352,6 +355,9 @@ void free_r1cs(R1csSet &r)
 {
     cudaFree(r.row_ptr);
     cudaFree(r.long_rows);
+    cudaFree(r.seg_ptr);
+    cudaFree(r.segs);
+    cudaFree(r.partials);
     cudaFree(r.col);
     cudaFree(r.val);
     r = R1csSet();
@@ -366,16 +372,30 @@ int r1cs_upload(R1csSet &r, const uint32_t *row_ptr, const uint32_t *col, const 
     B200_CUDA_CHECK(cudaMalloc((void **)&r.col, (r.nnz ? r.nnz : 1) * 4));
     B200_CUDA_CHECK(cudaMalloc(&r.val, (r.nnz ? r.nnz : 1) * sizeof(Fr)));
     B200_CUDA_CHECK(cudaMemcpyAsync(r.row_ptr, row_ptr, rows * 4, cudaMemcpyHostToDevice, s));
-    std::vector<uint32_t> long_rows;
+    std::vector<uint32_t> long_rows, seg_ptr;
+    std::vector<ntt::LongSeg> segs;
     for (size_t i = 0; i + 1 < rows; ++i) {
         if (row_ptr[i + 1] - row_ptr[i] > ntt::R1CS_LONG_ROW) {
+            seg_ptr.push_back((uint32_t)segs.size());
+            for (uint32_t e = row_ptr[i]; e < row_ptr[i + 1]; e += ntt::R1CS_LONG_SEG) {
+                const uint32_t e1 = std::min<uint32_t>(e + ntt::R1CS_LONG_SEG, row_ptr[i + 1]);
+                segs.push_back(ntt::LongSeg{(uint32_t)i, e, e1, (uint32_t)long_rows.size()});
+            }
             long_rows.push_back((uint32_t)i);
         }
     }
+    seg_ptr.push_back((uint32_t)segs.size());
     r.num_long = long_rows.size();
+    r.num_segs = segs.size();
     if (r.num_long) {
         B200_CUDA_CHECK(cudaMalloc((void **)&r.long_rows, r.num_long * 4));
+        B200_CUDA_CHECK(cudaMalloc((void **)&r.seg_ptr, seg_ptr.size() * 4));
+        B200_CUDA_CHECK(cudaMalloc((void **)&r.segs, segs.size() * sizeof(ntt::LongSeg)));
+        B200_CUDA_CHECK(cudaMalloc(&r.partials, segs.size() * sizeof(Fr)));
         B200_CUDA_CHECK(cudaMemcpyAsync(r.long_rows, long_rows.data(), r.num_long * 4, cudaMemcpyHostToDevice, s));
+        B200_CUDA_CHECK(cudaMemcpyAsync(r.seg_ptr, seg_ptr.data(), seg_ptr.size() * 4, cudaMemcpyHostToDevice, s));
+        B200_CUDA_CHECK(cudaMemcpyAsync(r.segs, segs.data(), segs.size() * sizeof(ntt::LongSeg), cudaMemcpyHostToDevice, s));
+        B200_CUDA_CHECK(cudaStreamSynchronize(s)); // the host vectors go out of scope
     }
     if (r.nnz) {
         B200_CUDA_CHECK(cudaMemcpyAsync(r.col, col, r.nnz * 4, cudaMemcpyHostToDevice, s));
@@ -392,8 +412,11 @@ template<class Fr> int r1cs_eval_launch(const R1csSet &r, const Fr *d_w, size_t 
         r.nc, r.ni, m, r.row_ptr, r.col, static_cast<const Fr *>(r.val), d_w, aA, aB, aC);
     B200_LAUNCH_CHECK();
     if (r.num_long) {
-        ntt::k_r1cs_eval_long<Fr><<<(unsigned)r.num_long, ntt::R1CS_LONG_THREADS, 0, s>>>(
-            r.nc, r.long_rows, r.row_ptr, r.col, static_cast<const Fr *>(r.val), d_w, aA, aB, aC);
+        ntt::k_r1cs_eval_long<Fr><<<(unsigned)r.num_segs, ntt::R1CS_LONG_THREADS, 0, s>>>(
+            r.segs, r.col, static_cast<const Fr *>(r.val), d_w, static_cast<Fr *>(r.partials));
+        B200_LAUNCH_CHECK();
+        ntt::k_r1cs_long_finish<Fr><<<(unsigned)r.num_long, ntt::R1CS_LONG_THREADS, 0, s>>>(
+            r.nc, r.long_rows, r.seg_ptr, static_cast<const Fr *>(r.partials), aA, aB, aC);
         B200_LAUNCH_CHECK();
     }
     return B200_OK;

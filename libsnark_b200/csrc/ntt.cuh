@@ -346,6 +346,7 @@ template<class Fr> __global__ void k_scale(uint64_t m, Fr *a, const Fr *c)
 
 constexpr uint32_t R1CS_LONG_ROW = 64;
 constexpr int R1CS_LONG_THREADS = 256;
+constexpr uint32_t R1CS_LONG_SEG = 2048; // terms per CTA of the long-row kernel
 
 // Sparse R1CS evaluation (r1cs_to_qap.tcc:236-248, :293-296; linear_combination::evaluate,
 // variable.tcc:288-299): rows [0, nc) of A, [nc, 2nc) of B, [2nc, 3nc) of C in one CSR.
@@ -378,20 +379,14 @@ __global__ void k_r1cs_eval(uint64_t nc, uint64_t ni, uint64_t m, const uint32_t
     gstore(dst + i, acc);
 }
 
-// Rows with more than R1CS_LONG_ROW terms (a sum over all variables is a common last constraint):
-// one CTA per row, strided partial sums, shared-memory tree.
-template<class Fr>
-__global__ void __launch_bounds__(R1CS_LONG_THREADS)
-    k_r1cs_eval_long(uint64_t nc, const uint32_t *long_rows, const uint32_t *row_ptr, const uint32_t *col, const Fr *val,
-                     const Fr *w, Fr *aA, Fr *aB, Fr *aC)
+// Rows with more than R1CS_LONG_ROW terms (a sum over all variables is a common last constraint) are
+// cut into segments of R1CS_LONG_SEG terms: one CTA per segment (strided partial sums, shared-memory
+// tree) writes a partial; a second launch adds the partials of each row (one CTA per row).
+struct LongSeg {
+    uint32_t row, e0, e1, slot; // slot: index of the row in the long-row list
+};
+template<class Fr> __device__ Fr cta_tree_sum(Fr acc, Fr *part)
 {
-    __shared__ Fr part[R1CS_LONG_THREADS];
-    const uint64_t row = long_rows[blockIdx.x];
-    const uint32_t e0 = row_ptr[row], e1 = row_ptr[row + 1];
-    Fr acc = Fr::zero();
-    for (uint32_t e = e0 + threadIdx.x; e < e1; e += R1CS_LONG_THREADS) {
-        acc = acc + gload(val + e) * gload(w + col[e]);
-    }
     part[threadIdx.x] = acc;
     __syncthreads();
     for (int half = R1CS_LONG_THREADS / 2; half > 0; half >>= 1) {
@@ -400,10 +395,41 @@ __global__ void __launch_bounds__(R1CS_LONG_THREADS)
         }
         __syncthreads();
     }
+    return part[0];
+}
+template<class Fr>
+__global__ void __launch_bounds__(R1CS_LONG_THREADS)
+    k_r1cs_eval_long(const LongSeg *segs, const uint32_t *col, const Fr *val, const Fr *w, Fr *partials)
+{
+    __shared__ Fr part[R1CS_LONG_THREADS];
+    const LongSeg sg = segs[blockIdx.x];
+    Fr acc = Fr::zero();
+    for (uint32_t e = sg.e0 + threadIdx.x; e < sg.e1; e += R1CS_LONG_THREADS) {
+        acc = acc + gload(val + e) * gload(w + col[e]);
+    }
+    const Fr total = cta_tree_sum(acc, part);
     if (threadIdx.x == 0) {
+        gstore(partials + blockIdx.x, total);
+    }
+}
+// seg_ptr[k] .. seg_ptr[k+1]: the segments of long row k (consecutive in `partials`)
+template<class Fr>
+__global__ void __launch_bounds__(R1CS_LONG_THREADS)
+    k_r1cs_long_finish(uint64_t nc, const uint32_t *long_rows, const uint32_t *seg_ptr, const Fr *partials, Fr *aA, Fr *aB,
+                       Fr *aC)
+{
+    __shared__ Fr part[R1CS_LONG_THREADS];
+    const uint32_t s0 = seg_ptr[blockIdx.x], s1 = seg_ptr[blockIdx.x + 1];
+    Fr acc = Fr::zero();
+    for (uint32_t k = s0 + threadIdx.x; k < s1; k += R1CS_LONG_THREADS) {
+        acc = acc + gload(partials + k);
+    }
+    const Fr total = cta_tree_sum(acc, part);
+    if (threadIdx.x == 0) {
+        const uint64_t row = long_rows[blockIdx.x];
         const uint64_t mat = row / nc, i = row - mat * nc;
         Fr *dst = mat == 0 ? aA : (mat == 1 ? aB : aC);
-        gstore(dst + i, part[0]);
+        gstore(dst + i, total);
     }
 }
 
