@@ -185,7 +185,7 @@ struct Task {
 
 HD void build_tasks_body(
     size_t b, const uint32_t *counts, const uint32_t *offsets, const uint32_t *task_off, Task *tasks,
-    uint32_t *multi_count, uint32_t *multi_list)
+    uint32_t *multi_count, uint32_t *multi_list, uint32_t collapse)
 {
     const uint32_t cnt = counts[b];
     const uint32_t first = task_off[b];
@@ -196,7 +196,7 @@ HD void build_tasks_body(
         tk.len = (cnt - done) < (uint32_t)SEG ? (cnt - done) : (uint32_t)SEG;
         tasks[first + s] = tk;
     }
-    if (cnt > (uint32_t)(COLLAPSE_TASKS * SEG)) { // many tasks: their partial sums are merged by k_collapse
+    if (cnt > collapse * (uint32_t)SEG) { // many tasks: their partial sums are merged by k_collapse
 #if defined(__CUDA_ARCH__)
         multi_list[atomicAdd(multi_count, 1u)] = (uint32_t)b;
 #else
@@ -240,9 +240,9 @@ HD void reduce_chunk_body(
     for (int k = CHUNK - 1; k >= 0; --k) {
         const uint32_t t0 = task_off[b0 + k];
         const uint32_t t1 = task_off[b0 + k + 1];
-        // up to COLLAPSE_TASKS partial sums are added here; beyond that k_collapse has already
+        // up to g.collapse partial sums are added here; beyond that k_collapse has already
         // left the bucket's total in its first task slot
-        const uint32_t tend = (t1 - t0 > (uint32_t)COLLAPSE_TASKS) ? t0 + 1 : t1;
+        const uint32_t tend = (t1 - t0 > g.collapse) ? t0 + 1 : t1;
         for (uint32_t t = t0; t < tend; ++t) {
             const XYZZ<F> s = load_vec(partial + t);
             add_cold(run, s);
@@ -454,11 +454,11 @@ static __global__ void k_scan_finish(
 
 static __global__ void k_build_tasks(
     const uint32_t *counts, const uint32_t *offsets, const uint32_t *task_off, uint32_t nb, Task *tasks,
-    uint32_t *multi_count, uint32_t *multi_list)
+    uint32_t *multi_count, uint32_t *multi_list, uint32_t collapse)
 {
     const size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (b < nb) {
-        build_tasks_body(b, counts, offsets, task_off, tasks, multi_count, multi_list);
+        build_tasks_body(b, counts, offsets, task_off, tasks, multi_count, multi_list, collapse);
     }
 }
 

@@ -9,7 +9,7 @@ namespace msm
 {
 
 constexpr int SEG = 64;   // max entries per accumulation task
-constexpr int COLLAPSE_TASKS = 4; // buckets with more tasks than this are pre-merged by k_collapse
+constexpr int COLLAPSE_TASKS = 4; // floor of Geometry::collapse (see there)
 constexpr int CHUNK = 8;  // buckets per reduce thread
 constexpr int REDUCE_BLOCK = 128; // reduce threads per CTA (all in one window)
 
@@ -22,6 +22,11 @@ struct Geometry {
     uint32_t cpw; // chunks per window = B / CHUNK
     uint32_t rb;  // reduce CTA size = min(REDUCE_BLOCK, cpw)
     uint32_t opw; // reduce CTAs (= partial window sums) per window = cpw / rb
+    // Buckets with more tasks than this are pre-merged by k_collapse (warp per bucket); up to this
+    // many partial sums are added inline by the reduce thread. Scales with the AVERAGE tasks per bucket
+    // so that the collapse kernel only ever sees outliers (at 2^24 with c = 17 the average bucket has
+    // 4 tasks; a fixed threshold of 4 sent half a million buckets through it: 24 ms).
+    uint32_t collapse;
 };
 
 // Window width: minimise  W(c) * (10 n + 100 * 2^(c-1))  field mults (10 per mixed add,
@@ -47,6 +52,8 @@ inline Geometry make_geometry(uint64_t n, int scalar_bits, int force_c = 0)
     g.cpw = g.B / CHUNK;
     g.rb = g.cpw < (uint32_t)REDUCE_BLOCK ? g.cpw : (uint32_t)REDUCE_BLOCK;
     g.opw = g.cpw / g.rb;
+    const uint64_t avg_tasks = (n / g.B + SEG - 1) / SEG;
+    g.collapse = (uint32_t)(2 * avg_tasks + 2 > (uint64_t)COLLAPSE_TASKS ? 2 * avg_tasks + 2 : (uint64_t)COLLAPSE_TASKS);
     return g;
 }
 

@@ -127,7 +127,7 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
     B200_LAUNCH_CHECK();
     k_scatter<<<grid_for(n, 256), 256, 0, s>>>(t, NL, g, cursor, entries);
     B200_LAUNCH_CHECK();
-    k_build_tasks<<<grid_for(g.NB, 256), 256, 0, s>>>(counts, offsets, task_off, g.NB, tasks, multi_count, multi_list);
+    k_build_tasks<<<grid_for(g.NB, 256), 256, 0, s>>>(counts, offsets, task_off, g.NB, tasks, multi_count, multi_list, g.collapse);
     B200_LAUNCH_CHECK();
     B200_CUDA_CHECK(cudaEventRecord(tm.ev[1], s));
     // 5: bucket accumulation (grid sized for the task upper bound; surplus CTAs exit at once)

@@ -203,7 +203,7 @@ template<class Fr, class F> static int msm_emulated(const void *bases_ref, size_
     }
     std::vector<Task> tasks(toff + 1);
     for (size_t b = 0; b < g.NB; ++b) {
-        build_tasks_body(b, counts.data(), offsets.data(), task_off.data(), tasks.data(), &multi_count, multi_list.data());
+        build_tasks_body(b, counts.data(), offsets.data(), task_off.data(), tasks.data(), &multi_count, multi_list.data(), g.collapse);
     }
     std::vector<XYZZ<F>> partial(toff + 1);
     for (uint32_t k = 0; k < toff; ++k) {
