@@ -297,7 +297,8 @@ def imad_peak(iters=4096):
 # ---- NTT -------------------------------------------------------------------------------------
 
 class evaluation_domain:
-    """libfqfft::basic_radix2_domain<Fr> (what get_evaluation_domain returns for m = 2^k)."""
+    """libfqfft::basic_radix2_domain<Fr> (m = 2^k) or step_radix2_domain<Fr> (m = 2^k + 2^r), the two domain kinds
+    get_evaluation_domain hands out for these fields; the library picks the kind from m."""
 
     def __init__(self, curve, m):
         self.curve, self.m = _cid(curve), int(m)
@@ -328,9 +329,23 @@ class evaluation_domain:
         return a
 
 
+def domain_size_for(min_size):
+    """The size get_evaluation_domain settles on (get_evaluation_domain.tcc:37-58): min_size when it is 2^k or
+    2^k + 2^r, else big + the small part rounded up to a power of two."""
+    min_size = int(min_size)
+    if min_size < 2 or min_size & (min_size - 1) == 0:
+        return min_size
+    big = 1 << (min_size.bit_length() - 1)
+    small = min_size - big
+    rounded = 1 << (small - 1).bit_length() if small > 1 else 1
+    return big + rounded
+
+
 def get_evaluation_domain(curve, min_size):
-    """libfqfft::get_evaluation_domain (get_evaluation_domain.tcc:32-70), power-of-two sizes only."""
-    return evaluation_domain(curve, min_size)
+    """libfqfft::get_evaluation_domain (get_evaluation_domain.tcc:32-70): basic_radix2_domain for powers of two,
+    step_radix2_domain otherwise (the extended/geometric/arithmetic domains are not needed for these fields'
+    2-adicities at any practical size)."""
+    return evaluation_domain(curve, domain_size_for(min_size))
 
 
 def r1cs_to_qap_witness_map_h(curve, aA, aB, aC):

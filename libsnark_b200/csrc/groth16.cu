@@ -136,7 +136,7 @@ int b200_groth16_pk_create(int curve, const void *alpha_g1, const void *beta_g1,
     const size_t nB = b200_bases_size(B_query_g2);
     if (b200_bases_size(A_query) != nv + 1 || b200_bases_size(B_query_g1) != nB || nB > nv + 1 ||
         b200_bases_size(H_query) + 1 < m || b200_bases_size(L_query) != nv - ni || ni > nv ||
-        m < num_constraints + ni + 1 || (m & (m - 1)) != 0) {
+        m < num_constraints + ni + 1) {
         return rt::set_error(B200_ERR_ARG,
                              "query sizes do not match the constraint system (r1cs_gg_ppzksnark.tcc:506-511)");
     }

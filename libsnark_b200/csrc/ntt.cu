@@ -181,9 +181,21 @@ int log2_exact(size_t m)
 rt::DevBuf g_bufA, g_bufB, g_bufC, g_bufS, g_bufH;
 std::mutex g_mu;
 
+struct StepShape;
+template<class Fr> bool step_shape(size_t m, StepShape *sh);
+template<class Fr> int step_op_dev(int op, Fr *a, Fr *tmp, const StepShape &sh, const void *g);
+template<class Fr> int step_try_op(int op, Fr *data, Fr *tmp, Fr *out, size_t m, const void *g, bool *handled);
+
 template<class Fr> int ntt_op_dev(int op, Fr *data, Fr *tmp, Fr *out, size_t m, const void *g)
 {
     const int lgn = log2_exact(m);
+    if (lgn < 0) {
+        bool handled = false;
+        const int rc = step_try_op<Fr>(op, data, tmp, out, m, g, &handled);
+        if (handled) {
+            return rc;
+        }
+    }
     if (lgn < 0 || lgn > Fr::params::S) {
         // get_evaluation_domain / basic_radix2_domain ctor (basic_radix2_domain.tcc:25-52)
         return rt::set_error(B200_ERR_DOMAIN, "basic_radix2_domain: size %zu is not a power of two in [2, 2^%d]", m,
@@ -246,9 +258,19 @@ template<class Fr> int ntt_dev(int op, void *dev_data, size_t m, const void *g)
     return B200_OK;
 }
 
+template<class Fr> int step_divide_by_z_host(void *data, size_t m, bool *handled);
+template<class Fr> int step_witness_map_try(Fr *dA, Fr *dB, Fr *dC, size_t m, Fr *dH, bool *handled);
+
 template<class Fr> int divide_by_z(void *data, size_t m)
 {
     const int lgn = log2_exact(m);
+    if (lgn < 0) {
+        bool handled = false;
+        const int rc = step_divide_by_z_host<Fr>(data, m, &handled);
+        if (handled) {
+            return rc;
+        }
+    }
     if (lgn < 0 || lgn > Fr::params::S) {
         return rt::set_error(B200_ERR_DOMAIN, "basic_radix2_domain: bad size %zu", m);
     }
@@ -278,6 +300,13 @@ template<class Fr> int divide_by_z(void *data, size_t m)
 template<class Fr> int witness_map_dev(Fr *dA, Fr *dB, Fr *dC, size_t m, Fr *dH)
 {
     const int lgn = log2_exact(m);
+    if (lgn < 0) {
+        bool handled = false;
+        const int rc = step_witness_map_try<Fr>(dA, dB, dC, m, dH, &handled);
+        if (handled) {
+            return rc;
+        }
+    }
     if (lgn < 0 || lgn > Fr::params::S) {
         return rt::set_error(B200_ERR_DOMAIN, "basic_radix2_domain: bad size %zu", m);
     }
@@ -337,6 +366,337 @@ template<class Fr> int witness_map_host(const void *aA, const void *aB, const vo
     B200_CUDA_CHECK(cudaMemcpyAsync(out_H, g_bufH.p, bytes + sizeof(Fr), cudaMemcpyDeviceToHost, s));
     B200_CUDA_CHECK(cudaStreamSynchronize(s));
     return B200_OK;
+}
+
+// ---- step_radix2_domain ---------------------------------------------------------------------------
+// m = big + small (big = 2^k > small = 2^r): what get_evaluation_domain returns for every size that is
+// not a power of two (get_evaluation_domain.tcc:41-58; step_radix2_domain.tcc:20-62).
+struct StepShape {
+    size_t m = 0, big = 0, small = 0, compr = 0;
+    int lg_big = 0, lg_small = 0;
+};
+template<class Fr> bool step_shape(size_t m, StepShape *sh)
+{
+    if (m < 3 || (m & (m - 1)) == 0) {
+        return false;
+    }
+    int lg = 0;
+    while ((1ull << (lg + 1)) <= m) {
+        ++lg;
+    }
+    const size_t big = 1ull << lg, small = m - big;
+    if (small & (small - 1)) {
+        return false;
+    }
+    if (lg + 1 > Fr::params::S) {
+        return false;
+    }
+    sh->m = m;
+    sh->big = big;
+    sh->small = small;
+    sh->compr = big / small;
+    sh->lg_big = lg;
+    sh->lg_small = 0;
+    while ((1ull << sh->lg_small) < small) {
+        ++sh->lg_small;
+    }
+    return true;
+}
+
+template<class Fr> Fr host_pow(Fr base, uint64_t e)
+{
+    Fr acc = Fr::one();
+    for (; e; e >>= 1) {
+        if (e & 1) {
+            acc = acc * base;
+        }
+        base = base.sqr();
+    }
+    return acc;
+}
+
+template<class Fr> struct StepDomain {
+    StepShape sh;
+    Domain<Fr> *d2 = nullptr, *dbig = nullptr, *dsmall = nullptr; // sizes 2 big, big, small (null when small == 1)
+    rt::DevBuf consts; // [0] 1/2  [1] A  [2] B  [3] w2s  [4] Z1^-1  [5] 1/small (when small == 1: one)
+    rt::DevBuf zinv, gpow, ginv;
+    bool has_zinv = false;
+    uint32_t g_host[Fr::N];
+    bool has_g = false;
+    const Fr *c(int i) { return consts.template as<Fr>() + i; }
+};
+template<class Fr> std::map<size_t, std::unique_ptr<StepDomain<Fr>>> &step_domains()
+{
+    static std::map<size_t, std::unique_ptr<StepDomain<Fr>>> m;
+    return m;
+}
+
+template<class Fr> int get_step_domain(const StepShape &sh, StepDomain<Fr> **out)
+{
+    auto &mp = step_domains<Fr>();
+    auto it = mp.find(sh.m);
+    if (it == mp.end()) {
+        std::unique_ptr<StepDomain<Fr>> d(new StepDomain<Fr>());
+        d->sh = sh;
+        int rc;
+        if ((rc = get_domain<Fr>(sh.lg_big + 1, nullptr, &d->d2)) || (rc = get_domain<Fr>(sh.lg_big, nullptr, &d->dbig))) {
+            return rc;
+        }
+        if (sh.lg_small >= 1 && (rc = get_domain<Fr>(sh.lg_small, nullptr, &d->dsmall))) {
+            return rc;
+        }
+        // constants on the host (a handful of exponentiations; step_radix2_domain.tcc:252-276)
+        Fr w, g;
+        for (int i = 0; i < Fr::N; ++i) {
+            w.v[i] = Fr::params::root_of_unity(i);
+            g.v[i] = Fr::params::generator(i); // FieldT::multiplicative_generator
+        }
+        for (int i = Fr::params::S; i > sh.lg_big + 1; --i) {
+            w = w.sqr(); // omega = get_root_of_unity(2 big)
+        }
+        const Fr one = Fr::one();
+        const Fr z0 = host_pow(g, sh.big) - one;
+        const Fr w_small = host_pow(w, sh.small);
+        const Fr gw = g * w;
+        const Fr z1 = (host_pow(gw, sh.big) - one) * (host_pow(gw, sh.small) - w_small);
+        Fr hc[6];
+        hc[0] = (one + one).inverse();
+        hc[1] = host_pow(g, sh.small) * z0;
+        hc[2] = w_small * z0;
+        hc[3] = host_pow(w, 2 * sh.small);
+        hc[4] = z1.inverse();
+        hc[5] = one;
+        if (d->consts.reserve(sizeof(hc))) {
+            return B200_ERR_CUDA;
+        }
+        B200_CUDA_CHECK(cudaMemcpyAsync(d->consts.p, hc, sizeof(hc), cudaMemcpyHostToDevice, rt::stream()));
+        B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
+        it = mp.emplace(sh.m, std::move(d)).first;
+    }
+    *out = it->second.get();
+    return B200_OK;
+}
+
+// g^i and g^-i, i < m, for the coset transforms (tables rebuilt when the generator changes)
+template<class Fr> int step_coset_tables(StepDomain<Fr> &d, const uint32_t *g)
+{
+    if (d.has_g && memcmp(g, d.g_host, sizeof(d.g_host)) == 0) {
+        return B200_OK;
+    }
+    // the size-2big radix-2 domain holds g^(2^b) and g^-(2^b) for b <= lg_big: enough for indices < 2 big
+    Domain<Fr> *d2 = nullptr;
+    int rc = get_domain<Fr>(d.sh.lg_big + 1, g, &d2);
+    if (rc) {
+        return rc;
+    }
+    if (d.gpow.reserve(d.sh.m * sizeof(Fr)) || d.ginv.reserve(d.sh.m * sizeof(Fr))) {
+        return B200_ERR_CUDA;
+    }
+    cudaStream_t s = rt::stream();
+    ntt::k_pow_table<Fr><<<grid_for(d.sh.m, 256), 256, 0, s>>>(d.sh.m, d2->pows_g(), d.sh.lg_big + 1, nullptr, d.gpow.template as<Fr>());
+    B200_LAUNCH_CHECK();
+    ntt::k_pow_table<Fr><<<grid_for(d.sh.m, 256), 256, 0, s>>>(d.sh.m, d2->pows_gi(), d.sh.lg_big + 1, nullptr, d.ginv.template as<Fr>());
+    B200_LAUNCH_CHECK();
+    memcpy(d.g_host, g, sizeof(d.g_host));
+    d.has_g = true;
+    return B200_OK;
+}
+
+rt::DevBuf g_stepD;
+
+// sum over the compr rows of v (compr x small, row-major) into row 0
+template<class Fr> int fold_rows(Fr *v, const StepShape &sh)
+{
+    for (size_t rows = sh.compr; rows > 1; rows >>= 1) {
+        const uint64_t half = (rows >> 1) * sh.small;
+        ntt::k_fold_halve<Fr><<<grid_for(half, 256), 256, 0, rt::stream()>>>(half, v);
+        B200_LAUNCH_CHECK();
+    }
+    return B200_OK;
+}
+
+// step_radix2_domain::FFT (:65-113) in place on a (m elements, device); tmp: >= big elements
+template<class Fr> int step_fft(StepDomain<Fr> &d, Fr *a, Fr *tmp)
+{
+    const StepShape &sh = d.sh;
+    if (g_stepD.reserve(sh.big * sizeof(Fr))) {
+        return B200_ERR_CUDA;
+    }
+    Fr *dd = g_stepD.as<Fr>();
+    cudaStream_t s = rt::stream();
+    ntt::k_step_fft_pre<Fr><<<grid_for(sh.big, 256), 256, 0, s>>>(sh.big, sh.small, d.d2->twiddles.template as<Fr>(), a, dd);
+    B200_LAUNCH_CHECK();
+    int rc;
+    if ((rc = fold_rows<Fr>(dd, sh)) || (rc = run_transform<Fr>(*d.dbig, 0, a, tmp, a, nullptr, nullptr, nullptr))) {
+        return rc;
+    }
+    if (d.dsmall) {
+        return run_transform<Fr>(*d.dsmall, 0, dd, tmp, a + sh.big, nullptr, nullptr, nullptr);
+    }
+    B200_CUDA_CHECK(cudaMemcpyAsync(a + sh.big, dd, sizeof(Fr), cudaMemcpyDeviceToDevice, s));
+    return B200_OK;
+}
+
+// step_radix2_domain::iFFT (:115-174) in place
+template<class Fr> int step_ifft(StepDomain<Fr> &d, Fr *a, Fr *tmp)
+{
+    const StepShape &sh = d.sh;
+    if (g_stepD.reserve(sh.big * sizeof(Fr))) {
+        return B200_ERR_CUDA;
+    }
+    Fr *dd = g_stepD.as<Fr>();
+    cudaStream_t s = rt::stream();
+    int rc;
+    if ((rc = run_transform<Fr>(*d.dbig, 1, a, tmp, a, nullptr, nullptr, d.dbig->c(1)))) {
+        return rc;
+    }
+    if (d.dsmall && (rc = run_transform<Fr>(*d.dsmall, 1, a + sh.big, tmp, a + sh.big, nullptr, nullptr, d.dsmall->c(1)))) {
+        return rc;
+    }
+    const Fr *T2 = d.d2->twiddles.template as<Fr>();
+    ntt::k_step_ifft_tmp<Fr><<<grid_for(sh.big, 256), 256, 0, s>>>(sh.big, sh.small, T2, a, dd);
+    B200_LAUNCH_CHECK();
+    if ((rc = fold_rows<Fr>(dd, sh))) {
+        return rc;
+    }
+    ntt::k_step_ifft_post<Fr><<<grid_for(sh.small, 256), 256, 0, s>>>(sh.big, sh.small, T2, dd, d.c(0), a);
+    B200_LAUNCH_CHECK();
+    return B200_OK;
+}
+
+template<class Fr> int step_op_dev(int op, Fr *a, Fr *tmp, const StepShape &sh, const void *g)
+{
+    StepDomain<Fr> *d = nullptr;
+    int rc = get_step_domain<Fr>(sh, &d);
+    if (rc) {
+        return rc;
+    }
+    const bool coset = (op == B200_COSET_FFT || op == B200_ICOSET_FFT);
+    if (coset) {
+        if (!g) {
+            return rt::set_error(B200_ERR_ARG, "coset transform needs a generator");
+        }
+        if ((rc = step_coset_tables<Fr>(*d, static_cast<const uint32_t *>(g)))) {
+            return rc;
+        }
+    }
+    cudaStream_t s = rt::stream();
+    switch (op) {
+    case B200_FFT: return step_fft<Fr>(*d, a, tmp);
+    case B200_IFFT: return step_ifft<Fr>(*d, a, tmp);
+    case B200_COSET_FFT: // _multiply_by_coset then FFT (:176-181)
+        ntt::k_mul_table<Fr><<<grid_for(sh.m, 256), 256, 0, s>>>(sh.m, a, d->gpow.template as<Fr>());
+        B200_LAUNCH_CHECK();
+        return step_fft<Fr>(*d, a, tmp);
+    case B200_ICOSET_FFT: // iFFT then _multiply_by_coset(g^-1) (:183-188)
+        if ((rc = step_ifft<Fr>(*d, a, tmp))) {
+            return rc;
+        }
+        ntt::k_mul_table<Fr><<<grid_for(sh.m, 256), 256, 0, s>>>(sh.m, a, d->ginv.template as<Fr>());
+        B200_LAUNCH_CHECK();
+        return B200_OK;
+    }
+    return rt::set_error(B200_ERR_ARG, "unknown NTT op %d", op);
+}
+
+template<class Fr> int step_try_op(int op, Fr *data, Fr *tmp, Fr *out, size_t m, const void *g, bool *handled)
+{
+    StepShape sh;
+    *handled = step_shape<Fr>(m, &sh);
+    if (!*handled) {
+        return B200_OK;
+    }
+    if (out != data) {
+        return rt::set_error(B200_ERR_ARG, "step domain transforms run in place");
+    }
+    return step_op_dev<Fr>(op, data, tmp, sh, g);
+}
+
+// step_radix2_domain::divide_by_Z_on_coset (:252-276), coset = Fr::multiplicative_generator
+template<class Fr> int step_divide_by_z_dev(StepDomain<Fr> &d, Fr *p)
+{
+    const StepShape &sh = d.sh;
+    cudaStream_t s = rt::stream();
+    if (!d.has_zinv) {
+        if (d.zinv.reserve(sh.compr * sizeof(Fr))) {
+            return B200_ERR_CUDA;
+        }
+        ntt::k_step_zinv<Fr><<<grid_for(sh.compr, 128), 128, 0, s>>>(sh.compr, d.c(1), d.zinv.template as<Fr>());
+        B200_LAUNCH_CHECK();
+        d.has_zinv = true;
+    }
+    ntt::k_step_divz<Fr><<<grid_for(sh.m, 256), 256, 0, s>>>(sh.big, sh.m, sh.compr, d.zinv.template as<Fr>(), d.c(4), p);
+    B200_LAUNCH_CHECK();
+    return B200_OK;
+}
+
+// r1cs_to_qap_witness_map (r1cs_to_qap.tcc:252-330, d1 = d2 = d3 = 0) over a step domain
+template<class Fr> int step_witness_map_dev(Fr *dA, Fr *dB, Fr *dC, const StepShape &sh, Fr *dH)
+{
+    StepDomain<Fr> *d = nullptr;
+    int rc = get_step_domain<Fr>(sh, &d);
+    if (rc) {
+        return rc;
+    }
+    uint32_t gen[Fr::N];
+    for (int i = 0; i < Fr::N; ++i) {
+        gen[i] = Fr::params::generator(i);
+    }
+    if (g_bufS.reserve(sh.big * sizeof(Fr))) {
+        return B200_ERR_CUDA;
+    }
+    Fr *S = g_bufS.as<Fr>();
+    Fr *vecs[3] = {dA, dB, dC};
+    for (int v = 0; v < 3; ++v) {
+        if ((rc = step_op_dev<Fr>(B200_IFFT, vecs[v], S, sh, nullptr)) ||
+            (rc = step_op_dev<Fr>(B200_COSET_FFT, vecs[v], S, sh, gen))) {
+            return rc;
+        }
+    }
+    cudaStream_t s = rt::stream();
+    ntt::k_pointwise_abc<Fr><<<grid_for(sh.m, 256), 256, 0, s>>>(sh.m, dA, dB, dC, dH);
+    B200_LAUNCH_CHECK();
+    if ((rc = step_divide_by_z_dev<Fr>(*d, dH)) || (rc = step_op_dev<Fr>(B200_ICOSET_FFT, dH, S, sh, gen))) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaMemsetAsync(dH + sh.m, 0, sizeof(Fr), s));
+    return B200_OK;
+}
+
+template<class Fr> int step_divide_by_z_host(void *data, size_t m, bool *handled)
+{
+    StepShape sh;
+    *handled = step_shape<Fr>(m, &sh);
+    if (!*handled) {
+        return B200_OK;
+    }
+    StepDomain<Fr> *d = nullptr;
+    int rc = get_step_domain<Fr>(sh, &d);
+    if (rc) {
+        return rc;
+    }
+    const size_t bytes = m * sizeof(Fr);
+    if (g_bufA.reserve(bytes)) {
+        return B200_ERR_CUDA;
+    }
+    cudaStream_t s = rt::stream();
+    B200_CUDA_CHECK(cudaMemcpyAsync(g_bufA.p, data, bytes, cudaMemcpyHostToDevice, s));
+    if ((rc = step_divide_by_z_dev<Fr>(*d, g_bufA.as<Fr>()))) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaMemcpyAsync(data, g_bufA.p, bytes, cudaMemcpyDeviceToHost, s));
+    B200_CUDA_CHECK(cudaStreamSynchronize(s));
+    return B200_OK;
+}
+
+template<class Fr> int step_witness_map_try(Fr *dA, Fr *dB, Fr *dC, size_t m, Fr *dH, bool *handled)
+{
+    StepShape sh;
+    *handled = step_shape<Fr>(m, &sh);
+    if (!*handled) {
+        return B200_OK;
+    }
+    return step_witness_map_dev<Fr>(dA, dB, dC, sh, dH);
 }
 
 // ---- R1CS on the device -------------------------------------------------------------------------

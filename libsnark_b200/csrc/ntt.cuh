@@ -344,6 +344,107 @@ template<class Fr> __global__ void k_scale(uint64_t m, Fr *a, const Fr *c)
     }
 }
 
+// ---- step_radix2_domain (libfqfft/evaluation_domain/domains/step_radix2_domain.tcc) ---------------
+// Domain of size m = big + small, big = 2^k > small = 2^r: the factory's choice for every size that
+// is not a power of two (get_evaluation_domain.tcc:41-58). A transform is two radix-2 transforms
+// (sizes big and small) plus the element-wise steps below; T2[e] = omega^e, e < big, is the
+// twiddle table of the radix-2 domain of size 2 big (omega = its root of unity).
+
+// FFT, step_radix2_domain.tcc:73-88: c[i] = a[i] + a[i+big] (i < small) else a[i];
+// d[i] = omega^i * (a[i] - a[i+big] or a[i]). c overwrites a[0, big), d goes to its own buffer.
+template<class Fr>
+__global__ void k_step_fft_pre(uint64_t big, uint64_t small, const Fr *T2, Fr *a, Fr *d)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= big) {
+        return;
+    }
+    const Fr x = gload(a + i);
+    Fr c = x, dd = x;
+    if (i < small) {
+        const Fr y = gload(a + i + big);
+        c = x + y;
+        dd = x - y;
+    }
+    gstore(a + i, c);
+    gstore(d + i, dd * gload(T2 + i));
+}
+// one halving step of e[i] = sum_j d[i + j small] (:90-98): v[t] += v[t + half]
+template<class Fr> __global__ void k_fold_halve(uint64_t half, Fr *v)
+{
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < half) {
+        gstore(v + t, gload(v + t) + gload(v + t + half));
+    }
+}
+// iFFT, :135-150: tmp[i] = U0[i] omega^i for i >= small, 0 below (the j = 0 term is not subtracted)
+template<class Fr>
+__global__ void k_step_ifft_tmp(uint64_t big, uint64_t small, const Fr *T2, const Fr *u0, Fr *tmp)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < big) {
+        gstore(tmp + i, i < small ? Fr::zero() : gload(u0 + i) * gload(T2 + i));
+    }
+}
+// iFFT, :152-173: U1[i] = (U1[i] - s[i]) omega^-i; a[i] = (U0[i] + U1[i]) / 2; a[big+i] = (U0[i] - U1[i]) / 2
+template<class Fr>
+__global__ void k_step_ifft_post(uint64_t big, uint64_t small, const Fr *T2, const Fr *s, const Fr *over_two, Fr *a)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= small) {
+        return;
+    }
+    const Fr u0 = gload(a + i);
+    Fr u1 = gload(a + big + i) - gload(s + i);
+    if (i != 0) {
+        u1 = u1 * gload(T2 + (big - i)).neg(); // omega^big = -1
+    }
+    const Fr h = gload(over_two);
+    gstore(a + i, (u0 + u1) * h);
+    gstore(a + big + i, (u0 - u1) * h);
+}
+// a[i] *= table[i]
+template<class Fr> __global__ void k_mul_table(uint64_t n, Fr *a, const Fr *table)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        gstore(a + i, gload(a + i) * gload(table + i));
+    }
+}
+// divide_by_Z_on_coset, :252-276: zinv[k] = (A w2s^k - B)^-1, k < compr (the factor has period compr in i)
+template<class Fr> __global__ void k_step_zinv(uint64_t compr, const Fr *abw /* A, B, w2s */, Fr *zinv)
+{
+    const uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= compr) {
+        return;
+    }
+    Fr elt = Fr::one(), base = gload(abw + 2);
+    for (uint64_t e = k; e; e >>= 1) {
+        if (e & 1) {
+            elt = elt * base;
+        }
+        base = base.sqr();
+    }
+    gstore(zinv + k, (gload(abw) * elt - gload(abw + 1)).inverse());
+}
+template<class Fr>
+__global__ void k_step_divz(uint64_t big, uint64_t m, uint64_t compr, const Fr *zinv, const Fr *z1inv, Fr *p)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < m) {
+        const Fr f = i < big ? gload(zinv + (i & (compr - 1))) : gload(z1inv);
+        gstore(p + i, gload(p + i) * f);
+    }
+}
+// h[i] = a[i] b[i] - c[i]
+template<class Fr> __global__ void k_pointwise_abc(uint64_t m, const Fr *a, const Fr *b, const Fr *c, Fr *h)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < m) {
+        gstore(h + i, gload(a + i) * gload(b + i) - gload(c + i));
+    }
+}
+
 constexpr uint32_t R1CS_LONG_ROW = 64;
 constexpr int R1CS_LONG_THREADS = 256;
 constexpr uint32_t R1CS_LONG_SEG = 2048; // terms per CTA of the long-row kernel

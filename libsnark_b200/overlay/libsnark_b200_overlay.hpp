@@ -14,7 +14,7 @@
 //   libff::multi_exp_filter_one_zero<...same...>                       (multiexp.hpp:83-88)
 //   libsnark::kc_multi_exp_with_mixed_addition<G2, G1, Fr, BDLO12_signed, special>
 //                                       (libsnark/knowledge_commitment/kc_multiexp.hpp:32-44)
-//   libfqfft::basic_radix2_domain<Fr>::{FFT, iFFT, cosetFFT, icosetFFT, divide_by_Z_on_coset}
+//   libfqfft::basic_radix2_domain<Fr> and step_radix2_domain<Fr>::{FFT, iFFT, cosetFFT, icosetFFT, divide_by_Z_on_coset}
 //                                       (libfqfft/evaluation_domain/domains/basic_radix2_domain.hpp)
 // for G in {G1, G2} of alt_bn128, bls12_377 and bw6_761. Every other instantiation (other methods,
 // base forms, curves, domains) keeps the reference's CPU template. There is no CPU fallback inside
@@ -44,6 +44,7 @@
 #include <libff/algebra/scalar_multiplication/multiexp.hpp>
 #include <libff/common/profiling.hpp>
 #include <libfqfft/evaluation_domain/domains/basic_radix2_domain.hpp>
+#include <libfqfft/evaluation_domain/domains/step_radix2_domain.hpp>
 #include <libfqfft/evaluation_domain/get_evaluation_domain.hpp>
 #include <libfqfft/tools/exceptions.hpp>
 #include <libsnark/knowledge_commitment/kc_multiexp.hpp>
@@ -513,31 +514,36 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
     }                                                                                                                  \
     }
 
-#define B200_OVERLAY_NTT(FR)                                                                                           \
-    namespace libfqfft                                                                                                 \
-    {                                                                                                                  \
-    template<> inline void basic_radix2_domain<FR>::FFT(std::vector<FR> &a)                                            \
+#define B200_OVERLAY_DOMAIN(DOMAIN, FR)                                                                                \
+    template<> inline void DOMAIN<FR>::FFT(std::vector<FR> &a)                                                         \
     {                                                                                                                  \
         libsnark_b200::ntt<FR>(a, this->m, B200_FFT, nullptr);                                                         \
     }                                                                                                                  \
-    template<> inline void basic_radix2_domain<FR>::iFFT(std::vector<FR> &a)                                           \
+    template<> inline void DOMAIN<FR>::iFFT(std::vector<FR> &a)                                                        \
     {                                                                                                                  \
         libsnark_b200::ntt<FR>(a, this->m, B200_IFFT, nullptr);                                                        \
     }                                                                                                                  \
-    template<> inline void basic_radix2_domain<FR>::cosetFFT(std::vector<FR> &a, const FR &g)                          \
+    template<> inline void DOMAIN<FR>::cosetFFT(std::vector<FR> &a, const FR &g)                                       \
     {                                                                                                                  \
         libsnark_b200::ntt<FR>(a, this->m, B200_COSET_FFT, &g);                                                        \
     }                                                                                                                  \
-    template<> inline void basic_radix2_domain<FR>::icosetFFT(std::vector<FR> &a, const FR &g)                         \
+    template<> inline void DOMAIN<FR>::icosetFFT(std::vector<FR> &a, const FR &g)                                      \
     {                                                                                                                  \
         libsnark_b200::ntt<FR>(a, this->m, B200_ICOSET_FFT, &g);                                                       \
     }                                                                                                                  \
-    template<> inline void basic_radix2_domain<FR>::divide_by_Z_on_coset(std::vector<FR> &P)                           \
+    template<> inline void DOMAIN<FR>::divide_by_Z_on_coset(std::vector<FR> &P)                                        \
     {                                                                                                                  \
         libsnark_b200::check(                                                                                          \
             b200_divide_by_Z_on_coset(libsnark_b200::curve_of<FR>::curve, P.data(), this->m),                          \
             "b200_divide_by_Z_on_coset");                                                                              \
-    }                                                                                                                  \
+    }
+// basic_radix2_domain (m = 2^k) and step_radix2_domain (m = 2^k + 2^r, step_radix2_domain.tcc:65-276): the
+// library tells them apart by m.
+#define B200_OVERLAY_NTT(FR)                                                                                           \
+    namespace libfqfft                                                                                                 \
+    {                                                                                                                  \
+    B200_OVERLAY_DOMAIN(basic_radix2_domain, FR)                                                                       \
+    B200_OVERLAY_DOMAIN(step_radix2_domain, FR)                                                                        \
     }
 
 B200_OVERLAY_MSM(libff::alt_bn128_G1, libff::alt_bn128_Fr)

@@ -149,3 +149,48 @@ def test_c_abi_prover_bit_exact(ref, b200, curve, log_m, real_keys):
             cs.free()
     finally:
         fx.close()
+
+
+@pytest.mark.parametrize("curve,nc,ni", [("alt_bn128", 1024 + 100, 10), ("alt_bn128", (1 << 14) + 3, 2), ("bls12_377", 600, 5)])
+def test_prover_on_step_domain(ref, b200, curve, nc, ni):
+    """Constraint counts that are not a power of two: the reference's factory picks step_radix2_domain; the witness map
+    (every H coefficient) and the whole proof still match bit for bit."""
+    fx = ref.groth16_setup(curve, nc, ni, real_keys=False)
+    try:
+        m = fx.sizes["m"]
+        assert m & (m - 1) and m == b200.domain_size_for(nc + ni + 1)
+        pk, cs = _device_pk(b200, fx)
+        try:
+            assert np.array_equal(cs.witness_map_h(fx.full_assignment(), m), fx.witness_map()[0])
+            rs = ref.field_random(curve, refo.FR, 0xF00D, 2)
+            want, _ = fx.prove(rs[0], rs[1])
+            got, _ = pk.prove(fx.primary_input, fx.auxiliary_input, rs[0], rs[1])
+            assert np.array_equal(got, want)
+        finally:
+            pk.free()
+            cs.free()
+    finally:
+        fx.close()
+
+
+def test_overlay_step_domain(ref, overlay):
+    """The overlay's step_radix2_domain specialisations: operators through the reference's own factory, and the
+    reference prover (operators overlaid, and the one-call device prover) on a circuit whose size is not a power of two."""
+    curve = "alt_bn128"
+    m = (1 << 11) + (1 << 7)
+    a = ref.field_random(curve, refo.FR, 31, m)
+    g = ref.field_consts(curve, refo.FR)["generator"]
+    for op in (refo.FFT, refo.IFFT, refo.COSET_FFT, refo.ICOSET_FFT, refo.DIV_Z_COSET):
+        assert np.array_equal(overlay.fft(curve, op, a, g, via_factory=True), ref.fft(curve, op, a, g, via_factory=True))
+    fx = ref.groth16_setup(curve, 3000, 7, real_keys=True)
+    try:
+        assert fx.sizes["m"] & (fx.sizes["m"] - 1)
+        rs = ref.field_random(curve, refo.FR, 0xC0FFEE, 2)
+        want, _ = fx.prove(rs[0], rs[1])
+        got, _ = fx.prove(rs[0], rs[1], via=overlay)
+        assert np.array_equal(got, want)
+        got, _ = fx.prove_fused(rs[0], rs[1], via=overlay)
+        assert np.array_equal(got, want)
+        assert fx.verify(got) == 1
+    finally:
+        fx.close()

@@ -53,10 +53,11 @@ def test_fft_small_known_vector(ref, b200):
 
 
 def test_domain_size_exception(b200):
-    """basic_radix2_domain.tcc:57,65: a.size() != m throws DomainSizeException; non powers of two have no basic domain."""
+    """basic_radix2_domain.tcc:57,65: a.size() != m throws DomainSizeException; a size that is neither 2^k nor
+    2^k + 2^r has no radix-2 domain (the factory never asks for one: it rounds, get_evaluation_domain.tcc:41-58)."""
     a = np.zeros((6, 4), dtype=np.uint64)
     with pytest.raises(b200.DomainSizeException):
-        b200.get_evaluation_domain("alt_bn128", 6).FFT(a)
+        b200.evaluation_domain("alt_bn128", 7).FFT(np.zeros((7, 4), dtype=np.uint64))
     with pytest.raises(b200.DomainSizeException):
         b200.get_evaluation_domain("alt_bn128", 8).FFT(a)
 
@@ -92,3 +93,28 @@ def test_witness_map_h(ref, b200, curve, log_m):
     got = b200.r1cs_to_qap_witness_map_h(curve, aA, aB, aC)
     assert np.array_equal(got, want)
     fx.close()
+
+
+@pytest.mark.parametrize("curve", CURVES)
+@pytest.mark.parametrize("m", [3, 5, 6, 12, 20, 48, 1024 + 64, (1 << 14) + (1 << 13), (1 << 16) + 1, (1 << 16) + 256])
+def test_step_radix2_domain_matches_reference(ref, b200, curve, m):
+    """step_radix2_domain (sizes 2^k + 2^r: what get_evaluation_domain returns for every non-power-of-two size,
+    get_evaluation_domain.tcc:41-58): all four transforms and divide_by_Z_on_coset, bit-exact
+    (step_radix2_domain.tcc:65-276)."""
+    a = ref.field_random(curve, refo.FR, 100 + m, m)
+    g = _gen(ref, curve)
+    dom = b200.get_evaluation_domain(curve, m)
+    assert dom.m == m
+    for name, op in [("FFT", refo.FFT), ("iFFT", refo.IFFT), ("cosetFFT", refo.COSET_FFT), ("icosetFFT", refo.ICOSET_FFT)]:
+        got = getattr(dom, name)(a, g) if "coset" in name else getattr(dom, name)(a)
+        assert np.array_equal(got, ref.fft(curve, op, a, g, via_factory=True)), (name, m)
+    assert np.array_equal(dom.divide_by_Z_on_coset(a), ref.fft(curve, refo.DIV_Z_COSET, a, g, via_factory=True))
+    assert np.array_equal(dom.iFFT(dom.FFT(a)), a)
+
+
+def test_factory_rounding(b200):
+    """get_evaluation_domain.tcc:37-58: 2^k stays, 2^k + 2^r stays, anything else rounds its small part up."""
+    assert b200.domain_size_for(1 << 20) == 1 << 20
+    assert b200.domain_size_for((1 << 20) + 11) == (1 << 20) + 16          # SURVEY.md §8d: 1048592
+    assert b200.domain_size_for((1 << 10) + 100) == (1 << 10) + 128
+    assert b200.domain_size_for(1000) == 1024

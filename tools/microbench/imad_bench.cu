@@ -159,6 +159,32 @@ template<class F> __global__ void __launch_bounds__(128) k_fp_mul(uint64_t *out,
     a = a + b + c + d;
     out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = a.v[0];
 }
+// one dependent chain per thread / three independent chains per thread (ILP probe)
+template<class F> __global__ void __launch_bounds__(128) k_fp_mul1(uint64_t *out, const F *in, int iters)
+{
+    F a = in[threadIdx.x], b = in[threadIdx.x + 128];
+    for (int it = 0; it < iters; ++it) {
+        a = F::mul_inline(a, b);
+        b = F::mul_inline(b, a);
+        a = F::mul_inline(a, b);
+        b = F::mul_inline(b, a);
+    }
+    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = (a + b).v[0];
+}
+template<class F> __global__ void __launch_bounds__(128) k_fp_mul3(uint64_t *out, const F *in, int iters)
+{
+    F a = in[threadIdx.x], b = in[threadIdx.x + 128], c = in[threadIdx.x + 256], d = in[threadIdx.x + 384];
+    F e = a + c, f = b + d;
+    for (int it = 0; it < iters; ++it) {
+        a = F::mul_inline(a, b);
+        c = F::mul_inline(c, d);
+        e = F::mul_inline(e, f);
+        b = b + a;
+        d = d + c;
+        f = f + e;
+    }
+    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = (a + c + e).v[0];
+}
 template<class P> __global__ void __launch_bounds__(128) k_fpu_mul(uint64_t *out, const Fp<P> *in, int iters)
 {
     typedef FpUOf<P> U;
@@ -236,7 +262,16 @@ int main()
         CHECK(cudaMemcpy(in, h, sizeof(h), cudaMemcpyHostToDevice));
     }
     const int mit = 2048;
-    for (int cta_per_sm : {2, 4, 8}) {
+    for (int cta_per_sm : {1, 2, 4}) {
+        const int g2 = sms * cta_per_sm;
+        double ms = time_ms([&] { k_fp_mul1<F><<<g2, 128>>>(out, in, mit); });
+        double muls = (double)g2 * 128 * mit * 4;
+        printf("I Fp<254> ONE chain/thread,   %d CTA/SM x128 (%d warps/SMSP): %.2f Tmad/s\n", cta_per_sm, cta_per_sm, muls * 136 / ms * 1e3 / 1e12);
+        ms = time_ms([&] { k_fp_mul3<F><<<g2, 128>>>(out, in, mit); });
+        muls = (double)g2 * 128 * mit * 3;
+        printf("J Fp<254> THREE chains/thread, %d CTA/SM x128 (%d warps/SMSP): %.2f Tmad/s\n", cta_per_sm, cta_per_sm, muls * 136 / ms * 1e3 / 1e12);
+    }
+    for (int cta_per_sm : {1, 2, 4, 8}) {
         const int g2 = sms * cta_per_sm;
         double ms = time_ms([&] { k_fp_mul<F><<<g2, 128>>>(out, in, mit); });
         double muls = (double)g2 * 128 * mit * 4;
