@@ -210,6 +210,17 @@ template<class F>
 HD void accumulate_task(const Task &tk, const uint32_t *entries, const Affine<F> *bases, XYZZ<F> *out)
 {
     XYZZ<F> acc = XYZZ<F>::inf();
+#if defined(B200_ACC_NO_PREFETCH)
+    // wide fields: the next base is NOT held in registers across the addition (it would cost
+    // 2 sizeof(F) / 4 registers of a budget that is already spilling); the other resident warps
+    // cover the load latency instead
+    for (uint32_t k = 0; k < tk.len; ++k) {
+        const uint32_t e = entries[tk.start + k];
+        Affine<F> cur = load_vec_ro(bases + (e & 0x7fffffffu));
+        cur.y = cur.y.cneg((e >> 31) != 0);
+        madd(acc, cur);
+    }
+#else
     uint32_t e = entries[tk.start];
     Affine<F> p = load_vec_ro(bases + (e & 0x7fffffffu));
     for (uint32_t k = 0; k < tk.len; ++k) {
@@ -222,6 +233,7 @@ HD void accumulate_task(const Task &tk, const uint32_t *entries, const Affine<F>
         cur.y = cur.y.cneg(negate);
         madd(acc, cur);
     }
+#endif
     store_vec(out, acc);
 }
 
@@ -466,9 +478,14 @@ static __global__ void k_build_tasks(
 // contiguous) and are redistributed over the threads in order of decreasing length, which
 // keeps the trip counts inside each warp nearly equal.
 constexpr int ACC_THREADS = 128;
+// Resident CTAs per SM the accumulate kernel is compiled for (caps its registers): the wide fields and
+// Fp2 otherwise take 222-255 registers and run two warps per scheduler (profiles/r1_ncu_accumulate_g2.md).
+#ifndef B200_ACC_MIN_BLOCKS
+#define B200_ACC_MIN_BLOCKS 1
+#endif
 
 template<class F>
-__global__ void __launch_bounds__(ACC_THREADS) k_accumulate(
+__global__ void __launch_bounds__(ACC_THREADS, B200_ACC_MIN_BLOCKS) k_accumulate(
     const Task *tasks, const uint32_t *num_tasks, const uint32_t *entries, const Affine<F> *bases,
     XYZZ<F> *partial)
 {
