@@ -15,7 +15,9 @@ bucket sort -> bucket accumulation -> bucket reduction -> window fold -> normali
 N > 1  : weak scaling by base range: every rank owns a 2^20-point shard of one
          N*2^20-point MSM, computes its per-window sums, the ranks all-gather them over NCCL and rank 0
          folds. value = N*2^20 points / max-over-ranks time.
-Secondary metrics of BASELINE.json ("NTT elem/s @2^24") ride along under "ntt" (N = 1 only).
+Secondary metrics of BASELINE.json ride along: "ntt" (NTT elem/s @2^24, N = 1 only) and "groth16_prove" (Groth16 prove
+ms @2^20 BN254: b200_groth16_prove at N = 1; at N > 1 the same fixed problem sharded over the N ranks by
+libsnark_b200.DistributedProver, tools/prove_multi.py — strong scaling).
 Inputs are synthetic (device-generated points, numpy scalars): nothing under oracle/ is touched by the
 timed path; oracle/_ref is used for the cpu_baseline leg and for --impl reference only.
 """
@@ -295,6 +297,13 @@ def run_b200_arm(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
     }
+    prove_multi_obj = None
+    if world > 1 and not args.no_prove:
+        # the whole prover sharded over the ranks (strong scaling of the fixed 2^20 problem); all ranks take part
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import prove_multi
+        prove_multi_obj = prove_multi.run(b, torch, dist, CURVE, args.prove_log_m, max(3, min(args.steps, 10)),
+                                          max(3, args.warmup))
     if rank == 0:
         wide, lo, _ = b.imad_peak()
         c = line["config"]["window_bits"]
@@ -318,6 +327,8 @@ def run_b200_arm(args):
             line["ntt"] = bench_ntt(b, torch, args.ntt_log_m, wide)
         if world == 1 and not args.no_prove:
             line["groth16_prove"] = bench_groth16(b, args.prove_log_m, max(3, min(args.steps, 10)), max(3, args.warmup))
+        if prove_multi_obj is not None:
+            line["groth16_prove"] = prove_multi_obj
         if world == 1 and not args.no_cpu_baseline:
             try:
                 rate, threads, sample, _ = reference_msm_rate(args.log_n, 2, 1, budget_s=20.0)

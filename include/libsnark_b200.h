@@ -157,6 +157,13 @@ int b200_r1cs_evaluate(b200_r1cs_t handle, const void *w, size_t m, void *aA, vo
  * num_variables + 1 elements) -> dH = coefficients_for_H (device, m + 1 elements). The MSMs can
  * then consume d_w and dH in place (b200_msm_resident with scalars_on_device = 1). */
 int b200_witness_map_r1cs_dev(b200_r1cs_t handle, const void *d_w, size_t m, void *dH);
+/* The two halves of b200_witness_map_r1cs_dev, for provers that run the A, B and C chains on different
+ * GPUs (r1cs_to_qap.tcc:252-290 and :293-330). m must be a power of two.
+ * chain : which = 0/1/2 -> the evaluations of the a-/b-/c-combinations from d_w, iFFT, cosetFFT(g) into
+ *         d_out (device, m elements).
+ * finish: (dA * dB - dC) / Z on the coset, icosetFFT -> dH (device, m + 1 elements); dA is clobbered. */
+int b200_witness_chain_r1cs_dev(b200_r1cs_t handle, const void *d_w, size_t m, int which, void *d_out);
+int b200_witness_finish_dev(int curve, void *dA, const void *dB, const void *dC, size_t m, void *dH);
 /* d_dst[i] = d_src[d_idx[i]], Fr elements, all pointers device (the scalars of a sparse
  * knowledge-commitment query, kc_multiexp.tcc:52-89). */
 int b200_gather_dev(int curve, const void *d_src, const uint32_t *d_idx, size_t n, void *d_dst);
@@ -184,6 +191,46 @@ int b200_groth16_pk_free(b200_groth16_pk_t handle);
 int b200_groth16_prove(b200_groth16_pk_t handle, const void *primary_input,
                        const void *auxiliary_input, const void *r, const void *s, void *proof_out,
                        double *stage_ms);
+
+/* ---- the prover sharded over the GPUs of one box (the reference splits every multi_exp
+ *      over OpenMP threads the same way, multiexp.tcc:663-687). One process per GPU; rank g of `world`
+ *      holds entries b200_shard_range(total, world, g) of each query: A (num_variables + 1 points),
+ *      B (B_total entries of the sparse vector), H (domain_size - 1), L (num_variables - num_inputs),
+ *      and the whole constraint system. A rank computes the window sums of its five partial MSMs into
+ *      one "blob" of b200_groth16_shard_bytes() bytes in device memory; the ranks all-gather the blobs
+ *      (NCCL over NVLink) and b200_groth16_assemble — host code, no device needed — folds them into the
+ *      proof. ------------------------------------------------------------------------------------- */
+void b200_shard_range(size_t total, int world, int rank, size_t *first, size_t *count);
+/* query_sizes = {A, B, H, L} totals as above. */
+size_t b200_groth16_shard_bytes(int curve, const size_t query_sizes[4], int world);
+/* As b200_groth16_pk_create with the handles holding this rank's shards. B_indices_shard = this rank's slice
+ * of sparse_vector::indices (NULL when B_total == num_variables + 1, i.e. every index is present). */
+int b200_groth16_pk_create_shard(int curve, const void *alpha_g1, const void *beta_g1, const void *beta_g2,
+                                 const void *delta_g1, const void *delta_g2, b200_bases_t A_shard,
+                                 b200_bases_t B_g2_shard, b200_bases_t B_g1_shard,
+                                 const uint32_t *B_indices_shard, size_t B_total, b200_bases_t H_shard,
+                                 b200_bases_t L_shard, b200_r1cs_t r1cs, size_t num_constraints,
+                                 size_t num_inputs, size_t num_variables, size_t domain_size, int rank,
+                                 int world, b200_groth16_pk_t *handle);
+/* One rank's share of one proof in one call: witness (host) in, blob (device) out; the witness map is
+ * computed on every rank. stage_ms as b200_groth16_prove. */
+int b200_groth16_prove_shard(b200_groth16_pk_t handle, const void *primary_input,
+                             const void *auxiliary_input, void *dev_blob, double *stage_ms);
+/* The same in steps, so that the caller can place collectives between them:
+ *   begin : (1 | primary | auxiliary) to the device.
+ *   chain : b200_witness_chain_r1cs_dev on the uploaded witness (which = 0/1/2 for A/B/C) -> dev_out.
+ *   h     : coefficients_for_H — from the witness alone when dA = dB = dC = NULL (all seven transforms on
+ *           this rank), else b200_witness_finish_dev on three chain results (broadcast between ranks).
+ *   msm   : the partial MSMs selected by mask (bit 0 A, 1 B.g2, 2 B.g1, 3 H, 4 L) into their blob slots;
+ *           H needs `h` first, the others only `begin`. */
+int b200_groth16_shard_begin(b200_groth16_pk_t handle, const void *primary_input, const void *auxiliary_input);
+int b200_groth16_shard_chain(b200_groth16_pk_t handle, int which, void *dev_out);
+int b200_groth16_shard_h(b200_groth16_pk_t handle, void *dA, const void *dB, const void *dC);
+int b200_groth16_shard_msm(b200_groth16_pk_t handle, unsigned mask, void *dev_blob);
+/* blobs = `world` blobs in rank order (host memory). proof_out as b200_groth16_prove. */
+int b200_groth16_assemble(int curve, const void *alpha_g1, const void *beta_g1, const void *beta_g2,
+                          const void *delta_g1, const void *delta_g2, const size_t query_sizes[4], int world,
+                          const void *blobs, const void *r, const void *s, void *proof_out);
 
 /* ---- measurement helpers (used by bench.py; not part of the reference surface) ------- */
 /* Integer-pipe microbenchmarks, multiply-adds per second: wide = 32x32+64 IMAD.WIDE.U32(.X) chains

@@ -38,6 +38,10 @@ EXPORTS = [
     "b200_imad_carry_peak", "b200_imad_peak", "b200_last_msm_timing", "b200_launch_count",
     "b200_r1cs_upload", "b200_r1cs_free", "b200_r1cs_evaluate", "b200_witness_map_r1cs_dev", "b200_gather_dev",
     "b200_groth16_pk_create", "b200_groth16_pk_free", "b200_groth16_prove",
+    "b200_witness_chain_r1cs_dev", "b200_witness_finish_dev",
+    "b200_shard_range", "b200_groth16_shard_bytes", "b200_groth16_pk_create_shard", "b200_groth16_prove_shard",
+    "b200_groth16_shard_begin", "b200_groth16_shard_chain", "b200_groth16_shard_h", "b200_groth16_shard_msm",
+    "b200_groth16_assemble",
 ]
 
 
@@ -102,6 +106,20 @@ def lib():
                                              C.POINTER(u64)]
         L.b200_groth16_pk_free.argtypes = [u64]
         L.b200_groth16_prove.argtypes = [u64, vp, vp, vp, vp, vp, C.POINTER(C.c_double)]
+        L.b200_witness_chain_r1cs_dev.argtypes = [u64, vp, sz, i, vp]
+        L.b200_witness_finish_dev.argtypes = [i, vp, vp, vp, sz, vp]
+        L.b200_shard_range.restype = None
+        L.b200_shard_range.argtypes = [sz, i, i, C.POINTER(sz), C.POINTER(sz)]
+        L.b200_groth16_shard_bytes.restype = sz
+        L.b200_groth16_shard_bytes.argtypes = [i, C.POINTER(sz), i]
+        L.b200_groth16_pk_create_shard.argtypes = [i, vp, vp, vp, vp, vp, u64, u64, u64, vp, sz, u64, u64, u64, sz, sz, sz,
+                                                   sz, i, i, C.POINTER(u64)]
+        L.b200_groth16_prove_shard.argtypes = [u64, vp, vp, vp, C.POINTER(C.c_double)]
+        L.b200_groth16_shard_begin.argtypes = [u64, vp, vp]
+        L.b200_groth16_shard_chain.argtypes = [u64, i, vp]
+        L.b200_groth16_shard_h.argtypes = [u64, vp, vp, vp]
+        L.b200_groth16_shard_msm.argtypes = [u64, C.c_uint, vp]
+        L.b200_groth16_assemble.argtypes = [i, vp, vp, vp, vp, vp, C.POINTER(sz), i, vp, vp, vp, vp]
         L.b200_last_msm_timing.argtypes = [C.POINTER(C.c_double)]
         L.b200_launch_count.restype = u64
         L.b200_msm_resident_windows_dev.argtypes = [u64, sz, sz, vp, i, vp]
@@ -436,6 +454,156 @@ class Groth16ProvingKey:
             self.handle = 0
             for rb in self.sets:
                 rb.free()
+
+
+# ---- the prover sharded over several GPUs ------------------------------------------
+
+MSM_A, MSM_B_G2, MSM_B_G1, MSM_H, MSM_L = 1, 2, 4, 8, 16
+
+
+def shard_range(total, world, rank):
+    """(first, count) of rank's contiguous slice of a `total`-entry query (b200_shard_range)."""
+    f, c = C.c_size_t(0), C.c_size_t(0)
+    lib().b200_shard_range(total, world, rank, C.byref(f), C.byref(c))
+    return f.value, c.value
+
+
+def groth16_shard_bytes(curve, query_sizes, world):
+    qs = (C.c_size_t * 4)(*[int(x) for x in query_sizes])
+    return lib().b200_groth16_shard_bytes(_cid(curve), qs, world)
+
+
+def groth16_assemble(curve, alpha_g1, beta_g1, beta_g2, delta_g1, delta_g2, query_sizes, world, blobs, r, s):
+    """The gathered window sums of all ranks -> the proof (host arithmetic only; b200_groth16_assemble)."""
+    c = _cid(curve)
+    pts = [_u64(x) for x in (alpha_g1, beta_g1, beta_g2, delta_g1, delta_g2)]
+    blobs = np.ascontiguousarray(blobs).view(np.uint8).reshape(-1)
+    qs = (C.c_size_t * 4)(*[int(x) for x in query_sizes])
+    if blobs.shape[0] != world * lib().b200_groth16_shard_bytes(c, qs, world):
+        raise B200Error(ERR_ARG, "blobs must hold world * b200_groth16_shard_bytes bytes")
+    r, s = _u64(r), _u64(s)
+    out = np.zeros((2 * sizeof_group(c, G1) + sizeof_group(c, G2)) // 8, dtype=np.uint64)
+    _check(lib().b200_groth16_assemble(c, *[_p(x) for x in pts], qs, world, _p(blobs), _p(r), _p(s), _p(out)))
+    return out
+
+
+class Groth16ProvingKeyShard:
+    """Rank `rank` of `world`'s share of a proving key: the slice b200_shard_range gives it of each of A_query,
+    B_query (G2 and G1 halves, with the matching slice of the sparse vector's indices), H_query and L_query, plus
+    the whole constraint system. With sliced=False the arguments are the whole queries and the slices are cut here;
+    with sliced=True they already are this rank's slices and B_total = the whole B query's entry count."""
+
+    def __init__(self, curve, alpha_g1, beta_g1, beta_g2, delta_g1, delta_g2, A_query, B_query_g2, B_query_g1,
+                 B_indices, H_query, L_query, r1cs, domain_size, rank, world, sliced=False, B_total=None):
+        self.curve, self.r1cs, self.rank, self.world, self.m = curve, r1cs, rank, world, int(domain_size)
+        nv, ni = r1cs.nv, r1cs.ni
+        if B_total is None:
+            B_total = B_query_g2.shape[0] if not sliced else nv + 1
+        self.query_sizes = [nv + 1, int(B_total), self.m - 1, nv - ni]
+        rng = [shard_range(t, world, rank) for t in self.query_sizes]
+        self.ranges = rng
+
+        def cut(a, q):
+            if a is None:
+                return None
+            return a if sliced else a[rng[q][0]:rng[q][0] + rng[q][1]]
+        qs = [cut(A_query, 0), cut(B_query_g2, 1), cut(B_query_g1, 1), cut(H_query[:self.m - 1] if not sliced else H_query, 2),
+              cut(L_query, 3)]
+        groups = [G1, G2, G1, G1, G1]
+        self.sets = [ResidentBases(curve, g, q) if q.shape[0] else None for g, q in zip(groups, qs)]
+        idx = cut(None if B_indices is None else np.ascontiguousarray(B_indices, dtype=np.uint32), 1)
+        if idx is not None:
+            idx = np.ascontiguousarray(idx)
+        self.points = [_u64(x).copy() for x in (alpha_g1, beta_g1, beta_g2, delta_g1, delta_g2)]
+        hs = [0 if x is None else x.handle for x in self.sets]
+        h = C.c_uint64(0)
+        _check(lib().b200_groth16_pk_create_shard(
+            _cid(curve), *[_p(x) for x in self.points], hs[0], hs[1], hs[2], None if idx is None else _p(idx),
+            self.query_sizes[1], hs[3], hs[4], r1cs.handle, r1cs.nc, ni, nv, self.m, rank, world, C.byref(h)))
+        self.handle = h.value
+        self.blob_bytes = groth16_shard_bytes(curve, self.query_sizes, world)
+        self.fr_bytes = sizeof_fr(curve)
+
+    def prove_shard(self, primary_input, auxiliary_input, dev_blob):
+        """This rank's five partial MSMs (window sums) into the device blob at address dev_blob; the witness map is
+        computed locally. Returns the stage times in ms."""
+        pi, ai = _u64(primary_input), _u64(auxiliary_input)
+        ms = (C.c_double * 7)()
+        _check(lib().b200_groth16_prove_shard(self.handle, _p(pi), _p(ai), C.c_void_p(dev_blob), ms))
+        return dict(zip(["upload", "witness_map", "A", "B", "H", "L", "total"], list(ms)))
+
+    def begin(self, primary_input, auxiliary_input):
+        pi, ai = _u64(primary_input), _u64(auxiliary_input)
+        _check(lib().b200_groth16_shard_begin(self.handle, _p(pi), _p(ai)))
+
+    def chain(self, which, dev_out):
+        _check(lib().b200_groth16_shard_chain(self.handle, which, C.c_void_p(dev_out)))
+
+    def h(self, dA=None, dB=None, dC=None):
+        _check(lib().b200_groth16_shard_h(self.handle, *[None if x is None else C.c_void_p(x) for x in (dA, dB, dC)]))
+
+    def msm(self, mask, dev_blob):
+        _check(lib().b200_groth16_shard_msm(self.handle, mask, C.c_void_p(dev_blob)))
+
+    def assemble(self, r, s, blobs):
+        return groth16_assemble(self.curve, *self.points, self.query_sizes, self.world, blobs, r, s)
+
+    def free(self):
+        if self.handle:
+            _check(lib().b200_groth16_pk_free(self.handle))
+            self.handle = 0
+            for rb in self.sets:
+                if rb is not None:
+                    rb.free()
+
+
+class DistributedProver:
+    """r1cs_gg_ppzksnark_prover over the ranks of an initialised torch.distributed (NCCL) process group, one
+    Groth16ProvingKeyShard per rank. Per proof: every rank uploads the witness; with chain_parallel (>= 3 ranks,
+    power-of-two domain) ranks 0, 1, 2 each run one of the A, B, C iFFT/cosetFFT chains and broadcast the result
+    while all ranks already run their A, B and L shard MSMs, then every rank finishes H — otherwise each rank
+    computes the whole witness map; the ranks' window sums are all-gathered (a few KB per rank) and folded on the
+    host. torch is used for the NCCL plumbing and the device buffers the collectives work on, nothing else."""
+
+    def __init__(self, shard, chain_parallel=None):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self.pk = torch, dist, shard
+        self.dev = torch.device("cuda", torch.cuda.current_device())
+        pow2 = shard.m & (shard.m - 1) == 0
+        self.chain_parallel = (shard.world >= 3 and pow2) if chain_parallel is None else bool(chain_parallel)
+        if self.chain_parallel and not (shard.world >= 3 and pow2):
+            raise B200Error(ERR_ARG, "chain-parallel witness map needs >= 3 ranks and a power-of-two domain")
+        self.blob = torch.zeros(shard.blob_bytes, dtype=torch.uint8, device=self.dev)
+        self.gathered = torch.zeros(shard.world * shard.blob_bytes, dtype=torch.uint8, device=self.dev)
+        self.chains = ([torch.empty(shard.m * shard.fr_bytes, dtype=torch.uint8, device=self.dev) for _ in range(3)]
+                       if self.chain_parallel else None)
+
+    def prove(self, primary_input, auxiliary_input, r, s, fold_on_all_ranks=False):
+        """The proof on rank 0 (on every rank with fold_on_all_ranks), None elsewhere."""
+        torch, dist, pk = self.torch, self.dist, self.pk
+        if self.chain_parallel:
+            pk.begin(primary_input, auxiliary_input)
+            if pk.rank < 3:
+                pk.chain(pk.rank, self.chains[pk.rank].data_ptr())
+            works = [dist.broadcast(self.chains[i], src=i, async_op=True) for i in range(3)]
+            pk.msm(MSM_A | MSM_B_G2 | MSM_B_G1 | MSM_L, self.blob.data_ptr())
+            for w in works:
+                w.wait()
+            torch.cuda.current_stream().synchronize()
+            pk.h(*[c.data_ptr() for c in self.chains])
+            pk.msm(MSM_H, self.blob.data_ptr())
+        else:
+            pk.prove_shard(primary_input, auxiliary_input, self.blob.data_ptr())
+        if pk.world > 1:
+            dist.all_gather_into_tensor(self.gathered, self.blob)
+            src = self.gathered
+        else:
+            src = self.blob
+        if pk.rank == 0 or fold_on_all_ranks:
+            return pk.assemble(r, s, src.cpu().numpy())
+        torch.cuda.current_stream().synchronize()
+        return None
 
 
 class DeviceBuffer:

@@ -11,6 +11,7 @@
 // The five MSMs and the witness map run on the GPU; the closing handful of group operations and
 // four scalar multiplications of single points run on the host (as in the reference, and for the
 // same reason as host_fold.hpp: a serial chain on one point).
+#include <algorithm>
 #include <chrono>
 #include <cstring>
 #include <map>
@@ -18,6 +19,8 @@
 #include <vector>
 
 #include "curves.cuh"
+#include "host_fold.hpp"
+#include "msm_geometry.hpp"
 #include "msm.cuh"
 #include "runtime.hpp"
 
@@ -35,7 +38,49 @@ struct ProvingKey {
     void *d_B_idx = nullptr; // device copy of B_query.indices when the query is sparse
     void *d_w = nullptr, *d_h = nullptr, *d_g = nullptr;
     void *h_w = nullptr; // pinned staging for (1 | primary | auxiliary)
+    // sharded keys (b200_groth16_pk_create_shard): this rank's slice [first, first + count) of each
+    // query, in the order A, B, H, L; tot = the whole query's size
+    int rank = 0, world = 1;
+    size_t tot[4] = {0, 0, 0, 0}, first[4] = {0, 0, 0, 0}, cnt[4] = {0, 0, 0, 0};
 };
+
+// The five MSMs of the prover in blob order, and the query (A, B, H, L) each one reads.
+constexpr int NUM_MSM = 5;
+constexpr int MSM_QUERY[NUM_MSM] = {0, 1, 1, 2, 3};
+constexpr int MSM_GROUP[NUM_MSM] = {B200_G1, B200_G2, B200_G1, B200_G1, B200_G1};
+
+void shard_range(size_t total, int world, int rank, size_t *first, size_t *count)
+{
+    const size_t per = (total + (size_t)world - 1) / (size_t)world;
+    const size_t f = std::min(total, per * (size_t)rank);
+    *first = f;
+    *count = std::min(per, total - f);
+}
+
+// Where each MSM's window sums sit inside one rank's blob. Every rank's blob has the same size (the
+// ranks all-gather them): a slot holds the largest window count any rank's shard of that query has.
+struct BlobLayout {
+    size_t off[NUM_MSM], total;
+};
+BlobLayout blob_layout(int curve, const size_t tot[4], int world)
+{
+    BlobLayout L;
+    size_t at = 0;
+    for (int k = 0; k < NUM_MSM; ++k) {
+        int wmax = 0;
+        for (int g = 0; g < world; ++g) {
+            size_t f, c;
+            shard_range(tot[MSM_QUERY[k]], world, g, &f, &c);
+            if (c) {
+                wmax = std::max(wmax, b200_msm_num_windows(curve, c));
+            }
+        }
+        L.off[k] = at;
+        at += (size_t)wmax * b200_msm_window_bytes(curve, MSM_GROUP[k]);
+    }
+    L.total = at ? at : 16;
+    return L;
+}
 
 std::mutex g_mu;
 std::map<uint64_t, ProvingKey> g_keys;
@@ -72,8 +117,12 @@ template<class Fr, class F> XYZZ<F> scalar_mul(const Fr &k_mont, const XYZZ<F> &
     return acc;
 }
 
+struct KeyPoints {
+    const void *alpha_g1, *beta_g1, *beta_g2, *delta_g1, *delta_g2;
+};
+
 template<int CURVE>
-int assemble(const ProvingKey &pk, const void *r_, const void *s_, const void *At, const void *Bg2, const void *Bg1,
+int assemble(const KeyPoints &pk, const void *r_, const void *s_, const void *At, const void *Bg2, const void *Bg1,
              const void *Ht, const void *Lt, void *proof_out)
 {
     typedef typename group_traits<CURVE, GROUP_G1>::Fr Fr;
@@ -82,18 +131,18 @@ int assemble(const ProvingKey &pk, const void *r_, const void *s_, const void *A
     Fr r, s;
     memcpy(&r, r_, sizeof(Fr));
     memcpy(&s, s_, sizeof(Fr));
-    const XYZZ<F1> delta1 = load_ref<F1>(pk.delta_g1.data());
-    const XYZZ<F2> delta2 = load_ref<F2>(pk.delta_g2.data());
+    const XYZZ<F1> delta1 = load_ref<F1>(pk.delta_g1);
+    const XYZZ<F2> delta2 = load_ref<F2>(pk.delta_g2);
 
-    XYZZ<F1> gA = load_ref<F1>(pk.alpha_g1.data());
+    XYZZ<F1> gA = load_ref<F1>(pk.alpha_g1);
     add(gA, load_ref<F1>(At));
     add(gA, scalar_mul<Fr, F1>(r, delta1));
 
-    XYZZ<F1> gB1 = load_ref<F1>(pk.beta_g1.data());
+    XYZZ<F1> gB1 = load_ref<F1>(pk.beta_g1);
     add(gB1, load_ref<F1>(Bg1));
     add(gB1, scalar_mul<Fr, F1>(s, delta1));
 
-    XYZZ<F2> gB2 = load_ref<F2>(pk.beta_g2.data());
+    XYZZ<F2> gB2 = load_ref<F2>(pk.beta_g2);
     add(gB2, load_ref<F2>(Bg2));
     add(gB2, scalar_mul<Fr, F2>(s, delta2));
 
@@ -109,6 +158,133 @@ int assemble(const ProvingKey &pk, const void *r_, const void *s_, const void *A
     memcpy(o, &oA, sizeof(oA));
     memcpy(o + sizeof(oA), &oB, sizeof(oB));
     memcpy(o + sizeof(oA) + sizeof(oB), &oC, sizeof(oC));
+    return B200_OK;
+}
+
+// Sum over the shards of one query: every rank's W window sums are folded by Horner's rule
+// (host_fold.hpp); consecutive shards with the same window geometry share one fold.
+template<int CURVE, int GROUP>
+void fold_shards(size_t total, int world, const uint8_t *blobs, size_t blob_stride, size_t slot_off, void *out)
+{
+    typedef typename group_traits<CURVE, GROUP>::F F;
+    typedef typename group_traits<CURVE, GROUP>::Fr Fr;
+    XYZZ<F> sum = XYZZ<F>::inf();
+    std::vector<XYZZ<F>> run;
+    int run_W = 0, run_c = 0;
+    size_t run_shards = 0;
+    auto flush = [&]() {
+        if (run_shards) {
+            const msm::RefPoint<F> r = msm::host_fold<F>(run.data(), run_W, run_c, run_shards);
+            add(sum, load_ref<F>(&r));
+            run.clear();
+            run_shards = 0;
+        }
+    };
+    for (int g = 0; g < world; ++g) {
+        size_t first, cnt;
+        shard_range(total, world, g, &first, &cnt);
+        if (!cnt) {
+            continue;
+        }
+        const msm::Geometry geo = msm::make_geometry(cnt, Fr::params::BITS);
+        if (run_shards && (geo.W != run_W || geo.c != run_c)) {
+            flush();
+        }
+        run_W = geo.W;
+        run_c = geo.c;
+        const size_t at = run.size();
+        run.resize(at + (size_t)geo.W);
+        memcpy(run.data() + at, blobs + (size_t)g * blob_stride + slot_off, (size_t)geo.W * sizeof(XYZZ<F>));
+        ++run_shards;
+    }
+    flush();
+    const msm::RefPoint<F> r = msm::normalise(sum);
+    memcpy(out, &r, sizeof(r));
+}
+
+template<int CURVE>
+int assemble_shards(const KeyPoints &kp, const size_t tot[4], int world, const void *blobs_, const void *r, const void *s,
+                    void *proof_out)
+{
+    typedef typename group_traits<CURVE, GROUP_G1>::F F1;
+    typedef typename group_traits<CURVE, GROUP_G2>::F F2;
+    const BlobLayout L = blob_layout(CURVE, tot, world);
+    const uint8_t *blobs = static_cast<const uint8_t *>(blobs_);
+    msm::RefPoint<F1> At, Bg1, Ht, Lt;
+    msm::RefPoint<F2> Bg2;
+    fold_shards<CURVE, GROUP_G1>(tot[0], world, blobs, L.total, L.off[0], &At);
+    fold_shards<CURVE, GROUP_G2>(tot[1], world, blobs, L.total, L.off[1], &Bg2);
+    fold_shards<CURVE, GROUP_G1>(tot[1], world, blobs, L.total, L.off[2], &Bg1);
+    fold_shards<CURVE, GROUP_G1>(tot[2], world, blobs, L.total, L.off[3], &Ht);
+    fold_shards<CURVE, GROUP_G1>(tot[3], world, blobs, L.total, L.off[4], &Lt);
+    return assemble<CURVE>(kp, r, s, &At, &Bg2, &Bg1, &Ht, &Lt, proof_out);
+}
+
+ProvingKey *find_key(b200_groth16_pk_t handle)
+{
+    auto it = g_keys.find(handle);
+    if (it == g_keys.end()) {
+        rt::set_error(B200_ERR_HANDLE, "unknown proving-key handle %llu", (unsigned long long)handle);
+        return nullptr;
+    }
+    return &it->second;
+}
+
+// (1 | primary | auxiliary) into the pinned staging buffer and on to the device, r1cs_gg_ppzksnark.tcc:525-529
+int upload_witness(const ProvingKey &pk, const void *primary_input, const void *auxiliary_input)
+{
+    const size_t fr = b200_sizeof_fr(pk.curve);
+    uint8_t *w = static_cast<uint8_t *>(pk.h_w);
+    uint32_t one[32];
+    for (int i = 0; i < (int)(fr / 4); ++i) {
+        one[i] = pk.curve == B200_ALT_BN128   ? alt_bn128_fr::params::one(i)
+                 : pk.curve == B200_BLS12_377 ? bls12_377_fr::params::one(i)
+                                              : bw6_761_fr::params::one(i);
+    }
+    memcpy(w, one, fr);
+    memcpy(w + fr, primary_input, pk.ni * fr);
+    memcpy(w + (1 + pk.ni) * fr, auxiliary_input, (pk.nv - pk.ni) * fr);
+    return b200_memcpy_h2d(pk.d_w, w, (pk.nv + 1) * fr);
+}
+
+// The MSMs of this rank's shards selected by `mask` (bit k = MSM k in blob order A, B.g2, B.g1, H, L).
+int shard_msms(const ProvingKey &pk, unsigned mask, void *dev_blob, double *ms5)
+{
+    const size_t fr = b200_sizeof_fr(pk.curve);
+    const BlobLayout L = blob_layout(pk.curve, pk.tot, pk.world);
+    const b200_bases_t sets[NUM_MSM] = {pk.A, pk.B_g2, pk.B_g1, pk.H, pk.L};
+    const uint8_t *w = static_cast<const uint8_t *>(pk.d_w);
+    const void *scB = w + pk.first[1] * fr;
+    bool gathered = false;
+    for (int k = 0; k < NUM_MSM; ++k) {
+        const size_t cnt = pk.cnt[MSM_QUERY[k]];
+        if (!(mask >> k & 1u) || !cnt) {
+            continue;
+        }
+        const double t0 = now_ms();
+        const void *sc = nullptr;
+        switch (k) {
+        case 0: sc = w + pk.first[0] * fr; break;
+        case 1:
+        case 2:
+            if (pk.d_B_idx && !gathered) {
+                if (int rc = b200_gather_dev(pk.curve, pk.d_w, static_cast<const uint32_t *>(pk.d_B_idx), cnt, pk.d_g)) {
+                    return rc;
+                }
+                gathered = true;
+            }
+            sc = pk.d_B_idx ? pk.d_g : scB;
+            break;
+        case 3: sc = static_cast<const uint8_t *>(pk.d_h) + pk.first[2] * fr; break;
+        default: sc = w + (pk.ni + 1 + pk.first[3]) * fr; break;
+        }
+        if (int rc = b200_msm_resident_windows_dev(sets[k], 0, cnt, sc, 1, static_cast<uint8_t *>(dev_blob) + L.off[k])) {
+            return rc;
+        }
+        if (ms5) {
+            ms5[k] += now_ms() - t0;
+        }
+    }
     return B200_OK;
 }
 
@@ -228,21 +404,8 @@ int b200_groth16_prove(b200_groth16_pk_t handle, const void *primary_input, cons
     double t0 = now_ms(), t = t0, t1;
     double st[7] = {0, 0, 0, 0, 0, 0, 0};
 
-    // (1 | primary | auxiliary), r1cs_gg_ppzksnark.tcc:525-529
-    uint8_t *w = static_cast<uint8_t *>(pk.h_w);
-    {
-        uint32_t one[32];
-        for (int i = 0; i < (int)(fr / 4); ++i) {
-            one[i] = pk.curve == B200_ALT_BN128   ? alt_bn128_fr::params::one(i)
-                     : pk.curve == B200_BLS12_377 ? bls12_377_fr::params::one(i)
-                                                  : bw6_761_fr::params::one(i);
-        }
-        memcpy(w, one, fr);
-        memcpy(w + fr, primary_input, pk.ni * fr);
-        memcpy(w + (1 + pk.ni) * fr, auxiliary_input, (pk.nv - pk.ni) * fr);
-    }
     int rc;
-    if ((rc = b200_memcpy_h2d(pk.d_w, w, (pk.nv + 1) * fr))) {
+    if ((rc = upload_witness(pk, primary_input, auxiliary_input))) {
         return rc;
     }
     t1 = now_ms(), st[0] = t1 - t, t = t1;
@@ -278,15 +441,16 @@ int b200_groth16_prove(b200_groth16_pk_t handle, const void *primary_input, cons
     }
     t1 = now_ms(), st[5] = t1 - t, t = t1;
 
+    const KeyPoints kp = {pk.alpha_g1.data(), pk.beta_g1.data(), pk.beta_g2.data(), pk.delta_g1.data(), pk.delta_g2.data()};
     switch (pk.curve) {
     case B200_ALT_BN128:
-        rc = assemble<CURVE_ALT_BN128>(pk, r, s, At.data(), Bg2.data(), Bg1.data(), Ht.data(), Lt.data(), proof_out);
+        rc = assemble<CURVE_ALT_BN128>(kp, r, s, At.data(), Bg2.data(), Bg1.data(), Ht.data(), Lt.data(), proof_out);
         break;
     case B200_BLS12_377:
-        rc = assemble<CURVE_BLS12_377>(pk, r, s, At.data(), Bg2.data(), Bg1.data(), Ht.data(), Lt.data(), proof_out);
+        rc = assemble<CURVE_BLS12_377>(kp, r, s, At.data(), Bg2.data(), Bg1.data(), Ht.data(), Lt.data(), proof_out);
         break;
     default:
-        rc = assemble<CURVE_BW6_761>(pk, r, s, At.data(), Bg2.data(), Bg1.data(), Ht.data(), Lt.data(), proof_out);
+        rc = assemble<CURVE_BW6_761>(kp, r, s, At.data(), Bg2.data(), Bg1.data(), Ht.data(), Lt.data(), proof_out);
         break;
     }
     st[6] = now_ms() - t0;
@@ -295,6 +459,216 @@ int b200_groth16_prove(b200_groth16_pk_t handle, const void *primary_input, cons
         memcpy(stage_ms, st, sizeof(st));
     }
     return rc;
+}
+
+/* ---- sharded prover: one process per GPU, every query cut by base range ---------- */
+
+void b200_shard_range(size_t total, int world, int rank, size_t *first, size_t *count)
+{
+    size_t f = 0, c = 0;
+    if (world > 0 && rank >= 0 && rank < world) {
+        shard_range(total, world, rank, &f, &c);
+    }
+    if (first) {
+        *first = f;
+    }
+    if (count) {
+        *count = c;
+    }
+}
+
+size_t b200_groth16_shard_bytes(int curve, const size_t query_sizes[4], int world)
+{
+    if (!query_sizes || world < 1 || !b200_sizeof_fr(curve)) {
+        return 0;
+    }
+    return blob_layout(curve, query_sizes, world).total;
+}
+
+int b200_groth16_pk_create_shard(int curve, const void *alpha_g1, const void *beta_g1, const void *beta_g2,
+                                 const void *delta_g1, const void *delta_g2, b200_bases_t A_shard,
+                                 b200_bases_t B_g2_shard, b200_bases_t B_g1_shard, const uint32_t *B_indices_shard,
+                                 size_t B_total, b200_bases_t H_shard, b200_bases_t L_shard, b200_r1cs_t r1cs,
+                                 size_t num_constraints, size_t num_inputs, size_t num_variables, size_t domain_size,
+                                 int rank, int world, b200_groth16_pk_t *handle)
+{
+    if (!alpha_g1 || !beta_g1 || !beta_g2 || !delta_g1 || !delta_g2 || !handle) {
+        return rt::set_error(B200_ERR_ARG, "null pointer");
+    }
+    const size_t g1 = b200_sizeof_group(curve, B200_G1), g2 = b200_sizeof_group(curve, B200_G2);
+    if (!g1 || !g2) {
+        return rt::set_error(B200_ERR_ARG, "unknown curve %d", curve);
+    }
+    if (world < 1 || rank < 0 || rank >= world) {
+        return rt::set_error(B200_ERR_ARG, "rank %d outside a world of %d", rank, world);
+    }
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    const size_t nv = num_variables, ni = num_inputs, m = domain_size;
+    if (ni > nv || m < num_constraints + ni + 1 || B_total > nv + 1 || (!B_indices_shard && B_total != nv + 1)) {
+        return rt::set_error(B200_ERR_ARG, "sizes do not describe a proving key (r1cs_gg_ppzksnark.tcc:506-511)");
+    }
+    ProvingKey pk;
+    pk.curve = curve;
+    pk.alpha_g1.assign((const uint8_t *)alpha_g1, (const uint8_t *)alpha_g1 + g1);
+    pk.beta_g1.assign((const uint8_t *)beta_g1, (const uint8_t *)beta_g1 + g1);
+    pk.beta_g2.assign((const uint8_t *)beta_g2, (const uint8_t *)beta_g2 + g2);
+    pk.delta_g1.assign((const uint8_t *)delta_g1, (const uint8_t *)delta_g1 + g1);
+    pk.delta_g2.assign((const uint8_t *)delta_g2, (const uint8_t *)delta_g2 + g2);
+    pk.A = A_shard;
+    pk.B_g2 = B_g2_shard;
+    pk.B_g1 = B_g1_shard;
+    pk.H = H_shard;
+    pk.L = L_shard;
+    pk.r1cs = r1cs;
+    pk.nc = num_constraints;
+    pk.ni = ni;
+    pk.nv = nv;
+    pk.m = m;
+    pk.rank = rank;
+    pk.world = world;
+    pk.tot[0] = nv + 1;
+    pk.tot[1] = B_total;
+    pk.tot[2] = m - 1;
+    pk.tot[3] = nv - ni;
+    for (int q = 0; q < 4; ++q) {
+        shard_range(pk.tot[q], world, rank, &pk.first[q], &pk.cnt[q]);
+    }
+    pk.nB = pk.cnt[1];
+    if (b200_bases_size(A_shard) != pk.cnt[0] || b200_bases_size(B_g2_shard) != pk.cnt[1] ||
+        b200_bases_size(B_g1_shard) != pk.cnt[1] || b200_bases_size(H_shard) != pk.cnt[2] ||
+        b200_bases_size(L_shard) != pk.cnt[3]) {
+        return rt::set_error(B200_ERR_ARG, "a query shard does not hold b200_shard_range(total, world = %d, rank = %d) points",
+                             world, rank);
+    }
+    const size_t fr = b200_sizeof_fr(curve);
+    if (B_indices_shard) {
+        for (size_t k = 0; k < pk.cnt[1]; ++k) {
+            if (B_indices_shard[k] > nv || (k && B_indices_shard[k] <= B_indices_shard[k - 1])) {
+                return rt::set_error(B200_ERR_ARG, "B_indices must be increasing and <= num_variables");
+            }
+        }
+    }
+    int rc = B200_OK;
+    if ((rc = b200_dev_alloc((nv + 1) * fr, &pk.d_w)) || (rc = b200_dev_alloc((m + 1) * fr, &pk.d_h))) {
+        return rc;
+    }
+    if (B_indices_shard && pk.cnt[1]) {
+        if ((rc = b200_dev_alloc(pk.cnt[1] * 4, &pk.d_B_idx)) ||
+            (rc = b200_memcpy_h2d(pk.d_B_idx, B_indices_shard, pk.cnt[1] * 4)) ||
+            (rc = b200_dev_alloc(pk.cnt[1] * fr, &pk.d_g))) {
+            return rc;
+        }
+    }
+    B200_CUDA_CHECK(cudaHostAlloc(&pk.h_w, (nv + 1) * fr, cudaHostAllocDefault));
+    std::lock_guard<std::mutex> lk(g_mu);
+    *handle = g_next++;
+    g_keys[*handle] = pk;
+    return B200_OK;
+}
+
+int b200_groth16_shard_begin(b200_groth16_pk_t handle, const void *primary_input, const void *auxiliary_input)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    const ProvingKey *pk = find_key(handle);
+    if (!pk) {
+        return B200_ERR_HANDLE;
+    }
+    if (!auxiliary_input || (pk->ni && !primary_input)) {
+        return rt::set_error(B200_ERR_ARG, "null input");
+    }
+    return upload_witness(*pk, primary_input, auxiliary_input);
+}
+
+int b200_groth16_shard_chain(b200_groth16_pk_t handle, int which, void *dev_out)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    const ProvingKey *pk = find_key(handle);
+    if (!pk) {
+        return B200_ERR_HANDLE;
+    }
+    return b200_witness_chain_r1cs_dev(pk->r1cs, pk->d_w, pk->m, which, dev_out);
+}
+
+int b200_groth16_shard_h(b200_groth16_pk_t handle, void *dA, const void *dB, const void *dC)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    const ProvingKey *pk = find_key(handle);
+    if (!pk) {
+        return B200_ERR_HANDLE;
+    }
+    if (!dA && !dB && !dC) {
+        return b200_witness_map_r1cs_dev(pk->r1cs, pk->d_w, pk->m, pk->d_h);
+    }
+    return b200_witness_finish_dev(pk->curve, dA, dB, dC, pk->m, pk->d_h);
+}
+
+int b200_groth16_shard_msm(b200_groth16_pk_t handle, unsigned mask, void *dev_blob)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    const ProvingKey *pk = find_key(handle);
+    if (!pk) {
+        return B200_ERR_HANDLE;
+    }
+    if (!dev_blob) {
+        return rt::set_error(B200_ERR_ARG, "null pointer");
+    }
+    return shard_msms(*pk, mask, dev_blob, nullptr);
+}
+
+int b200_groth16_prove_shard(b200_groth16_pk_t handle, const void *primary_input, const void *auxiliary_input,
+                             void *dev_blob, double *stage_ms)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    const ProvingKey *pk = find_key(handle);
+    if (!pk) {
+        return B200_ERR_HANDLE;
+    }
+    if (!auxiliary_input || !dev_blob || (pk->ni && !primary_input)) {
+        return rt::set_error(B200_ERR_ARG, "null pointer");
+    }
+    double st[7] = {0, 0, 0, 0, 0, 0, 0}, msm[NUM_MSM] = {0, 0, 0, 0, 0};
+    const double t0 = now_ms();
+    int rc = upload_witness(*pk, primary_input, auxiliary_input);
+    if (rc) {
+        return rc;
+    }
+    double t1 = now_ms();
+    st[0] = t1 - t0;
+    if ((rc = b200_witness_map_r1cs_dev(pk->r1cs, pk->d_w, pk->m, pk->d_h))) {
+        return rc;
+    }
+    st[1] = now_ms() - t1;
+    if ((rc = shard_msms(*pk, 0x1f, dev_blob, msm))) {
+        return rc;
+    }
+    st[2] = msm[0];
+    st[3] = msm[1] + msm[2];
+    st[4] = msm[3];
+    st[5] = msm[4];
+    st[6] = now_ms() - t0;
+    if (stage_ms) {
+        memcpy(stage_ms, st, sizeof(st));
+    }
+    return B200_OK;
+}
+
+int b200_groth16_assemble(int curve, const void *alpha_g1, const void *beta_g1, const void *beta_g2,
+                          const void *delta_g1, const void *delta_g2, const size_t query_sizes[4], int world,
+                          const void *blobs, const void *r, const void *s, void *proof_out)
+{
+    if (!alpha_g1 || !beta_g1 || !beta_g2 || !delta_g1 || !delta_g2 || !query_sizes || !blobs || !r || !s || !proof_out ||
+        world < 1) {
+        return rt::set_error(B200_ERR_ARG, "null pointer or empty world");
+    }
+    const KeyPoints kp = {alpha_g1, beta_g1, beta_g2, delta_g1, delta_g2};
+    switch (curve) {
+    case B200_ALT_BN128: return assemble_shards<CURVE_ALT_BN128>(kp, query_sizes, world, blobs, r, s, proof_out);
+    case B200_BLS12_377: return assemble_shards<CURVE_BLS12_377>(kp, query_sizes, world, blobs, r, s, proof_out);
+    case B200_BW6_761: return assemble_shards<CURVE_BW6_761>(kp, query_sizes, world, blobs, r, s, proof_out);
+    default: return rt::set_error(B200_ERR_ARG, "unknown curve %d", curve);
+    }
 }
 
 } // extern "C"

@@ -296,57 +296,81 @@ template<class Fr> int divide_by_z(void *data, size_t m)
     return B200_OK;
 }
 
+// The basic radix-2 domain of size m with g = FieldT::multiplicative_generator (r1cs_to_qap.tcc:273).
+template<class Fr> int witness_domain(size_t m, Domain<Fr> **d)
+{
+    const int lgn = log2_exact(m);
+    if (lgn < 0 || lgn > Fr::params::S) {
+        return rt::set_error(B200_ERR_DOMAIN, "basic_radix2_domain: bad size %zu", m);
+    }
+    uint32_t gen[Fr::N];
+    for (int i = 0; i < Fr::N; ++i) {
+        gen[i] = Fr::params::generator(i);
+    }
+    if (int rc = get_domain<Fr>(lgn, gen, d)) {
+        return rc;
+    }
+    return g_bufS.reserve(m * sizeof(Fr)) ? B200_ERR_CUDA : B200_OK;
+}
+
+// One of the three chains of r1cs_to_qap.tcc:252-290: iFFT then cosetFFT, in place on X (m elements).
+// The 1/m of the inverse and the g^i of the coset are one table multiplication fused into the
+// inverse's last pass. With an odd pass count the inverse lands in S and the forward transform
+// brings it back: no device copies.
+template<class Fr> int witness_chain(Domain<Fr> &d, Fr *X)
+{
+    const Fr *gpow_minv = nullptr;
+    if (int rc = coset_table(d, T_GPOW_MINV, &gpow_minv)) {
+        return rc;
+    }
+    Fr *S = g_bufS.as<Fr>();
+    const bool odd = ((d.lgn + MAX_DEG - 1) / MAX_DEG) & 1;
+    Fr *mid = odd ? S : X, *other = odd ? X : S;
+    if (int rc = run_transform<Fr>(d, 1, X, S, mid, nullptr, gpow_minv, nullptr)) {
+        return rc;
+    }
+    return run_transform<Fr>(d, 0, mid, other, X, nullptr, nullptr, nullptr);
+}
+
+// r1cs_to_qap.tcc:293-330: (A*B - C) / Z on the coset, icosetFFT, coefficients_for_H[m] = 0. dA clobbered.
+template<class Fr> int witness_finish(Domain<Fr> &d, size_t m, Fr *dA, const Fr *dB, const Fr *dC, Fr *dH)
+{
+    const Fr *ginv_minv = nullptr;
+    if (int rc = coset_table(d, T_GINV_MINV, &ginv_minv)) {
+        return rc;
+    }
+    cudaStream_t s = rt::stream();
+    ntt::k_pointwise_h<Fr><<<grid_for(m, 256), 256, 0, s>>>(m, dA, dB, dC, d.c(4), dA);
+    B200_LAUNCH_CHECK();
+    if (int rc = run_transform<Fr>(d, 1, dA, g_bufS.as<Fr>(), dH, nullptr, ginv_minv, nullptr)) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaMemsetAsync(dH + m, 0, sizeof(Fr), s));
+    return B200_OK;
+}
+
 // r1cs_to_qap.tcc:252-330 with d1 = d2 = d3 = 0. dA, dB, dC clobbered; dH gets m + 1 elements.
 template<class Fr> int witness_map_dev(Fr *dA, Fr *dB, Fr *dC, size_t m, Fr *dH)
 {
-    const int lgn = log2_exact(m);
-    if (lgn < 0) {
+    if (log2_exact(m) < 0) {
         bool handled = false;
         const int rc = step_witness_map_try<Fr>(dA, dB, dC, m, dH, &handled);
         if (handled) {
             return rc;
         }
     }
-    if (lgn < 0 || lgn > Fr::params::S) {
-        return rt::set_error(B200_ERR_DOMAIN, "basic_radix2_domain: bad size %zu", m);
-    }
-    uint32_t gen[Fr::N];
-    for (int i = 0; i < Fr::N; ++i) {
-        gen[i] = Fr::params::generator(i); // g = FieldT::multiplicative_generator (r1cs_to_qap.tcc:273)
-    }
     Domain<Fr> *d = nullptr;
-    int rc = get_domain<Fr>(lgn, gen, &d);
+    int rc = witness_domain<Fr>(m, &d);
     if (rc) {
         return rc;
     }
-    if (g_bufS.reserve(m * sizeof(Fr))) {
-        return B200_ERR_CUDA;
-    }
-    Fr *S = g_bufS.as<Fr>();
-    const Fr *gpow_minv = nullptr, *ginv_minv = nullptr;
-    if ((rc = coset_table(*d, T_GPOW_MINV, &gpow_minv)) || (rc = coset_table(*d, T_GINV_MINV, &ginv_minv))) {
-        return rc;
-    }
-    cudaStream_t s = rt::stream();
     Fr *vecs[3] = {dA, dB, dC};
-    const bool odd = ((lgn + MAX_DEG - 1) / MAX_DEG) & 1;
     for (int v = 0; v < 3; ++v) {
-        // iFFT then cosetFFT: the 1/m of the inverse and the g^i of the coset are one table
-        // multiplication fused into the inverse's last pass. With an odd pass count the
-        // inverse lands in S and the forward transform brings it back: no device copies.
-        Fr *X = vecs[v], *mid = odd ? S : X, *other = odd ? X : S;
-        if ((rc = run_transform<Fr>(*d, 1, X, S, mid, nullptr, gpow_minv, nullptr)) ||
-            (rc = run_transform<Fr>(*d, 0, mid, other, X, nullptr, nullptr, nullptr))) {
+        if ((rc = witness_chain<Fr>(*d, vecs[v]))) {
             return rc;
         }
     }
-    ntt::k_pointwise_h<Fr><<<grid_for(m, 256), 256, 0, s>>>(m, dA, dB, dC, d->c(4), dA);
-    B200_LAUNCH_CHECK();
-    if ((rc = run_transform<Fr>(*d, 1, dA, S, dH, nullptr, ginv_minv, nullptr))) {
-        return rc;
-    }
-    B200_CUDA_CHECK(cudaMemsetAsync(dH + m, 0, sizeof(Fr), s)); // coefficients_for_H[m] = 0
-    return B200_OK;
+    return witness_finish<Fr>(*d, m, dA, dB, dC, dH);
 }
 
 template<class Fr> int witness_map_host(const void *aA, const void *aB, const void *aC, size_t m, void *out_H)
@@ -826,6 +850,48 @@ template<class Fr> int gather_dev(const void *d_src, const uint32_t *d_idx, size
     return B200_OK;
 }
 
+// One chain of the witness map on its own (multi-GPU: the A, B and C chains run on different GPUs,
+// SURVEY.md §8e): evaluations of the constraint rows from d_w, iFFT, cosetFFT -> d_out (m elements).
+template<class Fr> int witness_chain_r1cs_dev(const R1csSet &r, const void *d_w, size_t m, int which, void *d_out)
+{
+    if (m < r.nc + r.ni + 1) {
+        return rt::set_error(B200_ERR_DOMAIN, "domain size %zu < num_constraints + num_inputs + 1 = %zu", m,
+                             r.nc + r.ni + 1);
+    }
+    Domain<Fr> *d = nullptr;
+    if (int rc = witness_domain<Fr>(m, &d)) {
+        return rc;
+    }
+    const size_t bytes = m * sizeof(Fr);
+    if (g_bufA.reserve(bytes) || g_bufB.reserve(bytes) || g_bufC.reserve(bytes)) {
+        return B200_ERR_CUDA;
+    }
+    if (int rc = r1cs_eval_launch<Fr>(r, static_cast<const Fr *>(d_w), m, g_bufA.as<Fr>(), g_bufB.as<Fr>(), g_bufC.as<Fr>())) {
+        return rc;
+    }
+    Fr *X = which == 0 ? g_bufA.as<Fr>() : which == 1 ? g_bufB.as<Fr>() : g_bufC.as<Fr>();
+    if (int rc = witness_chain<Fr>(*d, X)) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaMemcpyAsync(d_out, X, bytes, cudaMemcpyDeviceToDevice, rt::stream()));
+    B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
+    return B200_OK;
+}
+
+template<class Fr> int witness_finish_dev(void *dA, const void *dB, const void *dC, size_t m, void *dH)
+{
+    Domain<Fr> *d = nullptr;
+    if (int rc = witness_domain<Fr>(m, &d)) {
+        return rc;
+    }
+    if (int rc = witness_finish<Fr>(*d, m, static_cast<Fr *>(dA), static_cast<const Fr *>(dB), static_cast<const Fr *>(dC),
+                                    static_cast<Fr *>(dH))) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
+    return B200_OK;
+}
+
 #define DISPATCH_FR(curve, call)                                                                   \
     switch (curve) {                                                                               \
     case B200_ALT_BN128: {                                                                         \
@@ -1022,6 +1088,32 @@ int b200_witness_map_r1cs_dev(b200_r1cs_t handle, const void *d_w, size_t m, voi
     }
     B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
     return B200_OK;
+}
+
+int b200_witness_chain_r1cs_dev(b200_r1cs_t handle, const void *d_w, size_t m, int which, void *d_out)
+{
+    if (!d_w || !d_out || which < 0 || which > 2) {
+        return rt::set_error(B200_ERR_ARG, "null pointer or chain index outside 0..2");
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_r1cs.find(handle);
+    if (it == g_r1cs.end()) {
+        return rt::set_error(B200_ERR_HANDLE, "unknown R1CS handle %llu", (unsigned long long)handle);
+    }
+    const R1csSet &r = it->second;
+    DISPATCH_FR(r.curve, witness_chain_r1cs_dev<Fr>(r, d_w, m, which, d_out));
+}
+
+int b200_witness_finish_dev(int curve, void *dA, const void *dB, const void *dC, size_t m, void *dH)
+{
+    if (!dA || !dB || !dC || !dH) {
+        return rt::set_error(B200_ERR_ARG, "null pointer");
+    }
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    DISPATCH_FR(curve, witness_finish_dev<Fr>(dA, dB, dC, m, dH));
 }
 
 int b200_gather_dev(int curve, const void *d_src, const uint32_t *d_idx, size_t n, void *d_dst)

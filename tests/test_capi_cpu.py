@@ -135,6 +135,126 @@ def test_sharded_fold_gloo_world2(b, tmp_path):
     assert np.array_equal(np.load(out), want)
 
 
+# ---- sharded prover: host logic (b200_shard_range, blob layout, b200_groth16_assemble) -----------------
+
+QUERY_SIZES = [2001, 1900, 2047, 1991]          # A, B, H, L totals of a pretend key (alt_bn128)
+
+
+def _fake_blob(b, world, rank):
+    """One rank's blob: window sums of its five pretend partial MSMs = distinct affine golden points
+    (X | Y | ZZ = ZZZ = one). Returns (blob bytes, {msm k: affine points in the reference layout})."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "msm.npz"))
+    g1, g2 = g["rand.alt_bn128.g1.bases"], g["rand.alt_bn128.g2.bases"]
+    L = b.lib()
+    blob = np.zeros(b.groth16_shard_bytes("alt_bn128", QUERY_SIZES, world), dtype=np.uint8)
+    pts, at = {}, 0
+    for k, (q, grp) in enumerate(zip([0, 1, 1, 2, 3], [1, 2, 1, 1, 1])):
+        wmax = max(L.b200_msm_num_windows(0, b.shard_range(QUERY_SIZES[q], world, r)[1]) for r in range(world))
+        W = L.b200_msm_num_windows(0, b.shard_range(QUERY_SIZES[q], world, rank)[1])
+        src = g1 if grp == 1 else g2
+        fl = 4 if grp == 1 else 8                  # u64 limbs per coordinate
+        p = src[(rank * 5 + k) * 3:(rank * 5 + k) * 3 + W] if W <= 3 else np.resize(src[(rank * 5 + k):], (W, src.shape[1]))
+        one = p[:, 2 * fl:3 * fl]
+        win = np.ascontiguousarray(np.concatenate([p[:, :2 * fl], one, one], axis=1))
+        blob[at:at + win.nbytes] = win.view(np.uint8).reshape(-1)
+        at += wmax * L.b200_msm_window_bytes(0, grp)
+        pts[k] = p
+    assert at == blob.shape[0]
+    return blob, pts
+
+
+def _expected_proof(b, P, world, all_pts):
+    """alpha + A | beta + B.g2 | H + L for r = s = 0, by Horner over every rank's windows with the C oracle."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "msm.npz"))
+    L = b.lib()
+
+    def fold(k, q, grp):
+        total = None
+        for r in range(world):
+            n = b.shard_range(QUERY_SIZES[q], world, r)[1]
+            W, c = L.b200_msm_num_windows(0, n), L.b200_msm_window_bits(0, n)
+            acc = None
+            for w in range(W - 1, -1, -1):
+                if acc is not None:
+                    for _ in range(c):
+                        acc = P.group_op("alt_bn128", grp, 2, acc)
+                p = all_pts[r][k][w:w + 1]
+                acc = p if acc is None else P.group_op("alt_bn128", grp, 0, acc, p)
+            total = acc if total is None else P.group_op("alt_bn128", grp, 0, total, acc)
+        return total
+    key = _key_points(g)
+    gA = P.group_op("alt_bn128", 1, 0, key[0][None, :], fold(0, 0, 1))
+    gB = P.group_op("alt_bn128", 2, 0, key[2][None, :], fold(1, 1, 2))
+    gC = P.group_op("alt_bn128", 1, 0, fold(3, 2, 1), fold(4, 3, 1))
+    return np.concatenate([gA[0], gB[0], gC[0]])
+
+
+def _key_points(g):
+    g1, g2 = g["rand.alt_bn128.g1.bases"], g["rand.alt_bn128.g2.bases"]
+    return [g1[90], g1[91], g2[90], g1[92], g2[91]]      # alpha_g1, beta_g1, beta_g2, delta_g1, delta_g2
+
+
+def test_shard_range_covers_every_query(b):
+    for total in (0, 1, 7, 8, 9, 1000, (1 << 20) - 1):
+        for world in (1, 2, 3, 8):
+            at = 0
+            for r in range(world):
+                f, c = b.shard_range(total, world, r)
+                assert f == at
+                at += c
+            assert at == total
+
+
+def test_sharded_assemble_host(b):
+    """b200_groth16_assemble on blobs of 1, 2 and 3 pretend ranks (ragged shards, different window geometry per
+    query) against the C oracle's group law."""
+    from oracle import port
+    P = port.OraclePort()
+    g = np.load(os.path.join(ROOT, "tests", "golden", "msm.npz"))
+    zero = np.zeros(4, dtype=np.uint64)
+    for world in (1, 2, 3):
+        blobs, pts = zip(*[_fake_blob(b, world, r) for r in range(world)])
+        got = b.groth16_assemble("alt_bn128", *_key_points(g), QUERY_SIZES, world, np.concatenate(blobs), zero, zero)
+        assert np.array_equal(got, _expected_proof(b, P, world, pts)), world
+
+
+SHARD_WORKER = r'''
+import os, sys
+import numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+sys.path.insert(0, os.path.join(sys.argv[1], "tests"))
+import libsnark_b200 as b
+import test_capi_cpu as T
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+dist.init_process_group("gloo")
+blob, _ = T._fake_blob(b, world, rank)
+mine = torch.from_numpy(blob)
+gathered = torch.empty(world * mine.numel(), dtype=torch.uint8)
+dist.all_gather_into_tensor(gathered, mine)          # DistributedProver's NCCL all-gather, on gloo here
+if rank == 0:
+    g = np.load(os.path.join(sys.argv[1], "tests", "golden", "msm.npz"))
+    zero = np.zeros(4, dtype=np.uint64)
+    np.save(sys.argv[2], b.groth16_assemble("alt_bn128", *T._key_points(g), T.QUERY_SIZES, world, gathered.numpy(), zero, zero))
+dist.barrier()
+dist.destroy_process_group()
+'''
+
+
+def test_sharded_prover_gloo_world2(b, tmp_path):
+    """world_size-2 run of the sharded prover's host side: every rank's blob all-gathered, proof assembled on rank 0."""
+    script = tmp_path / "worker.py"
+    script.write_text(SHARD_WORKER)
+    out = tmp_path / "proof.npy"
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29537")
+    subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                    "--master-addr", "127.0.0.1", "--master-port", "29537", str(script), ROOT, str(out)],
+                   check=True, env=env, timeout=300)
+    from oracle import port
+    P = port.OraclePort()
+    pts = [_fake_blob(b, 2, r)[1] for r in range(2)]
+    assert np.array_equal(np.load(out), _expected_proof(b, P, 2, pts))
+
+
 def test_product_does_not_touch_the_oracle():
     """The shipped path (package + shared library) never imports, links or opens anything under oracle/."""
     import subprocess
