@@ -52,6 +52,8 @@ def parse_args():
     ap.add_argument("--ntt-log-m", type=int, default=24)
     ap.add_argument("--no-prove", action="store_true", help="skip the Groth16 prove measurement")
     ap.add_argument("--prove-log-m", type=int, default=20)
+    ap.add_argument("--no-tables", action="store_true",
+                    help="do not precompute the [2^(c w)] P rows of the resident bases (b200_bases_precompute)")
     return ap.parse_args()
 
 
@@ -199,7 +201,9 @@ def run_b200_arm(args):
     # ---- synthetic inputs: this rank's shard of the global (world * n)-point MSM ----------------
     bases = b.make_bases(CURVE, b.G1, n, k0=1 + rank * n)
     rb = b.ResidentBases(CURVE, b.G1, bases)
+    rb_plain = None if args.no_tables or world > 1 else b.ResidentBases(CURVE, b.G1, bases)   # the same key without tables
     del bases
+    table_rows = 0 if args.no_tables else rb.precompute()
     scalars = b.random_scalars(CURVE, n, seed=1234 + rank)
     pinned = torch.empty((n, 4), dtype=torch.int64, pin_memory=True)
     pinned_np = pinned.numpy().view(np.uint64)
@@ -274,6 +278,16 @@ def run_b200_arm(args):
     if rank == 0 and r0 is not None and not np.array_equal(r0, r1):
         raise SystemExit("bench.py: resident and e2e paths disagree")
 
+    plain = None
+    if rb_plain is not None:
+        for _ in range(Wm):
+            rb_plain.multi_exp(None, device_ptr=dscal.ptr)
+        _, pw, pst = timed(lambda: rb_plain.multi_exp(None, device_ptr=dscal.ptr), K)
+        plain = {"value": n / (float(np.mean(pw)) * 1e-3) / 1e6, "unit": "Mpts/s", "ms_per_step": float(np.mean(pw)),
+                 "stage_ms": {k: float(np.mean([s_[k] for s_ in pst])) for k in pst[0]},
+                 "note": "the same MSM over the same resident key without b200_bases_precompute (17 windows, 17 bucket sets)"}
+        rb_plain.free()
+
     # the host fold is part of the step, so the step time is the wall clock of the synchronous call
     ms_step = float(np.mean(wall_ms))
     total_pts = world * n
@@ -287,6 +301,10 @@ def run_b200_arm(args):
         "dtype": "u32 limbs (254-bit modular)", "data": "synthetic",
         "config": {"workload": WORKLOAD, "points_per_gpu": n, "parallelism": f"base-range shards x{world}",
                    "window_bits": int(b.lib().b200_msm_window_bits(b.ALT_BN128, n)), "windows": W,
+                   "precomputed_table_rows": int(table_rows),
+                   "tables": ("b200_bases_precompute: the resident key holds [2^(c w)] P for every window w (built once at "
+                              "key upload, %d x 64 MiB), all windows share one bucket set; window_bits/windows above are "
+                              "the table-free geometry the window-sum interface keeps" % table_rows) if table_rows else "off",
                    "l2": "256 MiB buffer written between timed iterations (outside the timed span)"},
         "ms_per_step_device_events": float(np.mean(ev_ms)),
         "stage_ms": {k: float(np.mean([s[k] for s in stage])) for k in stage[0]},
@@ -297,24 +315,28 @@ def run_b200_arm(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
     }
+    if plain is not None:
+        line["without_tables"] = plain
     prove_multi_obj = None
     if world > 1 and not args.no_prove:
         # the whole prover sharded over the ranks (strong scaling of the fixed 2^20 problem); all ranks take part
         sys.path.insert(0, os.path.join(ROOT, "tools"))
         import prove_multi
         prove_multi_obj = prove_multi.run(b, torch, dist, CURVE, args.prove_log_m, max(3, min(args.steps, 10)),
-                                          max(3, args.warmup))
+                                          max(3, args.warmup), tables=not args.no_tables)
     if rank == 0:
         wide, lo, _ = b.imad_peak()
         c = line["config"]["window_bits"]
-        imads = 11 * W * n * 136  # bucket accumulation only: W*N mixed adds x 11 modmuls x MM(8)
+        # bucket accumulation only: (windows actually accumulated) * N mixed adds x 11 modmuls x MM(8)
+        W_acc = table_rows if table_rows else W
+        imads = 11 * W_acc * n * 136
         ach = imads / (acc_ms * 1e-3)
         line["roofline"] = {
             "bound": "int-pipe", "kernel": "k_accumulate", "achieved": ach / 1e12, "peak": wide / 1e12,
             "unit": "Tmad/s (32x32+64 multiply-adds)", "frac": ach / wide,
             # dram__bytes_read.sum + dram__bytes_write.sum of one k_accumulate launch at this workload,
             # profiles/r1_ncu_full_msm.md (ncu --set full); algorithmic bytes are 68 B per mixed add
-            "traffic": 525.8e6, "algorithmic_bytes": 68.0 * W * n,
+            "traffic": 525.8e6 if not table_rows else None, "algorithmic_bytes": 68.0 * W_acc * n,
             "peak_source": "b200_imad_peak, measured in this run: chains of IMAD.WIDE.U32.X (the 32x32+64 multiply-add a "
                            "Montgomery product is made of; it holds the FMA-heavy pipe for two issue slots, 32 per clock "
                            "per SM). MEASURED_PEAKS.json has no integer figure.",
@@ -326,7 +348,8 @@ def run_b200_arm(args):
         if world == 1 and not args.no_ntt:
             line["ntt"] = bench_ntt(b, torch, args.ntt_log_m, wide)
         if world == 1 and not args.no_prove:
-            line["groth16_prove"] = bench_groth16(b, args.prove_log_m, max(3, min(args.steps, 10)), max(3, args.warmup))
+            line["groth16_prove"] = bench_groth16(b, args.prove_log_m, max(3, min(args.steps, 10)), max(3, args.warmup),
+                                                  tables=not args.no_tables)
         if prove_multi_obj is not None:
             line["groth16_prove"] = prove_multi_obj
         if world == 1 and not args.no_cpu_baseline:
@@ -343,7 +366,7 @@ def run_b200_arm(args):
         dist.destroy_process_group()
 
 
-def bench_groth16(b, log_m, steps, warmup):
+def bench_groth16(b, log_m, steps, warmup, tables=True):
     """BASELINE.json metric 'Groth16 prove ms @2^20 BN254': b200_groth16_prove (witness on the host in, proof on the host
     out) on a synthetic satisfiable R1CS of the shape of generate_r1cs_example_with_field_input with num_inputs = 10 and
     num_constraints = 2^log_m - 11, proving key = distinct device-generated points of the right
@@ -363,7 +386,8 @@ def bench_groth16(b, log_m, steps, warmup):
         k += n
     p1 = b.make_bases(CURVE, b.G1, 3, k0=k)
     p2 = b.make_bases(CURVE, b.G2, 2, k0=k + 3)
-    pk = b.Groth16ProvingKey(CURVE, p1[0], p1[1], p2[0], p1[2], p2[1], qs[0], qs[1], qs[2], None, qs[3], qs[4], cs, m)
+    pk = b.Groth16ProvingKey(CURVE, p1[0], p1[1], p2[0], p1[2], p2[1], qs[0], qs[1], qs[2], None, qs[3], qs[4], cs, m,
+                             precompute=tables)
     setup_s = time.time() - t0
     rs = b.random_scalars(CURVE, 2, seed=99)
     proof = None
@@ -384,7 +408,7 @@ def bench_groth16(b, log_m, steps, warmup):
            "sizes": {"num_constraints": sy["nc"], "num_inputs": ni, "num_variables": nv, "domain": m,
                      "r1cs_nnz": int(sy["col"].shape[0])},
            "h2d_bytes_per_step": int((nv + 1) * 32), "d2h_bytes_per_step": int(5 * 17 * 128 + 17 * 256),
-           "setup_s": setup_s,
+           "setup_s": setup_s, "precomputed_tables": bool(tables),
            "note": "wall clock around b200_groth16_prove: witness (host) -> H2D -> sparse R1CS evaluation -> 7 NTTs -> "
                    "A, B(G2+G1), H, L MSMs on device-resident scalars -> window sums D2H -> host fold and proof assembly; "
                    "proving key and constraint system resident on the device (uploaded once, outside the timed region)"}

@@ -77,6 +77,15 @@ int b200_msm(int curve, int group, const void *bases, size_t base_stride, size_t
 typedef uint64_t b200_bases_t;
 int b200_bases_upload(int curve, int group, const void *bases, size_t base_stride, size_t n,
                       b200_bases_t *handle);
+/* Optional, once per resident set: precomputes the rows [2^(c w)] P_i, w < W (affine), so that an MSM
+ * over the set scatters the digits of ALL windows into one set of 2^(c-1) buckets and pays the bucket
+ * reduction once instead of W times; c is then chosen larger (fewer windows, fewer additions). Costs W
+ * times the set's device memory (2^20 alt_bn128 G1 points: 64 MiB -> 1 GiB) and one field inversion per
+ * table entry, once. The reference's counterpart of trading memory for window work is the fixed-base
+ * window table of batch_exp (multiexp.tcc:809-946). Results are unchanged (same group element).
+ * b200_bases_table_rows: W after a successful precompute, else 0. */
+int b200_bases_precompute(b200_bases_t handle);
+int b200_bases_table_rows(b200_bases_t handle);
 int b200_bases_free(b200_bases_t handle);
 size_t b200_bases_size(b200_bases_t handle);
 

@@ -41,7 +41,7 @@ EXPORTS = [
     "b200_witness_chain_r1cs_dev", "b200_witness_finish_dev",
     "b200_shard_range", "b200_groth16_shard_bytes", "b200_groth16_pk_create_shard", "b200_groth16_prove_shard",
     "b200_groth16_shard_begin", "b200_groth16_shard_chain", "b200_groth16_shard_h", "b200_groth16_shard_msm",
-    "b200_groth16_assemble",
+    "b200_groth16_assemble", "b200_bases_precompute", "b200_bases_table_rows",
 ]
 
 
@@ -80,6 +80,8 @@ def lib():
         L.b200_msm.argtypes = [i, i, vp, sz, sz, vp, vp]
         L.b200_bases_upload.argtypes = [i, i, vp, sz, sz, C.POINTER(u64)]
         L.b200_bases_free.argtypes = [u64]
+        L.b200_bases_precompute.argtypes = [u64]
+        L.b200_bases_table_rows.argtypes = [u64]
         L.b200_bases_size.restype = sz
         L.b200_bases_size.argtypes = [u64]
         L.b200_msm_resident.argtypes = [u64, sz, sz, vp, i, vp]
@@ -220,6 +222,11 @@ class ResidentBases:
         h = C.c_uint64(0)
         _check(lib().b200_bases_upload(self.curve, group, _p(bases), stride, n, C.byref(h)))
         self.handle, self.n = h.value, n
+
+    def precompute(self):
+        """b200_bases_precompute: rows [2^(c w)] P on the device; returns the number of rows."""
+        _check(lib().b200_bases_precompute(self.handle))
+        return lib().b200_bases_table_rows(self.handle)
 
     def multi_exp(self, scalars, first=0, n=None, device_ptr=None):
         n = self.n - first if n is None else n
@@ -425,11 +432,14 @@ class Groth16ProvingKey:
     (r1cs_gg_ppzksnark.tcc:460-603) with caller-supplied r, s."""
 
     def __init__(self, curve, alpha_g1, beta_g1, beta_g2, delta_g1, delta_g2, A_query, B_query_g2, B_query_g1,
-                 B_indices, H_query, L_query, r1cs, domain_size):
+                 B_indices, H_query, L_query, r1cs, domain_size, precompute=False):
         self.curve, self.r1cs = curve, r1cs
         self.sets = [ResidentBases(curve, G1, A_query), ResidentBases(curve, G2, B_query_g2),
                      ResidentBases(curve, G1, B_query_g1), ResidentBases(curve, G1, H_query),
                      ResidentBases(curve, G1, L_query)]
+        if precompute:
+            for rb in self.sets:
+                rb.precompute()
         pts = [_u64(x) for x in (alpha_g1, beta_g1, beta_g2, delta_g1, delta_g2)]
         idx = None if B_indices is None else np.ascontiguousarray(B_indices, dtype=np.uint32)
         h = C.c_uint64(0)
@@ -494,7 +504,8 @@ class Groth16ProvingKeyShard:
     with sliced=True they already are this rank's slices and B_total = the whole B query's entry count."""
 
     def __init__(self, curve, alpha_g1, beta_g1, beta_g2, delta_g1, delta_g2, A_query, B_query_g2, B_query_g1,
-                 B_indices, H_query, L_query, r1cs, domain_size, rank, world, sliced=False, B_total=None):
+                 B_indices, H_query, L_query, r1cs, domain_size, rank, world, sliced=False, B_total=None,
+                 precompute=False):
         self.curve, self.r1cs, self.rank, self.world, self.m = curve, r1cs, rank, world, int(domain_size)
         nv, ni = r1cs.nv, r1cs.ni
         if B_total is None:
@@ -511,6 +522,10 @@ class Groth16ProvingKeyShard:
               cut(L_query, 3)]
         groups = [G1, G2, G1, G1, G1]
         self.sets = [ResidentBases(curve, g, q) if q.shape[0] else None for g, q in zip(groups, qs)]
+        if precompute:
+            for rb in self.sets:
+                if rb is not None:
+                    rb.precompute()
         idx = cut(None if B_indices is None else np.ascontiguousarray(B_indices, dtype=np.uint32), 1)
         if idx is not None:
             idx = np.ascontiguousarray(idx)

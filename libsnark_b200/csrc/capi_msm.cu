@@ -16,12 +16,13 @@ namespace
 
 struct GroupVt {
     int (*bases_upload)(int, int, const void *, size_t, size_t, rt::BaseSet *);
+    int (*bases_precompute)(rt::BaseSet *);
     int (*msm_windows)(const rt::BaseSet &, size_t, size_t, const void *, void *, int *, int *);
     int (*msm_fold)(const void *, int, int, int, size_t, void *);
     size_t (*window_point_bytes)();
     int (*scalar_bits)();
 };
-#define GROUP_VT(name) {name##_bases_upload, name##_msm_windows, name##_msm_fold, name##_window_point_bytes, name##_scalar_bits}
+#define GROUP_VT(name) {name##_bases_upload, name##_bases_precompute, name##_msm_windows, name##_msm_fold, name##_window_point_bytes, name##_scalar_bits}
 
 struct CurveVt {
     GroupVt g[2]; // [0] = G1, [1] = G2
@@ -229,6 +230,24 @@ int b200_bases_free(b200_bases_t handle)
     free_set(it->second);
     g_sets.erase(it);
     return B200_OK;
+}
+
+int b200_bases_precompute(b200_bases_t handle)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_sets.find(handle);
+    if (it == g_sets.end()) {
+        return rt::set_error(B200_ERR_HANDLE, "unknown base-set handle %llu", (unsigned long long)handle);
+    }
+    const CurveVt *v = vt(it->second.curve);
+    return v->grp(it->second.group).bases_precompute(&it->second);
+}
+
+int b200_bases_table_rows(b200_bases_t handle)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_sets.find(handle);
+    return it == g_sets.end() ? 0 : it->second.table_W;
 }
 
 size_t b200_bases_size(b200_bases_t handle)

@@ -157,7 +157,7 @@ HD void histogram_body(size_t i, const uint32_t *t, int NL, const Geometry &g, u
         const int32_t d = window_digit(ti, NL, g, w);
         if (d != 0) {
             const uint32_t mag = (uint32_t)(d < 0 ? -d : d);
-            atomic_inc_u32(counts + (size_t)w * g.B + (mag - 1));
+            atomic_inc_u32(counts + (size_t)w * g.bstride + (mag - 1));
         }
     }
 }
@@ -169,8 +169,8 @@ HD void scatter_body(size_t i, const uint32_t *t, int NL, const Geometry &g, uin
         const int32_t d = window_digit(ti, NL, g, w);
         if (d != 0) {
             const uint32_t mag = (uint32_t)(d < 0 ? -d : d);
-            const uint32_t pos = atomic_inc_u32(cursor + (size_t)w * g.B + (mag - 1));
-            entries[pos] = (uint32_t)i | (d < 0 ? 0x80000000u : 0u);
+            const uint32_t pos = atomic_inc_u32(cursor + (size_t)w * g.bstride + (mag - 1));
+            entries[pos] = ((uint32_t)i + (uint32_t)w * g.estride) | (d < 0 ? 0x80000000u : 0u);
         }
     }
 }
@@ -322,6 +322,40 @@ HD void convert_base_body(size_t i, const uint8_t *src, size_t stride, Affine<F>
     }
     inf[i] = is_inf ? 1 : 0;
     store_vec(dst + i, a);
+}
+
+// Precomputed tables: row w of the table holds [2^(c w)] P_i, affine, for every base i (row 0 = the bases).
+// One thread per base walks up the rows: c doublings, one normalisation (a field inversion — this is a
+// once-per-key cost). A multiple that is the point at infinity (possible only for a base outside the
+// prime-order subgroup) cannot be stored as an affine point: it raises *fail and the caller drops the table.
+template<class F>
+HD void build_table_body(size_t i, size_t row, int c, int W, Affine<F> *table, const uint8_t *inf, uint32_t *fail)
+{
+    if (inf != nullptr && inf[i]) {
+        Affine<F> z;
+        z.x = F::zero();
+        z.y = F::zero();
+        for (int w = 1; w < W; ++w) {
+            store_vec(table + (size_t)w * row + i, z);
+        }
+        return;
+    }
+    Affine<F> a = load_vec(table + i);
+    for (int w = 1; w < W; ++w) {
+        XYZZ<F> q = dbl_affine_cold(a);
+        for (int k = 1; k < c; ++k) {
+            dbl_cold(q);
+        }
+        if (!to_affine(q, a)) {
+#if defined(__CUDA_ARCH__)
+            atomicOr(fail, 1u);
+#else
+            *fail |= 1u;
+#endif
+            return;
+        }
+        store_vec(table + (size_t)w * row + i, a);
+    }
 }
 
 #if defined(__CUDACC__)

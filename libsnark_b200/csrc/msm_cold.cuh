@@ -101,6 +101,22 @@ __global__ void __launch_bounds__(WSUM_THREADS) k_window_sum(Geometry g, const X
 }
 
 template<class F>
+__global__ void __launch_bounds__(128) k_build_table(size_t n, int c, int W, Affine<F> *table, const uint8_t *inf, uint32_t *fail)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        build_table_body<F>(i, n, c, W, table, inf, fail);
+    }
+}
+
+template<class F> int table_launch(size_t n, int c, int W, Affine<F> *table, const uint8_t *inf, uint32_t *fail)
+{
+    k_build_table<F><<<(unsigned)((n + 127) / 128), 128, 0, rt::stream()>>>(n, c, W, table, inf, fail);
+    B200_LAUNCH_CHECK();
+    return B200_OK;
+}
+
+template<class F>
 int reduce_launch(const Geometry &g, const uint32_t *task_off, const uint32_t *multi_count,
                   const uint32_t *multi_list, XYZZ<F> *partial, XYZZ<F> *block_out, XYZZ<F> *windows_dev)
 {

@@ -27,6 +27,11 @@ struct Geometry {
     // so that the collapse kernel only ever sees outliers (at 2^24 with c = 17 the average bucket has
     // 4 tasks; a fixed threshold of 4 sent half a million buckets through it: 24 ms).
     uint32_t collapse;
+    // Where window w's digits go: bucket w * bstride + |digit| - 1, entry value w * estride + point index.
+    // Plain MSM: bstride = B, estride = 0 (W bucket sets over one base array). With precomputed tables
+    // [2^(c w)] P (make_table_geometry): bstride = 0, estride = the table's row length — every window feeds
+    // the SAME B buckets with the matching multiple of the base, and the W-fold reduction becomes one.
+    uint32_t bstride, estride;
 };
 
 // Window width: minimise  W(c) * (10 n + 100 * 2^(c-1))  field mults (10 per mixed add,
@@ -53,6 +58,38 @@ inline Geometry make_geometry(uint64_t n, int scalar_bits, int force_c = 0)
     g.rb = g.cpw < (uint32_t)REDUCE_BLOCK ? g.cpw : (uint32_t)REDUCE_BLOCK;
     g.opw = g.cpw / g.rb;
     const uint64_t avg_tasks = (n / g.B + SEG - 1) / SEG;
+    g.collapse = (uint32_t)(2 * avg_tasks + 2 > (uint64_t)COLLAPSE_TASKS ? 2 * avg_tasks + 2 : (uint64_t)COLLAPSE_TASKS);
+    g.bstride = g.B;
+    g.estride = 0;
+    return g;
+}
+
+// Window width for a base set with precomputed tables [2^(c w)] P, w < W: all W n entries land in one set
+// of 2^(c-1) buckets, so the reduction is paid once: minimise 10 W(c) n + 100 * 2^(c-1).
+inline int table_window_bits(uint64_t n, int scalar_bits)
+{
+    int best_c = 5;
+    double best = 1e300;
+    for (int c = 5; c <= 20; ++c) {
+        const int W = (scalar_bits + 1 + c - 1) / c;
+        const double cost = 10.0 * (double)W * (double)n + 100.0 * (double)(1u << (c - 1));
+        if (cost < best) {
+            best = cost;
+            best_c = c;
+        }
+    }
+    return best_c;
+}
+
+// Geometry of an MSM over n points of a table of row length `row` built for window width c.
+// The digit extraction sees W windows; everything after the scatter sees ONE window of B buckets.
+inline Geometry make_table_geometry(uint64_t n, int scalar_bits, int c, uint64_t row)
+{
+    Geometry g = make_geometry(n, scalar_bits, c);
+    g.bstride = 0;
+    g.estride = (uint32_t)row;
+    g.NB = g.B;
+    const uint64_t avg_tasks = ((uint64_t)g.W * n / g.B + SEG - 1) / SEG;
     g.collapse = (uint32_t)(2 * avg_tasks + 2 > (uint64_t)COLLAPSE_TASKS ? 2 * avg_tasks + 2 : (uint64_t)COLLAPSE_TASKS);
     return g;
 }

@@ -28,6 +28,9 @@ template<class F>
 int reduce_launch(const Geometry &g, const uint32_t *task_off, const uint32_t *multi_count,
                   const uint32_t *multi_list, XYZZ<F> *partial, XYZZ<F> *block_out, XYZZ<F> *windows_dev);
 
+// Table rows 1..W-1 of a base set (build_table_body); defined in msm_cold.cuh like reduce_launch.
+template<class F> int table_launch(size_t n, int c, int W, Affine<F> *table, const uint8_t *inf, uint32_t *fail);
+
 inline unsigned grid_for(size_t n, unsigned block) { return (unsigned)((n + block - 1) / block); }
 
 template<class F>
@@ -69,14 +72,68 @@ int bases_upload(int curve, int group, const void *host, size_t stride, size_t n
     return B200_OK;
 }
 
+// b200_bases_precompute: grows the set's point array to W rows, row w = [2^(c w)] P, for the window width
+// that is best once the reduction is paid for a single bucket set (table_window_bits). On failure (out of
+// memory, a multiple at infinity) the set is left as it was, without tables.
+template<class Fr, class F> int bases_precompute(rt::BaseSet *bs)
+{
+    if (bs->table_c || bs->n == 0) {
+        return B200_OK;
+    }
+    const int c = table_window_bits(bs->n, Fr::params::BITS);
+    const int W = (Fr::params::BITS + 1 + c - 1) / c;
+    if ((uint64_t)W * bs->n >= 0x7fffffffull) {
+        return rt::set_error(B200_ERR_ARG, "a table of %d rows of %zu points exceeds the 32-bit entry index", W, bs->n);
+    }
+    Workspace &ws = workspace();
+    cudaStream_t s = rt::stream();
+    if (ws.any_inf.reserve(16)) {
+        return B200_ERR_CUDA;
+    }
+    Affine<F> *table = nullptr;
+    B200_CUDA_CHECK(cudaMalloc((void **)&table, (size_t)W * bs->n * sizeof(Affine<F>)));
+    cudaError_t e = cudaMemcpyAsync(table, bs->pts, bs->n * sizeof(Affine<F>), cudaMemcpyDeviceToDevice, s);
+    if (e == cudaSuccess) {
+        e = cudaMemsetAsync(ws.any_inf.p, 0, 4, s);
+    }
+    int rc = e == cudaSuccess ? table_launch<F>(bs->n, c, W, table, bs->inf, ws.any_inf.as<uint32_t>()) : B200_ERR_CUDA;
+    uint32_t fail = 0;
+    if (rc == B200_OK) {
+        e = cudaMemcpyAsync(&fail, ws.any_inf.p, 4, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) {
+            e = cudaStreamSynchronize(s);
+        }
+    }
+    if (rc != B200_OK || e != cudaSuccess || fail) {
+        cudaFree(table);
+        if (rc != B200_OK) {
+            return rc;
+        }
+        if (e != cudaSuccess) {
+            return rt::set_error(B200_ERR_CUDA, "table build failed: %s", cudaGetErrorString(e));
+        }
+        return rt::set_error(B200_ERR_ARG, "a multiple 2^(c w) P of a base is the point at infinity: no table built");
+    }
+    cudaFree(bs->pts);
+    bs->pts = table;
+    bs->table_c = c;
+    bs->table_W = W;
+    return B200_OK;
+}
+
 // Runs stages 1-7; leaves W window sums (XYZZ<F>) at windows_dev.
 template<class Fr, class F>
 int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scalars_dev, void *windows_dev, int *W_out, int *c_out)
 {
     constexpr int NL = Fr::N;
-    const Geometry g = make_geometry(n, Fr::params::BITS);
-    *W_out = g.W;
-    *c_out = g.c;
+    // What the caller sees is always the plain geometry of n (b200_msm_num_windows / b200_msm_fold_windows).
+    // Over a table the whole sum comes out as "window 0" and the other windows are the point at infinity,
+    // which the Horner fold passes through unchanged.
+    const Geometry pub = make_geometry(n, Fr::params::BITS);
+    const Geometry g = bs.table_c ? make_table_geometry(n, Fr::params::BITS, bs.table_c, bs.n) : pub;
+    const int reduce_windows = bs.table_c ? 1 : g.W;
+    *W_out = pub.W;
+    *c_out = pub.c;
     Workspace &ws = workspace();
     cudaStream_t s = rt::stream();
     rt::MsmTiming &tm = rt::msm_timing();
@@ -92,7 +149,7 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
         ws.task_off.reserve(((size_t)g.NB + 1) * 4) || ws.tile_sums.reserve((size_t)ntiles * 8 + 8) ||
         ws.entries.reserve(max_entries * 4 + 16) || ws.tasks.reserve(max_tasks * sizeof(Task)) ||
         ws.partial.reserve(max_tasks * sizeof(XYZZ<F>)) ||
-        ws.chunk_out.reserve(((size_t)g.W * g.opw) * sizeof(XYZZ<F>)) || ws.multi.reserve(((size_t)g.NB + 4) * 4)) {
+        ws.chunk_out.reserve(((size_t)reduce_windows * g.opw) * sizeof(XYZZ<F>)) || ws.multi.reserve(((size_t)g.NB + 4) * 4)) {
         return B200_ERR_CUDA;
     }
     const Affine<F> *bases = static_cast<const Affine<F> *>(bs.pts) + first;
@@ -137,10 +194,16 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
     B200_CUDA_CHECK(cudaEventRecord(tm.ev[2], s));
     // 6-7: bucket reduction
     {
-        const int rc = reduce_launch<F>(g, task_off, multi_count, multi_list, partial, chunk_out,
+        Geometry gr = g;
+        gr.W = reduce_windows;
+        const int rc = reduce_launch<F>(gr, task_off, multi_count, multi_list, partial, chunk_out,
                                          static_cast<XYZZ<F> *>(windows_dev));
         if (rc) {
             return rc;
+        }
+        if (pub.W > reduce_windows) { // XYZZ infinity is all zeros
+            B200_CUDA_CHECK(cudaMemsetAsync(static_cast<XYZZ<F> *>(windows_dev) + reduce_windows, 0,
+                                            (size_t)(pub.W - reduce_windows) * sizeof(XYZZ<F>), s));
         }
     }
     B200_CUDA_CHECK(cudaEventRecord(tm.ev[3], s));
@@ -177,6 +240,10 @@ template<class F> int msm_fold(const void *windows, int on_device, int W, int c,
                             rt::BaseSet *out)                                                                  \
     {                                                                                                          \
         return msm::bases_upload<group_traits<CURVE, GROUP>::F>(curve, group, host, stride, n, out);           \
+    }                                                                                                          \
+    int name##_bases_precompute(rt::BaseSet *bs)                                                               \
+    {                                                                                                          \
+        return msm::bases_precompute<group_traits<CURVE, GROUP>::Fr, group_traits<CURVE, GROUP>::F>(bs);       \
     }                                                                                                          \
     int name##_msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scalars_dev,            \
                            void *windows_dev, int *W, int *c)                                                  \

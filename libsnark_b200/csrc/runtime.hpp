@@ -55,6 +55,8 @@ struct BaseSet {
     size_t point_bytes = 0; // sizeof(Affine<F>)
     void *pts = nullptr;    // Affine<F>[n]
     uint8_t *inf = nullptr; // n flags, or nullptr when no base is the point at infinity
+    // b200_bases_precompute: pts then holds table_W rows of n points, row w = [2^(table_c w)] P (msm.cuh)
+    int table_c = 0, table_W = 0;
 };
 
 struct MsmTiming {
@@ -71,6 +73,7 @@ MsmTiming &msm_timing();
 #define B200_DECLARE_GROUP_ENTRY(name)                                                             \
     int name##_bases_upload(int curve, int group, const void *host, size_t stride, size_t n,      \
                             rt::BaseSet *out);                                                     \
+    int name##_bases_precompute(rt::BaseSet *bs);                                                  \
     int name##_msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scalars_dev, \
                            void *windows_dev, int *W, int *c);                                     \
     int name##_msm_fold(const void *windows, int on_device, int W, int c, size_t shards, void *out); \

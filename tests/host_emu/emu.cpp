@@ -169,16 +169,29 @@ extern "C" int emu_signed_digits(int curve, const void *scalars, size_t n, int c
 
 // The whole MSM pipeline of msm.cuh executed sequentially on the host (same bodies, same index
 // logic: histogram -> scan -> scatter -> tasks -> accumulate -> reduce -> fold).
-template<class Fr, class F> static int msm_emulated(const void *bases_ref, size_t n, const void *scalars, int force_c, void *out)
+// table = true: the precomputed-table variant (b200_bases_precompute): build_table_body fills rows [2^(c w)] P,
+// every window scatters into the one bucket set, the reduction runs over a single window.
+template<class Fr, class F>
+static int msm_emulated(const void *bases_ref, size_t n, const void *scalars, int force_c, void *out, bool table = false)
 {
     using namespace msm;
-    Geometry g = make_geometry(n, Fr::params::BITS, force_c);
+    const int tc = force_c ? force_c : table_window_bits(n, Fr::params::BITS);
+    Geometry g = table ? make_table_geometry(n, Fr::params::BITS, tc, n) : make_geometry(n, Fr::params::BITS, force_c);
     const Limbs<Fr::N> K = make_offset_constant<Fr::N>(g);
-    std::vector<Affine<F>> bases(n);
+    std::vector<Affine<F>> bases(table ? n * g.W : n);
     std::vector<uint8_t> inf(n);
     uint32_t any = 0;
     for (size_t i = 0; i < n; ++i) {
         convert_base_body<F>(i, (const uint8_t *)bases_ref, sizeof(RefPoint<F>), bases.data(), inf.data(), &any);
+    }
+    if (table) {
+        uint32_t fail = 0;
+        for (size_t i = 0; i < n; ++i) {
+            build_table_body<F>(i, n, g.c, g.W, bases.data(), any ? inf.data() : nullptr, &fail);
+        }
+        if (fail) {
+            return -7;
+        }
     }
     std::vector<uint32_t> t(n * Fr::N), counts(g.NB + 1, 0), offsets(g.NB + 1), cursor(g.NB + 1), task_off(g.NB + 1);
     for (size_t i = 0; i < n; ++i) {
@@ -218,7 +231,8 @@ template<class Fr, class F> static int msm_emulated(const void *bases_ref, size_
         partial[task_off[b]] = acc;
     }
     std::vector<XYZZ<F>> windows(g.W, XYZZ<F>::inf());
-    for (size_t gidx = 0; gidx < (size_t)g.W * g.cpw; ++gidx) {
+    const size_t reduce_windows = table ? 1 : (size_t)g.W;
+    for (size_t gidx = 0; gidx < reduce_windows * g.cpw; ++gidx) {
         XYZZ<F> s;
         reduce_chunk_body<F>(gidx, g, task_off.data(), partial.data(), &s);
         add(windows[gidx / g.cpw], s);
@@ -226,6 +240,19 @@ template<class Fr, class F> static int msm_emulated(const void *bases_ref, size_
     const RefPoint<F> r = host_fold<F>(windows.data(), g.W, g.c, 1);
     memcpy(out, &r, sizeof(r));
     return 0;
+}
+
+extern "C" int emu_msm_table(int curve, int group, const void *bases, size_t n, const void *scalars, int c, void *out)
+{
+    switch (curve * 4 + group) {
+    case 1: return msm_emulated<alt_bn128_fr, alt_bn128_fq>(bases, n, scalars, c, out, true);
+    case 2: return msm_emulated<alt_bn128_fr, alt_bn128_fq2>(bases, n, scalars, c, out, true);
+    case 5: return msm_emulated<bls12_377_fr, bls12_377_fq>(bases, n, scalars, c, out, true);
+    case 6: return msm_emulated<bls12_377_fr, bls12_377_fq2>(bases, n, scalars, c, out, true);
+    case 9:
+    case 10: return msm_emulated<bw6_761_fr, bw6_761_fq>(bases, n, scalars, c, out, true);
+    }
+    return -100;
 }
 
 extern "C" int emu_msm(int curve, int group, const void *bases, size_t n, const void *scalars, int force_c, void *out)

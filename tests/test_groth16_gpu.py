@@ -113,7 +113,7 @@ def test_device_resident_prover_bit_exact(ref, overlay, curve, log_m, real_keys)
         fx.close()
 
 
-def _device_pk(b200, fx):
+def _device_pk(b200, fx, precompute=False):
     """Everything b200_groth16_pk_create needs, read out of a reference fixture."""
     row_ptr, col, val = fx.r1cs_csr()
     sz = fx.sizes
@@ -122,7 +122,8 @@ def _device_pk(b200, fx):
     bvals = fx.B_values
     idx = fx.B_indices.astype(np.uint32)
     pk = b200.Groth16ProvingKey(fx.curve, *fx.pk_points(), fx.A_query, np.ascontiguousarray(bvals[:, :g2l]),
-                                np.ascontiguousarray(bvals[:, g2l:]), idx, fx.H_query, fx.L_query, cs, sz["m"])
+                                np.ascontiguousarray(bvals[:, g2l:]), idx, fx.H_query, fx.L_query, cs, sz["m"],
+                                precompute=precompute)
     return pk, cs
 
 
@@ -134,7 +135,7 @@ def test_c_abi_prover_bit_exact(ref, b200, curve, log_m, real_keys):
     ni = 10
     fx = ref.groth16_setup(curve, (1 << log_m) - ni - 1, ni, real_keys=real_keys)
     try:
-        pk, cs = _device_pk(b200, fx)
+        pk, cs = _device_pk(b200, fx, precompute=(log_m == 10))   # the 2^10 cases run over precomputed tables
         try:
             for seed in (0x5EED, 0xBEEF):
                 rs = ref.field_random(curve, refo.FR, seed, 2)

@@ -39,6 +39,7 @@ def emu():
     L.emu_group_op.argtypes = [i, i, i, vp, vp, vp, sz]
     L.emu_signed_digits.argtypes = [i, vp, sz, i, vp, C.POINTER(C.c_int)]
     L.emu_msm.argtypes = [i, i, vp, sz, vp, i, vp]
+    L.emu_msm_table.argtypes = [i, i, vp, sz, vp, i, vp]
     return L
 
 
@@ -121,3 +122,32 @@ def test_emulated_msm_heavy_bucket(emu):
     from oracle import port
     want = port.OraclePort().msm("alt_bn128", 1, bases, sc)
     assert np.array_equal(_emu_msm(emu, "alt_bn128", 1, bases, sc, 5), want)
+
+
+def _emu_msm_table(emu, curve, gid, bases, scalars, c=0):
+    bases, scalars = np.ascontiguousarray(bases), np.ascontiguousarray(scalars)
+    out = np.zeros(bases.shape[1], dtype=np.uint64)
+    assert emu.emu_msm_table(CURVES[curve], gid, _p(bases), scalars.shape[0], _p(scalars), c, _p(out)) == 0
+    return out
+
+
+@pytest.mark.parametrize("curve", list(CURVES))
+def test_emulated_msm_over_precomputed_tables(emu, curve):
+    """b200_bases_precompute's formulation: rows [2^(c w)] P built by build_table_body, every window scattered into
+    ONE bucket set, a single-window reduction — the same group element as the reference's multi_exp. (Each table
+    entry costs an emulated field inversion, so the wide fields get few points and wide windows.)"""
+    from oracle import port
+    P = port.OraclePort()
+    g = np.load(os.path.join(GOLD, "msm.npz"))
+    npts = {"alt_bn128": 96, "bls12_377": 40, "bw6_761": 12}[curve]
+    for gname, gid in [("g1", 1), ("g2", 2)]:
+        k = f"rand.{curve}.{gname}"
+        bases, sc = g[k + ".bases"][:npts], g[k + ".scalars"][:npts]
+        want = g[k + ".out"] if npts == 96 else P.msm(curve, gid, bases, sc)
+        for c in ([0, 13] if gid == 1 and curve == "alt_bn128" else [16]):
+            assert np.array_equal(_emu_msm_table(emu, curve, gid, bases, sc, c), want), (k, c)
+    if curve == "alt_bn128":
+        for kk in [1, 2, 5, 257]:
+            got = _emu_msm_table(emu, curve, 1, g["family.bases"][:kk], g[f"family.scalars{kk}"], 12)
+            assert np.array_equal(got, g[f"family.out{kk}"]), kk
+        assert np.array_equal(_emu_msm_table(emu, curve, 1, g["edge.bases"], g["edge.scalars"], 9), g["edge.out"])

@@ -153,3 +153,50 @@ def test_msm_full_size_linearity(ref, b200, curve, group, log_n):
     rhs = ref.group_op(curve, group, refo.GOP_ADD, got[None, :], r2[None, :])
     rhs = ref.group_op(curve, group, refo.GOP_TO_AFFINE, rhs)[0]
     assert np.array_equal(lhs, rhs)
+
+
+@pytest.mark.parametrize("curve,group", CURVE_GROUPS)
+def test_msm_over_precomputed_tables(ref, b200, curve, group):
+    """b200_bases_precompute: rows [2^(c w)] P built on the device, all windows into one bucket set. Same normalised
+    point as the reference for whole sets, sub-ranges, zero/one/equal scalars, an infinity base and window sums."""
+    n = 3000 if curve != "bw6_761" else 700
+    bases, scalars = _inputs(ref, curve, group, n, seed=11)
+    bases = bases.copy()
+    bases[7] = ref.group_op(curve, group, refo.GOP_TO_AFFINE, np.zeros((1, bases.shape[1]), np.uint64))[0]  # infinity
+    one = ref.field_consts(curve, refo.FR)["one"]
+    scalars[3] = 0
+    scalars[4] = one
+    rb = b200.ResidentBases(curve, group, bases)
+    try:
+        plain = rb.multi_exp(scalars)
+        rows = rb.precompute()
+        assert rows >= 8 and rb.precompute() == rows            # idempotent
+        want = ref.msm(curve, group, bases, scalars)
+        assert np.array_equal(plain, want)
+        assert np.array_equal(rb.multi_exp(scalars), want)
+        for first, cnt in [(0, 1), (5, n // 3), (n - 17, 17), (1, n - 1)]:
+            w = ref.msm(curve, group, bases[first:first + cnt], scalars[first:first + cnt])
+            assert np.array_equal(rb.multi_exp(scalars[first:first + cnt], first=first, n=cnt), w), (first, cnt)
+        eq = np.repeat(scalars[:1], n, axis=0)
+        assert np.array_equal(rb.multi_exp(eq), ref.msm(curve, group, bases, eq))
+        # window sums of two sub-ranges folded like two shards
+        half = n // 2
+        wins = np.concatenate([rb.window_sums(scalars[:half], first=0, n=half),
+                               rb.window_sums(scalars[half:2 * half], first=half, n=half)])
+        got = b200.fold_windows(curve, group, half, wins, 2)
+        assert np.array_equal(got, ref.msm(curve, group, bases[:2 * half], scalars[:2 * half]))
+    finally:
+        rb.free()
+
+
+@pytest.mark.parametrize("log_n", [16, 18])
+def test_msm_tables_large(ref, b200, log_n):
+    n = 1 << log_n
+    bases, scalars = _inputs(ref, "alt_bn128", refo.G1, n, seed=4)
+    rb = b200.ResidentBases("alt_bn128", refo.G1, bases)
+    try:
+        rb.precompute()
+        want = ref.msm("alt_bn128", refo.G1, bases, scalars, chunks=ref.num_threads())
+        assert np.array_equal(rb.multi_exp(scalars), want)
+    finally:
+        rb.free()

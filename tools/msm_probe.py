@@ -28,6 +28,15 @@ for curve, group, logn in CASES:
         out = rb.multi_exp(scalars)
         dt = time.time() - t0
         print("  iter", it, "wall ms", round(dt * 1e3, 3), {k: round(v, 3) for k, v in b.last_msm_timing().items()})
+    t0 = time.time()
+    rows = rb.precompute()
+    print("  precompute:", rows, "rows,", round(time.time() - t0, 3), "s")
+    for it in range(4):
+        t0 = time.time()
+        out_t = rb.multi_exp(scalars)
+        dt = time.time() - t0
+        print("  tables iter", it, "wall ms", round(dt * 1e3, 3), {k: round(v, 3) for k, v in b.last_msm_timing().items()})
+    print("  tables == plain:", np.array_equal(out, out_t))
     if logn <= 18:
         want = ref.msm(curve, group, bases, scalars, chunks=ref.num_threads())
         print("  parity:", np.array_equal(out, want))

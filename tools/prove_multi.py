@@ -23,7 +23,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tools"))
 
 
-def run(b, torch, dist, curve, log_m, steps, warmup, chain_parallel=None, check=False, sy=None):
+def run(b, torch, dist, curve, log_m, steps, warmup, chain_parallel=None, check=False, sy=None, tables=True):
     import synth_r1cs
     world = dist.get_world_size() if dist.is_initialized() else 1
     rank = dist.get_rank() if dist.is_initialized() else 0
@@ -47,7 +47,7 @@ def run(b, torch, dist, curve, log_m, steps, warmup, chain_parallel=None, check=
     p2 = b.make_bases(curve, b.G2, 2, k0=k + 3)
     pts = (p1[0], p1[1], p2[0], p1[2], p2[1])
     pk = b.Groth16ProvingKeyShard(curve, *pts, shards[0], shards[1], shards[2], None, shards[3], shards[4], cs, m, rank,
-                                  world, sliced=True, B_total=nv + 1)
+                                  world, sliced=True, B_total=nv + 1, precompute=tables)
     del shards
     prover = b.DistributedProver(pk, chain_parallel=chain_parallel)
     setup_s = time.time() - t0
@@ -78,7 +78,7 @@ def run(b, torch, dist, curve, log_m, steps, warmup, chain_parallel=None, check=
             assert np.array_equal(p, proof), "prover is not deterministic for fixed r, s"
     out = {"metric": f"Groth16 prove ms @2^{log_m} {curve}", "value": float(np.mean(times)), "unit": "ms",
            "min_ms": float(np.min(times)), "higher_is_better": False, "n_gpus": world, "scaling": "strong",
-           "steps": steps, "warmup": warmup, "chain_parallel_witness_map": bool(prover.chain_parallel),
+           "steps": steps, "warmup": warmup, "chain_parallel_witness_map": bool(prover.chain_parallel), "precomputed_tables": bool(tables),
            "sizes": {"num_constraints": sy["nc"], "num_inputs": ni, "num_variables": nv, "domain": m},
            "h2d_bytes_per_step_per_rank": int((nv + 1) * b.sizeof_fr(curve)),
            "allgather_bytes_per_rank": int(pk.blob_bytes), "setup_s": setup_s,
@@ -107,6 +107,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--check", action="store_true")
     ap.add_argument("--no-chain-parallel", action="store_true")
+    ap.add_argument("--no-tables", action="store_true")
     args = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -119,7 +120,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     b.init(local_rank)
     out = run(b, torch, dist, args.curve, args.log_m, args.steps, args.warmup,
-              chain_parallel=False if args.no_chain_parallel else None, check=args.check)
+              chain_parallel=False if args.no_chain_parallel else None, check=args.check, tables=not args.no_tables)
     if (dist.get_rank() if world > 1 else 0) == 0:
         print(json.dumps(out), flush=True)
     if world > 1:
