@@ -595,30 +595,53 @@ class DistributedProver:
                        if self.chain_parallel else None)
 
     def prove(self, primary_input, auxiliary_input, r, s, fold_on_all_ranks=False):
-        """The proof on rank 0 (on every rank with fold_on_all_ranks), None elsewhere."""
+        """The proof on rank 0 (on every rank with fold_on_all_ranks), None elsewhere. self.last_stages holds this
+        rank's host wall clock per phase in ms."""
+        import time
         torch, dist, pk = self.torch, self.dist, self.pk
+        t = [time.perf_counter()]
+        names = []
+
+        def lap(name):
+            t.append(time.perf_counter())
+            names.append(name)
         if self.chain_parallel:
             pk.begin(primary_input, auxiliary_input)
+            lap("upload")
             if pk.rank < 3:
                 pk.chain(pk.rank, self.chains[pk.rank].data_ptr())
+            lap("chain")
             works = [dist.broadcast(self.chains[i], src=i, async_op=True) for i in range(3)]
             pk.msm(MSM_A | MSM_B_G2 | MSM_B_G1 | MSM_L, self.blob.data_ptr())
+            lap("msm_A_B_L")
             for w in works:
                 w.wait()
             torch.cuda.current_stream().synchronize()
+            lap("broadcast_wait")
             pk.h(*[c.data_ptr() for c in self.chains])
+            lap("h_finish")
             pk.msm(MSM_H, self.blob.data_ptr())
+            lap("msm_H")
         else:
-            pk.prove_shard(primary_input, auxiliary_input, self.blob.data_ptr())
+            st = pk.prove_shard(primary_input, auxiliary_input, self.blob.data_ptr())
+            lap("prove_shard")
+            self.last_shard_stages = st
         if pk.world > 1:
             dist.all_gather_into_tensor(self.gathered, self.blob)
             src = self.gathered
         else:
             src = self.blob
+        out = None
         if pk.rank == 0 or fold_on_all_ranks:
-            return pk.assemble(r, s, src.cpu().numpy())
-        torch.cuda.current_stream().synchronize()
-        return None
+            host = src.cpu().numpy()
+            lap("all_gather_d2h")
+            out = pk.assemble(r, s, host)
+            lap("assemble")
+        else:
+            torch.cuda.current_stream().synchronize()
+            lap("all_gather")
+        self.last_stages = {n: (t[i + 1] - t[i]) * 1e3 for i, n in enumerate(names)}
+        return out
 
 
 class DeviceBuffer:

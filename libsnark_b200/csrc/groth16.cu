@@ -15,7 +15,9 @@
 #include <chrono>
 #include <cstring>
 #include <map>
+#include <future>
 #include <mutex>
+#include <thread>
 #include <vector>
 
 #include "curves.cuh"
@@ -133,24 +135,32 @@ int assemble(const KeyPoints &pk, const void *r_, const void *s_, const void *At
     memcpy(&s, s_, sizeof(Fr));
     const XYZZ<F1> delta1 = load_ref<F1>(pk.delta_g1);
     const XYZZ<F2> delta2 = load_ref<F2>(pk.delta_g2);
+    // The six scalar multiplications of .tcc:583-595 are serial double-and-add chains on one point each;
+    // the four that do not depend on an MSM result run side by side on host threads.
+    auto f_sd2 = std::async(std::launch::async, [&]() { return scalar_mul<Fr, F2>(s, delta2); });
+    auto f_rd1 = std::async(std::launch::async, [&]() { return scalar_mul<Fr, F1>(r, delta1); });
+    auto f_rsd1 = std::async(std::launch::async, [&]() { return scalar_mul<Fr, F1>(r * s, delta1); });
+    const XYZZ<F1> sd1 = scalar_mul<Fr, F1>(s, delta1);
 
     XYZZ<F1> gA = load_ref<F1>(pk.alpha_g1);
     add(gA, load_ref<F1>(At));
-    add(gA, scalar_mul<Fr, F1>(r, delta1));
+    add(gA, f_rd1.get());
 
     XYZZ<F1> gB1 = load_ref<F1>(pk.beta_g1);
     add(gB1, load_ref<F1>(Bg1));
-    add(gB1, scalar_mul<Fr, F1>(s, delta1));
+    add(gB1, sd1);
+    auto f_rgB1 = std::async(std::launch::async, [&]() { return scalar_mul<Fr, F1>(r, gB1); });
+    const XYZZ<F1> sgA = scalar_mul<Fr, F1>(s, gA);
 
     XYZZ<F2> gB2 = load_ref<F2>(pk.beta_g2);
     add(gB2, load_ref<F2>(Bg2));
-    add(gB2, scalar_mul<Fr, F2>(s, delta2));
+    add(gB2, f_sd2.get());
 
     XYZZ<F1> gC = load_ref<F1>(Ht);
     add(gC, load_ref<F1>(Lt));
-    add(gC, scalar_mul<Fr, F1>(s, gA));
-    add(gC, scalar_mul<Fr, F1>(r, gB1));
-    add(gC, neg(scalar_mul<Fr, F1>(r * s, delta1)));
+    add(gC, sgA);
+    add(gC, f_rgB1.get());
+    add(gC, neg(f_rsd1.get()));
 
     const msm::RefPoint<F1> oA = msm::normalise(gA), oC = msm::normalise(gC);
     const msm::RefPoint<F2> oB = msm::normalise(gB2);
@@ -243,8 +253,36 @@ int upload_witness(const ProvingKey &pk, const void *primary_input, const void *
     }
     memcpy(w, one, fr);
     memcpy(w + fr, primary_input, pk.ni * fr);
-    memcpy(w + (1 + pk.ni) * fr, auxiliary_input, (pk.nv - pk.ni) * fr);
-    return b200_memcpy_h2d(pk.d_w, w, (pk.nv + 1) * fr);
+    // The auxiliary input is the bulk (32 MiB at 2^20, 128 MiB at 2^22) and one core copies at ~10 GB/s: stage it into
+    // the pinned buffer with a few threads, and send each slice to the device as soon as it is staged.
+    const size_t head = (1 + pk.ni) * fr, bulk = (pk.nv - pk.ni) * fr;
+    const size_t T = std::max<size_t>(1, std::min<size_t>(4, bulk >> 22));
+    cudaStream_t st = rt::stream();
+    const uint8_t *src = static_cast<const uint8_t *>(auxiliary_input);
+    uint8_t *dst = w + head, *dev = static_cast<uint8_t *>(pk.d_w);
+    std::vector<std::thread> workers;
+    std::vector<size_t> cut(T + 1);
+    for (size_t t = 0; t <= T; ++t) {
+        cut[t] = t == T ? bulk : (bulk / T * t) & ~(size_t)63;
+    }
+    for (size_t t = 1; t < T; ++t) {
+        workers.emplace_back([=]() { memcpy(dst + cut[t], src + cut[t], cut[t + 1] - cut[t]); });
+    }
+    memcpy(dst, src, cut[1]);
+    cudaError_t e = cudaMemcpyAsync(dev, w, head + cut[1], cudaMemcpyHostToDevice, st);
+    for (size_t t = 1; t < T; ++t) {
+        workers[t - 1].join();
+        if (e == cudaSuccess) {
+            e = cudaMemcpyAsync(dev + head + cut[t], dst + cut[t], cut[t + 1] - cut[t], cudaMemcpyHostToDevice, st);
+        }
+    }
+    if (e == cudaSuccess) {
+        e = cudaStreamSynchronize(st);
+    }
+    if (e != cudaSuccess) {
+        return rt::set_error(B200_ERR_CUDA, "witness upload failed: %s", cudaGetErrorString(e));
+    }
+    return B200_OK;
 }
 
 // The MSMs of this rank's shards selected by `mask` (bit k = MSM k in blob order A, B.g2, B.g1, H, L).

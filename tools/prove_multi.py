@@ -85,6 +85,7 @@ def run(b, torch, dist, curve, log_m, steps, warmup, chain_parallel=None, check=
            "note": "wall clock, max over ranks, around DistributedProver.prove: witness (host, every rank) -> H2D -> witness map "
                    "(replicated, or the A/B/C chains on ranks 0-2 + NCCL broadcast) -> this rank's shard of the A, B(G2+G1), H, L "
                    "MSMs -> NCCL all-gather of the window sums -> host fold and proof assembly on rank 0"}
+    out["stages_rank0_ms"] = {k: round(v, 3) for k, v in prover.last_stages.items()}
     if check:
         ok = None
         if rank == 0:
