@@ -49,11 +49,33 @@ const CurveVt *vt(int curve)
 
 size_t group_bytes(const CurveVt *v, int group) { return 3 * v->fq_bytes * ((group == B200_G2 && v->g2_is_fq2) ? 2 : 1); }
 
-std::mutex g_mu;
+std::mutex g_mu; // guards g_sets
 std::map<uint64_t, rt::BaseSet> g_sets;
 uint64_t g_next_handle = 1;
 
-rt::DevBuf g_scalars, g_windows, g_out;
+// Per execution slot (runtime.hpp): the buffers of an MSM call and the lock that serialises the calls of one slot.
+struct SlotState {
+    std::mutex mu;
+    rt::DevBuf scalars, windows, out;
+};
+SlotState g_slot[rt::NUM_SLOTS];
+#define g_scalars g_slot[rt::slot()].scalars
+#define g_windows g_slot[rt::slot()].windows
+#define g_out g_slot[rt::slot()].out
+
+// A copy of the set's descriptor (the device arrays stay owned by the handle; the caller must not free a set
+// that an MSM is still running over).
+bool find_set(b200_bases_t handle, rt::BaseSet *out)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_sets.find(handle);
+    if (it == g_sets.end()) {
+        rt::set_error(B200_ERR_HANDLE, "unknown base-set handle %llu", (unsigned long long)handle);
+        return false;
+    }
+    *out = it->second;
+    return true;
+}
 
 // The reference's zero(): (0, one, 0).
 void write_zero_point(int curve, int group, void *out)
@@ -226,7 +248,7 @@ int b200_bases_free(b200_bases_t handle)
     if (it == g_sets.end()) {
         return rt::set_error(B200_ERR_HANDLE, "unknown base-set handle %llu", (unsigned long long)handle);
     }
-    cudaStreamSynchronize(rt::stream());
+    cudaDeviceSynchronize(); // an MSM of any slot may still be reading the set
     free_set(it->second);
     g_sets.erase(it);
     return B200_OK;
@@ -260,15 +282,15 @@ size_t b200_bases_size(b200_bases_t handle)
 int b200_msm_resident(b200_bases_t handle, size_t first, size_t n, const void *scalars, int scalars_on_device,
                       void *out)
 {
-    std::lock_guard<std::mutex> lk(g_mu);
-    auto it = g_sets.find(handle);
-    if (it == g_sets.end()) {
-        return rt::set_error(B200_ERR_HANDLE, "unknown base-set handle %llu", (unsigned long long)handle);
+    rt::BaseSet bs;
+    if (!find_set(handle, &bs)) {
+        return B200_ERR_HANDLE;
     }
     if (!out || (n && !scalars)) {
         return rt::set_error(B200_ERR_ARG, "null pointer");
     }
-    return msm_resident_impl(it->second, first, n, scalars, scalars_on_device, out, nullptr);
+    std::lock_guard<std::mutex> lk(g_slot[rt::slot()].mu);
+    return msm_resident_impl(bs, first, n, scalars, scalars_on_device, out, nullptr);
 }
 
 int b200_msm_num_windows(int curve, size_t n)
@@ -298,29 +320,29 @@ size_t b200_msm_window_bytes(int curve, int group)
 int b200_msm_resident_windows(b200_bases_t handle, size_t first, size_t n, const void *scalars,
                               int scalars_on_device, void *out_windows)
 {
-    std::lock_guard<std::mutex> lk(g_mu);
-    auto it = g_sets.find(handle);
-    if (it == g_sets.end()) {
-        return rt::set_error(B200_ERR_HANDLE, "unknown base-set handle %llu", (unsigned long long)handle);
+    rt::BaseSet bs;
+    if (!find_set(handle, &bs)) {
+        return B200_ERR_HANDLE;
     }
     if (!out_windows || !scalars || n == 0) {
         return rt::set_error(B200_ERR_ARG, "null pointer or empty range");
     }
-    return msm_resident_impl(it->second, first, n, scalars, scalars_on_device, nullptr, out_windows);
+    std::lock_guard<std::mutex> lk(g_slot[rt::slot()].mu);
+    return msm_resident_impl(bs, first, n, scalars, scalars_on_device, nullptr, out_windows);
 }
 
 int b200_msm_resident_windows_dev(b200_bases_t handle, size_t first, size_t n, const void *scalars,
                                   int scalars_on_device, void *dev_out_windows)
 {
-    std::lock_guard<std::mutex> lk(g_mu);
-    auto it = g_sets.find(handle);
-    if (it == g_sets.end()) {
-        return rt::set_error(B200_ERR_HANDLE, "unknown base-set handle %llu", (unsigned long long)handle);
+    rt::BaseSet bs;
+    if (!find_set(handle, &bs)) {
+        return B200_ERR_HANDLE;
     }
     if (!dev_out_windows || !scalars || n == 0) {
         return rt::set_error(B200_ERR_ARG, "null pointer or empty range");
     }
-    return msm_resident_impl(it->second, first, n, scalars, scalars_on_device, nullptr, nullptr, dev_out_windows);
+    std::lock_guard<std::mutex> lk(g_slot[rt::slot()].mu);
+    return msm_resident_impl(bs, first, n, scalars, scalars_on_device, nullptr, nullptr, dev_out_windows);
 }
 
 int b200_msm_fold_windows(int curve, int group, size_t n_per_shard, const void *windows, size_t num_shards, void *out)
@@ -352,7 +374,7 @@ int b200_msm(int curve, int group, const void *bases, size_t base_stride, size_t
         write_zero_point(curve, group, out);
         return B200_OK;
     }
-    std::lock_guard<std::mutex> lk(g_mu);
+    std::lock_guard<std::mutex> lk(g_slot[rt::slot()].mu);
     rt::BaseSet bs;
     int rc = v->grp(group).bases_upload(curve, group, bases, base_stride, n, &bs);
     if (rc) {

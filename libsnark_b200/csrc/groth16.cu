@@ -13,10 +13,13 @@
 // same reason as host_fold.hpp: a serial chain on one point).
 #include <algorithm>
 #include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <future>
 #include <mutex>
+#include <string>
 #include <thread>
 #include <vector>
 
@@ -123,9 +126,14 @@ struct KeyPoints {
     const void *alpha_g1, *beta_g1, *beta_g2, *delta_g1, *delta_g2;
 };
 
-template<int CURVE>
-int assemble(const KeyPoints &pk, const void *r_, const void *s_, const void *At, const void *Bg2, const void *Bg1,
-             const void *Ht, const void *Lt, void *proof_out)
+// The scalar multiplications of the proof assembly that need only r, s and the key (.tcc:583-595): r delta,
+// s delta (G1 and G2), (r s) delta. Serial double-and-add chains on one point each, side by side on host
+// threads; the one-GPU prover starts them while the GPU is busy with the MSMs.
+template<int CURVE> struct PreAssembled {
+    XYZZ<typename group_traits<CURVE, GROUP_G1>::F> rd1, sd1, rsd1;
+    XYZZ<typename group_traits<CURVE, GROUP_G2>::F> sd2;
+};
+template<int CURVE> PreAssembled<CURVE> pre_assemble(const KeyPoints &pk, const void *r_, const void *s_)
 {
     typedef typename group_traits<CURVE, GROUP_G1>::Fr Fr;
     typedef typename group_traits<CURVE, GROUP_G1>::F F1;
@@ -135,32 +143,48 @@ int assemble(const KeyPoints &pk, const void *r_, const void *s_, const void *At
     memcpy(&s, s_, sizeof(Fr));
     const XYZZ<F1> delta1 = load_ref<F1>(pk.delta_g1);
     const XYZZ<F2> delta2 = load_ref<F2>(pk.delta_g2);
-    // The six scalar multiplications of .tcc:583-595 are serial double-and-add chains on one point each;
-    // the four that do not depend on an MSM result run side by side on host threads.
     auto f_sd2 = std::async(std::launch::async, [&]() { return scalar_mul<Fr, F2>(s, delta2); });
     auto f_rd1 = std::async(std::launch::async, [&]() { return scalar_mul<Fr, F1>(r, delta1); });
     auto f_rsd1 = std::async(std::launch::async, [&]() { return scalar_mul<Fr, F1>(r * s, delta1); });
-    const XYZZ<F1> sd1 = scalar_mul<Fr, F1>(s, delta1);
+    PreAssembled<CURVE> p;
+    p.sd1 = scalar_mul<Fr, F1>(s, delta1);
+    p.sd2 = f_sd2.get();
+    p.rd1 = f_rd1.get();
+    p.rsd1 = f_rsd1.get();
+    return p;
+}
+
+template<int CURVE>
+int assemble(const KeyPoints &pk, const void *r_, const void *s_, const void *At, const void *Bg2, const void *Bg1,
+             const void *Ht, const void *Lt, void *proof_out, const PreAssembled<CURVE> *pre_given = nullptr)
+{
+    typedef typename group_traits<CURVE, GROUP_G1>::Fr Fr;
+    typedef typename group_traits<CURVE, GROUP_G1>::F F1;
+    typedef typename group_traits<CURVE, GROUP_G2>::F F2;
+    Fr r, s;
+    memcpy(&r, r_, sizeof(Fr));
+    memcpy(&s, s_, sizeof(Fr));
+    const PreAssembled<CURVE> pre = pre_given ? *pre_given : pre_assemble<CURVE>(pk, r_, s_);
 
     XYZZ<F1> gA = load_ref<F1>(pk.alpha_g1);
     add(gA, load_ref<F1>(At));
-    add(gA, f_rd1.get());
+    add(gA, pre.rd1);
 
     XYZZ<F1> gB1 = load_ref<F1>(pk.beta_g1);
     add(gB1, load_ref<F1>(Bg1));
-    add(gB1, sd1);
+    add(gB1, pre.sd1);
     auto f_rgB1 = std::async(std::launch::async, [&]() { return scalar_mul<Fr, F1>(r, gB1); });
     const XYZZ<F1> sgA = scalar_mul<Fr, F1>(s, gA);
 
     XYZZ<F2> gB2 = load_ref<F2>(pk.beta_g2);
     add(gB2, load_ref<F2>(Bg2));
-    add(gB2, f_sd2.get());
+    add(gB2, pre.sd2);
 
     XYZZ<F1> gC = load_ref<F1>(Ht);
     add(gC, load_ref<F1>(Lt));
     add(gC, sgA);
     add(gC, f_rgB1.get());
-    add(gC, neg(f_rsd1.get()));
+    add(gC, neg(pre.rsd1));
 
     const msm::RefPoint<F1> oA = msm::normalise(gA), oC = msm::normalise(gC);
     const msm::RefPoint<F2> oB = msm::normalise(gB2);
@@ -230,6 +254,107 @@ int assemble_shards(const KeyPoints &kp, const size_t tot[4], int world, const v
     return assemble<CURVE>(kp, r, s, &At, &Bg2, &Bg1, &Ht, &Lt, proof_out);
 }
 
+// ---- concurrent MSMs ----------------------------------------------------------------------------------
+// The prover's five MSMs are independent of each other (only H waits for the witness map). Each runs its
+// sort -> accumulate -> reduce pipeline in an execution slot of its own (runtime.hpp), driven by a host thread
+// of its own, so that the GPU always has bucket-accumulation work of one MSM in flight while another is in a
+// latency-bound stage. Slot plan: 0 (this thread) = witness map, then H; 1 = B.g2; 2 = A, then B.g1; 3 = L.
+struct MsmJob {
+    int k;             // blob order: 0 A, 1 B.g2, 2 B.g1, 3 H, 4 L
+    b200_bases_t set;
+    size_t n;
+    const void *scalars; // device
+    void *out;           // host point (windows_dev == false) or device window array
+    bool windows_dev;
+};
+struct JobResult {
+    int rc = B200_OK;
+    std::string err;
+};
+constexpr int MSM_SLOT[NUM_MSM] = {2, 1, 2, 0, 3};
+
+// Tuning knobs (environment, read per call): B200_MSM_SLOTS = five slot numbers "A,Bg2,Bg1,H,L" overriding the plan
+// above; B200_WM_FIRST = 0 starts the other slots before the witness map instead of after it.
+void slot_plan(int plan[NUM_MSM], bool *wm_first)
+{
+    for (int k = 0; k < NUM_MSM; ++k) {
+        plan[k] = MSM_SLOT[k];
+    }
+    if (const char *e = getenv("B200_MSM_SLOTS")) {
+        int v[NUM_MSM];
+        if (sscanf(e, "%d,%d,%d,%d,%d", &v[0], &v[1], &v[2], &v[3], &v[4]) == NUM_MSM) {
+            for (int k = 0; k < NUM_MSM; ++k) {
+                plan[k] = v[k] < 0 || v[k] >= rt::NUM_SLOTS ? 0 : v[k];
+            }
+        }
+    }
+    const char *w = getenv("B200_WM_FIRST");
+    *wm_first = !(w && w[0] == '0');
+}
+
+int run_job(const MsmJob &j, double *ms5)
+{
+    const double t0 = now_ms();
+    const int rc = j.windows_dev ? b200_msm_resident_windows_dev(j.set, 0, j.n, j.scalars, 1, j.out)
+                                 : b200_msm_resident(j.set, 0, j.n, j.scalars, 1, j.out);
+    if (ms5) {
+        ms5[j.k] = now_ms() - t0;
+    }
+    return rc;
+}
+
+JobResult run_slot_jobs(int slot, std::vector<MsmJob> jobs, double *ms5)
+{
+    JobResult r;
+    r.rc = rt::bind_thread(slot);
+    for (size_t i = 0; i < jobs.size() && r.rc == B200_OK; ++i) {
+        r.rc = run_job(jobs[i], ms5);
+    }
+    if (r.rc != B200_OK) {
+        r.err = rt::last_error(); // thread-local: carry the text back to the calling thread
+    }
+    return r;
+}
+
+// Runs `jobs` (any subset of the five MSMs) over the slots; `before_h`, if set, runs on this thread ahead of the H
+// job (the witness map). Returns the first failure.
+template<class BeforeH> int run_msms(const std::vector<MsmJob> &jobs, double *ms5, BeforeH before_h)
+{
+    int plan[NUM_MSM];
+    bool wm_first = true;
+    slot_plan(plan, &wm_first);
+    std::vector<MsmJob> per_slot[rt::NUM_SLOTS];
+    for (const MsmJob &j : jobs) {
+        per_slot[plan[j.k]].push_back(j);
+    }
+    std::future<JobResult> fut[rt::NUM_SLOTS];
+    // The witness map is integer-pipe work like the accumulations, so overlapping it buys nothing — and its ~25 short
+    // launches each queue behind resident accumulate CTAs (measured: 13 ms instead of 2 ms). It runs alone, first.
+    int rc = wm_first ? before_h() : B200_OK;
+    for (int sl = 1; sl < rt::NUM_SLOTS && rc == B200_OK; ++sl) {
+        if (!per_slot[sl].empty()) {
+            fut[sl] = std::async(std::launch::async, run_slot_jobs, sl, per_slot[sl], ms5);
+        }
+    }
+    if (!wm_first) {
+        rc = before_h();
+    }
+    for (size_t i = 0; i < per_slot[0].size() && rc == B200_OK; ++i) {
+        rc = run_job(per_slot[0][i], ms5);
+    }
+    std::string err = rc != B200_OK ? rt::last_error() : "";
+    for (int sl = 1; sl < rt::NUM_SLOTS; ++sl) {
+        if (fut[sl].valid()) {
+            const JobResult r = fut[sl].get();
+            if (rc == B200_OK && r.rc != B200_OK) {
+                rc = r.rc;
+                err = r.err;
+            }
+        }
+    }
+    return rc == B200_OK ? B200_OK : rt::set_error(rc, "%s", err.c_str());
+}
+
 ProvingKey *find_key(b200_groth16_pk_t handle)
 {
     auto it = g_keys.find(handle);
@@ -285,45 +410,100 @@ int upload_witness(const ProvingKey &pk, const void *primary_input, const void *
     return B200_OK;
 }
 
-// The MSMs of this rank's shards selected by `mask` (bit k = MSM k in blob order A, B.g2, B.g1, H, L).
-int shard_msms(const ProvingKey &pk, unsigned mask, void *dev_blob, double *ms5)
+// The MSMs of this rank's shards selected by `mask` (bit k = MSM k in blob order A, B.g2, B.g1, H, L), run
+// concurrently (run_msms); with_witness_map computes coefficients_for_H on this thread first.
+int shard_msms(const ProvingKey &pk, unsigned mask, void *dev_blob, double *ms5, bool with_witness_map, double *wm_ms)
 {
     const size_t fr = b200_sizeof_fr(pk.curve);
     const BlobLayout L = blob_layout(pk.curve, pk.tot, pk.world);
     const b200_bases_t sets[NUM_MSM] = {pk.A, pk.B_g2, pk.B_g1, pk.H, pk.L};
     const uint8_t *w = static_cast<const uint8_t *>(pk.d_w);
     const void *scB = w + pk.first[1] * fr;
-    bool gathered = false;
-    for (int k = 0; k < NUM_MSM; ++k) {
-        const size_t cnt = pk.cnt[MSM_QUERY[k]];
-        if (!(mask >> k & 1u) || !cnt) {
-            continue;
-        }
-        const double t0 = now_ms();
-        const void *sc = nullptr;
-        switch (k) {
-        case 0: sc = w + pk.first[0] * fr; break;
-        case 1:
-        case 2:
-            if (pk.d_B_idx && !gathered) {
-                if (int rc = b200_gather_dev(pk.curve, pk.d_w, static_cast<const uint32_t *>(pk.d_B_idx), cnt, pk.d_g)) {
-                    return rc;
-                }
-                gathered = true;
-            }
-            sc = pk.d_B_idx ? pk.d_g : scB;
-            break;
-        case 3: sc = static_cast<const uint8_t *>(pk.d_h) + pk.first[2] * fr; break;
-        default: sc = w + (pk.ni + 1 + pk.first[3]) * fr; break;
-        }
-        if (int rc = b200_msm_resident_windows_dev(sets[k], 0, cnt, sc, 1, static_cast<uint8_t *>(dev_blob) + L.off[k])) {
+    if (pk.d_B_idx && (mask & 6u) && pk.cnt[1]) {
+        if (int rc = b200_gather_dev(pk.curve, pk.d_w, static_cast<const uint32_t *>(pk.d_B_idx), pk.cnt[1], pk.d_g)) {
             return rc;
         }
-        if (ms5) {
-            ms5[k] += now_ms() - t0;
+        scB = pk.d_g;
+    }
+    const void *sc[NUM_MSM] = {w + pk.first[0] * fr, scB, scB, static_cast<const uint8_t *>(pk.d_h) + pk.first[2] * fr,
+                               w + (pk.ni + 1 + pk.first[3]) * fr};
+    std::vector<MsmJob> jobs;
+    for (int k = 0; k < NUM_MSM; ++k) {
+        const size_t cnt = pk.cnt[MSM_QUERY[k]];
+        if ((mask >> k & 1u) && cnt) {
+            jobs.push_back(MsmJob{k, sets[k], cnt, sc[k], static_cast<uint8_t *>(dev_blob) + L.off[k], true});
         }
     }
-    return B200_OK;
+    return run_msms(jobs, ms5, [&]() -> int {
+        if (!with_witness_map) {
+            return B200_OK;
+        }
+        const double t0 = now_ms();
+        const int rc = b200_witness_map_r1cs_dev(pk.r1cs, pk.d_w, pk.m, pk.d_h);
+        if (wm_ms) {
+            *wm_ms = now_ms() - t0;
+        }
+        return rc;
+    });
+}
+
+// r1cs_gg_ppzksnark_prover over a one-GPU key (b200_groth16_prove).
+template<int CURVE>
+int prove_impl(const ProvingKey &pk, const void *primary_input, const void *auxiliary_input, const void *r, const void *s,
+               void *proof_out, double *stage_ms)
+{
+    const size_t fr = b200_sizeof_fr(pk.curve);
+    const size_t g1 = b200_sizeof_group(pk.curve, B200_G1), g2 = b200_sizeof_group(pk.curve, B200_G2);
+    const double t0 = now_ms();
+    double st[7] = {0, 0, 0, 0, 0, 0, 0};
+    const KeyPoints kp = {pk.alpha_g1.data(), pk.beta_g1.data(), pk.beta_g2.data(), pk.delta_g1.data(), pk.delta_g2.data()};
+    // host work that needs only r, s and the key goes first, beside everything else
+    auto f_pre = std::async(std::launch::async, [&]() { return pre_assemble<CURVE>(kp, r, s); });
+
+    int rc;
+    if ((rc = upload_witness(pk, primary_input, auxiliary_input))) {
+        return rc;
+    }
+    st[0] = now_ms() - t0;
+    std::vector<uint8_t> At(g1), Bg1(g1), Ht(g1), Lt(g1), Bg2(g2);
+    const void *scB = pk.d_w;
+    if (pk.d_B_idx) {
+        if ((rc = b200_gather_dev(pk.curve, pk.d_w, static_cast<const uint32_t *>(pk.d_B_idx), pk.nB, pk.d_g))) {
+            return rc;
+        }
+        scB = pk.d_g;
+    }
+    // the five MSMs side by side (run_msms); this thread computes H's scalars first
+    double msm_ms[NUM_MSM] = {0, 0, 0, 0, 0};
+    const std::vector<MsmJob> jobs = {
+        {0, pk.A, pk.nv + 1, pk.d_w, At.data(), false},
+        {1, pk.B_g2, pk.nB, scB, Bg2.data(), false},
+        {2, pk.B_g1, pk.nB, scB, Bg1.data(), false},
+        {3, pk.H, pk.m - 1, pk.d_h, Ht.data(), false},
+        {4, pk.L, pk.nv - pk.ni, static_cast<const uint8_t *>(pk.d_w) + (pk.ni + 1) * fr, Lt.data(), false},
+    };
+    rc = run_msms(jobs, msm_ms, [&]() -> int {
+        const double w0 = now_ms();
+        const int wrc = b200_witness_map_r1cs_dev(pk.r1cs, pk.d_w, pk.m, pk.d_h);
+        st[1] = now_ms() - w0;
+        return wrc;
+    });
+    if (rc) {
+        return rc;
+    }
+    // wall clock of each MSM inside its own slot; they overlap, so they do not add up to the total
+    st[2] = msm_ms[0];
+    st[3] = msm_ms[1] + msm_ms[2];
+    st[4] = msm_ms[3];
+    st[5] = msm_ms[4];
+    const PreAssembled<CURVE> pre = f_pre.get();
+    rc = assemble<CURVE>(kp, r, s, At.data(), Bg2.data(), Bg1.data(), Ht.data(), Lt.data(), proof_out, &pre);
+    st[6] = now_ms() - t0;
+    if (stage_ms) {
+        // witness upload | witness map | A | B | H | L | total (the last includes the host assembly)
+        memcpy(stage_ms, st, sizeof(st));
+    }
+    return rc;
 }
 
 } // namespace
@@ -437,66 +617,11 @@ int b200_groth16_prove(b200_groth16_pk_t handle, const void *primary_input, cons
     if (pk.ni && !primary_input) {
         return rt::set_error(B200_ERR_ARG, "null primary input");
     }
-    const size_t fr = b200_sizeof_fr(pk.curve);
-    const size_t g1 = b200_sizeof_group(pk.curve, B200_G1), g2 = b200_sizeof_group(pk.curve, B200_G2);
-    double t0 = now_ms(), t = t0, t1;
-    double st[7] = {0, 0, 0, 0, 0, 0, 0};
-
-    int rc;
-    if ((rc = upload_witness(pk, primary_input, auxiliary_input))) {
-        return rc;
-    }
-    t1 = now_ms(), st[0] = t1 - t, t = t1;
-    if ((rc = b200_witness_map_r1cs_dev(pk.r1cs, pk.d_w, pk.m, pk.d_h))) {
-        return rc;
-    }
-    t1 = now_ms(), st[1] = t1 - t, t = t1;
-
-    std::vector<uint8_t> At(g1), Bg1(g1), Ht(g1), Lt(g1), Bg2(g2);
-    if ((rc = b200_msm_resident(pk.A, 0, pk.nv + 1, pk.d_w, 1, At.data()))) {
-        return rc;
-    }
-    t1 = now_ms(), st[2] = t1 - t, t = t1;
-    const void *scB = pk.d_w;
-    if (pk.d_B_idx) {
-        if ((rc = b200_gather_dev(pk.curve, pk.d_w, static_cast<const uint32_t *>(pk.d_B_idx), pk.nB, pk.d_g))) {
-            return rc;
-        }
-        scB = pk.d_g;
-    }
-    if ((rc = b200_msm_resident(pk.B_g2, 0, pk.nB, scB, 1, Bg2.data())) ||
-        (rc = b200_msm_resident(pk.B_g1, 0, pk.nB, scB, 1, Bg1.data()))) {
-        return rc;
-    }
-    t1 = now_ms(), st[3] = t1 - t, t = t1;
-    if ((rc = b200_msm_resident(pk.H, 0, pk.m - 1, pk.d_h, 1, Ht.data()))) {
-        return rc;
-    }
-    t1 = now_ms(), st[4] = t1 - t, t = t1;
-    if ((rc = b200_msm_resident(pk.L, 0, pk.nv - pk.ni, static_cast<const uint8_t *>(pk.d_w) + (pk.ni + 1) * fr, 1,
-                                Lt.data()))) {
-        return rc;
-    }
-    t1 = now_ms(), st[5] = t1 - t, t = t1;
-
-    const KeyPoints kp = {pk.alpha_g1.data(), pk.beta_g1.data(), pk.beta_g2.data(), pk.delta_g1.data(), pk.delta_g2.data()};
     switch (pk.curve) {
-    case B200_ALT_BN128:
-        rc = assemble<CURVE_ALT_BN128>(kp, r, s, At.data(), Bg2.data(), Bg1.data(), Ht.data(), Lt.data(), proof_out);
-        break;
-    case B200_BLS12_377:
-        rc = assemble<CURVE_BLS12_377>(kp, r, s, At.data(), Bg2.data(), Bg1.data(), Ht.data(), Lt.data(), proof_out);
-        break;
-    default:
-        rc = assemble<CURVE_BW6_761>(kp, r, s, At.data(), Bg2.data(), Bg1.data(), Ht.data(), Lt.data(), proof_out);
-        break;
+    case B200_ALT_BN128: return prove_impl<CURVE_ALT_BN128>(pk, primary_input, auxiliary_input, r, s, proof_out, stage_ms);
+    case B200_BLS12_377: return prove_impl<CURVE_BLS12_377>(pk, primary_input, auxiliary_input, r, s, proof_out, stage_ms);
+    default: return prove_impl<CURVE_BW6_761>(pk, primary_input, auxiliary_input, r, s, proof_out, stage_ms);
     }
-    st[6] = now_ms() - t0;
-    if (stage_ms) {
-        // witness upload | witness map | A | B | H | L | total (the last includes the host assembly)
-        memcpy(stage_ms, st, sizeof(st));
-    }
-    return rc;
 }
 
 /* ---- sharded prover: one process per GPU, every query cut by base range ---------- */
@@ -652,7 +777,7 @@ int b200_groth16_shard_msm(b200_groth16_pk_t handle, unsigned mask, void *dev_bl
     if (!dev_blob) {
         return rt::set_error(B200_ERR_ARG, "null pointer");
     }
-    return shard_msms(*pk, mask, dev_blob, nullptr);
+    return shard_msms(*pk, mask, dev_blob, nullptr, false, nullptr);
 }
 
 int b200_groth16_prove_shard(b200_groth16_pk_t handle, const void *primary_input, const void *auxiliary_input,
@@ -672,13 +797,8 @@ int b200_groth16_prove_shard(b200_groth16_pk_t handle, const void *primary_input
     if (rc) {
         return rc;
     }
-    double t1 = now_ms();
-    st[0] = t1 - t0;
-    if ((rc = b200_witness_map_r1cs_dev(pk->r1cs, pk->d_w, pk->m, pk->d_h))) {
-        return rc;
-    }
-    st[1] = now_ms() - t1;
-    if ((rc = shard_msms(*pk, 0x1f, dev_blob, msm))) {
+    st[0] = now_ms() - t0;
+    if ((rc = shard_msms(*pk, 0x1f, dev_blob, msm, true, &st[1]))) {
         return rc;
     }
     st[2] = msm[0];

@@ -17,10 +17,10 @@ namespace msm
 struct Workspace {
     rt::DevBuf t, counts, offsets, cursor, task_off, tile_sums, entries, tasks, partial, chunk_out, staging, any_inf, multi;
 };
-inline Workspace &workspace()
+inline Workspace &workspace() // of the calling thread's execution slot (runtime.hpp)
 {
-    static Workspace ws;
-    return ws;
+    static Workspace ws[rt::NUM_SLOTS];
+    return ws[rt::slot()];
 }
 
 // Stages 6-7; defined in msm_cold.cuh and instantiated in msm_cold_<curve>_<group>.cu.

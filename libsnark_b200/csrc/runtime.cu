@@ -14,9 +14,11 @@ namespace
 {
 thread_local char g_err[512] = "";
 int g_device = -1;
-cudaStream_t g_stream = nullptr;
+cudaStream_t g_streams[NUM_SLOTS] = {nullptr, nullptr, nullptr, nullptr};
+#define g_stream g_streams[0]
+thread_local int g_slot = 0;
 std::atomic<uint64_t> g_launches{0};
-MsmTiming g_timing;
+MsmTiming g_timing[NUM_SLOTS];
 cudaEvent_t g_timer[2] = {nullptr, nullptr};
 } // namespace
 
@@ -46,9 +48,16 @@ static int do_init(int device)
     }
     B200_CUDA_CHECK(cudaSetDevice(device));
     if (!g_stream) {
-        B200_CUDA_CHECK(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking));
-        for (int i = 0; i < 5; ++i) {
-            B200_CUDA_CHECK(cudaEventCreate(&g_timing.ev[i]));
+        int least = 0, greatest = 0;
+        B200_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+        for (int k = 0; k < NUM_SLOTS; ++k) {
+            // numerically lower = higher priority: slot 0 highest, slot 1 next (the prover's G2 MSM, whose long
+            // bucket reduction should not be the last thing running), the others lowest
+            const int prio = k == 0 ? greatest : (k == 1 && greatest + 1 <= least) ? greatest + 1 : least;
+            B200_CUDA_CHECK(cudaStreamCreateWithPriority(&g_streams[k], cudaStreamNonBlocking, prio));
+            for (int i = 0; i < 5; ++i) {
+                B200_CUDA_CHECK(cudaEventCreate(&g_timing[k].ev[i]));
+            }
         }
     }
     g_device = device;
@@ -56,9 +65,22 @@ static int do_init(int device)
 }
 
 bool ensure_init() { return (g_stream && g_device >= 0) || do_init(0) == B200_OK; }
-cudaStream_t stream() { return g_stream; }
+cudaStream_t stream() { return g_streams[g_slot]; }
+int slot() { return g_slot; }
+int bind_thread(int slot)
+{
+    if (slot < 0 || slot >= NUM_SLOTS) {
+        return set_error(B200_ERR_ARG, "slot %d outside [0, %d)", slot, NUM_SLOTS);
+    }
+    if (!ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    B200_CUDA_CHECK(cudaSetDevice(g_device));
+    g_slot = slot;
+    return B200_OK;
+}
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
-MsmTiming &msm_timing() { return g_timing; }
+MsmTiming &msm_timing() { return g_timing[g_slot]; }
 
 int DevBuf::reserve(size_t bytes)
 {
@@ -67,7 +89,7 @@ int DevBuf::reserve(size_t bytes)
     }
     if (p) {
         // stream-ordered users of the old buffer must be done before it is freed
-        cudaStreamSynchronize(g_stream);
+        cudaStreamSynchronize(stream());
         cudaFree(p);
         p = nullptr;
         cap = 0;

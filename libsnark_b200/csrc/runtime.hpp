@@ -16,7 +16,15 @@ namespace rt
 int set_error(int code, const char *fmt, ...);
 const char *last_error();
 bool ensure_init();         // true when a device is bound (b200_init called or lazily device 0)
-cudaStream_t stream();      // the library's compute stream
+// Execution slots: a slot = one stream + one set of MSM workspaces + one timing record. A host thread works in
+// exactly one slot (0 unless it called bind_thread); the prover runs its independent MSMs in different slots on
+// different host threads so that the latency-bound stages of one (sort, bucket reduction, host fold) overlap the
+// integer-pipe-bound bucket accumulation of another. Slot 0 has the highest stream priority (it carries the
+// witness map, which the H MSM waits for).
+constexpr int NUM_SLOTS = 4;
+int slot();                 // the calling host thread's slot
+int bind_thread(int slot);  // call first in a new host thread: selects the slot and the library's device
+cudaStream_t stream();      // the compute stream of the calling thread's slot
 void count_launch(int n = 1);
 
 #define B200_CUDA_CHECK(expr)                                                                      \

@@ -14,5 +14,6 @@ timeout 900 $TR --master-port 29562 bench.py --gpus $N --steps 10 --warmup 3 > g
 head -c 600 gpurun_out/multi_n${N}_bench.json; tail -2 gpurun_out/multi_n${N}_bench.err
 timeout 1200 $TR --master-port 29563 tools/prove_multi.py --curve bls12_377 --log-m 22 --steps 3 --warmup 2 > gpurun_out/multi_n${N}_prove22_bls12_377.json 2> gpurun_out/multi_n${N}_prove22.err
 tail -c 600 gpurun_out/multi_n${N}_prove22_bls12_377.json; tail -2 gpurun_out/multi_n${N}_prove22.err
-timeout 1500 $TR --master-port 29564 tools/msm_sweep.py --curves bls12_377 bw6_761 --min-log 16 --max-log $MAXLOG --ref-max-log 0 --tables > gpurun_out/multi_n${N}_sweep.jsonl 2> gpurun_out/multi_n${N}_sweep.err
-cat gpurun_out/multi_n${N}_sweep.jsonl | cut -c1-330; tail -2 gpurun_out/multi_n${N}_sweep.err
+[ "$MAXLOG" -gt 0 ] && timeout 1500 $TR --master-port 29564 tools/msm_sweep.py --curves bls12_377 bw6_761 --min-log 16 --max-log $MAXLOG --ref-max-log 0 --tables > gpurun_out/multi_n${N}_sweep.jsonl 2> gpurun_out/multi_n${N}_sweep.err
+[ "$MAXLOG" -gt 0 ] && (cat gpurun_out/multi_n${N}_sweep.jsonl | cut -c1-330; tail -2 gpurun_out/multi_n${N}_sweep.err)
+exit 0
