@@ -233,6 +233,10 @@ int b200_groth16_prove_shard(b200_groth16_pk_t handle, const void *primary_input
  *   msm   : the partial MSMs selected by mask (bit 0 A, 1 B.g2, 2 B.g1, 3 H, 4 L) into their blob slots;
  *           H needs `h` first, the others only `begin`. */
 int b200_groth16_shard_begin(b200_groth16_pk_t handle, const void *primary_input, const void *auxiliary_input);
+/* The uploaded witness (1 | primary | auxiliary), (num_variables + 1) Fr, copied device-to-device between the key's
+ * buffer and dev_buf: to_key = 0 after `begin` on the rank that holds the witness, to_key = 1 on the ranks that
+ * received dev_buf by an NCCL broadcast — one host upload per proof instead of one per rank. */
+int b200_groth16_shard_witness_copy(b200_groth16_pk_t handle, void *dev_buf, int to_key);
 int b200_groth16_shard_chain(b200_groth16_pk_t handle, int which, void *dev_out);
 int b200_groth16_shard_h(b200_groth16_pk_t handle, void *dA, const void *dB, const void *dC);
 int b200_groth16_shard_msm(b200_groth16_pk_t handle, unsigned mask, void *dev_blob);

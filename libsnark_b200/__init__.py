@@ -41,7 +41,7 @@ EXPORTS = [
     "b200_witness_chain_r1cs_dev", "b200_witness_finish_dev",
     "b200_shard_range", "b200_groth16_shard_bytes", "b200_groth16_pk_create_shard", "b200_groth16_prove_shard",
     "b200_groth16_shard_begin", "b200_groth16_shard_chain", "b200_groth16_shard_h", "b200_groth16_shard_msm",
-    "b200_groth16_assemble", "b200_bases_precompute", "b200_bases_table_rows",
+    "b200_groth16_assemble", "b200_bases_precompute", "b200_bases_table_rows", "b200_groth16_shard_witness_copy",
 ]
 
 
@@ -119,6 +119,7 @@ def lib():
         L.b200_groth16_prove_shard.argtypes = [u64, vp, vp, vp, C.POINTER(C.c_double)]
         L.b200_groth16_shard_begin.argtypes = [u64, vp, vp]
         L.b200_groth16_shard_chain.argtypes = [u64, i, vp]
+        L.b200_groth16_shard_witness_copy.argtypes = [u64, vp, i]
         L.b200_groth16_shard_h.argtypes = [u64, vp, vp, vp]
         L.b200_groth16_shard_msm.argtypes = [u64, C.c_uint, vp]
         L.b200_groth16_assemble.argtypes = [i, vp, vp, vp, vp, vp, C.POINTER(sz), i, vp, vp, vp, vp]
@@ -551,6 +552,9 @@ class Groth16ProvingKeyShard:
         pi, ai = _u64(primary_input), _u64(auxiliary_input)
         _check(lib().b200_groth16_shard_begin(self.handle, _p(pi), _p(ai)))
 
+    def witness_copy(self, dev_buf, to_key):
+        _check(lib().b200_groth16_shard_witness_copy(self.handle, C.c_void_p(dev_buf), int(to_key)))
+
     def chain(self, which, dev_out):
         _check(lib().b200_groth16_shard_chain(self.handle, which, C.c_void_p(dev_out)))
 
@@ -593,10 +597,26 @@ class DistributedProver:
         self.gathered = torch.zeros(shard.world * shard.blob_bytes, dtype=torch.uint8, device=self.dev)
         self.chains = ([torch.empty(shard.m * shard.fr_bytes, dtype=torch.uint8, device=self.dev) for _ in range(3)]
                        if self.chain_parallel else None)
+        self.wbuf = (torch.empty((shard.r1cs.nv + 1) * shard.fr_bytes, dtype=torch.uint8, device=self.dev)
+                     if shard.world > 1 else None)
+
+    def _distribute_witness(self, primary_input, auxiliary_input):
+        """Rank 0 uploads the witness once; the other ranks get it over NVLink (NCCL broadcast) — the witness lives in one
+        process, and eight host uploads of it would share one host memory system."""
+        pk = self.pk
+        if pk.rank == 0:
+            pk.begin(primary_input, auxiliary_input)
+            if pk.world > 1:
+                pk.witness_copy(self.wbuf.data_ptr(), 0)
+        if pk.world > 1:
+            self.dist.broadcast(self.wbuf, src=0)
+            self.torch.cuda.current_stream().synchronize()
+            if pk.rank != 0:
+                pk.witness_copy(self.wbuf.data_ptr(), 1)
 
     def prove(self, primary_input, auxiliary_input, r, s, fold_on_all_ranks=False):
-        """The proof on rank 0 (on every rank with fold_on_all_ranks), None elsewhere. self.last_stages holds this
-        rank's host wall clock per phase in ms."""
+        """The proof on rank 0 (on every rank with fold_on_all_ranks), None elsewhere. Only rank 0 reads primary_input and
+        auxiliary_input. self.last_stages holds this rank's host wall clock per phase in ms."""
         import time
         torch, dist, pk = self.torch, self.dist, self.pk
         t = [time.perf_counter()]
@@ -605,9 +625,9 @@ class DistributedProver:
         def lap(name):
             t.append(time.perf_counter())
             names.append(name)
+        self._distribute_witness(primary_input, auxiliary_input)
+        lap("upload_broadcast")
         if self.chain_parallel:
-            pk.begin(primary_input, auxiliary_input)
-            lap("upload")
             if pk.rank < 3:
                 pk.chain(pk.rank, self.chains[pk.rank].data_ptr())
             lap("chain")
@@ -623,9 +643,10 @@ class DistributedProver:
             pk.msm(MSM_H, self.blob.data_ptr())
             lap("msm_H")
         else:
-            st = pk.prove_shard(primary_input, auxiliary_input, self.blob.data_ptr())
-            lap("prove_shard")
-            self.last_shard_stages = st
+            pk.h()
+            lap("witness_map")
+            pk.msm(MSM_A | MSM_B_G2 | MSM_B_G1 | MSM_H | MSM_L, self.blob.data_ptr())
+            lap("msm")
         if pk.world > 1:
             dist.all_gather_into_tensor(self.gathered, self.blob)
             src = self.gathered

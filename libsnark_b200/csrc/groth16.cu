@@ -744,6 +744,23 @@ int b200_groth16_shard_begin(b200_groth16_pk_t handle, const void *primary_input
     return upload_witness(*pk, primary_input, auxiliary_input);
 }
 
+int b200_groth16_shard_witness_copy(b200_groth16_pk_t handle, void *dev_buf, int to_key)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    const ProvingKey *pk = find_key(handle);
+    if (!pk) {
+        return B200_ERR_HANDLE;
+    }
+    if (!dev_buf) {
+        return rt::set_error(B200_ERR_ARG, "null pointer");
+    }
+    const size_t bytes = (pk->nv + 1) * b200_sizeof_fr(pk->curve);
+    cudaStream_t st = rt::stream();
+    B200_CUDA_CHECK(cudaMemcpyAsync(to_key ? pk->d_w : dev_buf, to_key ? dev_buf : pk->d_w, bytes, cudaMemcpyDeviceToDevice, st));
+    B200_CUDA_CHECK(cudaStreamSynchronize(st));
+    return B200_OK;
+}
+
 int b200_groth16_shard_chain(b200_groth16_pk_t handle, int which, void *dev_out)
 {
     std::lock_guard<std::mutex> lk(g_mu);

@@ -248,8 +248,8 @@ HD void reduce_chunk_body(
     // chunk_out: where this thread's weighted sum goes (a register/local struct in the kernel)
     XYZZ<F> run = XYZZ<F>::inf();
     XYZZ<F> sum = XYZZ<F>::inf();
-    const size_t b0 = gidx * CHUNK;
-    for (int k = CHUNK - 1; k >= 0; --k) {
+    const size_t b0 = gidx * g.chunk;
+    for (int k = (int)g.chunk - 1; k >= 0; --k) {
         const uint32_t t0 = task_off[b0 + k];
         const uint32_t t1 = task_off[b0 + k + 1];
         // up to g.collapse partial sums are added here; beyond that k_collapse has already
@@ -262,7 +262,7 @@ HD void reduce_chunk_body(
         add_cold(sum, run);
     }
     // sum = sum_k (k+1) S_k ; the chunk starts at local bucket m = (gidx % cpw) * CHUNK, so add m * run.
-    const uint32_t m = (uint32_t)(gidx % g.cpw) * CHUNK;
+    const uint32_t m = (uint32_t)(gidx % g.cpw) * g.chunk;
     if (m != 0 && !run.is_inf()) {
         XYZZ<F> acc = run;
         int top = 31;

@@ -32,6 +32,7 @@ struct Geometry {
     // [2^(c w)] P (make_table_geometry): bstride = 0, estride = the table's row length — every window feeds
     // the SAME B buckets with the matching multiple of the base, and the W-fold reduction becomes one.
     uint32_t bstride, estride;
+    uint32_t chunk; // buckets per reduce thread (CHUNK; smaller over tables, see make_table_geometry)
 };
 
 // Window width: minimise  W(c) * (10 n + 100 * 2^(c-1))  field mults (10 per mixed add,
@@ -61,6 +62,7 @@ inline Geometry make_geometry(uint64_t n, int scalar_bits, int force_c = 0)
     g.collapse = (uint32_t)(2 * avg_tasks + 2 > (uint64_t)COLLAPSE_TASKS ? 2 * avg_tasks + 2 : (uint64_t)COLLAPSE_TASKS);
     g.bstride = g.B;
     g.estride = 0;
+    g.chunk = CHUNK;
     return g;
 }
 
@@ -83,12 +85,22 @@ inline int table_window_bits(uint64_t n, int scalar_bits)
 
 // Geometry of an MSM over n points of a table of row length `row` built for window width c.
 // The digit extraction sees W windows; everything after the scatter sees ONE window of B buckets.
-inline Geometry make_table_geometry(uint64_t n, int scalar_bits, int c, uint64_t row)
+// The single bucket set is reduced by B / chunk threads, each a serial chain of group additions at a fraction
+// of a warp per scheduler (ncu: 6 % occupancy, latency-bound): with ONE window there are W times fewer reduce
+// threads than in the plain geometry, so the chunk is cut to TABLE_CHUNK buckets to shorten every chain.
+constexpr int TABLE_CHUNK = 2;
+inline Geometry make_table_geometry(uint64_t n, int scalar_bits, int c, uint64_t row, int chunk = TABLE_CHUNK)
 {
     Geometry g = make_geometry(n, scalar_bits, c);
     g.bstride = 0;
     g.estride = (uint32_t)row;
     g.NB = g.B;
+    if (chunk > 0 && (uint32_t)chunk <= g.B && g.B % (uint32_t)chunk == 0) {
+        g.chunk = (uint32_t)chunk;
+        g.cpw = g.B / g.chunk;
+        g.rb = g.cpw < (uint32_t)REDUCE_BLOCK ? g.cpw : (uint32_t)REDUCE_BLOCK;
+        g.opw = g.cpw / g.rb;
+    }
     const uint64_t avg_tasks = ((uint64_t)g.W * n / g.B + SEG - 1) / SEG;
     g.collapse = (uint32_t)(2 * avg_tasks + 2 > (uint64_t)COLLAPSE_TASKS ? 2 * avg_tasks + 2 : (uint64_t)COLLAPSE_TASKS);
     return g;

@@ -80,9 +80,9 @@ def run(b, torch, dist, curve, log_m, steps, warmup, chain_parallel=None, check=
            "min_ms": float(np.min(times)), "higher_is_better": False, "n_gpus": world, "scaling": "strong",
            "steps": steps, "warmup": warmup, "chain_parallel_witness_map": bool(prover.chain_parallel), "precomputed_tables": bool(tables),
            "sizes": {"num_constraints": sy["nc"], "num_inputs": ni, "num_variables": nv, "domain": m},
-           "h2d_bytes_per_step_per_rank": int((nv + 1) * b.sizeof_fr(curve)),
+           "h2d_bytes_per_step": int((nv + 1) * b.sizeof_fr(curve)), "witness_broadcast_bytes": int((nv + 1) * b.sizeof_fr(curve)) if world > 1 else 0,
            "allgather_bytes_per_rank": int(pk.blob_bytes), "setup_s": setup_s,
-           "note": "wall clock, max over ranks, around DistributedProver.prove: witness (host, every rank) -> H2D -> witness map "
+           "note": "wall clock, max over ranks, around DistributedProver.prove: witness (host, rank 0) -> H2D -> NCCL broadcast -> witness map "
                    "(replicated, or the A/B/C chains on ranks 0-2 + NCCL broadcast) -> this rank's shard of the A, B(G2+G1), H, L "
                    "MSMs -> NCCL all-gather of the window sums -> host fold and proof assembly on rank 0"}
     out["stages_rank0_ms"] = {k: round(v, 3) for k, v in prover.last_stages.items()}
