@@ -336,12 +336,15 @@ def run_b200_arm(args):
             "unit": "Tmad/s (32x32+64 multiply-adds)", "frac": ach / wide,
             # dram__bytes_read.sum + dram__bytes_write.sum of one k_accumulate launch at this workload,
             # profiles/r1_ncu_full_msm.md (ncu --set full); algorithmic bytes are 68 B per mixed add
-            "traffic": 525.8e6 if not table_rows else None, "algorithmic_bytes": 68.0 * W_acc * n,
+            # dram__bytes_read.sum + dram__bytes_write.sum of one k_accumulate launch (ncu --set full): over the tables
+            # profiles/r1s5_ncu_tables_msm.md, without them profiles/r1_ncu_full_msm.md
+            "traffic": 2074.1e6 if table_rows else 525.8e6, "algorithmic_bytes": 68.0 * W_acc * n,
             "peak_source": "b200_imad_peak, measured in this run: chains of IMAD.WIDE.U32.X (the 32x32+64 multiply-add a "
                            "Montgomery product is made of; it holds the FMA-heavy pipe for two issue slots, 32 per clock "
                            "per SM). MEASURED_PEAKS.json has no integer figure.",
             "imad32_issue_peak": lo / 1e12, "frac_of_imad32_issue_peak": ach / lo,
-            "pipe_utilisation_ncu": 0.839,  # sm__pipe_fmaheavy_cycles_active, profiles/r1_ncu_full_msm.md
+            # sm__pipe_fmaheavy_cycles_active of the same captures
+            "pipe_utilisation_ncu": 0.868 if table_rows else 0.839,
             "whole_msm_achieved": msm_algorithmic_imads(n, c, W) / (ms_step * 1e-3) / 1e12,
             "kernel_ms": acc_ms,
         }
