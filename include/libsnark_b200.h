@@ -245,6 +245,15 @@ int b200_groth16_assemble(int curve, const void *alpha_g1, const void *beta_g1, 
                           const void *delta_g1, const void *delta_g2, const size_t query_sizes[4], int world,
                           const void *blobs, const void *r, const void *s, void *proof_out);
 
+/* ---- key generation: libff::batch_exp / batch_exp_with_coeff (multiexp.hpp, multiexp.tcc:879-946:
+ *      res[i] = windowed_exp(table of g, coeff * v[i])) followed by libff::batch_to_special (:949-974), which is how
+ *      r1cs_gg_ppzksnark_generator builds A_query, H_query, L_query and — through libsnark::kc_batch_exp
+ *      (kc_multiexp.tcc:147-239) — B_query (r1cs_gg_ppzksnark.tcc:321-398).
+ *      g: one point, reference layout, special form. coeff: one Fr (Montgomery) or NULL for 1. scalars: n Fr.
+ *      out: n points, reference layout, special form: (x, y, one), or zero() = (0, one, 0) where coeff * v[i] = 0. */
+int b200_batch_exp(int curve, int group, const void *g, const void *coeff, const void *scalars, size_t n,
+                   void *out);
+
 /* ---- measurement helpers (used by bench.py; not part of the reference surface) ------- */
 /* Integer-pipe microbenchmarks, multiply-adds per second: wide = 32x32+64 IMAD.WIDE.U32(.X) chains
  * (what a Montgomery product is made of; two issue slots each), lo = 32-bit IMAD (the pipe's

@@ -41,7 +41,7 @@ EXPORTS = [
     "b200_witness_chain_r1cs_dev", "b200_witness_finish_dev",
     "b200_shard_range", "b200_groth16_shard_bytes", "b200_groth16_pk_create_shard", "b200_groth16_prove_shard",
     "b200_groth16_shard_begin", "b200_groth16_shard_chain", "b200_groth16_shard_h", "b200_groth16_shard_msm",
-    "b200_groth16_assemble", "b200_bases_precompute", "b200_bases_table_rows", "b200_groth16_shard_witness_copy",
+    "b200_groth16_assemble", "b200_bases_precompute", "b200_bases_table_rows", "b200_groth16_shard_witness_copy", "b200_batch_exp",
 ]
 
 
@@ -123,6 +123,7 @@ def lib():
         L.b200_groth16_shard_h.argtypes = [u64, vp, vp, vp]
         L.b200_groth16_shard_msm.argtypes = [u64, C.c_uint, vp]
         L.b200_groth16_assemble.argtypes = [i, vp, vp, vp, vp, vp, C.POINTER(sz), i, vp, vp, vp, vp]
+        L.b200_batch_exp.argtypes = [i, i, vp, vp, vp, sz, vp]
         L.b200_last_msm_timing.argtypes = [C.POINTER(C.c_double)]
         L.b200_launch_count.restype = u64
         L.b200_msm_resident_windows_dev.argtypes = [u64, sz, sz, vp, i, vp]
@@ -210,6 +211,17 @@ def kc_multi_exp_with_mixed_addition(curve, indices, values, min_idx, max_idx, s
     _check(lib().b200_kc_msm(c, _p(indices), _p(values), indices.shape[0], min_idx, max_idx, _p(scalars),
                              scalars.shape[0], _p(g2), _p(g1), None))
     return g2, g1
+
+
+def batch_exp(curve, group, g, scalars, coeff=None):
+    """libff::batch_exp (coeff None) / batch_exp_with_coeff followed by batch_to_special: (coeff * scalars[i]) * g for
+    every i, in special form (multiexp.tcc:879-974). g: one point in special form."""
+    c = _cid(curve)
+    g, scalars = _u64(g), _u64(scalars)
+    coeff = None if coeff is None else _u64(coeff)
+    out = np.zeros((scalars.shape[0], sizeof_group(c, group) // 8), dtype=np.uint64)
+    _check(lib().b200_batch_exp(c, group, _p(g), _p(coeff), _p(scalars), scalars.shape[0], _p(out)))
+    return out
 
 
 class ResidentBases:

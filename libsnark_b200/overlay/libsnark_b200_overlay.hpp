@@ -161,6 +161,54 @@ inline void release_cached_bases()
     bases_cache::get().clear();
 }
 
+// (coeff * v[i]) * g for every i, in special form: libff::batch_exp / batch_exp_with_coeff + batch_to_special
+// (multiexp.tcc:879-974). The base is entry [0][1] of the reference's window table (get_window_table, :808-844).
+template<typename GroupT, typename FieldT>
+std::vector<GroupT> batch_exp_special(const libff::window_table<GroupT> &table, const FieldT *coeff, const FieldT *v, size_t n)
+{
+    std::vector<GroupT> res(n, GroupT::zero());
+    if (n == 0) {
+        return res;
+    }
+    if (table.empty() || table[0].size() < 2) {
+        throw std::runtime_error("libsnark_b200: batch_exp needs a window table with at least two entries");
+    }
+    GroupT g = table[0][1];
+    g.to_special();
+    check(b200_batch_exp(curve_of<GroupT>::curve, curve_of<GroupT>::group, &g, coeff, v, n, res.data()), "b200_batch_exp");
+    return res;
+}
+
+// libsnark::kc_batch_exp (kc_multiexp.tcc:147-239): zeros of v are skipped, the rest become
+// (T1_coeff * v[i]) * g_T1 | (T2_coeff * v[i]) * g_T2, always in special form.
+template<typename T1, typename T2, typename FieldT>
+libsnark::knowledge_commitment_vector<T1, T2> kc_batch_exp_special(const libff::window_table<T1> &T1_table,
+                                                                   const libff::window_table<T2> &T2_table,
+                                                                   const FieldT &T1_coeff, const FieldT &T2_coeff,
+                                                                   const std::vector<FieldT> &v)
+{
+    libsnark::knowledge_commitment_vector<T1, T2> res;
+    res.domain_size_ = v.size();
+    std::vector<FieldT> nz;
+    for (size_t i = 0; i < v.size(); ++i) {
+        if (!v[i].is_zero()) {
+            nz.push_back(v[i]);
+            res.indices.push_back(i);
+        }
+    }
+    if (!libff::inhibit_profiling_info) {
+        libff::print_indent();
+        printf("Non-zero coordinate count: %zu/%zu (%0.2f%%)\n", nz.size(), v.size(), 100. * nz.size() / v.size());
+    }
+    const std::vector<T1> a = batch_exp_special<T1, FieldT>(T1_table, &T1_coeff, nz.data(), nz.size());
+    const std::vector<T2> b = batch_exp_special<T2, FieldT>(T2_table, &T2_coeff, nz.data(), nz.size());
+    res.values.reserve(nz.size());
+    for (size_t k = 0; k < nz.size(); ++k) {
+        res.values.emplace_back(libsnark::knowledge_commitment<T1, T2>(a[k], b[k]));
+    }
+    return res;
+}
+
 // sum_i scalar[i] * base[i] over contiguous host ranges (the reference's iterator pairs).
 template<typename GroupT, typename FieldT>
 GroupT msm_contiguous(const GroupT *bases, size_t n, const FieldT *scalars)
@@ -582,9 +630,37 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
     }                                                                                                                  \
     }
 
+// key generation: batch_exp (the 4-argument overload forwards to this one, multiexp.tcc:879-887),
+// batch_exp_with_coeff. The results come back in special form, which every caller accepts (group equality is
+// projective) and which r1cs_gg_ppzksnark_generator asks for anyway (batch_to_special, .tcc:353-386).
+#define B200_OVERLAY_BATCH_EXP(G, FR)                                                                                  \
+    namespace libff                                                                                                    \
+    {                                                                                                                  \
+    template<>                                                                                                         \
+    inline std::vector<G> batch_exp<G, FR>(const size_t, const size_t, const window_table<G> &table,                  \
+                                           const std::vector<FR> &v, size_t num_entries)                              \
+    {                                                                                                                  \
+        return libsnark_b200::batch_exp_special<G, FR>(table, nullptr, v.data(), num_entries);                         \
+    }                                                                                                                  \
+    template<>                                                                                                         \
+    inline std::vector<G> batch_exp_with_coeff<G, FR>(const size_t, const size_t, const window_table<G> &table,       \
+                                                      const FR &coeff, const std::vector<FR> &v)                      \
+    {                                                                                                                  \
+        return libsnark_b200::batch_exp_special<G, FR>(table, &coeff, v.data(), v.size());                             \
+    }                                                                                                                  \
+    }
+
 #define B200_OVERLAY_KC(G2T, G1T, FR)                                                                                  \
     namespace libsnark                                                                                                 \
     {                                                                                                                  \
+    template<>                                                                                                         \
+    inline knowledge_commitment_vector<G2T, G1T> kc_batch_exp<G2T, G1T, FR>(                                           \
+        const size_t, const size_t, const size_t, const libff::window_table<G2T> &T1_table,                            \
+        const libff::window_table<G1T> &T2_table, const FR &T1_coeff, const FR &T2_coeff, const std::vector<FR> &v,   \
+        const size_t, bool)                                                                                            \
+    {                                                                                                                  \
+        return libsnark_b200::kc_batch_exp_special<G2T, G1T, FR>(T1_table, T2_table, T1_coeff, T2_coeff, v);          \
+    }                                                                                                                  \
     template<>                                                                                                         \
     inline knowledge_commitment<G2T, G1T> kc_multi_exp_with_mixed_addition<                                            \
         G2T, G1T, FR, libff::multi_exp_method_BDLO12_signed, libff::multi_exp_base_form_special>(                      \
@@ -630,16 +706,22 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
 
 B200_OVERLAY_MSM(libff::alt_bn128_G1, libff::alt_bn128_Fr)
 B200_OVERLAY_MSM(libff::alt_bn128_G2, libff::alt_bn128_Fr)
+B200_OVERLAY_BATCH_EXP(libff::alt_bn128_G1, libff::alt_bn128_Fr)
+B200_OVERLAY_BATCH_EXP(libff::alt_bn128_G2, libff::alt_bn128_Fr)
 B200_OVERLAY_KC(libff::alt_bn128_G2, libff::alt_bn128_G1, libff::alt_bn128_Fr)
 B200_OVERLAY_NTT(libff::alt_bn128_Fr)
 
 B200_OVERLAY_MSM(libff::bls12_377_G1, libff::bls12_377_Fr)
 B200_OVERLAY_MSM(libff::bls12_377_G2, libff::bls12_377_Fr)
+B200_OVERLAY_BATCH_EXP(libff::bls12_377_G1, libff::bls12_377_Fr)
+B200_OVERLAY_BATCH_EXP(libff::bls12_377_G2, libff::bls12_377_Fr)
 B200_OVERLAY_KC(libff::bls12_377_G2, libff::bls12_377_G1, libff::bls12_377_Fr)
 B200_OVERLAY_NTT(libff::bls12_377_Fr)
 
 B200_OVERLAY_MSM(libff::bw6_761_G1, libff::bw6_761_Fr)
 B200_OVERLAY_MSM(libff::bw6_761_G2, libff::bw6_761_Fr)
+B200_OVERLAY_BATCH_EXP(libff::bw6_761_G1, libff::bw6_761_Fr)
+B200_OVERLAY_BATCH_EXP(libff::bw6_761_G2, libff::bw6_761_Fr)
 B200_OVERLAY_KC(libff::bw6_761_G2, libff::bw6_761_G1, libff::bw6_761_Fr)
 B200_OVERLAY_NTT(libff::bw6_761_Fr)
 

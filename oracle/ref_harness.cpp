@@ -250,6 +250,59 @@ template<typename ppT> struct H {
         return 0;
     }
 
+    // The reference's key-generation operators as r1cs_gg_ppzksnark_generator uses them (.tcc:321-398):
+    // get_exp_window_size + get_window_table + batch_exp / batch_exp_with_coeff + batch_to_special.
+    template<typename GroupT>
+    static int batch_exp_special(const void *g_, const void *coeff_, const void *scalars, size_t n, void *out)
+    {
+        GroupT g;
+        memcpy(&g, g_, sizeof(GroupT));
+        const FrT *sp = static_cast<const FrT *>(scalars);
+        const std::vector<FrT> v(sp, sp + n);
+        const size_t scalar_size = FrT::size_in_bits();
+        const size_t window = get_exp_window_size<GroupT>(n ? n : 1);
+        const window_table<GroupT> table = get_window_table(scalar_size, window, g);
+        std::vector<GroupT> res;
+        if (coeff_) {
+            FrT coeff;
+            memcpy(&coeff, coeff_, sizeof(FrT));
+            res = batch_exp_with_coeff(scalar_size, window, table, coeff, v);
+        } else {
+            res = batch_exp(scalar_size, window, table, v);
+        }
+        batch_to_special<GroupT>(res);
+        memcpy(out, res.data(), n * sizeof(GroupT));
+        return 0;
+    }
+
+    // libsnark::kc_batch_exp<G2, G1, Fr>(..., output_special = true) over v (zeros are skipped: sparse result).
+    // out_values: room for n (G2 | G1) pairs; out_indices: room for n; *nnz = entries written.
+    static int kc_batch_exp_special(const void *g2_, const void *g1_, const void *c2_, const void *c1_, const void *scalars,
+                                    size_t n, size_t chunks, void *out_values, uint64_t *out_indices, uint64_t *nnz)
+    {
+        G2T g2;
+        G1T g1;
+        FrT c2, c1;
+        memcpy(&g2, g2_, sizeof(G2T));
+        memcpy(&g1, g1_, sizeof(G1T));
+        memcpy(&c2, c2_, sizeof(FrT));
+        memcpy(&c1, c1_, sizeof(FrT));
+        const FrT *sp = static_cast<const FrT *>(scalars);
+        const std::vector<FrT> v(sp, sp + n);
+        const size_t scalar_size = FrT::size_in_bits();
+        const size_t w2 = get_exp_window_size<G2T>(n ? n : 1), w1 = get_exp_window_size<G1T>(n ? n : 1);
+        const window_table<G2T> t2 = get_window_table(scalar_size, w2, g2);
+        const window_table<G1T> t1 = get_window_table(scalar_size, w1, g1);
+        const knowledge_commitment_vector<G2T, G1T> r =
+            kc_batch_exp<G2T, G1T, FrT>(scalar_size, w2, w1, t2, t1, c2, c1, v, chunks, true);
+        *nnz = r.values.size();
+        memcpy(out_values, r.values.data(), r.values.size() * sizeof(knowledge_commitment<G2T, G1T>));
+        for (size_t i = 0; i < r.indices.size(); ++i) {
+            out_indices[i] = r.indices[i];
+        }
+        return 0;
+    }
+
     // out[i] = [s_i] * generator, normalised to special (affine) form.
     template<typename GroupT> static int scalar_mul_gen(const void *scalars, size_t n, void *out)
     {
@@ -909,6 +962,25 @@ static int make_bases_(int curve, int group, size_t n, uint64_t seed, void *out)
 API int ref_make_bases(int curve, int group, size_t n, uint64_t seed, void *out)
 {
     return make_bases_(curve, group, n, seed, out);
+}
+
+static int batch_exp_(int curve, int group, const void *g, const void *coeff, const void *s, size_t n, void *out)
+{
+    DISPATCH_GROUP(curve, group, batch_exp_special, g, coeff, s, n, out);
+}
+API int ref_batch_exp(int curve, int group, const void *g, const void *coeff, const void *s, size_t n, void *out)
+{
+    return batch_exp_(curve, group, g, coeff, s, n, out);
+}
+static int kc_batch_exp_(int curve, const void *g2, const void *g1, const void *c2, const void *c1, const void *s, size_t n,
+                         size_t chunks, void *out_values, uint64_t *out_indices, uint64_t *nnz)
+{
+    DISPATCH(curve, HH::kc_batch_exp_special(g2, g1, c2, c1, s, n, chunks, out_values, out_indices, nnz));
+}
+API int ref_kc_batch_exp(int curve, const void *g2, const void *g1, const void *c2, const void *c1, const void *s, size_t n,
+                         size_t chunks, void *out_values, uint64_t *out_indices, uint64_t *nnz)
+{
+    return kc_batch_exp_(curve, g2, g1, c2, c1, s, n, chunks, out_values, out_indices, nnz);
 }
 
 static int scalar_mul_gen_(int curve, int group, const void *s, size_t n, void *out)

@@ -64,6 +64,9 @@ class RefOracle:
         L.ref_group_op.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
         L.ref_make_bases.argtypes = [C.c_int, C.c_int, C.c_size_t, C.c_uint64, C.c_void_p]
         L.ref_scalar_mul_gen.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.ref_batch_exp.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.ref_kc_batch_exp.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t,
+                                       C.c_void_p, C.c_void_p, C.c_void_p]
         L.ref_msm.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]
         L.ref_kc_msm.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
                                  C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p, C.c_void_p]
@@ -174,6 +177,29 @@ class RefOracle:
         out = np.zeros((n, self._glimbs(curve, group)), dtype=np.uint64)
         assert self.lib.ref_make_bases(self.info(curve)["id"], group, n, seed, _p(out)) == 0
         return out
+
+    def batch_exp(self, curve, group, g, scalars, coeff=None):
+        """libff get_window_table + batch_exp (coeff None) / batch_exp_with_coeff + batch_to_special (multiexp.tcc:808-974)."""
+        g = np.ascontiguousarray(g, dtype=np.uint64)
+        scalars = np.ascontiguousarray(scalars, dtype=np.uint64)
+        coeff = None if coeff is None else np.ascontiguousarray(coeff, dtype=np.uint64)
+        out = np.zeros((scalars.shape[0], self._glimbs(curve, group)), dtype=np.uint64)
+        assert self.lib.ref_batch_exp(self.info(curve)["id"], group, _p(g), None if coeff is None else _p(coeff), _p(scalars),
+                                      scalars.shape[0], _p(out)) == 0
+        return out
+
+    def kc_batch_exp(self, curve, g2, g1, c2, c1, scalars, chunks=1):
+        """libsnark::kc_batch_exp<G2, G1, Fr>(..., output_special = true) -> (indices, values[nnz, G2 | G1])."""
+        g2, g1, c2, c1 = [np.ascontiguousarray(x, dtype=np.uint64) for x in (g2, g1, c2, c1)]
+        scalars = np.ascontiguousarray(scalars, dtype=np.uint64)
+        n = scalars.shape[0]
+        vals = np.zeros((n, self._glimbs(curve, G2) + self._glimbs(curve, G1)), dtype=np.uint64)
+        idx = np.zeros(n, dtype=np.uint64)
+        nnz = np.zeros(1, dtype=np.uint64)
+        assert self.lib.ref_kc_batch_exp(self.info(curve)["id"], _p(g2), _p(g1), _p(c2), _p(c1), _p(scalars), n, chunks, _p(vals),
+                                         _p(idx), _p(nnz)) == 0
+        k = int(nnz[0])
+        return idx[:k].copy(), vals[:k].copy()
 
     def scalar_mul_gen(self, curve, group, scalars):
         scalars = np.ascontiguousarray(scalars, dtype=np.uint64)

@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "curves.cuh"
+#include "batch_exp.cuh"
 #include "host_fold.hpp"
 #include "msm.cuh"
 
@@ -251,6 +252,39 @@ extern "C" int emu_msm_table(int curve, int group, const void *bases, size_t n, 
     case 6: return msm_emulated<bls12_377_fr, bls12_377_fq2>(bases, n, scalars, c, out, true);
     case 9:
     case 10: return msm_emulated<bw6_761_fr, bw6_761_fq>(bases, n, scalars, c, out, true);
+    }
+    return -100;
+}
+
+// batch_exp.cuh on the host: table build, one exp_body per scalar, normalise_body per group of K results.
+template<class Fr, class F> static int batch_exp_emulated(const void *g_ref, const void *coeff, const void *scalars, size_t n, void *out)
+{
+    msm::RefPoint<F> g;
+    memcpy(&g, g_ref, sizeof(g));
+    std::vector<Affine<F>> table;
+    if (!bexp::build_table<Fr, F>(g, table)) {
+        return -7;
+    }
+    std::vector<XYZZ<F>> acc(n);
+    for (size_t i = 0; i < n; ++i) {
+        bexp::exp_body<Fr, F>(i, (const Fr *)scalars, (const Fr *)coeff, table.data(), acc.data());
+    }
+    const size_t K = bexp::norm_group<F>();
+    for (size_t t = 0; t * K < n; ++t) {
+        bexp::normalise_body<F>(t, n, acc.data(), (msm::RefPoint<F> *)out);
+    }
+    return 0;
+}
+
+extern "C" int emu_batch_exp(int curve, int group, const void *g, const void *coeff, const void *scalars, size_t n, void *out)
+{
+    switch (curve * 4 + group) {
+    case 1: return batch_exp_emulated<alt_bn128_fr, alt_bn128_fq>(g, coeff, scalars, n, out);
+    case 2: return batch_exp_emulated<alt_bn128_fr, alt_bn128_fq2>(g, coeff, scalars, n, out);
+    case 5: return batch_exp_emulated<bls12_377_fr, bls12_377_fq>(g, coeff, scalars, n, out);
+    case 6: return batch_exp_emulated<bls12_377_fr, bls12_377_fq2>(g, coeff, scalars, n, out);
+    case 9:
+    case 10: return batch_exp_emulated<bw6_761_fr, bw6_761_fq>(g, coeff, scalars, n, out);
     }
     return -100;
 }

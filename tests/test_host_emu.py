@@ -40,6 +40,7 @@ def emu():
     L.emu_signed_digits.argtypes = [i, vp, sz, i, vp, C.POINTER(C.c_int)]
     L.emu_msm.argtypes = [i, i, vp, sz, vp, i, vp]
     L.emu_msm_table.argtypes = [i, i, vp, sz, vp, i, vp]
+    L.emu_batch_exp.argtypes = [i, i, vp, vp, vp, sz, vp]
     return L
 
 
@@ -151,3 +152,27 @@ def test_emulated_msm_over_precomputed_tables(emu, curve):
             got = _emu_msm_table(emu, curve, 1, g["family.bases"][:kk], g[f"family.scalars{kk}"], 12)
             assert np.array_equal(got, g[f"family.out{kk}"]), kk
         assert np.array_equal(_emu_msm_table(emu, curve, 1, g["edge.bases"], g["edge.scalars"], 9), g["edge.out"])
+
+
+@pytest.mark.parametrize("curve", list(CURVES))
+def test_emulated_batch_exp(emu, curve):
+    """batch_exp.cuh (fixed-base table, one mixed addition per 8-bit digit, simultaneous inversion) on the host ==
+    (coeff * v[i]) * g normalised, i.e. libff::batch_exp(_with_coeff) + batch_to_special, via the C oracle."""
+    from oracle import port
+    P = port.OraclePort()
+    g = np.load(os.path.join(GOLD, "msm.npz"))
+    for gname, gid in [("g1", 1), ("g2", 2)]:
+        k = f"rand.{curve}.{gname}"
+        base = np.ascontiguousarray(g[k + ".bases"][5])
+        sc = np.ascontiguousarray(g[k + ".scalars"][:11]).copy()
+        sc[3] = 0
+        one = np.load(os.path.join(GOLD, "fields.npz"))
+        coeff = np.ascontiguousarray(g[k + ".scalars"][20])
+        for c in (None, coeff):
+            out = np.zeros((sc.shape[0], base.shape[0]), dtype=np.uint64)
+            assert emu.emu_batch_exp(CURVES[curve], gid, _p(base), None if c is None else _p(c), _p(sc), sc.shape[0], _p(out)) == 0
+            eff = sc if c is None else P.field_op(curve, 0, 2, np.repeat(c[None, :], sc.shape[0], axis=0), sc)
+            for i in range(sc.shape[0]):
+                want = P.msm(curve, gid, base[None, :], eff[i:i + 1])
+                assert np.array_equal(out[i], want), (k, i, c is not None)
+        assert not out[3][2 * (base.shape[0] // 3):].any()       # zero scalar -> Z = 0
