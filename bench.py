@@ -393,6 +393,12 @@ def bench_groth16(b, log_m, steps, warmup, tables=True):
                              precompute=tables)
     setup_s = time.time() - t0
     rs = b.random_scalars(CURVE, 2, seed=99)
+    # the witness lies in page-locked host memory, as the e2e contract says (the library then skips its staging copy)
+    import torch
+    aux_pinned = torch.empty(sy["auxiliary"].shape, dtype=torch.int64, pin_memory=True)
+    aux_np = aux_pinned.numpy().view(np.uint64)
+    aux_np[:] = sy["auxiliary"]
+    sy = dict(sy, auxiliary=aux_np)
     proof = None
     for _ in range(warmup):
         proof, _ = pk.prove(sy["primary"], sy["auxiliary"], rs[0], rs[1])
@@ -437,10 +443,19 @@ def bench_ntt(b, torch, log_m, wide_peak):
         assert L.b200_ntt_dev(b.ALT_BN128, b.FFT, C.c_void_p(buf.ptr), m, None) == 0
     ms = b.timer_stop() / steps
     buf.free()
-    t0 = time.perf_counter()
-    out = b.get_evaluation_domain(CURVE, m).FFT(data)
-    e2e_ms = (time.perf_counter() - t0) * 1e3
-    del out
+    # e2e: the reference-facing call (b200_ntt = basic_radix2_domain<Fr>::FFT, in place on a HOST vector), here a
+    # page-locked one: H2D of the 2^24 elements, the transform, D2H of the result, all inside the timed call
+    pinned = torch.empty((m, 4), dtype=torch.int64, pin_memory=True)
+    pn = pinned.numpy().view(np.uint64)
+    pn[:] = data
+    assert L.b200_ntt(b.ALT_BN128, b.FFT, C.c_void_p(pn.ctypes.data), m, None) == 0
+    e2e = []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        assert L.b200_ntt(b.ALT_BN128, b.FFT, C.c_void_p(pn.ctypes.data), m, None) == 0
+        e2e.append((time.perf_counter() - t0) * 1e3)
+    e2e_ms = float(np.mean(e2e))
+    del pinned, pn
     peaks = measured_peaks()
     gbs = 2 * m * 32 / (ms * 1e-3) / 1e9
     return {"metric": "NTT elem/s", "log_m": log_m, "value": m / (ms * 1e-3), "unit": "elem/s", "ms": ms,

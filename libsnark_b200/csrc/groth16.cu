@@ -378,6 +378,21 @@ int upload_witness(const ProvingKey &pk, const void *primary_input, const void *
     }
     memcpy(w, one, fr);
     memcpy(w + fr, primary_input, pk.ni * fr);
+    {
+        // A caller that keeps its witness in page-locked memory (cudaHostAlloc / cudaHostRegister, e.g. a pinned torch
+        // tensor) needs no staging: the bulk goes to the device straight from where it lies.
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, auxiliary_input) == cudaSuccess && at.type == cudaMemoryTypeHost) {
+            cudaStream_t st0 = rt::stream();
+            const size_t head0 = (1 + pk.ni) * fr;
+            B200_CUDA_CHECK(cudaMemcpyAsync(pk.d_w, w, head0, cudaMemcpyHostToDevice, st0));
+            B200_CUDA_CHECK(cudaMemcpyAsync(static_cast<uint8_t *>(pk.d_w) + head0, auxiliary_input, (pk.nv - pk.ni) * fr,
+                                            cudaMemcpyHostToDevice, st0));
+            B200_CUDA_CHECK(cudaStreamSynchronize(st0));
+            return B200_OK;
+        }
+        cudaGetLastError(); // an unregistered pointer may leave an error behind on old runtimes
+    }
     // The auxiliary input is the bulk (32 MiB at 2^20, 128 MiB at 2^22) and one core copies at ~10 GB/s: stage it into
     // the pinned buffer with a few threads, and send each slice to the device as soon as it is staged.
     const size_t head = (1 + pk.ni) * fr, bulk = (pk.nv - pk.ni) * fr;
