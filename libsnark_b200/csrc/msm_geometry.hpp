@@ -35,6 +35,34 @@ struct Geometry {
     uint32_t chunk; // buckets per reduce thread (CHUNK; smaller over tables, see make_table_geometry)
 };
 
+// Buckets per reduce thread. The reduction is a serial chain of group additions per thread, run at a fraction of
+// a warp per scheduler (ncu: 6 % occupancy). While the reduce threads number well under one wave of the machine,
+// halving the chunk shortens every chain and costs nothing: over tables (one bucket set, 2^16 buckets) 8 -> 2
+// buckets per thread takes alt_bn128 G1 from 0.76 to 0.57 ms and bw6_761 from 4.6 to 3.2 ms
+// (profiles/r1s5_reduce_chunk_tune.log). Once the threads approach a full wave (4 reduce CTAs per SM) the kernel
+// is throughput-bound and every extra thread's offset multiplication is paid in full: the plain 2^20 geometry
+// (17 x 2^14 buckets) with 4 instead of 8 buckets per thread went from 0.56 to 0.75 ms. Hence: the smallest chunk
+// that keeps the thread count under about half a wave.
+constexpr uint64_t REDUCE_THREADS_TARGET = 40000;
+inline uint32_t pick_chunk(uint64_t buckets)
+{
+    uint32_t chunk = CHUNK;
+    while (chunk > 2 && buckets / (chunk / 2) <= REDUCE_THREADS_TARGET) {
+        chunk /= 2;
+    }
+    return chunk;
+}
+inline void set_chunk(Geometry &g, uint32_t chunk)
+{
+    if (chunk == 0 || chunk > g.B || g.B % chunk != 0) {
+        chunk = g.B < (uint32_t)CHUNK ? g.B : (uint32_t)CHUNK;
+    }
+    g.chunk = chunk;
+    g.cpw = g.B / g.chunk;
+    g.rb = g.cpw < (uint32_t)REDUCE_BLOCK ? g.cpw : (uint32_t)REDUCE_BLOCK;
+    g.opw = g.cpw / g.rb;
+}
+
 // Window width: minimise  W(c) * (10 n + 100 * 2^(c-1))  field mults (10 per mixed add,
 // ~100 per bucket in the reduction as measured: the reduction runs at low occupancy), c in [5, 20].
 inline Geometry make_geometry(uint64_t n, int scalar_bits, int force_c = 0)
@@ -55,14 +83,11 @@ inline Geometry make_geometry(uint64_t n, int scalar_bits, int force_c = 0)
     g.W = (scalar_bits + 1 + g.c - 1) / g.c;
     g.B = 1u << (g.c - 1);
     g.NB = (uint32_t)g.W * g.B;
-    g.cpw = g.B / CHUNK;
-    g.rb = g.cpw < (uint32_t)REDUCE_BLOCK ? g.cpw : (uint32_t)REDUCE_BLOCK;
-    g.opw = g.cpw / g.rb;
+    set_chunk(g, pick_chunk((uint64_t)g.W * g.B));
     const uint64_t avg_tasks = (n / g.B + SEG - 1) / SEG;
     g.collapse = (uint32_t)(2 * avg_tasks + 2 > (uint64_t)COLLAPSE_TASKS ? 2 * avg_tasks + 2 : (uint64_t)COLLAPSE_TASKS);
     g.bstride = g.B;
     g.estride = 0;
-    g.chunk = CHUNK;
     return g;
 }
 
@@ -85,22 +110,13 @@ inline int table_window_bits(uint64_t n, int scalar_bits)
 
 // Geometry of an MSM over n points of a table of row length `row` built for window width c.
 // The digit extraction sees W windows; everything after the scatter sees ONE window of B buckets.
-// The single bucket set is reduced by B / chunk threads, each a serial chain of group additions at a fraction
-// of a warp per scheduler (ncu: 6 % occupancy, latency-bound): with ONE window there are W times fewer reduce
-// threads than in the plain geometry, so the chunk is cut to TABLE_CHUNK buckets to shorten every chain.
-constexpr int TABLE_CHUNK = 2;
-inline Geometry make_table_geometry(uint64_t n, int scalar_bits, int c, uint64_t row, int chunk = TABLE_CHUNK)
+inline Geometry make_table_geometry(uint64_t n, int scalar_bits, int c, uint64_t row, int chunk = 0)
 {
     Geometry g = make_geometry(n, scalar_bits, c);
     g.bstride = 0;
     g.estride = (uint32_t)row;
     g.NB = g.B;
-    if (chunk > 0 && (uint32_t)chunk <= g.B && g.B % (uint32_t)chunk == 0) {
-        g.chunk = (uint32_t)chunk;
-        g.cpw = g.B / g.chunk;
-        g.rb = g.cpw < (uint32_t)REDUCE_BLOCK ? g.cpw : (uint32_t)REDUCE_BLOCK;
-        g.opw = g.cpw / g.rb;
-    }
+    set_chunk(g, chunk > 0 ? (uint32_t)chunk : pick_chunk(g.B)); // ONE bucket set: W times fewer reduce threads
     const uint64_t avg_tasks = ((uint64_t)g.W * n / g.B + SEG - 1) / SEG;
     g.collapse = (uint32_t)(2 * avg_tasks + 2 > (uint64_t)COLLAPSE_TASKS ? 2 * avg_tasks + 2 : (uint64_t)COLLAPSE_TASKS);
     return g;

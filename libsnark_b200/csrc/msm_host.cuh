@@ -131,7 +131,7 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
     // Over a table the whole sum comes out as "window 0" and the other windows are the point at infinity,
     // which the Horner fold passes through unchanged.
     const Geometry pub = make_geometry(n, Fr::params::BITS);
-    static const int table_chunk = getenv("B200_TABLE_CHUNK") ? atoi(getenv("B200_TABLE_CHUNK")) : TABLE_CHUNK; // tuning knob
+    static const int table_chunk = getenv("B200_TABLE_CHUNK") ? atoi(getenv("B200_TABLE_CHUNK")) : 0; // tuning knob
     const Geometry g = bs.table_c ? make_table_geometry(n, Fr::params::BITS, bs.table_c, bs.n, table_chunk) : pub;
     const int reduce_windows = bs.table_c ? 1 : g.W;
     *W_out = pub.W;
