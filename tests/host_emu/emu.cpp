@@ -276,6 +276,17 @@ template<class Fr, class F> static int batch_exp_emulated(const void *g_ref, con
     return 0;
 }
 
+// msm_geometry.hpp as the launch code sees it: {c, W, B, NB, cpw, rb, opw, collapse, bstride, estride, chunk}
+extern "C" int emu_geometry(uint64_t n, int scalar_bits, int table, uint32_t *out)
+{
+    using namespace msm;
+    const Geometry g = table ? make_table_geometry(n, scalar_bits, table_window_bits(n, scalar_bits), n)
+                             : make_geometry(n, scalar_bits);
+    const uint32_t v[11] = {(uint32_t)g.c, (uint32_t)g.W, g.B, g.NB, g.cpw, g.rb, g.opw, g.collapse, g.bstride, g.estride, g.chunk};
+    memcpy(out, v, sizeof(v));
+    return 0;
+}
+
 extern "C" int emu_batch_exp(int curve, int group, const void *g, const void *coeff, const void *scalars, size_t n, void *out)
 {
     switch (curve * 4 + group) {

@@ -61,6 +61,12 @@ def test_no_cpu_fallback(b):
     assert e.value.code == b.ERR_CUDA and "no CPU fallback" in str(e.value)
     with pytest.raises(b.B200Error):
         b.multi_exp("alt_bn128", b.G1, np.zeros((2, 12), np.uint64), np.zeros((2, 4), np.uint64))
+    with pytest.raises(b.B200Error) as e:
+        b.batch_exp("alt_bn128", b.G1, np.zeros(12, np.uint64), np.zeros((3, 4), np.uint64))
+    assert e.value.code == b.ERR_CUDA
+    L = b.lib()
+    assert L.b200_bases_precompute(4242) == b.ERR_HANDLE and L.b200_bases_table_rows(4242) == 0
+    assert L.b200_groth16_shard_msm(4242, 31, None) == b.ERR_HANDLE
 
 
 def _fake_windows(P, curve, group, W, shard, glimbs):

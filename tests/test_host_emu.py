@@ -41,6 +41,7 @@ def emu():
     L.emu_msm.argtypes = [i, i, vp, sz, vp, i, vp]
     L.emu_msm_table.argtypes = [i, i, vp, sz, vp, i, vp]
     L.emu_batch_exp.argtypes = [i, i, vp, vp, vp, sz, vp]
+    L.emu_geometry.argtypes = [C.c_uint64, i, i, vp]
     return L
 
 
@@ -176,3 +177,27 @@ def test_emulated_batch_exp(emu, curve):
                 want = P.msm(curve, gid, base[None, :], eff[i:i + 1])
                 assert np.array_equal(out[i], want), (k, i, c is not None)
         assert not out[3][2 * (base.shape[0] // 3):].any()       # zero scalar -> Z = 0
+
+
+def test_geometry_invariants(emu):
+    """Window / bucket / reduce geometry (msm_geometry.hpp) over the sizes and scalar widths in scope: the windows cover
+    the scalar plus its sign carry, the reduce chunks tile the buckets exactly, CTA sizes are powers of two, and the
+    chunk follows the reduce-thread budget."""
+    for bits in (253, 254, 377):
+        for log_n in list(range(0, 27, 2)) + [17, 21]:
+            n = max(1, (1 << log_n) - (log_n % 3))
+            for table in (0, 1):
+                if table and 30 * n >= (1 << 31):
+                    continue
+                out = np.zeros(11, dtype=np.uint32)
+                assert emu.emu_geometry(n, bits, table, _p(out)) == 0
+                c, W, B, NB, cpw, rb, opw, collapse, bstride, estride, chunk = [int(x) for x in out]
+                assert 5 <= c <= 20 and W * c >= bits + 1 and (W - 1) * c < bits + 1
+                assert B == 1 << (c - 1) and NB == (B if table else W * B)
+                assert chunk in (2, 4, 8) and cpw * chunk == B and opw * rb == cpw
+                assert rb & (rb - 1) == 0 and 1 <= rb <= 128
+                assert (bstride, estride) == ((0, n) if table else (B, 0))
+                threads = (1 if table else W) * cpw
+                assert chunk == 8 or threads <= 40000
+                assert chunk == 2 or 2 * threads > 40000       # the next smaller chunk would exceed the budget
+                assert collapse >= 4
