@@ -240,6 +240,10 @@ int b200_groth16_shard_witness_copy(b200_groth16_pk_t handle, void *dev_buf, int
 int b200_groth16_shard_chain(b200_groth16_pk_t handle, int which, void *dev_out);
 int b200_groth16_shard_h(b200_groth16_pk_t handle, void *dA, const void *dB, const void *dC);
 int b200_groth16_shard_msm(b200_groth16_pk_t handle, unsigned mask, void *dev_blob);
+/* `h` on three chain results and `msm` in one call: the pointwise step, the icosetFFT and the H shard MSM run beside
+ * the other selected MSMs instead of after them. */
+int b200_groth16_shard_finish_msm(b200_groth16_pk_t handle, void *dA, const void *dB, const void *dC, unsigned mask,
+                                  void *dev_blob);
 /* blobs = `world` blobs in rank order (host memory). proof_out as b200_groth16_prove. */
 int b200_groth16_assemble(int curve, const void *alpha_g1, const void *beta_g1, const void *beta_g2,
                           const void *delta_g1, const void *delta_g2, const size_t query_sizes[4], int world,

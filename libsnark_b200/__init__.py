@@ -41,7 +41,7 @@ EXPORTS = [
     "b200_witness_chain_r1cs_dev", "b200_witness_finish_dev",
     "b200_shard_range", "b200_groth16_shard_bytes", "b200_groth16_pk_create_shard", "b200_groth16_prove_shard",
     "b200_groth16_shard_begin", "b200_groth16_shard_chain", "b200_groth16_shard_h", "b200_groth16_shard_msm",
-    "b200_groth16_assemble", "b200_bases_precompute", "b200_bases_table_rows", "b200_groth16_shard_witness_copy", "b200_batch_exp",
+    "b200_groth16_assemble", "b200_bases_precompute", "b200_bases_table_rows", "b200_groth16_shard_witness_copy", "b200_batch_exp", "b200_groth16_shard_finish_msm",
 ]
 
 
@@ -122,6 +122,7 @@ def lib():
         L.b200_groth16_shard_witness_copy.argtypes = [u64, vp, i]
         L.b200_groth16_shard_h.argtypes = [u64, vp, vp, vp]
         L.b200_groth16_shard_msm.argtypes = [u64, C.c_uint, vp]
+        L.b200_groth16_shard_finish_msm.argtypes = [u64, vp, vp, vp, C.c_uint, vp]
         L.b200_groth16_assemble.argtypes = [i, vp, vp, vp, vp, vp, C.POINTER(sz), i, vp, vp, vp, vp]
         L.b200_batch_exp.argtypes = [i, i, vp, vp, vp, sz, vp]
         L.b200_last_msm_timing.argtypes = [C.POINTER(C.c_double)]
@@ -576,6 +577,10 @@ class Groth16ProvingKeyShard:
     def msm(self, mask, dev_blob):
         _check(lib().b200_groth16_shard_msm(self.handle, mask, C.c_void_p(dev_blob)))
 
+    def finish_msm(self, dA, dB, dC, mask, dev_blob):
+        _check(lib().b200_groth16_shard_finish_msm(self.handle, C.c_void_p(dA), C.c_void_p(dB), C.c_void_p(dC), mask,
+                                                   C.c_void_p(dev_blob)))
+
     def assemble(self, r, s, blobs):
         return groth16_assemble(self.curve, *self.points, self.query_sizes, self.world, blobs, r, s)
 
@@ -643,17 +648,14 @@ class DistributedProver:
             if pk.rank < 3:
                 pk.chain(pk.rank, self.chains[pk.rank].data_ptr())
             lap("chain")
-            works = [dist.broadcast(self.chains[i], src=i, async_op=True) for i in range(3)]
-            pk.msm(MSM_A | MSM_B_G2 | MSM_B_G1 | MSM_L, self.blob.data_ptr())
-            lap("msm_A_B_L")
-            for w in works:
-                w.wait()
+            for i in range(3):
+                dist.broadcast(self.chains[i], src=i)
             torch.cuda.current_stream().synchronize()
-            lap("broadcast_wait")
-            pk.h(*[c.data_ptr() for c in self.chains])
-            lap("h_finish")
-            pk.msm(MSM_H, self.blob.data_ptr())
-            lap("msm_H")
+            lap("chain_broadcast")
+            # pointwise + icosetFFT + the H shard MSM on this thread's slot, the A, B, L shard MSMs beside them
+            pk.finish_msm(self.chains[0].data_ptr(), self.chains[1].data_ptr(), self.chains[2].data_ptr(),
+                          MSM_A | MSM_B_G2 | MSM_B_G1 | MSM_H | MSM_L, self.blob.data_ptr())
+            lap("h_and_msm")
         else:
             pk.h()
             lap("witness_map")

@@ -318,11 +318,14 @@ JobResult run_slot_jobs(int slot, std::vector<MsmJob> jobs, double *ms5)
 
 // Runs `jobs` (any subset of the five MSMs) over the slots; `before_h`, if set, runs on this thread ahead of the H
 // job (the witness map). Returns the first failure.
-template<class BeforeH> int run_msms(const std::vector<MsmJob> &jobs, double *ms5, BeforeH before_h)
+template<class BeforeH> int run_msms(const std::vector<MsmJob> &jobs, double *ms5, BeforeH before_h, bool before_h_is_short = false)
 {
     int plan[NUM_MSM];
     bool wm_first = true;
     slot_plan(plan, &wm_first);
+    if (before_h_is_short) {
+        wm_first = false; // a handful of launches (pointwise + one inverse transform): let the other slots start at once
+    }
     std::vector<MsmJob> per_slot[rt::NUM_SLOTS];
     for (const MsmJob &j : jobs) {
         per_slot[plan[j.k]].push_back(j);
@@ -427,7 +430,8 @@ int upload_witness(const ProvingKey &pk, const void *primary_input, const void *
 
 // The MSMs of this rank's shards selected by `mask` (bit k = MSM k in blob order A, B.g2, B.g1, H, L), run
 // concurrently (run_msms); with_witness_map computes coefficients_for_H on this thread first.
-int shard_msms(const ProvingKey &pk, unsigned mask, void *dev_blob, double *ms5, bool with_witness_map, double *wm_ms)
+int shard_msms(const ProvingKey &pk, unsigned mask, void *dev_blob, double *ms5, bool with_witness_map, double *wm_ms,
+               void *dA = nullptr, const void *dB = nullptr, const void *dC = nullptr)
 {
     const size_t fr = b200_sizeof_fr(pk.curve);
     const BlobLayout L = blob_layout(pk.curve, pk.tot, pk.world);
@@ -449,17 +453,23 @@ int shard_msms(const ProvingKey &pk, unsigned mask, void *dev_blob, double *ms5,
             jobs.push_back(MsmJob{k, sets[k], cnt, sc[k], static_cast<uint8_t *>(dev_blob) + L.off[k], true});
         }
     }
-    return run_msms(jobs, ms5, [&]() -> int {
-        if (!with_witness_map) {
-            return B200_OK;
-        }
-        const double t0 = now_ms();
-        const int rc = b200_witness_map_r1cs_dev(pk.r1cs, pk.d_w, pk.m, pk.d_h);
-        if (wm_ms) {
-            *wm_ms = now_ms() - t0;
-        }
-        return rc;
-    });
+    return run_msms(
+        jobs, ms5,
+        [&]() -> int {
+            if (dA) { // the three chain results are here: pointwise step + icosetFFT -> coefficients_for_H
+                return b200_witness_finish_dev(pk.curve, dA, dB, dC, pk.m, pk.d_h);
+            }
+            if (!with_witness_map) {
+                return B200_OK;
+            }
+            const double t0 = now_ms();
+            const int rc = b200_witness_map_r1cs_dev(pk.r1cs, pk.d_w, pk.m, pk.d_h);
+            if (wm_ms) {
+                *wm_ms = now_ms() - t0;
+            }
+            return rc;
+        },
+        dA != nullptr);
 }
 
 // r1cs_gg_ppzksnark_prover over a one-GPU key (b200_groth16_prove).
@@ -810,6 +820,20 @@ int b200_groth16_shard_msm(b200_groth16_pk_t handle, unsigned mask, void *dev_bl
         return rt::set_error(B200_ERR_ARG, "null pointer");
     }
     return shard_msms(*pk, mask, dev_blob, nullptr, false, nullptr);
+}
+
+int b200_groth16_shard_finish_msm(b200_groth16_pk_t handle, void *dA, const void *dB, const void *dC, unsigned mask,
+                                  void *dev_blob)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    const ProvingKey *pk = find_key(handle);
+    if (!pk) {
+        return B200_ERR_HANDLE;
+    }
+    if (!dA || !dB || !dC || !dev_blob) {
+        return rt::set_error(B200_ERR_ARG, "null pointer");
+    }
+    return shard_msms(*pk, mask, dev_blob, nullptr, false, nullptr, dA, dB, dC);
 }
 
 int b200_groth16_prove_shard(b200_groth16_pk_t handle, const void *primary_input, const void *auxiliary_input,

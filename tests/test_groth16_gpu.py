@@ -276,6 +276,17 @@ def test_chain_parallel_witness_map(ref, b200, curve, log_m):
                 buf.free()
             got = keys[0].assemble(rs[0], rs[1], np.concatenate(blobs))
             assert np.array_equal(got, want)
+            # the fused form DistributedProver uses: finish + all five shard MSMs in one call
+            blobs = []
+            for k in keys:
+                for c, a in zip(chains, saved):
+                    c.upload(a)
+                buf = b200.DeviceBuffer(k.blob_bytes)
+                k.finish_msm(chains[0].ptr, chains[1].ptr, chains[2].ptr,
+                             b200.MSM_A | b200.MSM_B_G2 | b200.MSM_B_G1 | b200.MSM_H | b200.MSM_L, buf.ptr)
+                blobs.append(buf.download((k.blob_bytes,), dtype=np.uint8))
+                buf.free()
+            assert np.array_equal(keys[0].assemble(rs[0], rs[1], np.concatenate(blobs)), want)
             # and H itself: chains -> finish == the reference's coefficients_for_H
             for c, a in zip(chains, saved):
                 c.upload(a)
