@@ -462,7 +462,10 @@ def bench_ntt(b, torch, log_m, wide_peak):
             "e2e": {"value": m / (e2e_ms * 1e-3), "unit": "elem/s", "ms": e2e_ms,
                     "h2d_bytes_per_step": int(data.nbytes), "d2h_bytes_per_step": int(data.nbytes)},
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
-                         "frac": gbs / peaks.get("hbm_gbs"), "traffic": None,
+                         "frac": gbs / peaks.get("hbm_gbs"),
+                         # dram__bytes_read + dram__bytes_write of one k_ntt_pass launch without scale tables (0.537 + 0.490 GB,
+                         # profiles/r1_ncu_ntt_pass.md) x the 3 passes of a 2^24 transform; scaled by size for other log_m
+                         "traffic": 3 * (0.537e9 + 0.4896e9) * (m / float(1 << 24)) * (-(-log_m // 8) / 3.0),
                          "algorithmic_bytes": 2 * m * 32,
                          "int_pipe_note": "(m/2) log2(m) modmuls x 136 multiply-adds against the IMAD.WIDE peak; see DESIGN.md §5"},
             "modmul_Tmad_s": (m // 2) * log_m * 136 / (ms * 1e-3) / 1e12,
