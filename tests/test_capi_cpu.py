@@ -169,8 +169,9 @@ def _fake_blob(b, world, rank):
     return blob, pts
 
 
-def _expected_proof(b, P, world, all_pts):
-    """alpha + A | beta + B.g2 | H + L for r = s = 0, by Horner over every rank's windows with the C oracle."""
+def _expected_proof(b, P, world, all_pts, r=None, s=None):
+    """The proof of r1cs_gg_ppzksnark.tcc:583-595 from every rank's windows (Horner) with the C oracle's group law:
+    g_A = alpha + A + r delta, g_B = beta + B + s delta (G2 and G1), g_C = H + L + s g_A + r g_B(G1) - r s delta."""
     g = np.load(os.path.join(ROOT, "tests", "golden", "msm.npz"))
     L = b.lib()
 
@@ -189,9 +190,18 @@ def _expected_proof(b, P, world, all_pts):
             total = acc if total is None else P.group_op("alt_bn128", grp, 0, total, acc)
         return total
     key = _key_points(g)
-    gA = P.group_op("alt_bn128", 1, 0, key[0][None, :], fold(0, 0, 1))
-    gB = P.group_op("alt_bn128", 2, 0, key[2][None, :], fold(1, 1, 2))
-    gC = P.group_op("alt_bn128", 1, 0, fold(3, 2, 1), fold(4, 3, 1))
+    add = lambda grp, x, y: P.group_op("alt_bn128", grp, 0, x, y)
+    gA = add(1, key[0][None, :], fold(0, 0, 1))
+    gB = add(2, key[2][None, :], fold(1, 1, 2))
+    gC = add(1, fold(3, 2, 1), fold(4, 3, 1))
+    if r is not None:
+        mul = lambda grp, k, pt: P.msm("alt_bn128", grp, np.ascontiguousarray(pt).reshape(1, -1), k[None, :])[None, :]
+        gB1 = add(1, add(1, key[1][None, :], fold(2, 1, 1)), mul(1, s, key[3]))
+        gA = add(1, gA, mul(1, r, key[3]))
+        gB = add(2, gB, mul(2, s, key[4]))
+        rs = P.field_op("alt_bn128", 0, 2, r[None, :], s[None, :])[0]
+        neg = P.group_op("alt_bn128", 1, 3, mul(1, rs, key[3]))
+        gC = add(1, add(1, add(1, gC, mul(1, s, gA[0])), mul(1, r, gB1[0])), neg)
     return np.concatenate([gA[0], gB[0], gC[0]])
 
 
@@ -222,6 +232,9 @@ def test_sharded_assemble_host(b):
         blobs, pts = zip(*[_fake_blob(b, world, r) for r in range(world)])
         got = b.groth16_assemble("alt_bn128", *_key_points(g), QUERY_SIZES, world, np.concatenate(blobs), zero, zero)
         assert np.array_equal(got, _expected_proof(b, P, world, pts)), world
+        r, s = g["rand.alt_bn128.g1.scalars"][40 + world], g["rand.alt_bn128.g1.scalars"][50 + world]
+        got = b.groth16_assemble("alt_bn128", *_key_points(g), QUERY_SIZES, world, np.concatenate(blobs), r, s)
+        assert np.array_equal(got, _expected_proof(b, P, world, pts, r, s)), world
 
 
 SHARD_WORKER = r'''
