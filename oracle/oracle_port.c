@@ -589,6 +589,84 @@ API int port_msm(int curve, int group, int method, const void *bases, size_t str
     return 0;
 }
 
+/* ---- key generation: fixed-base batch exponentiation ------------------------------------------------
+ * get_window_table (multiexp.tcc:808-844): powers_of_g[outer][inner] = inner * 2^(window * outer) * g;
+ * windowed_exp (:846-876): res = sum_outer powers_of_g[outer][bits of pow in window outer];
+ * batch_exp (:879-914) / batch_exp_with_coeff (:916-946): res[i] = windowed_exp(coeff * v[i]);
+ * batch_to_special (:949-974): every result normalised, zero -> zero().to_special() = (0, 1, 0).
+ * g: one point (reference layout); coeff: Fr (Montgomery) or NULL; window: 1..16 (the reference picks it from a
+ * per-curve table, get_exp_window_size :771-806 — it does not change the result). out: n points, special form. */
+API int port_batch_exp(int curve, int group, const void *g_, const void *coeff, const void *scalars, size_t n,
+                       size_t window, void *out)
+{
+    if (set_context(curve, group) || window < 1 || window > 16) return -1;
+    const int nr = curve_table[curve].fr.n;
+    const size_t scalar_size = bigint_num_bits(curve_table[curve].fr.mod, nr); /* Fr::size_in_bits() */
+    const size_t in_window = (size_t)1 << window;
+    const size_t outerc = (scalar_size + window - 1) / window;
+    const size_t last_in_window = (size_t)1 << (scalar_size - (outerc - 1) * window);
+    pt_t *table = (pt_t *)malloc(outerc * in_window * sizeof(pt_t));
+    pt_t gouter;
+    pt_load(&gouter, (const uint64_t *)g_);
+    for (size_t outer = 0; outer < outerc; ++outer) { /* :830-841 */
+        pt_t ginner;
+        pt_zero(&ginner);
+        const size_t cur = outer == outerc - 1 ? last_in_window : in_window;
+        for (size_t inner = 0; inner < in_window; ++inner) {
+            if (inner < cur) {
+                table[outer * in_window + inner] = ginner;
+                pt_add(&ginner, &ginner, &gouter);
+            } else {
+                pt_zero(&table[outer * in_window + inner]);
+            }
+        }
+        for (size_t i = 0; i < window; ++i) pt_dbl(&gouter, &gouter);
+    }
+    /* coeff * v[i] in Fr (Montgomery product, fp.tcc:51-228), then as_bigint */
+    uint64_t *eff = (uint64_t *)malloc((n ? n : 1) * nr * 8);
+    {
+        const field_params *fq = g_f;
+        g_f = &curve_table[curve].fr;
+        for (size_t i = 0; i < n; ++i) {
+            fp_t a, c, p;
+            fp_zero(&a);
+            memcpy(a.v, (const uint64_t *)scalars + i * nr, 8 * nr);
+            if (coeff) {
+                fp_zero(&c);
+                memcpy(c.v, coeff, 8 * nr);
+                fp_mul(&p, &c, &a);
+                a = p;
+            }
+            memcpy(eff + i * nr, a.v, 8 * nr);
+        }
+        g_f = fq;
+    }
+    uint64_t *std = scalars_to_std(curve, eff, n);
+    const size_t glimbs = (size_t)3 * g_deg * g_f->n;
+    for (size_t i = 0; i < n; ++i) {
+        const uint64_t *pw = std + i * nr;
+        pt_t res = table[0]; /* powers_of_g[0][0] = zero() */
+        for (size_t outer = 0; outer < outerc; ++outer) { /* :859-871 */
+            size_t inner = 0;
+            for (size_t k = 0; k < window; ++k) {
+                const size_t bit = outer * window + k;
+                if (bit < (size_t)64 * nr && ((pw[bit >> 6] >> (bit & 63)) & 1)) inner |= (size_t)1 << k;
+            }
+            pt_add(&res, &res, &table[outer * in_window + inner]);
+        }
+        if (pt_is_zero(&res)) {
+            pt_zero(&res);
+        } else {
+            pt_to_affine(&res);
+        }
+        pt_store((uint64_t *)out + i * glimbs, &res);
+    }
+    free(table);
+    free(eff);
+    free(std);
+    return 0;
+}
+
 /* kc_multiexp.tcc:31-113: sparse vector of (G2, G1) pairs; entries with min_idx <= index < max_idx. */
 API int port_kc_msm(int curve, const uint64_t *indices, const void *values, size_t nnz, size_t min_idx, size_t max_idx,
                     const void *scalars, void *out_g2, void *out_g1)

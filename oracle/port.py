@@ -37,6 +37,7 @@ class OraclePort:
         L.port_witness_map_h.argtypes = [i, vp, vp, vp, sz, vp]
         L.port_field_op.argtypes = [i, i, i, vp, vp, vp, sz]
         L.port_group_op.argtypes = [i, i, i, vp, vp, vp, sz]
+        L.port_batch_exp.argtypes = [i, i, vp, vp, vp, sz, sz, vp]
 
     def group_limbs(self, curve, group):
         c = _cid(curve)
@@ -50,6 +51,17 @@ class OraclePort:
         out = np.zeros(self.group_limbs(c, group), dtype=np.uint64)
         stride = stride if stride is not None else (bases.strides[0] if bases.ndim == 2 else 0)
         assert self.lib.port_msm(c, group, method, _p(bases), stride, n, _p(scalars), _p(out)) == 0
+        return out
+
+    def batch_exp(self, curve, group, g, scalars, coeff=None, window=5):
+        """get_window_table + batch_exp / batch_exp_with_coeff + batch_to_special (multiexp.tcc:808-974)."""
+        c = _cid(curve)
+        g = np.ascontiguousarray(g, dtype=np.uint64)
+        scalars = np.ascontiguousarray(scalars, dtype=np.uint64)
+        coeff = None if coeff is None else np.ascontiguousarray(coeff, dtype=np.uint64)
+        out = np.zeros((scalars.shape[0], self.group_limbs(c, group)), dtype=np.uint64)
+        assert self.lib.port_batch_exp(c, group, _p(g), None if coeff is None else _p(coeff), _p(scalars), scalars.shape[0],
+                                       window, _p(out)) == 0
         return out
 
     def kc_msm(self, curve, indices, values, min_idx, max_idx, scalars):

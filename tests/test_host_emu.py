@@ -177,6 +177,15 @@ def test_emulated_batch_exp(emu, curve):
                 want = P.msm(curve, gid, base[None, :], eff[i:i + 1])
                 assert np.array_equal(out[i], want), (k, i, c is not None)
         assert not out[3][2 * (base.shape[0] // 3):].any()       # zero scalar -> Z = 0
+    # and against the vectors the unmodified reference produced (tests/golden/keygen.npz, tools/gen_golden.py)
+    kg = np.load(os.path.join(GOLD, "keygen.npz"))
+    sc, coeff = np.ascontiguousarray(kg[f"{curve}.scalars"]), np.ascontiguousarray(kg[f"{curve}.coeff"][0])
+    for gname, gid in [("g1", 1), ("g2", 2)]:
+        base = np.ascontiguousarray(kg[f"{curve}.{gname}.base"])
+        for c, want in ((None, kg[f"{curve}.{gname}.out"]), (coeff, kg[f"{curve}.{gname}.out_coeff"])):
+            out = np.zeros_like(want)
+            assert emu.emu_batch_exp(CURVES[curve], gid, _p(base), None if c is None else _p(c), _p(sc), sc.shape[0], _p(out)) == 0
+            assert np.array_equal(out, want), (gname, c is not None)
 
 
 def test_geometry_invariants(emu):

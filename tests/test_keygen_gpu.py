@@ -107,3 +107,15 @@ def test_overlay_generator_keys_verify(ref, overlay, curve, nc):
         assert verify(bad) != 1
     finally:
         fx.close()
+
+
+@pytest.mark.parametrize("curve", ["alt_bn128", "bls12_377", "bw6_761"])
+def test_batch_exp_golden_fixtures(b200, curve):
+    """b200_batch_exp against the committed vectors the unmodified reference produced (tests/golden/keygen.npz)."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "keygen.npz"))
+    sc, coeff = g[f"{curve}.scalars"], g[f"{curve}.coeff"]
+    for gname, gid in [("g1", refo.G1), ("g2", refo.G2)]:
+        base = g[f"{curve}.{gname}.base"]
+        assert np.array_equal(b200.batch_exp(curve, gid, base, sc), g[f"{curve}.{gname}.out"])
+        assert np.array_equal(b200.batch_exp(curve, gid, base, sc, coeff[0]), g[f"{curve}.{gname}.out_coeff"])

@@ -146,3 +146,32 @@ def test_witness_map_golden(P, curve):
     # degree of H is m - 2: H[m-1] == H[m] == 0, H[m-2] != 0 (r1cs_gg_ppzksnark.tcc:488-490)
     H = g[k + ".H"]
     assert not H[-1].any() and not H[-2].any() and H[-3].any()
+
+
+@pytest.mark.parametrize("curve", CURVES)
+def test_batch_exp_golden(P, curve):
+    """Key generation: get_window_table + batch_exp / batch_exp_with_coeff + batch_to_special
+    (multiexp.tcc:808-974). The window width is a tuning parameter of the reference and must not change the result."""
+    g = np.load(os.path.join(GOLD, "keygen.npz"))
+    sc, coeff = g[f"{curve}.scalars"], g[f"{curve}.coeff"]
+    for gname, gid in [("g1", 1), ("g2", 2)]:
+        base = g[f"{curve}.{gname}.base"]
+        for window in (1, 4, 9):
+            assert np.array_equal(P.batch_exp(curve, gid, base, sc, window=window), g[f"{curve}.{gname}.out"]), (gname, window)
+        assert np.array_equal(P.batch_exp(curve, gid, base, sc, coeff[0], window=6), g[f"{curve}.{gname}.out_coeff"]), gname
+        assert not g[f"{curve}.{gname}.out"][3][2 * (base.shape[0] // 3):].any()          # scalar 0 -> zero(): Z = 0
+        assert np.array_equal(g[f"{curve}.{gname}.out"][4], base)                          # scalar 1 -> the base itself
+    # kc_batch_exp (kc_multiexp.tcc:147-239): zeros skipped, (coeff0 v) g2 | (coeff1 v) g1 per remaining entry
+    idx, vals = g[f"{curve}.kc.indices"], g[f"{curve}.kc.values"]
+    assert idx.tolist() == [i for i in range(sc.shape[0]) if i != 3]
+    g2l = g[f"{curve}.g2.base"].shape[0]
+    nz = sc[idx.astype(np.int64)]
+    assert np.array_equal(vals[:, :g2l], P.batch_exp(curve, 2, g[f"{curve}.g2.base"], nz, coeff[0]))
+    assert np.array_equal(vals[:, g2l:], P.batch_exp(curve, 1, g[f"{curve}.g1.base"], nz, coeff[1]))
+    try:
+        from oracle import refo
+        ref = refo.RefOracle()
+    except (OSError, FileNotFoundError):
+        return
+    for gname, gid in [("g1", 1), ("g2", 2)]:
+        assert np.array_equal(ref.batch_exp(curve, gid, g[f"{curve}.{gname}.base"], sc, coeff[0]), g[f"{curve}.{gname}.out_coeff"])
