@@ -801,6 +801,156 @@ static int fft_inplace(fp_t *a, size_t m, int op, const fp_t *g)
     }
     return -1;
 }
+/* ---- step_radix2_domain (libfqfft/evaluation_domain/domains/step_radix2_domain.tcc): m = big + small, big = 2^k >
+ * small = 2^r — what get_evaluation_domain returns for sizes that are not a power of two
+ * (get_evaluation_domain.tcc:41-58). Same op codes as fft_inplace. */
+static void fp_from_u64(fp_t *r, uint64_t v)
+{
+    fp_zero(r);
+    r->v[0] = v;
+    fp_to_mont(r, r);
+}
+static int step_shape(size_t m, size_t *big, size_t *small) /* valid_for_size, :20-45 */
+{
+    if (m <= 1 || !(m & (m - 1))) return -2;
+    size_t l = 0;
+    while (((size_t)1 << l) < m) ++l; /* libff::log2 = ceil */
+    *big = (size_t)1 << (l - 1);
+    *small = m - *big;
+    if (*small & (*small - 1)) return -2;
+    if (l > (size_t)g_f->s) return -2;
+    return 0;
+}
+static int step_inplace(fp_t *a, size_t m, int op, const fp_t *g)
+{
+    size_t big, small;
+    if (step_shape(m, &big, &small)) return -2; /* DomainSizeException */
+    fp_t omega, big_omega, small_omega, t;
+    if (get_root_of_unity(&omega, 2 * big) || get_root_of_unity(&small_omega, small)) return -2; /* :57-61 */
+    fp_sqr(&big_omega, &omega);
+    const size_t compr = big / small;
+    switch (op) {
+    case 0: { /* FFT, :65-104 */
+        fp_t *c = (fp_t *)calloc(big, sizeof(fp_t)), *d = (fp_t *)calloc(big, sizeof(fp_t)),
+             *e = (fp_t *)calloc(small, sizeof(fp_t));
+        fp_t omega_i;
+        fp_one(&omega_i);
+        for (size_t i = 0; i < big; ++i) {
+            if (i < small) {
+                fp_add(&c[i], &a[i], &a[i + big]);
+                fp_sub(&t, &a[i], &a[i + big]);
+            } else {
+                c[i] = a[i];
+                t = a[i];
+            }
+            fp_mul(&d[i], &omega_i, &t);
+            fp_mul(&omega_i, &omega_i, &omega);
+        }
+        for (size_t i = 0; i < small; ++i)
+            for (size_t j = 0; j < compr; ++j) fp_add(&e[i], &e[i], &d[i + j * small]);
+        serial_radix2_fft(c, big, &big_omega);
+        serial_radix2_fft(e, small, &small_omega);
+        memcpy(a, c, big * sizeof(fp_t));
+        memcpy(a + big, e, small * sizeof(fp_t));
+        free(c);
+        free(d);
+        free(e);
+        return 0;
+    }
+    case 1: { /* iFFT, :106-171 */
+        fp_t *U0 = (fp_t *)malloc(big * sizeof(fp_t)), *U1 = (fp_t *)malloc(small * sizeof(fp_t)),
+             *tmp = (fp_t *)malloc(big * sizeof(fp_t));
+        memcpy(U0, a, big * sizeof(fp_t));
+        memcpy(U1, a + big, small * sizeof(fp_t));
+        fp_inv(&t, &big_omega);
+        serial_radix2_fft(U0, big, &t);
+        fp_inv(&t, &small_omega);
+        serial_radix2_fft(U1, small, &t);
+        fp_t inv;
+        fp_from_u64(&t, big);
+        fp_inv(&inv, &t);
+        for (size_t i = 0; i < big; ++i) fp_mul(&U0[i], &U0[i], &inv);
+        fp_from_u64(&t, small);
+        fp_inv(&inv, &t);
+        for (size_t i = 0; i < small; ++i) fp_mul(&U1[i], &U1[i], &inv);
+        fp_t omega_i;
+        fp_one(&omega_i);
+        for (size_t i = 0; i < big; ++i) {
+            fp_mul(&tmp[i], &U0[i], &omega_i);
+            fp_mul(&omega_i, &omega_i, &omega);
+        }
+        for (size_t i = small; i < big; ++i) a[i] = U0[i]; /* A_suffix */
+        for (size_t i = 0; i < small; ++i)
+            for (size_t j = 1; j < compr; ++j) fp_sub(&U1[i], &U1[i], &tmp[i + j * small]);
+        fp_t omega_inv, omega_inv_i, over_two;
+        fp_inv(&omega_inv, &omega);
+        fp_one(&omega_inv_i);
+        for (size_t i = 0; i < small; ++i) {
+            fp_mul(&U1[i], &U1[i], &omega_inv_i);
+            fp_mul(&omega_inv_i, &omega_inv_i, &omega_inv);
+        }
+        fp_from_u64(&t, 2);
+        fp_inv(&over_two, &t);
+        for (size_t i = 0; i < small; ++i) {
+            fp_add(&t, &U0[i], &U1[i]);
+            fp_mul(&a[i], &t, &over_two);
+            fp_sub(&t, &U0[i], &U1[i]);
+            fp_mul(&a[big + i], &t, &over_two);
+        }
+        free(U0);
+        free(U1);
+        free(tmp);
+        return 0;
+    }
+    case 2: /* cosetFFT, :173-178 */
+        multiply_by_coset(a, m, g);
+        return step_inplace(a, m, 0, g);
+    case 3: /* icosetFFT, :180-185 */
+        step_inplace(a, m, 1, g);
+        fp_inv(&t, g);
+        multiply_by_coset(a, m, &t);
+        return 0;
+    case 4: { /* divide_by_Z_on_coset, :249-279, coset = multiplicative_generator */
+        fp_t coset, one, Z0, cs_z0, os_z0, o2s, elt, u, v, w;
+        fp_zero(&coset);
+        memcpy(coset.v, g_f->generator, 8 * g_f->n);
+        fp_one(&one);
+        fp_pow_u64(&Z0, &coset, big);
+        fp_sub(&Z0, &Z0, &one);
+        fp_pow_u64(&u, &coset, small);
+        fp_mul(&cs_z0, &u, &Z0);
+        fp_pow_u64(&u, &omega, small);
+        fp_mul(&os_z0, &u, &Z0);
+        fp_pow_u64(&o2s, &omega, 2 * small);
+        fp_one(&elt);
+        for (size_t i = 0; i < big; ++i) {
+            fp_mul(&u, &cs_z0, &elt);
+            fp_sub(&u, &u, &os_z0);
+            fp_inv(&v, &u);
+            fp_mul(&a[i], &a[i], &v);
+            fp_mul(&elt, &elt, &o2s);
+        }
+        fp_mul(&w, &coset, &omega);
+        fp_pow_u64(&u, &w, big);
+        fp_sub(&u, &u, &one);
+        fp_pow_u64(&v, &w, small);
+        fp_pow_u64(&t, &omega, small);
+        fp_sub(&v, &v, &t);
+        fp_mul(&u, &u, &v);
+        fp_inv(&v, &u);
+        for (size_t i = 0; i < small; ++i) fp_mul(&a[big + i], &a[big + i], &v);
+        return 0;
+    }
+    }
+    return -1;
+}
+/* get_evaluation_domain (get_evaluation_domain.tcc:32-70) for the sizes these fields meet: basic radix-2 for powers
+ * of two, step radix-2 for 2^k + 2^r. */
+static int domain_inplace(fp_t *a, size_t m, int op, const fp_t *g)
+{
+    return (m & (m - 1)) ? step_inplace(a, m, op, g) : fft_inplace(a, m, op, g);
+}
+
 static fp_t *load_frs(const uint64_t *src, size_t m)
 {
     fp_t *a = (fp_t *)calloc(m ? m : 1, sizeof(fp_t));
@@ -817,15 +967,49 @@ API int port_fft(int curve, int op, void *data, size_t m, const void *g)
 {
     if (curve < 0 || curve > 2) return -1;
     g_f = &curve_table[curve].fr;
-    if (m < 1 || (m & (m - 1))) return -2;
+    if (m < 1) return -2;
     fp_t gg;
     fp_zero(&gg);
     memcpy(gg.v, g ? g : (const void *)g_f->generator, 8 * g_f->n);
     fp_t *a = load_frs((const uint64_t *)data, m);
-    const int rc = fft_inplace(a, m, op, &gg);
+    const int rc = domain_inplace(a, m, op, &gg);
     if (!rc) store_frs((uint64_t *)data, a, m);
     free(a);
     return rc;
+}
+
+/* The evaluations r1cs_to_qap_witness_map builds before its first transform (r1cs_to_qap.tcc:236-248 for aA, aB;
+ * :293-296 for aC; linear_combination::evaluate, variable.tcc:288-299). The constraint system comes as one CSR:
+ * rows [0, nc) = the a-combinations, [nc, 2nc) = b, [2nc, 3nc) = c; col = linear_term::index (0 = the constant ONE);
+ * w = (1 | primary | auxiliary), so that full_variable_assignment[index - 1] = w[index]. */
+API int port_r1cs_evaluate(int curve, size_t nc, size_t ni, const uint32_t *row_ptr, const uint32_t *col,
+                           const void *val, const void *w_, size_t m, void *aA, void *aB, void *aC)
+{
+    if (curve < 0 || curve > 2 || m < nc + ni + 1) return -1;
+    g_f = &curve_table[curve].fr;
+    const int nr = g_f->n;
+    const uint64_t *w = (const uint64_t *)w_, *v = (const uint64_t *)val;
+    uint64_t *out[3] = {(uint64_t *)aA, (uint64_t *)aB, (uint64_t *)aC};
+    for (int k = 0; k < 3; ++k) memset(out[k], 0, m * nr * 8);
+    /* the additional constraints input_i * 0 = 0 (:240-243): aA[nc + i] = (i > 0 ? full[i - 1] : one) = w[i] */
+    for (size_t i = 0; i <= ni; ++i) memcpy(out[0] + (nc + i) * nr, w + i * nr, 8 * nr);
+    for (int k = 0; k < 3; ++k) {
+        for (size_t i = 0; i < nc; ++i) {
+            fp_t acc;
+            fp_zero(&acc);
+            for (uint32_t e = row_ptr[k * nc + i]; e < row_ptr[k * nc + i + 1]; ++e) {
+                fp_t x, c, p;
+                fp_zero(&x);
+                fp_zero(&c);
+                memcpy(x.v, w + (size_t)col[e] * nr, 8 * nr); /* index 0 -> w[0] = one */
+                memcpy(c.v, v + (size_t)e * nr, 8 * nr);
+                fp_mul(&p, &x, &c);
+                fp_add(&acc, &acc, &p);
+            }
+            memcpy(out[k] + i * nr, acc.v, 8 * nr);
+        }
+    }
+    return 0;
 }
 
 /* r1cs_to_qap.tcc:252-330 with d1 = d2 = d3 = 0: aA, aB, aC (m each) -> coefficients_for_H (m + 1). */
@@ -837,17 +1021,17 @@ API int port_witness_map_h(int curve, const void *aA, const void *aB, const void
     fp_zero(&gen);
     memcpy(gen.v, g_f->generator, 8 * g_f->n);
     fp_t *A = load_frs((const uint64_t *)aA, m), *B = load_frs((const uint64_t *)aB, m), *Cc = load_frs((const uint64_t *)aC, m);
-    int rc = fft_inplace(A, m, 1, &gen);
-    if (!rc) rc = fft_inplace(B, m, 1, &gen);
+    int rc = domain_inplace(A, m, 1, &gen);
+    if (!rc) rc = domain_inplace(B, m, 1, &gen);
     if (!rc) {
-        fft_inplace(A, m, 2, &gen);
-        fft_inplace(B, m, 2, &gen);
+        domain_inplace(A, m, 2, &gen);
+        domain_inplace(B, m, 2, &gen);
         for (size_t i = 0; i < m; ++i) fp_mul(&A[i], &A[i], &B[i]);
-        fft_inplace(Cc, m, 1, &gen);
-        fft_inplace(Cc, m, 2, &gen);
+        domain_inplace(Cc, m, 1, &gen);
+        domain_inplace(Cc, m, 2, &gen);
         for (size_t i = 0; i < m; ++i) fp_sub(&A[i], &A[i], &Cc[i]);
-        fft_inplace(A, m, 4, &gen);
-        fft_inplace(A, m, 3, &gen);
+        domain_inplace(A, m, 4, &gen);
+        domain_inplace(A, m, 3, &gen);
         store_frs((uint64_t *)out_H, A, m);
         memset((uint64_t *)out_H + m * g_f->n, 0, 8 * g_f->n);
     }

@@ -38,6 +38,7 @@ class OraclePort:
         L.port_field_op.argtypes = [i, i, i, vp, vp, vp, sz]
         L.port_group_op.argtypes = [i, i, i, vp, vp, vp, sz]
         L.port_batch_exp.argtypes = [i, i, vp, vp, vp, sz, sz, vp]
+        L.port_r1cs_evaluate.argtypes = [i, sz, sz, vp, vp, vp, vp, sz, vp, vp, vp]
 
     def group_limbs(self, curve, group):
         c = _cid(curve)
@@ -51,6 +52,17 @@ class OraclePort:
         out = np.zeros(self.group_limbs(c, group), dtype=np.uint64)
         stride = stride if stride is not None else (bases.strides[0] if bases.ndim == 2 else 0)
         assert self.lib.port_msm(c, group, method, _p(bases), stride, n, _p(scalars), _p(out)) == 0
+        return out
+
+    def r1cs_evaluate(self, curve, nc, ni, row_ptr, col, val, w, m):
+        """(aA, aB, aC) as r1cs_to_qap_witness_map builds them (r1cs_to_qap.tcc:236-248, :293-296) from a CSR."""
+        row_ptr = np.ascontiguousarray(row_ptr, dtype=np.uint32)
+        col = np.ascontiguousarray(col, dtype=np.uint32)
+        val = np.ascontiguousarray(val, dtype=np.uint64)
+        w = np.ascontiguousarray(w, dtype=np.uint64)
+        out = [np.zeros((m, w.shape[1]), dtype=np.uint64) for _ in range(3)]
+        assert self.lib.port_r1cs_evaluate(_cid(curve), nc, ni, _p(row_ptr), _p(col), _p(val), _p(w), m, _p(out[0]), _p(out[1]),
+                                           _p(out[2])) == 0
         return out
 
     def batch_exp(self, curve, group, g, scalars, coeff=None, window=5):

@@ -118,3 +118,34 @@ def test_factory_rounding(b200):
     assert b200.domain_size_for((1 << 20) + 11) == (1 << 20) + 16          # 1048592
     assert b200.domain_size_for((1 << 10) + 100) == (1 << 10) + 128
     assert b200.domain_size_for(1000) == 1024
+
+
+@pytest.mark.parametrize("curve", ["alt_bn128", "bls12_377", "bw6_761"])
+def test_step_domain_golden_fixtures(b200, curve):
+    """The device step_radix2_domain against the committed vectors the unmodified reference produced
+    (tests/golden/step.npz, tools/gen_golden.py:gen_step), and — alt_bn128 — the device sparse R1CS evaluation and
+    witness map of a circuit over a step domain against the reference's aA, aB, aC and H."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "step.npz"))
+    coset = g[f"{curve}.generator"]                       # Fr::multiplicative_generator, Montgomery limbs
+    for m in [3, 6, 24, 80, 288]:
+        a = g[f"{curve}.m{m}.in"]
+        dom = b200.get_evaluation_domain(curve, m)
+        assert dom.m == m
+        assert np.array_equal(dom.FFT(a), g[f"{curve}.m{m}.fft"])
+        assert np.array_equal(dom.iFFT(a), g[f"{curve}.m{m}.ifft"])
+        assert np.array_equal(dom.cosetFFT(a, coset), g[f"{curve}.m{m}.coset_fft"])
+        assert np.array_equal(dom.icosetFFT(a, coset), g[f"{curve}.m{m}.icoset_fft"])
+        assert np.array_equal(dom.divide_by_Z_on_coset(a), g[f"{curve}.m{m}.div_z"])
+    if curve == "alt_bn128":
+        nc, ni, nv, m = [int(x) for x in g["witness.sizes"]]
+        cs = b200.R1CS(curve, nc, ni, nv, g["witness.row_ptr"], g["witness.col"], g["witness.val"])
+        try:
+            for got, want in zip(cs.evaluate(g["witness.w"], m), (g["witness.aA"], g["witness.aB"], g["witness.aC"])):
+                assert np.array_equal(got, want)
+            assert np.array_equal(cs.witness_map_h(g["witness.w"], m), g["witness.H"])
+            assert np.array_equal(b200.r1cs_to_qap_witness_map_h(curve, g["witness.aA"], g["witness.aB"], g["witness.aC"]),
+                                  g["witness.H"])
+        finally:
+            cs.free()
+

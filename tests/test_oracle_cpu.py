@@ -175,3 +175,33 @@ def test_batch_exp_golden(P, curve):
         return
     for gname, gid in [("g1", 1), ("g2", 2)]:
         assert np.array_equal(ref.batch_exp(curve, gid, g[f"{curve}.{gname}.base"], sc, coeff[0]), g[f"{curve}.{gname}.out_coeff"])
+
+
+@pytest.mark.parametrize("curve", CURVES)
+def test_step_radix2_domain_golden(P, curve):
+    """step_radix2_domain (sizes 2^k + 2^r; step_radix2_domain.tcc:65-279) restated in the C oracle == the vectors the
+    reference produced through get_evaluation_domain; plus the whole witness map over a step domain."""
+    g = np.load(os.path.join(GOLD, "step.npz"))
+    ops = {"fft": 0, "ifft": 1, "coset_fft": 2, "icoset_fft": 3, "div_z": 4}
+    for m in [3, 6, 24, 80, 288]:
+        a = g[f"{curve}.m{m}.in"]
+        for name, op in ops.items():
+            assert np.array_equal(P.fft(curve, op, a, g[f"{curve}.generator"]), g[f"{curve}.m{m}.{name}"]), (m, name)
+        # round trips are the identity
+        assert np.array_equal(P.fft(curve, 1, P.fft(curve, 0, a)), a)
+        assert np.array_equal(P.fft(curve, 3, P.fft(curve, 2, a)), a)
+    if curve == "alt_bn128":
+        got = P.witness_map_h(curve, g["witness.aA"], g["witness.aB"], g["witness.aC"])
+        assert got.shape[0] == 1152 + 1 and np.array_equal(got, g["witness.H"])
+
+
+def test_r1cs_evaluation_golden(P):
+    """The sparse evaluation <a_i, w>, <b_i, w>, <c_i, w> with the input-consistency rows (r1cs_to_qap.tcc:236-248,
+    :293-296; linear_combination::evaluate, variable.tcc:288-299) restated over the CSR the device path uploads ==
+    the aA, aB, aC the reference built for the same circuit; and from there every coefficient of H."""
+    g = np.load(os.path.join(GOLD, "step.npz"))
+    nc, ni, nv, m = [int(x) for x in g["witness.sizes"]]
+    assert g["witness.w"].shape[0] == nv + 1 and g["witness.row_ptr"].shape[0] == 3 * nc + 1
+    aA, aB, aC = P.r1cs_evaluate("alt_bn128", nc, ni, g["witness.row_ptr"], g["witness.col"], g["witness.val"], g["witness.w"], m)
+    assert np.array_equal(aA, g["witness.aA"]) and np.array_equal(aB, g["witness.aB"]) and np.array_equal(aC, g["witness.aC"])
+    assert np.array_equal(P.witness_map_h("alt_bn128", aA, aB, aC), g["witness.H"])
