@@ -135,7 +135,8 @@ def test_fft_roundtrip_and_domain_error(P):
     assert np.array_equal(P.fft("alt_bn128", 1, P.fft("alt_bn128", 0, a)), a)
     assert np.array_equal(P.fft("alt_bn128", 3, P.fft("alt_bn128", 2, a)), a)
     with pytest.raises(RuntimeError):
-        P.fft("alt_bn128", 0, a[:6])  # DomainSizeException analogue
+        P.fft("alt_bn128", 0, a[:7])  # neither 2^k nor 2^k + 2^r: DomainSizeException analogue
+    assert P.fft("alt_bn128", 0, a[:6]).shape[0] == 6  # 4 + 2 is a step_radix2_domain
 
 
 @pytest.mark.parametrize("curve", CURVES)
