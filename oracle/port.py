@@ -65,6 +65,36 @@ class OraclePort:
                                            _p(out[2])) == 0
         return out
 
+    def groth16_prove(self, curve, key, r1cs, w, r, s):
+        """r1cs_gg_ppzksnark_prover (r1cs_gg_ppzksnark.tcc:460-603) with caller-supplied r, s, composed from the
+        restated pieces: sparse evaluation + witness map (r1cs_to_qap.tcc:209-344, d1 = d2 = d3 = 0), the four
+        multi-exponentiations (:531-580; A and L through multi_exp_filter_one_zero, B through
+        kc_multi_exp_with_mixed_addition, H through multi_exp) and the assembly (:583-595).
+        key: dict alpha_g1, beta_g1, beta_g2, delta_g1, delta_g2, A, B_indices, B_values (G2 | G1), H, L.
+        r1cs: dict nc, ni, nv, m, row_ptr, col, val. Returns g_A | g_B | g_C normalised."""
+        nc, ni, nv, m = r1cs["nc"], r1cs["ni"], r1cs["nv"], r1cs["m"]
+        w = np.ascontiguousarray(w, dtype=np.uint64)
+        aA, aB, aC = self.r1cs_evaluate(curve, nc, ni, r1cs["row_ptr"], r1cs["col"], r1cs["val"], w, m)
+        Hc = self.witness_map_h(curve, aA, aB, aC)
+        At = self.msm(curve, 1, key["A"], w, method=2)
+        Bg2, Bg1 = self.kc_msm(curve, key["B_indices"], key["B_values"], 0, nv + 1, w)
+        Ht = self.msm(curve, 1, key["H"][:m - 1], Hc[:m - 1])
+        Lt = self.msm(curve, 1, key["L"], w[ni + 1:], method=2)
+
+        def add(grp, x, y):
+            return self.group_op(curve, grp, 0, np.asarray(x).reshape(1, -1), np.asarray(y).reshape(1, -1))[0]
+
+        def mul(grp, k, pt):
+            return self.msm(curve, grp, np.asarray(pt).reshape(1, -1), np.asarray(k).reshape(1, -1))
+        r, s = np.asarray(r, dtype=np.uint64), np.asarray(s, dtype=np.uint64)
+        gA = add(1, add(1, key["alpha_g1"], At), mul(1, r, key["delta_g1"]))
+        gB1 = add(1, add(1, key["beta_g1"], Bg1), mul(1, s, key["delta_g1"]))
+        gB2 = add(2, add(2, key["beta_g2"], Bg2), mul(2, s, key["delta_g2"]))
+        rs = self.field_op(curve, 0, 2, r.reshape(1, -1), s.reshape(1, -1))[0]
+        neg = self.group_op(curve, 1, 3, mul(1, rs, key["delta_g1"]).reshape(1, -1))[0]
+        gC = add(1, add(1, add(1, add(1, Ht, Lt), mul(1, s, gA)), mul(1, r, gB1)), neg)
+        return np.concatenate([gA, gB2, gC])
+
     def batch_exp(self, curve, group, g, scalars, coeff=None, window=5):
         """get_window_table + batch_exp / batch_exp_with_coeff + batch_to_special (multiexp.tcc:808-974)."""
         c = _cid(curve)
