@@ -323,3 +323,37 @@ def test_distributed_prover_nccl(ref, b200, tmp_path):
                           "--log-m", "12", "--check"], capture_output=True, text=True, timeout=900)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert '"matches_single_gpu": true' in out.stdout
+
+
+@pytest.mark.parametrize("curve,nc", [("alt_bn128", 117), ("alt_bn128", 90), ("bls12_377", 59), ("bw6_761", 27)])
+def test_prover_against_golden_proofs(b200, curve, nc):
+    """b200_groth16_prove and the sharded prover on the committed fixtures (tests/golden/groth16.npz: keys from the
+    reference's generator, proof from the reference's prover, r and s fixed) — no reference code in the loop."""
+    from test_oracle_cpu import groth16_fixture
+    key, r1cs, w, r, s, proof = groth16_fixture(curve, nc)
+    ni = r1cs["ni"]
+    g2l = key["beta_g2"].shape[0]
+    cs = b200.R1CS(curve, r1cs["nc"], ni, r1cs["nv"], r1cs["row_ptr"], r1cs["col"], r1cs["val"])
+    args = (curve, key["alpha_g1"], key["beta_g1"], key["beta_g2"], key["delta_g1"], key["delta_g2"], key["A"],
+            np.ascontiguousarray(key["B_values"][:, :g2l]), np.ascontiguousarray(key["B_values"][:, g2l:]),
+            key["B_indices"].astype(np.uint32), key["H"], key["L"], cs, r1cs["m"])
+    pk = b200.Groth16ProvingKey(*args, precompute=True)
+    try:
+        got, _ = pk.prove(w[1:1 + ni], w[1 + ni:], r, s)
+        assert np.array_equal(got, proof)
+    finally:
+        pk.free()
+    world = 3
+    keys = [b200.Groth16ProvingKeyShard(*args, rank, world) for rank in range(world)]
+    try:
+        blobs = []
+        for k in keys:
+            buf = b200.DeviceBuffer(k.blob_bytes)
+            k.prove_shard(w[1:1 + ni], w[1 + ni:], buf.ptr)
+            blobs.append(buf.download((k.blob_bytes,), dtype=np.uint8))
+            buf.free()
+        assert np.array_equal(keys[0].assemble(r, s, np.concatenate(blobs)), proof)
+    finally:
+        for k in keys:
+            k.free()
+        cs.free()
