@@ -20,7 +20,15 @@
  *   FFT       : _basic_serial_radix2_FFT, _multiply_by_coset
  *               libfqfft/evaluation_domain/domains/basic_radix2_domain_aux.tcc:44-79, :174-183
  *               FFT / iFFT / cosetFFT / icosetFFT / divide_by_Z_on_coset  basic_radix2_domain.tcc:54-126
- *   H chain   : libsnark/reductions/r1cs_to_qap/r1cs_to_qap.tcc:252-330 (d1 = d2 = d3 = 0)
+ *   step FFT  : step_radix2_domain FFT / iFFT / cosetFFT / icosetFFT / divide_by_Z_on_coset
+ *               libfqfft/evaluation_domain/domains/step_radix2_domain.tcc:20-279 (sizes 2^k + 2^r)
+ *   R1CS eval : aA, aB, aC incl. the input-consistency rows  libsnark/reductions/r1cs_to_qap/r1cs_to_qap.tcc:236-248,
+ *               :293-296; linear_combination::evaluate  libsnark/relations/variable.tcc:288-299
+ *   H chain   : libsnark/reductions/r1cs_to_qap/r1cs_to_qap.tcc:252-330 (d1 = d2 = d3 = 0), over either domain kind
+ *   key gen   : get_window_table / windowed_exp / batch_exp / batch_exp_with_coeff / batch_to_special
+ *               libff/algebra/scalar_multiplication/multiexp.tcc:808-974
+ *   prover    : the orchestration r1cs_gg_ppzksnark.tcc:460-603 is composed from these in oracle/port.py::groth16_prove
+ *               and pinned to whole proofs of the reference (tests/golden/groth16.npz)
  */
 #include <stdint.h>
 #include <stdlib.h>
