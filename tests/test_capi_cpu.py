@@ -302,3 +302,38 @@ def test_synthetic_r1cs_is_satisfied():
         ev = [sum(ints[c] for c in col[rp[r]:rp[r + 1]]) % p for r in range(3 * nc)]
         for i in range(nc):
             assert ev[i] * ev[nc + i] % p == ev[2 * nc + i], (curve, i)
+
+
+@pytest.mark.parametrize("curve,nc", [("alt_bn128", 90), ("bls12_377", 59), ("bw6_761", 27)])
+def test_assemble_reproduces_reference_proofs(b, curve, nc):
+    """b200_groth16_assemble (host fold + r1cs_gg_ppzksnark.tcc:583-595, incl. the G2 arithmetic of each curve) on the
+    committed fixtures: the five MSM results — computed here by the C oracle — enter as one-shard blobs with the whole
+    sum in window 0, and the assembled proof must be the reference prover's (tests/golden/groth16.npz)."""
+    from oracle import port
+    from test_oracle_cpu import groth16_fixture
+    P = port.OraclePort()
+    key, r1cs, w, r, s, proof = groth16_fixture(curve, nc)
+    ncons, ni, nv, m = r1cs["nc"], r1cs["ni"], r1cs["nv"], r1cs["m"]
+    aA, aB, aC = P.r1cs_evaluate(curve, ncons, ni, r1cs["row_ptr"], r1cs["col"], r1cs["val"], w, m)
+    Hc = P.witness_map_h(curve, aA, aB, aC)
+    Bg2, Bg1 = P.kc_msm(curve, key["B_indices"], key["B_values"], 0, nv + 1, w)
+    sums = [P.msm(curve, 1, key["A"], w, method=2), Bg2, Bg1, P.msm(curve, 1, key["H"][:m - 1], Hc[:m - 1]),
+            P.msm(curve, 1, key["L"], w[ni + 1:], method=2)]
+    sizes = [nv + 1, key["B_indices"].shape[0], m - 1, nv - ni]
+    L = b.lib()
+    cid = b.CURVES[curve]
+    blob = np.zeros(b.groth16_shard_bytes(curve, sizes, 1), dtype=np.uint8)
+    at = 0
+    for k, (q, grp) in enumerate(zip([0, 1, 1, 2, 3], [1, 2, 1, 1, 1])):
+        pt = sums[k]
+        fl = pt.shape[0] // 3                       # u64 limbs per coordinate
+        assert pt[2 * fl:].any(), "an MSM of the fixture is the point at infinity"
+        one = pt[2 * fl:]                           # Z of a normalised point = one
+        win = np.ascontiguousarray(np.concatenate([pt[:2 * fl], one, one]))       # X | Y | ZZ | ZZZ
+        assert win.nbytes == L.b200_msm_window_bytes(cid, grp)
+        blob[at:at + win.nbytes] = win.view(np.uint8)
+        at += L.b200_msm_num_windows(cid, sizes[q]) * win.nbytes
+    assert at == blob.shape[0]
+    got = b.groth16_assemble(curve, key["alpha_g1"], key["beta_g1"], key["beta_g2"], key["delta_g1"], key["delta_g2"], sizes, 1,
+                             blob, r, s)
+    assert np.array_equal(got, proof)
