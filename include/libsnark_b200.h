@@ -196,7 +196,9 @@ int b200_groth16_pk_free(b200_groth16_pk_t handle);
  * arrays of Montgomery Fr, r and s the zero-knowledge randomness (the reference draws them at
  * .tcc:499-500; the caller supplies them here so that proofs are reproducible). proof_out =
  * g_A (G1) | g_B (G2) | g_C (G1), normalised, reference layouts. stage_ms (nullable, 7 doubles):
- * witness upload, witness map, A, B, H, L, total. */
+ * witness upload, witness map, A, B, H, L, total — the five MSMs run concurrently, so A..L are the wall clock of
+ * each inside its own execution slot and do not add up to the total. An auxiliary_input in page-locked memory
+ * (cudaHostAlloc / cudaHostRegister) is uploaded from where it lies; pageable memory is staged by a few host threads. */
 int b200_groth16_prove(b200_groth16_pk_t handle, const void *primary_input,
                        const void *auxiliary_input, const void *r, const void *s, void *proof_out,
                        double *stage_ms);
