@@ -83,9 +83,10 @@ int b200_bases_upload(int curve, int group, const void *bases, size_t base_strid
  * times the set's device memory (2^20 alt_bn128 G1 points: 64 MiB -> 1 GiB) and one field inversion per
  * table entry, once. The reference's counterpart of trading memory for window work is the fixed-base
  * window table of batch_exp (multiexp.tcc:809-946). Results are unchanged (same group element).
- * b200_bases_table_rows: W after a successful precompute, else 0. */
+ * b200_bases_table_rows: W after a successful precompute, else 0; b200_bases_table_window_bits: the table's c. */
 int b200_bases_precompute(b200_bases_t handle);
 int b200_bases_table_rows(b200_bases_t handle);
+int b200_bases_table_window_bits(b200_bases_t handle);
 int b200_bases_free(b200_bases_t handle);
 size_t b200_bases_size(b200_bases_t handle);
 
@@ -202,6 +203,14 @@ int b200_groth16_pk_free(b200_groth16_pk_t handle);
 int b200_groth16_prove(b200_groth16_pk_t handle, const void *primary_input,
                        const void *auxiliary_input, const void *r, const void *s, void *proof_out,
                        double *stage_ms);
+/* The same prover with the witness already in HBM: b200_groth16_witness_upload places (1 | primary | auxiliary)
+ * in the key's device buffer (what b200_groth16_prove does first), b200_groth16_prove_resident runs everything
+ * after that copy — r1cs_gg_ppzksnark.tcc:489-598 on the resident witness — so that a caller who proves several
+ * (r, s) over one witness, or a benchmark that separates the PCIe copy from the compute, pays the upload once.
+ * stage_ms as b200_groth16_prove with the upload entry 0. */
+int b200_groth16_witness_upload(b200_groth16_pk_t handle, const void *primary_input, const void *auxiliary_input);
+int b200_groth16_prove_resident(b200_groth16_pk_t handle, const void *r, const void *s, void *proof_out,
+                                double *stage_ms);
 
 /* ---- the prover sharded over the GPUs of one box (the reference splits every multi_exp
  *      over OpenMP threads the same way, multiexp.tcc:663-687). One process per GPU; rank g of `world`

@@ -42,6 +42,7 @@ EXPORTS = [
     "b200_shard_range", "b200_groth16_shard_bytes", "b200_groth16_pk_create_shard", "b200_groth16_prove_shard",
     "b200_groth16_shard_begin", "b200_groth16_shard_chain", "b200_groth16_shard_h", "b200_groth16_shard_msm",
     "b200_groth16_assemble", "b200_bases_precompute", "b200_bases_table_rows", "b200_groth16_shard_witness_copy", "b200_batch_exp", "b200_groth16_shard_finish_msm",
+    "b200_groth16_witness_upload", "b200_groth16_prove_resident", "b200_bases_table_window_bits",
 ]
 
 
@@ -82,6 +83,7 @@ def lib():
         L.b200_bases_free.argtypes = [u64]
         L.b200_bases_precompute.argtypes = [u64]
         L.b200_bases_table_rows.argtypes = [u64]
+        L.b200_bases_table_window_bits.argtypes = [u64]
         L.b200_bases_size.restype = sz
         L.b200_bases_size.argtypes = [u64]
         L.b200_msm_resident.argtypes = [u64, sz, sz, vp, i, vp]
@@ -108,6 +110,8 @@ def lib():
                                              C.POINTER(u64)]
         L.b200_groth16_pk_free.argtypes = [u64]
         L.b200_groth16_prove.argtypes = [u64, vp, vp, vp, vp, vp, C.POINTER(C.c_double)]
+        L.b200_groth16_witness_upload.argtypes = [u64, vp, vp]
+        L.b200_groth16_prove_resident.argtypes = [u64, vp, vp, vp, C.POINTER(C.c_double)]
         L.b200_witness_chain_r1cs_dev.argtypes = [u64, vp, sz, i, vp]
         L.b200_witness_finish_dev.argtypes = [i, vp, vp, vp, sz, vp]
         L.b200_shard_range.restype = None
@@ -470,6 +474,19 @@ class Groth16ProvingKey:
         out = np.zeros(self._proof_limbs, dtype=np.uint64)
         ms = (C.c_double * 7)()
         _check(lib().b200_groth16_prove(self.handle, _p(pi), _p(ai), _p(r), _p(s), _p(out), ms))
+        return out, dict(zip(["upload", "witness_map", "A", "B", "H", "L", "total"], list(ms)))
+
+    def upload_witness(self, primary_input, auxiliary_input):
+        """(1 | primary | auxiliary) into the key's device buffer (b200_groth16_witness_upload)."""
+        pi, ai = _u64(primary_input), _u64(auxiliary_input)
+        _check(lib().b200_groth16_witness_upload(self.handle, _p(pi), _p(ai)))
+
+    def prove_resident(self, r, s):
+        """prove() over the witness last uploaded (b200_groth16_prove_resident): no host-to-device copy."""
+        r, s = _u64(r), _u64(s)
+        out = np.zeros(self._proof_limbs, dtype=np.uint64)
+        ms = (C.c_double * 7)()
+        _check(lib().b200_groth16_prove_resident(self.handle, _p(r), _p(s), _p(out), ms))
         return out, dict(zip(["upload", "witness_map", "A", "B", "H", "L", "total"], list(ms)))
 
     def free(self):

@@ -272,6 +272,13 @@ int b200_bases_table_rows(b200_bases_t handle)
     return it == g_sets.end() ? 0 : it->second.table_W;
 }
 
+int b200_bases_table_window_bits(b200_bases_t handle)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_sets.find(handle);
+    return it == g_sets.end() ? 0 : it->second.table_c;
+}
+
 size_t b200_bases_size(b200_bases_t handle)
 {
     std::lock_guard<std::mutex> lk(g_mu);

@@ -475,7 +475,7 @@ int shard_msms(const ProvingKey &pk, unsigned mask, void *dev_blob, double *ms5,
 // r1cs_gg_ppzksnark_prover over a one-GPU key (b200_groth16_prove).
 template<int CURVE>
 int prove_impl(const ProvingKey &pk, const void *primary_input, const void *auxiliary_input, const void *r, const void *s,
-               void *proof_out, double *stage_ms)
+               void *proof_out, double *stage_ms, bool witness_resident = false)
 {
     const size_t fr = b200_sizeof_fr(pk.curve);
     const size_t g1 = b200_sizeof_group(pk.curve, B200_G1), g2 = b200_sizeof_group(pk.curve, B200_G2);
@@ -486,7 +486,7 @@ int prove_impl(const ProvingKey &pk, const void *primary_input, const void *auxi
     auto f_pre = std::async(std::launch::async, [&]() { return pre_assemble<CURVE>(kp, r, s); });
 
     int rc;
-    if ((rc = upload_witness(pk, primary_input, auxiliary_input))) {
+    if (!witness_resident && (rc = upload_witness(pk, primary_input, auxiliary_input))) {
         return rc;
     }
     st[0] = now_ms() - t0;
@@ -646,6 +646,39 @@ int b200_groth16_prove(b200_groth16_pk_t handle, const void *primary_input, cons
     case B200_ALT_BN128: return prove_impl<CURVE_ALT_BN128>(pk, primary_input, auxiliary_input, r, s, proof_out, stage_ms);
     case B200_BLS12_377: return prove_impl<CURVE_BLS12_377>(pk, primary_input, auxiliary_input, r, s, proof_out, stage_ms);
     default: return prove_impl<CURVE_BW6_761>(pk, primary_input, auxiliary_input, r, s, proof_out, stage_ms);
+    }
+}
+
+int b200_groth16_witness_upload(b200_groth16_pk_t handle, const void *primary_input, const void *auxiliary_input)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    const ProvingKey *pk = find_key(handle);
+    if (!pk) {
+        return B200_ERR_HANDLE;
+    }
+    if (!auxiliary_input || (pk->ni && !primary_input)) {
+        return rt::set_error(B200_ERR_ARG, "null input");
+    }
+    return upload_witness(*pk, primary_input, auxiliary_input);
+}
+
+int b200_groth16_prove_resident(b200_groth16_pk_t handle, const void *r, const void *s, void *proof_out, double *stage_ms)
+{
+    if (!r || !s || !proof_out) {
+        return rt::set_error(B200_ERR_ARG, "null pointer");
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    const ProvingKey *pk = find_key(handle);
+    if (!pk) {
+        return B200_ERR_HANDLE;
+    }
+    if (pk->world != 1) {
+        return rt::set_error(B200_ERR_ARG, "b200_groth16_prove_resident needs a whole (unsharded) key");
+    }
+    switch (pk->curve) {
+    case B200_ALT_BN128: return prove_impl<CURVE_ALT_BN128>(*pk, nullptr, nullptr, r, s, proof_out, stage_ms, true);
+    case B200_BLS12_377: return prove_impl<CURVE_BLS12_377>(*pk, nullptr, nullptr, r, s, proof_out, stage_ms, true);
+    default: return prove_impl<CURVE_BW6_761>(*pk, nullptr, nullptr, r, s, proof_out, stage_ms, true);
     }
 }
 
