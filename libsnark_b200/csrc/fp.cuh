@@ -427,6 +427,101 @@ template<class P> struct alignas(16) Fp {
         }
         return result;
     }
+
+    // The same value as inverse() by the binary extended Euclidean algorithm on the residue: subtractions, shifts and
+    // selects only, no multiplications but the closing fix-up. It exists for the top of the batched inversion trees of
+    // the MSM's affine rounds (msm_affine.cuh), where a handful of warps invert a few thousand values and what counts
+    // is the LATENCY of one inversion: the Fermat chain above is bits(p) dependent Montgomery products (~0.2 ms alone
+    // on an SM for 254 bits, milliseconds for bw6_761's 761); one step here is a few short carry chains.
+    //   u = a, v = p, x1 = 1, x2 = 0;  invariants x1 a == u, x2 a == v (mod p), v odd.
+    //   step: u even -> u /= 2, x1 /= 2 (mod p);  u odd -> order so that u >= v, then u = (u - v) / 2, x1 = (x1 - x2) / 2.
+    //   every step removes a bit of u or v, so u reaches 0 within 2 bits(p) steps, with v = gcd = 1 and x2 = a^-1.
+    // Each step is written branch-free (the lanes of a warp run different inputs). this = aR (Montgomery) -> returns
+    // a^-1 R = (aR)^-1 R^2 = montmul((aR)^-1, R^3). Zero maps to zero.
+    HD Fp inverse_fast() const
+    {
+        uint32_t u[N], w[N], x1[N], x2[N];
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            u[i] = v[i];
+            w[i] = P::mod(i);
+            x1[i] = i == 0 ? 1u : 0u;
+            x2[i] = 0u;
+        }
+        for (int step = 0; step < 2 * 32 * N; ++step) {
+            uint32_t nz = 0;
+#pragma unroll
+            for (int i = 0; i < N; ++i) {
+                nz |= u[i];
+            }
+            if (nz == 0) {
+                break;
+            }
+            const uint32_t odd = 0u - (u[0] & 1u);              // all-ones when u is odd
+            // borrow of u - w: u < w
+            prim::sub_cc(u[0], w[0]);
+#pragma unroll
+            for (int i = 1; i < N; ++i) {
+                prim::subc_cc(u[i], w[i]);
+            }
+            const uint32_t lt = prim::subc(0, 0);                // all-ones when u < w
+            const uint32_t sw = odd & lt;
+#pragma unroll
+            for (int i = 0; i < N; ++i) {                         // conditional swap (u, x1) <-> (w, x2)
+                const uint32_t du = (u[i] ^ w[i]) & sw, dx = (x1[i] ^ x2[i]) & sw;
+                u[i] ^= du;
+                w[i] ^= du;
+                x1[i] ^= dx;
+                x2[i] ^= dx;
+            }
+            // u -= w when odd (then u is even)
+            u[0] = prim::sub_cc(u[0], w[0] & odd);
+#pragma unroll
+            for (int i = 1; i < N; ++i) {
+                u[i] = prim::subc_cc(u[i], w[i] & odd);
+            }
+            // x1 = x1 - x2 mod p when odd
+            x1[0] = prim::sub_cc(x1[0], x2[0] & odd);
+#pragma unroll
+            for (int i = 1; i < N; ++i) {
+                x1[i] = prim::subc_cc(x1[i], x2[i] & odd);
+            }
+            const uint32_t neg = prim::subc(0, 0);
+            x1[0] = prim::add_cc(x1[0], P::mod(0) & neg);
+#pragma unroll
+            for (int i = 1; i < N - 1; ++i) {
+                x1[i] = prim::addc_cc(x1[i], P::mod(i) & neg);
+            }
+            x1[N - 1] = prim::addc(x1[N - 1], P::mod(N - 1) & neg);
+            // u /= 2
+#pragma unroll
+            for (int i = 0; i < N - 1; ++i) {
+                u[i] = (u[i] >> 1) | (u[i + 1] << 31);
+            }
+            u[N - 1] >>= 1;
+            // x1 = x1 / 2 mod p: (x1 + p when odd) >> 1; x1 + p < 2p < 2^(32N)
+            const uint32_t xo = 0u - (x1[0] & 1u);
+            x1[0] = prim::add_cc(x1[0], P::mod(0) & xo);
+#pragma unroll
+            for (int i = 1; i < N - 1; ++i) {
+                x1[i] = prim::addc_cc(x1[i], P::mod(i) & xo);
+            }
+            x1[N - 1] = prim::addc(x1[N - 1], P::mod(N - 1) & xo);
+#pragma unroll
+            for (int i = 0; i < N - 1; ++i) {
+                x1[i] = (x1[i] >> 1) | (x1[i + 1] << 31);
+            }
+            x1[N - 1] >>= 1;
+        }
+        Fp r;
+        const bool z = is_zero();
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            r.v[i] = z ? 0u : x2[i];
+        }
+        const Fp r3 = r2() * r2(); // R^2 * R^2 * R^-1 = R^3
+        return r * r3;
+    }
 };
 
 // Fp2 = Fp[u] / (u^2 - nr).  libff Fp2_model (fp2.hpp; mul fp2.tcc:102-114 Karatsuba,
@@ -502,6 +597,11 @@ template<class P2> struct Fp2 {
         const F t1 = c1.sqr();
         const F t2 = t0 - P2::mul_by_nr(t1);
         const F t3 = t2.inverse();
+        return Fp2{c0 * t3, (c1 * t3).neg()};
+    }
+    HD Fp2 inverse_fast() const
+    {
+        const F t3 = (c0.sqr() - P2::mul_by_nr(c1.sqr())).inverse_fast();
         return Fp2{c0 * t3, (c1 * t3).neg()};
     }
 };

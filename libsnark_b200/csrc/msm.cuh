@@ -185,18 +185,19 @@ struct Task {
 
 HD void build_tasks_body(
     size_t b, const uint32_t *counts, const uint32_t *offsets, const uint32_t *task_off, Task *tasks,
-    uint32_t *multi_count, uint32_t *multi_list, uint32_t collapse)
+    uint32_t *multi_count, uint32_t *multi_list, uint32_t collapse, uint32_t rounds = 0, uint32_t seg = SEG)
 {
-    const uint32_t cnt = counts[b];
+    // with affine rounds (msm_affine.cuh) the tasks are cut over the bucket's survivors
+    const uint32_t cnt = padded_count(counts[b], rounds) >> rounds;
     const uint32_t first = task_off[b];
-    const uint32_t off = offsets[b];
-    for (uint32_t s = 0, done = 0; done < cnt; ++s, done += SEG) {
+    const uint32_t off = offsets[b] >> rounds;
+    for (uint32_t s = 0, done = 0; done < cnt; ++s, done += seg) {
         Task tk;
         tk.start = off + done;
-        tk.len = (cnt - done) < (uint32_t)SEG ? (cnt - done) : (uint32_t)SEG;
+        tk.len = (cnt - done) < seg ? (cnt - done) : seg;
         tasks[first + s] = tk;
     }
-    if (cnt > collapse * (uint32_t)SEG) { // many tasks: their partial sums are merged by k_collapse
+    if (cnt > collapse * seg) { // many tasks: their partial sums are merged by k_collapse
 #if defined(__CUDA_ARCH__)
         multi_list[atomicAdd(multi_count, 1u)] = (uint32_t)b;
 #else
@@ -427,16 +428,24 @@ __device__ __forceinline__ uint2 block_exclusive_scan2(uint2 v, uint2 *total)
     return make_uint2(base.x + inc.x - v.x, base.y + inc.y - v.y);
 }
 
-static __global__ void k_scan_tiles(const uint32_t *counts, uint32_t nb, uint2 *tile_sums)
+// Both scans see a bucket's count padded to a multiple of 2^rounds (affine rounds, msm_affine.cuh; rounds = 0: as is).
+__device__ __forceinline__ uint2 scan_item(uint32_t c, uint32_t rounds)
+{
+    const uint32_t p = padded_count(c, rounds);
+    const uint32_t seg = rounds ? SEG_PTS : SEG; // Geometry::seg
+    return make_uint2(p, ((p >> rounds) + seg - 1) / seg);
+}
+
+static __global__ void k_scan_tiles(const uint32_t *counts, uint32_t nb, uint2 *tile_sums, uint32_t rounds)
 {
     const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
     uint2 s = make_uint2(0, 0);
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; ++k) {
         const uint32_t i = base + k;
-        const uint32_t c = i < nb ? counts[i] : 0u;
-        s.x += c;
-        s.y += (c + SEG - 1) / SEG;
+        const uint2 it = scan_item(i < nb ? counts[i] : 0u, rounds);
+        s.x += it.x;
+        s.y += it.y;
     }
     uint2 tot;
     block_exclusive_scan2(s, &tot);
@@ -464,7 +473,7 @@ static __global__ void k_scan_tile_sums(uint2 *tile_sums, uint32_t ntiles)
 
 static __global__ void k_scan_finish(
     const uint32_t *counts, uint32_t nb, const uint2 *tile_sums, uint32_t *offsets, uint32_t *cursor,
-    uint32_t *task_off)
+    uint32_t *task_off, uint32_t rounds)
 {
     const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
     uint32_t c[SCAN_ITEMS];
@@ -473,8 +482,9 @@ static __global__ void k_scan_finish(
     for (int k = 0; k < SCAN_ITEMS; ++k) {
         const uint32_t i = base + k;
         c[k] = i < nb ? counts[i] : 0u;
-        s.x += c[k];
-        s.y += (c[k] + SEG - 1) / SEG;
+        const uint2 it = scan_item(c[k], rounds);
+        s.x += it.x;
+        s.y += it.y;
     }
     uint2 tot;
     uint2 ex = block_exclusive_scan2(s, &tot);
@@ -489,8 +499,9 @@ static __global__ void k_scan_finish(
             cursor[i] = ex.x;
             task_off[i] = ex.y;
         }
-        ex.x += c[k];
-        ex.y += (c[k] + SEG - 1) / SEG;
+        const uint2 it = scan_item(c[k], rounds);
+        ex.x += it.x;
+        ex.y += it.y;
         if (i + 1 == nb) { // totals
             offsets[nb] = ex.x;
             task_off[nb] = ex.y;
@@ -500,11 +511,12 @@ static __global__ void k_scan_finish(
 
 static __global__ void k_build_tasks(
     const uint32_t *counts, const uint32_t *offsets, const uint32_t *task_off, uint32_t nb, Task *tasks,
-    uint32_t *multi_count, uint32_t *multi_list, uint32_t collapse)
+    uint32_t *multi_count, uint32_t *multi_list, uint32_t collapse, uint32_t rounds)
 {
     const size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (b < nb) {
-        build_tasks_body(b, counts, offsets, task_off, tasks, multi_count, multi_list, collapse);
+        build_tasks_body(b, counts, offsets, task_off, tasks, multi_count, multi_list, collapse, rounds,
+                         rounds ? (uint32_t)SEG_PTS : (uint32_t)SEG);
     }
 }
 

@@ -1,0 +1,351 @@
+// msm_affine.cuh — batched-affine rounds in front of the bucket accumulation.
+//
+// The bucket loop of libff's multi_exp_inner (multiexp.tcc:540-550, mixed_add into a Jacobian bucket, 11 field
+// products) became an XYZZ mixed add in msm.cuh (10 products). The integer pipe is ~87 % busy in that kernel, so the
+// only way left to go faster is to spend fewer products per addition: an AFFINE addition
+//     lambda = (y2 - y1) / (x2 - x1),  x3 = lambda^2 - x1 - x2,  y3 = lambda (x1 - x3) - y1
+// costs 2 products + 1 square + ONE INVERSION, and inversions batch: with Montgomery's trick n inversions cost one
+// inversion + 3 (n - 1) products (libff uses the same trick in batch_invert, field_utils.tcc:330-350). One ROUND adds
+// the sorted entries of every bucket pairwise — (e0 + e1), (e2 + e3), ... — halving every bucket; all pairs of the
+// round, of all buckets, share one tree of batched inversions, so an addition costs ~6.3 products instead of 10.
+// After `rounds` rounds (Geometry::rounds, 0-4) the survivors — 1/2^rounds of the entries — go through the XYZZ
+// accumulation of msm.cuh as before. The sum of a bucket is a group element: the order of the additions cannot be
+// seen in the result, which stays bit-identical to the reference's after normalisation.
+//
+// Layout. The counting sort pads every bucket to a multiple of 2^rounds entries (pad = NULL_ENTRY), so pair q of round
+// r is simply elements (2q, 2q + 1) of the previous round's array and never straddles two buckets; bucket b's
+// survivors sit at offsets[b] >> rounds. A pad, and the sum P + (-P), is the affine pair (0, 0) — not a point of
+// y^2 = x^3 + b for b != 0 — which every later stage treats as the neutral element.
+//
+// One round = 7 launches:  up0 (per pair: denominator d = x2 - x1, running products per thread) -> up (two more
+// levels of running products, AFF_K elements per thread) -> top (one inversion per remaining element, binary
+// Euclid, Fp::inverse_fast) -> down, down (inverses of every level's elements) -> down0 (inverse of each pair's d,
+// the affine addition, result written). Thread t of a level owns elements t, t + T, t + 2T, ... (T = threads of the
+// level), so every access is coalesced.
+#pragma once
+#include "msm.cuh"
+
+namespace b200
+{
+namespace msm
+{
+
+constexpr int AFF_K = 16;                       // elements per thread at every level of the inversion tree
+constexpr uint32_t NULL_ENTRY = 0xffffffffu;    // padding of the entries array
+
+struct AffLevels {
+    uint32_t pairs, n1, n2, n3;
+};
+HD AffLevels aff_levels(uint32_t total_entries, int round)
+{
+    AffLevels lv;
+    lv.pairs = total_entries >> round;
+    lv.n1 = (lv.pairs + AFF_K - 1) / AFF_K;
+    lv.n2 = (lv.n1 + AFF_K - 1) / AFF_K;
+    lv.n3 = (lv.n2 + AFF_K - 1) / AFF_K;
+    return lv;
+}
+
+template<class F> HD Affine<F> null_point()
+{
+    Affine<F> p;
+    p.x = F::zero();
+    p.y = F::zero();
+    return p;
+}
+template<class F> HD bool is_null(const Affine<F> &p) { return p.x.is_zero() && p.y.is_zero(); }
+
+// Where a round's inputs come from: round 1 reads (index | sign) entries and gathers the bases, later rounds read the
+// previous round's points.
+template<class F> struct SrcEntries {
+    const uint32_t *entries;
+    const Affine<F> *bases;
+    HD Affine<F> load(uint32_t i) const
+    {
+        const uint32_t e = entries[i];
+        if (e == NULL_ENTRY) {
+            return null_point<F>();
+        }
+        Affine<F> p = load_vec_ro(bases + (e & 0x7fffffffu));
+        p.y = p.y.cneg((e >> 31) != 0);
+        return p;
+    }
+    // x only (the common case of the up pass needs nothing else); null reported through the flag
+    HD F load_x(uint32_t i, bool &null) const
+    {
+        const uint32_t e = entries[i];
+        null = e == NULL_ENTRY;
+        if (null) {
+            return F::zero();
+        }
+        return load_vec_ro(&bases[e & 0x7fffffffu].x);
+    }
+};
+template<class F> struct SrcPoints {
+    const Affine<F> *pts;
+    HD Affine<F> load(uint32_t i) const { return load_vec(pts + i); }
+    HD F load_x(uint32_t i, bool &null) const
+    {
+        const F x = load_vec(&pts[i].x);
+        null = false;
+        if (x.is_zero()) { // (0, 0) is the neutral element; (0, y != 0) may be a point
+            null = load_vec(&pts[i].y).is_zero();
+        }
+        return x;
+    }
+};
+
+// What a pair needs inverted, and what kind of pair it is.
+enum PairKind { PAIR_ADD = 0, PAIR_DBL = 1, PAIR_NULL = 2, PAIR_KEEP_A = 3, PAIR_KEEP_B = 4 };
+
+template<class F> HD F pair_den(const Affine<F> &A, const Affine<F> &B, int &kind)
+{
+    const bool an = is_null(A), bn = is_null(B);
+    if (an || bn) {
+        kind = an ? (bn ? PAIR_NULL : PAIR_KEEP_B) : PAIR_KEEP_A;
+        return F::one();
+    }
+    const F d = B.x - A.x;
+    if (d.is_zero()) {
+        if (A.y == B.y && !A.y.is_zero()) {
+            kind = PAIR_DBL; // P + P: lambda = 3 x^2 / (2 y)
+            return A.y.dbl();
+        }
+        kind = PAIR_NULL; // P + (-P)
+        return F::one();
+    }
+    kind = PAIR_ADD;
+    return d;
+}
+
+// The same denominator from the x coordinates alone where that is enough (up pass).
+template<class F, class Src> HD F pair_den_x(const Src &src, uint32_t q)
+{
+    bool an, bn;
+    const F ax = src.load_x(2 * q, an);
+    const F bx = src.load_x(2 * q + 1, bn);
+    if (an || bn) {
+        return F::one();
+    }
+    const F d = bx - ax;
+    if (d.is_zero()) { // rare: needs the y coordinates
+        int kind;
+        return pair_den(src.load(2 * q), src.load(2 * q + 1), kind);
+    }
+    return d;
+}
+
+// ---- level 0, up: thread t multiplies the denominators of its pairs, leaving every running product in P0 ----------
+// The denominators do not depend on the running product: they are fetched AFF_U pairs ahead of the chain of products so
+// that the gathers (round 1: two 32-byte x coordinates per pair out of a table far larger than L2) overlap it.
+constexpr int AFF_U = 4;
+template<class F, class Src> HD void aff_up0_body(uint32_t t, const AffLevels &lv, const Src &src, F *P0, F *T1)
+{
+    F acc = F::one();
+    for (int j0 = 0; j0 < AFF_K; j0 += AFF_U) {
+        F d[AFF_U];
+#pragma unroll
+        for (int u = 0; u < AFF_U; ++u) {
+            const uint32_t q = (uint32_t)(j0 + u) * lv.n1 + t;
+            d[u] = q < lv.pairs ? pair_den_x<F, Src>(src, q) : F::one();
+        }
+#pragma unroll
+        for (int u = 0; u < AFF_U; ++u) {
+            const uint32_t q = (uint32_t)(j0 + u) * lv.n1 + t;
+            if (q < lv.pairs) {
+                acc = (j0 + u) ? acc * d[u] : d[u];
+                store_vec(P0 + q, acc);
+            }
+        }
+    }
+    store_vec(T1 + t, acc);
+}
+
+// ---- upper levels, up: the same over an array E of `count` elements, `threads` = ceil(count / AFF_K) -----------------
+template<class F> HD void aff_up_body(uint32_t t, uint32_t count, uint32_t threads, const F *E, F *Pre, F *T)
+{
+    F acc = F::one();
+    for (int j0 = 0; j0 < AFF_K; j0 += AFF_U) {
+        F e[AFF_U];
+#pragma unroll
+        for (int u = 0; u < AFF_U; ++u) {
+            const uint32_t q = (uint32_t)(j0 + u) * threads + t;
+            e[u] = q < count ? load_vec(E + q) : F::one();
+        }
+#pragma unroll
+        for (int u = 0; u < AFF_U; ++u) {
+            const uint32_t q = (uint32_t)(j0 + u) * threads + t;
+            if (q < count) {
+                acc = (j0 + u) ? acc * e[u] : e[u];
+                store_vec(Pre + q, acc);
+            }
+        }
+    }
+    store_vec(T + t, acc);
+}
+
+// ---- upper levels, down: Inv[t] = inverse of thread t's total; E is overwritten by the inverses of its elements ----
+template<class F> HD void aff_down_body(uint32_t t, uint32_t count, uint32_t threads, F *E, const F *Pre, const F *Inv)
+{
+    F inv = load_vec(Inv + t);
+    for (int j0 = AFF_K - AFF_U; j0 >= 0; j0 -= AFF_U) {
+        F e[AFF_U], prev[AFF_U];
+#pragma unroll
+        for (int u = AFF_U - 1; u >= 0; --u) {
+            const int j = j0 + u;
+            const uint32_t q = (uint32_t)j * threads + t;
+            if (q < count && j) {
+                e[u] = load_vec(E + q);
+                prev[u] = load_vec(Pre + (q - threads));
+            }
+        }
+#pragma unroll
+        for (int u = AFF_U - 1; u >= 0; --u) {
+            const int j = j0 + u;
+            const uint32_t q = (uint32_t)j * threads + t;
+            if (q >= count) {
+                continue;
+            }
+            if (j == 0) {
+                store_vec(E + q, inv);
+            } else {
+                store_vec(E + q, inv * prev[u]);
+                inv = inv * e[u];
+            }
+        }
+    }
+}
+
+// ---- level 0, down: inverse of each pair's denominator, then the affine addition -----------------------------------
+template<class F> HD Affine<F> pair_add(const Affine<F> &A, const Affine<F> &B, int kind, const F &dinv)
+{
+    F num = B.y - A.y;
+    if (kind == PAIR_DBL) {
+        const F x2 = A.x.sqr();
+        num = x2.dbl() + x2;
+    }
+    const F lam = num * dinv;
+    Affine<F> r;
+    r.x = lam.sqr() - A.x - B.x;
+    r.y = lam * (A.x - r.x) - A.y;
+    if (kind >= PAIR_NULL) {
+        r = kind == PAIR_NULL ? null_point<F>() : (kind == PAIR_KEEP_A ? A : B);
+    }
+    return r;
+}
+
+template<class F, class Src>
+HD void aff_down0_body(uint32_t t, const AffLevels &lv, const Src &src, const F *P0, const F *I1, Affine<F> *out)
+{
+    F inv = load_vec(I1 + t);
+    int j = AFF_K - 1;
+    while (j > 0 && (uint32_t)j * lv.n1 + t >= lv.pairs) {
+        --j;
+    }
+#if defined(B200_ACC_NO_PREFETCH)
+    for (; j >= 0; --j) {
+        const uint32_t q = (uint32_t)j * lv.n1 + t;
+        const Affine<F> A = src.load(2 * q), B = src.load(2 * q + 1);
+        int kind;
+        const F d = pair_den(A, B, kind);
+        F dinv = inv;
+        if (j) {
+            dinv = inv * load_vec(P0 + (q - lv.n1));
+            inv = inv * d;
+        }
+        store_vec(out + q, pair_add(A, B, kind, dinv));
+    }
+#else
+    // the operands of pair j - 1 are fetched while pair j is added
+    uint32_t q = (uint32_t)j * lv.n1 + t;
+    Affine<F> nA = src.load(2 * q), nB = src.load(2 * q + 1);
+    F nP = j ? load_vec(P0 + (q - lv.n1)) : F::one();
+    for (; j >= 0; --j) {
+        q = (uint32_t)j * lv.n1 + t;
+        const Affine<F> A = nA, B = nB;
+        const F prev = nP;
+        if (j) {
+            const uint32_t qn = q - lv.n1;
+            nA = src.load(2 * qn);
+            nB = src.load(2 * qn + 1);
+            if (j > 1) {
+                nP = load_vec(P0 + (qn - lv.n1));
+            }
+        }
+        int kind;
+        const F d = pair_den(A, B, kind);
+        F dinv = inv;
+        if (j) {
+            dinv = inv * prev;
+            inv = inv * d;
+        }
+        store_vec(out + q, pair_add(A, B, kind, dinv));
+    }
+#endif
+}
+
+// ---- the XYZZ accumulation over the survivors (points instead of entries; (0, 0) skipped) ---------------------------
+template<class F> HD void accumulate_task_pts(const Task &tk, const Affine<F> *pts, XYZZ<F> *out)
+{
+    XYZZ<F> acc = XYZZ<F>::inf();
+#if defined(B200_ACC_NO_PREFETCH)
+    for (uint32_t k = 0; k < tk.len; ++k) {
+        const Affine<F> cur = load_vec(pts + tk.start + k);
+        if (!is_null(cur)) {
+            madd(acc, cur);
+        }
+    }
+#else
+    Affine<F> p = load_vec(pts + tk.start);
+    for (uint32_t k = 0; k < tk.len; ++k) {
+        const Affine<F> cur = p;
+        if (k + 1 < tk.len) { // the next survivor is fetched while this one is added
+            p = load_vec(pts + tk.start + k + 1);
+        }
+        if (!is_null(cur)) {
+            madd(acc, cur);
+        }
+    }
+#endif
+    store_vec(out, acc);
+}
+
+#if defined(__CUDACC__)
+constexpr int AFF_THREADS = 128;
+
+template<class F, class Src>
+__global__ void __launch_bounds__(AFF_THREADS) k_aff_up0(const uint32_t *total_entries, int round, Src src, F *P0, F *T1)
+{
+    const AffLevels lv = aff_levels(*total_entries, round);
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < lv.n1) {
+        aff_up0_body<F, Src>(t, lv, src, P0, T1);
+    }
+}
+
+template<class F, class Src>
+__global__ void __launch_bounds__(AFF_THREADS) k_aff_down0(const uint32_t *total_entries, int round, Src src, const F *P0,
+                                                           const F *I1, Affine<F> *out)
+{
+    const AffLevels lv = aff_levels(*total_entries, round);
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < lv.n1) {
+        aff_down0_body<F, Src>(t, lv, src, P0, I1, out);
+    }
+}
+
+// Survivors through the XYZZ path: same CTA-local ordering by task length as k_accumulate.
+template<class F>
+__global__ void __launch_bounds__(ACC_THREADS, B200_ACC_MIN_BLOCKS) k_accumulate_pts(
+    const Task *tasks, const uint32_t *num_tasks, const Affine<F> *pts, XYZZ<F> *partial)
+{
+    const uint32_t T = *num_tasks;
+    const uint32_t id = blockIdx.x * ACC_THREADS + threadIdx.x;
+    if (id < T) {
+        accumulate_task_pts<F>(tasks[id], pts, partial + id);
+    }
+}
+#endif
+
+} // namespace msm
+} // namespace b200

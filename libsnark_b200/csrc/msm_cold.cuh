@@ -4,6 +4,7 @@
 // comparatively few warps, so compact code beats inlined code.
 #pragma once
 #include "msm.cuh"
+#include "msm_affine.cuh"
 #include "runtime.hpp"
 
 namespace b200
@@ -112,6 +113,57 @@ __global__ void __launch_bounds__(128) k_build_table(size_t n, int c, int W, Aff
 template<class F> int table_launch(size_t n, int c, int W, Affine<F> *table, const uint8_t *inf, uint32_t *fail)
 {
     k_build_table<F><<<(unsigned)((n + 127) / 128), 128, 0, rt::stream()>>>(n, c, W, table, inf, fail);
+    B200_LAUNCH_CHECK();
+    return B200_OK;
+}
+
+// ---- the upper levels of an affine round's inversion tree (msm_affine.cuh): few threads, chains of dependent products ----
+// level 1: elements = T1 (lv.n1 of them), threads = lv.n2; level 2: elements = T2 (lv.n2), threads = lv.n3.
+template<class F>
+__global__ void __launch_bounds__(128) k_aff_up(const uint32_t *total_entries, int round, int level, const F *E, F *Pre, F *T)
+{
+    const AffLevels lv = aff_levels(*total_entries, round);
+    const uint32_t count = level == 1 ? lv.n1 : lv.n2, threads = level == 1 ? lv.n2 : lv.n3;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < threads) {
+        aff_up_body<F>(t, count, threads, E, Pre, T);
+    }
+}
+template<class F>
+__global__ void __launch_bounds__(128) k_aff_down(const uint32_t *total_entries, int round, int level, F *E, const F *Pre, const F *Inv)
+{
+    const AffLevels lv = aff_levels(*total_entries, round);
+    const uint32_t count = level == 1 ? lv.n1 : lv.n2, threads = level == 1 ? lv.n2 : lv.n3;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < threads) {
+        aff_down_body<F>(t, count, threads, E, Pre, Inv);
+    }
+}
+// One inversion per element of the top level, 32 threads per CTA so that the few hundred warps spread over all SMs.
+template<class F> __global__ void __launch_bounds__(32) k_aff_top(const uint32_t *total_entries, int round, F *T3)
+{
+    const AffLevels lv = aff_levels(*total_entries, round);
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < lv.n3) {
+        store_vec(T3 + t, load_vec(T3 + t).inverse_fast());
+    }
+}
+
+template<class F>
+int affine_tree_launch(const uint32_t *total_entries, int round, uint32_t max_entries, F *T1, F *P1, F *T2, F *P2, F *T3)
+{
+    cudaStream_t s = rt::stream();
+    const AffLevels mx = aff_levels(max_entries, round);
+    const auto grid = [](uint32_t n, uint32_t b) { return (n + b - 1) / b; };
+    k_aff_up<F><<<grid(mx.n2, 128), 128, 0, s>>>(total_entries, round, 1, T1, P1, T2);
+    B200_LAUNCH_CHECK();
+    k_aff_up<F><<<grid(mx.n3, 128), 128, 0, s>>>(total_entries, round, 2, T2, P2, T3);
+    B200_LAUNCH_CHECK();
+    k_aff_top<F><<<grid(mx.n3, 32), 32, 0, s>>>(total_entries, round, T3);
+    B200_LAUNCH_CHECK();
+    k_aff_down<F><<<grid(mx.n3, 128), 128, 0, s>>>(total_entries, round, 2, T2, P2, T3);
+    B200_LAUNCH_CHECK();
+    k_aff_down<F><<<grid(mx.n2, 128), 128, 0, s>>>(total_entries, round, 1, T1, P1, T2);
     B200_LAUNCH_CHECK();
     return B200_OK;
 }

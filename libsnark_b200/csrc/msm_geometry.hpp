@@ -9,6 +9,7 @@ namespace msm
 {
 
 constexpr int SEG = 64;   // max entries per accumulation task
+constexpr int SEG_PTS = 16; // max survivors per task after affine rounds: few, short tasks balance badly over the SMs
 constexpr int COLLAPSE_TASKS = 4; // floor of Geometry::collapse (see there)
 constexpr int CHUNK = 8;  // buckets per reduce thread
 constexpr int REDUCE_BLOCK = 128; // reduce threads per CTA (all in one window)
@@ -33,7 +34,41 @@ struct Geometry {
     // the SAME B buckets with the matching multiple of the base, and the W-fold reduction becomes one.
     uint32_t bstride, estride;
     uint32_t chunk; // buckets per reduce thread (CHUNK; smaller over tables, see make_table_geometry)
+    // Batched-affine rounds ahead of the XYZZ accumulation (msm_affine.cuh): every bucket is padded to a multiple of
+    // 2^rounds entries by the counting sort, `rounds` pairwise-addition rounds leave ceil(count / 2^rounds) survivors per
+    // bucket at offsets[b] >> rounds, and the tasks of the accumulation are cut over the survivors. 0 = none.
+    uint32_t rounds;
+    uint32_t seg;   // task length: SEG entries, or SEG_PTS survivors when rounds > 0
 };
+
+// Entries of a bucket after padding to a multiple of 2^rounds, and its survivors after the rounds.
+inline
+#if defined(__CUDACC__)
+    __host__ __device__
+#endif
+    uint32_t padded_count(uint32_t count, uint32_t rounds)
+{
+    const uint32_t mask = (1u << rounds) - 1u;
+    return (count + mask) & ~mask;
+}
+
+// How many affine rounds pay: a round over the survivors of the previous one saves ~3.7 of 10 field products per
+// addition but costs a fixed ~0.1 ms of dependent small launches (the inversion tree), and the padding costs up to
+// 2^rounds - 1 dead slots per bucket. Rounds while the average bucket still holds >= 16 entries, at most 3; none for
+// small MSMs, whose accumulation is shorter than the rounds' fixed cost.
+inline uint32_t pick_rounds(uint64_t entries, uint64_t buckets)
+{
+    if (entries < (1ull << 21)) {
+        return 0;
+    }
+    uint32_t r = 0;
+    uint64_t avg = entries / (buckets ? buckets : 1);
+    while (r < 3 && avg >= 16) {
+        ++r;
+        avg >>= 1;
+    }
+    return r;
+}
 
 // Buckets per reduce thread. The reduction is a serial chain of group additions per thread, run at a fraction of
 // a warp per scheduler (ncu: 6 % occupancy). While the reduce threads number well under one wave of the machine,
@@ -88,7 +123,19 @@ inline Geometry make_geometry(uint64_t n, int scalar_bits, int force_c = 0)
     g.collapse = (uint32_t)(2 * avg_tasks + 2 > (uint64_t)COLLAPSE_TASKS ? 2 * avg_tasks + 2 : (uint64_t)COLLAPSE_TASKS);
     g.bstride = g.B;
     g.estride = 0;
+    g.rounds = 0;
+    g.seg = SEG;
     return g;
+}
+
+// Sets the number of affine rounds (and the collapse threshold, which counts tasks over the survivors).
+inline void set_rounds(Geometry &g, uint32_t rounds, uint64_t entries)
+{
+    g.rounds = rounds;
+    g.seg = rounds ? SEG_PTS : SEG;
+    const uint64_t buckets = g.bstride ? (uint64_t)g.W * g.B : g.B;
+    const uint64_t avg_tasks = ((entries / buckets >> rounds) + g.seg - 1) / g.seg;
+    g.collapse = (uint32_t)(2 * avg_tasks + 2 > (uint64_t)COLLAPSE_TASKS ? 2 * avg_tasks + 2 : (uint64_t)COLLAPSE_TASKS);
 }
 
 // Window width for a base set with precomputed tables [2^(c w)] P, w < W: all W n entries land in one set

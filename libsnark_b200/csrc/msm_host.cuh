@@ -8,6 +8,7 @@
 
 #include "host_fold.hpp"
 #include "msm.cuh"
+#include "msm_affine.cuh"
 #include "runtime.hpp"
 
 namespace b200
@@ -17,6 +18,7 @@ namespace msm
 
 struct Workspace {
     rt::DevBuf t, counts, offsets, cursor, task_off, tile_sums, entries, tasks, partial, chunk_out, staging, any_inf, multi;
+    rt::DevBuf aff_p0, aff_t1, aff_p1, aff_t2, aff_p2, aff_t3, aff_a, aff_b; // affine rounds (msm_affine.cuh)
 };
 inline Workspace &workspace() // of the calling thread's execution slot (runtime.hpp)
 {
@@ -28,6 +30,10 @@ inline Workspace &workspace() // of the calling thread's execution slot (runtime
 template<class F>
 int reduce_launch(const Geometry &g, const uint32_t *task_off, const uint32_t *multi_count,
                   const uint32_t *multi_list, XYZZ<F> *partial, XYZZ<F> *block_out, XYZZ<F> *windows_dev);
+
+// Upper levels of an affine round's inversion tree; defined in msm_cold.cuh like reduce_launch.
+template<class F>
+int affine_tree_launch(const uint32_t *total_entries, int round, uint32_t max_entries, F *T1, F *P1, F *T2, F *P2, F *T3);
 
 // Table rows 1..W-1 of a base set (build_table_body); defined in msm_cold.cuh like reduce_launch.
 template<class F> int table_launch(size_t n, int c, int W, Affine<F> *table, const uint8_t *inf, uint32_t *fail);
@@ -132,16 +138,24 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
     // which the Horner fold passes through unchanged.
     const Geometry pub = make_geometry(n, Fr::params::BITS);
     static const int table_chunk = getenv("B200_TABLE_CHUNK") ? atoi(getenv("B200_TABLE_CHUNK")) : 0; // tuning knob
-    const Geometry g = bs.table_c ? make_table_geometry(n, Fr::params::BITS, bs.table_c, bs.n, table_chunk) : pub;
+    Geometry g = bs.table_c ? make_table_geometry(n, Fr::params::BITS, bs.table_c, bs.n, table_chunk) : pub;
     const int reduce_windows = bs.table_c ? 1 : g.W;
+    {
+        // affine rounds ahead of the XYZZ accumulation; B200_AFFINE_ROUNDS = 0..4 overrides the choice (tuning knob)
+        static const int forced = getenv("B200_AFFINE_ROUNDS") ? atoi(getenv("B200_AFFINE_ROUNDS")) : -1;
+        const uint64_t ents = (uint64_t)g.W * n;
+        const uint32_t r = forced >= 0 ? (uint32_t)(forced > 4 ? 4 : forced) : pick_rounds(ents, g.NB);
+        set_rounds(g, r, ents);
+    }
+    const uint32_t R = g.rounds;
     *W_out = pub.W;
     *c_out = pub.c;
     Workspace &ws = workspace();
     cudaStream_t s = rt::stream();
     rt::MsmTiming &tm = rt::msm_timing();
 
-    const size_t max_entries = (size_t)g.W * n;
-    const size_t max_tasks = (size_t)g.NB + max_entries / SEG + 1;
+    const size_t max_entries = (size_t)g.W * n + (size_t)g.NB * ((1u << R) - 1u); // incl. the padding of every bucket
+    const size_t max_tasks = (size_t)g.NB + (max_entries >> R) / g.seg + 1;
     const uint32_t ntiles = grid_for(g.NB, SCAN_TILE);
     if (max_entries >= 0x7fffffffull || max_tasks >= 0xffffffffull) {
         return rt::set_error(B200_ERR_ARG, "MSM of %zu points exceeds the 32-bit entry index", n);
@@ -152,6 +166,14 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
         ws.entries.reserve(max_entries * 4 + 16) || ws.tasks.reserve(max_tasks * sizeof(Task)) ||
         ws.partial.reserve(max_tasks * sizeof(XYZZ<F>)) ||
         ws.chunk_out.reserve(((size_t)reduce_windows * g.opw) * sizeof(XYZZ<F>)) || ws.multi.reserve(((size_t)g.NB + 4) * 4)) {
+        return B200_ERR_CUDA;
+    }
+    const AffLevels amax = aff_levels((uint32_t)max_entries, 1);
+    if (R && (ws.aff_p0.reserve((size_t)amax.pairs * sizeof(F)) || ws.aff_t1.reserve((size_t)amax.n1 * sizeof(F)) ||
+              ws.aff_p1.reserve((size_t)amax.n1 * sizeof(F)) || ws.aff_t2.reserve((size_t)amax.n2 * sizeof(F)) ||
+              ws.aff_p2.reserve((size_t)amax.n2 * sizeof(F)) || ws.aff_t3.reserve((size_t)amax.n3 * sizeof(F)) ||
+              ws.aff_a.reserve((max_entries / 2 + 1) * sizeof(Affine<F>)) ||
+              (R > 1 && ws.aff_b.reserve((max_entries / 4 + 1) * sizeof(Affine<F>))))) {
         return B200_ERR_CUDA;
     }
     const Affine<F> *bases = static_cast<const Affine<F> *>(bs.pts) + first;
@@ -178,20 +200,58 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
     B200_LAUNCH_CHECK();
     k_histogram<<<grid_for(n, 256), 256, 0, s>>>(t, NL, g, counts);
     B200_LAUNCH_CHECK();
-    k_scan_tiles<<<ntiles, SCAN_THREADS, 0, s>>>(counts, g.NB, tile_sums);
+    k_scan_tiles<<<ntiles, SCAN_THREADS, 0, s>>>(counts, g.NB, tile_sums, R);
     B200_LAUNCH_CHECK();
     k_scan_tile_sums<<<1, SCAN_THREADS, 0, s>>>(tile_sums, ntiles);
     B200_LAUNCH_CHECK();
-    k_scan_finish<<<ntiles, SCAN_THREADS, 0, s>>>(counts, g.NB, tile_sums, offsets, cursor, task_off);
+    k_scan_finish<<<ntiles, SCAN_THREADS, 0, s>>>(counts, g.NB, tile_sums, offsets, cursor, task_off, R);
     B200_LAUNCH_CHECK();
+    if (R) { // the padding of every bucket reads as NULL_ENTRY
+        B200_CUDA_CHECK(cudaMemsetAsync(entries, 0xff, max_entries * 4, s));
+    }
     k_scatter<<<grid_for(n, 256), 256, 0, s>>>(t, NL, g, cursor, entries);
     B200_LAUNCH_CHECK();
-    k_build_tasks<<<grid_for(g.NB, 256), 256, 0, s>>>(counts, offsets, task_off, g.NB, tasks, multi_count, multi_list, g.collapse);
+    k_build_tasks<<<grid_for(g.NB, 256), 256, 0, s>>>(counts, offsets, task_off, g.NB, tasks, multi_count, multi_list, g.collapse, R);
     B200_LAUNCH_CHECK();
     B200_CUDA_CHECK(cudaEventRecord(tm.ev[1], s));
     // 5: bucket accumulation (grid sized for the task upper bound; surplus CTAs exit at once)
-    k_accumulate<F><<<grid_for(max_tasks, ACC_THREADS), ACC_THREADS, 0, s>>>(
-        tasks, task_off + g.NB, entries, bases, partial);
+    if (R) {
+        // affine rounds: round r halves every bucket; pairs of round r = (padded entries) >> r
+        const uint32_t *total = offsets + g.NB;
+        Affine<F> *buf[2] = {ws.aff_a.as<Affine<F>>(), ws.aff_b.as<Affine<F>>()};
+        F *P0 = ws.aff_p0.as<F>(), *T1 = ws.aff_t1.as<F>();
+        const Affine<F> *prev = nullptr;
+        for (uint32_t r = 1; r <= R; ++r) {
+            const AffLevels mx = aff_levels((uint32_t)max_entries, (int)r);
+            Affine<F> *out = buf[(r - 1) & 1];
+            const unsigned grid = grid_for(mx.n1, AFF_THREADS);
+            if (r == 1) {
+                const SrcEntries<F> src{entries, bases};
+                k_aff_up0<F, SrcEntries<F>><<<grid, AFF_THREADS, 0, s>>>(total, (int)r, src, P0, T1);
+            } else {
+                const SrcPoints<F> src{prev};
+                k_aff_up0<F, SrcPoints<F>><<<grid, AFF_THREADS, 0, s>>>(total, (int)r, src, P0, T1);
+            }
+            B200_LAUNCH_CHECK();
+            if (int rc = affine_tree_launch<F>(total, (int)r, (uint32_t)max_entries, T1, ws.aff_p1.as<F>(), ws.aff_t2.as<F>(),
+                                               ws.aff_p2.as<F>(), ws.aff_t3.as<F>())) {
+                return rc;
+            }
+            if (r == 1) {
+                const SrcEntries<F> src{entries, bases};
+                k_aff_down0<F, SrcEntries<F>><<<grid, AFF_THREADS, 0, s>>>(total, (int)r, src, P0, T1, out);
+            } else {
+                const SrcPoints<F> src{prev};
+                k_aff_down0<F, SrcPoints<F>><<<grid, AFF_THREADS, 0, s>>>(total, (int)r, src, P0, T1, out);
+            }
+            B200_LAUNCH_CHECK();
+            prev = out;
+        }
+        k_accumulate_pts<F><<<grid_for(max_tasks, ACC_THREADS), ACC_THREADS, 0, s>>>(tasks, task_off + g.NB, prev, partial);
+    } else {
+        k_accumulate<F><<<grid_for(max_tasks, ACC_THREADS), ACC_THREADS, 0, s>>>(
+            tasks, task_off + g.NB, entries, bases, partial);
+    }
     B200_LAUNCH_CHECK();
     B200_CUDA_CHECK(cudaEventRecord(tm.ev[2], s));
     // 6-7: bucket reduction

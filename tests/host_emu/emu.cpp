@@ -10,6 +10,7 @@
 #include "batch_exp.cuh"
 #include "host_fold.hpp"
 #include "msm.cuh"
+#include "msm_affine.cuh"
 
 using namespace b200;
 
@@ -173,11 +174,14 @@ extern "C" int emu_signed_digits(int curve, const void *scalars, size_t n, int c
 // table = true: the precomputed-table variant (b200_bases_precompute): build_table_body fills rows [2^(c w)] P,
 // every window scatters into the one bucket set, the reduction runs over a single window.
 template<class Fr, class F>
-static int msm_emulated(const void *bases_ref, size_t n, const void *scalars, int force_c, void *out, bool table = false)
+static int msm_emulated(const void *bases_ref, size_t n, const void *scalars, int force_c, void *out, bool table = false,
+                        int rounds = 0)
 {
     using namespace msm;
     const int tc = force_c ? force_c : table_window_bits(n, Fr::params::BITS);
     Geometry g = table ? make_table_geometry(n, Fr::params::BITS, tc, n) : make_geometry(n, Fr::params::BITS, force_c);
+    set_rounds(g, (uint32_t)rounds, (uint64_t)g.W * n);
+    const uint32_t R = g.rounds;
     const Limbs<Fr::N> K = make_offset_constant<Fr::N>(g);
     std::vector<Affine<F>> bases(table ? n * g.W : n);
     std::vector<uint8_t> inf(n);
@@ -202,26 +206,74 @@ static int msm_emulated(const void *bases_ref, size_t n, const void *scalars, in
         histogram_body(i, t.data(), Fr::N, g, counts.data());
     }
     uint32_t off = 0, toff = 0;
-    for (uint32_t b = 0; b < g.NB; ++b) {
+    for (uint32_t b = 0; b < g.NB; ++b) { // k_scan_*: counts padded to a multiple of 2^rounds
         offsets[b] = cursor[b] = off;
         task_off[b] = toff;
-        off += counts[b];
-        toff += (counts[b] + SEG - 1) / SEG;
+        const uint32_t pc = padded_count(counts[b], R);
+        off += pc;
+        toff += ((pc >> R) + g.seg - 1) / g.seg;
     }
     offsets[g.NB] = off;
     task_off[g.NB] = toff;
-    std::vector<uint32_t> entries(off + 1), multi_list(g.NB + 1);
+    std::vector<uint32_t> entries(off + 1, NULL_ENTRY), multi_list(g.NB + 1);
     uint32_t multi_count = 0;
     for (size_t i = 0; i < n; ++i) {
         scatter_body(i, t.data(), Fr::N, g, cursor.data(), entries.data());
     }
     std::vector<Task> tasks(toff + 1);
     for (size_t b = 0; b < g.NB; ++b) {
-        build_tasks_body(b, counts.data(), offsets.data(), task_off.data(), tasks.data(), &multi_count, multi_list.data(), g.collapse);
+        build_tasks_body(b, counts.data(), offsets.data(), task_off.data(), tasks.data(), &multi_count, multi_list.data(), g.collapse, R, g.seg);
     }
     std::vector<XYZZ<F>> partial(toff + 1);
-    for (uint32_t k = 0; k < toff; ++k) {
-        accumulate_task<F>(tasks[k], entries.data(), bases.data(), &partial[k]);
+    if (R) {
+        // the affine rounds of msm_affine.cuh, launch by launch, every "thread" in turn
+        std::vector<Affine<F>> buf[2];
+        const Affine<F> *prev = nullptr;
+        for (uint32_t r = 1; r <= R; ++r) {
+            const AffLevels lv = aff_levels(off, (int)r);
+            std::vector<F> P0(lv.pairs + 1), T1(lv.n1 + 1), P1(lv.n1 + 1), T2(lv.n2 + 1), P2(lv.n2 + 1), T3(lv.n3 + 1);
+            std::vector<Affine<F>> &o = buf[(r - 1) & 1];
+            o.assign(lv.pairs + 1, null_point<F>());
+            const SrcEntries<F> se{entries.data(), bases.data()};
+            const SrcPoints<F> sp{prev};
+            for (uint32_t t = 0; t < lv.n1; ++t) {
+                if (r == 1) {
+                    aff_up0_body<F, SrcEntries<F>>(t, lv, se, P0.data(), T1.data());
+                } else {
+                    aff_up0_body<F, SrcPoints<F>>(t, lv, sp, P0.data(), T1.data());
+                }
+            }
+            for (uint32_t t = 0; t < lv.n2; ++t) {
+                aff_up_body<F>(t, lv.n1, lv.n2, T1.data(), P1.data(), T2.data());
+            }
+            for (uint32_t t = 0; t < lv.n3; ++t) {
+                aff_up_body<F>(t, lv.n2, lv.n3, T2.data(), P2.data(), T3.data());
+            }
+            for (uint32_t t = 0; t < lv.n3; ++t) {
+                T3[t] = T3[t].inverse_fast();
+            }
+            for (uint32_t t = 0; t < lv.n3; ++t) {
+                aff_down_body<F>(t, lv.n2, lv.n3, T2.data(), P2.data(), T3.data());
+            }
+            for (uint32_t t = 0; t < lv.n2; ++t) {
+                aff_down_body<F>(t, lv.n1, lv.n2, T1.data(), P1.data(), T2.data());
+            }
+            for (uint32_t t = 0; t < lv.n1; ++t) {
+                if (r == 1) {
+                    aff_down0_body<F, SrcEntries<F>>(t, lv, se, P0.data(), T1.data(), o.data());
+                } else {
+                    aff_down0_body<F, SrcPoints<F>>(t, lv, sp, P0.data(), T1.data(), o.data());
+                }
+            }
+            prev = o.data();
+        }
+        for (uint32_t k = 0; k < toff; ++k) {
+            accumulate_task_pts<F>(tasks[k], prev, &partial[k]);
+        }
+    } else {
+        for (uint32_t k = 0; k < toff; ++k) {
+            accumulate_task<F>(tasks[k], entries.data(), bases.data(), &partial[k]);
+        }
     }
     for (uint32_t k = 0; k < multi_count; ++k) { // k_collapse
         const uint32_t b = multi_list[k];
@@ -310,5 +362,39 @@ extern "C" int emu_msm(int curve, int group, const void *bases, size_t n, const 
     case 9:
     case 10: return msm_emulated<bw6_761_fr, bw6_761_fq>(bases, n, scalars, force_c, out);
     }
+    return -100;
+}
+
+// The pipeline with `rounds` batched-affine rounds ahead of the XYZZ accumulation (msm_affine.cuh), plain or over tables.
+extern "C" int emu_msm_affine(int curve, int group, const void *bases, size_t n, const void *scalars, int force_c, int table,
+                              int rounds, void *out)
+{
+    switch (curve * 4 + group) {
+    case 1: return msm_emulated<alt_bn128_fr, alt_bn128_fq>(bases, n, scalars, force_c, out, table != 0, rounds);
+    case 2: return msm_emulated<alt_bn128_fr, alt_bn128_fq2>(bases, n, scalars, force_c, out, table != 0, rounds);
+    case 5: return msm_emulated<bls12_377_fr, bls12_377_fq>(bases, n, scalars, force_c, out, table != 0, rounds);
+    case 6: return msm_emulated<bls12_377_fr, bls12_377_fq2>(bases, n, scalars, force_c, out, table != 0, rounds);
+    case 9:
+    case 10: return msm_emulated<bw6_761_fr, bw6_761_fq>(bases, n, scalars, force_c, out, table != 0, rounds);
+    }
+    return -100;
+}
+
+// Fp::inverse_fast (binary Euclid) on the host emulation: op 6 of emu_field_op would do, kept separate for clarity.
+template<class F> static int inv_fast(const void *a_, void *o_, size_t n)
+{
+    const F *a = (const F *)a_;
+    F *o = (F *)o_;
+    for (size_t i = 0; i < n; ++i) {
+        o[i] = a[i].inverse_fast();
+    }
+    return 0;
+}
+extern "C" int emu_inverse_fast(int curve, int field, const void *a, void *o, size_t n)
+{
+    FIELD_DISPATCH(inv_fast, a, o, n)
+    if (curve == 0 && field == 2) return inv_fast<alt_bn128_fq2>(a, o, n);
+    if (curve == 1 && field == 2) return inv_fast<bls12_377_fq2>(a, o, n);
+    if (curve == 2 && field == 2) return inv_fast<bw6_761_fq>(a, o, n);
     return -100;
 }

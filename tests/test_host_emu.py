@@ -42,6 +42,8 @@ def emu():
     L.emu_msm_table.argtypes = [i, i, vp, sz, vp, i, vp]
     L.emu_batch_exp.argtypes = [i, i, vp, vp, vp, sz, vp]
     L.emu_geometry.argtypes = [C.c_uint64, i, i, vp]
+    L.emu_msm_affine.argtypes = [i, i, vp, sz, vp, i, i, i, vp]
+    L.emu_inverse_fast.argtypes = [i, i, vp, vp, sz]
     return L
 
 
@@ -210,3 +212,83 @@ def test_geometry_invariants(emu):
                 assert chunk == 8 or threads <= 40000
                 assert chunk == 2 or 2 * threads > 40000       # the next smaller chunk would exceed the budget
                 assert collapse >= 4
+
+
+@pytest.mark.parametrize("curve", list(CURVES))
+def test_emulated_inverse_fast(emu, curve):
+    """Fp::inverse_fast / Fp2::inverse_fast (binary Euclid, the top of the affine rounds' inversion trees) == the
+    reference's invert() on the golden field vectors; zero maps to zero."""
+    g = np.load(os.path.join(GOLD, "fields.npz"))
+    for fname, fid in [("fr", 0), ("fq", 1), ("fq2", 2)]:
+        k = f"{curve}.{fname}"
+        if k + ".a" not in g:
+            continue
+        a = np.ascontiguousarray(g[k + ".a"]).copy()
+        want = np.ascontiguousarray(g[k + ".inv"]).copy()
+        a[0] = 0
+        want[0] = 0
+        out = np.zeros_like(a)
+        assert emu.emu_inverse_fast(CURVES[curve], fid, _p(a), _p(out), a.shape[0]) == 0
+        assert np.array_equal(out, want), k
+
+
+def _emu_msm_affine(emu, curve, gid, bases, scalars, c, table, rounds):
+    bases, scalars = np.ascontiguousarray(bases), np.ascontiguousarray(scalars)
+    out = np.zeros(bases.shape[1], dtype=np.uint64)
+    assert emu.emu_msm_affine(CURVES[curve], gid, _p(bases), scalars.shape[0], _p(scalars), c, table, rounds, _p(out)) == 0
+    return out
+
+
+@pytest.mark.parametrize("curve", list(CURVES))
+def test_emulated_msm_affine_rounds(emu, curve):
+    """The batched-affine rounds of msm_affine.cuh (padding of the counting sort, pair denominators, three-level
+    inversion tree, affine additions, XYZZ accumulation over the survivors) give the reference's group element, for
+    1-3 rounds, plain and over tables, with narrow windows so that buckets hold many entries."""
+    from oracle import port
+    P = port.OraclePort()
+    g = np.load(os.path.join(GOLD, "msm.npz"))
+    npts = {"alt_bn128": 96, "bls12_377": 40, "bw6_761": 16}[curve]
+    for gname, gid in [("g1", 1), ("g2", 2)]:
+        k = f"rand.{curve}.{gname}"
+        bases, sc = g[k + ".bases"][:npts], g[k + ".scalars"][:npts]
+        want = g[k + ".out"] if npts == 96 else P.msm(curve, gid, bases, sc)
+        for rounds in ([1, 2, 3] if gid == 1 else [2]):
+            assert np.array_equal(_emu_msm_affine(emu, curve, gid, bases, sc, 5, 0, rounds), want), (k, rounds)
+    if curve == "alt_bn128":
+        bases, sc = g["rand.alt_bn128.g1.bases"][:48], g["rand.alt_bn128.g1.scalars"][:48]
+        want = P.msm(curve, 1, bases, sc)
+        for rounds in (1, 3):
+            assert np.array_equal(_emu_msm_affine(emu, curve, 1, bases, sc, 13, 1, rounds), want), ("table", rounds)
+
+
+def test_emulated_msm_affine_exceptional_pairs(emu):
+    """Pairs the affine formula cannot add: P + P (repeated bases with equal scalars -> doubling), P + (-P) (a base with
+    scalars s and r - s -> the neutral pair (0, 0)), pads, zero and one scalars, an infinity base, the reference KATs."""
+    from oracle import port
+    P = port.OraclePort()
+    g = np.load(os.path.join(GOLD, "msm.npz"))
+    # all-equal scalars over repeated bases: every bucket holds runs of identical points
+    bases = np.repeat(g["family.bases"], 3, axis=0)[:300]
+    sc = np.repeat(g["rand.alt_bn128.g1.scalars"][:1], 300, axis=0)
+    want = P.msm("alt_bn128", 1, bases, sc)
+    for rounds in (1, 2, 3):
+        assert np.array_equal(_emu_msm_affine(emu, "alt_bn128", 1, bases, sc, 5, 0, rounds), want), rounds
+    # s and -s on the same base, interleaved with ordinary entries, zeros and ones
+    b2 = np.ascontiguousarray(g["rand.alt_bn128.g1.bases"][:64]).copy()
+    s2 = np.ascontiguousarray(g["rand.alt_bn128.g1.scalars"][:64]).copy()
+    neg = P.field_op("alt_bn128", 0, 4, s2[:16], s2[:16])      # op 4 = neg
+    b2[16:32] = b2[:16]
+    s2[16:32] = neg
+    s2[40] = 0
+    r_mod = 21888242871839275222246405745257275088548364400416034343698204186575808495617
+    s2[41] = np.frombuffer(((1 << 256) % r_mod).to_bytes(32, "little"), dtype=np.uint64)   # Montgomery form of 1
+    b2[50] = 0
+    b2[50, 4] = b2[0, 8]    # (0, 1, 0): y = one copied from an affine point's z
+    want = P.msm("alt_bn128", 1, b2, s2)
+    for rounds in (1, 2, 3):
+        for c in (5, 8):
+            assert np.array_equal(_emu_msm_affine(emu, "alt_bn128", 1, b2, s2, c, 0, rounds), want), (rounds, c)
+    for kk in [1, 2, 5, 257]:
+        got = _emu_msm_affine(emu, "alt_bn128", 1, g["family.bases"][:kk], g[f"family.scalars{kk}"], 6, 0, 2)
+        assert np.array_equal(got, g[f"family.out{kk}"]), kk
+    assert np.array_equal(_emu_msm_affine(emu, "alt_bn128", 1, g["edge.bases"], g["edge.scalars"], 9, 0, 3), g["edge.out"])
