@@ -135,6 +135,20 @@ int b200_kc_msm(int curve, const size_t *indices, const void *values, size_t nnz
  *      m not a power of two, m < 2 or log2(m) > Fr::s  ->  B200_ERR_DOMAIN. ----------------- */
 int b200_ntt(int curve, int op, void *data, size_t m, const void *g);
 int b200_ntt_dev(int curve, int op, void *dev_data, size_t m, const void *g);
+/* b200_ntt_dev without any device allocation. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it). Same arguments, result and status codes as b200_ntt_dev for basic_radix2_domain sizes
+ * m = 2^k, k <= B200_NTT_NOALLOC_MAX_LOG; a larger power of two returns B200_ERR_ARG ("exceeds the static scratch"),
+ * other sizes B200_ERR_DOMAIN (the step domains are not served here). The ping-pong buffer, the twiddle table, the
+ * coset table and the domain constants live in one file-scope device array of B200_NTT_NOALLOC_SCRATCH_BYTES that
+ * every GPU which loads the library holds until the process exits; the call performs no cudaMalloc / cudaFree and no
+ * allocating library call (call b200_init once at set-up: it creates the library's streams). All calls share that
+ * array and it keeps the last call's tables (rebuilt only when curve, size, generator or coset direction change):
+ * calls that overlap on the GPU — two host threads in different execution slots, two processes' worth of streams on
+ * one context — race; serialise them. */
+#define B200_NTT_NOALLOC_MAX_LOG 16
+#define B200_NTT_NOALLOC_SCRATCH_BYTES ((((size_t)5 << (B200_NTT_NOALLOC_MAX_LOG - 1)) + 256) * 48)
+int b200_ntt_dev_noalloc(int curve, int op, void *dev_data, size_t m, const void *g);
 /* basic_radix2_domain::divide_by_Z_on_coset (basic_radix2_domain.tcc:117-126) with
  * coset generator Fr::multiplicative_generator. */
 int b200_divide_by_Z_on_coset(int curve, void *data, size_t m);

@@ -43,6 +43,7 @@ EXPORTS = [
     "b200_groth16_shard_begin", "b200_groth16_shard_chain", "b200_groth16_shard_h", "b200_groth16_shard_msm",
     "b200_groth16_assemble", "b200_bases_precompute", "b200_bases_table_rows", "b200_groth16_shard_witness_copy", "b200_batch_exp", "b200_groth16_shard_finish_msm",
     "b200_groth16_witness_upload", "b200_groth16_prove_resident", "b200_bases_table_window_bits",
+    "b200_ntt_dev_noalloc",
 ]
 
 
@@ -97,6 +98,7 @@ def lib():
         L.b200_kc_msm.argtypes = [i, vp, vp, sz, sz, sz, vp, sz, vp, vp, vp]
         L.b200_ntt.argtypes = [i, i, vp, sz, vp]
         L.b200_ntt_dev.argtypes = [i, i, vp, sz, vp]
+        L.b200_ntt_dev_noalloc.argtypes = [i, i, vp, sz, vp]
         L.b200_divide_by_Z_on_coset.argtypes = [i, vp, sz]
         L.b200_witness_map_h.argtypes = [i, vp, vp, vp, sz, vp]
         L.b200_witness_map_h_dev.argtypes = [i, vp, vp, vp, sz, vp]

@@ -1129,3 +1129,157 @@ int b200_gather_dev(int curve, const void *d_src, const uint32_t *d_idx, size_t 
 }
 
 } // extern "C"
+
+// ---- b200_ntt_dev_noalloc: the radix-2 transforms without any device allocation ------------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). Everything b200_ntt_dev keeps in
+// grow-only cudaMalloc buffers — the Stockham ping-pong buffer, the twiddle table, the domain constants and the
+// coset table — lives in ONE file-scope device array of a fixed size instead. Every GPU that loads the library
+// holds these bytes until the process exits. All calls share the array: calls that overlap on the GPU race.
+namespace
+{
+
+constexpr int NOALLOC_MAX_LOG = B200_NTT_NOALLOC_MAX_LOG;  // m <= 2^16 elements per call
+constexpr size_t NOALLOC_MAX_FR = 48;                      // bytes of the widest Fr (bw6_761: 6 x u64)
+constexpr size_t NOALLOC_SMALL = 256 * NOALLOC_MAX_FR;     // consts[8] | g[1] | pows[192], padded
+// tmp[m] | twiddles[m / 2] | coset table[m] | small
+constexpr size_t NOALLOC_SCRATCH_BYTES = ((size_t)5 << (NOALLOC_MAX_LOG - 1)) * NOALLOC_MAX_FR + NOALLOC_SMALL;
+
+static_assert(NOALLOC_SCRATCH_BYTES == B200_NTT_NOALLOC_SCRATCH_BYTES, "header and scratch disagree");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+// What the array holds from earlier calls on one device (the tables are rebuilt only when the key changes).
+struct NoallocState {
+    unsigned char *base = nullptr; // device address of g_noalloc_scratch on this device (cudaGetSymbolAddress)
+    int curve = -1, lgn = 0;
+    bool has_g = false;
+    uint32_t g[NOALLOC_MAX_FR / 4];
+    int coset_which = -1; // CosetTable currently in the coset slot, -1 none
+};
+constexpr int NOALLOC_MAX_DEVICES = 64;
+NoallocState g_noalloc[NOALLOC_MAX_DEVICES];
+
+// g arrives by value (kernel parameter space), so no host-to-device copy is needed for it
+template<class Fr> __global__ void k_noalloc_consts(int lgn, Fr g, Fr *g_slot, Fr *consts, Fr *pows)
+{
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        ntt::gstore(g_slot, g);
+        ntt::domain_consts_body<Fr>(lgn, g_slot, consts, pows, pows + 64, pows + 128);
+    }
+}
+
+template<class Fr> int ntt_dev_noalloc(NoallocState &st, int curve, int op, void *dev_data, size_t m, const void *g)
+{
+    const int lgn = log2_exact(m);
+    if (lgn < 0 || lgn > Fr::params::S) {
+        return rt::set_error(B200_ERR_DOMAIN, "basic_radix2_domain: size %zu is not a power of two in [2, 2^%d]", m,
+                             Fr::params::S);
+    }
+    if (lgn > NOALLOC_MAX_LOG) {
+        return rt::set_error(B200_ERR_ARG,
+                             "b200_ntt_dev_noalloc: m = %zu exceeds the static scratch (at most 2^%d elements; use "
+                             "b200_ntt_dev for larger transforms)",
+                             m, NOALLOC_MAX_LOG);
+    }
+    const bool coset = (op == B200_COSET_FFT || op == B200_ICOSET_FFT);
+    if (op < B200_FFT || op > B200_ICOSET_FFT) {
+        return rt::set_error(B200_ERR_ARG, "unknown NTT op %d", op);
+    }
+    if (coset && !g) {
+        return rt::set_error(B200_ERR_ARG, "coset transform needs a generator");
+    }
+    static_assert(sizeof(Fr) <= NOALLOC_MAX_FR, "scratch is sized for 48-byte scalars");
+    cudaStream_t s = rt::stream();
+    Fr *tmp = reinterpret_cast<Fr *>(st.base);
+    Fr *twiddles = reinterpret_cast<Fr *>(st.base + ((size_t)2 << (NOALLOC_MAX_LOG - 1)) * NOALLOC_MAX_FR);
+    Fr *coset_tbl = reinterpret_cast<Fr *>(st.base + ((size_t)3 << (NOALLOC_MAX_LOG - 1)) * NOALLOC_MAX_FR);
+    Fr *small = reinterpret_cast<Fr *>(st.base + ((size_t)5 << (NOALLOC_MAX_LOG - 1)) * NOALLOC_MAX_FR);
+    Fr *consts = small, *g_slot = small + 8, *pows = small + 16;
+
+    uint32_t gen[Fr::N];
+    if (coset) {
+        memcpy(gen, g, sizeof(gen));
+    } else if (st.curve == curve && st.has_g) {
+        memcpy(gen, st.g, sizeof(gen)); // plain transforms do not care which generator the constants carry
+    } else {
+        for (int i = 0; i < Fr::N; ++i) {
+            gen[i] = Fr::params::generator(i);
+        }
+    }
+    const bool new_domain = st.curve != curve || st.lgn != lgn;
+    const bool new_g = new_domain || !st.has_g || memcmp(gen, st.g, sizeof(gen)) != 0;
+    if (new_g) {
+        st.curve = -1; // stays invalid if a launch below fails
+        Fr gv;
+        memcpy(gv.v, gen, sizeof(gen));
+        k_noalloc_consts<Fr><<<1, 32, 0, s>>>(lgn, gv, g_slot, consts, pows);
+        B200_LAUNCH_CHECK();
+        st.coset_which = -1;
+    }
+    if (new_domain) {
+        const uint64_t half = 1ull << (lgn - 1);
+        ntt::k_pow_table<Fr><<<grid_for(half, 256), 256, 0, s>>>(half, pows, lgn - 1, nullptr, twiddles);
+        B200_LAUNCH_CHECK();
+    }
+    if (new_g) {
+        st.curve = curve;
+        st.lgn = lgn;
+        st.has_g = true;
+        memcpy(st.g, gen, sizeof(gen));
+    }
+    if (coset) {
+        const int which = op == B200_COSET_FFT ? T_GPOW : T_GINV_MINV;
+        if (st.coset_which != which) {
+            st.coset_which = -1;
+            ntt::k_pow_table<Fr><<<grid_for(m, 256), 256, 0, s>>>(m, which == T_GPOW ? pows + 64 : pows + 128, lgn,
+                                                                  which == T_GPOW ? nullptr : consts + 1, coset_tbl);
+            B200_LAUNCH_CHECK();
+            st.coset_which = which;
+        }
+    }
+    // run_transform reads only lgn and the twiddle pointer of a Domain; this one owns nothing
+    Domain<Fr> d;
+    d.lgn = lgn;
+    d.twiddles.p = twiddles;
+    Fr *data = static_cast<Fr *>(dev_data);
+    int rc = B200_OK;
+    switch (op) {
+    case B200_FFT: rc = run_transform<Fr>(d, 0, data, tmp, data, nullptr, nullptr, nullptr); break;
+    case B200_IFFT: rc = run_transform<Fr>(d, 1, data, tmp, data, nullptr, nullptr, consts + 1); break;
+    case B200_COSET_FFT: rc = run_transform<Fr>(d, 0, data, tmp, data, coset_tbl, nullptr, nullptr); break;
+    case B200_ICOSET_FFT: rc = run_transform<Fr>(d, 1, data, tmp, data, nullptr, coset_tbl, nullptr); break;
+    }
+    if (rc) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaStreamSynchronize(s));
+    return B200_OK;
+}
+
+} // namespace
+
+extern "C" int b200_ntt_dev_noalloc(int curve, int op, void *dev_data, size_t m, const void *g)
+{
+    if (!dev_data) {
+        return rt::set_error(B200_ERR_ARG, "null data");
+    }
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    int dev = -1;
+    B200_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) {
+        return rt::set_error(B200_ERR_ARG, "device %d outside [0, %d)", dev, NOALLOC_MAX_DEVICES);
+    }
+    std::lock_guard<std::mutex> lk(g_mu); // also guards run_transform's shared-memory attribute cache
+    NoallocState &st = g_noalloc[dev];
+    if (!st.base) {
+        // In host code g_noalloc_scratch is only a stand-in for the symbol: the address a kernel may use on THIS
+        // device comes from the runtime, once per device, with that device current.
+        void *p = nullptr;
+        B200_CUDA_CHECK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        st.base = static_cast<unsigned char *>(p);
+    }
+    DISPATCH_FR(curve, ntt_dev_noalloc<Fr>(st, curve, op, dev_data, m, g));
+}
