@@ -140,6 +140,7 @@ def lib():
         L.b200_test_field_op.argtypes = [i, i, i, vp, vp, vp, sz]
         L.b200_test_fp_convert.argtypes = [i, i, i, vp, vp, sz]
         L.b200_test_group_op.argtypes = [i, i, i, vp, vp, vp, sz]
+        L.b200_test_signed_digits.argtypes = [i, vp, sz, i, vp, C.POINTER(i)]
         _lib = L
     return _lib
 
@@ -318,12 +319,28 @@ def make_bases(curve, group, n, k0=1):
     return out
 
 
+# the scalar-field moduli (alt_bn128_init.cpp, bls12_377_init.cpp, bw6_761_init.cpp: Fr::modulus)
+FR_MODULUS = {ALT_BN128: 0x30644e72e131a029b85045b68181585d2833e84879b9709143e1f593f0000001,
+              BLS12_377: 0x12ab655e9a2ca55660b44d1e5c37b00159aa76fed00000010a11800000000001,
+              BW6_761: 0x1ae3a4617c510eac63b05c06ca1493b1a22d9f300f5138f1ef3622fba094800170b5d44300000008508c00000000001}
+
+
+def scalars_from_ints(curve, values):
+    """Python integers (standard form) -> Montgomery Fr limbs, the layout every entry point takes."""
+    c = _cid(curve)
+    r, L = FR_MODULUS[c], sizeof_fr(c) // 8
+    out = np.zeros((len(values), L), dtype=np.uint64)
+    for k, v in enumerate(values):
+        m = (int(v) % r) * (1 << (64 * L)) % r
+        for j in range(L):
+            out[k, j] = (m >> (64 * j)) & 0xFFFFFFFFFFFFFFFF
+    return out
+
+
 def random_scalars(curve, n, seed=0):
     """n uniformly random Fr residues (any value < r is a valid Montgomery representative)."""
     c = _cid(curve)
-    r = {ALT_BN128: 0x30644e72e131a029b85045b68181585d2833e84879b9709143e1f593f0000001,
-         BLS12_377: 0x12ab655e9a2ca55660b44d1e5c37b00159aa76fed00000010a11800000000001,
-         BW6_761: 0x1ae3a4617c510eac63b05c06ca1493b1a22d9f300f5138f1ef3622fba094800170b5d44300000008508c00000000001}[c]
+    r = FR_MODULUS[c]
     L = sizeof_fr(c) // 8
     rng = np.random.default_rng(seed)
     a = rng.integers(0, 1 << 64, size=(n, L), dtype=np.uint64)
@@ -743,4 +760,15 @@ def test_group_op(curve, group, op, a, b):
     return out
 
 
-test_field_op.__test__ = test_fp_convert.__test__ = test_group_op.__test__ = False
+def test_signed_digits(curve, scalars, c):
+    """The device's digit extraction (k_prepare + window_digit) for window width c: (n, W) int64."""
+    scalars = _u64(scalars)
+    n = scalars.shape[0]
+    bits = {ALT_BN128: 254, BLS12_377: 253, BW6_761: 377}[_cid(curve)]
+    W = C.c_int(0)
+    out = np.zeros(n * ((bits + c) // c + 1), dtype=np.int64)
+    _check(lib().b200_test_signed_digits(_cid(curve), _p(scalars), n, c, _p(out), C.byref(W)))
+    return out[: n * W.value].reshape(n, W.value)
+
+
+test_field_op.__test__ = test_fp_convert.__test__ = test_group_op.__test__ = test_signed_digits.__test__ = False

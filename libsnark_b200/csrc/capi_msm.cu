@@ -3,6 +3,7 @@
 #include <cstring>
 #include <map>
 #include <mutex>
+#include <shared_mutex>
 #include <vector>
 
 #include "curve_params.cuh"
@@ -50,6 +51,10 @@ const CurveVt *vt(int curve)
 size_t group_bytes(const CurveVt *v, int group) { return 3 * v->fq_bytes * ((group == B200_G2 && v->g2_is_fq2) ? 2 : 1); }
 
 std::mutex g_mu; // guards g_sets
+// Lifetime of the sets' device arrays: every MSM over a resident set holds this shared for the whole (synchronous)
+// call, b200_bases_free and b200_bases_precompute — which free or replace the arrays — hold it exclusively.
+// Lock order everywhere: g_life, then the slot's mutex, then g_mu.
+std::shared_mutex g_life;
 std::map<uint64_t, rt::BaseSet> g_sets;
 uint64_t g_next_handle = 1;
 
@@ -230,6 +235,7 @@ int b200_bases_upload(int curve, int group, const void *bases, size_t base_strid
     if (!rt::ensure_init()) {
         return B200_ERR_CUDA;
     }
+    std::lock_guard<std::mutex> slot_lk(g_slot[rt::slot()].mu); // the upload stages through the slot's workspace
     std::lock_guard<std::mutex> lk(g_mu);
     rt::BaseSet bs;
     const int rc = v->grp(group).bases_upload(curve, group, bases, base_stride, n, &bs);
@@ -243,6 +249,7 @@ int b200_bases_upload(int curve, int group, const void *bases, size_t base_strid
 
 int b200_bases_free(b200_bases_t handle)
 {
+    std::unique_lock<std::shared_mutex> life(g_life);
     std::lock_guard<std::mutex> lk(g_mu);
     auto it = g_sets.find(handle);
     if (it == g_sets.end()) {
@@ -256,6 +263,8 @@ int b200_bases_free(b200_bases_t handle)
 
 int b200_bases_precompute(b200_bases_t handle)
 {
+    std::unique_lock<std::shared_mutex> life(g_life); // the set's point array is replaced: no MSM may be reading it
+    std::lock_guard<std::mutex> slot_lk(g_slot[rt::slot()].mu);
     std::lock_guard<std::mutex> lk(g_mu);
     auto it = g_sets.find(handle);
     if (it == g_sets.end()) {
@@ -289,6 +298,7 @@ size_t b200_bases_size(b200_bases_t handle)
 int b200_msm_resident(b200_bases_t handle, size_t first, size_t n, const void *scalars, int scalars_on_device,
                       void *out)
 {
+    std::shared_lock<std::shared_mutex> life(g_life);
     rt::BaseSet bs;
     if (!find_set(handle, &bs)) {
         return B200_ERR_HANDLE;
@@ -327,6 +337,7 @@ size_t b200_msm_window_bytes(int curve, int group)
 int b200_msm_resident_windows(b200_bases_t handle, size_t first, size_t n, const void *scalars,
                               int scalars_on_device, void *out_windows)
 {
+    std::shared_lock<std::shared_mutex> life(g_life);
     rt::BaseSet bs;
     if (!find_set(handle, &bs)) {
         return B200_ERR_HANDLE;
@@ -341,6 +352,7 @@ int b200_msm_resident_windows(b200_bases_t handle, size_t first, size_t n, const
 int b200_msm_resident_windows_dev(b200_bases_t handle, size_t first, size_t n, const void *scalars,
                                   int scalars_on_device, void *dev_out_windows)
 {
+    std::shared_lock<std::shared_mutex> life(g_life);
     rt::BaseSet bs;
     if (!find_set(handle, &bs)) {
         return B200_ERR_HANDLE;

@@ -533,6 +533,51 @@ int prove_impl(const ProvingKey &pk, const void *primary_input, const void *auxi
 
 } // namespace
 
+// Releases the device / pinned buffers a ProvingKey owns (the base sets and the R1CS belong to the caller).
+static void release_key_buffers(ProvingKey &pk)
+{
+    if (pk.d_w) {
+        b200_dev_free(pk.d_w);
+    }
+    if (pk.d_h) {
+        b200_dev_free(pk.d_h);
+    }
+    if (pk.d_g) {
+        b200_dev_free(pk.d_g);
+    }
+    if (pk.d_B_idx) {
+        b200_dev_free(pk.d_B_idx);
+    }
+    if (pk.h_w) {
+        cudaFreeHost(pk.h_w);
+    }
+    pk.d_w = pk.d_h = pk.d_g = pk.d_B_idx = pk.h_w = nullptr;
+}
+
+// The key's buffers, all or nothing: a failure part-way (usually out of memory) releases what was allocated.
+static int alloc_key_buffers(ProvingKey &pk, size_t fr, const uint32_t *B_indices, size_t nB_idx)
+{
+    int rc = B200_OK;
+    if ((rc = b200_dev_alloc((pk.nv + 1) * fr, &pk.d_w)) || (rc = b200_dev_alloc((pk.m + 1) * fr, &pk.d_h))) {
+        release_key_buffers(pk);
+        return rc;
+    }
+    if (B_indices && nB_idx) {
+        if ((rc = b200_dev_alloc(nB_idx * 4, &pk.d_B_idx)) || (rc = b200_memcpy_h2d(pk.d_B_idx, B_indices, nB_idx * 4)) ||
+            (rc = b200_dev_alloc(nB_idx * fr, &pk.d_g))) {
+            release_key_buffers(pk);
+            return rc;
+        }
+    }
+    const cudaError_t e = cudaHostAlloc(&pk.h_w, (pk.nv + 1) * fr, cudaHostAllocDefault);
+    if (e != cudaSuccess) {
+        pk.h_w = nullptr;
+        release_key_buffers(pk);
+        return rt::set_error(B200_ERR_CUDA, "cudaHostAlloc(%zu) failed: %s", (pk.nv + 1) * fr, cudaGetErrorString(e));
+    }
+    return B200_OK;
+}
+
 extern "C" {
 
 int b200_groth16_pk_create(int curve, const void *alpha_g1, const void *beta_g1, const void *beta_g2,
@@ -589,17 +634,9 @@ int b200_groth16_pk_create(int curve, const void *alpha_g1, const void *beta_g1,
     } else if (nB != nv + 1) {
         return rt::set_error(B200_ERR_ARG, "a B query shorter than num_variables + 1 needs its index list");
     }
-    int rc = B200_OK;
-    if ((rc = b200_dev_alloc((nv + 1) * fr, &pk.d_w)) || (rc = b200_dev_alloc((m + 1) * fr, &pk.d_h))) {
+    if (const int rc = alloc_key_buffers(pk, fr, dense ? nullptr : B_indices, nB)) {
         return rc;
     }
-    if (!dense) {
-        if ((rc = b200_dev_alloc(nB * 4, &pk.d_B_idx)) || (rc = b200_memcpy_h2d(pk.d_B_idx, B_indices, nB * 4)) ||
-            (rc = b200_dev_alloc(nB * fr, &pk.d_g))) {
-            return rc;
-        }
-    }
-    B200_CUDA_CHECK(cudaHostAlloc(&pk.h_w, (nv + 1) * fr, cudaHostAllocDefault));
     std::lock_guard<std::mutex> lk(g_mu);
     *handle = g_next++;
     g_keys[*handle] = pk;
@@ -613,16 +650,7 @@ int b200_groth16_pk_free(b200_groth16_pk_t handle)
     if (it == g_keys.end()) {
         return rt::set_error(B200_ERR_HANDLE, "unknown proving-key handle %llu", (unsigned long long)handle);
     }
-    ProvingKey &pk = it->second;
-    b200_dev_free(pk.d_w);
-    b200_dev_free(pk.d_h);
-    if (pk.d_g) {
-        b200_dev_free(pk.d_g);
-    }
-    if (pk.d_B_idx) {
-        b200_dev_free(pk.d_B_idx);
-    }
-    cudaFreeHost(pk.h_w);
+    release_key_buffers(it->second);
     g_keys.erase(it);
     return B200_OK;
 }
@@ -772,17 +800,9 @@ int b200_groth16_pk_create_shard(int curve, const void *alpha_g1, const void *be
         }
     }
     int rc = B200_OK;
-    if ((rc = b200_dev_alloc((nv + 1) * fr, &pk.d_w)) || (rc = b200_dev_alloc((m + 1) * fr, &pk.d_h))) {
+    if ((rc = alloc_key_buffers(pk, fr, B_indices_shard, pk.cnt[1]))) {
         return rc;
     }
-    if (B_indices_shard && pk.cnt[1]) {
-        if ((rc = b200_dev_alloc(pk.cnt[1] * 4, &pk.d_B_idx)) ||
-            (rc = b200_memcpy_h2d(pk.d_B_idx, B_indices_shard, pk.cnt[1] * 4)) ||
-            (rc = b200_dev_alloc(pk.cnt[1] * fr, &pk.d_g))) {
-            return rc;
-        }
-    }
-    B200_CUDA_CHECK(cudaHostAlloc(&pk.h_w, (nv + 1) * fr, cudaHostAllocDefault));
     std::lock_guard<std::mutex> lk(g_mu);
     *handle = g_next++;
     g_keys[*handle] = pk;

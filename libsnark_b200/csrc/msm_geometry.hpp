@@ -2,6 +2,7 @@
 // kernels' launch code and the C-ABI's b200_msm_num_windows).
 #pragma once
 #include <cstdint>
+#include <cstdlib>
 
 namespace b200
 {
@@ -96,6 +97,30 @@ inline void set_chunk(Geometry &g, uint32_t chunk)
     g.cpw = g.B / g.chunk;
     g.rb = g.cpw < (uint32_t)REDUCE_BLOCK ? g.cpw : (uint32_t)REDUCE_BLOCK;
     g.opw = g.cpw / g.rb;
+}
+
+constexpr int REDUCE_ROW = 256; // = msm::RROW (msm.cuh): items per reduce CTA
+// Buckets per level-1 thread (a power of two): 1 while that leaves the machine short of CTAs (the reduction is then a
+// pure latency chain and every serial addition counts), more once the rows outnumber what the SMs hold at once (the
+// per-bucket work falls from ~7 to ~3 additions); at least what keeps a window within REDUCE_ROW rows. B200_REDUCE_CPT overrides.
+inline uint32_t pick_lg_cpt(uint64_t windows, uint64_t B)
+{
+    static const int forced = getenv("B200_REDUCE_CPT") ? atoi(getenv("B200_REDUCE_CPT")) : -1;
+    uint32_t lg = 0;
+    if (forced >= 0) {
+        lg = (uint32_t)forced;
+    } else {
+        while (lg < 3 && (windows * B >> lg) / REDUCE_ROW > 2 * 148 * 2) {
+            ++lg;
+        }
+    }
+    while ((B >> lg) / REDUCE_ROW > REDUCE_ROW) {
+        ++lg;
+    }
+    while (lg > 0 && (1ull << lg) > B) {
+        --lg;
+    }
+    return lg;
 }
 
 // Window width: minimise  W(c) * (10 n + 100 * 2^(c-1))  field mults (10 per mixed add,

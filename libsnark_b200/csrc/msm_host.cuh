@@ -56,15 +56,27 @@ int bases_upload(int curve, int group, const void *host, size_t stride, size_t n
             return B200_ERR_CUDA;
         }
         B200_CUDA_CHECK(cudaMalloc(&pts, n * sizeof(Affine<F>)));
-        B200_CUDA_CHECK(cudaMalloc((void **)&inf, n));
-        B200_CUDA_CHECK(cudaMemcpyAsync(ws.staging.p, host, bytes, cudaMemcpyHostToDevice, s));
-        B200_CUDA_CHECK(cudaMemsetAsync(ws.any_inf.p, 0, 4, s));
-        k_convert_bases<F><<<grid_for(n, 256), 256, 0, s>>>(
-            ws.staging.as<uint8_t>(), stride, n, static_cast<Affine<F> *>(pts), inf, ws.any_inf.as<uint32_t>());
-        B200_LAUNCH_CHECK();
         uint32_t any = 0;
-        B200_CUDA_CHECK(cudaMemcpyAsync(&any, ws.any_inf.p, 4, cudaMemcpyDeviceToHost, s));
-        B200_CUDA_CHECK(cudaStreamSynchronize(s));
+        // every failure after the first allocation releases what was allocated (such failures are usually
+        // out-of-memory, where a leak of the partial set makes things worse)
+        const auto convert = [&]() -> int {
+            B200_CUDA_CHECK(cudaMalloc((void **)&inf, n));
+            B200_CUDA_CHECK(cudaMemcpyAsync(ws.staging.p, host, bytes, cudaMemcpyHostToDevice, s));
+            B200_CUDA_CHECK(cudaMemsetAsync(ws.any_inf.p, 0, 4, s));
+            k_convert_bases<F><<<grid_for(n, 256), 256, 0, s>>>(
+                ws.staging.as<uint8_t>(), stride, n, static_cast<Affine<F> *>(pts), inf, ws.any_inf.as<uint32_t>());
+            B200_LAUNCH_CHECK();
+            B200_CUDA_CHECK(cudaMemcpyAsync(&any, ws.any_inf.p, 4, cudaMemcpyDeviceToHost, s));
+            B200_CUDA_CHECK(cudaStreamSynchronize(s));
+            return B200_OK;
+        };
+        if (const int rc = convert()) {
+            cudaFree(pts);
+            if (inf) {
+                cudaFree(inf);
+            }
+            return rc;
+        }
         if (!any) {
             cudaFree(inf);
             inf = nullptr;
@@ -165,7 +177,8 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
         ws.task_off.reserve(((size_t)g.NB + 1) * 4) || ws.tile_sums.reserve((size_t)ntiles * 8 + 8) ||
         ws.entries.reserve(max_entries * 4 + 16) || ws.tasks.reserve(max_tasks * sizeof(Task)) ||
         ws.partial.reserve(max_tasks * sizeof(XYZZ<F>)) ||
-        ws.chunk_out.reserve(((size_t)reduce_windows * g.opw) * sizeof(XYZZ<F>)) || ws.multi.reserve(((size_t)g.NB + 4) * 4)) {
+        ws.chunk_out.reserve(((size_t)reduce_windows * g.opw + 2 * (size_t)reduce_windows * (g.B / RROW + 1)) * sizeof(XYZZ<F>)) ||
+        ws.multi.reserve(((size_t)g.NB + 4) * 4)) {
         return B200_ERR_CUDA;
     }
     const AffLevels amax = aff_levels((uint32_t)max_entries, 1);

@@ -1,6 +1,7 @@
 // runtime.cu — device binding, stream, error string, workspace buffers, device-memory C-ABI.
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "runtime.hpp"
@@ -37,6 +38,11 @@ static int do_init(int device)
     if (g_device == device && g_stream) {
         return B200_OK;
     }
+    if (g_stream) {
+        // one process per GPU: the streams, events and every workspace live on the device bound first
+        return set_error(B200_ERR_ARG, "b200_init(%d): this process is already bound to device %d (one process per GPU)",
+                         device, g_device);
+    }
     int count = 0;
     cudaError_t e = cudaGetDeviceCount(&count);
     if (e != cudaSuccess || count == 0) {
@@ -64,7 +70,19 @@ static int do_init(int device)
     return B200_OK;
 }
 
-bool ensure_init() { return (g_stream && g_device >= 0) || do_init(0) == B200_OK; }
+// Lazy binding (a compute entry point called before b200_init): the CUDA current device of the calling thread,
+// which is 0 unless the caller selected another one.
+bool ensure_init()
+{
+    if (g_stream && g_device >= 0) {
+        return true;
+    }
+    int cur = 0;
+    if (cudaGetDevice(&cur) != cudaSuccess) {
+        cur = 0;
+    }
+    return do_init(cur) == B200_OK;
+}
 cudaStream_t stream() { return g_streams[g_slot]; }
 int slot() { return g_slot; }
 int bind_thread(int slot)

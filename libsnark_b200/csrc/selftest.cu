@@ -120,6 +120,46 @@ template<class F> int group_op(int op, const void *a, const void *b, void *o, si
     });
 }
 
+// The digits the MSM's sort sees: k_prepare (scalar -> t = s + K) on the device, then window_digit for every window,
+// for a forced window width c (field_get_signed_digit, field_utils.tcc:82-115, is what they must equal).
+static __global__ void k_dump_digits(const uint32_t *t, int NL, msm::Geometry g, int64_t *out)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < g.n) {
+        for (int w = 0; w < g.W; ++w) {
+            out[i * g.W + w] = msm::window_digit(t + i * NL, NL, g, w);
+        }
+    }
+}
+
+rt::DevBuf g_dt, g_dd;
+
+template<class Fr> int signed_digits(const void *scalars, size_t n, int c, int64_t *out, int *W_out)
+{
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    if (c < 2 || c > 24 || n == 0) {
+        return rt::set_error(B200_ERR_ARG, "window width %d outside [2, 24] or no scalars", c);
+    }
+    const msm::Geometry g = msm::make_geometry(n, Fr::params::BITS, c);
+    const size_t bytes = n * sizeof(Fr);
+    if (g_a.reserve(bytes) || g_dt.reserve(bytes + 16) || g_dd.reserve(n * g.W * sizeof(int64_t))) {
+        return B200_ERR_CUDA;
+    }
+    cudaStream_t s = rt::stream();
+    B200_CUDA_CHECK(cudaMemcpyAsync(g_a.p, scalars, bytes, cudaMemcpyHostToDevice, s));
+    msm::k_prepare<Fr><<<(unsigned)((n + 63) / 64), 64, 0, s>>>(g_a.as<Fr>(), g_dt.as<uint32_t>(), n,
+                                                                msm::make_offset_constant<Fr::N>(g), nullptr);
+    B200_LAUNCH_CHECK();
+    k_dump_digits<<<(unsigned)((n + 63) / 64), 64, 0, s>>>(g_dt.as<uint32_t>(), Fr::N, g, g_dd.as<int64_t>());
+    B200_LAUNCH_CHECK();
+    B200_CUDA_CHECK(cudaMemcpyAsync(out, g_dd.p, n * g.W * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+    B200_CUDA_CHECK(cudaStreamSynchronize(s));
+    *W_out = g.W;
+    return B200_OK;
+}
+
 } // namespace
 
 extern "C" {
@@ -168,5 +208,18 @@ __attribute__((visibility("default"))) int b200_test_group_op(int curve, int gro
     case 10: return group_op<bw6_761_fq>(op, a, b, o, n);
     }
     return rt::set_error(B200_ERR_ARG, "bad curve/group");
+}
+
+// out: n * W signed digits (row-major, W = ceil((bits + 1) / c) returned in *W_out) as the device's digit extraction
+// produces them for window width c.
+__attribute__((visibility("default"))) int b200_test_signed_digits(int curve, const void *scalars, size_t n, int c,
+                                                                   int64_t *out, int *W_out)
+{
+    switch (curve) {
+    case 0: return signed_digits<alt_bn128_fr>(scalars, n, c, out, W_out);
+    case 1: return signed_digits<bls12_377_fr>(scalars, n, c, out, W_out);
+    case 2: return signed_digits<bw6_761_fr>(scalars, n, c, out, W_out);
+    }
+    return rt::set_error(B200_ERR_ARG, "bad curve");
 }
 }

@@ -22,9 +22,14 @@
 // libfqfft::DomainSizeException for a size the basic radix-2 domain does not have).
 //
 // Proving-key residency: the reference passes host iterators on every call and gives no lifetime
-// signal, so base vectors are cached on the device keyed by (host pointer, stride, count, a
-// fingerprint of the first and last point). libsnark_b200::release_cached_bases() drops the cache
-// (call it before freeing or mutating a proving key).
+// signal, so base vectors of 2^12 points or more are cached on the device keyed by (host pointer,
+// stride, count, curve, group, a content fingerprint). The fingerprint hashes 256 points spread evenly
+// over the vector (every point with B200_OVERLAY_FINGERPRINT=full or set_cache_fingerprint_full(true)),
+// so a different key of the same shape at a reused address is uploaded afresh instead of being served
+// stale; the constraint-system and index caches carry content fingerprints the same way. The cache is
+// bounded (B200_OVERLAY_CACHE_BYTES of host-side vector bytes, default 16 GiB, least recently used
+// evicted first). Smaller vectors (verifier accumulations, generator temporaries) go through the
+// uncached b200_msm. libsnark_b200::release_cached_bases() drops the cache explicitly.
 #ifndef LIBSNARK_B200_OVERLAY_HPP_
 #define LIBSNARK_B200_OVERLAY_HPP_
 
@@ -85,6 +90,40 @@ inline void check(int rc, const char *what)
     throw std::runtime_error(msg);
 }
 
+// ---- content fingerprints of the cached host data ---------------------------------------------------
+// 64-bit multiply-xorshift over 8-byte words (all hashed types are arrays of 64-bit limbs / size_t).
+inline unsigned long long hash_words(unsigned long long h, const void *p, size_t bytes)
+{
+    const unsigned char *b = static_cast<const unsigned char *>(p);
+    size_t i = 0;
+    for (; i + 8 <= bytes; i += 8) {
+        unsigned long long w;
+        memcpy(&w, b + i, 8);
+        h = (h ^ w) * 0x9E3779B97F4A7C15ull;
+        h ^= h >> 29;
+    }
+    for (; i < bytes; ++i) {
+        h = (h ^ b[i]) * 1099511628211ull;
+    }
+    return h;
+}
+inline bool &fingerprint_full_flag()
+{
+    static bool full = [] {
+        const char *e = getenv("B200_OVERLAY_FINGERPRINT");
+        return e != nullptr && strcmp(e, "full") == 0;
+    }();
+    return full;
+}
+// true: every cached vector / constraint system is hashed in full on every lookup (hundreds of MB per proof at
+// 2^20 — a few ms on 16 cores' worth of memory bandwidth, single-threaded tens of ms); false: evenly spread samples.
+inline void set_cache_fingerprint_full(bool full) { fingerprint_full_flag() = full; }
+constexpr size_t FINGERPRINT_SAMPLES = 256;
+constexpr size_t CACHE_MIN_POINTS = size_t(1) << 12; // smaller base vectors are one-off: not cached
+
+struct pk_cache;
+inline void pk_cache_clear();
+
 struct bases_cache {
     typedef std::tuple<const void *, size_t, size_t, int, int, unsigned long long> key_t;
     // A set that is seen a second time is a proving-key query, not a one-off vector: it then gets its window tables
@@ -92,30 +131,68 @@ struct bases_cache {
     struct entry {
         b200_bases_t handle;
         bool tables_tried;
+        size_t bytes;             // host-side size of the vector (the budget's unit; tables multiply the device side)
+        unsigned long long used;  // tick of the last lookup
     };
     std::map<key_t, entry> sets;
+    unsigned long long tick = 0, pin = 0; // entries used after `pin` belong to the call in progress: never evicted
+    size_t total_bytes = 0;
+    void begin_group() { pin = tick; }    // call before the lookups of one operator call
     static bases_cache &get()
     {
         static bases_cache c;
         return c;
     }
+    static size_t budget()
+    {
+        static const size_t b = getenv("B200_OVERLAY_CACHE_BYTES") ? (size_t)strtoull(getenv("B200_OVERLAY_CACHE_BYTES"), nullptr, 10)
+                                                                     : (size_t(16) << 30);
+        return b;
+    }
     static unsigned long long fingerprint(const void *p, size_t stride, size_t n, size_t point_bytes)
     {
-        unsigned long long h = 1469598103934665603ull; // FNV-1a over the first and the last point
+        unsigned long long h = 1469598103934665603ull ^ n;
         const unsigned char *b = static_cast<const unsigned char *>(p);
-        const size_t offs[2] = {0, n ? (n - 1) * stride : 0};
-        for (size_t k = 0; k < 2 && n; ++k) {
-            for (size_t i = 0; i < point_bytes; ++i) {
-                h = (h ^ b[offs[k] + i]) * 1099511628211ull;
+        if (n <= FINGERPRINT_SAMPLES || fingerprint_full_flag()) {
+            for (size_t i = 0; i < n; ++i) {
+                h = hash_words(h, b + i * stride, point_bytes);
             }
+            return h;
+        }
+        for (size_t k = 0; k < FINGERPRINT_SAMPLES; ++k) { // first, last and 254 evenly spread points
+            const size_t i = (size_t)((unsigned __int128)k * (n - 1) / (FINGERPRINT_SAMPLES - 1));
+            h = hash_words(h, b + i * stride, point_bytes);
         }
         return h;
+    }
+    void evict_to(size_t limit)
+    {
+        bool any = false;
+        while (total_bytes > limit) {
+            auto lru = sets.end();
+            for (auto it = sets.begin(); it != sets.end(); ++it) {
+                if (it->second.used <= pin && (lru == sets.end() || it->second.used < lru->second.used)) {
+                    lru = it;
+                }
+            }
+            if (lru == sets.end()) {
+                break; // everything left is in use by this call: over budget until it ends
+            }
+            if (!any) {
+                pk_cache_clear(); // prover keys hold base handles: drop them before any handle dies
+                any = true;
+            }
+            b200_bases_free(lru->second.handle);
+            total_bytes -= lru->second.bytes;
+            sets.erase(lru);
+        }
     }
     b200_bases_t lookup(int curve, int group, const void *p, size_t stride, size_t n, size_t point_bytes)
     {
         const key_t key(p, stride, n, curve, group, fingerprint(p, stride, n, point_bytes));
         auto it = sets.find(key);
         if (it != sets.end()) {
+            it->second.used = ++tick;
             if (!it->second.tables_tried) {
                 it->second.tables_tried = true;
                 static const bool no_tables = getenv("B200_OVERLAY_NO_TABLES") != nullptr;
@@ -125,9 +202,24 @@ struct bases_cache {
             }
             return it->second.handle;
         }
+        // same address and shape, other contents: the old copy is stale for good
+        for (auto st = sets.begin(); st != sets.end();) {
+            const key_t &k = st->first;
+            if (std::get<0>(k) == p && std::get<1>(k) == stride && std::get<3>(k) == curve && std::get<4>(k) == group) {
+                pk_cache_clear();
+                b200_bases_free(st->second.handle);
+                total_bytes -= st->second.bytes;
+                st = sets.erase(st);
+            } else {
+                ++st;
+            }
+        }
+        const size_t bytes = n * point_bytes;
+        evict_to(budget() > bytes ? budget() - bytes : 0);
         b200_bases_t h = 0;
         check(b200_bases_upload(curve, group, p, stride, n, &h), "b200_bases_upload");
-        sets[key] = entry{h, false};
+        sets[key] = entry{h, false, bytes, ++tick};
+        total_bytes += bytes;
         return h;
     }
     void clear()
@@ -136,11 +228,14 @@ struct bases_cache {
             b200_bases_free(kv.second.handle);
         }
         sets.clear();
+        total_bytes = 0;
     }
 };
 // b200_groth16_pk_t per (A, B.g2, B.g1, H, L, R1CS) handle tuple (r1cs_gg_ppzksnark_prover_fused)
 struct pk_cache {
-    typedef std::tuple<b200_bases_t, b200_bases_t, b200_bases_t, b200_bases_t, b200_bases_t, unsigned long long> key_t;
+    // the last field: fingerprint of the five single points and of B_query.indices (everything pk_create copies)
+    typedef std::tuple<b200_bases_t, b200_bases_t, b200_bases_t, b200_bases_t, b200_bases_t, unsigned long long,
+                       unsigned long long> key_t;
     std::map<key_t, b200_groth16_pk_t> keys;
     static pk_cache &get()
     {
@@ -155,6 +250,7 @@ struct pk_cache {
         keys.clear();
     }
 };
+inline void pk_cache_clear() { pk_cache::get().clear(); }
 inline void release_cached_bases()
 {
     pk_cache::get().clear(); // the keys refer to the base handles freed next
@@ -218,6 +314,11 @@ GroupT msm_contiguous(const GroupT *bases, size_t n, const FieldT *scalars)
         return out;
     }
     typedef curve_of<GroupT> tr;
+    if (n < CACHE_MIN_POINTS) { // a one-off vector (verifier accumulation, generator temporary): nothing kept on the device
+        check(b200_msm(tr::curve, tr::group, bases, sizeof(GroupT), n, scalars, &out), "b200_msm");
+        return out;
+    }
+    bases_cache::get().begin_group();
     const b200_bases_t h = bases_cache::get().lookup(tr::curve, tr::group, bases, sizeof(GroupT), n, sizeof(GroupT));
     check(b200_msm_resident(h, 0, n, scalars, 0, &out), "b200_msm_resident");
     return out;
@@ -268,6 +369,7 @@ libsnark::knowledge_commitment<T1, T2> kc_msm(
     const size_t n = vec.values.size();
     const size_t off2 = reinterpret_cast<const unsigned char *>(&vec.values[0].h) - vals;
     bases_cache &c = bases_cache::get();
+    c.begin_group();
     const b200_bases_t hg = c.lookup(curve_of<T1>::curve, curve_of<T1>::group, vals, sizeof(KC), n, sizeof(T1));
     const b200_bases_t hh = c.lookup(curve_of<T2>::curve, curve_of<T2>::group, vals + off2, sizeof(KC), n, sizeof(T2));
     check(b200_msm_resident(hg, first, cnt, gathered.data(), 0, &out.g), "b200_msm_resident (kc.g)");
@@ -345,6 +447,7 @@ struct r1cs_cache {
     struct entry {
         b200_r1cs_t handle = 0;
         size_t nc = 0, nv = 0;
+        unsigned long long fp = 0;
     };
     std::map<const void *, entry> sets;
     static r1cs_cache &get()
@@ -352,11 +455,41 @@ struct r1cs_cache {
         static r1cs_cache c;
         return c;
     }
+    // num_inputs and the terms (index, coefficient) of up to FINGERPRINT_SAMPLES evenly spread constraints — of all
+    // constraints in full mode
+    template<typename FieldT> static unsigned long long fingerprint(const libsnark::r1cs_constraint_system<FieldT> &cs)
+    {
+        const size_t nc = cs.num_constraints();
+        unsigned long long h = 1469598103934665603ull ^ cs.num_inputs();
+        const bool all = nc <= FINGERPRINT_SAMPLES || fingerprint_full_flag();
+        const size_t samples = all ? nc : FINGERPRINT_SAMPLES;
+        for (size_t k = 0; k < samples; ++k) {
+            const size_t i = all ? k : (size_t)((unsigned __int128)k * (nc - 1) / (FINGERPRINT_SAMPLES - 1));
+            const libsnark::linear_combination<FieldT> *lcs[3] = {&cs.constraints[i].a, &cs.constraints[i].b, &cs.constraints[i].c};
+            for (const auto *lc : lcs) {
+                const unsigned long long cnt = lc->terms.size();
+                h = hash_words(h, &cnt, 8);
+                for (const auto &t : lc->terms) {
+                    const unsigned long long idx = t.index;
+                    h = hash_words(h, &idx, 8);
+                    h = hash_words(h, &t.coeff, sizeof(FieldT));
+                }
+            }
+        }
+        return h;
+    }
     template<typename FieldT> b200_r1cs_t lookup(const libsnark::r1cs_constraint_system<FieldT> &cs)
     {
+        const unsigned long long fp = fingerprint(cs);
         auto it = sets.find(&cs);
-        if (it != sets.end() && it->second.nc == cs.num_constraints() && it->second.nv == cs.num_variables()) {
+        if (it != sets.end() && it->second.nc == cs.num_constraints() && it->second.nv == cs.num_variables() &&
+            it->second.fp == fp) {
             return it->second.handle;
+        }
+        if (it != sets.end()) { // same address, other contents
+            pk_cache::get().clear();
+            b200_r1cs_free(it->second.handle);
+            sets.erase(it);
         }
         const size_t nc = cs.num_constraints();
         std::vector<uint32_t> row_ptr(3 * nc + 1, 0);
@@ -383,6 +516,7 @@ struct r1cs_cache {
         entry en;
         en.nc = nc;
         en.nv = cs.num_variables();
+        en.fp = fp;
         check(b200_r1cs_upload(curve_of<FieldT>::curve, nc, cs.num_inputs(), cs.num_variables(), row_ptr.data(),
                                col.data(), val.data(), &en.handle),
               "b200_r1cs_upload");
@@ -409,6 +543,7 @@ struct index_cache {
         void *d_idx = nullptr;
         bool dense = true;
         size_t n = 0;
+        unsigned long long fp = 0;
     };
     std::map<const void *, entry> sets;
     static index_cache &get()
@@ -418,12 +553,22 @@ struct index_cache {
     }
     const entry &lookup(const std::vector<size_t> &indices)
     {
+        // the whole array is hashed: 8 bytes per entry, about a millisecond at 2^20
+        const unsigned long long fp = hash_words(1469598103934665603ull, indices.data(), indices.size() * sizeof(size_t));
         auto it = sets.find(indices.data());
-        if (it != sets.end() && it->second.n == indices.size()) {
+        if (it != sets.end() && it->second.n == indices.size() && it->second.fp == fp) {
             return it->second;
+        }
+        if (it != sets.end()) {
+            pk_cache::get().clear(); // a prover key may hold the old index list
+            if (it->second.d_idx) {
+                b200_dev_free(it->second.d_idx);
+            }
+            sets.erase(it);
         }
         entry en;
         en.n = indices.size();
+        en.fp = fp;
         std::vector<uint32_t> idx(indices.size());
         for (size_t k = 0; k < indices.size(); ++k) {
             idx[k] = (uint32_t)indices[k];
@@ -470,6 +615,7 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
         // tables from the second proof on), the CSR and the five single points become a b200_groth16_pk_t once;
         // b200_groth16_prove then runs the witness map and the five MSMs concurrently on the device.
         bases_cache &bc = bases_cache::get();
+        bc.begin_group();
         const auto &vec = pk.B_query;
         const unsigned char *vals = reinterpret_cast<const unsigned char *>(vec.values.data());
         const size_t off2 = vec.values.empty() ? 0 : reinterpret_cast<const unsigned char *>(&vec.values[0].h) - vals;
@@ -480,7 +626,13 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
         const b200_bases_t hL = bc.lookup(curve, B200_G1, pk.L_query.data(), sizeof(G1T), pk.L_query.size(), sizeof(G1T));
         const b200_r1cs_t hr = r1cs_cache::get().lookup(cs);
         std::map<pk_cache::key_t, b200_groth16_pk_t> &keys = pk_cache::get().keys;
-        const pk_cache::key_t key(hA, hB2, hB1, hH, hL, hr);
+        unsigned long long pfp = hash_words(1469598103934665603ull, &pk.alpha_g1, sizeof(G1T));
+        pfp = hash_words(pfp, &pk.beta_g1, sizeof(G1T));
+        pfp = hash_words(pfp, &pk.beta_g2, sizeof(G2T));
+        pfp = hash_words(pfp, &pk.delta_g1, sizeof(G1T));
+        pfp = hash_words(pfp, &pk.delta_g2, sizeof(G2T));
+        pfp = hash_words(pfp, vec.indices.data(), vec.indices.size() * sizeof(size_t));
+        const pk_cache::key_t key(hA, hB2, hB1, hH, hL, hr, pfp);
         auto it = keys.find(key);
         if (it == keys.end()) {
             G1T alpha = pk.alpha_g1, beta1 = pk.beta_g1, delta1 = pk.delta_g1;
@@ -530,6 +682,7 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
     lap("witness map (device)");
 
     bases_cache &bc = bases_cache::get();
+    bc.begin_group();
     const FrT *dw = static_cast<const FrT *>(d_w.p);
     // A (:531-541): A_query[0 .. nv] x w
     G1T evaluation_At = G1T::zero();

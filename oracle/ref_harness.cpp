@@ -746,6 +746,52 @@ template<typename ppT> struct H {
         return 0;
     }
 
+    // Test hook for the overlay's caches: a DIFFERENT key of identical shape written over the fixture's key at the
+    // same host addresses (new generator randomness: every query point and single point changes). mutate_row >= 0
+    // also doubles the a- and c-coefficients of that constraint (still satisfied by the same witness) before the
+    // key is generated, so that the constraint system changes in place too.
+    static int rekey_in_place(const groth16_fixture<ppT> *cf, long mutate_row)
+    {
+        groth16_fixture<ppT> *f = const_cast<groth16_fixture<ppT> *>(cf);
+        if (!f->real_keys) {
+            return -1;
+        }
+        auto &pk = f->keypair.pk;
+        if (mutate_row >= 0) {
+            if ((size_t)mutate_row >= pk.constraint_system.num_constraints()) {
+                return -2;
+            }
+            for (auto *cs : {&pk.constraint_system, &f->example.constraint_system}) {
+                for (auto &t : cs->constraints[mutate_row].a.terms) {
+                    t.coeff = t.coeff + t.coeff;
+                }
+                for (auto &t : cs->constraints[mutate_row].c.terms) {
+                    t.coeff = t.coeff + t.coeff;
+                }
+            }
+        }
+        if (!pk.constraint_system.is_satisfied(f->example.primary_input, f->example.auxiliary_input)) {
+            return -3;
+        }
+        r1cs_gg_ppzksnark_keypair<ppT> kp = r1cs_gg_ppzksnark_generator<ppT>(pk.constraint_system);
+        if (kp.pk.A_query.size() != pk.A_query.size() || kp.pk.H_query.size() != pk.H_query.size() ||
+            kp.pk.L_query.size() != pk.L_query.size() || kp.pk.B_query.values.size() != pk.B_query.values.size() ||
+            kp.pk.B_query.indices != pk.B_query.indices) {
+            return -8;
+        }
+        std::copy(kp.pk.A_query.begin(), kp.pk.A_query.end(), pk.A_query.begin());
+        std::copy(kp.pk.H_query.begin(), kp.pk.H_query.end(), pk.H_query.begin());
+        std::copy(kp.pk.L_query.begin(), kp.pk.L_query.end(), pk.L_query.begin());
+        std::copy(kp.pk.B_query.values.begin(), kp.pk.B_query.values.end(), pk.B_query.values.begin());
+        pk.alpha_g1 = kp.pk.alpha_g1;
+        pk.beta_g1 = kp.pk.beta_g1;
+        pk.beta_g2 = kp.pk.beta_g2;
+        pk.delta_g1 = kp.pk.delta_g1;
+        pk.delta_g2 = kp.pk.delta_g2;
+        f->keypair.vk = kp.vk;
+        return 0;
+    }
+
     static int verify(const groth16_fixture<ppT> *f, const void *proof)
     {
         if (!f->real_keys) {
@@ -1157,6 +1203,25 @@ API int ref_groth16_prove_stock(void *h_, void *out, double *ms)
     fixture_handle *h = static_cast<fixture_handle *>(h_);
     DISPATCH_FIXTURE(h, prove_stock, out, ms);
     return -100;
+}
+
+API int ref_groth16_rekey_in_place(void *h_, long mutate_row)
+{
+    fixture_handle *h = static_cast<fixture_handle *>(h_);
+    DISPATCH_FIXTURE(h, rekey_in_place, mutate_row);
+    return -100;
+}
+
+// overlay build: every cache lookup hashes the whole vector / constraint system (libsnark_b200::set_cache_fingerprint_full)
+API int ref_overlay_set_fingerprint_full(int full)
+{
+#ifdef B200_OVERLAY
+    libsnark_b200::set_cache_fingerprint_full(full != 0);
+    return 0;
+#else
+    (void)full;
+    return -7;
+#endif
 }
 
 API int ref_groth16_verify(void *h_, const void *proof)

@@ -55,6 +55,7 @@ class RefOracle:
         L.ref_groth16_prove_fused.argtypes = [C.c_void_p] * 5
         L.ref_groth16_r1cs_csr.argtypes = [C.c_void_p] * 5
         L.ref_groth16_verify.argtypes = [C.c_void_p, C.c_void_p]
+        L.ref_groth16_rekey_in_place.argtypes = [C.c_void_p, C.c_long]
         L.ref_bdlo12_signed_optimal_c.restype = C.c_uint64
         L.ref_bdlo12_signed_optimal_c.argtypes = [C.c_uint64]
         L.ref_field_sha512.argtypes = [C.c_int, C.c_int, C.c_uint64, C.c_size_t, C.c_void_p]
@@ -372,6 +373,12 @@ class Groth16Fixture:
     def verify(self, proof):
         proof = np.ascontiguousarray(proof, dtype=np.uint64)
         return self.ref.lib.ref_groth16_verify(self.h, _p(proof))
+
+    def rekey_in_place(self, mutate_row=-1):
+        """A different key of identical shape written over this fixture's key at the same host addresses (test hook
+        for the overlay's caches); mutate_row >= 0 also changes that constraint's coefficients in place."""
+        rc = self.ref.lib.ref_groth16_rekey_in_place(self.h, int(mutate_row))
+        assert rc == 0, rc
 
     def close(self):
         if self.h:

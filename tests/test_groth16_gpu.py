@@ -357,3 +357,32 @@ def test_prover_against_golden_proofs(b200, curve, nc):
         for k in keys:
             k.free()
         cs.free()
+
+
+def test_overlay_caches_see_a_new_key_at_the_same_address(ref, overlay):
+    """the overlay caches host data by address. A different key of identical shape written over
+    the old one in place — `for ex in examples: keypair = generator(ex); prover(keypair.pk, ...)` on one stack slot —
+    must be uploaded afresh, not served from the stale device copy: content fingerprints in every cache key."""
+    curve = "alt_bn128"
+    fx = ref.groth16_setup(curve, (1 << 14) - 11, 10, real_keys=True)   # queries of 2^14 points: cached, tables on 2nd use
+    r, s = _rs(ref, curve)
+    try:
+        for _ in range(2):                                             # second proof: served from the caches
+            got, _ = fx.prove_fused(r, s, via=overlay)
+            assert np.array_equal(got, fx.prove(r, s)[0]) and fx.verify(got) == 1
+        # every query and single point replaced in place, constraint 0 (always sampled) rescaled in place
+        fx.rekey_in_place(mutate_row=0)
+        want, _ = fx.prove(r, s)
+        for _ in range(2):
+            got, _ = fx.prove_fused(r, s, via=overlay)
+            assert np.array_equal(got, want) and fx.verify(got) == 1
+        assert np.array_equal(fx.prove(r, s, via=overlay)[0], want)    # operator-level path (multi_exp specialisations)
+        # full-content fingerprints: a single constraint in the middle changed, key regenerated in place
+        assert overlay.lib.ref_overlay_set_fingerprint_full(1) == 0
+        fx.rekey_in_place(mutate_row=(1 << 13) + 77)
+        want, _ = fx.prove(r, s)
+        got, _ = fx.prove_fused(r, s, via=overlay)
+        assert np.array_equal(got, want) and fx.verify(got) == 1
+    finally:
+        overlay.lib.ref_overlay_set_fingerprint_full(0)
+        fx.close()
