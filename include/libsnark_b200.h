@@ -269,6 +269,12 @@ int b200_groth16_shard_msm(b200_groth16_pk_t handle, unsigned mask, void *dev_bl
  * the other selected MSMs instead of after them. */
 int b200_groth16_shard_finish_msm(b200_groth16_pk_t handle, void *dA, const void *dB, const void *dC, unsigned mask,
                                   void *dev_blob);
+/* `msm` for the MSMs that need only the witness (mask over A, B.g2, B.g1, L; not H), started in the background: the call
+ * returns at once, the caller runs the chain / broadcast / `h` / H-MSM steps of the same proof beside them (the reference
+ * overlaps nothing here: r1cs_gg_ppzksnark.tcc:489-581 is sequential), and _end waits for the blob slots and reports the
+ * first failure. One begin per key at a time; the key must not be freed in between. */
+int b200_groth16_shard_msm_begin(b200_groth16_pk_t handle, unsigned mask, void *dev_blob);
+int b200_groth16_shard_msm_end(b200_groth16_pk_t handle);
 /* blobs = `world` blobs in rank order (host memory). proof_out as b200_groth16_prove. */
 int b200_groth16_assemble(int curve, const void *alpha_g1, const void *beta_g1, const void *beta_g2,
                           const void *delta_g1, const void *delta_g2, const size_t query_sizes[4], int world,

@@ -43,7 +43,7 @@ EXPORTS = [
     "b200_groth16_shard_begin", "b200_groth16_shard_chain", "b200_groth16_shard_h", "b200_groth16_shard_msm",
     "b200_groth16_assemble", "b200_bases_precompute", "b200_bases_table_rows", "b200_groth16_shard_witness_copy", "b200_batch_exp", "b200_groth16_shard_finish_msm",
     "b200_groth16_witness_upload", "b200_groth16_prove_resident", "b200_bases_table_window_bits",
-    "b200_ntt_dev_noalloc",
+    "b200_ntt_dev_noalloc", "b200_groth16_shard_msm_begin", "b200_groth16_shard_msm_end",
 ]
 
 
@@ -129,6 +129,8 @@ def lib():
         L.b200_groth16_shard_h.argtypes = [u64, vp, vp, vp]
         L.b200_groth16_shard_msm.argtypes = [u64, C.c_uint, vp]
         L.b200_groth16_shard_finish_msm.argtypes = [u64, vp, vp, vp, C.c_uint, vp]
+        L.b200_groth16_shard_msm_begin.argtypes = [u64, C.c_uint, vp]
+        L.b200_groth16_shard_msm_end.argtypes = [u64]
         L.b200_groth16_assemble.argtypes = [i, vp, vp, vp, vp, vp, C.POINTER(sz), i, vp, vp, vp, vp]
         L.b200_batch_exp.argtypes = [i, i, vp, vp, vp, sz, vp]
         L.b200_last_msm_timing.argtypes = [C.POINTER(C.c_double)]
@@ -613,6 +615,13 @@ class Groth16ProvingKeyShard:
     def msm(self, mask, dev_blob):
         _check(lib().b200_groth16_shard_msm(self.handle, mask, C.c_void_p(dev_blob)))
 
+    def msm_begin(self, mask, dev_blob):
+        """The witness-only MSMs (A, B.g2, B.g1, L) started in the background; msm_end waits for them."""
+        _check(lib().b200_groth16_shard_msm_begin(self.handle, mask, C.c_void_p(dev_blob)))
+
+    def msm_end(self):
+        _check(lib().b200_groth16_shard_msm_end(self.handle))
+
     def finish_msm(self, dA, dB, dC, mask, dev_blob):
         _check(lib().b200_groth16_shard_finish_msm(self.handle, C.c_void_p(dA), C.c_void_p(dB), C.c_void_p(dC), mask,
                                                    C.c_void_p(dev_blob)))
@@ -680,23 +689,30 @@ class DistributedProver:
             names.append(name)
         self._distribute_witness(primary_input, auxiliary_input)
         lap("upload_broadcast")
-        if self.chain_parallel:
-            if pk.rank < 3:
-                pk.chain(pk.rank, self.chains[pk.rank].data_ptr())
-            lap("chain")
-            for i in range(3):
-                dist.broadcast(self.chains[i], src=i)
-            torch.cuda.current_stream().synchronize()
-            lap("chain_broadcast")
-            # pointwise + icosetFFT + the H shard MSM on this thread's slot, the A, B, L shard MSMs beside them
-            pk.finish_msm(self.chains[0].data_ptr(), self.chains[1].data_ptr(), self.chains[2].data_ptr(),
-                          MSM_A | MSM_B_G2 | MSM_B_G1 | MSM_H | MSM_L, self.blob.data_ptr())
-            lap("h_and_msm")
-        else:
-            pk.h()
-            lap("witness_map")
-            pk.msm(MSM_A | MSM_B_G2 | MSM_B_G1 | MSM_H | MSM_L, self.blob.data_ptr())
-            lap("msm")
+        # the A, B and L shard MSMs need nothing but the witness: they run in the background from here on, beside the
+        # chains, their broadcast and the H computation (whose kernels go to higher-priority streams)
+        pk.msm_begin(MSM_A | MSM_B_G2 | MSM_B_G1 | MSM_L, self.blob.data_ptr())
+        try:
+            if self.chain_parallel:
+                if pk.rank < 3:
+                    pk.chain(pk.rank, self.chains[pk.rank].data_ptr())
+                lap("chain")
+                for i in range(3):
+                    dist.broadcast(self.chains[i], src=i)
+                torch.cuda.current_stream().synchronize()
+                lap("chain_broadcast")
+                # pointwise + icosetFFT + the H shard MSM on this thread's slot
+                pk.finish_msm(self.chains[0].data_ptr(), self.chains[1].data_ptr(), self.chains[2].data_ptr(), MSM_H,
+                              self.blob.data_ptr())
+                lap("h_msm")
+            else:
+                pk.h()
+                lap("witness_map")
+                pk.msm(MSM_H, self.blob.data_ptr())
+                lap("h_msm")
+        finally:
+            pk.msm_end()
+        lap("other_msms_tail")
         if pk.world > 1:
             dist.all_gather_into_tensor(self.gathered, self.blob)
             src = self.gathered

@@ -18,12 +18,13 @@ namespace
 struct GroupVt {
     int (*bases_upload)(int, int, const void *, size_t, size_t, rt::BaseSet *);
     int (*bases_precompute)(rt::BaseSet *);
-    int (*msm_windows)(const rt::BaseSet &, size_t, size_t, const void *, void *, int *, int *);
+    int (*msm_windows)(const rt::BaseSet &, size_t, size_t, const void *, void *, int *, int *, const rt::SharedSort *, uint32_t);
+    int (*msm_sort)(const rt::BaseSet &, size_t, const void *, rt::SharedSort *, cudaStream_t);
     int (*msm_fold)(const void *, int, int, int, size_t, void *);
     size_t (*window_point_bytes)();
     int (*scalar_bits)();
 };
-#define GROUP_VT(name) {name##_bases_upload, name##_bases_precompute, name##_msm_windows, name##_msm_fold, name##_window_point_bytes, name##_scalar_bits}
+#define GROUP_VT(name) {name##_bases_upload, name##_bases_precompute, name##_msm_windows, name##_msm_sort, name##_msm_fold, name##_window_point_bytes, name##_scalar_bits}
 
 struct CurveVt {
     GroupVt g[2]; // [0] = G1, [1] = G2
@@ -100,7 +101,8 @@ void write_zero_point(int curve, int group, void *out)
 }
 
 int msm_resident_impl(const rt::BaseSet &bs, size_t first, size_t n, const void *scalars, int on_device,
-                      void *out, void *out_windows, void *dev_out_windows = nullptr)
+                      void *out, void *out_windows, void *dev_out_windows = nullptr, const rt::SharedSort *shared = nullptr,
+                      uint32_t skip = 0)
 {
     const CurveVt *v = vt(bs.curve);
     if (first + n > bs.n) {
@@ -131,7 +133,7 @@ int msm_resident_impl(const rt::BaseSet &bs, size_t first, size_t n, const void 
         return B200_ERR_CUDA;
     }
     int W = 0, c = 0;
-    int rc = v->grp(bs.group).msm_windows(bs, first, n, sdev, g_windows.p, &W, &c);
+    int rc = v->grp(bs.group).msm_windows(bs, first, n, sdev, g_windows.p, &W, &c, shared, skip);
     if (rc) {
         return rc;
     }
@@ -205,6 +207,56 @@ void scalar_stats(int curve, const void *scalars, size_t n, size_t *stats)
 }
 
 } // namespace
+
+namespace b200
+{
+namespace rt
+{
+
+bool msm_shared_eligible(const b200_bases_t sets[4], const size_t n[4], uint32_t skip)
+{
+    BaseSet bs[4];
+    for (int k = 0; k < 4; ++k) {
+        if (!find_set(sets[k], &bs[k])) {
+            return false;
+        }
+    }
+    for (int k = 0; k < 4; ++k) {
+        if (bs[k].curve != bs[0].curve || !bs[k].table_c || bs[k].table_c != bs[0].table_c || bs[k].inf || n[k] > bs[k].n ||
+            n[k] == 0) {
+            return false;
+        }
+    }
+    return n[1] == n[0] && n[2] == n[0] && n[3] + skip == n[0];
+}
+
+int msm_shared_sort(b200_bases_t set, size_t n, const void *scalars_dev, SharedSort *out, cudaStream_t s)
+{
+    std::shared_lock<std::shared_mutex> life(g_life);
+    BaseSet bs;
+    if (!find_set(set, &bs)) {
+        return B200_ERR_HANDLE;
+    }
+    return vt(bs.curve)->grp(bs.group).msm_sort(bs, n, scalars_dev, out, s);
+}
+
+int msm_resident_shared(b200_bases_t handle, size_t n, const void *scalars_dev, void *out_host, void *dev_out_windows,
+                        const SharedSort *shared, uint32_t skip)
+{
+    std::shared_lock<std::shared_mutex> life(g_life);
+    BaseSet bs;
+    if (!find_set(handle, &bs)) {
+        return B200_ERR_HANDLE;
+    }
+    if ((!out_host && !dev_out_windows) || !scalars_dev || n == 0) {
+        return set_error(B200_ERR_ARG, "null pointer or empty range");
+    }
+    std::lock_guard<std::mutex> lk(g_slot[rt::slot()].mu);
+    return msm_resident_impl(bs, 0, n, scalars_dev, 1, out_host, nullptr, dev_out_windows, shared, skip);
+}
+
+} // namespace rt
+} // namespace b200
 
 extern "C" {
 

@@ -66,30 +66,19 @@ template<class F> HD XYZZ<F> dbl_affine(const Affine<F> &p)
 
 // acc = 2 * acc   — EFD dbl-2008-s-1, a = 0. (y == 0 cannot occur on these prime-order groups,
 // but is handled: U = 0 gives ZZ = 0 = infinity, which is the right answer for a 2-torsion point.)
-// Which product a formula uses: the field's operators (inlined in the hot kernels, one shared body in translation units
-// built with -DB200_OUTLINE_MUL), or F::mul_i / F::sqr_i (always side by side: the latency-bound cold kernels).
-struct MulOp {
-    template<class F> HD static F mul(const F &a, const F &b) { return a * b; }
-    template<class F> HD static F sqr(const F &a) { return a.sqr(); }
-};
-struct MulIlp {
-    template<class F> HD static F mul(const F &a, const F &b) { return F::mul_i(a, b); }
-    template<class F> HD static F sqr(const F &a) { return F::sqr_i(a); }
-};
-
-template<class F, class M = MulOp> HD void dbl(XYZZ<F> &a)
+template<class F> HD void dbl(XYZZ<F> &a)
 {
     const F u = a.y.dbl();
-    const F v = M::sqr(u);
-    const F w = M::mul(u, v);
-    const F s = M::mul(a.x, v);
-    const F x2 = M::sqr(a.x);
+    const F v = u.sqr();
+    const F w = u * v;
+    const F s = a.x * v;
+    const F x2 = a.x.sqr();
     const F m = x2.dbl() + x2;
-    const F x3 = M::sqr(m) - s.dbl();
-    a.y = M::mul(m, s - x3) - M::mul(w, a.y);
+    const F x3 = m.sqr() - s.dbl();
+    a.y = m * (s - x3) - w * a.y;
     a.x = x3;
-    a.zz = M::mul(v, a.zz);
-    a.zzz = M::mul(w, a.zzz);
+    a.zz = v * a.zz;
+    a.zzz = w * a.zzz;
 }
 
 #if defined(__CUDACC__)
@@ -147,29 +136,26 @@ template<class F> HD void madd(XYZZ<F> &a, const Affine<F> &p)
 
 // acc += b   — EFD add-2008-s. Counterpart of libff add / operator+ (alt_bn128_g1.cpp:97-206).
 // Same structure as madd: no early exits, selects for the infinity cases.
-template<class F, class M = MulOp> HD void add(XYZZ<F> &a, const XYZZ<F> &b)
+template<class F> HD void add(XYZZ<F> &a, const XYZZ<F> &b)
 {
     const bool a_inf = a.is_inf(), b_inf = b.is_inf();
-    const F u1 = M::mul(a.x, b.zz);
-    const F u2 = M::mul(b.x, a.zz);
-    const F s1 = M::mul(a.y, b.zzz);
-    const F s2 = M::mul(b.y, a.zzz);
-    const F zz12 = M::mul(a.zz, b.zz);
-    const F zzz12 = M::mul(a.zzz, b.zzz);
+    const F u1 = a.x * b.zz;
+    const F u2 = b.x * a.zz;
+    const F s1 = a.y * b.zzz;
+    const F s2 = b.y * a.zzz;
     const F pd = u2 - u1;
     const F rd = s2 - s1;
-    const F pp = M::sqr(pd);
-    const F rr = M::sqr(rd);
-    const F ppp = M::mul(pd, pp);
-    const F q = M::mul(u1, pp);
+    const F pp = pd.sqr();
+    const F ppp = pd * pp;
+    const F q = u1 * pp;
     XYZZ<F> r;
-    r.x = rr - ppp - q.dbl();
-    r.y = M::mul(rd, q - r.x) - M::mul(s1, ppp);
-    r.zz = M::mul(zz12, pp);
-    r.zzz = M::mul(zzz12, ppp);
+    r.x = rd.sqr() - ppp - q.dbl();
+    r.y = rd * (q - r.x) - s1 * ppp;
+    r.zz = a.zz * b.zz * pp;
+    r.zzz = a.zzz * b.zzz * ppp;
     if (!a_inf && !b_inf && pd.is_zero() && rd.is_zero()) {
         r = a;
-        dbl<F, M>(r); // P + P
+        dbl(r); // P + P
     }
     r = select(a_inf, r, b);
     a = select(b_inf, r, a);
@@ -181,38 +167,6 @@ template<class F, class M = MulOp> HD void add(XYZZ<F> &a, const XYZZ<F> &b)
 template<class F> __device__ __noinline__ void add_outlined(XYZZ<F> &a, const XYZZ<F> &b) { add(a, b); }
 template<class F> __device__ __noinline__ void dbl_outlined(XYZZ<F> &a) { dbl(a); }
 #endif
-// The same two operations with their products side by side (MulIlp), one instance per translation unit: for kernels in
-// which one warp per scheduler walks a chain of dependent group operations (bucket reduction).
-#if defined(__CUDACC__)
-template<class F> __device__ __noinline__ void add_ilp_outlined(XYZZ<F> &a, const XYZZ<F> &b) { add<F, MulIlp>(a, b); }
-template<class F> __device__ __noinline__ void dbl_ilp_outlined(XYZZ<F> &a) { dbl<F, MulIlp>(a); }
-#endif
-// Points of more than 256 bytes (bls12_377 G2, bw6_761) do not fit the register file next to the temporaries of a
-// formula with every product in flight: they keep the compact out-of-line version.
-template<class F> HD void add_ilp(XYZZ<F> &a, const XYZZ<F> &b)
-{
-#if defined(__CUDA_ARCH__)
-    if (sizeof(XYZZ<F>) <= 256) {
-        add_ilp_outlined(a, b);
-    } else {
-        add_outlined(a, b);
-    }
-#else
-    add(a, b);
-#endif
-}
-template<class F> HD void dbl_ilp(XYZZ<F> &a)
-{
-#if defined(__CUDA_ARCH__)
-    if (sizeof(XYZZ<F>) <= 256) {
-        dbl_ilp_outlined(a);
-    } else {
-        dbl_outlined(a);
-    }
-#else
-    dbl(a);
-#endif
-}
 template<class F> HD void add_cold(XYZZ<F> &a, const XYZZ<F> &b)
 {
 #if defined(__CUDA_ARCH__)

@@ -397,20 +397,6 @@ template<class P> struct alignas(16) Fp {
     }
 
     HD Fp sqr() const { return (*this) * (*this); }
-    // Products for the latency-bound cold kernels (curve.cuh add_ilp / dbl_ilp): inlined even in translation units built
-    // with -DB200_OUTLINE_MUL, so that the independent products of one group addition interleave inside the single
-    // warp that runs them (a lone warp walking 14 out-of-line products one after the other needs ~7 us per addition).
-    // The 24-limb field keeps its shared body: one inlined product is already ~20 KB of code.
-    HD static Fp mul_i(const Fp &a, const Fp &b)
-    {
-#if defined(__CUDA_ARCH__)
-        if (N >= 16) {
-            return mul_outlined(a, b);
-        }
-#endif
-        return mul_inline(a, b);
-    }
-    HD static Fp sqr_i(const Fp &a) { return mul_i(a, a); }
 
     // Montgomery -> standard representation (libff as_bigint, fp.tcc:270-281): multiply by 1.
     HD Fp from_mont() const
@@ -602,38 +588,6 @@ template<class P2> struct Fp2 {
         return sqr_outlined(*this);
 #else
         return sqr_body(*this);
-#endif
-    }
-    // See Fp::mul_i: one out-of-line body per Fp2 operation whose two or three base-field products are inlined side by side.
-#if defined(__CUDACC__)
-    static __device__ __noinline__ Fp2 mul_o3(Fp2 a, Fp2 b)
-    {
-        const F aA = F::mul_i(a.c0, b.c0);
-        const F bB = F::mul_i(a.c1, b.c1);
-        const F s = F::mul_i(a.c0 + a.c1, b.c0 + b.c1);
-        return Fp2{aA + P2::mul_by_nr(bB), s - aA - bB};
-    }
-    static __device__ __noinline__ Fp2 sqr_o2(Fp2 a)
-    {
-        const F ab = F::mul_i(a.c0, a.c1);
-        const F t = F::mul_i(a.c0 + a.c1, a.c0 + P2::mul_by_nr(a.c1));
-        return Fp2{t - ab - P2::mul_by_nr(ab), ab + ab};
-    }
-#endif
-    HD static Fp2 mul_i(const Fp2 &a, const Fp2 &b)
-    {
-#if defined(__CUDA_ARCH__)
-        return mul_o3(a, b);
-#else
-        return mul_body(a, b);
-#endif
-    }
-    HD static Fp2 sqr_i(const Fp2 &a)
-    {
-#if defined(__CUDA_ARCH__)
-        return sqr_o2(a);
-#else
-        return sqr_body(a);
 #endif
     }
     HD Fp2 inverse() const

@@ -246,19 +246,27 @@ int assemble_shards(const KeyPoints &kp, const size_t tot[4], int world, const v
     const uint8_t *blobs = static_cast<const uint8_t *>(blobs_);
     msm::RefPoint<F1> At, Bg1, Ht, Lt;
     msm::RefPoint<F2> Bg2;
-    fold_shards<CURVE, GROUP_G1>(tot[0], world, blobs, L.total, L.off[0], &At);
-    fold_shards<CURVE, GROUP_G2>(tot[1], world, blobs, L.total, L.off[1], &Bg2);
-    fold_shards<CURVE, GROUP_G1>(tot[1], world, blobs, L.total, L.off[2], &Bg1);
-    fold_shards<CURVE, GROUP_G1>(tot[2], world, blobs, L.total, L.off[3], &Ht);
+    // the five folds and the r, s-only scalar multiplications are independent: side by side on host threads
+    auto f_pre = std::async(std::launch::async, [&]() { return pre_assemble<CURVE>(kp, r, s); });
+    auto f_g2 = std::async(std::launch::async, [&]() { fold_shards<CURVE, GROUP_G2>(tot[1], world, blobs, L.total, L.off[1], &Bg2); });
+    auto f_a = std::async(std::launch::async, [&]() { fold_shards<CURVE, GROUP_G1>(tot[0], world, blobs, L.total, L.off[0], &At); });
+    auto f_b1 = std::async(std::launch::async, [&]() { fold_shards<CURVE, GROUP_G1>(tot[1], world, blobs, L.total, L.off[2], &Bg1); });
+    auto f_h = std::async(std::launch::async, [&]() { fold_shards<CURVE, GROUP_G1>(tot[2], world, blobs, L.total, L.off[3], &Ht); });
     fold_shards<CURVE, GROUP_G1>(tot[3], world, blobs, L.total, L.off[4], &Lt);
-    return assemble<CURVE>(kp, r, s, &At, &Bg2, &Bg1, &Ht, &Lt, proof_out);
+    f_g2.get();
+    f_a.get();
+    f_b1.get();
+    f_h.get();
+    const PreAssembled<CURVE> pre = f_pre.get();
+    return assemble<CURVE>(kp, r, s, &At, &Bg2, &Bg1, &Ht, &Lt, proof_out, &pre);
 }
 
 // ---- concurrent MSMs ----------------------------------------------------------------------------------
 // The prover's five MSMs are independent of each other (only H waits for the witness map). Each runs its
 // sort -> accumulate -> reduce pipeline in an execution slot of its own (runtime.hpp), driven by a host thread
 // of its own, so that the GPU always has bucket-accumulation work of one MSM in flight while another is in a
-// latency-bound stage. Slot plan: 0 (this thread) = witness map, then H; 1 = B.g2; 2 = A, then B.g1; 3 = L.
+// latency-bound stage. Slot plan: 0 (this thread) = witness map, then B.g1, then H; 1 = B.g2; 2 = A; 3 = L
+// (profiles/r2_prove_slot_plans.jsonl: 21.7 -> 20.8 ms against A and B.g1 sharing slot 2).
 struct MsmJob {
     int k;             // blob order: 0 A, 1 B.g2, 2 B.g1, 3 H, 4 L
     b200_bases_t set;
@@ -266,12 +274,15 @@ struct MsmJob {
     const void *scalars; // device
     void *out;           // host point (windows_dev == false) or device window array
     bool windows_dev;
+    const rt::SharedSort *shared = nullptr; // the sort of the witness shared by A, B.g2, B.g1 and L (share_witness_sort)
+    uint32_t skip = 0;
 };
 struct JobResult {
     int rc = B200_OK;
     std::string err;
 };
-constexpr int MSM_SLOT[NUM_MSM] = {2, 1, 2, 0, 3};
+std::map<uint64_t, std::future<JobResult>> g_pending; // b200_groth16_shard_msm_begin .. _end, by key handle (under g_mu)
+constexpr int MSM_SLOT[NUM_MSM] = {2, 1, 0, 0, 3};
 
 // Tuning knobs (environment, read per call): B200_MSM_SLOTS = five slot numbers "A,Bg2,Bg1,H,L" overriding the plan
 // above; B200_WM_FIRST = 0 starts the other slots before the witness map instead of after it.
@@ -295,8 +306,10 @@ void slot_plan(int plan[NUM_MSM], bool *wm_first)
 int run_job(const MsmJob &j, double *ms5)
 {
     const double t0 = now_ms();
-    const int rc = j.windows_dev ? b200_msm_resident_windows_dev(j.set, 0, j.n, j.scalars, 1, j.out)
-                                 : b200_msm_resident(j.set, 0, j.n, j.scalars, 1, j.out);
+    const int rc = j.shared        ? rt::msm_resident_shared(j.set, j.n, j.scalars, j.windows_dev ? nullptr : j.out,
+                                                              j.windows_dev ? j.out : nullptr, j.shared, j.skip)
+                   : j.windows_dev ? b200_msm_resident_windows_dev(j.set, 0, j.n, j.scalars, 1, j.out)
+                                   : b200_msm_resident(j.set, 0, j.n, j.scalars, 1, j.out);
     if (ms5) {
         ms5[j.k] = now_ms() - t0;
     }
@@ -314,6 +327,35 @@ JobResult run_slot_jobs(int slot, std::vector<MsmJob> jobs, double *ms5)
         r.err = rt::last_error(); // thread-local: carry the text back to the calling thread
     }
     return r;
+}
+
+// A, B.g2, B.g1 and L all take the witness as their scalars (r1cs_gg_ppzksnark.tcc:539-581; L from variable
+// num_inputs + 1 on): when the whole key is on this GPU, B is dense and the four sets have window tables of one width,
+// their digits are sorted ONCE — on slot 1's stream, beside the witness map — and the four MSMs read that sort
+// (rt::SharedSort). Returns with the jobs marked, or unchanged when the conditions do not hold. B200_SHARED_SORT=0 turns
+// it off.
+rt::SharedSort g_shared_sort; // one proof at a time uses it (under g_mu)
+int share_witness_sort(const ProvingKey &pk, std::vector<MsmJob> &jobs)
+{
+    static const bool off = getenv("B200_SHARED_SORT") && getenv("B200_SHARED_SORT")[0] == '0';
+    if (off || pk.world != 1 || pk.d_B_idx || jobs.size() != NUM_MSM) {
+        return B200_OK;
+    }
+    const b200_bases_t sets[4] = {pk.A, pk.B_g2, pk.B_g1, pk.L};
+    const size_t n[4] = {jobs[0].n, jobs[1].n, jobs[2].n, jobs[4].n};
+    const uint32_t skip = (uint32_t)(pk.ni + 1);
+    if (!rt::msm_shared_eligible(sets, n, skip)) {
+        return B200_OK;
+    }
+    if (rt::msm_shared_sort(pk.A, n[0], pk.d_w, &g_shared_sort, rt::slot_stream(1)) != B200_OK) {
+        return B200_OK; // e.g. too small for affine rounds: every MSM sorts for itself
+    }
+    for (int k : {0, 1, 2, 4}) {
+        jobs[k].shared = &g_shared_sort;
+        jobs[k].scalars = pk.d_w;
+    }
+    jobs[4].skip = skip;
+    return B200_OK;
 }
 
 // Runs `jobs` (any subset of the five MSMs) over the slots; `before_h`, if set, runs on this thread ahead of the H
@@ -500,13 +542,16 @@ int prove_impl(const ProvingKey &pk, const void *primary_input, const void *auxi
     }
     // the five MSMs side by side (run_msms); this thread computes H's scalars first
     double msm_ms[NUM_MSM] = {0, 0, 0, 0, 0};
-    const std::vector<MsmJob> jobs = {
+    std::vector<MsmJob> jobs = {
         {0, pk.A, pk.nv + 1, pk.d_w, At.data(), false},
         {1, pk.B_g2, pk.nB, scB, Bg2.data(), false},
         {2, pk.B_g1, pk.nB, scB, Bg1.data(), false},
         {3, pk.H, pk.m - 1, pk.d_h, Ht.data(), false},
         {4, pk.L, pk.nv - pk.ni, static_cast<const uint8_t *>(pk.d_w) + (pk.ni + 1) * fr, Lt.data(), false},
     };
+    if ((rc = share_witness_sort(pk, jobs))) {
+        return rc;
+    }
     rc = run_msms(jobs, msm_ms, [&]() -> int {
         const double w0 = now_ms();
         const int wrc = b200_witness_map_r1cs_dev(pk.r1cs, pk.d_w, pk.m, pk.d_h);
@@ -878,15 +923,65 @@ int b200_groth16_shard_msm(b200_groth16_pk_t handle, unsigned mask, void *dev_bl
 int b200_groth16_shard_finish_msm(b200_groth16_pk_t handle, void *dA, const void *dB, const void *dC, unsigned mask,
                                   void *dev_blob)
 {
+    ProvingKey key;
+    {
+        std::lock_guard<std::mutex> lk(g_mu); // not held over the work: a begun msm_begin of the same key runs beside this
+        const ProvingKey *pk = find_key(handle);
+        if (!pk) {
+            return B200_ERR_HANDLE;
+        }
+        key = *pk;
+    }
+    if (!dA || !dB || !dC || !dev_blob) {
+        return rt::set_error(B200_ERR_ARG, "null pointer");
+    }
+    return shard_msms(key, mask, dev_blob, nullptr, false, nullptr, dA, dB, dC);
+}
+
+// The MSMs that need only the witness (A, B.g2, B.g1, L) started in the background, so that the caller can run the
+// collectives and the H computation of the same proof beside them; _end waits and reports.
+int b200_groth16_shard_msm_begin(b200_groth16_pk_t handle, unsigned mask, void *dev_blob)
+{
+    if (!dev_blob || (mask & 8u) || !(mask & 0x17u)) {
+        return rt::set_error(B200_ERR_ARG, "msm_begin takes a device blob and a mask over A, B.g2, B.g1, L (H waits for `h`)");
+    }
     std::lock_guard<std::mutex> lk(g_mu);
     const ProvingKey *pk = find_key(handle);
     if (!pk) {
         return B200_ERR_HANDLE;
     }
-    if (!dA || !dB || !dC || !dev_blob) {
-        return rt::set_error(B200_ERR_ARG, "null pointer");
+    if (g_pending.count(handle)) {
+        return rt::set_error(B200_ERR_ARG, "msm_begin: the previous msm_begin of this key has not been ended");
     }
-    return shard_msms(*pk, mask, dev_blob, nullptr, false, nullptr, dA, dB, dC);
+    const ProvingKey key = *pk;
+    g_pending[handle] = std::async(std::launch::async, [key, mask, dev_blob]() {
+        JobResult r;
+        r.rc = rt::bind_thread(1); // this thread only launches the index gather of a sparse B query; the MSMs bind their own slots
+        if (r.rc == B200_OK) {
+            r.rc = shard_msms(key, mask, dev_blob, nullptr, false, nullptr);
+        }
+        if (r.rc != B200_OK) {
+            r.err = rt::last_error();
+        }
+        return r;
+    });
+    return B200_OK;
+}
+
+int b200_groth16_shard_msm_end(b200_groth16_pk_t handle)
+{
+    std::future<JobResult> f;
+    {
+        std::lock_guard<std::mutex> lk(g_mu);
+        auto it = g_pending.find(handle);
+        if (it == g_pending.end()) {
+            return rt::set_error(B200_ERR_ARG, "msm_end without msm_begin");
+        }
+        f = std::move(it->second);
+        g_pending.erase(it);
+    }
+    const JobResult r = f.get();
+    return r.rc == B200_OK ? B200_OK : rt::set_error(r.rc, "%s", r.err.c_str());
 }
 
 int b200_groth16_prove_shard(b200_groth16_pk_t handle, const void *primary_input, const void *auxiliary_input,

@@ -170,7 +170,8 @@ HD void scatter_body(size_t i, const uint32_t *t, int NL, const Geometry &g, uin
         if (d != 0) {
             const uint32_t mag = (uint32_t)(d < 0 ? -d : d);
             const uint32_t pos = atomic_inc_u32(cursor + (size_t)w * g.bstride + (mag - 1));
-            entries[pos] = ((uint32_t)i + (uint32_t)w * g.estride) | (d < 0 ? 0x80000000u : 0u);
+            const uint32_t where = g.eshift ? ((uint32_t)i | ((uint32_t)w << g.eshift)) : ((uint32_t)i + (uint32_t)w * g.estride);
+            entries[pos] = where | (d < 0 ? 0x80000000u : 0u);
         }
     }
 }
@@ -239,41 +240,9 @@ HD void accumulate_task(const Task &tk, const uint32_t *entries, const Affine<F>
 }
 
 // ---- 6. bucket reduce -------------------------------------------------------------------------
-// Level 1 of the reduction (msm_cold.cuh, k_reduce_rows), the serial part of one thread: thread l of row `row` of window
-// w owns the 2^lg_cpt consecutive buckets starting at local index (row * RROW + l) << lg_cpt. run = their sum,
-// sum = their sum weighted 1 .. 2^lg_cpt (the reference's running sums, multiexp.tcc:91-125, over this short range).
-constexpr int RROW = 256; // threads (= items) per reduce CTA
-constexpr int RGRP = 16;  // group size of the in-CTA suffix scans
-template<class F>
-HD void reduce_thread_fold(const Geometry &g, uint32_t lg_cpt, uint32_t w, uint32_t row, uint32_t l, const uint32_t *task_off,
-                           const XYZZ<F> *partial, XYZZ<F> &run, XYZZ<F> &sum)
-{
-    const uint32_t cpt = 1u << lg_cpt;
-    const uint32_t first = (row * RROW + l) << lg_cpt;
-    run = XYZZ<F>::inf();
-    sum = XYZZ<F>::inf();
-    if (first >= g.B) {
-        return;
-    }
-    const size_t b0 = (size_t)w * g.B + first;
-    for (int k = (int)cpt - 1; k >= 0; --k) {
-        const uint32_t t0 = task_off[b0 + k], t1 = task_off[b0 + k + 1];
-        // up to g.collapse partial sums are added here; beyond that k_collapse has left the bucket's total in its
-        // first task slot
-        const uint32_t tend = (t1 - t0 > g.collapse) ? t0 + 1 : t1;
-        for (uint32_t t = t0; t < tend; ++t) {
-            const XYZZ<F> s = load_vec(partial + t);
-            add_ilp(run, s);
-        }
-        if (cpt > 1) {
-            add_ilp(sum, run);
-        }
-    }
-}
-
-// The chunked formulation of the same reduction (round 1): thread `gidx` owns buckets [gidx*CHUNK, (gidx+1)*CHUNK) (global
-// ids; B is a multiple of CHUNK so a chunk never straddles windows) and returns sum_k weight(k) * S_k over them, the
-// weight of a bucket being its index inside the window + 1: running sums plus a double-and-add for the chunk's offset.
+// Thread `gidx` owns buckets [gidx*CHUNK, (gidx+1)*CHUNK) (global ids; B is a multiple of
+// CHUNK so a chunk never straddles windows). Output = sum_k weight(k) * S_k, where the
+// weight of bucket k of the window is (local index + 1).
 template<class F>
 HD void reduce_chunk_body(
     size_t gidx, const Geometry &g, const uint32_t *task_off, const XYZZ<F> *partial, XYZZ<F> *chunk_out)

@@ -60,25 +60,47 @@ template<class F> HD bool is_null(const Affine<F> &p) { return p.x.is_zero() && 
 template<class F> struct SrcEntries {
     const uint32_t *entries;
     const Affine<F> *bases;
+    // A shared sort (Geometry::eshift > 0): entry = point | window << eshift over the scalars of a LONGER vector whose
+    // first `skip` points this MSM does not have (the prover's L query starts at variable num_inputs + 1): those read as
+    // the neutral element; row = this set's table row length.
+    uint32_t eshift = 0, row = 0, skip = 0;
+    HD bool locate(uint32_t e, uint32_t &idx) const
+    {
+        if (e == NULL_ENTRY) {
+            return false;
+        }
+        const uint32_t v = e & 0x7fffffffu;
+        if (eshift == 0) {
+            idx = v;
+            return true;
+        }
+        const uint32_t pt = v & ((1u << eshift) - 1u);
+        if (pt < skip) {
+            return false;
+        }
+        idx = (v >> eshift) * row + (pt - skip);
+        return true;
+    }
     HD Affine<F> load(uint32_t i) const
     {
         const uint32_t e = entries[i];
-        if (e == NULL_ENTRY) {
+        uint32_t idx;
+        if (!locate(e, idx)) {
             return null_point<F>();
         }
-        Affine<F> p = load_vec_ro(bases + (e & 0x7fffffffu));
+        Affine<F> p = load_vec_ro(bases + idx);
         p.y = p.y.cneg((e >> 31) != 0);
         return p;
     }
     // x only (the common case of the up pass needs nothing else); null reported through the flag
     HD F load_x(uint32_t i, bool &null) const
     {
-        const uint32_t e = entries[i];
-        null = e == NULL_ENTRY;
+        uint32_t idx;
+        null = !locate(entries[i], idx);
         if (null) {
             return F::zero();
         }
-        return load_vec_ro(&bases[e & 0x7fffffffu].x);
+        return load_vec_ro(&bases[idx].x);
     }
 };
 template<class F> struct SrcPoints {
@@ -312,9 +334,13 @@ template<class F> HD void accumulate_task_pts(const Task &tk, const Affine<F> *p
 
 #if defined(__CUDACC__)
 constexpr int AFF_THREADS = 128;
+// Resident CTAs per SM the level-0 kernels are compiled for (caps their registers; per field, csrc/Makefile)
+#ifndef B200_AFF_MIN_BLOCKS
+#define B200_AFF_MIN_BLOCKS 1
+#endif
 
 template<class F, class Src>
-__global__ void __launch_bounds__(AFF_THREADS) k_aff_up0(const uint32_t *total_entries, int round, Src src, F *P0, F *T1)
+__global__ void __launch_bounds__(AFF_THREADS, B200_AFF_MIN_BLOCKS) k_aff_up0(const uint32_t *total_entries, int round, Src src, F *P0, F *T1)
 {
     const AffLevels lv = aff_levels(*total_entries, round);
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -324,7 +350,7 @@ __global__ void __launch_bounds__(AFF_THREADS) k_aff_up0(const uint32_t *total_e
 }
 
 template<class F, class Src>
-__global__ void __launch_bounds__(AFF_THREADS) k_aff_down0(const uint32_t *total_entries, int round, Src src, const F *P0,
+__global__ void __launch_bounds__(AFF_THREADS, B200_AFF_MIN_BLOCKS) k_aff_down0(const uint32_t *total_entries, int round, Src src, const F *P0,
                                                            const F *I1, Affine<F> *out)
 {
     const AffLevels lv = aff_levels(*total_entries, round);

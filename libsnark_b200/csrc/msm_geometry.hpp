@@ -2,7 +2,6 @@
 // kernels' launch code and the C-ABI's b200_msm_num_windows).
 #pragma once
 #include <cstdint>
-#include <cstdlib>
 
 namespace b200
 {
@@ -40,6 +39,10 @@ struct Geometry {
     // bucket at offsets[b] >> rounds, and the tasks of the accumulation are cut over the survivors. 0 = none.
     uint32_t rounds;
     uint32_t seg;   // task length: SEG entries, or SEG_PTS survivors when rounds > 0
+    // Entry encoding. 0: the table index itself, point + window * estride. k > 0: point | window << k — a sort that does
+    // not know the row length, so that MSMs over DIFFERENT base sets with the SAME scalars can share it (msm_host.cuh,
+    // SharedSort): each decodes with its own row length.
+    uint32_t eshift;
 };
 
 // Entries of a bucket after padding to a multiple of 2^rounds, and its survivors after the rounds.
@@ -99,30 +102,6 @@ inline void set_chunk(Geometry &g, uint32_t chunk)
     g.opw = g.cpw / g.rb;
 }
 
-constexpr int REDUCE_ROW = 256; // = msm::RROW (msm.cuh): items per reduce CTA
-// Buckets per level-1 thread (a power of two): 1 while that leaves the machine short of CTAs (the reduction is then a
-// pure latency chain and every serial addition counts), more once the rows outnumber what the SMs hold at once (the
-// per-bucket work falls from ~7 to ~3 additions); at least what keeps a window within REDUCE_ROW rows. B200_REDUCE_CPT overrides.
-inline uint32_t pick_lg_cpt(uint64_t windows, uint64_t B)
-{
-    static const int forced = getenv("B200_REDUCE_CPT") ? atoi(getenv("B200_REDUCE_CPT")) : -1;
-    uint32_t lg = 0;
-    if (forced >= 0) {
-        lg = (uint32_t)forced;
-    } else {
-        while (lg < 3 && (windows * B >> lg) / REDUCE_ROW > 2 * 148 * 2) {
-            ++lg;
-        }
-    }
-    while ((B >> lg) / REDUCE_ROW > REDUCE_ROW) {
-        ++lg;
-    }
-    while (lg > 0 && (1ull << lg) > B) {
-        --lg;
-    }
-    return lg;
-}
-
 // Window width: minimise  W(c) * (10 n + 100 * 2^(c-1))  field mults (10 per mixed add,
 // ~100 per bucket in the reduction as measured: the reduction runs at low occupancy), c in [5, 20].
 inline Geometry make_geometry(uint64_t n, int scalar_bits, int force_c = 0)
@@ -150,6 +129,7 @@ inline Geometry make_geometry(uint64_t n, int scalar_bits, int force_c = 0)
     g.estride = 0;
     g.rounds = 0;
     g.seg = SEG;
+    g.eshift = 0;
     return g;
 }
 

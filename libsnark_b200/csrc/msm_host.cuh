@@ -29,11 +29,12 @@ inline Workspace &workspace() // of the calling thread's execution slot (runtime
 // Stages 6-7; defined in msm_cold.cuh and instantiated in msm_cold_<curve>_<group>.cu.
 template<class F>
 int reduce_launch(const Geometry &g, const uint32_t *task_off, const uint32_t *multi_count,
-                  const uint32_t *multi_list, XYZZ<F> *partial, XYZZ<F> *block_out, XYZZ<F> *windows_dev);
+                  const uint32_t *multi_list, XYZZ<F> *partial, XYZZ<F> *block_out, XYZZ<F> *windows_dev, cudaStream_t s);
 
 // Upper levels of an affine round's inversion tree; defined in msm_cold.cuh like reduce_launch.
 template<class F>
-int affine_tree_launch(const uint32_t *total_entries, int round, uint32_t max_entries, F *T1, F *P1, F *T2, F *P2, F *T3);
+int affine_tree_launch(const uint32_t *total_entries, int round, uint32_t max_entries, F *T1, F *P1, F *T2, F *P2, F *T3,
+                       cudaStream_t s);
 
 // Table rows 1..W-1 of a base set (build_table_body); defined in msm_cold.cuh like reduce_launch.
 template<class F> int table_launch(size_t n, int c, int W, Affine<F> *table, const uint8_t *inf, uint32_t *fail);
@@ -140,72 +141,47 @@ template<class Fr, class F> int bases_precompute(rt::BaseSet *bs)
     return B200_OK;
 }
 
-// Runs stages 1-7; leaves W window sums (XYZZ<F>) at windows_dev.
-template<class Fr, class F>
-int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scalars_dev, void *windows_dev, int *W_out, int *c_out)
+// Geometry of the MSM over n points of `bs`: the table geometry when the set has tables, plus the affine rounds.
+template<class Fr> Geometry run_geometry(const rt::BaseSet &bs, size_t n)
+{
+    static const int table_chunk = getenv("B200_TABLE_CHUNK") ? atoi(getenv("B200_TABLE_CHUNK")) : 0; // tuning knob
+    Geometry g = bs.table_c ? make_table_geometry(n, Fr::params::BITS, bs.table_c, bs.n, table_chunk)
+                            : make_geometry(n, Fr::params::BITS);
+    // affine rounds ahead of the XYZZ accumulation; B200_AFFINE_ROUNDS = 0..4 overrides the choice (tuning knob)
+    static const int forced = getenv("B200_AFFINE_ROUNDS") ? atoi(getenv("B200_AFFINE_ROUNDS")) : -1;
+    const uint64_t ents = (uint64_t)g.W * n;
+    const uint32_t r = forced >= 0 ? (uint32_t)(forced > 4 ? 4 : forced) : pick_rounds(ents, g.NB);
+    set_rounds(g, r, ents);
+    return g;
+}
+inline size_t max_entries_of(const Geometry &g, size_t n) { return (size_t)g.W * n + (size_t)g.NB * ((1u << g.rounds) - 1u); }
+inline size_t max_tasks_of(const Geometry &g, size_t max_entries) { return (size_t)g.NB + (max_entries >> g.rounds) / g.seg + 1; }
+
+// Stages 1-4 into the given buffers (a slot's workspace or a SharedSort).
+struct SortBuffers {
+    rt::DevBuf &t, &counts, &offsets, &cursor, &task_off, &tile_sums, &entries, &tasks, &multi;
+};
+template<class Fr>
+int sort_launch(const Geometry &g, size_t n, const void *scalars_dev, const uint8_t *inf, SortBuffers b, cudaStream_t s)
 {
     constexpr int NL = Fr::N;
-    // What the caller sees is always the plain geometry of n (b200_msm_num_windows / b200_msm_fold_windows).
-    // Over a table the whole sum comes out as "window 0" and the other windows are the point at infinity,
-    // which the Horner fold passes through unchanged.
-    const Geometry pub = make_geometry(n, Fr::params::BITS);
-    static const int table_chunk = getenv("B200_TABLE_CHUNK") ? atoi(getenv("B200_TABLE_CHUNK")) : 0; // tuning knob
-    Geometry g = bs.table_c ? make_table_geometry(n, Fr::params::BITS, bs.table_c, bs.n, table_chunk) : pub;
-    const int reduce_windows = bs.table_c ? 1 : g.W;
-    {
-        // affine rounds ahead of the XYZZ accumulation; B200_AFFINE_ROUNDS = 0..4 overrides the choice (tuning knob)
-        static const int forced = getenv("B200_AFFINE_ROUNDS") ? atoi(getenv("B200_AFFINE_ROUNDS")) : -1;
-        const uint64_t ents = (uint64_t)g.W * n;
-        const uint32_t r = forced >= 0 ? (uint32_t)(forced > 4 ? 4 : forced) : pick_rounds(ents, g.NB);
-        set_rounds(g, r, ents);
-    }
     const uint32_t R = g.rounds;
-    *W_out = pub.W;
-    *c_out = pub.c;
-    Workspace &ws = workspace();
-    cudaStream_t s = rt::stream();
-    rt::MsmTiming &tm = rt::msm_timing();
-
-    const size_t max_entries = (size_t)g.W * n + (size_t)g.NB * ((1u << R) - 1u); // incl. the padding of every bucket
-    const size_t max_tasks = (size_t)g.NB + (max_entries >> R) / g.seg + 1;
+    const size_t max_entries = max_entries_of(g, n), max_tasks = max_tasks_of(g, max_entries);
     const uint32_t ntiles = grid_for(g.NB, SCAN_TILE);
     if (max_entries >= 0x7fffffffull || max_tasks >= 0xffffffffull) {
         return rt::set_error(B200_ERR_ARG, "MSM of %zu points exceeds the 32-bit entry index", n);
     }
-    if (ws.t.reserve(n * NL * 4 + 16) || ws.counts.reserve(((size_t)g.NB + 1) * 4) ||
-        ws.offsets.reserve(((size_t)g.NB + 1) * 4) || ws.cursor.reserve(((size_t)g.NB + 1) * 4) ||
-        ws.task_off.reserve(((size_t)g.NB + 1) * 4) || ws.tile_sums.reserve((size_t)ntiles * 8 + 8) ||
-        ws.entries.reserve(max_entries * 4 + 16) || ws.tasks.reserve(max_tasks * sizeof(Task)) ||
-        ws.partial.reserve(max_tasks * sizeof(XYZZ<F>)) ||
-        ws.chunk_out.reserve(((size_t)reduce_windows * g.opw + 2 * (size_t)reduce_windows * (g.B / RROW + 1)) * sizeof(XYZZ<F>)) ||
-        ws.multi.reserve(((size_t)g.NB + 4) * 4)) {
+    if (b.t.reserve(n * NL * 4 + 16) || b.counts.reserve(((size_t)g.NB + 1) * 4) || b.offsets.reserve(((size_t)g.NB + 1) * 4) ||
+        b.cursor.reserve(((size_t)g.NB + 1) * 4) || b.task_off.reserve(((size_t)g.NB + 1) * 4) ||
+        b.tile_sums.reserve((size_t)ntiles * 8 + 8) || b.entries.reserve(max_entries * 4 + 16) ||
+        b.tasks.reserve(max_tasks * sizeof(Task)) || b.multi.reserve(((size_t)g.NB + 4) * 4)) {
         return B200_ERR_CUDA;
     }
-    const AffLevels amax = aff_levels((uint32_t)max_entries, 1);
-    if (R && (ws.aff_p0.reserve((size_t)amax.pairs * sizeof(F)) || ws.aff_t1.reserve((size_t)amax.n1 * sizeof(F)) ||
-              ws.aff_p1.reserve((size_t)amax.n1 * sizeof(F)) || ws.aff_t2.reserve((size_t)amax.n2 * sizeof(F)) ||
-              ws.aff_p2.reserve((size_t)amax.n2 * sizeof(F)) || ws.aff_t3.reserve((size_t)amax.n3 * sizeof(F)) ||
-              ws.aff_a.reserve((max_entries / 2 + 1) * sizeof(Affine<F>)) ||
-              (R > 1 && ws.aff_b.reserve((max_entries / 4 + 1) * sizeof(Affine<F>))))) {
-        return B200_ERR_CUDA;
-    }
-    const Affine<F> *bases = static_cast<const Affine<F> *>(bs.pts) + first;
-    const uint8_t *inf = bs.inf ? bs.inf + first : nullptr;
-    uint32_t *t = ws.t.as<uint32_t>();
-    uint32_t *counts = ws.counts.as<uint32_t>();
-    uint32_t *offsets = ws.offsets.as<uint32_t>();
-    uint32_t *cursor = ws.cursor.as<uint32_t>();
-    uint32_t *task_off = ws.task_off.as<uint32_t>();
-    uint2 *tile_sums = ws.tile_sums.as<uint2>();
-    uint32_t *entries = ws.entries.as<uint32_t>();
-    Task *tasks = ws.tasks.as<Task>();
-    XYZZ<F> *partial = ws.partial.as<XYZZ<F>>();
-    XYZZ<F> *chunk_out = ws.chunk_out.as<XYZZ<F>>();
-    uint32_t *multi_count = ws.multi.as<uint32_t>();
-    uint32_t *multi_list = multi_count + 4;
-
-    B200_CUDA_CHECK(cudaEventRecord(tm.ev[0], s));
-    // 1-4: digits and counting sort
+    uint32_t *t = b.t.as<uint32_t>(), *counts = b.counts.as<uint32_t>(), *offsets = b.offsets.as<uint32_t>();
+    uint32_t *cursor = b.cursor.as<uint32_t>(), *task_off = b.task_off.as<uint32_t>(), *entries = b.entries.as<uint32_t>();
+    uint2 *tile_sums = b.tile_sums.as<uint2>();
+    Task *tasks = b.tasks.as<Task>();
+    uint32_t *multi_count = b.multi.as<uint32_t>(), *multi_list = multi_count + 4;
     B200_CUDA_CHECK(cudaMemsetAsync(counts, 0, ((size_t)g.NB + 1) * 4, s));
     B200_CUDA_CHECK(cudaMemsetAsync(multi_count, 0, 16, s));
     const Limbs<NL> K = make_offset_constant<NL>(g);
@@ -226,6 +202,94 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
     B200_LAUNCH_CHECK();
     k_build_tasks<<<grid_for(g.NB, 256), 256, 0, s>>>(counts, offsets, task_off, g.NB, tasks, multi_count, multi_list, g.collapse, R);
     B200_LAUNCH_CHECK();
+    return B200_OK;
+}
+
+// The sort of n scalars over the geometry of `bs` (a set with tables), for several MSMs (rt::SharedSort).
+template<class Fr> int msm_sort(const rt::BaseSet &bs, size_t n, const void *scalars_dev, rt::SharedSort *out, cudaStream_t s)
+{
+    Geometry g = run_geometry<Fr>(bs, n);
+    int k = 1;
+    while ((1ull << k) < n) {
+        ++k;
+    }
+    if (!bs.table_c || g.rounds == 0 || bs.inf || (uint64_t)g.W << k >= 0x7fffffffull) {
+        return rt::set_error(B200_ERR_ARG, "this MSM cannot run over a shared sort");
+    }
+    g.eshift = (uint32_t)k;
+    if (!out->done) {
+        B200_CUDA_CHECK(cudaEventCreateWithFlags(&out->done, cudaEventDisableTiming));
+    }
+    SortBuffers b{out->t, out->counts, out->offsets, out->cursor, out->task_off, out->tile_sums, out->entries, out->tasks, out->multi};
+    if (int rc = sort_launch<Fr>(g, n, scalars_dev, nullptr, b, s)) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaEventRecord(out->done, s));
+    out->g = g;
+    out->max_entries = max_entries_of(g, n);
+    out->max_tasks = max_tasks_of(g, out->max_entries);
+    out->curve = bs.curve;
+    return B200_OK;
+}
+
+// Runs stages 1-7 (5-7 over a shared sort); leaves W window sums (XYZZ<F>) at windows_dev.
+template<class Fr, class F>
+int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scalars_dev, void *windows_dev, int *W_out, int *c_out,
+                const rt::SharedSort *shared = nullptr, uint32_t skip = 0)
+{
+    // What the caller sees is always the plain geometry of n (b200_msm_num_windows / b200_msm_fold_windows).
+    // Over a table the whole sum comes out as "window 0" and the other windows are the point at infinity,
+    // which the Horner fold passes through unchanged.
+    const Geometry pub = make_geometry(n, Fr::params::BITS);
+    if (shared && (!bs.table_c || bs.table_c != shared->g.c || bs.inf || first != 0 || n + skip != shared->g.n)) {
+        return rt::set_error(B200_ERR_ARG, "base set does not match the shared sort");
+    }
+    const Geometry g = shared ? shared->g : run_geometry<Fr>(bs, n);
+    const int reduce_windows = bs.table_c ? 1 : g.W;
+    const uint32_t R = g.rounds;
+    *W_out = pub.W;
+    *c_out = pub.c;
+    Workspace &ws = workspace();
+    cudaStream_t s = rt::stream();
+    rt::MsmTiming &tm = rt::msm_timing();
+
+    const size_t max_entries = shared ? shared->max_entries : max_entries_of(g, n);
+    const size_t max_tasks = shared ? shared->max_tasks : max_tasks_of(g, max_entries);
+    if (ws.partial.reserve(max_tasks * sizeof(XYZZ<F>)) ||
+        ws.chunk_out.reserve(((size_t)reduce_windows * g.opw) * sizeof(XYZZ<F>))) {
+        return B200_ERR_CUDA;
+    }
+    const AffLevels amax = aff_levels((uint32_t)max_entries, 1);
+    if (R && (ws.aff_p0.reserve((size_t)amax.pairs * sizeof(F)) || ws.aff_t1.reserve((size_t)amax.n1 * sizeof(F)) ||
+              ws.aff_p1.reserve((size_t)amax.n1 * sizeof(F)) || ws.aff_t2.reserve((size_t)amax.n2 * sizeof(F)) ||
+              ws.aff_p2.reserve((size_t)amax.n2 * sizeof(F)) || ws.aff_t3.reserve((size_t)amax.n3 * sizeof(F)) ||
+              ws.aff_a.reserve((max_entries / 2 + 1) * sizeof(Affine<F>)) ||
+              (R > 1 && ws.aff_b.reserve((max_entries / 4 + 1) * sizeof(Affine<F>))))) {
+        return B200_ERR_CUDA;
+    }
+    const Affine<F> *bases = static_cast<const Affine<F> *>(bs.pts) + first;
+    const uint8_t *inf = bs.inf ? bs.inf + first : nullptr;
+
+    B200_CUDA_CHECK(cudaEventRecord(tm.ev[0], s));
+    // 1-4: digits and counting sort
+    if (shared) {
+        B200_CUDA_CHECK(cudaStreamWaitEvent(s, shared->done, 0));
+    } else {
+        SortBuffers b{ws.t, ws.counts, ws.offsets, ws.cursor, ws.task_off, ws.tile_sums, ws.entries, ws.tasks, ws.multi};
+        if (int rc = sort_launch<Fr>(g, n, scalars_dev, inf, b, s)) {
+            return rc;
+        }
+    }
+    // (const_cast: a shared sort is only read)
+    rt::SharedSort *sh = const_cast<rt::SharedSort *>(shared);
+    uint32_t *offsets = shared ? sh->offsets.as<uint32_t>() : ws.offsets.as<uint32_t>();
+    uint32_t *task_off = shared ? sh->task_off.as<uint32_t>() : ws.task_off.as<uint32_t>();
+    uint32_t *entries = shared ? sh->entries.as<uint32_t>() : ws.entries.as<uint32_t>();
+    Task *tasks = shared ? sh->tasks.as<Task>() : ws.tasks.as<Task>();
+    uint32_t *multi_count = shared ? sh->multi.as<uint32_t>() : ws.multi.as<uint32_t>();
+    uint32_t *multi_list = multi_count + 4;
+    XYZZ<F> *partial = ws.partial.as<XYZZ<F>>();
+    XYZZ<F> *chunk_out = ws.chunk_out.as<XYZZ<F>>();
     B200_CUDA_CHECK(cudaEventRecord(tm.ev[1], s));
     // 5: bucket accumulation (grid sized for the task upper bound; surplus CTAs exit at once)
     if (R) {
@@ -234,25 +298,29 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
         Affine<F> *buf[2] = {ws.aff_a.as<Affine<F>>(), ws.aff_b.as<Affine<F>>()};
         F *P0 = ws.aff_p0.as<F>(), *T1 = ws.aff_t1.as<F>();
         const Affine<F> *prev = nullptr;
+        SrcEntries<F> esrc{entries, bases};
+        if (shared) {
+            esrc.eshift = g.eshift;
+            esrc.row = (uint32_t)bs.n;
+            esrc.skip = skip;
+        }
         for (uint32_t r = 1; r <= R; ++r) {
             const AffLevels mx = aff_levels((uint32_t)max_entries, (int)r);
             Affine<F> *out = buf[(r - 1) & 1];
             const unsigned grid = grid_for(mx.n1, AFF_THREADS);
             if (r == 1) {
-                const SrcEntries<F> src{entries, bases};
-                k_aff_up0<F, SrcEntries<F>><<<grid, AFF_THREADS, 0, s>>>(total, (int)r, src, P0, T1);
+                k_aff_up0<F, SrcEntries<F>><<<grid, AFF_THREADS, 0, s>>>(total, (int)r, esrc, P0, T1);
             } else {
                 const SrcPoints<F> src{prev};
                 k_aff_up0<F, SrcPoints<F>><<<grid, AFF_THREADS, 0, s>>>(total, (int)r, src, P0, T1);
             }
             B200_LAUNCH_CHECK();
             if (int rc = affine_tree_launch<F>(total, (int)r, (uint32_t)max_entries, T1, ws.aff_p1.as<F>(), ws.aff_t2.as<F>(),
-                                               ws.aff_p2.as<F>(), ws.aff_t3.as<F>())) {
+                                               ws.aff_p2.as<F>(), ws.aff_t3.as<F>(), s)) {
                 return rc;
             }
             if (r == 1) {
-                const SrcEntries<F> src{entries, bases};
-                k_aff_down0<F, SrcEntries<F>><<<grid, AFF_THREADS, 0, s>>>(total, (int)r, src, P0, T1, out);
+                k_aff_down0<F, SrcEntries<F>><<<grid, AFF_THREADS, 0, s>>>(total, (int)r, esrc, P0, T1, out);
             } else {
                 const SrcPoints<F> src{prev};
                 k_aff_down0<F, SrcPoints<F>><<<grid, AFF_THREADS, 0, s>>>(total, (int)r, src, P0, T1, out);
@@ -272,7 +340,7 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
         Geometry gr = g;
         gr.W = reduce_windows;
         const int rc = reduce_launch<F>(gr, task_off, multi_count, multi_list, partial, chunk_out,
-                                         static_cast<XYZZ<F> *>(windows_dev));
+                                         static_cast<XYZZ<F> *>(windows_dev), s);
         if (rc) {
             return rc;
         }
@@ -321,10 +389,15 @@ template<class F> int msm_fold(const void *windows, int on_device, int W, int c,
         return msm::bases_precompute<group_traits<CURVE, GROUP>::Fr, group_traits<CURVE, GROUP>::F>(bs);       \
     }                                                                                                          \
     int name##_msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scalars_dev,            \
-                           void *windows_dev, int *W, int *c)                                                  \
+                           void *windows_dev, int *W, int *c, const rt::SharedSort *shared, uint32_t skip)     \
     {                                                                                                          \
         return msm::msm_windows<group_traits<CURVE, GROUP>::Fr, group_traits<CURVE, GROUP>::F>(                \
-            bs, first, n, scalars_dev, windows_dev, W, c);                                                     \
+            bs, first, n, scalars_dev, windows_dev, W, c, shared, skip);                                       \
+    }                                                                                                          \
+    int name##_msm_sort(const rt::BaseSet &bs, size_t n, const void *scalars_dev, rt::SharedSort *out,        \
+                        cudaStream_t s)                                                                        \
+    {                                                                                                          \
+        return msm::msm_sort<group_traits<CURVE, GROUP>::Fr>(bs, n, scalars_dev, out, s);                      \
     }                                                                                                          \
     int name##_msm_fold(const void *windows, int on_device, int W, int c, size_t shards, void *out)           \
     {                                                                                                          \

@@ -84,6 +84,7 @@ bool ensure_init()
     return do_init(cur) == B200_OK;
 }
 cudaStream_t stream() { return g_streams[g_slot]; }
+cudaStream_t slot_stream(int slot) { return g_streams[slot < 0 || slot >= NUM_SLOTS ? 0 : slot]; }
 int slot() { return g_slot; }
 int bind_thread(int slot)
 {

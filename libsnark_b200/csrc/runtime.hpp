@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 
 #include "../../include/libsnark_b200.h"
+#include "msm_geometry.hpp"
 
 namespace b200
 {
@@ -25,6 +26,7 @@ constexpr int NUM_SLOTS = 4;
 int slot();                 // the calling host thread's slot
 int bind_thread(int slot);  // call first in a new host thread: selects the slot and the library's device
 cudaStream_t stream();      // the compute stream of the calling thread's slot
+cudaStream_t slot_stream(int slot);
 void count_launch(int n = 1);
 
 #define B200_CUDA_CHECK(expr)                                                                      \
@@ -67,12 +69,35 @@ struct BaseSet {
     int table_c = 0, table_W = 0;
 };
 
+// Stages 1-4 of an MSM (digits, counting sort, tasks: everything that depends on the scalars alone) computed once and
+// read by several MSMs over different base sets: the prover's A, B.g2, B.g1 and L queries all take the witness as their
+// scalars (r1cs_gg_ppzksnark.tcc:539-581), so one sort serves four MSMs. Filled by <group>_msm_sort, consumed through
+// the `shared` argument of <group>_msm_windows. The buffers belong to this object; `done` is recorded on the sorting
+// stream after the last sort kernel, and every consumer's stream waits for it.
+struct SharedSort {
+    DevBuf t, counts, offsets, cursor, task_off, tile_sums, entries, tasks, multi;
+    msm::Geometry g{};   // table geometry incl. rounds and eshift; g.n = the scalar count
+    size_t max_entries = 0, max_tasks = 0;
+    int curve = -1;
+    cudaEvent_t done = nullptr;
+};
+
 struct MsmTiming {
     cudaEvent_t ev[5]; // start | sorted | accumulated | reduced | windows on host
     double host_fold_ms = 0;
     bool valid = false;
 };
 MsmTiming &msm_timing();
+
+// capi_msm.cu, for the prover (groth16.cu). sets = {A, B.g2, B.g1, L}, n = their MSM lengths: true when one sort of the
+// n[0] witness scalars can serve all four (same curve, tables of one window width, no base at infinity, B dense,
+// n[3] = n[0] - skip). msm_shared_sort runs it on stream s over the geometry of sets[0];
+// msm_resident_shared is b200_msm_resident / b200_msm_resident_windows_dev over such a sort.
+bool msm_shared_eligible(const b200_bases_t sets[4], const size_t n[4], uint32_t skip);
+int msm_shared_sort(b200_bases_t set, size_t n, const void *scalars_dev, SharedSort *out, cudaStream_t s);
+// out_host (one folded point, as b200_msm_resident) or dev_out_windows (as b200_msm_resident_windows_dev), the other null
+int msm_resident_shared(b200_bases_t handle, size_t n, const void *scalars_dev, void *out_host, void *dev_out_windows,
+                        const SharedSort *shared, uint32_t skip);
 
 } // namespace rt
 
@@ -83,7 +108,10 @@ MsmTiming &msm_timing();
                             rt::BaseSet *out);                                                     \
     int name##_bases_precompute(rt::BaseSet *bs);                                                  \
     int name##_msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scalars_dev, \
-                           void *windows_dev, int *W, int *c);                                     \
+                           void *windows_dev, int *W, int *c, const rt::SharedSort *shared,       \
+                           uint32_t skip);                                                         \
+    int name##_msm_sort(const rt::BaseSet &bs, size_t n, const void *scalars_dev,                  \
+                        rt::SharedSort *out, cudaStream_t s);                                      \
     int name##_msm_fold(const void *windows, int on_device, int W, int c, size_t shards, void *out); \
     size_t name##_window_point_bytes();                                                            \
     int name##_scalar_bits();

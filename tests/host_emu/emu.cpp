@@ -173,9 +173,6 @@ extern "C" int emu_signed_digits(int curve, const void *scalars, size_t n, int c
 // logic: histogram -> scan -> scatter -> tasks -> accumulate -> reduce -> fold).
 // table = true: the precomputed-table variant (b200_bases_precompute): build_table_body fills rows [2^(c w)] P,
 // every window scatters into the one bucket set, the reduction runs over a single window.
-static int reduce_lg_cpt = -1; // -1: pick_lg_cpt as the launch code does; else forced (emu_set_reduce_lg_cpt)
-extern "C" void emu_set_reduce_lg_cpt(int v) { reduce_lg_cpt = v; }
-
 template<class Fr, class F>
 static int msm_emulated(const void *bases_ref, size_t n, const void *scalars, int force_c, void *out, bool table = false,
                         int rounds = 0)
@@ -288,81 +285,10 @@ static int msm_emulated(const void *bases_ref, size_t n, const void *scalars, in
     }
     std::vector<XYZZ<F>> windows(g.W, XYZZ<F>::inf());
     const size_t reduce_windows = table ? 1 : (size_t)g.W;
-    // The two-level reduction of msm_cold.cuh (k_reduce_rows / k_reduce_windows) with the CTA steps executed one
-    // thread after the other: the per-thread fold is the product's own function, the cross-thread part restates the
-    // decomposition  sum_t t P_t = sum_a [ sum_{b >= 1} suffix_{a,b} + 16 a total_a ]  that the kernels evaluate
-    // with shared-memory scans and trees.
-    const uint32_t lg_cpt = reduce_lg_cpt >= 0 ? (uint32_t)reduce_lg_cpt : pick_lg_cpt(reduce_windows, g.B);
-    const uint32_t per_row = (uint32_t)RROW << lg_cpt, rows = (g.B + per_row - 1) / per_row;
-    auto weighted = [](const std::vector<XYZZ<F>> &P, XYZZ<F> &R, XYZZ<F> &Q0) { // R = sum P_t, Q0 = sum t P_t
-        std::vector<XYZZ<F>> suf(P);
-        for (int a = 0; a < RROW / RGRP; ++a) {
-            for (int b = RGRP - 2; b >= 0; --b) {
-                add(suf[a * RGRP + b], suf[a * RGRP + b + 1]);
-            }
-        }
-        XYZZ<F> tree = XYZZ<F>::inf();
-        std::vector<XYZZ<F>> tot(RGRP);
-        for (int a = 0; a < RROW / RGRP; ++a) {
-            tot[a] = suf[a * RGRP];
-            for (int b = 1; b < RGRP; ++b) {
-                add(tree, suf[a * RGRP + b]);
-            }
-        }
-        for (int a = RGRP - 2; a >= 0; --a) {
-            add(tot[a], tot[a + 1]);
-        }
-        R = tot[0];
-        XYZZ<F> wr = XYZZ<F>::inf();
-        for (int a = 1; a < RGRP; ++a) {
-            add(wr, tot[a]);
-        }
-        for (int k = 0; k < 4; ++k) {
-            dbl(wr);
-        }
-        add(tree, wr);
-        Q0 = tree;
-    };
-    for (size_t w = 0; w < reduce_windows; ++w) {
-        std::vector<XYZZ<F>> rowR(RROW, XYZZ<F>::inf()), rowQ(RROW, XYZZ<F>::inf());
-        if (rows > (uint32_t)RROW) {
-            return -3;
-        }
-        for (uint32_t row = 0; row < rows; ++row) {
-            std::vector<XYZZ<F>> run(RROW), sum(RROW);
-            for (uint32_t l = 0; l < (uint32_t)RROW; ++l) {
-                reduce_thread_fold<F>(g, lg_cpt, (uint32_t)w, row, l, task_off.data(), partial.data(), run[l], sum[l]);
-            }
-            XYZZ<F> R, Q0, T = XYZZ<F>::inf();
-            weighted(run, R, Q0);
-            if (lg_cpt) {
-                for (uint32_t l = 0; l < (uint32_t)RROW; ++l) {
-                    add(T, sum[l]);
-                }
-            } else {
-                T = R;
-            }
-            for (uint32_t k = 0; k < lg_cpt; ++k) {
-                dbl(Q0);
-            }
-            add(T, Q0);
-            rowR[row] = R;
-            rowQ[row] = T;
-        }
-        if (rows == 1) {
-            windows[w] = rowQ[0];
-        } else {
-            XYZZ<F> R, Q0, T = XYZZ<F>::inf();
-            weighted(rowR, R, Q0);
-            for (uint32_t h = 0; h < rows; ++h) {
-                add(T, rowQ[h]);
-            }
-            for (uint32_t k = 0; k < 8 + lg_cpt; ++k) {
-                dbl(Q0);
-            }
-            add(T, Q0);
-            windows[w] = T;
-        }
+    for (size_t gidx = 0; gidx < reduce_windows * g.cpw; ++gidx) {
+        XYZZ<F> s;
+        reduce_chunk_body<F>(gidx, g, task_off.data(), partial.data(), &s);
+        add(windows[gidx / g.cpw], s);
     }
     const RefPoint<F> r = host_fold<F>(windows.data(), g.W, g.c, 1);
     memcpy(out, &r, sizeof(r));

@@ -117,22 +117,6 @@ def test_emulated_msm_pipeline(emu, curve):
             assert np.array_equal(_emu_msm(emu, curve, gid, g[k + ".bases"], g[k + ".scalars"], c), g[k + ".out"]), (k, c)
 
 
-def test_emulated_two_level_reduction(emu):
-    """The reduction's index logic (reduce_thread_fold + the rows / windows decomposition of msm_cold.cuh) where it has
-    several rows per window and several buckets per thread: c = 13 -> 4096 buckets = 16 rows of 256 at one bucket per
-    thread, 4 rows at 4 buckets per thread, 2 rows at 8."""
-    g = np.load(os.path.join(GOLD, "msm.npz"))
-    k = "rand.alt_bn128.g1"
-    try:
-        for lg in (0, 2, 3):
-            emu.emu_set_reduce_lg_cpt(lg)
-            assert np.array_equal(_emu_msm(emu, "alt_bn128", 1, g[k + ".bases"], g[k + ".scalars"], 13), g[k + ".out"]), lg
-        emu.emu_set_reduce_lg_cpt(1)
-        assert np.array_equal(_emu_msm(emu, "alt_bn128", 1, g["edge.bases"], g["edge.scalars"], 11), g["edge.out"])
-    finally:
-        emu.emu_set_reduce_lg_cpt(-1)
-
-
 def test_emulated_msm_heavy_bucket(emu):
     """All-equal scalars: every point lands in the same bucket of each window -> many tasks per bucket
     (the k_collapse path) and the narrow top window."""
