@@ -383,7 +383,9 @@ class Ctx:
             raise SystemExit("bench.py: no CUDA device (the product has no CPU fallback)")
         torch.cuda.set_device(self.local_rank)
         if self.world > 1:
-            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local_rank))
+            # NCCL on high-priority streams: its few CTAs must not queue behind the MSMs' machine-filling kernels
+            opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local_rank), pg_options=opts)
         b.init(self.local_rank)
         self.dev = torch.device("cuda", self.local_rank)
         self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)  # > 126 MB L2

@@ -263,6 +263,10 @@ int b200_groth16_shard_begin(b200_groth16_pk_t handle, const void *primary_input
  * received dev_buf by an NCCL broadcast — one host upload per proof instead of one per rank. */
 int b200_groth16_shard_witness_copy(b200_groth16_pk_t handle, void *dev_buf, int to_key);
 int b200_groth16_shard_chain(b200_groth16_pk_t handle, int which, void *dev_out);
+/* coefficients_for_H [first, first + count) copied device-to-device between the key's buffer and dev_buf (count Fr elements):
+ * to_key = 0 on the rank that ran `h`, to hand each rank the slice its H shard MSM reads (b200_shard_range of the H query)
+ * instead of every rank repeating the pointwise step and the inverse transform; to_key = 1 on the receiving ranks. */
+int b200_groth16_shard_h_copy(b200_groth16_pk_t handle, void *dev_buf, size_t first, size_t count, int to_key);
 int b200_groth16_shard_h(b200_groth16_pk_t handle, void *dA, const void *dB, const void *dC);
 int b200_groth16_shard_msm(b200_groth16_pk_t handle, unsigned mask, void *dev_blob);
 /* `h` on three chain results and `msm` in one call: the pointwise step, the icosetFFT and the H shard MSM run beside
@@ -275,6 +279,11 @@ int b200_groth16_shard_finish_msm(b200_groth16_pk_t handle, void *dA, const void
  * first failure. One begin per key at a time; the key must not be freed in between. */
 int b200_groth16_shard_msm_begin(b200_groth16_pk_t handle, unsigned mask, void *dev_blob);
 int b200_groth16_shard_msm_end(b200_groth16_pk_t handle);
+/* Optional, at the start of a sharded proof: starts the scalar multiplications of the assembly that need only r, s and
+ * delta (r delta_g1, s delta_g1, s delta_g2, (r s) delta_g1; r1cs_gg_ppzksnark.tcc:583-595) on host threads, so that they
+ * run beside the GPU work instead of after it. A later b200_groth16_assemble with the same curve, delta, r and s uses the
+ * result; without a matching preparation it computes them itself. The inputs are copied. */
+int b200_groth16_assemble_prepare(int curve, const void *delta_g1, const void *delta_g2, const void *r, const void *s);
 /* blobs = `world` blobs in rank order (host memory). proof_out as b200_groth16_prove. */
 int b200_groth16_assemble(int curve, const void *alpha_g1, const void *beta_g1, const void *beta_g2,
                           const void *delta_g1, const void *delta_g2, const size_t query_sizes[4], int world,

@@ -44,6 +44,7 @@ EXPORTS = [
     "b200_groth16_assemble", "b200_bases_precompute", "b200_bases_table_rows", "b200_groth16_shard_witness_copy", "b200_batch_exp", "b200_groth16_shard_finish_msm",
     "b200_groth16_witness_upload", "b200_groth16_prove_resident", "b200_bases_table_window_bits",
     "b200_ntt_dev_noalloc", "b200_groth16_shard_msm_begin", "b200_groth16_shard_msm_end",
+    "b200_groth16_assemble_prepare", "b200_groth16_shard_h_copy",
 ]
 
 
@@ -125,12 +126,14 @@ def lib():
         L.b200_groth16_prove_shard.argtypes = [u64, vp, vp, vp, C.POINTER(C.c_double)]
         L.b200_groth16_shard_begin.argtypes = [u64, vp, vp]
         L.b200_groth16_shard_chain.argtypes = [u64, i, vp]
+        L.b200_groth16_shard_h_copy.argtypes = [u64, vp, sz, sz, i]
         L.b200_groth16_shard_witness_copy.argtypes = [u64, vp, i]
         L.b200_groth16_shard_h.argtypes = [u64, vp, vp, vp]
         L.b200_groth16_shard_msm.argtypes = [u64, C.c_uint, vp]
         L.b200_groth16_shard_finish_msm.argtypes = [u64, vp, vp, vp, C.c_uint, vp]
         L.b200_groth16_shard_msm_begin.argtypes = [u64, C.c_uint, vp]
         L.b200_groth16_shard_msm_end.argtypes = [u64]
+        L.b200_groth16_assemble_prepare.argtypes = [i, vp, vp, vp, vp]
         L.b200_groth16_assemble.argtypes = [i, vp, vp, vp, vp, vp, C.POINTER(sz), i, vp, vp, vp, vp]
         L.b200_batch_exp.argtypes = [i, i, vp, vp, vp, sz, vp]
         L.b200_last_msm_timing.argtypes = [C.POINTER(C.c_double)]
@@ -609,6 +612,9 @@ class Groth16ProvingKeyShard:
     def chain(self, which, dev_out):
         _check(lib().b200_groth16_shard_chain(self.handle, which, C.c_void_p(dev_out)))
 
+    def h_copy(self, dev_buf, first, count, to_key):
+        _check(lib().b200_groth16_shard_h_copy(self.handle, C.c_void_p(dev_buf), first, count, int(to_key)))
+
     def h(self, dA=None, dB=None, dC=None):
         _check(lib().b200_groth16_shard_h(self.handle, *[None if x is None else C.c_void_p(x) for x in (dA, dB, dC)]))
 
@@ -625,6 +631,11 @@ class Groth16ProvingKeyShard:
     def finish_msm(self, dA, dB, dC, mask, dev_blob):
         _check(lib().b200_groth16_shard_finish_msm(self.handle, C.c_void_p(dA), C.c_void_p(dB), C.c_void_p(dC), mask,
                                                    C.c_void_p(dev_blob)))
+
+    def assemble_prepare(self, r, s):
+        """Starts the r, s-only scalar multiplications of the assembly on host threads (b200_groth16_assemble_prepare)."""
+        r, s = _u64(r), _u64(s)
+        _check(lib().b200_groth16_assemble_prepare(_cid(self.curve), _p(self.points[3]), _p(self.points[4]), _p(r), _p(s)))
 
     def assemble(self, r, s, blobs):
         return groth16_assemble(self.curve, *self.points, self.query_sizes, self.world, blobs, r, s)
@@ -657,24 +668,51 @@ class DistributedProver:
             raise B200Error(ERR_ARG, "chain-parallel witness map needs >= 3 ranks and a power-of-two domain")
         self.blob = torch.zeros(shard.blob_bytes, dtype=torch.uint8, device=self.dev)
         self.gathered = torch.zeros(shard.world * shard.blob_bytes, dtype=torch.uint8, device=self.dev)
-        self.chains = ([torch.empty(shard.m * shard.fr_bytes, dtype=torch.uint8, device=self.dev) for _ in range(3)]
-                       if self.chain_parallel else None)
+        # rank 0 holds all three chain results, ranks 1 and 2 their own; hbuf: H coefficients (whole on rank 0, a slice elsewhere)
+        self.chains = ([torch.empty(shard.m * shard.fr_bytes, dtype=torch.uint8, device=self.dev)
+                        if (shard.rank == 0 or shard.rank == i) else None for i in range(3)] if self.chain_parallel else None)
+        self.hbuf = (torch.empty((shard.m if shard.rank == 0 else shard.ranges[2][1] + 1) * shard.fr_bytes, dtype=torch.uint8,
+                                 device=self.dev) if self.chain_parallel else None)
+        self._copy_stream, self._whead = None, None
         self.wbuf = (torch.empty((shard.r1cs.nv + 1) * shard.fr_bytes, dtype=torch.uint8, device=self.dev)
                      if shard.world > 1 else None)
 
     def _distribute_witness(self, primary_input, auxiliary_input):
         """Rank 0 uploads the witness once; the other ranks get it over NVLink (NCCL broadcast) — the witness lives in one
-        process, and eight host uploads of it would share one host memory system."""
-        pk = self.pk
-        if pk.rank == 0:
+        process, and eight host uploads of it would share one host memory system. The upload and the broadcast are cut
+        into slices: slice k travels over NVLink while slice k + 1 crosses PCIe (one copy stream; the collective of a
+        slice is ordered behind its copy and runs on NCCL's own stream)."""
+        pk, torch, dist = self.pk, self.torch, self.dist
+        if pk.world == 1:
             pk.begin(primary_input, auxiliary_input)
-            if pk.world > 1:
-                pk.witness_copy(self.wbuf.data_ptr(), 0)
-        if pk.world > 1:
-            self.dist.broadcast(self.wbuf, src=0)
-            self.torch.cuda.current_stream().synchronize()
-            if pk.rank != 0:
-                pk.witness_copy(self.wbuf.data_ptr(), 1)
+            return
+        fr = pk.fr_bytes
+        total = self.wbuf.numel()
+        head = (1 + pk.r1cs.ni) * fr
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(priority=-1)
+            self._whead = torch.empty(head, dtype=torch.uint8, pin_memory=True)
+        nslices = 4 if total >= (8 << 20) else 1
+        cuts = [head + ((total - head) * k // nslices) // 256 * 256 for k in range(nslices)] + [total]
+        works = []
+        with torch.cuda.stream(self._copy_stream):
+            if pk.rank == 0:
+                hv = self._whead.numpy()
+                hv[:fr] = np.ascontiguousarray(scalars_from_ints(pk.curve, [1])).view(np.uint8).reshape(-1)
+                hv[fr:] = _u64(primary_input).view(np.uint8).reshape(-1)
+                aux = torch.from_numpy(_u64(auxiliary_input).view(np.uint8).reshape(-1))
+            for k in range(nslices):
+                a, b_ = (0 if k == 0 else cuts[k]), cuts[k + 1]
+                if pk.rank == 0:
+                    if k == 0:
+                        self.wbuf[:head].copy_(self._whead, non_blocking=True)
+                    lo = max(a, head)
+                    self.wbuf[lo:b_].copy_(aux[lo - head:b_ - head], non_blocking=True)
+                works.append(dist.broadcast(self.wbuf[a:b_], src=0, async_op=True))
+        for w in works:
+            w.wait()
+        torch.cuda.current_stream().synchronize()
+        pk.witness_copy(self.wbuf.data_ptr(), 1)
 
     def prove(self, primary_input, auxiliary_input, r, s, fold_on_all_ranks=False):
         """The proof on rank 0 (on every rank with fold_on_all_ranks), None elsewhere. Only rank 0 reads primary_input and
@@ -687,6 +725,8 @@ class DistributedProver:
         def lap(name):
             t.append(time.perf_counter())
             names.append(name)
+        if pk.rank == 0 or fold_on_all_ranks:
+            pk.assemble_prepare(r, s)   # host threads, beside everything below
         self._distribute_witness(primary_input, auxiliary_input)
         lap("upload_broadcast")
         # the A, B and L shard MSMs need nothing but the witness: they run in the background from here on, beside the
@@ -694,16 +734,40 @@ class DistributedProver:
         pk.msm_begin(MSM_A | MSM_B_G2 | MSM_B_G1 | MSM_L, self.blob.data_ptr())
         try:
             if self.chain_parallel:
+                # ranks 0, 1, 2 each run one of the A, B, C chains; ranks 1 and 2 send theirs to rank 0, which finishes
+                # coefficients_for_H (pointwise step + inverse coset transform) and hands every rank the slice its H
+                # shard MSM reads: 2 x 32 MiB into rank 0 and 32 MiB out of it at 2^20, where broadcasting the three
+                # chains moved 96 MiB to every rank (3.2 ms of an 8.6 ms proof on 8 GPUs)
+                fr = pk.fr_bytes
                 if pk.rank < 3:
                     pk.chain(pk.rank, self.chains[pk.rank].data_ptr())
                 lap("chain")
-                for i in range(3):
-                    dist.broadcast(self.chains[i], src=i)
-                torch.cuda.current_stream().synchronize()
-                lap("chain_broadcast")
-                # pointwise + icosetFFT + the H shard MSM on this thread's slot
-                pk.finish_msm(self.chains[0].data_ptr(), self.chains[1].data_ptr(), self.chains[2].data_ptr(), MSM_H,
-                              self.blob.data_ptr())
+                if pk.rank == 0:
+                    ops = [dist.P2POp(dist.irecv, self.chains[i], i) for i in (1, 2)]
+                    for w in dist.batch_isend_irecv(ops):
+                        w.wait()
+                    torch.cuda.current_stream().synchronize()
+                    pk.h(self.chains[0].data_ptr(), self.chains[1].data_ptr(), self.chains[2].data_ptr())
+                    pk.h_copy(self.hbuf.data_ptr(), 0, pk.m - 1, 0)
+                    ops = []
+                    for g in range(1, pk.world):
+                        f, c = shard_range(pk.m - 1, pk.world, g)
+                        if c:
+                            ops.append(dist.P2POp(dist.isend, self.hbuf[f * fr:(f + c) * fr], g))
+                    for w in dist.batch_isend_irecv(ops):
+                        w.wait()
+                else:
+                    if pk.rank in (1, 2):
+                        for w in dist.batch_isend_irecv([dist.P2POp(dist.isend, self.chains[pk.rank], 0)]):
+                            w.wait()
+                    f, c = pk.ranges[2]
+                    if c:
+                        for w in dist.batch_isend_irecv([dist.P2POp(dist.irecv, self.hbuf[:c * fr], 0)]):
+                            w.wait()
+                        torch.cuda.current_stream().synchronize()
+                        pk.h_copy(self.hbuf.data_ptr(), f, c, 1)
+                lap("h_exchange")
+                pk.msm(MSM_H, self.blob.data_ptr())
                 lap("h_msm")
             else:
                 pk.h()

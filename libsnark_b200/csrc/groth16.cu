@@ -236,6 +236,64 @@ void fold_shards(size_t total, int world, const uint8_t *blobs, size_t blob_stri
     memcpy(out, &r, sizeof(r));
 }
 
+// b200_groth16_assemble_prepare: the r, s-only scalar multiplications started ahead of the MSMs, keyed by the bytes of
+// (curve, delta_g1, delta_g2, r, s); b200_groth16_assemble picks a matching one up instead of computing them at the end.
+std::mutex g_pre_mu;
+std::map<std::string, std::shared_future<std::vector<uint8_t>>> g_pre;
+template<int CURVE> std::string pre_key(const KeyPoints &kp, const void *r, const void *s)
+{
+    typedef typename group_traits<CURVE, GROUP_G1>::Fr Fr;
+    typedef typename group_traits<CURVE, GROUP_G1>::F F1;
+    typedef typename group_traits<CURVE, GROUP_G2>::F F2;
+    std::string k(1, (char)CURVE);
+    k.append(static_cast<const char *>(kp.delta_g1), 3 * sizeof(F1));
+    k.append(static_cast<const char *>(kp.delta_g2), 3 * sizeof(F2));
+    k.append(static_cast<const char *>(r), sizeof(Fr));
+    k.append(static_cast<const char *>(s), sizeof(Fr));
+    return k;
+}
+template<int CURVE> int assemble_prepare(const void *delta_g1, const void *delta_g2, const void *r, const void *s)
+{
+    typedef typename group_traits<CURVE, GROUP_G1>::Fr Fr;
+    typedef typename group_traits<CURVE, GROUP_G1>::F F1;
+    typedef typename group_traits<CURVE, GROUP_G2>::F F2;
+    KeyPoints kp = {nullptr, nullptr, nullptr, delta_g1, delta_g2};
+    const std::string key = pre_key<CURVE>(kp, r, s);
+    // the inputs are copied: the caller's buffers need not outlive this call
+    std::vector<uint8_t> d1((const uint8_t *)delta_g1, (const uint8_t *)delta_g1 + 3 * sizeof(F1));
+    std::vector<uint8_t> d2((const uint8_t *)delta_g2, (const uint8_t *)delta_g2 + 3 * sizeof(F2));
+    std::vector<uint8_t> rs((const uint8_t *)r, (const uint8_t *)r + sizeof(Fr));
+    rs.insert(rs.end(), (const uint8_t *)s, (const uint8_t *)s + sizeof(Fr));
+    std::lock_guard<std::mutex> lk(g_pre_mu);
+    if (g_pre.size() > 16) {
+        g_pre.clear(); // abandoned preparations
+    }
+    g_pre[key] = std::async(std::launch::async, [d1, d2, rs]() {
+                     const KeyPoints k2 = {nullptr, nullptr, nullptr, d1.data(), d2.data()};
+                     const PreAssembled<CURVE> p = pre_assemble<CURVE>(k2, rs.data(), rs.data() + sizeof(Fr));
+                     std::vector<uint8_t> out(sizeof(p));
+                     memcpy(out.data(), &p, sizeof(p));
+                     return out;
+                 }).share();
+    return B200_OK;
+}
+template<int CURVE> bool take_prepared(const KeyPoints &kp, const void *r, const void *s, PreAssembled<CURVE> *out)
+{
+    std::shared_future<std::vector<uint8_t>> f;
+    {
+        std::lock_guard<std::mutex> lk(g_pre_mu);
+        auto it = g_pre.find(pre_key<CURVE>(kp, r, s));
+        if (it == g_pre.end()) {
+            return false;
+        }
+        f = it->second;
+        g_pre.erase(it);
+    }
+    const std::vector<uint8_t> bytes = f.get();
+    memcpy(out, bytes.data(), sizeof(*out));
+    return true;
+}
+
 template<int CURVE>
 int assemble_shards(const KeyPoints &kp, const size_t tot[4], int world, const void *blobs_, const void *r, const void *s,
                     void *proof_out)
@@ -247,7 +305,13 @@ int assemble_shards(const KeyPoints &kp, const size_t tot[4], int world, const v
     msm::RefPoint<F1> At, Bg1, Ht, Lt;
     msm::RefPoint<F2> Bg2;
     // the five folds and the r, s-only scalar multiplications are independent: side by side on host threads
-    auto f_pre = std::async(std::launch::async, [&]() { return pre_assemble<CURVE>(kp, r, s); });
+    auto f_pre = std::async(std::launch::async, [&]() {
+        PreAssembled<CURVE> p;
+        if (!take_prepared<CURVE>(kp, r, s, &p)) {
+            p = pre_assemble<CURVE>(kp, r, s);
+        }
+        return p;
+    });
     auto f_g2 = std::async(std::launch::async, [&]() { fold_shards<CURVE, GROUP_G2>(tot[1], world, blobs, L.total, L.off[1], &Bg2); });
     auto f_a = std::async(std::launch::async, [&]() { fold_shards<CURVE, GROUP_G1>(tot[0], world, blobs, L.total, L.off[0], &At); });
     auto f_b1 = std::async(std::launch::async, [&]() { fold_shards<CURVE, GROUP_G1>(tot[1], world, blobs, L.total, L.off[2], &Bg1); });
@@ -265,7 +329,7 @@ int assemble_shards(const KeyPoints &kp, const size_t tot[4], int world, const v
 // The prover's five MSMs are independent of each other (only H waits for the witness map). Each runs its
 // sort -> accumulate -> reduce pipeline in an execution slot of its own (runtime.hpp), driven by a host thread
 // of its own, so that the GPU always has bucket-accumulation work of one MSM in flight while another is in a
-// latency-bound stage. Slot plan: 0 (this thread) = witness map, then B.g1, then H; 1 = B.g2; 2 = A; 3 = L
+// latency-bound stage. Slot plan: 0 (this thread) = witness map, then H; 1 = B.g2; 2 = A; 3 = L; 4 = B.g1
 // (profiles/r2_prove_slot_plans.jsonl: 21.7 -> 20.8 ms against A and B.g1 sharing slot 2).
 struct MsmJob {
     int k;             // blob order: 0 A, 1 B.g2, 2 B.g1, 3 H, 4 L
@@ -282,7 +346,7 @@ struct JobResult {
     std::string err;
 };
 std::map<uint64_t, std::future<JobResult>> g_pending; // b200_groth16_shard_msm_begin .. _end, by key handle (under g_mu)
-constexpr int MSM_SLOT[NUM_MSM] = {2, 1, 0, 0, 3};
+constexpr int MSM_SLOT[NUM_MSM] = {2, 1, 4, 0, 3}; // H must stay in slot 0: it runs on the thread that computed its scalars
 
 // Tuning knobs (environment, read per call): B200_MSM_SLOTS = five slot numbers "A,Bg2,Bg1,H,L" overriding the plan
 // above; B200_WM_FIRST = 0 starts the other slots before the witness map instead of after it.
@@ -297,6 +361,7 @@ void slot_plan(int plan[NUM_MSM], bool *wm_first)
             for (int k = 0; k < NUM_MSM; ++k) {
                 plan[k] = v[k] < 0 || v[k] >= rt::NUM_SLOTS ? 0 : v[k];
             }
+            plan[3] = 0; // H waits for the scalars this thread computes: it cannot move to another slot's thread
         }
     }
     const char *w = getenv("B200_WM_FIRST");
@@ -884,6 +949,24 @@ int b200_groth16_shard_witness_copy(b200_groth16_pk_t handle, void *dev_buf, int
     return B200_OK;
 }
 
+int b200_groth16_shard_h_copy(b200_groth16_pk_t handle, void *dev_buf, size_t first, size_t count, int to_key)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    const ProvingKey *pk = find_key(handle);
+    if (!pk) {
+        return B200_ERR_HANDLE;
+    }
+    if (!dev_buf || first + count > pk->m + 1) {
+        return rt::set_error(B200_ERR_ARG, "null pointer or range beyond the %zu coefficients of H", pk->m + 1);
+    }
+    const size_t fr = b200_sizeof_fr(pk->curve);
+    uint8_t *h = static_cast<uint8_t *>(pk->d_h) + first * fr;
+    cudaStream_t st = rt::stream();
+    B200_CUDA_CHECK(cudaMemcpyAsync(to_key ? (void *)h : dev_buf, to_key ? dev_buf : (void *)h, count * fr, cudaMemcpyDeviceToDevice, st));
+    B200_CUDA_CHECK(cudaStreamSynchronize(st));
+    return B200_OK;
+}
+
 int b200_groth16_shard_chain(b200_groth16_pk_t handle, int which, void *dev_out)
 {
     std::lock_guard<std::mutex> lk(g_mu);
@@ -956,7 +1039,9 @@ int b200_groth16_shard_msm_begin(b200_groth16_pk_t handle, unsigned mask, void *
     const ProvingKey key = *pk;
     g_pending[handle] = std::async(std::launch::async, [key, mask, dev_blob]() {
         JobResult r;
-        r.rc = rt::bind_thread(1); // this thread only launches the index gather of a sparse B query; the MSMs bind their own slots
+        // a slot no plan uses: this thread launches the index gather of a sparse B query and runs the plan's slot-0 job
+        // (B.g1) itself, beside the caller's own slot-0 work (the chains, then H)
+        r.rc = rt::bind_thread(rt::NUM_SLOTS - 1);
         if (r.rc == B200_OK) {
             r.rc = shard_msms(key, mask, dev_blob, nullptr, false, nullptr);
         }
@@ -1014,6 +1099,19 @@ int b200_groth16_prove_shard(b200_groth16_pk_t handle, const void *primary_input
         memcpy(stage_ms, st, sizeof(st));
     }
     return B200_OK;
+}
+
+int b200_groth16_assemble_prepare(int curve, const void *delta_g1, const void *delta_g2, const void *r, const void *s)
+{
+    if (!delta_g1 || !delta_g2 || !r || !s) {
+        return rt::set_error(B200_ERR_ARG, "null pointer");
+    }
+    switch (curve) {
+    case B200_ALT_BN128: return assemble_prepare<CURVE_ALT_BN128>(delta_g1, delta_g2, r, s);
+    case B200_BLS12_377: return assemble_prepare<CURVE_BLS12_377>(delta_g1, delta_g2, r, s);
+    case B200_BW6_761: return assemble_prepare<CURVE_BW6_761>(delta_g1, delta_g2, r, s);
+    default: return rt::set_error(B200_ERR_ARG, "unknown curve %d", curve);
+    }
 }
 
 int b200_groth16_assemble(int curve, const void *alpha_g1, const void *beta_g1, const void *beta_g2,

@@ -58,16 +58,20 @@ inline
 
 // How many affine rounds pay: a round over the survivors of the previous one saves ~3.7 of 10 field products per
 // addition but costs a fixed ~0.1 ms of dependent small launches (the inversion tree), and the padding costs up to
-// 2^rounds - 1 dead slots per bucket. Rounds while the average bucket still holds >= 16 entries, at most 3; none for
+// 2^rounds - 1 dead slots per bucket. Rounds while the average bucket still holds >= 16 entries, at most 3 (2); none for
 // small MSMs, whose accumulation is shorter than the rounds' fixed cost.
 inline uint32_t pick_rounds(uint64_t entries, uint64_t buckets)
 {
     if (entries < (1ull << 21)) {
         return 0;
     }
+    // a third round only for the large MSMs (2^20 points over tables): below, its inversion tree costs more than the
+    // products it saves — standalone 2^18: 1.60 ms with two rounds, 1.74 with three; the 8-GPU prover, whose shard
+    // MSMs have 2^17 points: 7.6 ms with two, 8.6 with three (profiles/r2_rounds_vs_size.jsonl, r2_prove_multi_rounds_n8.jsonl)
+    const uint32_t max_r = entries >= (1ull << 23) ? 3 : 2;
     uint32_t r = 0;
     uint64_t avg = entries / (buckets ? buckets : 1);
-    while (r < 3 && avg >= 16) {
+    while (r < max_r && avg >= 16) {
         ++r;
         avg >>= 1;
     }

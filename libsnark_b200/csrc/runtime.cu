@@ -15,7 +15,7 @@ namespace
 {
 thread_local char g_err[512] = "";
 int g_device = -1;
-cudaStream_t g_streams[NUM_SLOTS] = {nullptr, nullptr, nullptr, nullptr};
+cudaStream_t g_streams[NUM_SLOTS] = {};
 #define g_stream g_streams[0]
 thread_local int g_slot = 0;
 std::atomic<uint64_t> g_launches{0};

@@ -22,7 +22,7 @@ bool ensure_init();         // true when a device is bound (b200_init called or 
 // different host threads so that the latency-bound stages of one (sort, bucket reduction, host fold) overlap the
 // integer-pipe-bound bucket accumulation of another. Slot 0 has the highest stream priority (it carries the
 // witness map, which the H MSM waits for).
-constexpr int NUM_SLOTS = 4;
+constexpr int NUM_SLOTS = 6;
 int slot();                 // the calling host thread's slot
 int bind_thread(int slot);  // call first in a new host thread: selects the slot and the library's device
 cudaStream_t stream();      // the compute stream of the calling thread's slot
