@@ -17,11 +17,18 @@
 // survivors sit at offsets[b] >> rounds. A pad, and the sum P + (-P), is the affine pair (0, 0) — not a point of
 // y^2 = x^3 + b for b != 0 — which every later stage treats as the neutral element.
 //
-// One round = 7 launches:  up0 (per pair: denominator d = x2 - x1, running products per thread) -> up (two more
-// levels of running products, AFF_K elements per thread) -> top (one inversion per remaining element, binary
-// Euclid, Fp::inverse_fast) -> down, down (inverses of every level's elements) -> down0 (inverse of each pair's d,
-// the affine addition, result written). Thread t of a level owns elements t, t + T, t + 2T, ... (T = threads of the
-// level), so every access is coalesced.
+// Ownership. A BLOCK is 2^rounds consecutive entries (-> one survivor); thread t owns blocks t, t + T, t + 2T, ... (AFF_KB of
+// them, T = threads) in EVERY round, and the rounds keep their arrays element-major (element e of block m at e * blocks + m):
+// the threads of a warp — consecutive blocks — read and write consecutive addresses in every round, and the inversion tree
+// above level 0 has the same size in all rounds. A thread's chain of a round = its pairs in the order the up pass
+// multiplied them; the down pass walks it backwards. Pex[q] = the product of the chain's elements before pair q.
+// One round = 7 launches: up (per pair: denominator d = x2 - x1, running products per thread) -> up, up (two more levels of
+// running products, AFF_K elements per thread) -> top (one inversion per remaining element, binary Euclid,
+// Fp::inverse_fast) -> down, down (inverses of every level's elements) -> round (inverse of each pair's d, the affine
+// addition, result written).
+// (Tried and dropped, profiles/r2_fused_rounds.jsonl: carrying the next round's up pass inside the down pass. The products
+// are the same, only the re-read of the sums is saved, and holding two sums plus a second running product costs more in
+// registers than that: alt_bn128 G1 2.74 -> 3.42 ms, G2 7.5 -> 12.4 ms.)
 #pragma once
 #include "msm.cuh"
 
@@ -30,17 +37,18 @@ namespace b200
 namespace msm
 {
 
-constexpr int AFF_K = 16;                       // elements per thread at every level of the inversion tree
+constexpr int AFF_K = 16;                       // elements per thread at the upper levels of the inversion tree
+constexpr int AFF_KB = 4;                       // blocks per thread at level 0 (2^(rounds - r) pairs each in round r)
 constexpr uint32_t NULL_ENTRY = 0xffffffffu;    // padding of the entries array
 
 struct AffLevels {
-    uint32_t pairs, n1, n2, n3;
+    uint32_t nblk, n1, n2, n3; // blocks; threads of level 0 (= elements of level 1), of level 1, of level 2
 };
-HD AffLevels aff_levels(uint32_t total_entries, int round)
+HD AffLevels aff_levels(uint32_t total_entries, uint32_t rounds)
 {
     AffLevels lv;
-    lv.pairs = total_entries >> round;
-    lv.n1 = (lv.pairs + AFF_K - 1) / AFF_K;
+    lv.nblk = total_entries >> rounds;
+    lv.n1 = (lv.nblk + AFF_KB - 1) / AFF_KB;
     lv.n2 = (lv.n1 + AFF_K - 1) / AFF_K;
     lv.n3 = (lv.n2 + AFF_K - 1) / AFF_K;
     return lv;
@@ -81,6 +89,8 @@ template<class F> struct SrcEntries {
         idx = (v >> eshift) * row + (pt - skip);
         return true;
     }
+    // element e of block m: the sorted entries are contiguous per block (per = 2^rounds of them)
+    HD uint32_t index(uint32_t m, uint32_t e, uint32_t /*nblk*/, uint32_t per) const { return m * per + e; }
     HD Affine<F> load(uint32_t i) const
     {
         const uint32_t e = entries[i];
@@ -105,6 +115,9 @@ template<class F> struct SrcEntries {
 };
 template<class F> struct SrcPoints {
     const Affine<F> *pts;
+    // element e of block m: the rounds keep their arrays element-major (all blocks' element 0, then element 1, ...), so
+    // that the threads of a warp — consecutive blocks — touch consecutive addresses
+    HD uint32_t index(uint32_t m, uint32_t e, uint32_t nblk, uint32_t /*per*/) const { return e * nblk + m; }
     HD Affine<F> load(uint32_t i) const { return load_vec(pts + i); }
     HD F load_x(uint32_t i, bool &null) const
     {
@@ -141,42 +154,62 @@ template<class F> HD F pair_den(const Affine<F> &A, const Affine<F> &B, int &kin
 }
 
 // The same denominator from the x coordinates alone where that is enough (up pass).
-template<class F, class Src> HD F pair_den_x(const Src &src, uint32_t q)
+template<class F, class Src> HD F pair_den_x(const Src &src, uint32_t ia, uint32_t ib)
 {
     bool an, bn;
-    const F ax = src.load_x(2 * q, an);
-    const F bx = src.load_x(2 * q + 1, bn);
+    const F ax = src.load_x(ia, an);
+    const F bx = src.load_x(ib, bn);
     if (an || bn) {
         return F::one();
     }
     const F d = bx - ax;
     if (d.is_zero()) { // rare: needs the y coordinates
         int kind;
-        return pair_den(src.load(2 * q), src.load(2 * q + 1), kind);
+        return pair_den(src.load(ia), src.load(ib), kind);
     }
     return d;
 }
 
-// ---- level 0, up: thread t multiplies the denominators of its pairs, leaving every running product in P0 ----------
+// ---- level 0, up: thread t multiplies the denominators of its pairs of round r ---------------------------------------
+// Odd rounds ascending, even rounds descending (the down pass of a round walks the other way).
 // The denominators do not depend on the running product: they are fetched AFF_U pairs ahead of the chain of products so
 // that the gathers (round 1: two 32-byte x coordinates per pair out of a table far larger than L2) overlap it.
+// Pair i of block m lives at i * nblk + m in Pex and in the rounds' output arrays (element-major, see SrcPoints).
 constexpr int AFF_U = 4;
-template<class F, class Src> HD void aff_up0_body(uint32_t t, const AffLevels &lv, const Src &src, F *P0, F *T1)
+HD uint32_t aff_owned_blocks(uint32_t t, const AffLevels &lv)
 {
+    uint32_t nb = 0;
+    while (nb < (uint32_t)AFF_KB && nb * lv.n1 + t < lv.nblk) {
+        ++nb;
+    }
+    return nb;
+}
+template<class F, class Src>
+HD void aff_up_round_body(uint32_t t, const AffLevels &lv, uint32_t rounds, uint32_t r, const Src &src, F *Pex, F *T1)
+{
+    const uint32_t L = 1u << (rounds - r), per = 2 * L; // pairs, elements per block in this round
+    const bool asc = (r & 1u) != 0;
+    const uint32_t nb = aff_owned_blocks(t, lv);
     F acc = F::one();
-    for (int j0 = 0; j0 < AFF_K; j0 += AFF_U) {
-        F d[AFF_U];
+    bool started = false;
+    for (uint32_t jj = 0; jj < nb; ++jj) {
+        const uint32_t m = (asc ? jj : nb - 1 - jj) * lv.n1 + t;
+        for (uint32_t i0 = 0; i0 < L; i0 += AFF_U) {
+            F d[AFF_U];
 #pragma unroll
-        for (int u = 0; u < AFF_U; ++u) {
-            const uint32_t q = (uint32_t)(j0 + u) * lv.n1 + t;
-            d[u] = q < lv.pairs ? pair_den_x<F, Src>(src, q) : F::one();
-        }
+            for (int u = 0; u < AFF_U; ++u) {
+                const uint32_t i = asc ? i0 + u : L - 1 - (i0 + u);
+                d[u] = i0 + u < L ? pair_den_x<F, Src>(src, src.index(m, 2 * i, lv.nblk, per), src.index(m, 2 * i + 1, lv.nblk, per))
+                                  : F::one();
+            }
 #pragma unroll
-        for (int u = 0; u < AFF_U; ++u) {
-            const uint32_t q = (uint32_t)(j0 + u) * lv.n1 + t;
-            if (q < lv.pairs) {
-                acc = (j0 + u) ? acc * d[u] : d[u];
-                store_vec(P0 + q, acc);
+            for (int u = 0; u < AFF_U; ++u) {
+                if (i0 + u < L) {
+                    const uint32_t i = asc ? i0 + u : L - 1 - (i0 + u);
+                    store_vec(Pex + i * lv.nblk + m, acc);
+                    acc = started ? acc * d[u] : d[u];
+                    started = true;
+                }
             }
         }
     }
@@ -256,54 +289,27 @@ template<class F> HD Affine<F> pair_add(const Affine<F> &A, const Affine<F> &B, 
     return r;
 }
 
+// Round r of `rounds` for thread t: the down pass over its chain (Pex, inverse of its total in I1) with the affine additions.
 template<class F, class Src>
-HD void aff_down0_body(uint32_t t, const AffLevels &lv, const Src &src, const F *P0, const F *I1, Affine<F> *out)
+HD void aff_round_body(uint32_t t, const AffLevels &lv, uint32_t rounds, uint32_t r, const Src &src, const F *Pex, const F *I1,
+                       Affine<F> *out)
 {
+    const uint32_t L = 1u << (rounds - r), per = 2 * L; // pairs per block in this round (1 in the last)
+    const bool desc = (r & 1u) != 0;                    // odd rounds were multiplied up ascending: walk them descending
+    const uint32_t nb = aff_owned_blocks(t, lv);
     F inv = load_vec(I1 + t);
-    int j = AFF_K - 1;
-    while (j > 0 && (uint32_t)j * lv.n1 + t >= lv.pairs) {
-        --j;
-    }
-#if defined(B200_ACC_NO_PREFETCH)
-    for (; j >= 0; --j) {
-        const uint32_t q = (uint32_t)j * lv.n1 + t;
-        const Affine<F> A = src.load(2 * q), B = src.load(2 * q + 1);
-        int kind;
-        const F d = pair_den(A, B, kind);
-        F dinv = inv;
-        if (j) {
-            dinv = inv * load_vec(P0 + (q - lv.n1));
+    for (uint32_t jj = 0; jj < nb; ++jj) {
+        const uint32_t m = (desc ? nb - 1 - jj : jj) * lv.n1 + t;
+        for (uint32_t ii = 0; ii < L; ++ii) {
+            const uint32_t i = desc ? L - 1 - ii : ii;
+            const Affine<F> A = src.load(src.index(m, 2 * i, lv.nblk, per)), B = src.load(src.index(m, 2 * i + 1, lv.nblk, per));
+            int kind;
+            const F d = pair_den(A, B, kind);
+            const F dinv = inv * load_vec(Pex + i * lv.nblk + m);
             inv = inv * d;
+            store_vec(out + i * lv.nblk + m, pair_add(A, B, kind, dinv));
         }
-        store_vec(out + q, pair_add(A, B, kind, dinv));
     }
-#else
-    // the operands of pair j - 1 are fetched while pair j is added
-    uint32_t q = (uint32_t)j * lv.n1 + t;
-    Affine<F> nA = src.load(2 * q), nB = src.load(2 * q + 1);
-    F nP = j ? load_vec(P0 + (q - lv.n1)) : F::one();
-    for (; j >= 0; --j) {
-        q = (uint32_t)j * lv.n1 + t;
-        const Affine<F> A = nA, B = nB;
-        const F prev = nP;
-        if (j) {
-            const uint32_t qn = q - lv.n1;
-            nA = src.load(2 * qn);
-            nB = src.load(2 * qn + 1);
-            if (j > 1) {
-                nP = load_vec(P0 + (qn - lv.n1));
-            }
-        }
-        int kind;
-        const F d = pair_den(A, B, kind);
-        F dinv = inv;
-        if (j) {
-            dinv = inv * prev;
-            inv = inv * d;
-        }
-        store_vec(out + q, pair_add(A, B, kind, dinv));
-    }
-#endif
 }
 
 // ---- the XYZZ accumulation over the survivors (points instead of entries; (0, 0) skipped) ---------------------------
@@ -340,23 +346,25 @@ constexpr int AFF_THREADS = 128;
 #endif
 
 template<class F, class Src>
-__global__ void __launch_bounds__(AFF_THREADS, B200_AFF_MIN_BLOCKS) k_aff_up0(const uint32_t *total_entries, int round, Src src, F *P0, F *T1)
+__global__ void __launch_bounds__(AFF_THREADS, B200_AFF_MIN_BLOCKS) k_aff_up_round(const uint32_t *total_entries, uint32_t rounds,
+                                                                                   uint32_t r, Src src, F *Pex, F *T1)
 {
-    const AffLevels lv = aff_levels(*total_entries, round);
+    const AffLevels lv = aff_levels(*total_entries, rounds);
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t < lv.n1) {
-        aff_up0_body<F, Src>(t, lv, src, P0, T1);
+        aff_up_round_body<F, Src>(t, lv, rounds, r, src, Pex, T1);
     }
 }
 
 template<class F, class Src>
-__global__ void __launch_bounds__(AFF_THREADS, B200_AFF_MIN_BLOCKS) k_aff_down0(const uint32_t *total_entries, int round, Src src, const F *P0,
-                                                           const F *I1, Affine<F> *out)
+__global__ void __launch_bounds__(AFF_THREADS, B200_AFF_MIN_BLOCKS) k_aff_round(const uint32_t *total_entries, uint32_t rounds,
+                                                                                uint32_t r, Src src, const F *Pex, const F *I1,
+                                                                                Affine<F> *out)
 {
-    const AffLevels lv = aff_levels(*total_entries, round);
+    const AffLevels lv = aff_levels(*total_entries, rounds);
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t < lv.n1) {
-        aff_down0_body<F, Src>(t, lv, src, P0, I1, out);
+        aff_round_body<F, Src>(t, lv, rounds, r, src, Pex, I1, out);
     }
 }
 

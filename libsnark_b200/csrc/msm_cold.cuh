@@ -120,9 +120,9 @@ template<class F> int table_launch(size_t n, int c, int W, Affine<F> *table, con
 // ---- the upper levels of an affine round's inversion tree (msm_affine.cuh): few threads, chains of dependent products ----
 // level 1: elements = T1 (lv.n1 of them), threads = lv.n2; level 2: elements = T2 (lv.n2), threads = lv.n3.
 template<class F>
-__global__ void __launch_bounds__(128) k_aff_up(const uint32_t *total_entries, int round, int level, const F *E, F *Pre, F *T)
+__global__ void __launch_bounds__(128) k_aff_up(const uint32_t *total_entries, uint32_t rounds, int level, const F *E, F *Pre, F *T)
 {
-    const AffLevels lv = aff_levels(*total_entries, round);
+    const AffLevels lv = aff_levels(*total_entries, rounds);
     const uint32_t count = level == 1 ? lv.n1 : lv.n2, threads = level == 1 ? lv.n2 : lv.n3;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t < threads) {
@@ -130,9 +130,9 @@ __global__ void __launch_bounds__(128) k_aff_up(const uint32_t *total_entries, i
     }
 }
 template<class F>
-__global__ void __launch_bounds__(128) k_aff_down(const uint32_t *total_entries, int round, int level, F *E, const F *Pre, const F *Inv)
+__global__ void __launch_bounds__(128) k_aff_down(const uint32_t *total_entries, uint32_t rounds, int level, F *E, const F *Pre, const F *Inv)
 {
-    const AffLevels lv = aff_levels(*total_entries, round);
+    const AffLevels lv = aff_levels(*total_entries, rounds);
     const uint32_t count = level == 1 ? lv.n1 : lv.n2, threads = level == 1 ? lv.n2 : lv.n3;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t < threads) {
@@ -140,30 +140,31 @@ __global__ void __launch_bounds__(128) k_aff_down(const uint32_t *total_entries,
     }
 }
 // One inversion per element of the top level, 32 threads per CTA so that the few hundred warps spread over all SMs.
-template<class F> __global__ void __launch_bounds__(32) k_aff_top(const uint32_t *total_entries, int round, F *T3)
+template<class F> __global__ void __launch_bounds__(32) k_aff_top(const uint32_t *total_entries, uint32_t rounds, F *T3)
 {
-    const AffLevels lv = aff_levels(*total_entries, round);
+    const AffLevels lv = aff_levels(*total_entries, rounds);
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t < lv.n3) {
         store_vec(T3 + t, load_vec(T3 + t).inverse_fast());
     }
 }
 
+// Inverts the n1 thread totals in T1 in place (the tree is the same size in every round: one element per level-0 thread).
 template<class F>
-int affine_tree_launch(const uint32_t *total_entries, int round, uint32_t max_entries, F *T1, F *P1, F *T2, F *P2, F *T3,
+int affine_tree_launch(const uint32_t *total_entries, uint32_t rounds, uint32_t max_entries, F *T1, F *P1, F *T2, F *P2, F *T3,
                        cudaStream_t s)
 {
-    const AffLevels mx = aff_levels(max_entries, round);
+    const AffLevels mx = aff_levels(max_entries, rounds);
     const auto grid = [](uint32_t n, uint32_t b) { return (n + b - 1) / b; };
-    k_aff_up<F><<<grid(mx.n2, 128), 128, 0, s>>>(total_entries, round, 1, T1, P1, T2);
+    k_aff_up<F><<<grid(mx.n2, 128), 128, 0, s>>>(total_entries, rounds, 1, T1, P1, T2);
     B200_LAUNCH_CHECK();
-    k_aff_up<F><<<grid(mx.n3, 128), 128, 0, s>>>(total_entries, round, 2, T2, P2, T3);
+    k_aff_up<F><<<grid(mx.n3, 128), 128, 0, s>>>(total_entries, rounds, 2, T2, P2, T3);
     B200_LAUNCH_CHECK();
-    k_aff_top<F><<<grid(mx.n3, 32), 32, 0, s>>>(total_entries, round, T3);
+    k_aff_top<F><<<grid(mx.n3, 32), 32, 0, s>>>(total_entries, rounds, T3);
     B200_LAUNCH_CHECK();
-    k_aff_down<F><<<grid(mx.n3, 128), 128, 0, s>>>(total_entries, round, 2, T2, P2, T3);
+    k_aff_down<F><<<grid(mx.n3, 128), 128, 0, s>>>(total_entries, rounds, 2, T2, P2, T3);
     B200_LAUNCH_CHECK();
-    k_aff_down<F><<<grid(mx.n2, 128), 128, 0, s>>>(total_entries, round, 1, T1, P1, T2);
+    k_aff_down<F><<<grid(mx.n2, 128), 128, 0, s>>>(total_entries, rounds, 1, T1, P1, T2);
     B200_LAUNCH_CHECK();
     return B200_OK;
 }

@@ -9,7 +9,7 @@ namespace msm
 typedef group_traits<CURVE_BLS12_377, GROUP_G2>::F F_;
 template int reduce_launch<F_>(const Geometry &, const uint32_t *, const uint32_t *, const uint32_t *, XYZZ<F_> *,
                                XYZZ<F_> *, XYZZ<F_> *, cudaStream_t);
-template int affine_tree_launch<F_>(const uint32_t *, int, uint32_t, F_ *, F_ *, F_ *, F_ *, F_ *, cudaStream_t);
+template int affine_tree_launch<F_>(const uint32_t *, uint32_t, uint32_t, F_ *, F_ *, F_ *, F_ *, F_ *, cudaStream_t);
 template int table_launch<F_>(size_t, int, int, Affine<F_> *, const uint8_t *, uint32_t *);
 } // namespace msm
 } // namespace b200

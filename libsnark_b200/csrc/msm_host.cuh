@@ -33,7 +33,7 @@ int reduce_launch(const Geometry &g, const uint32_t *task_off, const uint32_t *m
 
 // Upper levels of an affine round's inversion tree; defined in msm_cold.cuh like reduce_launch.
 template<class F>
-int affine_tree_launch(const uint32_t *total_entries, int round, uint32_t max_entries, F *T1, F *P1, F *T2, F *P2, F *T3,
+int affine_tree_launch(const uint32_t *total_entries, uint32_t rounds, uint32_t max_entries, F *T1, F *P1, F *T2, F *P2, F *T3,
                        cudaStream_t s);
 
 // Table rows 1..W-1 of a base set (build_table_body); defined in msm_cold.cuh like reduce_launch.
@@ -259,8 +259,8 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
         ws.chunk_out.reserve(((size_t)reduce_windows * g.opw) * sizeof(XYZZ<F>))) {
         return B200_ERR_CUDA;
     }
-    const AffLevels amax = aff_levels((uint32_t)max_entries, 1);
-    if (R && (ws.aff_p0.reserve((size_t)amax.pairs * sizeof(F)) || ws.aff_t1.reserve((size_t)amax.n1 * sizeof(F)) ||
+    const AffLevels amax = aff_levels((uint32_t)max_entries, R);
+    if (R && (ws.aff_p0.reserve((max_entries / 2 + 1) * sizeof(F)) || ws.aff_t1.reserve((size_t)amax.n1 * sizeof(F)) ||
               ws.aff_p1.reserve((size_t)amax.n1 * sizeof(F)) || ws.aff_t2.reserve((size_t)amax.n2 * sizeof(F)) ||
               ws.aff_p2.reserve((size_t)amax.n2 * sizeof(F)) || ws.aff_t3.reserve((size_t)amax.n3 * sizeof(F)) ||
               ws.aff_a.reserve((max_entries / 2 + 1) * sizeof(Affine<F>)) ||
@@ -293,10 +293,10 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
     B200_CUDA_CHECK(cudaEventRecord(tm.ev[1], s));
     // 5: bucket accumulation (grid sized for the task upper bound; surplus CTAs exit at once)
     if (R) {
-        // affine rounds: round r halves every bucket; pairs of round r = (padded entries) >> r
+        // affine rounds (msm_affine.cuh): round r halves every bucket
         const uint32_t *total = offsets + g.NB;
         Affine<F> *buf[2] = {ws.aff_a.as<Affine<F>>(), ws.aff_b.as<Affine<F>>()};
-        F *P0 = ws.aff_p0.as<F>(), *T1 = ws.aff_t1.as<F>();
+        F *Pex = ws.aff_p0.as<F>(), *T1 = ws.aff_t1.as<F>();
         const Affine<F> *prev = nullptr;
         SrcEntries<F> esrc{entries, bases};
         if (shared) {
@@ -304,26 +304,24 @@ int msm_windows(const rt::BaseSet &bs, size_t first, size_t n, const void *scala
             esrc.row = (uint32_t)bs.n;
             esrc.skip = skip;
         }
+        const unsigned grid = grid_for(amax.n1, AFF_THREADS);
         for (uint32_t r = 1; r <= R; ++r) {
-            const AffLevels mx = aff_levels((uint32_t)max_entries, (int)r);
             Affine<F> *out = buf[(r - 1) & 1];
-            const unsigned grid = grid_for(mx.n1, AFF_THREADS);
+            const SrcPoints<F> psrc{prev};
             if (r == 1) {
-                k_aff_up0<F, SrcEntries<F>><<<grid, AFF_THREADS, 0, s>>>(total, (int)r, esrc, P0, T1);
+                k_aff_up_round<F, SrcEntries<F>><<<grid, AFF_THREADS, 0, s>>>(total, R, r, esrc, Pex, T1);
             } else {
-                const SrcPoints<F> src{prev};
-                k_aff_up0<F, SrcPoints<F>><<<grid, AFF_THREADS, 0, s>>>(total, (int)r, src, P0, T1);
+                k_aff_up_round<F, SrcPoints<F>><<<grid, AFF_THREADS, 0, s>>>(total, R, r, psrc, Pex, T1);
             }
             B200_LAUNCH_CHECK();
-            if (int rc = affine_tree_launch<F>(total, (int)r, (uint32_t)max_entries, T1, ws.aff_p1.as<F>(), ws.aff_t2.as<F>(),
+            if (int rc = affine_tree_launch<F>(total, R, (uint32_t)max_entries, T1, ws.aff_p1.as<F>(), ws.aff_t2.as<F>(),
                                                ws.aff_p2.as<F>(), ws.aff_t3.as<F>(), s)) {
                 return rc;
             }
             if (r == 1) {
-                k_aff_down0<F, SrcEntries<F>><<<grid, AFF_THREADS, 0, s>>>(total, (int)r, esrc, P0, T1, out);
+                k_aff_round<F, SrcEntries<F>><<<grid, AFF_THREADS, 0, s>>>(total, R, r, esrc, Pex, T1, out);
             } else {
-                const SrcPoints<F> src{prev};
-                k_aff_down0<F, SrcPoints<F>><<<grid, AFF_THREADS, 0, s>>>(total, (int)r, src, P0, T1, out);
+                k_aff_round<F, SrcPoints<F>><<<grid, AFF_THREADS, 0, s>>>(total, R, r, psrc, Pex, T1, out);
             }
             B200_LAUNCH_CHECK();
             prev = out;

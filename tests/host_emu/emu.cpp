@@ -229,18 +229,19 @@ static int msm_emulated(const void *bases_ref, size_t n, const void *scalars, in
         // the affine rounds of msm_affine.cuh, launch by launch, every "thread" in turn
         std::vector<Affine<F>> buf[2];
         const Affine<F> *prev = nullptr;
+        const AffLevels lv = aff_levels(off, R);
+        std::vector<F> Pex(off / 2 + 2, F::zero()), T1(lv.n1 + 1, F::zero());
+        std::vector<F> P1(lv.n1 + 1), T2(lv.n2 + 1), P2(lv.n2 + 1), T3(lv.n3 + 1);
+        const SrcEntries<F> se{entries.data(), bases.data()};
         for (uint32_t r = 1; r <= R; ++r) {
-            const AffLevels lv = aff_levels(off, (int)r);
-            std::vector<F> P0(lv.pairs + 1), T1(lv.n1 + 1), P1(lv.n1 + 1), T2(lv.n2 + 1), P2(lv.n2 + 1), T3(lv.n3 + 1);
             std::vector<Affine<F>> &o = buf[(r - 1) & 1];
-            o.assign(lv.pairs + 1, null_point<F>());
-            const SrcEntries<F> se{entries.data(), bases.data()};
+            o.assign((off >> r) + 1, null_point<F>());
             const SrcPoints<F> sp{prev};
             for (uint32_t t = 0; t < lv.n1; ++t) {
                 if (r == 1) {
-                    aff_up0_body<F, SrcEntries<F>>(t, lv, se, P0.data(), T1.data());
+                    aff_up_round_body<F, SrcEntries<F>>(t, lv, R, r, se, Pex.data(), T1.data());
                 } else {
-                    aff_up0_body<F, SrcPoints<F>>(t, lv, sp, P0.data(), T1.data());
+                    aff_up_round_body<F, SrcPoints<F>>(t, lv, R, r, sp, Pex.data(), T1.data());
                 }
             }
             for (uint32_t t = 0; t < lv.n2; ++t) {
@@ -260,9 +261,9 @@ static int msm_emulated(const void *bases_ref, size_t n, const void *scalars, in
             }
             for (uint32_t t = 0; t < lv.n1; ++t) {
                 if (r == 1) {
-                    aff_down0_body<F, SrcEntries<F>>(t, lv, se, P0.data(), T1.data(), o.data());
+                    aff_round_body<F, SrcEntries<F>>(t, lv, R, r, se, Pex.data(), T1.data(), o.data());
                 } else {
-                    aff_down0_body<F, SrcPoints<F>>(t, lv, sp, P0.data(), T1.data(), o.data());
+                    aff_round_body<F, SrcPoints<F>>(t, lv, R, r, sp, Pex.data(), T1.data(), o.data());
                 }
             }
             prev = o.data();
