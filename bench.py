@@ -1058,7 +1058,11 @@ def run_b200_arm(args):
             line["roofline"]["traffic"] = None
             nc = ncu_constants().get("accumulate_alt_bn128_g1", {})
             if nc:
+                # dram__bytes_read.sum + dram__bytes_write.sum of the accumulation stage's launches, from the committed
+                # ncu --set full capture of this command (not measured in this run)
+                line["roofline"]["traffic"] = nc.get("dram_bytes_per_launch")
                 line["roofline"]["traffic_ncu"] = nc.get("dram_bytes_per_launch")
+                line["roofline"]["traffic_what"] = nc.get("what")
                 line["roofline"]["pipe_utilisation_ncu"] = nc.get("fmaheavy_frac")
                 line["roofline"]["ncu_source"] = nc.get("source")
             line["roofline"]["peak_source"] = (

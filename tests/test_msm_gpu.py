@@ -189,7 +189,7 @@ def test_msm_over_precomputed_tables(ref, b200, curve, group):
         rb.free()
 
 
-@pytest.mark.parametrize("log_n", [16, 18])
+@pytest.mark.parametrize("log_n", [16, 18, 20])
 def test_msm_tables_large(ref, b200, log_n):
     n = 1 << log_n
     bases, scalars = _inputs(ref, "alt_bn128", refo.G1, n, seed=4)
