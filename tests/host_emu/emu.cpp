@@ -173,26 +173,44 @@ extern "C" int emu_signed_digits(int curve, const void *scalars, size_t n, int c
 // logic: histogram -> scan -> scatter -> tasks -> accumulate -> reduce -> fold).
 // table = true: the precomputed-table variant (b200_bases_precompute): build_table_body fills rows [2^(c w)] P,
 // every window scatters into the one bucket set, the reduction runs over a single window.
+// shared_skip >= 0: the sort is a SHARED one (rt::SharedSort, msm_host.cuh) over all n scalars with entries
+// point | window << eshift, consumed by a base set that lacks the first shared_skip points (bases_ref holds n - shared_skip
+// points, its table rows are that long): the prover's L query against the witness sort. Needs table and rounds > 0.
 template<class Fr, class F>
 static int msm_emulated(const void *bases_ref, size_t n, const void *scalars, int force_c, void *out, bool table = false,
-                        int rounds = 0)
+                        int rounds = 0, long shared_skip = -1)
 {
     using namespace msm;
+    const bool shared = shared_skip >= 0;
+    if (shared && (!table || rounds == 0 || (size_t)shared_skip >= n)) {
+        return -9;
+    }
+    const size_t nb = shared ? n - (size_t)shared_skip : n; // points of the consuming base set
     const int tc = force_c ? force_c : table_window_bits(n, Fr::params::BITS);
-    Geometry g = table ? make_table_geometry(n, Fr::params::BITS, tc, n) : make_geometry(n, Fr::params::BITS, force_c);
+    Geometry g = table ? make_table_geometry(n, Fr::params::BITS, tc, nb) : make_geometry(n, Fr::params::BITS, force_c);
     set_rounds(g, (uint32_t)rounds, (uint64_t)g.W * n);
+    if (shared) {
+        uint32_t k = 1;
+        while ((1ull << k) < n) {
+            ++k;
+        }
+        g.eshift = k;
+    }
     const uint32_t R = g.rounds;
     const Limbs<Fr::N> K = make_offset_constant<Fr::N>(g);
-    std::vector<Affine<F>> bases(table ? n * g.W : n);
+    std::vector<Affine<F>> bases(table ? nb * g.W : nb);
     std::vector<uint8_t> inf(n);
     uint32_t any = 0;
-    for (size_t i = 0; i < n; ++i) {
+    for (size_t i = 0; i < nb; ++i) {
         convert_base_body<F>(i, (const uint8_t *)bases_ref, sizeof(RefPoint<F>), bases.data(), inf.data(), &any);
+    }
+    if (shared && any) {
+        return -9; // a shared sort cannot zero the scalars of one set's infinity bases
     }
     if (table) {
         uint32_t fail = 0;
-        for (size_t i = 0; i < n; ++i) {
-            build_table_body<F>(i, n, g.c, g.W, bases.data(), any ? inf.data() : nullptr, &fail);
+        for (size_t i = 0; i < nb; ++i) {
+            build_table_body<F>(i, nb, g.c, g.W, bases.data(), any ? inf.data() : nullptr, &fail);
         }
         if (fail) {
             return -7;
@@ -232,7 +250,12 @@ static int msm_emulated(const void *bases_ref, size_t n, const void *scalars, in
         const AffLevels lv = aff_levels(off, R);
         std::vector<F> Pex(off / 2 + 2, F::zero()), T1(lv.n1 + 1, F::zero());
         std::vector<F> P1(lv.n1 + 1), T2(lv.n2 + 1), P2(lv.n2 + 1), T3(lv.n3 + 1);
-        const SrcEntries<F> se{entries.data(), bases.data()};
+        SrcEntries<F> se{entries.data(), bases.data()};
+        if (shared) {
+            se.eshift = g.eshift;
+            se.row = (uint32_t)nb;
+            se.skip = (uint32_t)shared_skip;
+        }
         for (uint32_t r = 1; r <= R; ++r) {
             std::vector<Affine<F>> &o = buf[(r - 1) & 1];
             o.assign((off >> r) + 1, null_point<F>());
@@ -294,6 +317,17 @@ static int msm_emulated(const void *bases_ref, size_t n, const void *scalars, in
     const RefPoint<F> r = host_fold<F>(windows.data(), g.W, g.c, 1);
     memcpy(out, &r, sizeof(r));
     return 0;
+}
+
+extern "C" int emu_msm_shared(int curve, int group, const void *bases, size_t n, const void *scalars, int c, int rounds, long skip,
+                              void *out)
+{
+    switch (curve * 4 + group) {
+    case 1: return msm_emulated<alt_bn128_fr, alt_bn128_fq>(bases, n, scalars, c, out, true, rounds, skip);
+    case 2: return msm_emulated<alt_bn128_fr, alt_bn128_fq2>(bases, n, scalars, c, out, true, rounds, skip);
+    case 5: return msm_emulated<bls12_377_fr, bls12_377_fq>(bases, n, scalars, c, out, true, rounds, skip);
+    }
+    return -100;
 }
 
 extern "C" int emu_msm_table(int curve, int group, const void *bases, size_t n, const void *scalars, int c, void *out)

@@ -44,6 +44,7 @@ def emu():
     L.emu_geometry.argtypes = [C.c_uint64, i, i, vp]
     L.emu_msm_affine.argtypes = [i, i, vp, sz, vp, i, i, i, vp]
     L.emu_inverse_fast.argtypes = [i, i, vp, vp, sz]
+    L.emu_msm_shared.argtypes = [i, i, vp, sz, vp, i, i, C.c_long, vp]
     return L
 
 
@@ -259,6 +260,28 @@ def test_emulated_msm_affine_rounds(emu, curve):
         want = P.msm(curve, 1, bases, sc)
         for rounds in (1, 3):
             assert np.array_equal(_emu_msm_affine(emu, curve, 1, bases, sc, 13, 1, rounds), want), ("table", rounds)
+
+
+def test_emulated_msm_over_a_shared_sort(emu):
+    """rt::SharedSort (msm_host.cuh): one sort of ALL the scalars with entries point | window << k, read by a base set with
+    its own table row length that lacks the first `skip` points (the prover's A / B queries: skip 0; its L query: skip =
+    num_inputs + 1). The result must be the MSM of that set with the scalars from `skip` on."""
+    from oracle import port
+    P = port.OraclePort()
+    g = np.load(os.path.join(GOLD, "msm.npz"))
+    for curve, gname, gid, npts in [("alt_bn128", "g1", 1, 96), ("alt_bn128", "g2", 2, 48), ("bls12_377", "g1", 1, 40)]:
+        k = f"rand.{curve}.{gname}"
+        bases, sc = np.ascontiguousarray(g[k + ".bases"][:npts]).copy(), np.ascontiguousarray(g[k + ".scalars"][:npts])
+        third = bases.shape[1] // 3
+        for i in np.nonzero(~bases[:, 2 * third:].any(axis=1))[0]:   # a shared sort takes no base at infinity (Z == 0)
+            bases[i] = bases[(i + 1) % npts]
+        for skip in (0, 11):
+            sub = np.ascontiguousarray(bases[skip:])
+            want = P.msm(curve, gid, sub, sc[skip:])
+            for rounds in (1, 3):
+                out = np.zeros(bases.shape[1], dtype=np.uint64)
+                assert emu.emu_msm_shared(CURVES[curve], gid, _p(sub), npts, _p(sc), 6, rounds, skip, _p(out)) == 0
+                assert np.array_equal(out, want), (k, skip, rounds)
 
 
 def test_emulated_msm_affine_exceptional_pairs(emu):
