@@ -152,6 +152,19 @@ int b200_ntt_dev_noalloc(int curve, int op, void *dev_data, size_t m, const void
 /* basic_radix2_domain::divide_by_Z_on_coset (basic_radix2_domain.tcc:117-126) with
  * coset generator Fr::multiplicative_generator. */
 int b200_divide_by_Z_on_coset(int curve, void *data, size_t m);
+/* The domain kinds behind the calls above and below, chosen from m the way libfqfft::get_evaluation_domain does
+ * (get_evaluation_domain.tcc:32-70), s = the field's 2-adicity FieldT::s:
+ *   m = 2^k, k <= s          basic_radix2_domain     (basic_radix2_domain.tcc)
+ *   m = 2^(s+1)              extended_radix2_domain  (extended_radix2_domain.tcc:21-236: the order-2^s subgroup and its
+ *                            coset by libff::coset_shift(); two size-2^s transforms plus element-wise steps)
+ *   m = 2^k + 2^r, k + 1 <= s   step_radix2_domain   (step_radix2_domain.tcc:20-276)
+ * b200_ntt*, b200_divide_by_Z_on_coset, the witness-map calls and the provers serve all three (the chain-by-chain
+ * calls b200_witness_chain_r1cs_dev / b200_witness_finish_dev serve basic domains only).
+ * b200_set_two_adicity mirrors libff's mutable static FieldT::s / FieldT::root_of_unity (e.g. alt_bn128_init.cpp:53-58):
+ * a host that lowers them gets the extended domain at 2^(s'+1); s = 0 restores the field's own value (28 / 47 / 46),
+ * with which only alt_bn128 reaches the extended domain at a size a GPU holds (2^29 elements). Roots of unity are always
+ * derived from the field's true root, as get_root_of_unity does from a consistently lowered pair. */
+int b200_set_two_adicity(int curve, int s);
 
 /* The NTT chain of libsnark::r1cs_to_qap_witness_map (r1cs_to_qap.tcc:252-330) for the
  * Groth16 case d1 = d2 = d3 = 0: in = the evaluations aA, aB, aC (m each, host);

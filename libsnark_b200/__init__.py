@@ -33,7 +33,7 @@ EXPORTS = [
     "b200_msm", "b200_bases_upload", "b200_bases_free", "b200_bases_size", "b200_msm_resident",
     "b200_msm_num_windows", "b200_msm_window_bits", "b200_msm_window_bytes", "b200_msm_resident_windows", "b200_msm_fold_windows",
     "b200_msm_filter_one_zero", "b200_kc_msm",
-    "b200_ntt", "b200_ntt_dev", "b200_divide_by_Z_on_coset", "b200_witness_map_h", "b200_witness_map_h_dev",
+    "b200_ntt", "b200_ntt_dev", "b200_divide_by_Z_on_coset", "b200_set_two_adicity", "b200_witness_map_h", "b200_witness_map_h_dev",
     "b200_msm_resident_windows_dev", "b200_timer_start", "b200_timer_stop", "b200_make_bases",
     "b200_imad_carry_peak", "b200_imad_peak", "b200_last_msm_timing", "b200_launch_count",
     "b200_r1cs_upload", "b200_r1cs_free", "b200_r1cs_evaluate", "b200_witness_map_r1cs_dev", "b200_gather_dev",
@@ -101,6 +101,7 @@ def lib():
         L.b200_ntt_dev.argtypes = [i, i, vp, sz, vp]
         L.b200_ntt_dev_noalloc.argtypes = [i, i, vp, sz, vp]
         L.b200_divide_by_Z_on_coset.argtypes = [i, vp, sz]
+        L.b200_set_two_adicity.argtypes = [i, i]
         L.b200_witness_map_h.argtypes = [i, vp, vp, vp, sz, vp]
         L.b200_witness_map_h_dev.argtypes = [i, vp, vp, vp, sz, vp]
         L.b200_imad_peak.argtypes = [i, C.POINTER(C.c_double), C.POINTER(C.c_double)]
@@ -363,9 +364,16 @@ def imad_peak(iters=4096):
 
 # ---- NTT -------------------------------------------------------------------------------------
 
+def set_two_adicity(curve, s):
+    """Mirrors libff's mutable FieldT::s (b200_set_two_adicity): with s' in force, 2^(s'+1) is the extended domain and
+    larger radix-2 sizes are refused. s = 0 restores the field's own 2-adicity."""
+    _check(lib().b200_set_two_adicity(_cid(curve), int(s)))
+
+
 class evaluation_domain:
-    """libfqfft::basic_radix2_domain<Fr> (m = 2^k) or step_radix2_domain<Fr> (m = 2^k + 2^r), the two domain kinds
-    get_evaluation_domain hands out for these fields; the library picks the kind from m."""
+    """libfqfft::basic_radix2_domain<Fr> (m = 2^k, k <= s), extended_radix2_domain<Fr> (m = 2^(s+1)) or
+    step_radix2_domain<Fr> (m = 2^k + 2^r): the domain kinds get_evaluation_domain hands out for these fields; the
+    library picks the kind from m."""
 
     def __init__(self, curve, m):
         self.curve, self.m = _cid(curve), int(m)
@@ -409,9 +417,9 @@ def domain_size_for(min_size):
 
 
 def get_evaluation_domain(curve, min_size):
-    """libfqfft::get_evaluation_domain (get_evaluation_domain.tcc:32-70): basic_radix2_domain for powers of two,
-    step_radix2_domain otherwise (the extended/geometric/arithmetic domains are not needed for these fields'
-    2-adicities at any practical size)."""
+    """libfqfft::get_evaluation_domain (get_evaluation_domain.tcc:32-70): basic_radix2_domain for powers of two up to
+    2^s, extended_radix2_domain for 2^(s+1), step_radix2_domain otherwise (the geometric / arithmetic sequence
+    domains are never reached for these fields: one of the radix-2 kinds accepts every size a GPU can hold)."""
     return evaluation_domain(curve, domain_size_for(min_size))
 
 

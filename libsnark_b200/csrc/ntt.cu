@@ -181,6 +181,17 @@ int log2_exact(size_t m)
 rt::DevBuf g_bufA, g_bufB, g_bufC, g_bufS, g_bufH;
 std::mutex g_mu;
 
+// The 2-adicity the domain factory works with: the field's own (FieldT::s), or the lower value a host set through
+// b200_set_two_adicity. libff keeps FieldT::s and FieldT::root_of_unity as mutable static parameters
+// (alt_bn128_init.cpp:53-58 and siblings), and get_evaluation_domain.tcc:37-58 reads them: sizes up to 2^s are
+// basic_radix2_domain, 2^(s+1) is extended_radix2_domain, 2^k + 2^r needs k + 1 <= s.
+template<class Fr> int &two_adicity()
+{
+    static int s = Fr::params::S;
+    return s;
+}
+
+template<class Fr> int ext_try_op(int op, Fr *data, Fr *tmp, Fr *out, size_t m, const void *g, bool *handled);
 struct StepShape;
 template<class Fr> bool step_shape(size_t m, StepShape *sh);
 template<class Fr> int step_op_dev(int op, Fr *a, Fr *tmp, const StepShape &sh, const void *g);
@@ -196,10 +207,17 @@ template<class Fr> int ntt_op_dev(int op, Fr *data, Fr *tmp, Fr *out, size_t m, 
             return rc;
         }
     }
-    if (lgn < 0 || lgn > Fr::params::S) {
+    if (lgn == two_adicity<Fr>() + 1) {
+        bool handled = false;
+        const int rc = ext_try_op<Fr>(op, data, tmp, out, m, g, &handled);
+        if (handled) {
+            return rc;
+        }
+    }
+    if (lgn < 0 || lgn > two_adicity<Fr>()) {
         // get_evaluation_domain / basic_radix2_domain ctor (basic_radix2_domain.tcc:25-52)
         return rt::set_error(B200_ERR_DOMAIN, "basic_radix2_domain: size %zu is not a power of two in [2, 2^%d]", m,
-                             Fr::params::S);
+                             two_adicity<Fr>());
     }
     const bool coset = (op == B200_COSET_FFT || op == B200_ICOSET_FFT);
     if (coset && !g) {
@@ -260,6 +278,8 @@ template<class Fr> int ntt_dev(int op, void *dev_data, size_t m, const void *g)
 
 template<class Fr> int step_divide_by_z_host(void *data, size_t m, bool *handled);
 template<class Fr> int step_witness_map_try(Fr *dA, Fr *dB, Fr *dC, size_t m, Fr *dH, bool *handled);
+template<class Fr> int ext_divide_by_z_host(void *data, size_t m);
+template<class Fr> int ext_witness_map_dev(Fr *dA, Fr *dB, Fr *dC, size_t m, Fr *dH);
 
 template<class Fr> int divide_by_z(void *data, size_t m)
 {
@@ -271,7 +291,10 @@ template<class Fr> int divide_by_z(void *data, size_t m)
             return rc;
         }
     }
-    if (lgn < 0 || lgn > Fr::params::S) {
+    if (lgn == two_adicity<Fr>() + 1) {
+        return ext_divide_by_z_host<Fr>(data, m);
+    }
+    if (lgn < 0 || lgn > two_adicity<Fr>()) {
         return rt::set_error(B200_ERR_DOMAIN, "basic_radix2_domain: bad size %zu", m);
     }
     Domain<Fr> *d = nullptr;
@@ -300,7 +323,7 @@ template<class Fr> int divide_by_z(void *data, size_t m)
 template<class Fr> int witness_domain(size_t m, Domain<Fr> **d)
 {
     const int lgn = log2_exact(m);
-    if (lgn < 0 || lgn > Fr::params::S) {
+    if (lgn < 0 || lgn > two_adicity<Fr>()) {
         return rt::set_error(B200_ERR_DOMAIN, "basic_radix2_domain: bad size %zu", m);
     }
     uint32_t gen[Fr::N];
@@ -359,6 +382,9 @@ template<class Fr> int witness_map_dev(Fr *dA, Fr *dB, Fr *dC, size_t m, Fr *dH)
             return rc;
         }
     }
+    if (log2_exact(m) == two_adicity<Fr>() + 1) {
+        return ext_witness_map_dev<Fr>(dA, dB, dC, m, dH);
+    }
     Domain<Fr> *d = nullptr;
     int rc = witness_domain<Fr>(m, &d);
     if (rc) {
@@ -412,7 +438,7 @@ template<class Fr> bool step_shape(size_t m, StepShape *sh)
     if (small & (small - 1)) {
         return false;
     }
-    if (lg + 1 > Fr::params::S) {
+    if (lg + 1 > two_adicity<Fr>()) {
         return false;
     }
     sh->m = m;
@@ -723,6 +749,264 @@ template<class Fr> int step_witness_map_try(Fr *dA, Fr *dB, Fr *dC, size_t m, Fr
     return step_witness_map_dev<Fr>(dA, dB, dC, sh, dH);
 }
 
+// ---- extended_radix2_domain -----------------------------------------------------------------------
+// m = 2 small with small = 2^s, s the 2-adicity in force (two_adicity): what get_evaluation_domain returns for
+// exactly that size (get_evaluation_domain.tcc:44-46; extended_radix2_domain.tcc:21-62). With the fields' own
+// parameters only alt_bn128 reaches it with a vector that fits a GPU (2^29 elements, 16 GiB).
+constexpr int EXT_LG_LO = 15;
+
+template<class Fr> struct ExtDomain {
+    int lg_small = 0;
+    size_t small = 0;
+    Domain<Fr> *dsmall = nullptr;
+    rt::DevBuf consts; // [0] shift^small  [1] (small (1 - shift^small))^-1  [2] Z0^-1  [3] Z1^-1
+    rt::DevBuf stab;   // two-level tables of shift^i and shift^-i, i < small
+    rt::DevBuf gtab;   // of g^i and g^-i, i < 2 small, for the generator in g_host
+    int lg_lo_s = 0, lg_lo_g = 0;
+    uint32_t g_host[Fr::N];
+    bool has_g = false;
+    const Fr *c(int i) { return consts.template as<Fr>() + i; }
+    // table t (0: b^i, 1: b^-i) of a buffer laid out lo0 | hi0 | lo1 | hi1 for `count` indices
+    static ntt::PowTable<Fr> table(rt::DevBuf &buf, int lg_lo, size_t count, int t)
+    {
+        const size_t nlo = (size_t)1 << lg_lo, nhi = count >> lg_lo;
+        const Fr *base = buf.template as<Fr>() + t * (nlo + nhi);
+        return ntt::PowTable<Fr>{base, base + nlo, lg_lo};
+    }
+};
+template<class Fr> std::map<int, std::unique_ptr<ExtDomain<Fr>>> &ext_domains()
+{
+    static std::map<int, std::unique_ptr<ExtDomain<Fr>>> m;
+    return m;
+}
+
+// lo[j] = b^j (j < 2^lg_lo), hi[k] = b^(k 2^lg_lo) (k < count >> lg_lo), for b and b^-1, computed on the host
+// (3 * 2^15 multiplications at most) and uploaded: lo0 | hi0 | lo1 | hi1
+template<class Fr> int ext_pow_tables(const Fr &b, size_t count, int lg_lo, rt::DevBuf &buf)
+{
+    const size_t nlo = (size_t)1 << lg_lo, nhi = count >> lg_lo;
+    std::vector<Fr> h(2 * (nlo + nhi));
+    const Fr bases[2] = {b, b.inverse()};
+    for (int t = 0; t < 2; ++t) {
+        Fr *lo = h.data() + t * (nlo + nhi), *hi = lo + nlo;
+        lo[0] = Fr::one();
+        for (size_t j = 1; j < nlo; ++j) {
+            lo[j] = lo[j - 1] * bases[t];
+        }
+        const Fr step = lo[nlo - 1] * bases[t]; // b^(2^lg_lo)
+        hi[0] = Fr::one();
+        for (size_t k = 1; k < nhi; ++k) {
+            hi[k] = hi[k - 1] * step;
+        }
+    }
+    if (buf.reserve(h.size() * sizeof(Fr))) {
+        return B200_ERR_CUDA;
+    }
+    B200_CUDA_CHECK(cudaMemcpyAsync(buf.p, h.data(), h.size() * sizeof(Fr), cudaMemcpyHostToDevice, rt::stream()));
+    B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
+    return B200_OK;
+}
+
+template<class Fr> int get_ext_domain(int lg_small, ExtDomain<Fr> **out)
+{
+    auto &mp = ext_domains<Fr>();
+    auto it = mp.find(lg_small);
+    if (it == mp.end()) {
+        std::unique_ptr<ExtDomain<Fr>> d(new ExtDomain<Fr>());
+        d->lg_small = lg_small;
+        d->small = (size_t)1 << lg_small;
+        int rc = get_domain<Fr>(lg_small, nullptr, &d->dsmall);
+        if (rc) {
+            return rc;
+        }
+        Fr g;
+        for (int i = 0; i < Fr::N; ++i) {
+            g.v[i] = Fr::params::generator(i); // FieldT::multiplicative_generator
+        }
+        const Fr one = Fr::one();
+        const Fr shift = g.sqr(); // libff::coset_shift, field_utils.tcc:152-155
+        const Fr ssm = host_pow(shift, d->small), gsm = host_pow(g, d->small);
+        Fr small_f = Fr::zero();
+        small_f.v[lg_small >> 5] = 1u << (lg_small & 31);
+        Fr hc[4];
+        hc[0] = ssm;
+        hc[1] = (small_f.to_mont() * (one - ssm)).inverse();                       // sconst, :107
+        hc[2] = ((gsm - one) * (gsm - ssm)).inverse();                             // Z0^-1, :224-228
+        hc[3] = ((gsm * ssm - one) * (gsm * ssm - ssm)).inverse();                 // Z1^-1, :225-229
+        if (d->consts.reserve(sizeof(hc))) {
+            return B200_ERR_CUDA;
+        }
+        B200_CUDA_CHECK(cudaMemcpyAsync(d->consts.p, hc, sizeof(hc), cudaMemcpyHostToDevice, rt::stream()));
+        B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));
+        d->lg_lo_s = lg_small < EXT_LG_LO ? lg_small : EXT_LG_LO;
+        if ((rc = ext_pow_tables<Fr>(shift, d->small, d->lg_lo_s, d->stab))) {
+            return rc;
+        }
+        it = mp.emplace(lg_small, std::move(d)).first;
+    }
+    *out = it->second.get();
+    return B200_OK;
+}
+
+template<class Fr> int ext_coset_tables(ExtDomain<Fr> &d, const uint32_t *g)
+{
+    if (d.has_g && memcmp(g, d.g_host, sizeof(d.g_host)) == 0) {
+        return B200_OK;
+    }
+    Fr gv;
+    memcpy(gv.v, g, sizeof(gv.v));
+    if (gv.is_zero()) {
+        return rt::set_error(B200_ERR_ARG, "coset generator is zero");
+    }
+    d.lg_lo_g = d.lg_small + 1 < EXT_LG_LO ? d.lg_small + 1 : EXT_LG_LO;
+    if (int rc = ext_pow_tables<Fr>(gv, 2 * d.small, d.lg_lo_g, d.gtab)) {
+        return rc;
+    }
+    memcpy(d.g_host, g, sizeof(d.g_host));
+    d.has_g = true;
+    return B200_OK;
+}
+
+// extended_radix2_domain::FFT (:64-91) in place on a (2 small elements); tmp: >= small elements
+template<class Fr> int ext_fft(ExtDomain<Fr> &d, Fr *a, Fr *tmp)
+{
+    cudaStream_t s = rt::stream();
+    ntt::k_ext_fft_pre<Fr><<<grid_for(d.small, 256), 256, 0, s>>>(d.small, a, ExtDomain<Fr>::table(d.stab, d.lg_lo_s, d.small, 0), d.c(0));
+    B200_LAUNCH_CHECK();
+    if (int rc = run_transform<Fr>(*d.dsmall, 0, a, tmp, a, nullptr, nullptr, nullptr)) {
+        return rc;
+    }
+    return run_transform<Fr>(*d.dsmall, 0, a + d.small, tmp, a + d.small, nullptr, nullptr, nullptr);
+}
+
+// extended_radix2_domain::iFFT (:93-120) in place
+template<class Fr> int ext_ifft(ExtDomain<Fr> &d, Fr *a, Fr *tmp)
+{
+    int rc;
+    if ((rc = run_transform<Fr>(*d.dsmall, 1, a, tmp, a, nullptr, nullptr, nullptr)) ||
+        (rc = run_transform<Fr>(*d.dsmall, 1, a + d.small, tmp, a + d.small, nullptr, nullptr, nullptr))) {
+        return rc;
+    }
+    ntt::k_ext_ifft_post<Fr><<<grid_for(d.small, 256), 256, 0, rt::stream()>>>(
+        d.small, a, ExtDomain<Fr>::table(d.stab, d.lg_lo_s, d.small, 1), d.c(0));
+    B200_LAUNCH_CHECK();
+    return B200_OK;
+}
+
+template<class Fr> int ext_op_dev(int op, Fr *a, Fr *tmp, int lg_small, const void *g)
+{
+    ExtDomain<Fr> *d = nullptr;
+    int rc = get_ext_domain<Fr>(lg_small, &d);
+    if (rc) {
+        return rc;
+    }
+    const bool coset = (op == B200_COSET_FFT || op == B200_ICOSET_FFT);
+    if (coset) {
+        if (!g) {
+            return rt::set_error(B200_ERR_ARG, "coset transform needs a generator");
+        }
+        if ((rc = ext_coset_tables<Fr>(*d, static_cast<const uint32_t *>(g)))) {
+            return rc;
+        }
+    }
+    const uint64_t m = 2 * d->small;
+    cudaStream_t s = rt::stream();
+    switch (op) {
+    case B200_FFT: return ext_fft<Fr>(*d, a, tmp);
+    case B200_IFFT: return ext_ifft<Fr>(*d, a, tmp);
+    case B200_COSET_FFT: // _multiply_by_coset then FFT (:122-127)
+        ntt::k_mul_pow<Fr><<<grid_for(m, 256), 256, 0, s>>>(m, a, ExtDomain<Fr>::table(d->gtab, d->lg_lo_g, m, 0));
+        B200_LAUNCH_CHECK();
+        return ext_fft<Fr>(*d, a, tmp);
+    case B200_ICOSET_FFT: // iFFT then _multiply_by_coset(g^-1) (:129-134)
+        if ((rc = ext_ifft<Fr>(*d, a, tmp))) {
+            return rc;
+        }
+        ntt::k_mul_pow<Fr><<<grid_for(m, 256), 256, 0, s>>>(m, a, ExtDomain<Fr>::table(d->gtab, d->lg_lo_g, m, 1));
+        B200_LAUNCH_CHECK();
+        return B200_OK;
+    }
+    return rt::set_error(B200_ERR_ARG, "unknown NTT op %d", op);
+}
+
+template<class Fr> int ext_try_op(int op, Fr *data, Fr *tmp, Fr *out, size_t m, const void *g, bool *handled)
+{
+    const int lgn = log2_exact(m);
+    *handled = lgn >= 2 && lgn == two_adicity<Fr>() + 1; // small = 1 has no radix-2 transform to run
+    if (!*handled) {
+        return B200_OK;
+    }
+    if (out != data) {
+        return rt::set_error(B200_ERR_ARG, "extended domain transforms run in place");
+    }
+    return ext_op_dev<Fr>(op, data, tmp, lgn - 1, g);
+}
+
+template<class Fr> int ext_divide_by_z_dev(ExtDomain<Fr> &d, Fr *p)
+{
+    ntt::k_ext_divz<Fr><<<grid_for(2 * d.small, 256), 256, 0, rt::stream()>>>(d.small, p, d.c(2));
+    B200_LAUNCH_CHECK();
+    return B200_OK;
+}
+
+template<class Fr> int ext_divide_by_z_host(void *data, size_t m)
+{
+    ExtDomain<Fr> *d = nullptr;
+    int rc = get_ext_domain<Fr>(log2_exact(m) - 1, &d);
+    if (rc) {
+        return rc;
+    }
+    const size_t bytes = m * sizeof(Fr);
+    if (g_bufA.reserve(bytes)) {
+        return B200_ERR_CUDA;
+    }
+    cudaStream_t s = rt::stream();
+    B200_CUDA_CHECK(cudaMemcpyAsync(g_bufA.p, data, bytes, cudaMemcpyHostToDevice, s));
+    if ((rc = ext_divide_by_z_dev<Fr>(*d, g_bufA.as<Fr>()))) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaMemcpyAsync(data, g_bufA.p, bytes, cudaMemcpyDeviceToHost, s));
+    B200_CUDA_CHECK(cudaStreamSynchronize(s));
+    return B200_OK;
+}
+
+// r1cs_to_qap_witness_map (r1cs_to_qap.tcc:252-330, d1 = d2 = d3 = 0) over an extended domain
+template<class Fr> int ext_witness_map_dev(Fr *dA, Fr *dB, Fr *dC, size_t m, Fr *dH)
+{
+    const int lg_small = log2_exact(m) - 1;
+    if (lg_small < 1) {
+        return rt::set_error(B200_ERR_DOMAIN, "extended_radix2_domain: bad size %zu", m);
+    }
+    ExtDomain<Fr> *d = nullptr;
+    int rc = get_ext_domain<Fr>(lg_small, &d);
+    if (rc) {
+        return rc;
+    }
+    uint32_t gen[Fr::N];
+    for (int i = 0; i < Fr::N; ++i) {
+        gen[i] = Fr::params::generator(i);
+    }
+    if (g_bufS.reserve(d->small * sizeof(Fr))) {
+        return B200_ERR_CUDA;
+    }
+    Fr *S = g_bufS.as<Fr>();
+    Fr *vecs[3] = {dA, dB, dC};
+    for (int v = 0; v < 3; ++v) {
+        if ((rc = ext_op_dev<Fr>(B200_IFFT, vecs[v], S, lg_small, nullptr)) ||
+            (rc = ext_op_dev<Fr>(B200_COSET_FFT, vecs[v], S, lg_small, gen))) {
+            return rc;
+        }
+    }
+    cudaStream_t s = rt::stream();
+    ntt::k_pointwise_abc<Fr><<<grid_for(m, 256), 256, 0, s>>>(m, dA, dB, dC, dH);
+    B200_LAUNCH_CHECK();
+    if ((rc = ext_divide_by_z_dev<Fr>(*d, dH)) || (rc = ext_op_dev<Fr>(B200_ICOSET_FFT, dH, S, lg_small, gen))) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaMemsetAsync(dH + m, 0, sizeof(Fr), s));
+    return B200_OK;
+}
+
 // ---- R1CS on the device -------------------------------------------------------------------------
 struct R1csSet {
     int curve = -1;
@@ -911,6 +1195,15 @@ template<class Fr> int witness_finish_dev(void *dA, const void *dB, const void *
 
 } // namespace
 
+template<class Fr> int set_two_adicity(int s)
+{
+    if (s < 0 || s > Fr::params::S) {
+        return rt::set_error(B200_ERR_ARG, "two-adicity %d outside [1, %d] (0 restores the field's own)", s, Fr::params::S);
+    }
+    two_adicity<Fr>() = s ? s : Fr::params::S;
+    return B200_OK;
+}
+
 extern "C" {
 
 int b200_ntt(int curve, int op, void *data, size_t m, const void *g)
@@ -935,6 +1228,12 @@ int b200_ntt_dev(int curve, int op, void *dev_data, size_t m, const void *g)
     }
     std::lock_guard<std::mutex> lk(g_mu);
     DISPATCH_FR(curve, ntt_dev<Fr>(op, dev_data, m, g));
+}
+
+int b200_set_two_adicity(int curve, int s)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    DISPATCH_FR(curve, set_two_adicity<Fr>(s));
 }
 
 int b200_divide_by_Z_on_coset(int curve, void *data, size_t m)
@@ -1172,9 +1471,9 @@ template<class Fr> __global__ void k_noalloc_consts(int lgn, Fr g, Fr *g_slot, F
 template<class Fr> int ntt_dev_noalloc(NoallocState &st, int curve, int op, void *dev_data, size_t m, const void *g)
 {
     const int lgn = log2_exact(m);
-    if (lgn < 0 || lgn > Fr::params::S) {
+    if (lgn < 0 || lgn > two_adicity<Fr>()) {
         return rt::set_error(B200_ERR_DOMAIN, "basic_radix2_domain: size %zu is not a power of two in [2, 2^%d]", m,
-                             Fr::params::S);
+                             two_adicity<Fr>());
     }
     if (lgn > NOALLOC_MAX_LOG) {
         return rt::set_error(B200_ERR_ARG,

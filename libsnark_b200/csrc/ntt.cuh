@@ -445,6 +445,59 @@ template<class Fr> __global__ void k_pointwise_abc(uint64_t m, const Fr *a, cons
     }
 }
 
+// ---- extended_radix2_domain (libfqfft/evaluation_domain/domains/extended_radix2_domain.tcc) --------
+// Domain of size m = 2 small, small = 2^s the largest radix-2 subgroup of the field: the subgroup H of order
+// small and its coset shift * H, shift = coset_shift() = multiplicative_generator^2. A transform is two radix-2
+// transforms of size small plus the element-wise steps below. Powers b^i of a fixed element come from a
+// two-level table: b^i = lo[i mod 2^lg_lo] * hi[i >> lg_lo] (both L2-resident; two multiplications per element
+// instead of a table as long as the vector, which at 2^29 elements would be 16 GiB).
+template<class Fr> struct PowTable {
+    const Fr *lo, *hi;
+    int lg_lo;
+    __device__ __forceinline__ Fr at(uint64_t i) const
+    {
+        return gload(lo + (i & ((1ull << lg_lo) - 1))) * gload(hi + (i >> lg_lo));
+    }
+};
+// FFT, :64-91: a0[i] = a[i] + a[i+small], a1[i] = shift^i (a[i] + shift^small a[i+small]); a0 | a1 in place
+template<class Fr> __global__ void k_ext_fft_pre(uint64_t small, Fr *a, PowTable<Fr> spow, const Fr *ssm)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < small) {
+        const Fr x = gload(a + i), y = gload(a + i + small);
+        gstore(a + i, x + y);
+        gstore(a + i + small, spow.at(i) * (x + gload(ssm) * y));
+    }
+}
+// iFFT, :93-120, on the unnormalised inverse transforms a0 | a1: a[i] = sconst (shift^-i a1[i] - shift^small a0[i]),
+// a[i+small] = sconst (a0[i] - shift^-i a1[i]); cst = { shift^small, (small (1 - shift^small))^-1 }
+template<class Fr> __global__ void k_ext_ifft_post(uint64_t small, Fr *a, PowTable<Fr> sinv, const Fr *cst)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < small) {
+        const Fr a0 = gload(a + i), t = sinv.at(i) * gload(a + i + small);
+        const Fr sc = gload(cst + 1);
+        gstore(a + i, sc * (t - gload(cst) * a0));
+        gstore(a + i + small, sc * (a0 - t));
+    }
+}
+// _multiply_by_coset (basic_radix2_domain_aux.tcc): a[i] *= g^i
+template<class Fr> __global__ void k_mul_pow(uint64_t n, Fr *a, PowTable<Fr> gpow)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        gstore(a + i, gload(a + i) * gpow.at(i));
+    }
+}
+// divide_by_Z_on_coset, :216-236: one factor per half
+template<class Fr> __global__ void k_ext_divz(uint64_t small, Fr *p, const Fr *zinv /* Z0^-1, Z1^-1 */)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < 2 * small) {
+        gstore(p + i, gload(p + i) * gload(zinv + (i >= small)));
+    }
+}
+
 constexpr uint32_t R1CS_LONG_ROW = 64;
 constexpr int R1CS_LONG_THREADS = 256;
 constexpr uint32_t R1CS_LONG_SEG = 2048; // terms per CTA of the long-row kernel

@@ -14,7 +14,8 @@
 //   libff::multi_exp_filter_one_zero<...same...>                       (multiexp.hpp:83-88)
 //   libsnark::kc_multi_exp_with_mixed_addition<G2, G1, Fr, BDLO12_signed, special>
 //                                       (libsnark/knowledge_commitment/kc_multiexp.hpp:32-44)
-//   libfqfft::basic_radix2_domain<Fr> and step_radix2_domain<Fr>::{FFT, iFFT, cosetFFT, icosetFFT, divide_by_Z_on_coset}
+//   libfqfft::basic_radix2_domain<Fr>, extended_radix2_domain<Fr> and step_radix2_domain<Fr>::{FFT, iFFT, cosetFFT,
+//   icosetFFT, divide_by_Z_on_coset}
 //                                       (libfqfft/evaluation_domain/domains/basic_radix2_domain.hpp)
 // for G in {G1, G2} of alt_bn128, bls12_377 and bw6_761. Every other instantiation (other methods,
 // base forms, curves, domains) keeps the reference's CPU template. There is no CPU fallback inside
@@ -49,6 +50,7 @@
 #include <libff/algebra/scalar_multiplication/multiexp.hpp>
 #include <libff/common/profiling.hpp>
 #include <libfqfft/evaluation_domain/domains/basic_radix2_domain.hpp>
+#include <libfqfft/evaluation_domain/domains/extended_radix2_domain.hpp>
 #include <libfqfft/evaluation_domain/domains/step_radix2_domain.hpp>
 #include <libfqfft/evaluation_domain/get_evaluation_domain.hpp>
 #include <libfqfft/tools/exceptions.hpp>
@@ -848,12 +850,14 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
             b200_divide_by_Z_on_coset(libsnark_b200::curve_of<FR>::curve, P.data(), this->m),                          \
             "b200_divide_by_Z_on_coset");                                                                              \
     }
-// basic_radix2_domain (m = 2^k) and step_radix2_domain (m = 2^k + 2^r, step_radix2_domain.tcc:65-276): the
-// library tells them apart by m.
+// basic_radix2_domain (m = 2^k, k <= s), extended_radix2_domain (m = 2^(s+1), extended_radix2_domain.tcc:64-236) and
+// step_radix2_domain (m = 2^k + 2^r, step_radix2_domain.tcc:65-276): the library tells them apart by m. A host that
+// lowers FieldT::s / FieldT::root_of_unity must tell the library (b200_set_two_adicity).
 #define B200_OVERLAY_NTT(FR)                                                                                           \
     namespace libfqfft                                                                                                 \
     {                                                                                                                  \
     B200_OVERLAY_DOMAIN(basic_radix2_domain, FR)                                                                       \
+    B200_OVERLAY_DOMAIN(extended_radix2_domain, FR)                                                                    \
     B200_OVERLAY_DOMAIN(step_radix2_domain, FR)                                                                        \
     }
 

@@ -721,11 +721,27 @@ static size_t bitreverse(size_t n, size_t l) /* libff/common/utils.cpp:59-67 */
     }
     return r;
 }
+/* FieldT::s as the domain factory sees it: libff keeps s and root_of_unity as mutable static parameters; a host that
+ * lowers them consistently (port_set_two_adicity) gets extended_radix2_domain at 2^(s+1). The root of a given order is
+ * the same either way, so it is always derived from the field's own pair. */
+static int g_two_adicity[3]; /* 0 = the field's own */
+static size_t two_adicity(void)
+{
+    for (int c = 0; c < 3; ++c)
+        if (g_f == &curve_table[c].fr && g_two_adicity[c]) return (size_t)g_two_adicity[c];
+    return (size_t)g_f->s;
+}
+API int port_set_two_adicity(int curve, int s)
+{
+    if (curve < 0 || curve > 2 || s < 0 || s > curve_table[curve].fr.s) return -1;
+    g_two_adicity[curve] = s;
+    return 0;
+}
 /* field_utils.tcc:190-206: root_of_unity^(2^(s - log n)) */
 static int get_root_of_unity(fp_t *w, size_t n)
 {
     const size_t logn = ff_log2(n);
-    if (n != ((size_t)1 << logn) || logn > (size_t)g_f->s) return -1;
+    if (n != ((size_t)1 << logn) || logn > two_adicity()) return -1;
     fp_zero(w);
     memcpy(w->v, g_f->root_of_unity, 8 * g_f->n);
     for (size_t i = g_f->s; i > logn; --i) fp_sqr(w, w);
@@ -826,7 +842,7 @@ static int step_shape(size_t m, size_t *big, size_t *small) /* valid_for_size, :
     *big = (size_t)1 << (l - 1);
     *small = m - *big;
     if (*small & (*small - 1)) return -2;
-    if (l > (size_t)g_f->s) return -2;
+    if (l > two_adicity()) return -2;
     return 0;
 }
 static int step_inplace(fp_t *a, size_t m, int op, const fp_t *g)
@@ -952,11 +968,104 @@ static int step_inplace(fp_t *a, size_t m, int op, const fp_t *g)
     }
     return -1;
 }
+/* ---- extended_radix2_domain (libfqfft/evaluation_domain/domains/extended_radix2_domain.tcc): m = 2 small,
+ * small = 2^s — the order-2^s subgroup and its coset by shift = coset_shift() = multiplicative_generator^2
+ * (field_utils.tcc:152-155). Same op codes as fft_inplace. */
+static int ext_inplace(fp_t *a, size_t m, int op, const fp_t *g)
+{
+    const size_t logm = ff_log2(m);
+    if (m <= 1 || m != ((size_t)1 << logm) || logm != two_adicity() + 1) return -2; /* ctor, :47-62 */
+    const size_t small = m / 2;
+    fp_t omega, shift, gen, ssm, one, t, u;
+    if (get_root_of_unity(&omega, small)) return -2;
+    fp_zero(&gen);
+    memcpy(gen.v, g_f->generator, 8 * g_f->n);
+    fp_sqr(&shift, &gen);
+    fp_pow_u64(&ssm, &shift, small);
+    fp_one(&one);
+    switch (op) {
+    case 0: { /* FFT, :64-91 */
+        fp_t *a0 = (fp_t *)malloc(small * sizeof(fp_t)), *a1 = (fp_t *)malloc(small * sizeof(fp_t));
+        fp_t shift_i;
+        fp_one(&shift_i);
+        for (size_t i = 0; i < small; ++i) {
+            fp_add(&a0[i], &a[i], &a[small + i]);
+            fp_mul(&t, &ssm, &a[small + i]);
+            fp_add(&t, &a[i], &t);
+            fp_mul(&a1[i], &shift_i, &t);
+            fp_mul(&shift_i, &shift_i, &shift);
+        }
+        serial_radix2_fft(a0, small, &omega);
+        serial_radix2_fft(a1, small, &omega);
+        memcpy(a, a0, small * sizeof(fp_t));
+        memcpy(a + small, a1, small * sizeof(fp_t));
+        free(a0);
+        free(a1);
+        return 0;
+    }
+    case 1: { /* iFFT, :93-120 */
+        fp_t *a0 = (fp_t *)malloc(small * sizeof(fp_t)), *a1 = (fp_t *)malloc(small * sizeof(fp_t));
+        memcpy(a0, a, small * sizeof(fp_t));
+        memcpy(a1, a + small, small * sizeof(fp_t));
+        fp_t omega_inv, sconst, shift_inv, shift_inv_i;
+        fp_inv(&omega_inv, &omega);
+        serial_radix2_fft(a0, small, &omega_inv);
+        serial_radix2_fft(a1, small, &omega_inv);
+        fp_from_u64(&t, small);
+        fp_sub(&u, &one, &ssm);
+        fp_mul(&t, &t, &u);
+        fp_inv(&sconst, &t);
+        fp_inv(&shift_inv, &shift);
+        fp_one(&shift_inv_i);
+        for (size_t i = 0; i < small; ++i) {
+            fp_mul(&u, &shift_inv_i, &a1[i]);  /* shift^-i a1[i] */
+            fp_mul(&t, &ssm, &a0[i]);
+            fp_sub(&t, &u, &t);
+            fp_mul(&a[i], &sconst, &t);
+            fp_sub(&t, &a0[i], &u);
+            fp_mul(&a[i + small], &sconst, &t);
+            fp_mul(&shift_inv_i, &shift_inv_i, &shift_inv);
+        }
+        free(a0);
+        free(a1);
+        return 0;
+    }
+    case 2: /* cosetFFT, :122-127 */
+        multiply_by_coset(a, m, g);
+        return ext_inplace(a, m, 0, g);
+    case 3: /* icosetFFT, :129-134 */
+        ext_inplace(a, m, 1, g);
+        fp_inv(&t, g);
+        multiply_by_coset(a, m, &t);
+        return 0;
+    case 4: { /* divide_by_Z_on_coset, :216-236, coset = multiplicative_generator */
+        fp_t csm, z0, z1, v;
+        fp_pow_u64(&csm, &gen, small);
+        fp_sub(&t, &csm, &one);
+        fp_sub(&u, &csm, &ssm);
+        fp_mul(&z0, &t, &u);
+        fp_mul(&v, &csm, &ssm);
+        fp_sub(&t, &v, &one);
+        fp_sub(&u, &v, &ssm);
+        fp_mul(&z1, &t, &u);
+        fp_inv(&z0, &z0);
+        fp_inv(&z1, &z1);
+        for (size_t i = 0; i < small; ++i) {
+            fp_mul(&a[i], &a[i], &z0);
+            fp_mul(&a[i + small], &a[i + small], &z1);
+        }
+        return 0;
+    }
+    }
+    return -1;
+}
 /* get_evaluation_domain (get_evaluation_domain.tcc:32-70) for the sizes these fields meet: basic radix-2 for powers
- * of two, step radix-2 for 2^k + 2^r. */
+ * of two up to 2^s, extended radix-2 for 2^(s+1), step radix-2 for 2^k + 2^r. */
 static int domain_inplace(fp_t *a, size_t m, int op, const fp_t *g)
 {
-    return (m & (m - 1)) ? step_inplace(a, m, op, g) : fft_inplace(a, m, op, g);
+    if (m & (m - 1)) return step_inplace(a, m, op, g);
+    if (m > 1 && ff_log2(m) == two_adicity() + 1) return ext_inplace(a, m, op, g);
+    return fft_inplace(a, m, op, g);
 }
 
 static fp_t *load_frs(const uint64_t *src, size_t m)

@@ -134,6 +134,10 @@ class OraclePort:
             raise RuntimeError(f"port_fft rc={rc}")
         return a
 
+    def set_two_adicity(self, curve, s):
+        """FieldT::s as the domain factory sees it (0 = the field's own): 2^(s+1) becomes the extended domain."""
+        assert self.lib.port_set_two_adicity(_cid(curve), int(s)) == 0
+
     def witness_map_h(self, curve, aA, aB, aC):
         aA, aB, aC = (np.ascontiguousarray(x, dtype=np.uint64) for x in (aA, aB, aC))
         m = aA.shape[0]

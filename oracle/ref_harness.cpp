@@ -438,6 +438,44 @@ template<typename ppT> struct H {
         return 0;
     }
 
+    // The same through the factory's domain (extended_radix2_domain / step_radix2_domain elements), the
+    // way libfqfft's own evaluation_domain_test.cpp checks every domain kind's FFT.
+    static int poly_eval_at_factory_domain(const void *coeffs, size_t m, const uint64_t *idx, size_t k, void *out)
+    {
+        const FrT *c = static_cast<const FrT *>(coeffs);
+        std::vector<FrT> cv(c, c + m);
+        FrT *o = static_cast<FrT *>(out);
+        try {
+            std::shared_ptr<libfqfft::evaluation_domain<FrT>> dom = libfqfft::get_evaluation_domain<FrT>(m);
+            for (size_t i = 0; i < k; ++i) {
+                o[i] = libfqfft::evaluate_polynomial(m, cv, dom->get_domain_element(idx[i]));
+            }
+        } catch (const libfqfft::DomainSizeException &) {
+            return -2;
+        }
+        return 0;
+    }
+
+    // libff keeps FieldT::s and FieldT::root_of_unity as mutable static parameters (set by init_*_params).
+    // Lowering them consistently (root -> root^(2^(s0 - s))) makes the UNMODIFIED get_evaluation_domain hand
+    // out extended_radix2_domain at 2^(s+1), a size a test can hold; s = 0 restores the field's own pair.
+    static int set_two_adicity(int s)
+    {
+        static const size_t s0 = FrT::s;
+        static const FrT root0 = FrT::root_of_unity;
+        if (s < 0 || (size_t)s > s0) {
+            return -1;
+        }
+        const size_t k = s ? (size_t)s : s0;
+        FrT r = root0;
+        for (size_t i = s0; i > k; --i) {
+            r = r.squared();
+        }
+        FrT::s = k;
+        FrT::root_of_unity = r;
+        return 0;
+    }
+
     // ---------------- Groth16 -------------------------------------------
 
     static groth16_fixture<ppT> *setup(size_t num_constraints, size_t num_inputs, int real_keys)
@@ -1098,6 +1136,23 @@ static int poly_eval_(int curve, const void *coeffs, size_t m, const uint64_t *i
 API int ref_poly_eval_at_domain(int curve, const void *coeffs, size_t m, const uint64_t *idx, size_t k, void *out)
 {
     return poly_eval_(curve, coeffs, m, idx, k, out);
+}
+
+static int poly_eval_factory_(int curve, const void *coeffs, size_t m, const uint64_t *idx, size_t k, void *out)
+{
+    DISPATCH(curve, HH::poly_eval_at_factory_domain(coeffs, m, idx, k, out));
+}
+API int ref_poly_eval_at_factory_domain(int curve, const void *coeffs, size_t m, const uint64_t *idx, size_t k, void *out)
+{
+    return poly_eval_factory_(curve, coeffs, m, idx, k, out);
+}
+static int set_two_adicity_(int curve, int s)
+{
+    DISPATCH(curve, HH::set_two_adicity(s));
+}
+API int ref_set_two_adicity(int curve, int s)
+{
+    return set_two_adicity_(curve, s);
 }
 
 struct fixture_handle {

@@ -73,6 +73,8 @@ class RefOracle:
                                  C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p, C.c_void_p]
         L.ref_fft.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]
         L.ref_poly_eval_at_domain.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.ref_poly_eval_at_factory_domain.argtypes = L.ref_poly_eval_at_domain.argtypes
+        L.ref_set_two_adicity.argtypes = [C.c_int, C.c_int]
         L.ref_field_consts.argtypes = [C.c_int, C.c_int, C.c_void_p]
         L.ref_curve_consts.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ref_info.argtypes = [C.c_int, C.c_void_p]
@@ -246,6 +248,20 @@ class RefOracle:
         assert self.lib.ref_poly_eval_at_domain(self.info(curve)["id"], _p(coeffs), coeffs.shape[0], _p(idx),
                                                 idx.shape[0], _p(out)) == 0
         return out
+
+    def poly_eval_at_factory_domain(self, curve, coeffs, idx):
+        """evaluate_polynomial at get_evaluation_domain(m)->get_domain_element(idx[i]) (any domain kind)."""
+        coeffs = np.ascontiguousarray(coeffs, dtype=np.uint64)
+        idx = np.ascontiguousarray(idx, dtype=np.uint64)
+        out = np.zeros((idx.shape[0], coeffs.shape[1]), dtype=np.uint64)
+        assert self.lib.ref_poly_eval_at_factory_domain(self.info(curve)["id"], _p(coeffs), coeffs.shape[0], _p(idx),
+                                                        idx.shape[0], _p(out)) == 0
+        return out
+
+    def set_two_adicity(self, curve, s):
+        """Lowers FieldT::s / FieldT::root_of_unity of the reference consistently (0 restores them): the unmodified
+        get_evaluation_domain then returns extended_radix2_domain at 2^(s+1)."""
+        assert self.lib.ref_set_two_adicity(self.info(curve)["id"], int(s)) == 0
 
     # ---- Groth16 -------------------------------------------------------------
     def groth16_setup(self, curve, num_constraints, num_inputs, real_keys=True):

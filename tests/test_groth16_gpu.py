@@ -175,6 +175,107 @@ def test_prover_on_step_domain(ref, b200, curve, nc, ni):
         fx.close()
 
 
+@pytest.mark.parametrize("curve,s,ni,real_keys", [("alt_bn128", 9, 10, True), ("alt_bn128", 13, 3, False),
+                                                  ("bls12_377", 8, 5, True), ("bw6_761", 6, 2, True)])
+def test_prover_on_extended_domain(ref, b200, curve, s, ni, real_keys):
+    """A circuit whose domain is extended_radix2_domain (2^(s+1) with FieldT::s = s on both sides): the witness map
+    (every H coefficient) and the whole proof — one GPU and cut over three ranks — match the reference bit for bit; with
+    keys from the reference's generator (run under the same setting) the reference verifier accepts."""
+    m = 1 << (s + 1)
+    ref.set_two_adicity(curve, s)
+    b200.set_two_adicity(curve, s)
+    try:
+        fx = ref.groth16_setup(curve, m - ni - 3, ni, real_keys=real_keys)   # 2^(s+1) - 2 rounds up to the extended size
+        try:
+            assert fx.sizes["m"] == m == b200.domain_size_for(m - 2)
+            pk, cs = _device_pk(b200, fx)
+            try:
+                assert np.array_equal(cs.witness_map_h(fx.full_assignment(), m), fx.witness_map()[0])
+                rs = ref.field_random(curve, refo.FR, 0xE87, 2)
+                want, _ = fx.prove(rs[0], rs[1])
+                got, _ = pk.prove(fx.primary_input, fx.auxiliary_input, rs[0], rs[1])
+                assert np.array_equal(got, want)
+                if real_keys:
+                    assert fx.verify(got) == 1
+            finally:
+                pk.free()
+                cs.free()
+            keys, cs = _shard_keys(b200, fx, 3)
+            try:
+                blobs = []
+                for k in keys:
+                    buf = b200.DeviceBuffer(k.blob_bytes)
+                    k.prove_shard(fx.primary_input, fx.auxiliary_input, buf.ptr)
+                    blobs.append(buf.download((k.blob_bytes,), dtype=np.uint8))
+                    buf.free()
+                assert np.array_equal(keys[0].assemble(rs[0], rs[1], np.concatenate(blobs)), want)
+            finally:
+                for k in keys:
+                    k.free()
+                cs.free()
+        finally:
+            fx.close()
+    finally:
+        ref.set_two_adicity(curve, 0)
+        b200.set_two_adicity(curve, 0)
+
+
+@pytest.mark.parametrize("curve,s,nc", [("alt_bn128", 6, 120), ("bls12_377", 5, 59), ("bw6_761", 4, 27)])
+def test_prover_on_extended_domain_golden(b200, curve, s, nc):
+    """The same on the committed fixtures (tests/golden/extended.npz) — no reference code in the loop."""
+    from test_oracle_cpu import groth16_fixture
+    key, r1cs, w, r, s_, proof = groth16_fixture(curve, nc, "extended.npz")
+    ni = r1cs["ni"]
+    g2l = key["beta_g2"].shape[0]
+    assert r1cs["m"] == 1 << (s + 1)
+    b200.set_two_adicity(curve, s)
+    try:
+        cs = b200.R1CS(curve, r1cs["nc"], ni, r1cs["nv"], r1cs["row_ptr"], r1cs["col"], r1cs["val"])
+        pk = b200.Groth16ProvingKey(curve, key["alpha_g1"], key["beta_g1"], key["beta_g2"], key["delta_g1"], key["delta_g2"],
+                                    key["A"], np.ascontiguousarray(key["B_values"][:, :g2l]),
+                                    np.ascontiguousarray(key["B_values"][:, g2l:]), key["B_indices"].astype(np.uint32),
+                                    key["H"], key["L"], cs, r1cs["m"])
+        try:
+            got, _ = pk.prove(w[1:1 + ni], w[1 + ni:], r, s_)
+            assert np.array_equal(got, proof)
+        finally:
+            pk.free()
+            cs.free()
+    finally:
+        b200.set_two_adicity(curve, 0)
+
+
+def test_overlay_extended_domain(ref, overlay, b200):
+    """The overlay's extended_radix2_domain specialisations: the reference's factory hands out the extended domain (its
+    FieldT::s lowered inside the overlay build too) and the member functions resolve to the CUDA library."""
+    curve, s = "alt_bn128", 11
+    m = 1 << (s + 1)
+    a = ref.field_random(curve, refo.FR, 77, m)
+    g = ref.field_consts(curve, refo.FR)["generator"]
+    for lib in (ref, overlay):
+        lib.set_two_adicity(curve, s)
+    b200.set_two_adicity(curve, s)
+    try:
+        for op in (refo.FFT, refo.IFFT, refo.COSET_FFT, refo.ICOSET_FFT, refo.DIV_Z_COSET):
+            assert np.array_equal(overlay.fft(curve, op, a, g, via_factory=True), ref.fft(curve, op, a, g, via_factory=True))
+        fx = ref.groth16_setup(curve, m - 9, 7, real_keys=True)
+        try:
+            assert fx.sizes["m"] == m
+            rs = ref.field_random(curve, refo.FR, 0xE88, 2)
+            want, _ = fx.prove(rs[0], rs[1])
+            got, _ = fx.prove(rs[0], rs[1], via=overlay)
+            assert np.array_equal(got, want)
+            got, _ = fx.prove_fused(rs[0], rs[1], via=overlay)
+            assert np.array_equal(got, want)
+            assert fx.verify(got) == 1
+        finally:
+            fx.close()
+    finally:
+        for lib in (ref, overlay):
+            lib.set_two_adicity(curve, 0)
+        b200.set_two_adicity(curve, 0)
+
+
 def test_overlay_step_domain(ref, overlay):
     """The overlay's step_radix2_domain specialisations: operators through the reference's own factory, and the
     reference prover (operators overlaid, and the one-call device prover) on a circuit whose size is not a power of two."""
@@ -288,6 +389,31 @@ def test_chain_parallel_witness_map(ref, b200, curve, log_m):
                 blobs.append(buf.download((k.blob_bytes,), dtype=np.uint8))
                 buf.free()
             assert np.array_equal(keys[0].assemble(rs[0], rs[1], np.concatenate(blobs)), want)
+            # the flow DistributedProver runs since round 2: the witness-only MSMs in the background (msm_begin), rank 0
+            # alone finishes H and hands every other rank the slice its H MSM reads (h_copy out / in), msm_end joins; the
+            # r, s-only part of the assembly is started ahead on host threads (assemble_prepare)
+            keys[0].assemble_prepare(rs[0], rs[1])
+            for c, a in zip(chains, saved):
+                c.upload(a)
+            hbuf = b200.DeviceBuffer(m * fr)
+            bufs = [b200.DeviceBuffer(k.blob_bytes) for k in keys]
+            mask = b200.MSM_A | b200.MSM_B_G2 | b200.MSM_B_G1 | b200.MSM_L
+            keys[0].msm_begin(mask, bufs[0].ptr)
+            keys[0].h(chains[0].ptr, chains[1].ptr, chains[2].ptr)
+            keys[0].h_copy(hbuf.ptr, 0, m - 1, 0)
+            keys[0].msm(b200.MSM_H, bufs[0].ptr)
+            keys[0].msm_end()
+            for k, buf in zip(keys[1:], bufs[1:]):
+                k.msm_begin(mask, buf.ptr)
+                f, cnt = k.ranges[2]
+                if cnt:
+                    k.h_copy(hbuf.ptr + f * fr, f, cnt, 1)
+                k.msm(b200.MSM_H, buf.ptr)
+                k.msm_end()
+            blobs = [buf.download((k.blob_bytes,), dtype=np.uint8) for k, buf in zip(keys, bufs)]
+            assert np.array_equal(keys[0].assemble(rs[0], rs[1], np.concatenate(blobs)), want)
+            for buf in bufs + [hbuf]:
+                buf.free()
             # and H itself: chains -> finish == the reference's coefficients_for_H
             for c, a in zip(chains, saved):
                 c.upload(a)

@@ -112,6 +112,62 @@ def test_step_radix2_domain_matches_reference(ref, b200, curve, m):
     assert np.array_equal(dom.iFFT(dom.FFT(a)), a)
 
 
+@pytest.mark.parametrize("curve,s", [("alt_bn128", 1), ("alt_bn128", 3), ("alt_bn128", 10), ("alt_bn128", 15), ("alt_bn128", 17),
+                                     ("bls12_377", 9), ("bls12_377", 16), ("bw6_761", 7), ("bw6_761", 12)])
+def test_extended_radix2_domain_matches_reference(ref, b200, curve, s):
+    """extended_radix2_domain (m = 2^(s+1): what get_evaluation_domain returns one step above the field's 2-adicity,
+    get_evaluation_domain.tcc:44-46): all four transforms and divide_by_Z_on_coset, bit-exact
+    (extended_radix2_domain.tcc:64-236). The unmodified reference reaches that domain at a testable size with
+    FieldT::s / FieldT::root_of_unity lowered (RefOracle.set_two_adicity); b200_set_two_adicity mirrors the setting."""
+    m = 1 << (s + 1)
+    a = ref.field_random(curve, refo.FR, 300 + s, m)
+    g = _gen(ref, curve)
+    g2 = ref.field_random(curve, refo.FR, 17, 1)[0]                 # a coset generator other than the field's
+    ref.set_two_adicity(curve, s)
+    b200.set_two_adicity(curve, s)
+    try:
+        dom = b200.get_evaluation_domain(curve, m)
+        for name, op in [("FFT", refo.FFT), ("iFFT", refo.IFFT), ("cosetFFT", refo.COSET_FFT), ("icosetFFT", refo.ICOSET_FFT)]:
+            for gg in ([g, g2] if "coset" in name else [g]):
+                got = getattr(dom, name)(a, gg) if "coset" in name else getattr(dom, name)(a)
+                assert np.array_equal(got, ref.fft(curve, op, a, gg, via_factory=True)), (name, s)
+        assert np.array_equal(dom.divide_by_Z_on_coset(a), ref.fft(curve, refo.DIV_Z_COSET, a, g, via_factory=True))
+        assert np.array_equal(dom.iFFT(dom.FFT(a)), a)
+        if s <= 10:   # libfqfft's own check of a domain kind: FFT == the polynomial at every get_domain_element(i)
+            assert np.array_equal(dom.FFT(a), ref.poly_eval_at_factory_domain(curve, a, np.arange(m)))
+        # one size up no radix-2 kind is valid any more; one size down is the plain radix-2 domain
+        with pytest.raises(b200.DomainSizeException):
+            b200.get_evaluation_domain(curve, 2 * m).FFT(np.concatenate([a, a]))
+        assert np.array_equal(b200.get_evaluation_domain(curve, m // 2).FFT(a[: m // 2]),
+                              ref.fft(curve, refo.FFT, a[: m // 2], g, via_factory=True))
+    finally:
+        ref.set_two_adicity(curve, 0)
+        b200.set_two_adicity(curve, 0)
+    # the field's own parameters again: 2^(s+1) is a basic domain
+    assert np.array_equal(b200.get_evaluation_domain(curve, m).FFT(a), ref.fft(curve, refo.FFT, a, g))
+
+
+@pytest.mark.parametrize("curve", ["alt_bn128", "bls12_377", "bw6_761"])
+def test_extended_domain_golden_fixtures(b200, curve):
+    """The device extended_radix2_domain against the committed vectors the unmodified reference produced with FieldT::s
+    lowered (tests/golden/extended.npz, tools/gen_golden.py:gen_extended) — no reference code in the loop."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "extended.npz"))
+    coset = g[f"{curve}.generator"]
+    for s in [1, 2, 5, 8]:
+        b200.set_two_adicity(curve, s)
+        try:
+            a = g[f"{curve}.s{s}.in"]
+            dom = b200.get_evaluation_domain(curve, 1 << (s + 1))
+            assert np.array_equal(dom.FFT(a), g[f"{curve}.s{s}.fft"])
+            assert np.array_equal(dom.iFFT(a), g[f"{curve}.s{s}.ifft"])
+            assert np.array_equal(dom.cosetFFT(a, coset), g[f"{curve}.s{s}.coset_fft"])
+            assert np.array_equal(dom.icosetFFT(a, coset), g[f"{curve}.s{s}.icoset_fft"])
+            assert np.array_equal(dom.divide_by_Z_on_coset(a), g[f"{curve}.s{s}.div_z"])
+        finally:
+            b200.set_two_adicity(curve, 0)
+
+
 def test_factory_rounding(b200):
     """get_evaluation_domain.tcc:37-58: 2^k stays, 2^k + 2^r stays, anything else rounds its small part up."""
     assert b200.domain_size_for(1 << 20) == 1 << 20

@@ -196,6 +196,44 @@ def test_step_radix2_domain_golden(P, curve):
         assert got.shape[0] == 1152 + 1 and np.array_equal(got, g["witness.H"])
 
 
+EXTENDED_CASES = [("alt_bn128", 6, 120), ("bls12_377", 5, 59), ("bw6_761", 4, 27)]   # curve, two-adicity, constraints
+
+
+@pytest.mark.parametrize("curve", CURVES)
+def test_extended_radix2_domain_golden(P, curve):
+    """extended_radix2_domain (m = 2^(s+1); extended_radix2_domain.tcc:21-236) restated in the C oracle == the vectors the
+    unmodified reference produced through get_evaluation_domain with FieldT::s lowered (tools/gen_golden.py:gen_extended,
+    where the FFT was also checked against evaluate_polynomial at every domain element)."""
+    g = np.load(os.path.join(GOLD, "extended.npz"))
+    ops = {"fft": 0, "ifft": 1, "coset_fft": 2, "icoset_fft": 3, "div_z": 4}
+    for s in [1, 2, 5, 8]:
+        P.set_two_adicity(curve, s)
+        try:
+            a = g[f"{curve}.s{s}.in"]
+            assert a.shape[0] == 1 << (s + 1)
+            for name, op in ops.items():
+                assert np.array_equal(P.fft(curve, op, a, g[f"{curve}.generator"]), g[f"{curve}.s{s}.{name}"]), (s, name)
+            assert np.array_equal(P.fft(curve, 1, P.fft(curve, 0, a)), a)
+            assert np.array_equal(P.fft(curve, 3, P.fft(curve, 2, a)), a)
+            with pytest.raises(RuntimeError):   # 2^(s+2): no radix-2 kind accepts it (DomainSizeException)
+                P.fft(curve, 0, np.concatenate([a, a]))
+        finally:
+            P.set_two_adicity(curve, 0)
+
+
+@pytest.mark.parametrize("curve,s,nc", EXTENDED_CASES)
+def test_whole_proof_on_extended_domain_golden(P, curve, s, nc):
+    """The restated prover over an extended domain == the reference prover's proof (reference generator, prover and
+    verifier run with FieldT::s = s; the proof verified there)."""
+    key, r1cs, w, r, s_, proof = groth16_fixture(curve, nc, "extended.npz")
+    assert r1cs["m"] == 1 << (s + 1)
+    P.set_two_adicity(curve, s)
+    try:
+        assert np.array_equal(P.groth16_prove(curve, key, r1cs, w, r, s_), proof)
+    finally:
+        P.set_two_adicity(curve, 0)
+
+
 def test_r1cs_evaluation_golden(P):
     """The sparse evaluation <a_i, w>, <b_i, w>, <c_i, w> with the input-consistency rows (r1cs_to_qap.tcc:236-248,
     :293-296; linear_combination::evaluate, variable.tcc:288-299) restated over the CSR the device path uploads ==
@@ -211,10 +249,10 @@ def test_r1cs_evaluation_golden(P):
 GROTH16_CASES = [("alt_bn128", 117), ("alt_bn128", 90), ("bls12_377", 59), ("bw6_761", 27)]
 
 
-def groth16_fixture(curve, nc):
+def groth16_fixture(curve, nc, file="groth16.npz"):
     """(key, r1cs, w, r, s, proof) of one case of tests/golden/groth16.npz (keys from the reference's generator, proof
-    from the reference's prover with r, s fixed; tools/gen_golden.py:gen_groth16)."""
-    g = np.load(os.path.join(GOLD, "groth16.npz"))
+    from the reference's prover with r, s fixed; tools/gen_golden.py:gen_groth16) or of extended.npz (gen_extended)."""
+    g = np.load(os.path.join(GOLD, file))
     k = f"{curve}.nc{nc}"
     n_c, ni, nv, m = [int(x) for x in g[k + ".sizes"]]
     key = {name: g[f"{k}.{name}"] for name in ["alpha_g1", "beta_g1", "beta_g2", "delta_g1", "delta_g2", "A", "B_values",
