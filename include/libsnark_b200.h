@@ -165,6 +165,13 @@ int b200_divide_by_Z_on_coset(int curve, void *data, size_t m);
  * with which only alt_bn128 reaches the extended domain at a size a GPU holds (2^29 elements). Roots of unity are always
  * derived from the field's true root, as get_root_of_unity does from a consistently lowered pair. */
 int b200_set_two_adicity(int curve, int s);
+/* The kind that serves a domain of exactly m elements (valid_for_size of the three classes in the factory's order),
+ * B200_DOMAIN_NONE when none does. */
+#define B200_DOMAIN_NONE 0
+#define B200_DOMAIN_BASIC 1
+#define B200_DOMAIN_EXTENDED 2
+#define B200_DOMAIN_STEP 3
+int b200_domain_kind(int curve, size_t m);
 
 /* The NTT chain of libsnark::r1cs_to_qap_witness_map (r1cs_to_qap.tcc:252-330) for the
  * Groth16 case d1 = d2 = d3 = 0: in = the evaluations aA, aB, aC (m each, host);

@@ -33,7 +33,7 @@ EXPORTS = [
     "b200_msm", "b200_bases_upload", "b200_bases_free", "b200_bases_size", "b200_msm_resident",
     "b200_msm_num_windows", "b200_msm_window_bits", "b200_msm_window_bytes", "b200_msm_resident_windows", "b200_msm_fold_windows",
     "b200_msm_filter_one_zero", "b200_kc_msm",
-    "b200_ntt", "b200_ntt_dev", "b200_divide_by_Z_on_coset", "b200_set_two_adicity", "b200_witness_map_h", "b200_witness_map_h_dev",
+    "b200_ntt", "b200_ntt_dev", "b200_divide_by_Z_on_coset", "b200_set_two_adicity", "b200_domain_kind", "b200_witness_map_h", "b200_witness_map_h_dev",
     "b200_msm_resident_windows_dev", "b200_timer_start", "b200_timer_stop", "b200_make_bases",
     "b200_imad_carry_peak", "b200_imad_peak", "b200_last_msm_timing", "b200_launch_count",
     "b200_r1cs_upload", "b200_r1cs_free", "b200_r1cs_evaluate", "b200_witness_map_r1cs_dev", "b200_gather_dev",
@@ -102,6 +102,7 @@ def lib():
         L.b200_ntt_dev_noalloc.argtypes = [i, i, vp, sz, vp]
         L.b200_divide_by_Z_on_coset.argtypes = [i, vp, sz]
         L.b200_set_two_adicity.argtypes = [i, i]
+        L.b200_domain_kind.argtypes = [i, sz]
         L.b200_witness_map_h.argtypes = [i, vp, vp, vp, sz, vp]
         L.b200_witness_map_h_dev.argtypes = [i, vp, vp, vp, sz, vp]
         L.b200_imad_peak.argtypes = [i, C.POINTER(C.c_double), C.POINTER(C.c_double)]
@@ -368,6 +369,14 @@ def set_two_adicity(curve, s):
     """Mirrors libff's mutable FieldT::s (b200_set_two_adicity): with s' in force, 2^(s'+1) is the extended domain and
     larger radix-2 sizes are refused. s = 0 restores the field's own 2-adicity."""
     _check(lib().b200_set_two_adicity(_cid(curve), int(s)))
+
+
+DOMAIN_NONE, DOMAIN_BASIC, DOMAIN_EXTENDED, DOMAIN_STEP = 0, 1, 2, 3
+
+
+def domain_kind(curve, m):
+    """Which radix-2 domain class serves exactly m elements (b200_domain_kind); DOMAIN_NONE when none does."""
+    return lib().b200_domain_kind(_cid(curve), int(m))
 
 
 class evaluation_domain:
@@ -670,10 +679,10 @@ class DistributedProver:
         import torch.distributed as dist
         self.torch, self.dist, self.pk = torch, dist, shard
         self.dev = torch.device("cuda", torch.cuda.current_device())
-        pow2 = shard.m & (shard.m - 1) == 0
-        self.chain_parallel = (shard.world >= 3 and pow2) if chain_parallel is None else bool(chain_parallel)
-        if self.chain_parallel and not (shard.world >= 3 and pow2):
-            raise B200Error(ERR_ARG, "chain-parallel witness map needs >= 3 ranks and a power-of-two domain")
+        basic = domain_kind(shard.curve, shard.m) == DOMAIN_BASIC   # the chain-by-chain calls serve basic_radix2_domain only
+        self.chain_parallel = (shard.world >= 3 and basic) if chain_parallel is None else bool(chain_parallel)
+        if self.chain_parallel and not (shard.world >= 3 and basic):
+            raise B200Error(ERR_ARG, "chain-parallel witness map needs >= 3 ranks and a basic radix-2 domain")
         self.blob = torch.zeros(shard.blob_bytes, dtype=torch.uint8, device=self.dev)
         self.gathered = torch.zeros(shard.world * shard.blob_bytes, dtype=torch.uint8, device=self.dev)
         # rank 0 holds all three chain results, ranks 1 and 2 their own; hbuf: H coefficients (whole on rank 0, a slice elsewhere)

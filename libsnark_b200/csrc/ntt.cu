@@ -1204,7 +1204,32 @@ template<class Fr> int set_two_adicity(int s)
     return B200_OK;
 }
 
+// get_evaluation_domain.tcc:37-58 for the sizes it accepts as they are: which radix-2 kind serves m
+template<class Fr> int domain_kind(size_t m)
+{
+    const int lgn = log2_exact(m);
+    if (lgn >= 1 && lgn <= two_adicity<Fr>()) {
+        return B200_DOMAIN_BASIC;
+    }
+    if (lgn >= 2 && lgn == two_adicity<Fr>() + 1) {
+        return B200_DOMAIN_EXTENDED;
+    }
+    StepShape sh;
+    return step_shape<Fr>(m, &sh) ? B200_DOMAIN_STEP : B200_DOMAIN_NONE;
+}
+
 extern "C" {
+
+int b200_domain_kind(int curve, size_t m)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    switch (curve) {
+    case B200_ALT_BN128: return domain_kind<alt_bn128_fr>(m);
+    case B200_BLS12_377: return domain_kind<bls12_377_fr>(m);
+    case B200_BW6_761: return domain_kind<bw6_761_fr>(m);
+    }
+    return B200_DOMAIN_NONE;
+}
 
 int b200_ntt(int curve, int op, void *data, size_t m, const void *g)
 {

@@ -50,6 +50,31 @@ def test_sizes_and_argument_validation(b):
     assert L.b200_bases_free(12345) == b.ERR_HANDLE
 
 
+def test_domain_kind_follows_the_factory(b):
+    """b200_domain_kind = valid_for_size of basic / extended / step in the order get_evaluation_domain.tcc:37-58 tries them
+    (host logic, no GPU); b200_set_two_adicity moves the boundaries the way lowering FieldT::s does."""
+    K = b.domain_kind
+    for curve, s in [("alt_bn128", 28), ("bls12_377", 47), ("bw6_761", 46)]:
+        assert K(curve, 1) == b.DOMAIN_NONE and K(curve, 2) == b.DOMAIN_BASIC
+        assert K(curve, 1 << 20) == b.DOMAIN_BASIC and K(curve, 1 << min(s, 40)) == b.DOMAIN_BASIC
+        assert K(curve, (1 << 20) + 16) == b.DOMAIN_STEP and K(curve, 3) == b.DOMAIN_STEP
+        assert K(curve, (1 << 20) + 11) == b.DOMAIN_NONE          # the factory rounds this one up first
+    assert K("alt_bn128", 1 << 29) == b.DOMAIN_EXTENDED and K("alt_bn128", 1 << 30) == b.DOMAIN_NONE
+    assert K("alt_bn128", (1 << 28) + 4) == b.DOMAIN_NONE        # step needs k + 1 <= s
+    assert K("alt_bn128", (1 << 27) + 4) == b.DOMAIN_STEP
+    b.set_two_adicity("alt_bn128", 9)
+    try:
+        assert K("alt_bn128", 512) == b.DOMAIN_BASIC and K("alt_bn128", 1024) == b.DOMAIN_EXTENDED
+        assert K("alt_bn128", 2048) == b.DOMAIN_NONE and K("alt_bn128", 256 + 8) == b.DOMAIN_STEP
+        assert K("alt_bn128", 512 + 8) == b.DOMAIN_NONE
+        assert K("bls12_377", 2048) == b.DOMAIN_BASIC             # per field
+    finally:
+        b.set_two_adicity("alt_bn128", 0)
+    assert K("alt_bn128", 1024) == b.DOMAIN_BASIC
+    with pytest.raises(b.B200Error):
+        b.set_two_adicity("alt_bn128", 29)
+
+
 def test_no_cpu_fallback(b):
     """Without a CUDA device every compute entry point fails loudly."""
     import torch
