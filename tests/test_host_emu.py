@@ -28,6 +28,8 @@ def _p(a):
 def emu():
     so = os.path.join(EMU_DIR, "libemu.so")
     src = os.path.join(EMU_DIR, "emu.cpp")
+    if os.environ.get("B200_EMU_SO"):   # an instrumented build (AddressSanitizer / UBSan), see test_emulation_under_sanitizers
+        so = os.environ["B200_EMU_SO"]
     hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".hpp"))]
     if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(f) for f in hdrs + [src]):
         subprocess.run(["g++", "-std=c++17", "-O1", "-shared", "-fPIC", "-DB200_HOST_EMULATE_PRIMS", "-I", CSRC,
