@@ -866,6 +866,7 @@ B200_OVERLAY_MSM(libff::alt_bn128_G2, libff::alt_bn128_Fr)
 B200_OVERLAY_BATCH_EXP(libff::alt_bn128_G1, libff::alt_bn128_Fr)
 B200_OVERLAY_BATCH_EXP(libff::alt_bn128_G2, libff::alt_bn128_Fr)
 B200_OVERLAY_KC(libff::alt_bn128_G2, libff::alt_bn128_G1, libff::alt_bn128_Fr)
+B200_OVERLAY_KC(libff::alt_bn128_G1, libff::alt_bn128_G1, libff::alt_bn128_Fr) // r1cs_ppzksnark's A and C queries (r1cs_ppzksnark.tcc:570-612)
 B200_OVERLAY_NTT(libff::alt_bn128_Fr)
 
 B200_OVERLAY_MSM(libff::bls12_377_G1, libff::bls12_377_Fr)
@@ -873,6 +874,7 @@ B200_OVERLAY_MSM(libff::bls12_377_G2, libff::bls12_377_Fr)
 B200_OVERLAY_BATCH_EXP(libff::bls12_377_G1, libff::bls12_377_Fr)
 B200_OVERLAY_BATCH_EXP(libff::bls12_377_G2, libff::bls12_377_Fr)
 B200_OVERLAY_KC(libff::bls12_377_G2, libff::bls12_377_G1, libff::bls12_377_Fr)
+B200_OVERLAY_KC(libff::bls12_377_G1, libff::bls12_377_G1, libff::bls12_377_Fr) // r1cs_ppzksnark's A and C queries (r1cs_ppzksnark.tcc:570-612)
 B200_OVERLAY_NTT(libff::bls12_377_Fr)
 
 B200_OVERLAY_MSM(libff::bw6_761_G1, libff::bw6_761_Fr)
@@ -880,6 +882,7 @@ B200_OVERLAY_MSM(libff::bw6_761_G2, libff::bw6_761_Fr)
 B200_OVERLAY_BATCH_EXP(libff::bw6_761_G1, libff::bw6_761_Fr)
 B200_OVERLAY_BATCH_EXP(libff::bw6_761_G2, libff::bw6_761_Fr)
 B200_OVERLAY_KC(libff::bw6_761_G2, libff::bw6_761_G1, libff::bw6_761_Fr)
+B200_OVERLAY_KC(libff::bw6_761_G1, libff::bw6_761_G1, libff::bw6_761_Fr) // r1cs_ppzksnark's A and C queries (r1cs_ppzksnark.tcc:570-612)
 B200_OVERLAY_NTT(libff::bw6_761_Fr)
 
 #endif // LIBSNARK_B200_OVERLAY_HPP_

@@ -51,6 +51,9 @@
 #include <libsnark/reductions/r1cs_to_qap/r1cs_to_qap.hpp>
 #include <libsnark/relations/constraint_satisfaction_problems/r1cs/examples/r1cs_examples.hpp>
 #include <libsnark/zk_proof_systems/ppzksnark/r1cs_gg_ppzksnark/r1cs_gg_ppzksnark.hpp>
+#include <libsnark/zk_proof_systems/ppzksnark/r1cs_ppzksnark/r1cs_ppzksnark.hpp>
+#include <libsnark/zk_proof_systems/ppzksnark/r1cs_se_ppzksnark/r1cs_se_ppzksnark.hpp>
+#include <sstream>
 
 #define API extern "C" __attribute__((visibility("default")))
 
@@ -359,6 +362,37 @@ template<typename ppT> struct H {
 
     // kc_multi_exp_with_mixed_addition over a sparse vector of (G2, G1) pairs.
     // values: nnz * (sizeof(G2)+sizeof(G1)) in the reference's knowledge_commitment layout.
+    // T1 = G2T: Groth16's B query; T1 = G1T: r1cs_ppzksnark's A and C queries (r1cs_ppzksnark.tcc:570-612)
+    template<typename T1>
+    static int kc_msm_t(
+        const uint64_t *indices,
+        const void *values,
+        size_t nnz,
+        size_t domain_size,
+        size_t min_idx,
+        size_t max_idx,
+        const void *scalars,
+        size_t nscalars,
+        size_t chunks,
+        void *out_g,
+        void *out_h)
+    {
+        typedef knowledge_commitment<T1, G1T> KC;
+        knowledge_commitment_vector<T1, G1T> vec;
+        vec.domain_size_ = domain_size;
+        vec.indices.assign(indices, indices + nnz);
+        const KC *v = static_cast<const KC *>(values);
+        vec.values.assign(v, v + nnz);
+        const FrT *s = static_cast<const FrT *>(scalars);
+        std::vector<FrT> sv(s, s + nscalars);
+        KC r = kc_multi_exp_with_mixed_addition<T1, G1T, FrT, kMethod, kForm>(
+            vec, min_idx, max_idx, sv.begin(), sv.end(), chunks);
+        r.g.to_affine_coordinates();
+        r.h.to_affine_coordinates();
+        memcpy(out_g, &r.g, sizeof(T1));
+        memcpy(out_h, &r.h, sizeof(G1T));
+        return 0;
+    }
     static int kc_msm(
         const uint64_t *indices,
         const void *values,
@@ -372,21 +406,22 @@ template<typename ppT> struct H {
         void *out_g2,
         void *out_g1)
     {
-        typedef knowledge_commitment<G2T, G1T> KC;
-        knowledge_commitment_vector<G2T, G1T> vec;
-        vec.domain_size_ = domain_size;
-        vec.indices.assign(indices, indices + nnz);
-        const KC *v = static_cast<const KC *>(values);
-        vec.values.assign(v, v + nnz);
-        const FrT *s = static_cast<const FrT *>(scalars);
-        std::vector<FrT> sv(s, s + nscalars);
-        KC r = kc_multi_exp_with_mixed_addition<G2T, G1T, FrT, kMethod, kForm>(
-            vec, min_idx, max_idx, sv.begin(), sv.end(), chunks);
-        r.g.to_affine_coordinates();
-        r.h.to_affine_coordinates();
-        memcpy(out_g2, &r.g, sizeof(G2T));
-        memcpy(out_g1, &r.h, sizeof(G1T));
-        return 0;
+        return kc_msm_t<G2T>(indices, values, nnz, domain_size, min_idx, max_idx, scalars, nscalars, chunks, out_g2, out_g1);
+    }
+    static int kc_msm_g1(
+        const uint64_t *indices,
+        const void *values,
+        size_t nnz,
+        size_t domain_size,
+        size_t min_idx,
+        size_t max_idx,
+        const void *scalars,
+        size_t nscalars,
+        size_t chunks,
+        void *out_g,
+        void *out_h)
+    {
+        return kc_msm_t<G1T>(indices, values, nnz, domain_size, min_idx, max_idx, scalars, nscalars, chunks, out_g, out_h);
     }
 
     // op: 0 FFT, 1 iFFT, 2 cosetFFT(g), 3 icosetFFT(g), 4 divide_by_Z_on_coset
@@ -1103,6 +1138,40 @@ static int kc_msm_(
         curve,
         HH::kc_msm(indices, values, nnz, domain_size, min_idx, max_idx, scalars, nscalars, chunks, out_g2, out_g1));
 }
+static int kc_msm_g1_(
+    int curve,
+    const uint64_t *indices,
+    const void *values,
+    size_t nnz,
+    size_t domain_size,
+    size_t min_idx,
+    size_t max_idx,
+    const void *scalars,
+    size_t nscalars,
+    size_t chunks,
+    void *out_g,
+    void *out_h)
+{
+    DISPATCH(
+        curve,
+        HH::kc_msm_g1(indices, values, nnz, domain_size, min_idx, max_idx, scalars, nscalars, chunks, out_g, out_h));
+}
+API int ref_kc_msm_g1(
+    int curve,
+    const uint64_t *indices,
+    const void *values,
+    size_t nnz,
+    size_t domain_size,
+    size_t min_idx,
+    size_t max_idx,
+    const void *scalars,
+    size_t nscalars,
+    size_t chunks,
+    void *out_g,
+    void *out_h)
+{
+    return kc_msm_g1_(curve, indices, values, nnz, domain_size, min_idx, max_idx, scalars, nscalars, chunks, out_g, out_h);
+}
 API int ref_kc_msm(
     int curve,
     const uint64_t *indices,
@@ -1284,4 +1353,131 @@ API int ref_groth16_verify(void *h_, const void *proof)
     fixture_handle *h = static_cast<fixture_handle *>(h_);
     DISPATCH_FIXTURE(h, verify, proof);
     return -100;
+}
+
+// ---- the sibling provers: r1cs_ppzksnark (PGHR13) and r1cs_se_ppzksnark ------------------
+// They call the same operators as the Groth16 prover (r1cs_ppzksnark.tcc:570-628: kc_multi_exp_with_mixed_addition
+// over <G1,G1> and <G2,G1>, multi_exp, multi_exp_filter_one_zero; r1cs_se_ppzksnark.tcc:500-554: multi_exp over G1
+// and G2; both witness maps go through evaluation_domain), instantiated here with Method = BDLO12_signed and
+// BaseForm = special — the instantiation the overlay specialises. Generator, prover (the reference's own entry
+// point: its d1, d2, d3 / r are drawn inside, so proofs are not reproducible) and verifier, unmodified; a proof
+// travels between the plain and the overlay build as the bytes of the reference's own operator<<.
+template<typename ppT> struct pghr13_scheme {
+    typedef r1cs_ppzksnark_keypair<ppT> keypair;
+    typedef r1cs_ppzksnark_proof<ppT> proof;
+    static keypair generate(const r1cs_constraint_system<Fr<ppT>> &cs)
+    {
+        return r1cs_ppzksnark_generator<ppT, libff::multi_exp_base_form_special>(cs);
+    }
+    static proof prove(const keypair &kp, const r1cs_example<Fr<ppT>> &ex)
+    {
+        return r1cs_ppzksnark_prover<ppT, libff::multi_exp_method_BDLO12_signed, libff::multi_exp_base_form_special>(
+            kp.pk, ex.primary_input, ex.auxiliary_input);
+    }
+    static bool verify(const keypair &kp, const r1cs_example<Fr<ppT>> &ex, const proof &pi)
+    {
+        return r1cs_ppzksnark_verifier_strong_IC<ppT>(kp.vk, ex.primary_input, pi);
+    }
+};
+template<typename ppT> struct se_scheme {
+    typedef r1cs_se_ppzksnark_keypair<ppT> keypair;
+    typedef r1cs_se_ppzksnark_proof<ppT> proof;
+    static keypair generate(const r1cs_constraint_system<Fr<ppT>> &cs)
+    {
+        return r1cs_se_ppzksnark_generator<ppT, libff::multi_exp_base_form_special>(cs);
+    }
+    static proof prove(const keypair &kp, const r1cs_example<Fr<ppT>> &ex)
+    {
+        return r1cs_se_ppzksnark_prover<ppT, libff::multi_exp_method_BDLO12_signed, libff::multi_exp_base_form_special>(
+            kp.pk, ex.primary_input, ex.auxiliary_input);
+    }
+    static bool verify(const keypair &kp, const r1cs_example<Fr<ppT>> &ex, const proof &pi)
+    {
+        return r1cs_se_ppzksnark_verifier_strong_IC<ppT>(kp.vk, ex.primary_input, pi);
+    }
+};
+
+struct sibling_base {
+    virtual ~sibling_base() {}
+    virtual int prove(void *out, size_t cap, size_t *len, double *ms) const = 0;
+    virtual int verify(const void *proof, size_t len) const = 0;
+};
+template<typename ppT, typename Scheme> struct sibling_fixture : sibling_base {
+    r1cs_example<Fr<ppT>> example;
+    typename Scheme::keypair keypair;
+    sibling_fixture(r1cs_example<Fr<ppT>> &&e) : example(std::move(e)), keypair(Scheme::generate(example.constraint_system)) {}
+    int prove(void *out, size_t cap, size_t *len, double *ms) const override
+    {
+        const double t0 = omp_get_wtime();
+        const typename Scheme::proof pi = Scheme::prove(keypair, example);
+        if (ms) {
+            *ms = (omp_get_wtime() - t0) * 1e3;
+        }
+        std::ostringstream ss;
+        ss << pi;
+        const std::string b = ss.str();
+        *len = b.size();
+        if (b.size() > cap) {
+            return -5;
+        }
+        memcpy(out, b.data(), b.size());
+        return 0;
+    }
+    int verify(const void *proof, size_t len) const override
+    {
+        std::istringstream ss(std::string(static_cast<const char *>(proof), len));
+        typename Scheme::proof pi;
+        ss >> pi;
+        return Scheme::verify(keypair, example, pi) ? 1 : 0;
+    }
+};
+template<typename ppT> static sibling_base *sibling_make(int scheme, size_t nc, size_t ni)
+{
+    ppT::init_public_params();
+    r1cs_example<Fr<ppT>> ex = generate_r1cs_example_with_field_input<Fr<ppT>>(nc, ni);
+    if (scheme == 0) {
+        return new sibling_fixture<ppT, pghr13_scheme<ppT>>(std::move(ex));
+    }
+    return new sibling_fixture<ppT, se_scheme<ppT>>(std::move(ex));
+}
+
+// scheme: 0 = r1cs_ppzksnark (PGHR13), 1 = r1cs_se_ppzksnark; curve: 0 alt_bn128, 1 bls12_377
+API void *ref_sibling_setup(int scheme, int curve, size_t num_constraints, size_t num_inputs)
+{
+    if (scheme < 0 || scheme > 1) {
+        return nullptr;
+    }
+    libff::inhibit_profiling_info = true;
+    libff::inhibit_profiling_counters = true;
+    switch (curve) {
+    case 0: return sibling_make<libff::alt_bn128_pp>(scheme, num_constraints, num_inputs);
+    case 1: return sibling_make<libff::bls12_377_pp>(scheme, num_constraints, num_inputs);
+    }
+    return nullptr;
+}
+// the fixture may have been built by the other build of this harness (plain / overlay): the objects are layout-identical
+// and the virtual call below would run the OTHER library's code, so both entry points re-dispatch on (scheme, curve)
+template<typename ppT, typename Scheme> static const sibling_fixture<ppT, Scheme> *sib(const void *h)
+{
+    return static_cast<const sibling_fixture<ppT, Scheme> *>(static_cast<const sibling_base *>(h));
+}
+#define SIBLING_DISPATCH(call)                                                                                         \
+    switch (scheme * 2 + curve) {                                                                                      \
+    case 0: return sib<libff::alt_bn128_pp, pghr13_scheme<libff::alt_bn128_pp>>(h)->sibling_fixture::call;             \
+    case 1: return sib<libff::bls12_377_pp, pghr13_scheme<libff::bls12_377_pp>>(h)->sibling_fixture::call;             \
+    case 2: return sib<libff::alt_bn128_pp, se_scheme<libff::alt_bn128_pp>>(h)->sibling_fixture::call;                 \
+    case 3: return sib<libff::bls12_377_pp, se_scheme<libff::bls12_377_pp>>(h)->sibling_fixture::call;                 \
+    }                                                                                                                  \
+    return -100;
+API int ref_sibling_prove(int scheme, int curve, const void *h, void *out, size_t cap, size_t *len, double *ms)
+{
+    SIBLING_DISPATCH(prove(out, cap, len, ms))
+}
+API int ref_sibling_verify(int scheme, int curve, const void *h, const void *proof, size_t len)
+{
+    SIBLING_DISPATCH(verify(proof, len))
+}
+API void ref_sibling_free(void *h)
+{
+    delete static_cast<sibling_base *>(h);
 }

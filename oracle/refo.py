@@ -71,10 +71,17 @@ class RefOracle:
         L.ref_msm.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]
         L.ref_kc_msm.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
                                  C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p, C.c_void_p]
+        L.ref_kc_msm_g1.argtypes = L.ref_kc_msm.argtypes
         L.ref_fft.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]
         L.ref_poly_eval_at_domain.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]
         L.ref_poly_eval_at_factory_domain.argtypes = L.ref_poly_eval_at_domain.argtypes
         L.ref_set_two_adicity.argtypes = [C.c_int, C.c_int]
+        L.ref_sibling_setup.argtypes = [C.c_int, C.c_int, C.c_size_t, C.c_size_t]
+        L.ref_sibling_setup.restype = C.c_void_p
+        L.ref_sibling_prove.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t),
+                                        C.POINTER(C.c_double)]
+        L.ref_sibling_verify.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t]
+        L.ref_sibling_free.argtypes = [C.c_void_p]
         L.ref_field_consts.argtypes = [C.c_int, C.c_int, C.c_void_p]
         L.ref_curve_consts.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ref_info.argtypes = [C.c_int, C.c_void_p]
@@ -220,14 +227,16 @@ class RefOracle:
         assert rc == 0, rc
         return out
 
-    def kc_msm(self, curve, indices, values, domain_size, min_idx, max_idx, scalars, chunks=1):
+    def kc_msm(self, curve, indices, values, domain_size, min_idx, max_idx, scalars, chunks=1, g1_pair=False):
+        """kc_multi_exp_with_mixed_addition over knowledge_commitment<G2, G1> (or <G1, G1> with g1_pair)."""
         indices = np.ascontiguousarray(indices, dtype=np.uint64)
         values = np.ascontiguousarray(values, dtype=np.uint64)
         scalars = np.ascontiguousarray(scalars, dtype=np.uint64)
-        g2 = np.zeros(self._glimbs(curve, G2), dtype=np.uint64)
+        g2 = np.zeros(self._glimbs(curve, G1 if g1_pair else G2), dtype=np.uint64)
         g1 = np.zeros(self._glimbs(curve, G1), dtype=np.uint64)
-        rc = self.lib.ref_kc_msm(self.info(curve)["id"], _p(indices), _p(values), indices.shape[0], domain_size,
-                                 min_idx, max_idx, _p(scalars), scalars.shape[0], chunks, _p(g2), _p(g1))
+        fn = self.lib.ref_kc_msm_g1 if g1_pair else self.lib.ref_kc_msm
+        rc = fn(self.info(curve)["id"], _p(indices), _p(values), indices.shape[0], domain_size,
+                min_idx, max_idx, _p(scalars), scalars.shape[0], chunks, _p(g2), _p(g1))
         assert rc == 0, rc
         return g2, g1
 
@@ -263,9 +272,44 @@ class RefOracle:
         get_evaluation_domain then returns extended_radix2_domain at 2^(s+1)."""
         assert self.lib.ref_set_two_adicity(self.info(curve)["id"], int(s)) == 0
 
+    def sibling_setup(self, scheme, curve, num_constraints, num_inputs):
+        return SiblingFixture(self, scheme, curve, num_constraints, num_inputs)
+
     # ---- Groth16 -------------------------------------------------------------
     def groth16_setup(self, curve, num_constraints, num_inputs, real_keys=True):
         return Groth16Fixture(self, curve, num_constraints, num_inputs, real_keys)
+
+
+PGHR13, SE_PPZKSNARK = 0, 1
+
+
+class SiblingFixture:
+    """r1cs_ppzksnark (PGHR13, scheme 0) or r1cs_se_ppzksnark (scheme 1) on the reference's synthetic R1CS: keys from
+    the reference generator (BaseForm = special), the reference's own prover entry point instantiated with
+    BDLO12_signed / special (proofs are randomised inside), the strong-IC verifier. `via` = the overlay build runs
+    ITS copy of the same unmodified prover — with the operators resolved to the CUDA library — on this fixture."""
+
+    def __init__(self, ref, scheme, curve, num_constraints, num_inputs):
+        self.ref, self.scheme, self.cid = ref, int(scheme), ref.info(curve)["id"]
+        self.h = ref.lib.ref_sibling_setup(self.scheme, self.cid, num_constraints, num_inputs)
+        assert self.h, "ref_sibling_setup failed"
+
+    def prove(self, via=None):
+        buf = np.zeros(1 << 14, dtype=np.uint8)
+        n, ms = C.c_size_t(0), C.c_double(0)
+        lib = (via or self.ref).lib
+        rc = lib.ref_sibling_prove(self.scheme, self.cid, self.h, _p(buf), buf.nbytes, C.byref(n), C.byref(ms))
+        assert rc == 0, rc
+        return buf[: n.value].copy(), ms.value
+
+    def verify(self, proof, via=None):
+        proof = np.ascontiguousarray(proof, dtype=np.uint8)
+        return (via or self.ref).lib.ref_sibling_verify(self.scheme, self.cid, self.h, _p(proof), proof.nbytes)
+
+    def close(self):
+        if self.h:
+            self.ref.lib.ref_sibling_free(self.h)
+            self.h = None
 
 
 class Groth16Fixture:

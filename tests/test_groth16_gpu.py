@@ -276,6 +276,46 @@ def test_overlay_extended_domain(ref, overlay, b200):
         b200.set_two_adicity(curve, 0)
 
 
+@pytest.mark.parametrize("scheme,curve,nc,ni", [(0, "alt_bn128", (1 << 12) - 11, 10), (0, "alt_bn128", 3000, 7),
+                                                (0, "bls12_377", 1500, 4), (1, "alt_bn128", 2000, 5),
+                                                (1, "bls12_377", 700, 3)])
+def test_overlay_sibling_provers(ref, overlay, b200, scheme, curve, nc, ni):
+    """The sibling provers of SURVEY.md §8f N4 — r1cs_ppzksnark (PGHR13, scheme 0: kc MSMs over <G1,G1> and <G2,G1>,
+    multi_exp, multi_exp_filter_one_zero; r1cs_ppzksnark.tcc:570-628) and r1cs_se_ppzksnark (scheme 1: G1 and G2 multi_exp
+    over the SAP witness; r1cs_se_ppzksnark.tcc:500-554) — compiled unmodified with the overlay interposed: their operators
+    and domain transforms run on the GPU, and the reference's own verifier (plain build) accepts the proofs. The provers
+    draw their randomness inside, so there is no bit-for-bit proof to compare; operator parity is the MSM / kc / NTT tests."""
+    fx = ref.sibling_setup(scheme, curve, nc, ni)
+    try:
+        before = b200.lib().b200_launch_count()
+        proof, _ = fx.prove(via=overlay)
+        assert b200.lib().b200_launch_count() > before + 20      # the CUDA path did the work
+        assert fx.verify(proof) == 1
+        assert fx.verify(proof, via=overlay) == 1
+        mine, _ = fx.prove()
+        assert fx.verify(mine) == 1 and not np.array_equal(mine, proof)
+    finally:
+        fx.close()
+
+
+def test_overlay_kc_msm_over_g1_pairs(ref, overlay):
+    """kc_multi_exp_with_mixed_addition<G1, G1, Fr, BDLO12_signed, special> (r1cs_ppzksnark's A and C queries) through
+    the overlay == the reference template, on a sparse vector with an index window."""
+    curve = "alt_bn128"
+    nnz, dom = 5000, 7000
+    values = np.concatenate([ref.make_bases(curve, refo.G1, nnz, 41), ref.make_bases(curve, refo.G1, nnz, 42)], axis=1)
+    rng = np.random.default_rng(5)
+    indices = np.sort(rng.choice(dom, nnz, replace=False)).astype(np.uint64)
+    scalars = ref.field_random(curve, refo.FR, 321, dom)
+    scalars[3] = 0
+    scalars[11] = ref.field_consts(curve, refo.FR)["one"]
+    for lo, hi in [(0, dom), (13, 6500)]:
+        sc = scalars[: hi - lo]
+        want = ref.kc_msm(curve, indices, values, dom, lo, hi, sc, g1_pair=True)
+        got = overlay.kc_msm(curve, indices, values, dom, lo, hi, sc, g1_pair=True)
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1]), (lo, hi)
+
+
 def test_overlay_step_domain(ref, overlay):
     """The overlay's step_radix2_domain specialisations: operators through the reference's own factory, and the
     reference prover (operators overlaid, and the one-call device prover) on a circuit whose size is not a power of two."""

@@ -267,3 +267,22 @@ def test_whole_proof_golden(P, curve, nc):
     domain —, the four multi-exponentiations, the assembly) == the reference prover's proof for the same r, s."""
     key, r1cs, w, r, s, proof = groth16_fixture(curve, nc)
     assert np.array_equal(P.groth16_prove(curve, key, r1cs, w, r, s), proof)
+
+
+@pytest.mark.parametrize("scheme", [0, 1])
+def test_sibling_provers_reference_roundtrip(ref, scheme):
+    """The harness around the sibling provers (r1cs_ppzksnark.tcc:570-628, r1cs_se_ppzksnark.tcc:500-554)
+    instantiated with BDLO12_signed / special: generator -> prover -> strong-IC verifier, all unmodified reference code;
+    a proof made for other keys is rejected. (The GPU tier runs the same prover from the overlay build.)"""
+    from oracle import refo
+    fx = ref.sibling_setup(scheme, "alt_bn128", 60, 3)
+    other = ref.sibling_setup(scheme, "alt_bn128", 60, 3)
+    try:
+        proof, _ = fx.prove()
+        assert fx.verify(proof) == 1
+        assert other.verify(proof) == 0
+        again, _ = fx.prove()
+        assert not np.array_equal(again, proof) and fx.verify(again) == 1   # d1, d2, d3 / r are drawn inside the prover
+    finally:
+        fx.close()
+        other.close()
