@@ -300,6 +300,23 @@ def test_overlay_sibling_provers(ref, overlay, b200, scheme, curve, nc, ni):
         fx.close()
 
 
+@pytest.mark.parametrize("scheme", [0, 1])
+def test_overlay_sibling_generators(ref, overlay, b200, scheme):
+    """The sibling GENERATORS compiled with the overlay (batch_exp / kc_batch_exp over <G1,G1> and <G2,G1> on the GPU,
+    r1cs_ppzksnark.tcc:321-398 and siblings): their keys, used by the plain build's prover, give proofs the plain build's
+    verifier accepts — and the overlay prover works on them as well."""
+    before = b200.lib().b200_launch_count()
+    fx = overlay.sibling_setup(scheme, "alt_bn128", 1200, 6)
+    try:
+        assert b200.lib().b200_launch_count() > before
+        proof, _ = fx.prove(via=ref)
+        assert fx.verify(proof, via=ref) == 1
+        proof2, _ = fx.prove(via=overlay)
+        assert fx.verify(proof2, via=ref) == 1
+    finally:
+        fx.close()
+
+
 def test_overlay_kc_msm_over_g1_pairs(ref, overlay):
     """kc_multi_exp_with_mixed_addition<G1, G1, Fr, BDLO12_signed, special> (r1cs_ppzksnark's A and C queries) through
     the overlay == the reference template, on a sparse vector with an index window."""
