@@ -98,6 +98,21 @@ inline unsigned long long hash_words(unsigned long long h, const void *p, size_t
 {
     const unsigned char *b = static_cast<const unsigned char *>(p);
     size_t i = 0;
+    if (bytes >= 4096) { // long inputs (index arrays of MBs): four independent lanes, so the multiplies overlap
+        unsigned long long l[4] = {h, h ^ 0x243F6A8885A308D3ull, h ^ 0x13198A2E03707344ull, h ^ 0xA4093822299F31D0ull};
+        for (; i + 32 <= bytes; i += 32) {
+            unsigned long long w[4];
+            memcpy(w, b + i, 32);
+            for (int k = 0; k < 4; ++k) {
+                l[k] = (l[k] ^ w[k]) * 0x9E3779B97F4A7C15ull;
+                l[k] ^= l[k] >> 29;
+            }
+        }
+        for (int k = 0; k < 4; ++k) {
+            h = (h ^ l[k]) * 0x9E3779B97F4A7C15ull;
+            h ^= h >> 29;
+        }
+    }
     for (; i + 8 <= bytes; i += 8) {
         unsigned long long w;
         memcpy(&w, b + i, 8);
@@ -122,6 +137,7 @@ inline bool &fingerprint_full_flag()
 inline void set_cache_fingerprint_full(bool full) { fingerprint_full_flag() = full; }
 constexpr size_t FINGERPRINT_SAMPLES = 256;
 constexpr size_t CACHE_MIN_POINTS = size_t(1) << 12; // smaller base vectors are one-off: not cached
+constexpr size_t FINGERPRINT_ROW_TERMS = 64;          // terms hashed of one sampled linear combination
 
 struct pk_cache;
 inline void pk_cache_clear();
@@ -457,8 +473,8 @@ struct r1cs_cache {
         static r1cs_cache c;
         return c;
     }
-    // num_inputs and the terms (index, coefficient) of up to FINGERPRINT_SAMPLES evenly spread constraints — of all
-    // constraints in full mode
+    // num_inputs and the terms (index, coefficient; up to FINGERPRINT_ROW_TERMS per linear combination) of up to
+    // FINGERPRINT_SAMPLES evenly spread constraints — everything in full mode
     template<typename FieldT> static unsigned long long fingerprint(const libsnark::r1cs_constraint_system<FieldT> &cs)
     {
         const size_t nc = cs.num_constraints();
@@ -471,7 +487,12 @@ struct r1cs_cache {
             for (const auto *lc : lcs) {
                 const unsigned long long cnt = lc->terms.size();
                 h = hash_words(h, &cnt, 8);
-                for (const auto &t : lc->terms) {
+                // a row can be as long as the variable count (the closing constraint of the reference's own examples sums
+                // every variable: 17 ms of hashing per proof at 2^20): of such a row, evenly spread terms only
+                const bool all_terms = fingerprint_full_flag() || cnt <= FINGERPRINT_ROW_TERMS;
+                const size_t nt = all_terms ? (size_t)cnt : FINGERPRINT_ROW_TERMS;
+                for (size_t q = 0; q < nt; ++q) {
+                    const auto &t = lc->terms[all_terms ? q : (size_t)((unsigned __int128)q * (cnt - 1) / (FINGERPRINT_ROW_TERMS - 1))];
                     const unsigned long long idx = t.index;
                     h = hash_words(h, &idx, 8);
                     h = hash_words(h, &t.coeff, sizeof(FieldT));
@@ -589,7 +610,7 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
     const libsnark::r1cs_gg_ppzksnark_proving_key<ppT> &pk,
     const libsnark::r1cs_gg_ppzksnark_primary_input<ppT> &primary_input,
     const libsnark::r1cs_gg_ppzksnark_auxiliary_input<ppT> &auxiliary_input, const libff::Fr<ppT> &r,
-    const libff::Fr<ppT> &s)
+    const libff::Fr<ppT> &s, bool force_pow_2_domain = false)
 {
     typedef libff::Fr<ppT> FrT;
     typedef libff::G1<ppT> G1T;
@@ -601,7 +622,8 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
     if (primary_input.size() != ni || primary_input.size() + auxiliary_input.size() != nv) {
         throw std::runtime_error("libsnark_b200: witness size does not match the constraint system");
     }
-    const size_t m = libfqfft::get_evaluation_domain<FrT>(cs.num_constraints() + ni + 1)->m;
+    const size_t min_n = cs.num_constraints() + ni + 1; // r1cs_to_qap.tcc:224-227
+    const size_t m = libfqfft::get_evaluation_domain<FrT>(force_pow_2_domain ? (size_t)1 << libff::log2(min_n) : min_n)->m;
     static const bool trace = getenv("B200_OVERLAY_TRACE") != nullptr;
     long long t_prev = libff::get_nsec_time();
     auto lap = [&](const char *what) {
@@ -616,6 +638,8 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
         // The whole prover behind one C-ABI call: the key's queries (from the caches below, with their window
         // tables from the second proof on), the CSR and the five single points become a b200_groth16_pk_t once;
         // b200_groth16_prove then runs the witness map and the five MSMs concurrently on the device.
+        static const bool times = getenv("B200_OVERLAY_TIMES") != nullptr; // one line per proof on stderr
+        const long long t_in = libff::get_nsec_time();
         bases_cache &bc = bases_cache::get();
         bc.begin_group();
         const auto &vec = pk.B_query;
@@ -626,7 +650,9 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
         const b200_bases_t hB1 = bc.lookup(curve, B200_G1, vals + off2, sizeof(KC), vec.values.size(), sizeof(G1T));
         const b200_bases_t hH = bc.lookup(curve, B200_G1, pk.H_query.data(), sizeof(G1T), pk.H_query.size(), sizeof(G1T));
         const b200_bases_t hL = bc.lookup(curve, B200_G1, pk.L_query.data(), sizeof(G1T), pk.L_query.size(), sizeof(G1T));
+        const long long t_bases = libff::get_nsec_time();
         const b200_r1cs_t hr = r1cs_cache::get().lookup(cs);
+        const long long t_r1cs = libff::get_nsec_time();
         std::map<pk_cache::key_t, b200_groth16_pk_t> &keys = pk_cache::get().keys;
         unsigned long long pfp = hash_words(1469598103934665603ull, &pk.alpha_g1, sizeof(G1T));
         pfp = hash_words(pfp, &pk.beta_g1, sizeof(G1T));
@@ -635,6 +661,7 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
         pfp = hash_words(pfp, &pk.delta_g2, sizeof(G2T));
         pfp = hash_words(pfp, vec.indices.data(), vec.indices.size() * sizeof(size_t));
         const pk_cache::key_t key(hA, hB2, hB1, hH, hL, hr, pfp);
+        const long long t_fp = libff::get_nsec_time();
         auto it = keys.find(key);
         if (it == keys.end()) {
             G1T alpha = pk.alpha_g1, beta1 = pk.beta_g1, delta1 = pk.delta_g1;
@@ -657,8 +684,16 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
             G1T c;
         } out;
         static_assert(sizeof(out) == 2 * sizeof(G1T) + sizeof(G2T), "proof points are laid out back to back");
-        check(b200_groth16_prove(it->second, primary_input.data(), auxiliary_input.data(), &r, &s, &out, nullptr),
+        double st[7] = {0, 0, 0, 0, 0, 0, 0};
+        const long long t_key = libff::get_nsec_time();
+        check(b200_groth16_prove(it->second, primary_input.data(), auxiliary_input.data(), &r, &s, &out, times ? st : nullptr),
               "b200_groth16_prove");
+        if (times) {
+            fprintf(stderr, "[b200 fused prover] cache lookups %.3f ms (bases %.3f, r1cs %.3f, key fingerprint %.3f, key %.3f), "
+                            "b200_groth16_prove %.3f ms (upload %.3f, witness map %.3f, total %.3f)\n",
+                    (t_key - t_in) * 1e-6, (t_bases - t_in) * 1e-6, (t_r1cs - t_bases) * 1e-6, (t_fp - t_r1cs) * 1e-6,
+                    (t_key - t_fp) * 1e-6, (libff::get_nsec_time() - t_key) * 1e-6, st[0], st[1], st[6]);
+        }
         return libsnark::r1cs_gg_ppzksnark_proof<ppT>(G1T(out.a), G2T(out.b), G1T(out.c));
     }
     // B200_OVERLAY_TRACE: the same proof stage by stage, one MSM after the other, with a time per stage on stderr.
@@ -746,10 +781,10 @@ template<typename ppT>
 libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
     const libsnark::r1cs_gg_ppzksnark_proving_key<ppT> &pk,
     const libsnark::r1cs_gg_ppzksnark_primary_input<ppT> &primary_input,
-    const libsnark::r1cs_gg_ppzksnark_auxiliary_input<ppT> &auxiliary_input)
+    const libsnark::r1cs_gg_ppzksnark_auxiliary_input<ppT> &auxiliary_input, bool force_pow_2_domain = false)
 {
-    return r1cs_gg_ppzksnark_prover_fused<ppT>(
-        pk, primary_input, auxiliary_input, libff::Fr<ppT>::random_element(), libff::Fr<ppT>::random_element());
+    const libff::Fr<ppT> r = libff::Fr<ppT>::random_element(), s = libff::Fr<ppT>::random_element();
+    return r1cs_gg_ppzksnark_prover_fused<ppT>(pk, primary_input, auxiliary_input, r, s, force_pow_2_domain);
 }
 
 } // namespace libsnark_b200
@@ -861,6 +896,29 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
     B200_OVERLAY_DOMAIN(step_radix2_domain, FR)                                                                        \
     }
 
+// The prover entry point itself, for its default instantiation (BDLO12_signed / special, r1cs_gg_ppzksnark.hpp:418-426):
+// r1cs_gg_ppzksnark_prover(pk, primary, auxiliary[, force_pow_2_domain]) in unmodified caller code becomes the
+// device-resident prover above — the key's queries and the CSR are uploaded and cached on first use, later proofs run
+// the witness map and the five MSMs on the device from the witness alone. r and s are drawn as the reference draws
+// them (r1cs_gg_ppzksnark.tcc:499-500). Define B200_OVERLAY_KEEP_REFERENCE_PROVER to keep the reference's body (its
+// operators are then still the specialisations below).
+#ifndef B200_OVERLAY_KEEP_REFERENCE_PROVER
+#define B200_OVERLAY_PROVER(PP)                                                                                        \
+    namespace libsnark                                                                                                 \
+    {                                                                                                                  \
+    template<>                                                                                                         \
+    inline r1cs_gg_ppzksnark_proof<PP>                                                                                 \
+    r1cs_gg_ppzksnark_prover<PP, libff::multi_exp_method_BDLO12_signed, libff::multi_exp_base_form_special>(           \
+        const r1cs_gg_ppzksnark_proving_key<PP> &pk, const r1cs_gg_ppzksnark_primary_input<PP> &primary_input,         \
+        const r1cs_gg_ppzksnark_auxiliary_input<PP> &auxiliary_input, bool force_pow_2_domain)                         \
+    {                                                                                                                  \
+        return libsnark_b200::r1cs_gg_ppzksnark_prover_fused<PP>(pk, primary_input, auxiliary_input, force_pow_2_domain); \
+    }                                                                                                                  \
+    }
+#else
+#define B200_OVERLAY_PROVER(PP)
+#endif
+
 B200_OVERLAY_MSM(libff::alt_bn128_G1, libff::alt_bn128_Fr)
 B200_OVERLAY_MSM(libff::alt_bn128_G2, libff::alt_bn128_Fr)
 B200_OVERLAY_BATCH_EXP(libff::alt_bn128_G1, libff::alt_bn128_Fr)
@@ -868,6 +926,7 @@ B200_OVERLAY_BATCH_EXP(libff::alt_bn128_G2, libff::alt_bn128_Fr)
 B200_OVERLAY_KC(libff::alt_bn128_G2, libff::alt_bn128_G1, libff::alt_bn128_Fr)
 B200_OVERLAY_KC(libff::alt_bn128_G1, libff::alt_bn128_G1, libff::alt_bn128_Fr) // r1cs_ppzksnark's A and C queries (r1cs_ppzksnark.tcc:570-612)
 B200_OVERLAY_NTT(libff::alt_bn128_Fr)
+B200_OVERLAY_PROVER(libff::alt_bn128_pp)
 
 B200_OVERLAY_MSM(libff::bls12_377_G1, libff::bls12_377_Fr)
 B200_OVERLAY_MSM(libff::bls12_377_G2, libff::bls12_377_Fr)
@@ -876,6 +935,7 @@ B200_OVERLAY_BATCH_EXP(libff::bls12_377_G2, libff::bls12_377_Fr)
 B200_OVERLAY_KC(libff::bls12_377_G2, libff::bls12_377_G1, libff::bls12_377_Fr)
 B200_OVERLAY_KC(libff::bls12_377_G1, libff::bls12_377_G1, libff::bls12_377_Fr) // r1cs_ppzksnark's A and C queries (r1cs_ppzksnark.tcc:570-612)
 B200_OVERLAY_NTT(libff::bls12_377_Fr)
+B200_OVERLAY_PROVER(libff::bls12_377_pp)
 
 B200_OVERLAY_MSM(libff::bw6_761_G1, libff::bw6_761_Fr)
 B200_OVERLAY_MSM(libff::bw6_761_G2, libff::bw6_761_Fr)
@@ -884,5 +944,6 @@ B200_OVERLAY_BATCH_EXP(libff::bw6_761_G2, libff::bw6_761_Fr)
 B200_OVERLAY_KC(libff::bw6_761_G2, libff::bw6_761_G1, libff::bw6_761_Fr)
 B200_OVERLAY_KC(libff::bw6_761_G1, libff::bw6_761_G1, libff::bw6_761_Fr) // r1cs_ppzksnark's A and C queries (r1cs_ppzksnark.tcc:570-612)
 B200_OVERLAY_NTT(libff::bw6_761_Fr)
+B200_OVERLAY_PROVER(libff::bw6_761_pp)
 
 #endif // LIBSNARK_B200_OVERLAY_HPP_
