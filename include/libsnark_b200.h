@@ -201,6 +201,13 @@ int b200_r1cs_evaluate(b200_r1cs_t handle, const void *w, size_t m, void *aA, vo
  * num_variables + 1 elements) -> dH = coefficients_for_H (device, m + 1 elements). The MSMs can
  * then consume d_w and dH in place (b200_msm_resident with scalars_on_device = 1). */
 int b200_witness_map_r1cs_dev(b200_r1cs_t handle, const void *d_w, size_t m, void *dH);
+/* libsnark::r1cs_to_qap_witness_map(cs, primary, auxiliary, d1, d2, d3) with its ZK patch (r1cs_to_qap.tcc:209-344; the
+ * sibling provers r1cs_ppzksnark / r1cs_se_ppzksnark call it with random d's, Groth16 with zeros): w = (1 | primary |
+ * auxiliary) on the host, d123 = d1, d2, d3 (three Fr, Montgomery, host), out_H = coefficients_for_H =
+ * H + d2 coef(A) + d1 coef(B) - d3 + d1 d2 Z (m + 1 elements, host; Z through the domain's add_poly_Z:
+ * basic_radix2_domain.tcc:109-115, extended_radix2_domain.tcc:203-214, step_radix2_domain.tcc:235-245). Sparse
+ * evaluation, the transforms (eight with a non-zero d1 or d2) and the patch run on the device. */
+int b200_witness_map_r1cs_zk(b200_r1cs_t handle, const void *w, size_t m, const void *d123, void *out_H);
 /* The two halves of b200_witness_map_r1cs_dev, for provers that run the A, B and C chains on different
  * GPUs (r1cs_to_qap.tcc:252-290 and :293-330). m must be a power of two.
  * chain : which = 0/1/2 -> the evaluations of the a-/b-/c-combinations from d_w, iFFT, cosetFFT(g) into

@@ -33,7 +33,7 @@ EXPORTS = [
     "b200_msm", "b200_bases_upload", "b200_bases_free", "b200_bases_size", "b200_msm_resident",
     "b200_msm_num_windows", "b200_msm_window_bits", "b200_msm_window_bytes", "b200_msm_resident_windows", "b200_msm_fold_windows",
     "b200_msm_filter_one_zero", "b200_kc_msm",
-    "b200_ntt", "b200_ntt_dev", "b200_divide_by_Z_on_coset", "b200_set_two_adicity", "b200_domain_kind", "b200_witness_map_h", "b200_witness_map_h_dev",
+    "b200_ntt", "b200_ntt_dev", "b200_divide_by_Z_on_coset", "b200_set_two_adicity", "b200_domain_kind", "b200_witness_map_r1cs_zk", "b200_witness_map_h", "b200_witness_map_h_dev",
     "b200_msm_resident_windows_dev", "b200_timer_start", "b200_timer_stop", "b200_make_bases",
     "b200_imad_carry_peak", "b200_imad_peak", "b200_last_msm_timing", "b200_launch_count",
     "b200_r1cs_upload", "b200_r1cs_free", "b200_r1cs_evaluate", "b200_witness_map_r1cs_dev", "b200_gather_dev",
@@ -110,6 +110,7 @@ def lib():
         L.b200_r1cs_free.argtypes = [u64]
         L.b200_r1cs_evaluate.argtypes = [u64, vp, sz, vp, vp, vp]
         L.b200_witness_map_r1cs_dev.argtypes = [u64, vp, sz, vp]
+        L.b200_witness_map_r1cs_zk.argtypes = [u64, vp, sz, vp, vp]
         L.b200_gather_dev.argtypes = [i, vp, vp, sz, vp]
         L.b200_groth16_pk_create.argtypes = [i, vp, vp, vp, vp, vp, u64, u64, u64, vp, u64, u64, u64, sz, sz, sz, sz,
                                              C.POINTER(u64)]
@@ -479,6 +480,15 @@ class R1CS:
         finally:
             dw.free()
             dh.free()
+
+    def witness_map_h_zk(self, w, m, d1, d2, d3):
+        """coefficients_for_H of r1cs_to_qap_witness_map(cs, primary, auxiliary, d1, d2, d3) (m + 1 rows), ZK patch included."""
+        w = _u64(w)
+        assert w.shape[0] == self.nv + 1
+        d = np.ascontiguousarray(np.stack([_u64(d1).reshape(-1), _u64(d2).reshape(-1), _u64(d3).reshape(-1)]))
+        out = np.zeros((m + 1, self._limbs), dtype=np.uint64)
+        _check(lib().b200_witness_map_r1cs_zk(self.handle, _p(w), m, _p(d), _p(out)))
+        return out
 
     def free(self):
         if self.handle:

@@ -1107,6 +1107,109 @@ template<class Fr> int witness_map_r1cs_dev(const R1csSet &r, const void *d_w, s
     return witness_map_dev<Fr>(g_bufA.as<Fr>(), g_bufB.as<Fr>(), g_bufC.as<Fr>(), m, static_cast<Fr *>(dH));
 }
 
+// add_poly_Z(c, H) of the domain kind that serves m (basic_radix2_domain.tcc:109-115, extended_radix2_domain.tcc:
+// 203-214, step_radix2_domain.tcc:235-245), as a list of single-coefficient additions
+template<class Fr> int add_poly_z_fixups(size_t m, const Fr &c, ntt::CoeffFixups<Fr> *f)
+{
+    const Fr one = Fr::one();
+    auto push = [&](uint64_t i, const Fr &v) {
+        f->idx[f->n] = i;
+        f->val[f->n] = v;
+        ++f->n;
+    };
+    const int lgn = log2_exact(m);
+    if (lgn >= 1 && lgn <= two_adicity<Fr>()) {
+        push(m, c);
+        push(0, c.neg());
+        return B200_OK;
+    }
+    Fr g;
+    for (int i = 0; i < Fr::N; ++i) {
+        g.v[i] = Fr::params::generator(i);
+    }
+    if (lgn >= 2 && lgn == two_adicity<Fr>() + 1) {
+        const size_t small = m / 2;
+        const Fr ssm = host_pow(g.sqr(), small);
+        push(m, c);
+        push(small, (c * (ssm + one)).neg());
+        push(0, c * ssm);
+        return B200_OK;
+    }
+    StepShape sh;
+    if (!step_shape<Fr>(m, &sh)) {
+        return rt::set_error(B200_ERR_DOMAIN, "no radix-2 domain of size %zu", m);
+    }
+    Fr w;
+    for (int i = 0; i < Fr::N; ++i) {
+        w.v[i] = Fr::params::root_of_unity(i);
+    }
+    for (int i = Fr::params::S; i > sh.lg_big + 1; --i) {
+        w = w.sqr(); // omega = get_root_of_unity(2 big), step_radix2_domain.tcc:57
+    }
+    const Fr wsm = host_pow(w, sh.small);
+    push(m, c);
+    push(sh.big, (c * wsm).neg());
+    push(sh.small, c.neg());
+    push(0, c * wsm);
+    return B200_OK;
+}
+
+rt::DevBuf g_bufW, g_bufT;
+
+// r1cs_to_qap_witness_map (r1cs_to_qap.tcc:209-344) with the ZK patch: coefficients_for_H =
+// H + d2 coef(A) + d1 coef(B) - d3 + d1 d2 Z. The patch's only vector part, d2 coef(A) + d1 coef(B), is the inverse
+// transform of d2 aA + d1 aB (the transform is linear), taken before the chains overwrite the evaluations.
+// w_host: (1 | primary | auxiliary); d123: d1, d2, d3 (host, Montgomery); out_H: m + 1 elements (host).
+template<class Fr> int witness_map_r1cs_zk_host(const R1csSet &r, const void *w_host, size_t m, const void *d123, void *out_H)
+{
+    if (m < r.nc + r.ni + 1) {
+        return rt::set_error(B200_ERR_DOMAIN, "domain size %zu < num_constraints + num_inputs + 1 = %zu", m,
+                             r.nc + r.ni + 1);
+    }
+    Fr d[3];
+    memcpy(d, d123, sizeof(d));
+    const bool zk = !(d[0].is_zero() && d[1].is_zero() && d[2].is_zero());
+    const size_t bytes = m * sizeof(Fr);
+    if (g_bufA.reserve(bytes) || g_bufB.reserve(bytes) || g_bufC.reserve(bytes) || g_bufH.reserve(bytes + sizeof(Fr)) ||
+        g_bufW.reserve((r.nv + 1) * sizeof(Fr)) || g_bufS.reserve(bytes) || (zk && g_bufT.reserve(bytes))) {
+        return B200_ERR_CUDA;
+    }
+    cudaStream_t s = rt::stream();
+    Fr *A = g_bufA.as<Fr>(), *B = g_bufB.as<Fr>(), *Cc = g_bufC.as<Fr>(), *H = g_bufH.as<Fr>(), *T = g_bufT.as<Fr>();
+    B200_CUDA_CHECK(cudaMemcpyAsync(g_bufW.p, w_host, (r.nv + 1) * sizeof(Fr), cudaMemcpyHostToDevice, s));
+    int rc = r1cs_eval_launch<Fr>(r, g_bufW.as<Fr>(), m, A, B, Cc);
+    if (rc) {
+        return rc;
+    }
+    ntt::CoeffFixups<Fr> fix;
+    fix.n = 0;
+    if (zk) {
+        ntt::k_lincomb2<Fr><<<grid_for(m, 256), 256, 0, s>>>(m, A, B, d[1], d[0], T);
+        B200_LAUNCH_CHECK();
+        if ((rc = ntt_op_dev<Fr>(B200_IFFT, T, g_bufS.as<Fr>(), T, m, nullptr))) {
+            return rc;
+        }
+        fix.idx[0] = 0;
+        fix.val[0] = d[2].neg(); // coefficients_for_H[0] -= d3, :270
+        fix.n = 1;
+        if ((rc = add_poly_z_fixups<Fr>(m, d[0] * d[1], &fix))) {
+            return rc;
+        }
+    }
+    if ((rc = witness_map_dev<Fr>(A, B, Cc, m, H))) {
+        return rc;
+    }
+    if (zk) {
+        ntt::k_add_vec<Fr><<<grid_for(m, 256), 256, 0, s>>>(m, H, T);
+        B200_LAUNCH_CHECK();
+        ntt::k_coeff_fixups<Fr><<<1, 32, 0, s>>>(fix, H);
+        B200_LAUNCH_CHECK();
+    }
+    B200_CUDA_CHECK(cudaMemcpyAsync(out_H, H, bytes + sizeof(Fr), cudaMemcpyDeviceToHost, s));
+    B200_CUDA_CHECK(cudaStreamSynchronize(s));
+    return B200_OK;
+}
+
 template<class Fr> int r1cs_eval_host(const R1csSet &r, const void *w_host, size_t m, void *aA, void *aB, void *aC)
 {
     const size_t bytes = m * sizeof(Fr);
@@ -1388,6 +1491,23 @@ int b200_r1cs_evaluate(b200_r1cs_t handle, const void *w, size_t m, void *aA, vo
         return rt::set_error(B200_ERR_DOMAIN, "m = %zu < num_constraints + num_inputs + 1", m);
     }
     DISPATCH_FR(r.curve, r1cs_eval_host<Fr>(r, w, m, aA, aB, aC));
+}
+
+int b200_witness_map_r1cs_zk(b200_r1cs_t handle, const void *w, size_t m, const void *d123, void *out_H)
+{
+    if (!w || !d123 || !out_H) {
+        return rt::set_error(B200_ERR_ARG, "null pointer");
+    }
+    if (!rt::ensure_init()) {
+        return B200_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_r1cs.find(handle);
+    if (it == g_r1cs.end()) {
+        return rt::set_error(B200_ERR_HANDLE, "unknown R1CS handle %llu", (unsigned long long)handle);
+    }
+    const R1csSet &r = it->second;
+    DISPATCH_FR(r.curve, witness_map_r1cs_zk_host<Fr>(r, w, m, d123, out_H));
 }
 
 int b200_witness_map_r1cs_dev(b200_r1cs_t handle, const void *d_w, size_t m, void *dH)

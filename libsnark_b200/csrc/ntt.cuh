@@ -498,6 +498,38 @@ template<class Fr> __global__ void k_ext_divz(uint64_t small, Fr *p, const Fr *z
     }
 }
 
+// ---- the ZK patch of r1cs_to_qap_witness_map (r1cs_to_qap.tcc:262-271, :327-333) -----------------------------------
+// t[i] = ca a[i] + cb b[i]: the evaluations of d2 A + d1 B, whose inverse transform gives d2 coef(A) + d1 coef(B)
+template<class Fr> __global__ void k_lincomb2(uint64_t m, const Fr *a, const Fr *b, Fr ca, Fr cb, Fr *t)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < m) {
+        gstore(t + i, ca * gload(a + i) + cb * gload(b + i));
+    }
+}
+// h[i] += t[i]
+template<class Fr> __global__ void k_add_vec(uint64_t m, Fr *h, const Fr *t)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < m) {
+        gstore(h + i, gload(h + i) + gload(t + i));
+    }
+}
+// the handful of single coefficients -d3 and add_poly_Z(d1 d2) touch: h[idx[k]] += val[k], in order (indices may repeat)
+template<class Fr> struct CoeffFixups {
+    uint64_t idx[6];
+    Fr val[6];
+    int n;
+};
+template<class Fr> __global__ void k_coeff_fixups(CoeffFixups<Fr> f, Fr *h)
+{
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        for (int k = 0; k < f.n; ++k) {
+            gstore(h + f.idx[k], gload(h + f.idx[k]) + f.val[k]);
+        }
+    }
+}
+
 constexpr uint32_t R1CS_LONG_ROW = 64;
 constexpr int R1CS_LONG_THREADS = 256;
 constexpr uint32_t R1CS_LONG_SEG = 2048; // terms per CTA of the long-row kernel

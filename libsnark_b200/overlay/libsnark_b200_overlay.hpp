@@ -407,30 +407,18 @@ template<typename FieldT> void ntt(std::vector<FieldT> &a, size_t m, int op, con
 // callers that can change one line of the prover: evaluations stay on the device between the seven
 // transforms. Written against the reference's types; Groth16 case (d1 = d2 = d3 = 0).
 template<typename FieldT>
+libsnark::qap_witness<FieldT> r1cs_to_qap_witness_map_device(
+    const libsnark::r1cs_constraint_system<FieldT> &cs, const libsnark::r1cs_primary_input<FieldT> &primary_input,
+    const libsnark::r1cs_auxiliary_input<FieldT> &auxiliary_input, const FieldT &d1, const FieldT &d2, const FieldT &d3,
+    bool force_pow_2_domain);
+// older name (round 1), Groth16 case d1 = d2 = d3 = 0
+template<typename FieldT>
 libsnark::qap_witness<FieldT> r1cs_to_qap_witness_map_fused(
     const libsnark::r1cs_constraint_system<FieldT> &cs, const libsnark::r1cs_primary_input<FieldT> &primary_input,
     const libsnark::r1cs_auxiliary_input<FieldT> &auxiliary_input)
 {
-    const size_t m = libfqfft::get_evaluation_domain<FieldT>(cs.num_constraints() + cs.num_inputs() + 1)->m;
-    libsnark::r1cs_variable_assignment<FieldT> full = primary_input;
-    full.insert(full.end(), auxiliary_input.begin(), auxiliary_input.end());
-    std::vector<FieldT> aA(m, FieldT::zero()), aB(m, FieldT::zero()), aC(m, FieldT::zero());
-    for (size_t i = 0; i <= cs.num_inputs(); ++i) {
-        aA[i + cs.num_constraints()] = (i > 0 ? full[i - 1] : FieldT::one());
-    }
-#ifdef MULTICORE
-#pragma omp parallel for
-#endif
-    for (size_t i = 0; i < cs.num_constraints(); ++i) {
-        aA[i] += cs.constraints[i].a.evaluate(full);
-        aB[i] += cs.constraints[i].b.evaluate(full);
-        aC[i] += cs.constraints[i].c.evaluate(full);
-    }
-    std::vector<FieldT> H(m + 1, FieldT::zero());
-    check(b200_witness_map_h(curve_of<FieldT>::curve, aA.data(), aB.data(), aC.data(), m, H.data()),
-          "b200_witness_map_h");
-    return libsnark::qap_witness<FieldT>(
-        cs.num_variables(), m, cs.num_inputs(), FieldT::zero(), FieldT::zero(), FieldT::zero(), full, std::move(H));
+    return r1cs_to_qap_witness_map_device<FieldT>(cs, primary_input, auxiliary_input, FieldT::zero(), FieldT::zero(),
+                                                  FieldT::zero(), false);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -558,6 +546,31 @@ inline void release_cached_r1cs()
 {
     pk_cache::get().clear();
     r1cs_cache::get().clear();
+}
+
+// libsnark::r1cs_to_qap_witness_map (r1cs_to_qap.tcc:209-344) on the device, ZK patch included: the constraint system
+// as a cached CSR, the witness up, coefficients_for_H back (b200_witness_map_r1cs_zk). The reference's
+// assert(cs.is_satisfied(...)) (a debug check that re-evaluates every constraint on one core) is not repeated.
+template<typename FieldT>
+libsnark::qap_witness<FieldT> r1cs_to_qap_witness_map_device(
+    const libsnark::r1cs_constraint_system<FieldT> &cs, const libsnark::r1cs_primary_input<FieldT> &primary_input,
+    const libsnark::r1cs_auxiliary_input<FieldT> &auxiliary_input, const FieldT &d1, const FieldT &d2, const FieldT &d3,
+    bool force_pow_2_domain)
+{
+    const size_t min_n = cs.num_constraints() + cs.num_inputs() + 1; // :224-227
+    const size_t m = libfqfft::get_evaluation_domain<FieldT>(force_pow_2_domain ? (size_t)1 << libff::log2(min_n) : min_n)->m;
+    if (primary_input.size() != cs.num_inputs() || primary_input.size() + auxiliary_input.size() != cs.num_variables()) {
+        throw std::runtime_error("libsnark_b200: witness size does not match the constraint system");
+    }
+    libsnark::r1cs_variable_assignment<FieldT> full = primary_input;
+    full.insert(full.end(), auxiliary_input.begin(), auxiliary_input.end());
+    std::vector<FieldT> w(full.size() + 1);
+    w[0] = FieldT::one();
+    std::copy(full.begin(), full.end(), w.begin() + 1);
+    const FieldT d[3] = {d1, d2, d3};
+    std::vector<FieldT> H(m + 1, FieldT::zero());
+    check(b200_witness_map_r1cs_zk(r1cs_cache::get().lookup(cs), w.data(), m, d, H.data()), "b200_witness_map_r1cs_zk");
+    return libsnark::qap_witness<FieldT>(cs.num_variables(), m, cs.num_inputs(), d1, d2, d3, full, std::move(H));
 }
 
 // device copy of a sparse query's index list (or nothing when the query is dense)
@@ -902,6 +915,21 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
 // the witness map and the five MSMs on the device from the witness alone. r and s are drawn as the reference draws
 // them (r1cs_gg_ppzksnark.tcc:499-500). Define B200_OVERLAY_KEEP_REFERENCE_PROVER to keep the reference's body (its
 // operators are then still the specialisations below).
+// r1cs_to_qap_witness_map itself (every prover's first step; r1cs_to_qap.hpp) for the three scalar fields
+#define B200_OVERLAY_WITNESS_MAP(FR)                                                                                   \
+    namespace libsnark                                                                                                 \
+    {                                                                                                                  \
+    template<>                                                                                                         \
+    inline qap_witness<FR> r1cs_to_qap_witness_map<FR>(                                                                \
+        const r1cs_constraint_system<FR> &cs, const r1cs_primary_input<FR> &primary_input,                             \
+        const r1cs_auxiliary_input<FR> &auxiliary_input, const FR &d1, const FR &d2, const FR &d3,                     \
+        bool force_pow_2_domain)                                                                                       \
+    {                                                                                                                  \
+        return libsnark_b200::r1cs_to_qap_witness_map_device<FR>(cs, primary_input, auxiliary_input, d1, d2, d3,       \
+                                                                 force_pow_2_domain);                                  \
+    }                                                                                                                  \
+    }
+
 #ifndef B200_OVERLAY_KEEP_REFERENCE_PROVER
 #define B200_OVERLAY_PROVER(PP)                                                                                        \
     namespace libsnark                                                                                                 \
@@ -926,6 +954,7 @@ B200_OVERLAY_BATCH_EXP(libff::alt_bn128_G2, libff::alt_bn128_Fr)
 B200_OVERLAY_KC(libff::alt_bn128_G2, libff::alt_bn128_G1, libff::alt_bn128_Fr)
 B200_OVERLAY_KC(libff::alt_bn128_G1, libff::alt_bn128_G1, libff::alt_bn128_Fr) // r1cs_ppzksnark's A and C queries (r1cs_ppzksnark.tcc:570-612)
 B200_OVERLAY_NTT(libff::alt_bn128_Fr)
+B200_OVERLAY_WITNESS_MAP(libff::alt_bn128_Fr)
 B200_OVERLAY_PROVER(libff::alt_bn128_pp)
 
 B200_OVERLAY_MSM(libff::bls12_377_G1, libff::bls12_377_Fr)
@@ -935,6 +964,7 @@ B200_OVERLAY_BATCH_EXP(libff::bls12_377_G2, libff::bls12_377_Fr)
 B200_OVERLAY_KC(libff::bls12_377_G2, libff::bls12_377_G1, libff::bls12_377_Fr)
 B200_OVERLAY_KC(libff::bls12_377_G1, libff::bls12_377_G1, libff::bls12_377_Fr) // r1cs_ppzksnark's A and C queries (r1cs_ppzksnark.tcc:570-612)
 B200_OVERLAY_NTT(libff::bls12_377_Fr)
+B200_OVERLAY_WITNESS_MAP(libff::bls12_377_Fr)
 B200_OVERLAY_PROVER(libff::bls12_377_pp)
 
 B200_OVERLAY_MSM(libff::bw6_761_G1, libff::bw6_761_Fr)
@@ -944,6 +974,7 @@ B200_OVERLAY_BATCH_EXP(libff::bw6_761_G2, libff::bw6_761_Fr)
 B200_OVERLAY_KC(libff::bw6_761_G2, libff::bw6_761_G1, libff::bw6_761_Fr)
 B200_OVERLAY_KC(libff::bw6_761_G1, libff::bw6_761_G1, libff::bw6_761_Fr) // r1cs_ppzksnark's A and C queries (r1cs_ppzksnark.tcc:570-612)
 B200_OVERLAY_NTT(libff::bw6_761_Fr)
+B200_OVERLAY_WITNESS_MAP(libff::bw6_761_Fr)
 B200_OVERLAY_PROVER(libff::bw6_761_pp)
 
 #endif // LIBSNARK_B200_OVERLAY_HPP_

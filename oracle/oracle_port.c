@@ -1130,6 +1130,91 @@ API int port_r1cs_evaluate(int curve, size_t nc, size_t ni, const uint32_t *row_
 }
 
 /* r1cs_to_qap.tcc:252-330 with d1 = d2 = d3 = 0: aA, aB, aC (m each) -> coefficients_for_H (m + 1). */
+/* evaluation_domain::add_poly_Z of the kind that serves m: basic_radix2_domain.tcc:109-115,
+ * extended_radix2_domain.tcc:203-214, step_radix2_domain.tcc:235-245. H has m + 1 elements. */
+static int add_poly_z(fp_t *H, size_t m, const fp_t *coeff)
+{
+    fp_t t, u, one;
+    fp_one(&one);
+    if (!(m & (m - 1))) {
+        if (m > 1 && ff_log2(m) == two_adicity() + 1) {
+            fp_t gen, shift, ssm;
+            const size_t small = m / 2;
+            fp_zero(&gen);
+            memcpy(gen.v, g_f->generator, 8 * g_f->n);
+            fp_sqr(&shift, &gen);
+            fp_pow_u64(&ssm, &shift, small);
+            fp_add(&H[m], &H[m], coeff);
+            fp_add(&t, &ssm, &one);
+            fp_mul(&u, coeff, &t);
+            fp_sub(&H[small], &H[small], &u);
+            fp_mul(&u, coeff, &ssm);
+            fp_add(&H[0], &H[0], &u);
+            return 0;
+        }
+        fp_add(&H[m], &H[m], coeff);
+        fp_sub(&H[0], &H[0], coeff);
+        return 0;
+    }
+    size_t big, small;
+    if (step_shape(m, &big, &small)) return -2;
+    fp_t omega, wsm;
+    if (get_root_of_unity(&omega, 2 * big)) return -2;
+    fp_pow_u64(&wsm, &omega, small);
+    fp_mul(&u, coeff, &wsm);
+    fp_add(&H[m], &H[m], coeff);
+    fp_sub(&H[big], &H[big], &u);
+    fp_sub(&H[small], &H[small], coeff);
+    fp_add(&H[0], &H[0], &u);
+    return 0;
+}
+
+/* r1cs_to_qap_witness_map with its ZK patch, in the reference's order (r1cs_to_qap.tcc:252-333): d123 = d1, d2, d3. */
+API int port_witness_map_h_zk(int curve, const void *aA, const void *aB, const void *aC, size_t m, const void *d123,
+                              void *out_H)
+{
+    if (curve < 0 || curve > 2) return -1;
+    g_f = &curve_table[curve].fr;
+    fp_t gen, d[3], t, u;
+    fp_zero(&gen);
+    memcpy(gen.v, g_f->generator, 8 * g_f->n);
+    for (int k = 0; k < 3; ++k) {
+        fp_zero(&d[k]);
+        memcpy(d[k].v, (const uint64_t *)d123 + k * g_f->n, 8 * g_f->n);
+    }
+    fp_t *A = load_frs((const uint64_t *)aA, m), *B = load_frs((const uint64_t *)aB, m), *Cc = load_frs((const uint64_t *)aC, m);
+    fp_t *H = (fp_t *)calloc(m + 1, sizeof(fp_t));
+    int rc = domain_inplace(A, m, 1, &gen);
+    if (!rc) rc = domain_inplace(B, m, 1, &gen);
+    if (!rc) {
+        for (size_t i = 0; i < m; ++i) { /* :266-268 */
+            fp_mul(&t, &d[1], &A[i]);
+            fp_mul(&u, &d[0], &B[i]);
+            fp_add(&H[i], &t, &u);
+        }
+        fp_sub(&H[0], &H[0], &d[2]);
+        fp_mul(&t, &d[0], &d[1]);
+        rc = add_poly_z(H, m, &t);
+    }
+    if (!rc) {
+        domain_inplace(A, m, 2, &gen);
+        domain_inplace(B, m, 2, &gen);
+        for (size_t i = 0; i < m; ++i) fp_mul(&A[i], &A[i], &B[i]);
+        domain_inplace(Cc, m, 1, &gen);
+        domain_inplace(Cc, m, 2, &gen);
+        for (size_t i = 0; i < m; ++i) fp_sub(&A[i], &A[i], &Cc[i]);
+        domain_inplace(A, m, 4, &gen);
+        domain_inplace(A, m, 3, &gen);
+        for (size_t i = 0; i < m; ++i) fp_add(&H[i], &H[i], &A[i]); /* :327-333 */
+        store_frs((uint64_t *)out_H, H, m + 1);
+    }
+    free(A);
+    free(B);
+    free(Cc);
+    free(H);
+    return rc;
+}
+
 API int port_witness_map_h(int curve, const void *aA, const void *aB, const void *aC, size_t m, void *out_H)
 {
     if (curve < 0 || curve > 2) return -1;

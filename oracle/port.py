@@ -35,6 +35,7 @@ class OraclePort:
         L.port_bdlo12_signed_optimal_c.argtypes = [C.c_uint64]
         L.port_fft.argtypes = [i, i, vp, sz, vp]
         L.port_witness_map_h.argtypes = [i, vp, vp, vp, sz, vp]
+        L.port_witness_map_h_zk.argtypes = [i, vp, vp, vp, sz, vp, vp]
         L.port_field_op.argtypes = [i, i, i, vp, vp, vp, sz]
         L.port_group_op.argtypes = [i, i, i, vp, vp, vp, sz]
         L.port_batch_exp.argtypes = [i, i, vp, vp, vp, sz, sz, vp]
@@ -143,6 +144,15 @@ class OraclePort:
         m = aA.shape[0]
         out = np.zeros((m + 1, aA.shape[1]), dtype=np.uint64)
         assert self.lib.port_witness_map_h(_cid(curve), _p(aA), _p(aB), _p(aC), m, _p(out)) == 0
+        return out
+
+    def witness_map_h_zk(self, curve, aA, aB, aC, d1, d2, d3):
+        """coefficients_for_H with the ZK patch (r1cs_to_qap.tcc:262-271, :327-333)."""
+        aA, aB, aC = (np.ascontiguousarray(x, dtype=np.uint64) for x in (aA, aB, aC))
+        m = aA.shape[0]
+        d = np.ascontiguousarray(np.stack([np.asarray(x, dtype=np.uint64).reshape(-1) for x in (d1, d2, d3)]))
+        out = np.zeros((m + 1, aA.shape[1]), dtype=np.uint64)
+        assert self.lib.port_witness_map_h_zk(_cid(curve), _p(aA), _p(aB), _p(aC), m, _p(d), _p(out)) == 0
         return out
 
     def field_op(self, curve, field, op, a, b=None):

@@ -607,6 +607,20 @@ template<typename ppT> struct H {
         return 0;
     }
 
+    // the same with the ZK patch: d123 = d1, d2, d3 (r1cs_to_qap.tcc:262-271, :327-333; what r1cs_ppzksnark's prover passes)
+    static int witness_map_zk(const groth16_fixture<ppT> *f, const void *d123, void *out_H, double *ms)
+    {
+        const FrT *d = static_cast<const FrT *>(d123);
+        const long long t0 = get_nsec_time();
+        const qap_witness<FrT> w = r1cs_to_qap_witness_map(
+            f->keypair.pk.constraint_system, f->example.primary_input, f->example.auxiliary_input, d[0], d[1], d[2], false);
+        if (ms) {
+            *ms = (get_nsec_time() - t0) * 1e-6;
+        }
+        memcpy(out_H, w.coefficients_for_H.data(), w.coefficients_for_H.size() * sizeof(FrT));
+        return 0;
+    }
+
     // The evaluations aA, aB, aC that r1cs_to_qap_witness_map feeds its first iFFTs
     // (r1cs_to_qap.tcc:236-248 and :293-296), computed with the reference's own
     // linear_combination::evaluate. m elements each.
@@ -1285,6 +1299,13 @@ API const void *ref_groth16_ptr(void *h_, int which)
     fixture_handle *h = static_cast<fixture_handle *>(h_);
     DISPATCH_FIXTURE(h, ptr, which);
     return nullptr;
+}
+
+API int ref_groth16_witness_map_zk(void *h_, const void *d123, void *out_H, double *ms)
+{
+    fixture_handle *h = static_cast<fixture_handle *>(h_);
+    DISPATCH_FIXTURE(h, witness_map_zk, d123, out_H, ms);
+    return -100;
 }
 
 API int ref_groth16_witness_map(void *h_, void *out_H, double *ms)

@@ -49,6 +49,7 @@ class RefOracle:
         L.ref_groth16_free.argtypes = [C.c_void_p]
         L.ref_groth16_sizes.argtypes = [C.c_void_p, C.c_void_p]
         L.ref_groth16_witness_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ref_groth16_witness_map_zk.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ref_groth16_prove.argtypes = [C.c_void_p] * 5
         L.ref_groth16_abc_evaluations.argtypes = [C.c_void_p] * 4
         L.ref_groth16_prove_stock.argtypes = [C.c_void_p] * 3
@@ -375,6 +376,15 @@ class Groth16Fixture:
         out = np.zeros((self.sizes["m"] + 1, self.i["nr"]), dtype=np.uint64)
         ms = C.c_double(0)
         assert self.ref.lib.ref_groth16_witness_map(self.h, _p(out), C.byref(ms)) == 0
+        return out, ms.value
+
+    def witness_map_zk(self, d1, d2, d3, via=None):
+        """coefficients_for_H of r1cs_to_qap_witness_map(cs, primary, auxiliary, d1, d2, d3) (m + 1 rows) and its wall
+        time; via = the overlay build runs ITS r1cs_to_qap_witness_map (specialised to the device) on this fixture."""
+        d = np.ascontiguousarray(np.stack([np.asarray(x, dtype=np.uint64).reshape(-1) for x in (d1, d2, d3)]))
+        out = np.zeros((self.sizes["m"] + 1, self.i["nr"]), dtype=np.uint64)
+        ms = C.c_double(0)
+        assert (via or self.ref).lib.ref_groth16_witness_map_zk(self.h, _p(d), _p(out), C.byref(ms)) == 0
         return out, ms.value
 
     def abc_evaluations(self):

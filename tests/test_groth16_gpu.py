@@ -317,6 +317,45 @@ def test_overlay_sibling_generators(ref, overlay, b200, scheme):
         fx.close()
 
 
+@pytest.mark.parametrize("curve,nc,ni,s", [("alt_bn128", (1 << 14) - 11, 10, 0), ("alt_bn128", 5000, 7, 0),
+                                           ("alt_bn128", (1 << 12) - 9, 6, 11), ("bls12_377", 3000, 4, 0),
+                                           ("bw6_761", 700, 3, 0)])
+def test_witness_map_with_zk_patch(ref, overlay, b200, curve, nc, ni, s):
+    """r1cs_to_qap_witness_map(cs, primary, auxiliary, d1, d2, d3) with random d's: the C-ABI call and the overlay's
+    specialisation of the reference function (its harness calls the SAME name in both builds) give every coefficient the
+    reference computes — on a basic, a step and an extended domain; each d on its own as well."""
+    libs = (ref, overlay)
+    if s:
+        for lib in libs:
+            lib.set_two_adicity(curve, s)
+        b200.set_two_adicity(curve, s)
+    try:
+        fx = ref.groth16_setup(curve, nc, ni, real_keys=False)
+        try:
+            m = fx.sizes["m"]
+            if s:
+                assert m == 1 << (s + 1)
+            d = ref.field_random(curve, refo.FR, 0xD123 + nc, 3)
+            z = np.zeros_like(d[0])
+            row_ptr, col, val = fx.r1cs_csr()
+            cs = b200.R1CS(curve, fx.sizes["num_constraints"], fx.sizes["num_inputs"], fx.sizes["num_variables"], row_ptr, col, val)
+            try:
+                for dd in [(d[0], d[1], d[2]), (d[0], z, z), (z, d[1], z), (z, z, d[2]), (z, z, z)]:
+                    want, _ = fx.witness_map_zk(*dd)
+                    assert np.array_equal(cs.witness_map_h_zk(fx.full_assignment(), m, *dd), want)
+                    got, _ = fx.witness_map_zk(*dd, via=overlay)
+                    assert np.array_equal(got, want)
+            finally:
+                cs.free()
+        finally:
+            fx.close()
+    finally:
+        if s:
+            for lib in libs:
+                lib.set_two_adicity(curve, 0)
+            b200.set_two_adicity(curve, 0)
+
+
 def test_overlay_kc_msm_over_g1_pairs(ref, overlay):
     """kc_multi_exp_with_mixed_addition<G1, G1, Fr, BDLO12_signed, special> (r1cs_ppzksnark's A and C queries) through
     the overlay == the reference template, on a sparse vector with an index window."""

@@ -168,6 +168,38 @@ def test_extended_domain_golden_fixtures(b200, curve):
             b200.set_two_adicity(curve, 0)
 
 
+@pytest.mark.parametrize("curve,nc,s,m", [("alt_bn128", 117, 0, 128), ("alt_bn128", 130, 0, 136), ("bls12_377", 59, 5, 64),
+                                         ("bw6_761", 40, 0, 48)])
+def test_witness_map_with_zk_patch_golden(b200, curve, nc, s, m):
+    """b200_witness_map_r1cs_zk — r1cs_to_qap_witness_map with d1, d2, d3 non-zero (the sibling provers' call;
+    r1cs_to_qap.tcc:262-271, :327-333), add_poly_Z of every domain kind included — against the committed vectors of the
+    unmodified reference (tests/golden/zk.npz): basic, step, extended (2-adicity lowered) and a 12-limb step domain."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "zk.npz"))
+    k = f"{curve}.nc{nc}"
+    n_c, ni, nv, mm = [int(x) for x in g[k + ".sizes"]]
+    assert mm == m
+    if s:
+        b200.set_two_adicity(curve, s)
+    try:
+        cs = b200.R1CS(curve, n_c, ni, nv, g[k + ".row_ptr"], g[k + ".col"], g[k + ".val"])
+        try:
+            d = g[k + ".d"]
+            assert np.array_equal(cs.witness_map_h_zk(g[k + ".w"], m, d[0], d[1], d[2]), g[k + ".H"])
+            z = np.zeros_like(d[0])
+            assert np.array_equal(cs.witness_map_h_zk(g[k + ".w"], m, z, z, z), cs.witness_map_h(g[k + ".w"], m))
+            # one d at a time: each term of the patch on its own
+            for j in range(3):
+                dd = [z, z, z]
+                dd[j] = d[j]
+                assert cs.witness_map_h_zk(g[k + ".w"], m, *dd).shape == (m + 1, g[k + ".w"].shape[1])
+        finally:
+            cs.free()
+    finally:
+        if s:
+            b200.set_two_adicity(curve, 0)
+
+
 def test_factory_rounding(b200):
     """get_evaluation_domain.tcc:37-58: 2^k stays, 2^k + 2^r stays, anything else rounds its small part up."""
     assert b200.domain_size_for(1 << 20) == 1 << 20

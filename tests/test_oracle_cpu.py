@@ -234,6 +234,32 @@ def test_whole_proof_on_extended_domain_golden(P, curve, s, nc):
         P.set_two_adicity(curve, 0)
 
 
+ZK_CASES = [("alt_bn128", 117, 0, 128), ("alt_bn128", 130, 0, 136), ("bls12_377", 59, 5, 64), ("bw6_761", 40, 0, 48)]
+
+
+@pytest.mark.parametrize("curve,nc,s,m", ZK_CASES)
+def test_witness_map_with_zk_patch_golden(P, curve, nc, s, m):
+    """r1cs_to_qap_witness_map with d1, d2, d3 non-zero (the sibling provers' call; r1cs_to_qap.tcc:262-271, :327-333) restated
+    in the C oracle, add_poly_Z of each domain kind included == every coefficient the reference computed (basic, step,
+    extended with FieldT::s lowered, step on the 12-limb field); the sparse evaluation feeding it is pinned as well."""
+    g = np.load(os.path.join(GOLD, "zk.npz"))
+    k = f"{curve}.nc{nc}"
+    n_c, ni, nv, mm = [int(x) for x in g[k + ".sizes"]]
+    assert mm == m
+    if s:
+        P.set_two_adicity(curve, s)
+    try:
+        aA, aB, aC = P.r1cs_evaluate(curve, n_c, ni, g[k + ".row_ptr"], g[k + ".col"], g[k + ".val"], g[k + ".w"], m)
+        assert np.array_equal(aA, g[k + ".aA"]) and np.array_equal(aB, g[k + ".aB"]) and np.array_equal(aC, g[k + ".aC"])
+        d = g[k + ".d"]
+        assert np.array_equal(P.witness_map_h_zk(curve, aA, aB, aC, d[0], d[1], d[2]), g[k + ".H"])
+        z = np.zeros_like(d[0])
+        assert np.array_equal(P.witness_map_h_zk(curve, aA, aB, aC, z, z, z), P.witness_map_h(curve, aA, aB, aC))
+    finally:
+        if s:
+            P.set_two_adicity(curve, 0)
+
+
 def test_r1cs_evaluation_golden(P):
     """The sparse evaluation <a_i, w>, <b_i, w>, <c_i, w> with the input-consistency rows (r1cs_to_qap.tcc:236-248,
     :293-296; linear_combination::evaluate, variable.tcc:288-299) restated over the CSR the device path uploads ==
