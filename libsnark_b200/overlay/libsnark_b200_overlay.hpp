@@ -56,6 +56,7 @@
 #include <libfqfft/tools/exceptions.hpp>
 #include <libsnark/knowledge_commitment/kc_multiexp.hpp>
 #include <libsnark/reductions/r1cs_to_qap/r1cs_to_qap.hpp>
+#include <libsnark/reductions/r1cs_to_sap/r1cs_to_sap.hpp>
 #include <libsnark/zk_proof_systems/ppzksnark/r1cs_gg_ppzksnark/r1cs_gg_ppzksnark.hpp>
 
 #include "libsnark_b200.h"
@@ -548,6 +549,74 @@ inline void release_cached_r1cs()
     r1cs_cache::get().clear();
 }
 
+// libsnark::r1cs_to_sap_witness_map (r1cs_to_sap.tcc:297-481; the witness map of r1cs_se_ppzksnark): the values of the
+// constraints' three linear combinations come from the device's sparse evaluation (the reference evaluates a and b four
+// times each per constraint on one core), the SAP vectors are formed on the host from them with additions only, and
+// H = (A^2 - C) / Z runs as one device pipeline (b200_witness_map_h with B = A); the ZK patch 2 d1 coef(A) - d2 + d1^2 Z
+// costs one more inverse transform. Exact field arithmetic: every coefficient equals the reference's.
+template<typename FieldT>
+libsnark::sap_witness<FieldT> r1cs_to_sap_witness_map_device(
+    const libsnark::r1cs_constraint_system<FieldT> &cs, const libsnark::r1cs_primary_input<FieldT> &primary_input,
+    const libsnark::r1cs_auxiliary_input<FieldT> &auxiliary_input, const FieldT &d1, const FieldT &d2)
+{
+    const size_t nc = cs.num_constraints(), ni = cs.num_inputs(), nv = cs.num_variables();
+    if (primary_input.size() != ni || primary_input.size() + auxiliary_input.size() != nv) {
+        throw std::runtime_error("libsnark_b200: witness size does not match the constraint system");
+    }
+    const std::shared_ptr<libfqfft::evaluation_domain<FieldT>> domain = libsnark::r1cs_to_sap_get_domain(cs);
+    const size_t m = domain->m;
+    libsnark::r1cs_variable_assignment<FieldT> full = primary_input;
+    full.insert(full.end(), auxiliary_input.begin(), auxiliary_input.end());
+    std::vector<FieldT> w(nv + 1);
+    w[0] = FieldT::one();
+    std::copy(full.begin(), full.end(), w.begin() + 1);
+    const size_t mr = nc + ni + 1; // rows [0, nc) of ea, eb, ec are <a_i, w>, <b_i, w>, <c_i, w>
+    std::vector<FieldT> ea(mr), eb(mr), ec(mr);
+    check(b200_r1cs_evaluate(r1cs_cache::get().lookup(cs), w.data(), mr, ea.data(), eb.data(), ec.data()), "b200_r1cs_evaluate");
+    const FieldT one = FieldT::one();
+    full.reserve(nv + nc + ni);
+    for (size_t i = 0; i < nc; ++i) { // :330-341, (a - b)^2
+        const FieldT t = ea[i] - eb[i];
+        full.push_back(t * t);
+    }
+    for (size_t i = 1; i <= ni; ++i) { // :342-351, (x_i - 1)^2
+        const FieldT t = full[i - 1] - one;
+        full.push_back(t * t);
+    }
+    auto times_four = [](const FieldT &x) {
+        const FieldT two = x + x;
+        return two + two;
+    };
+    std::vector<FieldT> aA(m, FieldT::zero()), aC(m, FieldT::zero());
+    const size_t off = 2 * nc, evo = nv + 1, evo2 = nv + nc;
+    for (size_t i = 0; i < nc; ++i) { // :357-363, :414-420
+        aA[2 * i] = ea[i] + eb[i];
+        aA[2 * i + 1] = ea[i] - eb[i];
+        aC[2 * i] = times_four(ec[i]) + full[evo + i - 1];
+        aC[2 * i + 1] = full[evo + i - 1];
+    }
+    aA[off] = one; // :367, :423
+    aC[off] = one;
+    for (size_t i = 1; i <= ni; ++i) { // :369-375, :425-433
+        aA[off + 2 * i - 1] = full[i - 1] + one;
+        aA[off + 2 * i] = full[i - 1] - one;
+        aC[off + 2 * i - 1] = times_four(full[i - 1]) + full[evo2 + i - 1];
+        aC[off + 2 * i] = full[evo2 + i - 1];
+    }
+    std::vector<FieldT> H(m + 1, FieldT::zero());
+    check(b200_witness_map_h(curve_of<FieldT>::curve, aA.data(), aA.data(), aC.data(), m, H.data()), "b200_witness_map_h");
+    if (!(d1.is_zero() && d2.is_zero())) { // :388-393 and :461-469
+        check(b200_ntt(curve_of<FieldT>::curve, B200_IFFT, aA.data(), m, nullptr), "b200_ntt");
+        const FieldT two_d1 = d1 + d1;
+        for (size_t i = 0; i < m; ++i) {
+            H[i] += two_d1 * aA[i];
+        }
+        H[0] -= d2;
+        domain->add_poly_Z(d1 * d1, H);
+    }
+    return libsnark::sap_witness<FieldT>(nv + nc + ni, m, ni, d1, d2, full, std::move(H));
+}
+
 // libsnark::r1cs_to_qap_witness_map (r1cs_to_qap.tcc:209-344) on the device, ZK patch included: the constraint system
 // as a cached CSR, the witness up, coefficients_for_H back (b200_witness_map_r1cs_zk). The reference's
 // assert(cs.is_satisfied(...)) (a debug check that re-evaluates every constraint on one core) is not repeated.
@@ -930,6 +999,19 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
     }                                                                                                                  \
     }
 
+// r1cs_to_sap_witness_map (r1cs_se_ppzksnark's first step; r1cs_to_sap.hpp)
+#define B200_OVERLAY_SAP_WITNESS_MAP(FR)                                                                               \
+    namespace libsnark                                                                                                 \
+    {                                                                                                                  \
+    template<>                                                                                                         \
+    inline sap_witness<FR> r1cs_to_sap_witness_map<FR>(                                                                \
+        const r1cs_constraint_system<FR> &cs, const r1cs_primary_input<FR> &primary_input,                             \
+        const r1cs_auxiliary_input<FR> &auxiliary_input, const FR &d1, const FR &d2)                                   \
+    {                                                                                                                  \
+        return libsnark_b200::r1cs_to_sap_witness_map_device<FR>(cs, primary_input, auxiliary_input, d1, d2);          \
+    }                                                                                                                  \
+    }
+
 #ifndef B200_OVERLAY_KEEP_REFERENCE_PROVER
 #define B200_OVERLAY_PROVER(PP)                                                                                        \
     namespace libsnark                                                                                                 \
@@ -955,6 +1037,7 @@ B200_OVERLAY_KC(libff::alt_bn128_G2, libff::alt_bn128_G1, libff::alt_bn128_Fr)
 B200_OVERLAY_KC(libff::alt_bn128_G1, libff::alt_bn128_G1, libff::alt_bn128_Fr) // r1cs_ppzksnark's A and C queries (r1cs_ppzksnark.tcc:570-612)
 B200_OVERLAY_NTT(libff::alt_bn128_Fr)
 B200_OVERLAY_WITNESS_MAP(libff::alt_bn128_Fr)
+B200_OVERLAY_SAP_WITNESS_MAP(libff::alt_bn128_Fr)
 B200_OVERLAY_PROVER(libff::alt_bn128_pp)
 
 B200_OVERLAY_MSM(libff::bls12_377_G1, libff::bls12_377_Fr)
@@ -965,6 +1048,7 @@ B200_OVERLAY_KC(libff::bls12_377_G2, libff::bls12_377_G1, libff::bls12_377_Fr)
 B200_OVERLAY_KC(libff::bls12_377_G1, libff::bls12_377_G1, libff::bls12_377_Fr) // r1cs_ppzksnark's A and C queries (r1cs_ppzksnark.tcc:570-612)
 B200_OVERLAY_NTT(libff::bls12_377_Fr)
 B200_OVERLAY_WITNESS_MAP(libff::bls12_377_Fr)
+B200_OVERLAY_SAP_WITNESS_MAP(libff::bls12_377_Fr)
 B200_OVERLAY_PROVER(libff::bls12_377_pp)
 
 B200_OVERLAY_MSM(libff::bw6_761_G1, libff::bw6_761_Fr)
@@ -975,6 +1059,7 @@ B200_OVERLAY_KC(libff::bw6_761_G2, libff::bw6_761_G1, libff::bw6_761_Fr)
 B200_OVERLAY_KC(libff::bw6_761_G1, libff::bw6_761_G1, libff::bw6_761_Fr) // r1cs_ppzksnark's A and C queries (r1cs_ppzksnark.tcc:570-612)
 B200_OVERLAY_NTT(libff::bw6_761_Fr)
 B200_OVERLAY_WITNESS_MAP(libff::bw6_761_Fr)
+B200_OVERLAY_SAP_WITNESS_MAP(libff::bw6_761_Fr)
 B200_OVERLAY_PROVER(libff::bw6_761_pp)
 
 #endif // LIBSNARK_B200_OVERLAY_HPP_

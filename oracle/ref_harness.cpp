@@ -49,6 +49,7 @@
 #include <libfqfft/polynomial_arithmetic/naive_evaluate.hpp>
 #include <libsnark/knowledge_commitment/kc_multiexp.hpp>
 #include <libsnark/reductions/r1cs_to_qap/r1cs_to_qap.hpp>
+#include <libsnark/reductions/r1cs_to_sap/r1cs_to_sap.hpp>
 #include <libsnark/relations/constraint_satisfaction_problems/r1cs/examples/r1cs_examples.hpp>
 #include <libsnark/zk_proof_systems/ppzksnark/r1cs_gg_ppzksnark/r1cs_gg_ppzksnark.hpp>
 #include <libsnark/zk_proof_systems/ppzksnark/r1cs_ppzksnark/r1cs_ppzksnark.hpp>
@@ -618,6 +619,31 @@ template<typename ppT> struct H {
             *ms = (get_nsec_time() - t0) * 1e-6;
         }
         memcpy(out_H, w.coefficients_for_H.data(), w.coefficients_for_H.size() * sizeof(FrT));
+        return 0;
+    }
+
+    // r1cs_to_sap_witness_map (r1cs_to_sap.tcc:297-481; r1cs_se_ppzksnark's witness map) on the fixture's constraint
+    // system: d12 = d1, d2; out_H gets degree + 1 coefficients (cap elements available), *degree the SAP domain size,
+    // out_extra (optional, nc + ni elements) the extra variables appended to the assignment
+    static int sap_witness_map(const groth16_fixture<ppT> *f, const void *d12, void *out_H, size_t cap, size_t *degree,
+                               void *out_extra, double *ms)
+    {
+        const FrT *d = static_cast<const FrT *>(d12);
+        const long long t0 = get_nsec_time();
+        const sap_witness<FrT> w = r1cs_to_sap_witness_map(
+            f->keypair.pk.constraint_system, f->example.primary_input, f->example.auxiliary_input, d[0], d[1]);
+        if (ms) {
+            *ms = (get_nsec_time() - t0) * 1e-6;
+        }
+        *degree = w.degree();
+        if (w.coefficients_for_H.size() > cap) {
+            return -5;
+        }
+        memcpy(out_H, w.coefficients_for_H.data(), w.coefficients_for_H.size() * sizeof(FrT));
+        if (out_extra) {
+            const size_t nv = f->keypair.pk.constraint_system.num_variables();
+            memcpy(out_extra, w.coefficients_for_ACs.data() + nv, (w.coefficients_for_ACs.size() - nv) * sizeof(FrT));
+        }
         return 0;
     }
 
@@ -1305,6 +1331,14 @@ API int ref_groth16_witness_map_zk(void *h_, const void *d123, void *out_H, doub
 {
     fixture_handle *h = static_cast<fixture_handle *>(h_);
     DISPATCH_FIXTURE(h, witness_map_zk, d123, out_H, ms);
+    return -100;
+}
+
+API int ref_groth16_sap_witness_map(void *h_, const void *d12, void *out_H, size_t cap, size_t *degree, void *out_extra,
+                                    double *ms)
+{
+    fixture_handle *h = static_cast<fixture_handle *>(h_);
+    DISPATCH_FIXTURE(h, sap_witness_map, d12, out_H, cap, degree, out_extra, ms);
     return -100;
 }
 

@@ -50,6 +50,8 @@ class RefOracle:
         L.ref_groth16_sizes.argtypes = [C.c_void_p, C.c_void_p]
         L.ref_groth16_witness_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.ref_groth16_witness_map_zk.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ref_groth16_sap_witness_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t),
+                                                  C.c_void_p, C.POINTER(C.c_double)]
         L.ref_groth16_prove.argtypes = [C.c_void_p] * 5
         L.ref_groth16_abc_evaluations.argtypes = [C.c_void_p] * 4
         L.ref_groth16_prove_stock.argtypes = [C.c_void_p] * 3
@@ -386,6 +388,19 @@ class Groth16Fixture:
         ms = C.c_double(0)
         assert (via or self.ref).lib.ref_groth16_witness_map_zk(self.h, _p(d), _p(out), C.byref(ms)) == 0
         return out, ms.value
+
+    def sap_witness_map(self, d1, d2, via=None):
+        """(coefficients_for_H, extra variables, ms) of r1cs_to_sap_witness_map(cs, primary, auxiliary, d1, d2) on this
+        fixture's constraint system; via = the overlay build's specialisation."""
+        d = np.ascontiguousarray(np.stack([np.asarray(x, dtype=np.uint64).reshape(-1) for x in (d1, d2)]))
+        sz = self.sizes
+        cap = 4 * (sz["num_constraints"] + sz["num_inputs"]) + 8
+        out = np.zeros((cap, self.i["nr"]), dtype=np.uint64)
+        extra = np.zeros((sz["num_constraints"] + sz["num_inputs"], self.i["nr"]), dtype=np.uint64)
+        deg, ms = C.c_size_t(0), C.c_double(0)
+        rc = (via or self.ref).lib.ref_groth16_sap_witness_map(self.h, _p(d), _p(out), cap, C.byref(deg), _p(extra), C.byref(ms))
+        assert rc == 0, rc
+        return out[: deg.value + 1].copy(), extra, ms.value
 
     def abc_evaluations(self):
         """aA, aB, aC of r1cs_to_qap.tcc:236-248/:293-296 (the inputs of the NTT chain)."""

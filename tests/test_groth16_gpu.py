@@ -356,6 +356,25 @@ def test_witness_map_with_zk_patch(ref, overlay, b200, curve, nc, ni, s):
             b200.set_two_adicity(curve, 0)
 
 
+@pytest.mark.parametrize("curve,nc,ni", [("alt_bn128", 4000, 7), ("alt_bn128", (1 << 11) - 3, 2), ("bls12_377", 1500, 4),
+                                         ("bw6_761", 300, 3)])
+def test_overlay_sap_witness_map(ref, overlay, curve, nc, ni):
+    """r1cs_to_sap_witness_map (r1cs_se_ppzksnark's witness map, r1cs_to_sap.tcc:297-481) through the overlay's
+    specialisation == the reference function: every coefficient of H and every extra variable, with random d1, d2, each
+    alone, and zeros; step and basic SAP domains."""
+    fx = ref.groth16_setup(curve, nc, ni, real_keys=False)
+    try:
+        d = ref.field_random(curve, refo.FR, 0x5A9 + nc, 2)
+        z = np.zeros_like(d[0])
+        for dd in [(d[0], d[1]), (d[0], z), (z, d[1]), (z, z)]:
+            want_h, want_x, _ = fx.sap_witness_map(*dd)
+            got_h, got_x, _ = fx.sap_witness_map(*dd, via=overlay)
+            assert want_h.shape[0] >= 2 * nc + 2 * ni + 2
+            assert np.array_equal(got_h, want_h) and np.array_equal(got_x, want_x)
+    finally:
+        fx.close()
+
+
 def test_overlay_kc_msm_over_g1_pairs(ref, overlay):
     """kc_multi_exp_with_mixed_addition<G1, G1, Fr, BDLO12_signed, special> (r1cs_ppzksnark's A and C queries) through
     the overlay == the reference template, on a sparse vector with an index window."""
