@@ -98,7 +98,7 @@ template<class F> struct SrcEntries {
         if (!locate(e, idx)) {
             return null_point<F>();
         }
-        Affine<F> p = load_vec_ro(bases + idx);
+        Affine<F> p = load_vec_gather(bases + idx);
         p.y = p.y.cneg((e >> 31) != 0);
         return p;
     }
@@ -110,7 +110,7 @@ template<class F> struct SrcEntries {
         if (null) {
             return F::zero();
         }
-        return load_vec_ro(&bases[idx].x);
+        return load_vec_gather(&bases[idx].x);
     }
 };
 template<class F> struct SrcPoints {

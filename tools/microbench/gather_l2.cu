@@ -12,6 +12,63 @@
 
 #define CHECK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %d\n", cudaGetErrorString(e), __LINE__); return 1; } } while (0)
 
+// MODE 0: plain ld.global; 1: ld.global.nc (__ldg, what the library's load_vec_ro emits); 2: ld.global.nc.L2::64B;
+// 3: ld.global.L1::no_allocate; 4: ld.global.cg
+template<int MODE> __device__ __forceinline__ uint4 ld16(const uint4 *p)
+{
+    uint4 v;
+    if (MODE == 0) {
+        v = *p;
+    } else if (MODE == 1) {
+        v = __ldg(p);
+    } else if (MODE == 2) {
+        asm volatile("ld.global.nc.L2::64B.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    } else if (MODE == 3) {
+        asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    } else {
+        asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    }
+    return v;
+}
+template<int MODE>
+__global__ void __launch_bounds__(128) k_up_mode(const uint4 *table, const uint32_t *entries, uint64_t npairs, uint4 *pex)
+{
+    const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npairs) return;
+    const uint32_t ia = entries[2 * p], ib = entries[2 * p + 1];
+    const uint4 a0 = ld16<MODE>(table + (uint64_t)ia * 4), a1 = ld16<MODE>(table + (uint64_t)ia * 4 + 1);
+    const uint4 b0 = ld16<MODE>(table + (uint64_t)ib * 4), b1 = ld16<MODE>(table + (uint64_t)ib * 4 + 1);
+    pex[p * 2] = make_uint4(a0.x ^ b0.x, a0.y + b0.y, a0.z ^ b0.z, a0.w + b0.w);
+    pex[p * 2 + 1] = make_uint4(a1.x ^ b1.x, a1.y + b1.y, a1.z ^ b1.z, a1.w + b1.w);
+}
+// the library's thread shape: one thread walks 16 consecutive pairs (4 blocks of 8 entries, consecutive threads own
+// consecutive blocks), loads issued 4 pairs ahead
+template<int MODE>
+__global__ void __launch_bounds__(128, 4) k_up_owner(const uint4 *table, const uint32_t *entries, uint64_t nthreads, uint4 *pex)
+{
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nthreads) return;
+    uint4 acc0 = make_uint4(1, 2, 3, 4), acc1 = acc0;
+    for (int jj = 0; jj < 4; ++jj) {
+        const uint64_t m = (uint64_t)jj * nthreads + t;   // block m: entries [8 m, 8 m + 8)
+        uint4 x[4][4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t ia = entries[8 * m + 2 * u], ib = entries[8 * m + 2 * u + 1];
+            x[u][0] = ld16<MODE>(table + (uint64_t)ia * 4);
+            x[u][1] = ld16<MODE>(table + (uint64_t)ia * 4 + 1);
+            x[u][2] = ld16<MODE>(table + (uint64_t)ib * 4);
+            x[u][3] = ld16<MODE>(table + (uint64_t)ib * 4 + 1);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            acc0.x ^= x[u][0].x + x[u][2].x; acc0.y += x[u][0].y ^ x[u][2].y; acc0.z ^= x[u][0].z; acc0.w += x[u][2].w;
+            acc1.x ^= x[u][1].x + x[u][3].x; acc1.y += x[u][1].y ^ x[u][3].y; acc1.z ^= x[u][1].z; acc1.w += x[u][3].w;
+            pex[((uint64_t)u * 4 * nthreads + m) * 2] = acc0;       // element-major, as Pex
+            pex[((uint64_t)u * 4 * nthreads + m) * 2 + 1] = acc1;
+        }
+    }
+}
 __global__ void __launch_bounds__(128) k_up(const uint4 *table, const uint32_t *entries, uint64_t first, uint64_t npairs, uint4 *pex)
 {
     const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -98,6 +155,27 @@ int main()
         CHECK(cudaEventElapsedTime(&ms, e0, e1));
     }
     printf("\"down_whole_ms\": %.3f", ms);
+    // load flavours, one launch each (timed; `ncu --metrics dram__bytes_read.sum` gives the bytes)
+#define MODE_RUN(K, MODE, GRID, ARG)                                                                \
+    for (int rep = 0; rep < 2; ++rep) {                                                             \
+        CHECK(cudaEventRecord(e0));                                                                 \
+        K<MODE><<<(unsigned)(GRID), 128>>>(table, entries, ARG, pex);                               \
+        CHECK(cudaEventRecord(e1));                                                                 \
+        CHECK(cudaEventSynchronize(e1));                                                            \
+        CHECK(cudaEventElapsedTime(&ms, e0, e1));                                                   \
+    }                                                                                               \
+    printf(", \"" #K "_mode" #MODE "_ms\": %.3f", ms);
+    MODE_RUN(k_up_mode, 0, (N / 2 + 127) / 128, N / 2)
+    MODE_RUN(k_up_mode, 1, (N / 2 + 127) / 128, N / 2)
+    MODE_RUN(k_up_mode, 2, (N / 2 + 127) / 128, N / 2)
+    MODE_RUN(k_up_mode, 3, (N / 2 + 127) / 128, N / 2)
+    MODE_RUN(k_up_mode, 4, (N / 2 + 127) / 128, N / 2)
+    {
+        const uint64_t nth = N / 32;   // 4 blocks of 8 entries per thread
+        MODE_RUN(k_up_owner, 0, (nth + 127) / 128, nth)
+        MODE_RUN(k_up_owner, 1, (nth + 127) / 128, nth)
+        MODE_RUN(k_up_owner, 4, (nth + 127) / 128, nth)
+    }
     const int Gs[] = {15, 5, 3, 2, 1};
     for (int G : Gs) {
         if (run(G, &ms)) return 1;
