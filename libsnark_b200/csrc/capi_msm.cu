@@ -125,7 +125,9 @@ int msm_resident_impl(const rt::BaseSet &bs, size_t first, size_t n, const void 
         if (g_scalars.reserve(n * v->fr_bytes)) {
             return B200_ERR_CUDA;
         }
-        B200_CUDA_CHECK(cudaMemcpyAsync(g_scalars.p, scalars, n * v->fr_bytes, cudaMemcpyHostToDevice, s));
+        if (const int rc = rt::staged_h2d(g_scalars.p, scalars, n * v->fr_bytes, s)) {
+            return rc;
+        }
         sdev = g_scalars.p;
     }
     const size_t wbytes = v->window_point_bytes(bs.group);

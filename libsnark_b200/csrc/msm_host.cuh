@@ -62,7 +62,9 @@ int bases_upload(int curve, int group, const void *host, size_t stride, size_t n
         // out-of-memory, where a leak of the partial set makes things worse)
         const auto convert = [&]() -> int {
             B200_CUDA_CHECK(cudaMalloc((void **)&inf, n));
-            B200_CUDA_CHECK(cudaMemcpyAsync(ws.staging.p, host, bytes, cudaMemcpyHostToDevice, s));
+            if (const int rc = rt::staged_h2d(ws.staging.p, host, bytes, s)) { // the reference's vectors are pageable
+                return rc;
+            }
             B200_CUDA_CHECK(cudaMemsetAsync(ws.any_inf.p, 0, 4, s));
             k_convert_bases<F><<<grid_for(n, 256), 256, 0, s>>>(
                 ws.staging.as<uint8_t>(), stride, n, static_cast<Affine<F> *>(pts), inf, ws.any_inf.as<uint32_t>());

@@ -3,6 +3,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
+#include <vector>
 
 #include "runtime.hpp"
 
@@ -129,6 +131,82 @@ void DevBuf::release()
     }
     p = nullptr;
     cap = 0;
+}
+
+namespace
+{
+struct PinnedBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+};
+PinnedBuf g_pinned[NUM_SLOTS];
+constexpr size_t STAGE_MIN = size_t(4) << 20;    // below this a pageable copy is as good
+constexpr size_t STAGE_CAP = size_t(128) << 20;  // page-locked bytes held per slot that stages large copies
+constexpr size_t STAGE_THREADS = 4;
+} // namespace
+
+int staged_h2d(void *dev_dst, const void *host_src, size_t bytes, cudaStream_t s)
+{
+    if (bytes == 0) {
+        return B200_OK;
+    }
+    bool direct = bytes < STAGE_MIN;
+    if (!direct) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, host_src) == cudaSuccess && at.type == cudaMemoryTypeHost) {
+            direct = true;
+        }
+        cudaGetLastError(); // an unregistered pointer may leave an error behind on old runtimes
+    }
+    PinnedBuf &pb = g_pinned[slot()];
+    if (!direct && pb.cap < (bytes < STAGE_CAP ? bytes : STAGE_CAP)) {
+        if (pb.p) {
+            cudaFreeHost(pb.p);
+            pb.p = nullptr;
+            pb.cap = 0;
+        }
+        const size_t want = bytes < STAGE_CAP ? bytes + bytes / 8 : STAGE_CAP;
+        if (cudaHostAlloc(&pb.p, want, cudaHostAllocDefault) != cudaSuccess) {
+            cudaGetLastError();
+            pb.p = nullptr;
+            direct = true; // no page-locked memory to be had: the plain copy still works
+        } else {
+            pb.cap = want;
+        }
+    }
+    if (direct) { // stream-ordered, as before: the caller's kernels queue up behind it
+        B200_CUDA_CHECK(cudaMemcpyAsync(dev_dst, host_src, bytes, cudaMemcpyHostToDevice, s));
+        return B200_OK;
+    }
+    const uint8_t *src = static_cast<const uint8_t *>(host_src);
+    uint8_t *dst = static_cast<uint8_t *>(dev_dst), *pin = static_cast<uint8_t *>(pb.p);
+    for (size_t done = 0; done < bytes;) {
+        const size_t part = bytes - done < pb.cap ? bytes - done : pb.cap;
+        size_t cut[STAGE_THREADS + 1];
+        for (size_t t = 0; t <= STAGE_THREADS; ++t) {
+            cut[t] = t == STAGE_THREADS ? part : (part / STAGE_THREADS * t) & ~(size_t)255;
+        }
+        std::vector<std::thread> workers;
+        for (size_t t = 1; t < STAGE_THREADS; ++t) {
+            workers.emplace_back([=]() { memcpy(pin + cut[t], src + done + cut[t], cut[t + 1] - cut[t]); });
+        }
+        memcpy(pin, src + done, cut[1]);
+        cudaError_t e = cudaMemcpyAsync(dst + done, pin, cut[1], cudaMemcpyHostToDevice, s);
+        for (size_t t = 1; t < STAGE_THREADS; ++t) {
+            workers[t - 1].join();
+            if (e == cudaSuccess) {
+                e = cudaMemcpyAsync(dst + done + cut[t], pin + cut[t], cut[t + 1] - cut[t], cudaMemcpyHostToDevice, s);
+            }
+        }
+        if (e == cudaSuccess) {
+            e = cudaStreamSynchronize(s); // the staging buffer is about to be overwritten / handed to the next call
+        }
+        if (e != cudaSuccess) {
+            return set_error(B200_ERR_CUDA, "staged host-to-device copy failed: %s", cudaGetErrorString(e));
+        }
+        done += part;
+    }
+    return B200_OK;
 }
 
 } // namespace rt

@@ -58,6 +58,13 @@ struct DevBuf {
     template<class T> T *as() { return static_cast<T *>(p); }
 };
 
+// Host-to-device copy of a buffer that may lie in PAGEABLE memory (the reference hands over std::vector storage). The
+// driver stages a pageable cudaMemcpyAsync through one bounce buffer on one core — 5-12 GB/s depending on the box; this
+// stages it through a page-locked buffer of the calling slot with a few host threads and sends every slice on as soon as
+// it is staged, returning when the copy is complete (the staging buffer is reused by the next call). Page-locked sources
+// (cudaHostAlloc / cudaHostRegister) and small copies are one stream-ordered cudaMemcpyAsync, not waited for.
+int staged_h2d(void *dev_dst, const void *host_src, size_t bytes, cudaStream_t s);
+
 // A device-resident base set (proving-key query) in device affine form.
 struct BaseSet {
     int curve = -1, group = 0;

@@ -1,24 +1,29 @@
 #!/bin/bash
-# Round 2, call Z9: L2::64B gather loads only (ownership and AFF_KB as before): parity subset, stage times, prove, traffic.
+# Round 2, call Z10: staged host-to-device copies of pageable bases / scalars (b200_msm, b200_bases_upload).
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_msm_gpu.py tests/test_kat_gpu.py -q -m gpu -x 2>&1 | tail -2
-{
-python tools/affine_probe.py --check-log 12 2>/dev/null | tail -1
-python tools/affine_probe.py --check-log 12 --group 2 2>/dev/null | tail -1
-python tools/affine_probe.py --check-log 12 --curve bls12_377 2>/dev/null | tail -1
-python tools/affine_probe.py --check-log 12 --curve bw6_761 --log-n 18 2>/dev/null | tail -1
-B200_AFFINE_ROUNDS=0 python tools/affine_probe.py --check-log 12 2>/dev/null | tail -1
-python tools/prove_quick.py --steps 10 2>/dev/null | tail -1
-} | tee gpurun_out/r2_aff_l2_64b.jsonl
-ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none --kernel-name regex:'k_aff_up_round|k_aff_round|k_accumulate' --launch-skip 14 --launch-count 7 --csv --log-file gpurun_out/r2_aff_l2_64b_ncu.csv python tools/affine_probe.py --check-log 10 > /dev/null 2>&1
-B200_AFFINE_ROUNDS=0 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none --kernel-name regex:'k_accumulate' --launch-skip 2 --launch-count 1 --csv --log-file gpurun_out/r2_acc_l2_64b_ncu.csv python tools/affine_probe.py --check-log 10 > /dev/null 2>&1
-python - <<'PY'
-import csv
-for f in ['gpurun_out/r2_aff_l2_64b_ncu.csv','gpurun_out/r2_acc_l2_64b_ncu.csv']:
-    rows=list(csv.reader(l for l in open(f) if l.startswith('"')))
-    hdr=rows[0]; k=hdr.index("Kernel Name"); mn=hdr.index("Metric Name"); mv=hdr.index("Metric Value"); idc=hdr.index("ID")
-    out={}
-    for r in rows[1:]:
-        out.setdefault((r[idc], r[k].split('<')[0][-18:]),{})[r[mn].split('__')[1][:18]]=r[mv]
-    for (i,kn),v in out.items(): print(i, kn, v)
+python - <<'PY' | tee gpurun_out/r2_cold_msm.json
+import json, time, numpy as np, libsnark_b200 as b
+b.init(0)
+out = {}
+for curve, group, logn in [("alt_bn128", b.G1, 20), ("alt_bn128", b.G2, 20), ("bls12_377", b.G1, 20), ("alt_bn128", b.G1, 16)]:
+    n = 1 << logn
+    bases = b.make_bases(curve, group, n, k0=1)
+    rng = np.random.default_rng(3)
+    limbs = b.sizeof_fr(curve) // 8
+    sc = rng.integers(0, 1 << 62, size=(n, limbs), dtype=np.uint64)
+    r0 = b.multi_exp(curve, group, bases, sc)
+    t = []
+    for _ in range(8):
+        b.lib().b200_sync()
+        t0 = time.perf_counter()
+        r = b.multi_exp(curve, group, bases, sc)
+        t.append((time.perf_counter() - t0) * 1e3)
+    assert np.array_equal(r, r0)
+    rb = b.ResidentBases(curve, group, bases)
+    want = rb.multi_exp(sc)
+    rb.free()
+    assert np.array_equal(want, r0)
+    out[f"{curve}.g{group}.2^{logn}"] = {"cold_ms": round(float(np.mean(t)), 2), "min_ms": round(float(np.min(t)), 2),
+                                          "h2d_MiB": round((bases.nbytes + sc.nbytes) / 2**20, 1), "all_ms": [round(x, 1) for x in t]}
+print(json.dumps(out))
 PY
