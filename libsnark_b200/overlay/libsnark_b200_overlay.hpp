@@ -741,7 +741,20 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> r1cs_gg_ppzksnark_prover_fused(
         pfp = hash_words(pfp, &pk.beta_g2, sizeof(G2T));
         pfp = hash_words(pfp, &pk.delta_g1, sizeof(G1T));
         pfp = hash_words(pfp, &pk.delta_g2, sizeof(G2T));
-        pfp = hash_words(pfp, vec.indices.data(), vec.indices.size() * sizeof(size_t));
+        // B_query.indices: 8 MiB at 2^20, 1.5 ms to hash in full on every proof — like the bases, evenly spread samples
+        // (4096 of them) plus the length unless B200_OVERLAY_FINGERPRINT=full; a regenerated key changes every point above
+        {
+            const size_t ni_ = vec.indices.size(), samples = 4096;
+            pfp = hash_words(pfp, &ni_, sizeof(ni_));
+            if (ni_ <= samples || fingerprint_full_flag()) {
+                pfp = hash_words(pfp, vec.indices.data(), ni_ * sizeof(size_t));
+            } else {
+                for (size_t k = 0; k < samples; ++k) {
+                    const size_t i = (size_t)((unsigned __int128)k * (ni_ - 1) / (samples - 1));
+                    pfp = hash_words(pfp, &vec.indices[i], sizeof(size_t));
+                }
+            }
+        }
         const pk_cache::key_t key(hA, hB2, hB1, hH, hL, hr, pfp);
         const long long t_fp = libff::get_nsec_time();
         auto it = keys.find(key);
