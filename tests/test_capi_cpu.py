@@ -362,3 +362,27 @@ def test_assemble_reproduces_reference_proofs(b, curve, nc):
     got = b.groth16_assemble(curve, key["alpha_g1"], key["beta_g1"], key["beta_g2"], key["delta_g1"], key["delta_g2"], sizes, 1,
                              blob, r, s)
     assert np.array_equal(got, proof)
+
+
+@pytest.mark.parametrize("extra", [[], ["-DB200_OVERLAY_KEEP_REFERENCE_PROVER"]])
+def test_overlay_header_compiles_against_the_reference(extra):
+    """libsnark_b200_overlay.hpp force-included into an empty translation unit, with the reference's own headers: every
+    explicit specialisation must match a primary template of the reference (a drifted signature is a hard error), with and
+    without the prover entry-point specialisation. Needs the reference tree (absent on the GPU box: skipped there)."""
+    ref = "/root/reference"
+    if not os.path.isdir(os.path.join(ref, "libsnark")):
+        pytest.skip("reference tree not present")
+    src = os.path.join(ROOT, "tests", "_overlay_syntax.cpp")
+    with open(src, "w") as f:
+        f.write("int main() { return 0; }\n")
+    try:
+        cmd = ["g++", "-std=c++11", "-fsyntax-only", "-fopenmp", "-w", "-DNO_PROCPS", "-DBINARY_OUTPUT", "-DMONTGOMERY_OUTPUT",
+               "-DUSE_ASM", "-DMULTICORE", "-DCURVE_ALT_BN128", *extra,
+               "-I", os.path.join(ROOT, "oracle", "gmp_shim"), "-I", ref, "-I", os.path.join(ref, "depends", "libff"),
+               "-I", os.path.join(ref, "depends", "libfqfft"), "-I", os.path.join(ROOT, "include"),
+               "-I", os.path.join(ROOT, "libsnark_b200", "overlay"),
+               "-include", os.path.join(ROOT, "libsnark_b200", "overlay", "libsnark_b200_overlay.hpp"), src]
+        out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+        assert out.returncode == 0, out.stderr[-3000:]
+    finally:
+        os.remove(src)
