@@ -158,8 +158,7 @@ int b200_divide_by_Z_on_coset(int curve, void *data, size_t m);
  *   m = 2^(s+1)              extended_radix2_domain  (extended_radix2_domain.tcc:21-236: the order-2^s subgroup and its
  *                            coset by libff::coset_shift(); two size-2^s transforms plus element-wise steps)
  *   m = 2^k + 2^r, k + 1 <= s   step_radix2_domain   (step_radix2_domain.tcc:20-276)
- * b200_ntt*, b200_divide_by_Z_on_coset, the witness-map calls and the provers serve all three (the chain-by-chain
- * calls b200_witness_chain_r1cs_dev / b200_witness_finish_dev serve basic domains only).
+ * b200_ntt*, b200_divide_by_Z_on_coset, the witness-map calls (whole and chain by chain) and the provers serve all three.
  * b200_set_two_adicity mirrors libff's mutable static FieldT::s / FieldT::root_of_unity (e.g. alt_bn128_init.cpp:53-58):
  * a host that lowers them gets the extended domain at 2^(s'+1); s = 0 restores the field's own value (28 / 47 / 46),
  * with which only alt_bn128 reaches the extended domain at a size a GPU holds (2^29 elements). Roots of unity are always
@@ -209,7 +208,7 @@ int b200_witness_map_r1cs_dev(b200_r1cs_t handle, const void *d_w, size_t m, voi
  * evaluation, the transforms (eight with a non-zero d1 or d2) and the patch run on the device. */
 int b200_witness_map_r1cs_zk(b200_r1cs_t handle, const void *w, size_t m, const void *d123, void *out_H);
 /* The two halves of b200_witness_map_r1cs_dev, for provers that run the A, B and C chains on different
- * GPUs (r1cs_to_qap.tcc:252-290 and :293-330). m must be a power of two.
+ * GPUs (r1cs_to_qap.tcc:252-290 and :293-330), on any of the three radix-2 domain kinds.
  * chain : which = 0/1/2 -> the evaluations of the a-/b-/c-combinations from d_w, iFFT, cosetFFT(g) into
  *         d_out (device, m elements).
  * finish: (dA * dB - dC) / Z on the coset, icosetFFT -> dH (device, m + 1 elements); dA is clobbered. */

@@ -678,8 +678,7 @@ class Groth16ProvingKeyShard:
 
 class DistributedProver:
     """r1cs_gg_ppzksnark_prover over the ranks of an initialised torch.distributed (NCCL) process group, one
-    Groth16ProvingKeyShard per rank. Per proof: every rank uploads the witness; with chain_parallel (>= 3 ranks,
-    power-of-two domain) ranks 0, 1, 2 each run one of the A, B, C iFFT/cosetFFT chains and broadcast the result
+    Groth16ProvingKeyShard per rank. Per proof: every rank uploads the witness; with chain_parallel (>= 3 ranks) ranks 0, 1, 2 each run one of the A, B, C iFFT/cosetFFT chains and broadcast the result
     while all ranks already run their A, B and L shard MSMs, then every rank finishes H — otherwise each rank
     computes the whole witness map; the ranks' window sums are all-gathered (a few KB per rank) and folded on the
     host. torch is used for the NCCL plumbing and the device buffers the collectives work on, nothing else."""
@@ -689,10 +688,10 @@ class DistributedProver:
         import torch.distributed as dist
         self.torch, self.dist, self.pk = torch, dist, shard
         self.dev = torch.device("cuda", torch.cuda.current_device())
-        basic = domain_kind(shard.curve, shard.m) == DOMAIN_BASIC   # the chain-by-chain calls serve basic_radix2_domain only
-        self.chain_parallel = (shard.world >= 3 and basic) if chain_parallel is None else bool(chain_parallel)
-        if self.chain_parallel and not (shard.world >= 3 and basic):
-            raise B200Error(ERR_ARG, "chain-parallel witness map needs >= 3 ranks and a basic radix-2 domain")
+        served = domain_kind(shard.curve, shard.m) != DOMAIN_NONE   # basic, extended or step radix-2 domain
+        self.chain_parallel = (shard.world >= 3 and served) if chain_parallel is None else bool(chain_parallel)
+        if self.chain_parallel and not (shard.world >= 3 and served):
+            raise B200Error(ERR_ARG, "chain-parallel witness map needs >= 3 ranks and a radix-2 domain size")
         self.blob = torch.zeros(shard.blob_bytes, dtype=torch.uint8, device=self.dev)
         self.gathered = torch.zeros(shard.world * shard.blob_bytes, dtype=torch.uint8, device=self.dev)
         # rank 0 holds all three chain results, ranks 1 and 2 their own; hbuf: H coefficients (whole on rank 0, a slice elsewhere)

@@ -1237,6 +1237,75 @@ template<class Fr> int gather_dev(const void *d_src, const uint32_t *d_idx, size
     return B200_OK;
 }
 
+// iFFT then cosetFFT(multiplicative_generator) of one vector, in place, on whichever radix-2 kind serves m: the fused
+// two-transform chain on a basic domain, the two operators one after the other on a step or extended domain.
+template<class Fr> int chain_any_domain(Fr *X, size_t m)
+{
+    const int lgn = log2_exact(m);
+    if (lgn >= 1 && lgn <= two_adicity<Fr>()) {
+        Domain<Fr> *d = nullptr;
+        if (int rc = witness_domain<Fr>(m, &d)) {
+            return rc;
+        }
+        return witness_chain<Fr>(*d, X);
+    }
+    uint32_t gen[Fr::N];
+    for (int i = 0; i < Fr::N; ++i) {
+        gen[i] = Fr::params::generator(i);
+    }
+    if (g_bufS.reserve(m * sizeof(Fr))) {
+        return B200_ERR_CUDA;
+    }
+    if (int rc = ntt_op_dev<Fr>(B200_IFFT, X, g_bufS.as<Fr>(), X, m, nullptr)) {
+        return rc;
+    }
+    return ntt_op_dev<Fr>(B200_COSET_FFT, X, g_bufS.as<Fr>(), X, m, gen);
+}
+
+// (A B - C) / Z on the coset, icosetFFT, H[m] = 0 on whichever kind serves m (r1cs_to_qap.tcc:293-330). dA clobbered.
+template<class Fr> int finish_any_domain(Fr *dA, const Fr *dB, const Fr *dC, size_t m, Fr *dH)
+{
+    const int lgn = log2_exact(m);
+    if (lgn >= 1 && lgn <= two_adicity<Fr>()) {
+        Domain<Fr> *d = nullptr;
+        if (int rc = witness_domain<Fr>(m, &d)) {
+            return rc;
+        }
+        return witness_finish<Fr>(*d, m, dA, dB, dC, dH);
+    }
+    uint32_t gen[Fr::N];
+    for (int i = 0; i < Fr::N; ++i) {
+        gen[i] = Fr::params::generator(i);
+    }
+    if (g_bufS.reserve(m * sizeof(Fr))) {
+        return B200_ERR_CUDA;
+    }
+    cudaStream_t s = rt::stream();
+    ntt::k_pointwise_abc<Fr><<<grid_for(m, 256), 256, 0, s>>>(m, dA, dB, dC, dH);
+    B200_LAUNCH_CHECK();
+    int rc;
+    if (lgn >= 2 && lgn == two_adicity<Fr>() + 1) {
+        ExtDomain<Fr> *d = nullptr;
+        if ((rc = get_ext_domain<Fr>(lgn - 1, &d)) || (rc = ext_divide_by_z_dev<Fr>(*d, dH))) {
+            return rc;
+        }
+    } else {
+        StepShape sh;
+        if (!step_shape<Fr>(m, &sh)) {
+            return rt::set_error(B200_ERR_DOMAIN, "no radix-2 domain of size %zu", m);
+        }
+        StepDomain<Fr> *d = nullptr;
+        if ((rc = get_step_domain<Fr>(sh, &d)) || (rc = step_divide_by_z_dev<Fr>(*d, dH))) {
+            return rc;
+        }
+    }
+    if ((rc = ntt_op_dev<Fr>(B200_ICOSET_FFT, dH, g_bufS.as<Fr>(), dH, m, gen))) {
+        return rc;
+    }
+    B200_CUDA_CHECK(cudaMemsetAsync(dH + m, 0, sizeof(Fr), s));
+    return B200_OK;
+}
+
 // One chain of the witness map on its own (multi-GPU: the A, B and C chains run on different GPUs,
 // SURVEY.md §8e): evaluations of the constraint rows from d_w, iFFT, cosetFFT -> d_out (m elements).
 template<class Fr> int witness_chain_r1cs_dev(const R1csSet &r, const void *d_w, size_t m, int which, void *d_out)
@@ -1244,10 +1313,6 @@ template<class Fr> int witness_chain_r1cs_dev(const R1csSet &r, const void *d_w,
     if (m < r.nc + r.ni + 1) {
         return rt::set_error(B200_ERR_DOMAIN, "domain size %zu < num_constraints + num_inputs + 1 = %zu", m,
                              r.nc + r.ni + 1);
-    }
-    Domain<Fr> *d = nullptr;
-    if (int rc = witness_domain<Fr>(m, &d)) {
-        return rc;
     }
     const size_t bytes = m * sizeof(Fr);
     if (g_bufA.reserve(bytes) || g_bufB.reserve(bytes) || g_bufC.reserve(bytes)) {
@@ -1257,7 +1322,7 @@ template<class Fr> int witness_chain_r1cs_dev(const R1csSet &r, const void *d_w,
         return rc;
     }
     Fr *X = which == 0 ? g_bufA.as<Fr>() : which == 1 ? g_bufB.as<Fr>() : g_bufC.as<Fr>();
-    if (int rc = witness_chain<Fr>(*d, X)) {
+    if (int rc = chain_any_domain<Fr>(X, m)) {
         return rc;
     }
     B200_CUDA_CHECK(cudaMemcpyAsync(d_out, X, bytes, cudaMemcpyDeviceToDevice, rt::stream()));
@@ -1267,12 +1332,8 @@ template<class Fr> int witness_chain_r1cs_dev(const R1csSet &r, const void *d_w,
 
 template<class Fr> int witness_finish_dev(void *dA, const void *dB, const void *dC, size_t m, void *dH)
 {
-    Domain<Fr> *d = nullptr;
-    if (int rc = witness_domain<Fr>(m, &d)) {
-        return rc;
-    }
-    if (int rc = witness_finish<Fr>(*d, m, static_cast<Fr *>(dA), static_cast<const Fr *>(dB), static_cast<const Fr *>(dC),
-                                    static_cast<Fr *>(dH))) {
+    if (int rc = finish_any_domain<Fr>(static_cast<Fr *>(dA), static_cast<const Fr *>(dB), static_cast<const Fr *>(dC), m,
+                                       static_cast<Fr *>(dH))) {
         return rc;
     }
     B200_CUDA_CHECK(cudaStreamSynchronize(rt::stream()));

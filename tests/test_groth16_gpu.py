@@ -463,14 +463,31 @@ def test_sharded_prover_bit_exact(ref, b200, curve, nc, ni, world, real_keys):
         fx.close()
 
 
-@pytest.mark.parametrize("curve,log_m", [("alt_bn128", 12), ("bls12_377", 10)])
-def test_chain_parallel_witness_map(ref, b200, curve, log_m):
+@pytest.mark.parametrize("curve,nc,s", [("alt_bn128", (1 << 12) - 11, 0), ("bls12_377", (1 << 10) - 11, 0),
+                                        ("alt_bn128", (1 << 11) + 100, 0),      # step domain 2^11 + 2^7
+                                        ("alt_bn128", (1 << 11) - 13, 10)])     # extended domain 2^11 with s = 10
+def test_chain_parallel_witness_map(ref, b200, curve, nc, s):
     """The stepwise sharded prover with the A, B, C chains computed separately (on three ranks in a real run, with
-    NCCL broadcasts in between): chain x3 -> finish gives every H coefficient; begin / msm / h / msm gives the proof."""
+    NCCL broadcasts in between): chain x3 -> finish gives every H coefficient; begin / msm / h / msm gives the proof.
+    On a basic, a step and an extended domain."""
+    if s:
+        ref.set_two_adicity(curve, s)
+        b200.set_two_adicity(curve, s)
+    try:
+        _chain_parallel_case(ref, b200, curve, nc, s)
+    finally:
+        if s:
+            ref.set_two_adicity(curve, 0)
+            b200.set_two_adicity(curve, 0)
+
+
+def _chain_parallel_case(ref, b200, curve, nc, s):
     ni, world = 10, 3
-    fx = ref.groth16_setup(curve, (1 << log_m) - ni - 1, ni, real_keys=False)
+    fx = ref.groth16_setup(curve, nc, ni, real_keys=False)
     try:
         m = fx.sizes["m"]
+        assert b200.domain_kind(curve, m) == (b200.DOMAIN_EXTENDED if s else b200.DOMAIN_BASIC if m & (m - 1) == 0
+                                              else b200.DOMAIN_STEP)
         keys, cs = _shard_keys(b200, fx, world)
         try:
             fr = b200.sizeof_fr(curve)

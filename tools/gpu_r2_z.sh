@@ -1,6 +1,4 @@
 #!/bin/bash
-# Round 2, closing run on the final tree: smoke() and the whole gpu suite.
+# Round 2, call Z14: chain-by-chain witness map on step and extended domains.
 mkdir -p gpurun_out
-python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -1
-(time timeout 1500 python -m pytest tests -q -m gpu -x 2>&1 | grep -v "^\*\|^  \*\|^(\|^$" | tail -3) 2>&1 | tee gpurun_out/r2s4_pytest.log
-timeout 300 python tools/prove_quick.py --steps 10 2>/dev/null | tail -1 | tee gpurun_out/r2s4_prove_quick.json
+timeout 900 python -m pytest tests/test_groth16_gpu.py -q -m gpu -x -k "chain_parallel or sharded or step or extended" 2>&1 | grep -v "^\*\|^$" | tail -6
