@@ -16,7 +16,7 @@ using namespace b200;
 namespace
 {
 
-constexpr int MAX_DEG = 8;
+constexpr int MAX_DEG = ntt::NTT_MAX_DEG;
 
 inline unsigned grid_for(uint64_t n, unsigned block) { return (unsigned)((n + block - 1) / block); }
 
@@ -116,23 +116,12 @@ int run_transform(Domain<Fr> &d, int inverse, Fr *in, Fr *tmp, Fr *out, const Fr
                   const Fr *post_const)
 {
     const int lgn = d.lgn;
-    const int P = (lgn + MAX_DEG - 1) / MAX_DEG;
+    ntt::PassLaunch plan[8];
+    const int P = ntt::plan_transform(lgn, inverse, Fr::N, plan);
     cudaStream_t s = rt::stream();
     Fr *cur = in;
-    int lgp = 0;
     for (int i = 0; i < P; ++i) {
-        ntt::PassParams pp;
-        pp.lgn = lgn;
-        pp.lgp = lgp;
-        pp.deg = lgn / P + (i < lgn % P ? 1 : 0);
-        pp.lgc = lgn - pp.deg < 3 ? lgn - pp.deg : 3;
-        pp.inverse = inverse;
-        pp.nsteps = 0;
-        for (int rem = pp.deg; rem > 0;) {
-            const int q = rem == 4 ? 2 : (rem >= 3 ? 3 : rem);
-            pp.step_q[pp.nsteps++] = q;
-            rem -= q;
-        }
+        const ntt::PassParams &pp = plan[i].pp;
         const bool last = (i == P - 1);
         Fr *dst = last ? out : (cur == in ? tmp : in);
         bool copy_back = false;
@@ -140,28 +129,21 @@ int run_transform(Domain<Fr> &d, int inverse, Fr *in, Fr *tmp, Fr *out, const Fr
             dst = tmp;
             copy_back = true;
         }
-        const uint64_t tile_elems = 1ull << (pp.deg + pp.lgc);
-        unsigned threads = (unsigned)(tile_elems / 8);
-        if (threads < 32) {
-            threads = 32;
-        }
-        const unsigned blocks = (unsigned)(1ull << (lgn - pp.deg - pp.lgc));
-        const size_t smem = (size_t)(Fr::N / 4) * 16 * ((size_t)1 << pp.deg) * ((1u << pp.lgc) + 1);
+        const size_t smem = plan[i].smem;
         static size_t smem_attr = 0;
         if (smem > smem_attr) {
             B200_CUDA_CHECK(cudaFuncSetAttribute(ntt::k_ntt_pass<Fr>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                  (int)(smem > 48 * 1024 ? smem : 48 * 1024)));
             smem_attr = smem;
         }
-        ntt::k_ntt_pass<Fr><<<blocks, threads, smem, s>>>(pp, cur, dst, d.twiddles.template as<Fr>(),
-                                                        i == 0 ? pre_table : nullptr, last ? post_table : nullptr,
-                                                        last ? post_const : nullptr);
+        ntt::k_ntt_pass<Fr><<<plan[i].blocks, plan[i].threads, smem, s>>>(pp, cur, dst, d.twiddles.template as<Fr>(),
+                                                                         i == 0 ? pre_table : nullptr, last ? post_table : nullptr,
+                                                                         last ? post_const : nullptr);
         B200_LAUNCH_CHECK();
         if (copy_back) {
             B200_CUDA_CHECK(cudaMemcpyAsync(out, tmp, sizeof(Fr) << lgn, cudaMemcpyDeviceToDevice, s));
         }
         cur = dst;
-        lgp += pp.deg;
     }
     return B200_OK;
 }

@@ -46,6 +46,44 @@ struct PassParams {
     int step_q[4];
 };
 
+// How a size-2^lgn transform is cut into passes (host side; shared by ntt.cu's launcher and the host emulation of the
+// kernel, tests/host_emu): at most NTT_MAX_DEG stage bits per pass, spread evenly; 8 columns per CTA where the size
+// allows; register steps of radix 8 (4 + 4 for a remainder of four stage bits).
+constexpr int NTT_MAX_DEG = 8;
+struct PassLaunch {
+    PassParams pp;
+    unsigned threads, blocks;
+    size_t smem;
+};
+inline int plan_transform(int lgn, int inverse, int fr_limbs32, PassLaunch *out /* >= 8 entries */)
+{
+    const int P = (lgn + NTT_MAX_DEG - 1) / NTT_MAX_DEG;
+    int lgp = 0;
+    for (int i = 0; i < P; ++i) {
+        PassParams &pp = out[i].pp;
+        pp.lgn = lgn;
+        pp.lgp = lgp;
+        pp.deg = lgn / P + (i < lgn % P ? 1 : 0);
+        pp.lgc = lgn - pp.deg < 3 ? lgn - pp.deg : 3;
+        pp.inverse = inverse;
+        pp.nsteps = 0;
+        for (int rem = pp.deg; rem > 0;) {
+            const int q = rem == 4 ? 2 : (rem >= 3 ? 3 : rem);
+            pp.step_q[pp.nsteps++] = q;
+            rem -= q;
+        }
+        const uint64_t tile_elems = 1ull << (pp.deg + pp.lgc);
+        out[i].threads = (unsigned)(tile_elems / 8);
+        if (out[i].threads < 32) {
+            out[i].threads = 32;
+        }
+        out[i].blocks = (unsigned)(1ull << (lgn - pp.deg - pp.lgc));
+        out[i].smem = (size_t)(fr_limbs32 / 4) * 16 * ((size_t)1 << pp.deg) * ((1u << pp.lgc) + 1);
+        lgp += pp.deg;
+    }
+    return P;
+}
+
 HD uint32_t bitrev(uint32_t v, int bits)
 {
     uint32_t r = 0;

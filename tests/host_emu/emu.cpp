@@ -11,6 +11,7 @@
 #include "host_fold.hpp"
 #include "msm.cuh"
 #include "msm_affine.cuh"
+#include "ntt.cuh"
 
 using namespace b200;
 
@@ -432,4 +433,101 @@ extern "C" int emu_inverse_fast(int curve, int field, const void *a, void *o, si
     if (curve == 1 && field == 2) return inv_fast<bls12_377_fq2>(a, o, n);
     if (curve == 2 && field == 2) return inv_fast<bw6_761_fq>(a, o, n);
     return -100;
+}
+
+// ---- the NTT pass kernel on the host ---------------------------------------------------------------------------------
+// k_ntt_pass (ntt.cuh) run as plain loops: the CTA's shared-memory tile is a host array, the phases between barriers are
+// called once with (tid, nthreads) = (0, 1) so that each covers the whole tile, and the passes, twiddle table, coset
+// tables and constants come from the same plan_transform / pow_table_body / domain_consts_body the launcher uses
+// (ntt.cu: get_domain, coset_table, run_transform, ntt_op_dev — mirrored here for basic radix-2 domains).
+template<class Fr> static void emu_pass(const ntt::PassLaunch &pl, const Fr *in, Fr *out, const Fr *tw, const Fr *pre, const Fr *post,
+                                        const Fr *post_const)
+{
+    const ntt::PassParams &pp = pl.pp;
+    std::vector<ntt::Vec4> smem(pl.smem / sizeof(ntt::Vec4) + 1);
+    for (unsigned b = 0; b < pl.blocks; ++b) {
+        ntt::Tile<Fr> tile;
+        tile.base = smem.data();
+        tile.row_stride = (1u << pp.lgc) + 1;
+        tile.plane = (1u << pp.deg) * tile.row_stride;
+        const uint64_t index0 = (uint64_t)b << pp.lgc;
+        ntt::load_phase<Fr>(0, 1, pp, index0, in, pre, tile);
+        int r = 0;
+        for (int st = 0; st < pp.nsteps; ++st) {
+            const int q = pp.step_q[st];
+            if (q == 3) {
+                ntt::step_phase<Fr, 3>(0, 1, pp, r, index0, tw, tile);
+            } else if (q == 2) {
+                ntt::step_phase<Fr, 2>(0, 1, pp, r, index0, tw, tile);
+            } else {
+                ntt::step_phase<Fr, 1>(0, 1, pp, r, index0, tw, tile);
+            }
+            r += q;
+        }
+        ntt::store_phase<Fr>(0, 1, pp, index0, out, post, post_const, tile);
+    }
+}
+
+// op: 0 FFT, 1 iFFT, 2 cosetFFT(g), 3 icosetFFT(g); in place on m = 2^lgn elements
+template<class Fr> static int emu_ntt_t(int op, void *data, size_t m, const void *g_)
+{
+    int lgn = 0;
+    while (((size_t)1 << lgn) < m) {
+        ++lgn;
+    }
+    if (m < 2 || ((size_t)1 << lgn) != m || lgn > Fr::params::S) {
+        return -2;
+    }
+    Fr g;
+    if (g_) {
+        memcpy(&g, g_, sizeof(Fr));
+    } else {
+        for (int i = 0; i < Fr::N; ++i) {
+            g.v[i] = Fr::params::generator(i);
+        }
+    }
+    std::vector<Fr> consts(8), pw(64), pg(64), pgi(64);
+    ntt::domain_consts_body<Fr>(lgn, &g, consts.data(), pw.data(), pg.data(), pgi.data());
+    std::vector<Fr> tw(m / 2 + 1), table(m);
+    for (uint64_t e = 0; e < m / 2; ++e) {
+        ntt::pow_table_body<Fr>(e, pw.data(), lgn - 1, nullptr, tw.data());
+    }
+    const Fr *pre = nullptr, *post = nullptr, *post_const = nullptr;
+    if (op == 2) { // a[i] *= g^i fused into the first pass's loads
+        for (uint64_t e = 0; e < m; ++e) {
+            ntt::pow_table_body<Fr>(e, pg.data(), lgn, nullptr, table.data());
+        }
+        pre = table.data();
+    } else if (op == 3) { // g^-i / m fused into the last pass's stores
+        for (uint64_t e = 0; e < m; ++e) {
+            ntt::pow_table_body<Fr>(e, pgi.data(), lgn, &consts[1], table.data());
+        }
+        post = table.data();
+    } else if (op == 1) {
+        post_const = &consts[1];
+    } else if (op != 0) {
+        return -1;
+    }
+    ntt::PassLaunch plan[8];
+    const int inverse = (op == 1 || op == 3) ? 1 : 0;
+    const int P = ntt::plan_transform(lgn, inverse, Fr::N, plan);
+    std::vector<Fr> a((Fr *)data, (Fr *)data + m), b(m);
+    Fr *cur = a.data(), *nxt = b.data();
+    for (int i = 0; i < P; ++i) {
+        emu_pass<Fr>(plan[i], cur, nxt, tw.data(), i == 0 ? pre : nullptr, i == P - 1 ? post : nullptr,
+                     i == P - 1 ? post_const : nullptr);
+        std::swap(cur, nxt);
+    }
+    memcpy(data, cur, m * sizeof(Fr));
+    return 0;
+}
+
+extern "C" int emu_ntt(int curve, int op, void *data, size_t m, const void *g)
+{
+    switch (curve) {
+    case 0: return emu_ntt_t<alt_bn128_fr>(op, data, m, g);
+    case 1: return emu_ntt_t<bls12_377_fr>(op, data, m, g);
+    case 2: return emu_ntt_t<bw6_761_fr>(op, data, m, g);
+    }
+    return -1;
 }

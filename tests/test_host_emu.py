@@ -47,6 +47,7 @@ def emu():
     L.emu_msm_affine.argtypes = [i, i, vp, sz, vp, i, i, i, vp]
     L.emu_inverse_fast.argtypes = [i, i, vp, vp, sz]
     L.emu_msm_shared.argtypes = [i, i, vp, sz, vp, i, i, C.c_long, vp]
+    L.emu_ntt.argtypes = [i, i, vp, sz, vp]
     return L
 
 
@@ -317,3 +318,40 @@ def test_emulated_msm_affine_exceptional_pairs(emu):
         got = _emu_msm_affine(emu, "alt_bn128", 1, g["family.bases"][:kk], g[f"family.scalars{kk}"], 6, 0, 2)
         assert np.array_equal(got, g[f"family.out{kk}"]), kk
     assert np.array_equal(_emu_msm_affine(emu, "alt_bn128", 1, g["edge.bases"], g["edge.scalars"], 9, 0, 3), g["edge.out"])
+
+
+def _emu_ntt(emu, curve, op, a, g=None):
+    a = np.array(a, dtype=np.uint64, order="C", copy=True)
+    g_ = None if g is None else np.ascontiguousarray(g, dtype=np.uint64)
+    assert emu.emu_ntt(CURVES[curve], op, _p(a), a.shape[0], None if g_ is None else _p(g_)) == 0
+    return a
+
+
+@pytest.mark.parametrize("curve", list(CURVES))
+def test_emulated_ntt_passes(emu, curve):
+    """k_ntt_pass (ntt.cuh: Stockham passes of up to 8 stage bits, rows gathered bit-reversed, radix-8 register steps, global
+    twiddles merged into the butterflies, coset / 1/m tables fused into the first loads and last stores) run on the host
+    with the launcher's own pass plan: the four transforms == the vectors of the unmodified reference for every committed
+    size (one pass), and == the pinned C oracle at 2^9 ... 2^13 (two passes, uneven splits, a coset generator that is
+    not the field's) — the index arithmetic of the device formulation, without a GPU."""
+    from oracle import port
+    P = port.OraclePort()
+    g = np.load(os.path.join(GOLD, "fft.npz"))
+    names = {0: "fft", 1: "ifft", 2: "cosetfft", 3: "icosetfft"}
+    gen = P.fft  # noqa: F841  (keeps the import visibly used)
+    for m in [2, 4, 8, 32, 256]:
+        a = g[f"{curve}.m{m}.in"]
+        for op, name in names.items():
+            assert np.array_equal(_emu_ntt(emu, curve, op, a), g[f"{curve}.m{m}.{name}"]), (m, name)
+    rng = np.random.default_rng(41)
+    limbs = g[f"{curve}.m2.in"].shape[1]
+    for lg in ([9, 10, 13] if curve == "alt_bn128" else [9, 11]):
+        m = 1 << lg
+        a = rng.integers(0, 1 << 62, size=(m, limbs), dtype=np.uint64)
+        a[:, -1] >>= np.uint64(10)                         # canonical residues (below the modulus)
+        other_g = a[5].copy()
+        for op in range(4):
+            assert np.array_equal(_emu_ntt(emu, curve, op, a), P.fft(curve, op, a)), (lg, op)
+        for op in (2, 3):
+            assert np.array_equal(_emu_ntt(emu, curve, op, a, other_g), P.fft(curve, op, a, other_g)), (lg, op, "g")
+        assert np.array_equal(_emu_ntt(emu, curve, 1, _emu_ntt(emu, curve, 0, a)), a)
