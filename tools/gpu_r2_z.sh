@@ -1,5 +1,5 @@
 #!/bin/bash
-# Round 2, call Z15: NTT launcher after the plan_transform refactor: the NTT and witness-map tests, one prove.
+# Round 2, closing run on the final tree: smoke() and the whole gpu suite.
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_ntt_gpu.py tests/test_zz_no_alloc.py -q -m gpu -x 2>&1 | tail -2
-timeout 300 python tools/prove_quick.py --steps 6 2>/dev/null | tail -1 | cut -c1-300
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -1
+(time timeout 1500 python -m pytest tests -q -m gpu -x 2>&1 | grep -v "^\*\|^  \*\|^(\|^$" | tail -3) 2>&1 | tee gpurun_out/r2s5_pytest.log
