@@ -435,17 +435,7 @@ template<class Fr> bool step_shape(size_t m, StepShape *sh)
     return true;
 }
 
-template<class Fr> Fr host_pow(Fr base, uint64_t e)
-{
-    Fr acc = Fr::one();
-    for (; e; e >>= 1) {
-        if (e & 1) {
-            acc = acc * base;
-        }
-        base = base.sqr();
-    }
-    return acc;
-}
+using ntt::host_pow;
 
 template<class Fr> struct StepDomain {
     StepShape sh;
@@ -735,7 +725,7 @@ template<class Fr> int step_witness_map_try(Fr *dA, Fr *dB, Fr *dC, size_t m, Fr
 // m = 2 small with small = 2^s, s the 2-adicity in force (two_adicity): what get_evaluation_domain returns for
 // exactly that size (get_evaluation_domain.tcc:44-46; extended_radix2_domain.tcc:21-62). With the fields' own
 // parameters only alt_bn128 reaches it with a vector that fits a GPU (2^29 elements, 16 GiB).
-constexpr int EXT_LG_LO = 15;
+using ntt::EXT_LG_LO;
 
 template<class Fr> struct ExtDomain {
     int lg_small = 0;
@@ -762,25 +752,12 @@ template<class Fr> std::map<int, std::unique_ptr<ExtDomain<Fr>>> &ext_domains()
     return m;
 }
 
-// lo[j] = b^j (j < 2^lg_lo), hi[k] = b^(k 2^lg_lo) (k < count >> lg_lo), for b and b^-1, computed on the host
-// (3 * 2^15 multiplications at most) and uploaded: lo0 | hi0 | lo1 | hi1
+// the two-level tables of b and b^-1 (ntt::ext_pow_tables_host: 3 * 2^15 multiplications at most), uploaded
 template<class Fr> int ext_pow_tables(const Fr &b, size_t count, int lg_lo, rt::DevBuf &buf)
 {
     const size_t nlo = (size_t)1 << lg_lo, nhi = count >> lg_lo;
     std::vector<Fr> h(2 * (nlo + nhi));
-    const Fr bases[2] = {b, b.inverse()};
-    for (int t = 0; t < 2; ++t) {
-        Fr *lo = h.data() + t * (nlo + nhi), *hi = lo + nlo;
-        lo[0] = Fr::one();
-        for (size_t j = 1; j < nlo; ++j) {
-            lo[j] = lo[j - 1] * bases[t];
-        }
-        const Fr step = lo[nlo - 1] * bases[t]; // b^(2^lg_lo)
-        hi[0] = Fr::one();
-        for (size_t k = 1; k < nhi; ++k) {
-            hi[k] = hi[k - 1] * step;
-        }
-    }
+    ntt::ext_pow_tables_host<Fr>(b, count, lg_lo, h.data());
     if (buf.reserve(h.size() * sizeof(Fr))) {
         return B200_ERR_CUDA;
     }
@@ -801,20 +778,8 @@ template<class Fr> int get_ext_domain(int lg_small, ExtDomain<Fr> **out)
         if (rc) {
             return rc;
         }
-        Fr g;
-        for (int i = 0; i < Fr::N; ++i) {
-            g.v[i] = Fr::params::generator(i); // FieldT::multiplicative_generator
-        }
-        const Fr one = Fr::one();
-        const Fr shift = g.sqr(); // libff::coset_shift, field_utils.tcc:152-155
-        const Fr ssm = host_pow(shift, d->small), gsm = host_pow(g, d->small);
-        Fr small_f = Fr::zero();
-        small_f.v[lg_small >> 5] = 1u << (lg_small & 31);
-        Fr hc[4];
-        hc[0] = ssm;
-        hc[1] = (small_f.to_mont() * (one - ssm)).inverse();                       // sconst, :107
-        hc[2] = ((gsm - one) * (gsm - ssm)).inverse();                             // Z0^-1, :224-228
-        hc[3] = ((gsm * ssm - one) * (gsm * ssm - ssm)).inverse();                 // Z1^-1, :225-229
+        Fr hc[4], shift;
+        ntt::ext_domain_consts_host<Fr>(lg_small, hc, &shift);
         if (d->consts.reserve(sizeof(hc))) {
             return B200_ERR_CUDA;
         }

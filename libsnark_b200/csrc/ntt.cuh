@@ -315,6 +315,86 @@ template<class Fr> HD void domain_consts_body(int lgn, const Fr *g_in, Fr *const
     gstore(consts + 5, Fr::one());
 }
 
+// ---- extended_radix2_domain: element-wise steps and host-side constants (kernels further down) --------------------------
+// Powers b^i of a fixed element from a two-level table: b^i = lo[i mod 2^lg_lo] * hi[i >> lg_lo].
+template<class Fr> struct PowTable {
+    const Fr *lo, *hi;
+    int lg_lo;
+    HD Fr at(uint64_t i) const { return gload(lo + (i & ((1ull << lg_lo) - 1))) * gload(hi + (i >> lg_lo)); }
+};
+// FFT, extended_radix2_domain.tcc:64-91: a0[i] = a[i] + a[i+small], a1[i] = shift^i (a[i] + shift^small a[i+small])
+template<class Fr> HD void ext_fft_pre_body(uint64_t i, uint64_t small, Fr *a, const PowTable<Fr> &spow, const Fr *ssm)
+{
+    const Fr x = gload(a + i), y = gload(a + i + small);
+    gstore(a + i, x + y);
+    gstore(a + i + small, spow.at(i) * (x + gload(ssm) * y));
+}
+// iFFT, :93-120, on the unnormalised inverse transforms a0 | a1: a[i] = sconst (shift^-i a1[i] - shift^small a0[i]),
+// a[i+small] = sconst (a0[i] - shift^-i a1[i]); cst = { shift^small, (small (1 - shift^small))^-1 }
+template<class Fr> HD void ext_ifft_post_body(uint64_t i, uint64_t small, Fr *a, const PowTable<Fr> &sinv, const Fr *cst)
+{
+    const Fr a0 = gload(a + i), t = sinv.at(i) * gload(a + i + small);
+    const Fr sc = gload(cst + 1);
+    gstore(a + i, sc * (t - gload(cst) * a0));
+    gstore(a + i + small, sc * (a0 - t));
+}
+// _multiply_by_coset (basic_radix2_domain_aux.tcc:174-183): a[i] *= g^i
+template<class Fr> HD void mul_pow_body(uint64_t i, Fr *a, const PowTable<Fr> &gpow) { gstore(a + i, gload(a + i) * gpow.at(i)); }
+// divide_by_Z_on_coset, :216-236: one factor per half
+template<class Fr> HD void ext_divz_body(uint64_t i, uint64_t small, Fr *p, const Fr *zinv) { gstore(p + i, gload(p + i) * gload(zinv + (i >= small))); }
+
+template<class Fr> inline Fr host_pow(Fr base, uint64_t e)
+{
+    Fr acc = Fr::one();
+    for (; e; e >>= 1) {
+        if (e & 1) {
+            acc = acc * base;
+        }
+        base = base.sqr();
+    }
+    return acc;
+}
+// [0] shift^small  [1] (small (1 - shift^small))^-1 (:107)  [2] Z0^-1  [3] Z1^-1 (:224-229), small = 2^lg_small,
+// shift = libff::coset_shift() = multiplicative_generator^2 (field_utils.tcc:152-155); *shift_out = shift
+template<class Fr> inline void ext_domain_consts_host(int lg_small, Fr hc[4], Fr *shift_out)
+{
+    Fr g;
+    for (int i = 0; i < Fr::N; ++i) {
+        g.v[i] = Fr::params::generator(i); // FieldT::multiplicative_generator
+    }
+    const uint64_t small = 1ull << lg_small;
+    const Fr one = Fr::one();
+    const Fr shift = g.sqr();
+    const Fr ssm = host_pow(shift, small), gsm = host_pow(g, small);
+    Fr small_f = Fr::zero();
+    small_f.v[lg_small >> 5] = 1u << (lg_small & 31);
+    hc[0] = ssm;
+    hc[1] = (small_f.to_mont() * (one - ssm)).inverse();
+    hc[2] = ((gsm - one) * (gsm - ssm)).inverse();
+    hc[3] = ((gsm * ssm - one) * (gsm * ssm - ssm)).inverse();
+    *shift_out = shift;
+}
+// lo[j] = b^j (j < 2^lg_lo), hi[k] = b^(k 2^lg_lo) (k < count >> lg_lo), for b (t = 0) and b^-1 (t = 1), laid out
+// lo0 | hi0 | lo1 | hi1 in h (2 * (2^lg_lo + (count >> lg_lo)) elements)
+template<class Fr> inline void ext_pow_tables_host(const Fr &b, size_t count, int lg_lo, Fr *h)
+{
+    const size_t nlo = (size_t)1 << lg_lo, nhi = count >> lg_lo;
+    const Fr bases[2] = {b, b.inverse()};
+    for (int t = 0; t < 2; ++t) {
+        Fr *lo = h + t * (nlo + nhi), *hi = lo + nlo;
+        lo[0] = Fr::one();
+        for (size_t j = 1; j < nlo; ++j) {
+            lo[j] = lo[j - 1] * bases[t];
+        }
+        const Fr step = lo[nlo - 1] * bases[t]; // b^(2^lg_lo)
+        hi[0] = Fr::one();
+        for (size_t k = 1; k < nhi; ++k) {
+            hi[k] = hi[k - 1] * step;
+        }
+    }
+}
+constexpr int EXT_LG_LO = 15;
+
 #if defined(__CUDACC__)
 
 template<class Fr>
@@ -486,53 +566,34 @@ template<class Fr> __global__ void k_pointwise_abc(uint64_t m, const Fr *a, cons
 // ---- extended_radix2_domain (libfqfft/evaluation_domain/domains/extended_radix2_domain.tcc) --------
 // Domain of size m = 2 small, small = 2^s the largest radix-2 subgroup of the field: the subgroup H of order
 // small and its coset shift * H, shift = coset_shift() = multiplicative_generator^2. A transform is two radix-2
-// transforms of size small plus the element-wise steps below. Powers b^i of a fixed element come from a
-// two-level table: b^i = lo[i mod 2^lg_lo] * hi[i >> lg_lo] (both L2-resident; two multiplications per element
-// instead of a table as long as the vector, which at 2^29 elements would be 16 GiB).
-template<class Fr> struct PowTable {
-    const Fr *lo, *hi;
-    int lg_lo;
-    __device__ __forceinline__ Fr at(uint64_t i) const
-    {
-        return gload(lo + (i & ((1ull << lg_lo) - 1))) * gload(hi + (i >> lg_lo));
-    }
-};
-// FFT, :64-91: a0[i] = a[i] + a[i+small], a1[i] = shift^i (a[i] + shift^small a[i+small]); a0 | a1 in place
+// transforms of size small plus the element-wise steps above (ext_*_body). The two-level power tables are L2-resident:
+// two multiplications per element instead of a table as long as the vector, which at 2^29 elements would be 16 GiB.
 template<class Fr> __global__ void k_ext_fft_pre(uint64_t small, Fr *a, PowTable<Fr> spow, const Fr *ssm)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < small) {
-        const Fr x = gload(a + i), y = gload(a + i + small);
-        gstore(a + i, x + y);
-        gstore(a + i + small, spow.at(i) * (x + gload(ssm) * y));
+        ext_fft_pre_body<Fr>(i, small, a, spow, ssm);
     }
 }
-// iFFT, :93-120, on the unnormalised inverse transforms a0 | a1: a[i] = sconst (shift^-i a1[i] - shift^small a0[i]),
-// a[i+small] = sconst (a0[i] - shift^-i a1[i]); cst = { shift^small, (small (1 - shift^small))^-1 }
 template<class Fr> __global__ void k_ext_ifft_post(uint64_t small, Fr *a, PowTable<Fr> sinv, const Fr *cst)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < small) {
-        const Fr a0 = gload(a + i), t = sinv.at(i) * gload(a + i + small);
-        const Fr sc = gload(cst + 1);
-        gstore(a + i, sc * (t - gload(cst) * a0));
-        gstore(a + i + small, sc * (a0 - t));
+        ext_ifft_post_body<Fr>(i, small, a, sinv, cst);
     }
 }
-// _multiply_by_coset (basic_radix2_domain_aux.tcc): a[i] *= g^i
 template<class Fr> __global__ void k_mul_pow(uint64_t n, Fr *a, PowTable<Fr> gpow)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {
-        gstore(a + i, gload(a + i) * gpow.at(i));
+        mul_pow_body<Fr>(i, a, gpow);
     }
 }
-// divide_by_Z_on_coset, :216-236: one factor per half
 template<class Fr> __global__ void k_ext_divz(uint64_t small, Fr *p, const Fr *zinv /* Z0^-1, Z1^-1 */)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < 2 * small) {
-        gstore(p + i, gload(p + i) * gload(zinv + (i >= small)));
+        ext_divz_body<Fr>(i, small, p, zinv);
     }
 }
 

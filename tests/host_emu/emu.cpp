@@ -468,16 +468,34 @@ template<class Fr> static void emu_pass(const ntt::PassLaunch &pl, const Fr *in,
     }
 }
 
-// op: 0 FFT, 1 iFFT, 2 cosetFFT(g), 3 icosetFFT(g); in place on m = 2^lgn elements
-template<class Fr> static int emu_ntt_t(int op, void *data, size_t m, const void *g_)
+// one transform of 2^lgn elements in place (run_transform of ntt.cu): twiddles and constants for the size, the passes
+template<class Fr> struct EmuDomain {
+    int lgn;
+    std::vector<Fr> consts, pw, pg, pgi, tw;
+    EmuDomain(int lgn_, const Fr &g) : lgn(lgn_), consts(8), pw(64), pg(64), pgi(64), tw(((size_t)1 << lgn_) / 2 + 1)
+    {
+        ntt::domain_consts_body<Fr>(lgn, &g, consts.data(), pw.data(), pg.data(), pgi.data());
+        for (uint64_t e = 0; e < ((uint64_t)1 << lgn) / 2; ++e) {
+            ntt::pow_table_body<Fr>(e, pw.data(), lgn - 1, nullptr, tw.data());
+        }
+    }
+    void run(Fr *data, int inverse, const Fr *pre, const Fr *post, const Fr *post_const) const
+    {
+        const size_t m = (size_t)1 << lgn;
+        ntt::PassLaunch plan[8];
+        const int P = ntt::plan_transform(lgn, inverse, Fr::N, plan);
+        std::vector<Fr> a(data, data + m), b(m);
+        Fr *cur = a.data(), *nxt = b.data();
+        for (int i = 0; i < P; ++i) {
+            emu_pass<Fr>(plan[i], cur, nxt, tw.data(), i == 0 ? pre : nullptr, i == P - 1 ? post : nullptr,
+                         i == P - 1 ? post_const : nullptr);
+            std::swap(cur, nxt);
+        }
+        memcpy(data, cur, m * sizeof(Fr));
+    }
+};
+template<class Fr> static Fr emu_generator(const void *g_)
 {
-    int lgn = 0;
-    while (((size_t)1 << lgn) < m) {
-        ++lgn;
-    }
-    if (m < 2 || ((size_t)1 << lgn) != m || lgn > Fr::params::S) {
-        return -2;
-    }
     Fr g;
     if (g_) {
         memcpy(&g, g_, sizeof(Fr));
@@ -486,39 +504,107 @@ template<class Fr> static int emu_ntt_t(int op, void *data, size_t m, const void
             g.v[i] = Fr::params::generator(i);
         }
     }
-    std::vector<Fr> consts(8), pw(64), pg(64), pgi(64);
-    ntt::domain_consts_body<Fr>(lgn, &g, consts.data(), pw.data(), pg.data(), pgi.data());
-    std::vector<Fr> tw(m / 2 + 1), table(m);
-    for (uint64_t e = 0; e < m / 2; ++e) {
-        ntt::pow_table_body<Fr>(e, pw.data(), lgn - 1, nullptr, tw.data());
+    return g;
+}
+
+// op: 0 FFT, 1 iFFT, 2 cosetFFT(g), 3 icosetFFT(g); in place on m = 2^lgn elements (ntt_op_dev, basic domain)
+template<class Fr> static int emu_ntt_t(int op, void *data, size_t m, const void *g_)
+{
+    int lgn = 0;
+    while (((size_t)1 << lgn) < m) {
+        ++lgn;
     }
+    if (m < 2 || ((size_t)1 << lgn) != m || lgn > Fr::params::S || op < 0 || op > 3) {
+        return -2;
+    }
+    const EmuDomain<Fr> d(lgn, emu_generator<Fr>(g_));
+    std::vector<Fr> table(m);
     const Fr *pre = nullptr, *post = nullptr, *post_const = nullptr;
     if (op == 2) { // a[i] *= g^i fused into the first pass's loads
         for (uint64_t e = 0; e < m; ++e) {
-            ntt::pow_table_body<Fr>(e, pg.data(), lgn, nullptr, table.data());
+            ntt::pow_table_body<Fr>(e, d.pg.data(), lgn, nullptr, table.data());
         }
         pre = table.data();
     } else if (op == 3) { // g^-i / m fused into the last pass's stores
         for (uint64_t e = 0; e < m; ++e) {
-            ntt::pow_table_body<Fr>(e, pgi.data(), lgn, &consts[1], table.data());
+            ntt::pow_table_body<Fr>(e, d.pgi.data(), lgn, &d.consts[1], table.data());
         }
         post = table.data();
     } else if (op == 1) {
-        post_const = &consts[1];
-    } else if (op != 0) {
-        return -1;
+        post_const = &d.consts[1];
     }
-    ntt::PassLaunch plan[8];
-    const int inverse = (op == 1 || op == 3) ? 1 : 0;
-    const int P = ntt::plan_transform(lgn, inverse, Fr::N, plan);
-    std::vector<Fr> a((Fr *)data, (Fr *)data + m), b(m);
-    Fr *cur = a.data(), *nxt = b.data();
-    for (int i = 0; i < P; ++i) {
-        emu_pass<Fr>(plan[i], cur, nxt, tw.data(), i == 0 ? pre : nullptr, i == P - 1 ? post : nullptr,
-                     i == P - 1 ? post_const : nullptr);
-        std::swap(cur, nxt);
+    d.run((Fr *)data, (op == 1 || op == 3) ? 1 : 0, pre, post, post_const);
+    return 0;
+}
+
+// extended_radix2_domain of size m = 2 small (ext_op_dev / ext_fft / ext_ifft / ext_divide_by_z_dev of ntt.cu), any
+// small = 2^k: op 0-3 as above, 4 = divide_by_Z_on_coset
+template<class Fr> static int emu_ext_ntt_t(int op, void *data_, size_t m, const void *g_)
+{
+    int lgn = 0;
+    while (((size_t)1 << lgn) < m) {
+        ++lgn;
     }
-    memcpy(data, cur, m * sizeof(Fr));
+    if (m < 4 || ((size_t)1 << lgn) != m || lgn - 1 > Fr::params::S || op < 0 || op > 4) {
+        return -2;
+    }
+    const int lg_small = lgn - 1;
+    const uint64_t small = m / 2;
+    Fr *a = (Fr *)data_;
+    Fr hc[4], shift;
+    ntt::ext_domain_consts_host<Fr>(lg_small, hc, &shift);
+    if (op == 4) {
+        for (uint64_t i = 0; i < m; ++i) {
+            ntt::ext_divz_body<Fr>(i, small, a, hc + 2);
+        }
+        return 0;
+    }
+    const int lg_lo_s = lg_small < ntt::EXT_LG_LO ? lg_small : ntt::EXT_LG_LO;
+    const size_t ns = ((size_t)1 << lg_lo_s) + (small >> lg_lo_s);
+    std::vector<Fr> stab(2 * ns);
+    ntt::ext_pow_tables_host<Fr>(shift, small, lg_lo_s, stab.data());
+    const ntt::PowTable<Fr> spow{stab.data(), stab.data() + ((size_t)1 << lg_lo_s), lg_lo_s};
+    const ntt::PowTable<Fr> sinv{stab.data() + ns, stab.data() + ns + ((size_t)1 << lg_lo_s), lg_lo_s};
+    const Fr g = emu_generator<Fr>(g_);
+    const int lg_lo_g = lgn < ntt::EXT_LG_LO ? lgn : ntt::EXT_LG_LO;
+    const size_t ng = ((size_t)1 << lg_lo_g) + (m >> lg_lo_g);
+    std::vector<Fr> gtab(2 * ng);
+    if (op >= 2) {
+        ntt::ext_pow_tables_host<Fr>(g, m, lg_lo_g, gtab.data());
+    }
+    const ntt::PowTable<Fr> gpow{gtab.data(), gtab.data() + ((size_t)1 << lg_lo_g), lg_lo_g};
+    const ntt::PowTable<Fr> ginv{gtab.data() + ng, gtab.data() + ng + ((size_t)1 << lg_lo_g), lg_lo_g};
+    const EmuDomain<Fr> d(lg_small, g);
+    const auto fft = [&]() {
+        for (uint64_t i = 0; i < small; ++i) {
+            ntt::ext_fft_pre_body<Fr>(i, small, a, spow, hc);
+        }
+        d.run(a, 0, nullptr, nullptr, nullptr);
+        d.run(a + small, 0, nullptr, nullptr, nullptr);
+    };
+    const auto ifft = [&]() {
+        d.run(a, 1, nullptr, nullptr, nullptr);
+        d.run(a + small, 1, nullptr, nullptr, nullptr);
+        for (uint64_t i = 0; i < small; ++i) {
+            ntt::ext_ifft_post_body<Fr>(i, small, a, sinv, hc);
+        }
+    };
+    switch (op) {
+    case 0: fft(); break;
+    case 1: ifft(); break;
+    case 2:
+        for (uint64_t i = 0; i < m; ++i) {
+            ntt::mul_pow_body<Fr>(i, a, gpow);
+        }
+        fft();
+        break;
+    case 3:
+        ifft();
+        for (uint64_t i = 0; i < m; ++i) {
+            ntt::mul_pow_body<Fr>(i, a, ginv);
+        }
+        break;
+    }
     return 0;
 }
 
@@ -528,6 +614,15 @@ extern "C" int emu_ntt(int curve, int op, void *data, size_t m, const void *g)
     case 0: return emu_ntt_t<alt_bn128_fr>(op, data, m, g);
     case 1: return emu_ntt_t<bls12_377_fr>(op, data, m, g);
     case 2: return emu_ntt_t<bw6_761_fr>(op, data, m, g);
+    }
+    return -1;
+}
+extern "C" int emu_ext_ntt(int curve, int op, void *data, size_t m, const void *g)
+{
+    switch (curve) {
+    case 0: return emu_ext_ntt_t<alt_bn128_fr>(op, data, m, g);
+    case 1: return emu_ext_ntt_t<bls12_377_fr>(op, data, m, g);
+    case 2: return emu_ext_ntt_t<bw6_761_fr>(op, data, m, g);
     }
     return -1;
 }

@@ -48,6 +48,7 @@ def emu():
     L.emu_inverse_fast.argtypes = [i, i, vp, vp, sz]
     L.emu_msm_shared.argtypes = [i, i, vp, sz, vp, i, i, C.c_long, vp]
     L.emu_ntt.argtypes = [i, i, vp, sz, vp]
+    L.emu_ext_ntt.argtypes = [i, i, vp, sz, vp]
     return L
 
 
@@ -355,3 +356,19 @@ def test_emulated_ntt_passes(emu, curve):
         for op in (2, 3):
             assert np.array_equal(_emu_ntt(emu, curve, op, a, other_g), P.fft(curve, op, a, other_g)), (lg, op, "g")
         assert np.array_equal(_emu_ntt(emu, curve, 1, _emu_ntt(emu, curve, 0, a)), a)
+
+
+@pytest.mark.parametrize("curve", list(CURVES))
+def test_emulated_extended_domain(emu, curve):
+    """The device formulation of extended_radix2_domain (ntt.cuh: ext_fft_pre_body / ext_ifft_post_body / mul_pow_body /
+    ext_divz_body over the two-level power tables, constants from ext_domain_consts_host, two emulated radix-2 transforms per
+    call) == the vectors the unmodified reference produced with FieldT::s lowered (tests/golden/extended.npz): all five
+    operations at 2^2 ... 2^9 — the same functions ntt.cu launches, without a GPU."""
+    g = np.load(os.path.join(GOLD, "extended.npz"))
+    coset = g[f"{curve}.generator"]
+    for s in [1, 2, 5, 8]:
+        a = g[f"{curve}.s{s}.in"]
+        for op, name in [(0, "fft"), (1, "ifft"), (2, "coset_fft"), (3, "icoset_fft"), (4, "div_z")]:
+            out = np.array(a, dtype=np.uint64, order="C", copy=True)
+            assert emu.emu_ext_ntt(CURVES[curve], op, _p(out), out.shape[0], _p(np.ascontiguousarray(coset))) == 0
+            assert np.array_equal(out, g[f"{curve}.s{s}.{name}"]), (s, name)

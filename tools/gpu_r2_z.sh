@@ -1,5 +1,4 @@
 #!/bin/bash
-# Round 2, closing run on the final tree: smoke() and the whole gpu suite.
+# Round 2, call Z16: extended-domain kernels after the body refactor: NTT and prover tests on step / extended domains.
 mkdir -p gpurun_out
-python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -1
-(time timeout 1500 python -m pytest tests -q -m gpu -x 2>&1 | grep -v "^\*\|^  \*\|^(\|^$" | tail -3) 2>&1 | tee gpurun_out/r2s5_pytest.log
+timeout 900 python -m pytest tests/test_ntt_gpu.py tests/test_groth16_gpu.py -q -m gpu -x -k "extended or step or zk_patch or chain_parallel or fft_ops" 2>&1 | tail -2
