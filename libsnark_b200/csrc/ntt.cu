@@ -468,26 +468,8 @@ template<class Fr> int get_step_domain(const StepShape &sh, StepDomain<Fr> **out
             return rc;
         }
         // constants on the host (a handful of exponentiations; step_radix2_domain.tcc:252-276)
-        Fr w, g;
-        for (int i = 0; i < Fr::N; ++i) {
-            w.v[i] = Fr::params::root_of_unity(i);
-            g.v[i] = Fr::params::generator(i); // FieldT::multiplicative_generator
-        }
-        for (int i = Fr::params::S; i > sh.lg_big + 1; --i) {
-            w = w.sqr(); // omega = get_root_of_unity(2 big)
-        }
-        const Fr one = Fr::one();
-        const Fr z0 = host_pow(g, sh.big) - one;
-        const Fr w_small = host_pow(w, sh.small);
-        const Fr gw = g * w;
-        const Fr z1 = (host_pow(gw, sh.big) - one) * (host_pow(gw, sh.small) - w_small);
         Fr hc[6];
-        hc[0] = (one + one).inverse();
-        hc[1] = host_pow(g, sh.small) * z0;
-        hc[2] = w_small * z0;
-        hc[3] = host_pow(w, 2 * sh.small);
-        hc[4] = z1.inverse();
-        hc[5] = one;
+        ntt::step_domain_consts_host<Fr>(sh.lg_big, sh.small, hc);
         if (d->consts.reserve(sizeof(hc))) {
             return B200_ERR_CUDA;
         }

@@ -315,6 +315,61 @@ template<class Fr> HD void domain_consts_body(int lgn, const Fr *g_in, Fr *const
     gstore(consts + 5, Fr::one());
 }
 
+// ---- step_radix2_domain: element-wise steps and host-side constants (kernels further down) ------------------------------
+// m = big + small, big = 2^k > small = 2^r; T2[e] = omega^e, e < big, is the twiddle table of the radix-2 domain of size
+// 2 big (omega = its root of unity). Line numbers: step_radix2_domain.tcc.
+// FFT, :73-88: c[i] = a[i] + a[i+big] (i < small) else a[i]; d[i] = omega^i * (a[i] - a[i+big] or a[i])
+template<class Fr> HD void step_fft_pre_body(uint64_t i, uint64_t big, uint64_t small, const Fr *T2, Fr *a, Fr *d)
+{
+    const Fr x = gload(a + i);
+    Fr c = x, dd = x;
+    if (i < small) {
+        const Fr y = gload(a + i + big);
+        c = x + y;
+        dd = x - y;
+    }
+    gstore(a + i, c);
+    gstore(d + i, dd * gload(T2 + i));
+}
+// one halving step of e[i] = sum_j d[i + j small] (:90-98): v[t] += v[t + half]
+template<class Fr> HD void fold_halve_body(uint64_t t, uint64_t half, Fr *v) { gstore(v + t, gload(v + t) + gload(v + t + half)); }
+// iFFT, :135-150: tmp[i] = U0[i] omega^i for i >= small, 0 below (the j = 0 term is not subtracted)
+template<class Fr> HD void step_ifft_tmp_body(uint64_t i, uint64_t small, const Fr *T2, const Fr *u0, Fr *tmp)
+{
+    gstore(tmp + i, i < small ? Fr::zero() : gload(u0 + i) * gload(T2 + i));
+}
+// iFFT, :152-173: U1[i] = (U1[i] - s[i]) omega^-i; a[i] = (U0[i] + U1[i]) / 2; a[big+i] = (U0[i] - U1[i]) / 2
+template<class Fr> HD void step_ifft_post_body(uint64_t i, uint64_t big, const Fr *T2, const Fr *s, const Fr *over_two, Fr *a)
+{
+    const Fr u0 = gload(a + i);
+    Fr u1 = gload(a + big + i) - gload(s + i);
+    if (i != 0) {
+        u1 = u1 * gload(T2 + (big - i)).neg(); // omega^big = -1
+    }
+    const Fr h = gload(over_two);
+    gstore(a + i, (u0 + u1) * h);
+    gstore(a + big + i, (u0 - u1) * h);
+}
+// a[i] *= table[i]
+template<class Fr> HD void mul_table_body(uint64_t i, Fr *a, const Fr *table) { gstore(a + i, gload(a + i) * gload(table + i)); }
+// divide_by_Z_on_coset, :252-276: zinv[k] = (A w2s^k - B)^-1, k < compr (the factor has period compr in i)
+template<class Fr> HD void step_zinv_body(uint64_t k, const Fr *abw /* A, B, w2s */, Fr *zinv)
+{
+    Fr elt = Fr::one(), base = gload(abw + 2);
+    for (uint64_t e = k; e; e >>= 1) {
+        if (e & 1) {
+            elt = elt * base;
+        }
+        base = base.sqr();
+    }
+    gstore(zinv + k, (gload(abw) * elt - gload(abw + 1)).inverse());
+}
+template<class Fr> HD void step_divz_body(uint64_t i, uint64_t big, uint64_t compr, const Fr *zinv, const Fr *z1inv, Fr *p)
+{
+    const Fr f = i < big ? gload(zinv + (i & (compr - 1))) : gload(z1inv);
+    gstore(p + i, gload(p + i) * f);
+}
+
 // ---- extended_radix2_domain: element-wise steps and host-side constants (kernels further down) --------------------------
 // Powers b^i of a fixed element from a two-level table: b^i = lo[i mod 2^lg_lo] * hi[i >> lg_lo].
 template<class Fr> struct PowTable {
@@ -353,6 +408,31 @@ template<class Fr> inline Fr host_pow(Fr base, uint64_t e)
         base = base.sqr();
     }
     return acc;
+}
+// step domain constants (step_radix2_domain.tcc:252-276): [0] 1/2  [1] A = g^small Z0  [2] B = omega^small Z0
+// [3] omega^(2 small)  [4] Z1^-1  [5] one;  Z0 = g^big - 1, omega = the root of unity of order 2 big, g = multiplicative_generator
+template<class Fr> inline void step_domain_consts_host(int lg_big, uint64_t small, Fr hc[6])
+{
+    const uint64_t big = 1ull << lg_big;
+    Fr w, g;
+    for (int i = 0; i < Fr::N; ++i) {
+        w.v[i] = Fr::params::root_of_unity(i);
+        g.v[i] = Fr::params::generator(i);
+    }
+    for (int i = Fr::params::S; i > lg_big + 1; --i) {
+        w = w.sqr(); // omega = get_root_of_unity(2 big)
+    }
+    const Fr one = Fr::one();
+    const Fr z0 = host_pow(g, big) - one;
+    const Fr w_small = host_pow(w, small);
+    const Fr gw = g * w;
+    const Fr z1 = (host_pow(gw, big) - one) * (host_pow(gw, small) - w_small);
+    hc[0] = (one + one).inverse();
+    hc[1] = host_pow(g, small) * z0;
+    hc[2] = w_small * z0;
+    hc[3] = host_pow(w, 2 * small);
+    hc[4] = z1.inverse();
+    hc[5] = one;
 }
 // [0] shift^small  [1] (small (1 - shift^small))^-1 (:107)  [2] Z0^-1  [3] Z1^-1 (:224-229), small = 2^lg_small,
 // shift = libff::coset_shift() = multiplicative_generator^2 (field_utils.tcc:152-155); *shift_out = shift
@@ -468,90 +548,56 @@ template<class Fr> __global__ void k_scale(uint64_t m, Fr *a, const Fr *c)
 // (sizes big and small) plus the element-wise steps below; T2[e] = omega^e, e < big, is the
 // twiddle table of the radix-2 domain of size 2 big (omega = its root of unity).
 
-// FFT, step_radix2_domain.tcc:73-88: c[i] = a[i] + a[i+big] (i < small) else a[i];
-// d[i] = omega^i * (a[i] - a[i+big] or a[i]). c overwrites a[0, big), d goes to its own buffer.
-template<class Fr>
-__global__ void k_step_fft_pre(uint64_t big, uint64_t small, const Fr *T2, Fr *a, Fr *d)
+// (the element-wise steps themselves: step_*_body above)
+template<class Fr> __global__ void k_step_fft_pre(uint64_t big, uint64_t small, const Fr *T2, Fr *a, Fr *d)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= big) {
-        return;
+    if (i < big) {
+        step_fft_pre_body<Fr>(i, big, small, T2, a, d);
     }
-    const Fr x = gload(a + i);
-    Fr c = x, dd = x;
-    if (i < small) {
-        const Fr y = gload(a + i + big);
-        c = x + y;
-        dd = x - y;
-    }
-    gstore(a + i, c);
-    gstore(d + i, dd * gload(T2 + i));
 }
-// one halving step of e[i] = sum_j d[i + j small] (:90-98): v[t] += v[t + half]
 template<class Fr> __global__ void k_fold_halve(uint64_t half, Fr *v)
 {
     const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t < half) {
-        gstore(v + t, gload(v + t) + gload(v + t + half));
+        fold_halve_body<Fr>(t, half, v);
     }
 }
-// iFFT, :135-150: tmp[i] = U0[i] omega^i for i >= small, 0 below (the j = 0 term is not subtracted)
-template<class Fr>
-__global__ void k_step_ifft_tmp(uint64_t big, uint64_t small, const Fr *T2, const Fr *u0, Fr *tmp)
+template<class Fr> __global__ void k_step_ifft_tmp(uint64_t big, uint64_t small, const Fr *T2, const Fr *u0, Fr *tmp)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < big) {
-        gstore(tmp + i, i < small ? Fr::zero() : gload(u0 + i) * gload(T2 + i));
+        step_ifft_tmp_body<Fr>(i, small, T2, u0, tmp);
     }
 }
-// iFFT, :152-173: U1[i] = (U1[i] - s[i]) omega^-i; a[i] = (U0[i] + U1[i]) / 2; a[big+i] = (U0[i] - U1[i]) / 2
 template<class Fr>
 __global__ void k_step_ifft_post(uint64_t big, uint64_t small, const Fr *T2, const Fr *s, const Fr *over_two, Fr *a)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= small) {
-        return;
+    if (i < small) {
+        step_ifft_post_body<Fr>(i, big, T2, s, over_two, a);
     }
-    const Fr u0 = gload(a + i);
-    Fr u1 = gload(a + big + i) - gload(s + i);
-    if (i != 0) {
-        u1 = u1 * gload(T2 + (big - i)).neg(); // omega^big = -1
-    }
-    const Fr h = gload(over_two);
-    gstore(a + i, (u0 + u1) * h);
-    gstore(a + big + i, (u0 - u1) * h);
 }
-// a[i] *= table[i]
 template<class Fr> __global__ void k_mul_table(uint64_t n, Fr *a, const Fr *table)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {
-        gstore(a + i, gload(a + i) * gload(table + i));
+        mul_table_body<Fr>(i, a, table);
     }
 }
-// divide_by_Z_on_coset, :252-276: zinv[k] = (A w2s^k - B)^-1, k < compr (the factor has period compr in i)
 template<class Fr> __global__ void k_step_zinv(uint64_t compr, const Fr *abw /* A, B, w2s */, Fr *zinv)
 {
     const uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= compr) {
-        return;
+    if (k < compr) {
+        step_zinv_body<Fr>(k, abw, zinv);
     }
-    Fr elt = Fr::one(), base = gload(abw + 2);
-    for (uint64_t e = k; e; e >>= 1) {
-        if (e & 1) {
-            elt = elt * base;
-        }
-        base = base.sqr();
-    }
-    gstore(zinv + k, (gload(abw) * elt - gload(abw + 1)).inverse());
 }
 template<class Fr>
 __global__ void k_step_divz(uint64_t big, uint64_t m, uint64_t compr, const Fr *zinv, const Fr *z1inv, Fr *p)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < m) {
-        const Fr f = i < big ? gload(zinv + (i & (compr - 1))) : gload(z1inv);
-        gstore(p + i, gload(p + i) * f);
+        step_divz_body<Fr>(i, big, compr, zinv, z1inv, p);
     }
 }
 // h[i] = a[i] b[i] - c[i]

@@ -608,6 +608,114 @@ template<class Fr> static int emu_ext_ntt_t(int op, void *data_, size_t m, const
     return 0;
 }
 
+// step_radix2_domain of size m = big + small (step_fft / step_ifft / step_op_dev / step_divide_by_z_dev of ntt.cu):
+// op 0-3 as above, 4 = divide_by_Z_on_coset
+template<class Fr> static int emu_step_ntt_t(int op, void *data_, size_t m, const void *g_)
+{
+    if (m < 3 || (m & (m - 1)) == 0 || op < 0 || op > 4) {
+        return -2;
+    }
+    int lg_big = 0;
+    while (((size_t)1 << (lg_big + 1)) <= m) {
+        ++lg_big;
+    }
+    const uint64_t big = 1ull << lg_big, small = m - big;
+    if ((small & (small - 1)) || lg_big + 1 > Fr::params::S) {
+        return -2;
+    }
+    int lg_small = 0;
+    while (((uint64_t)1 << lg_small) < small) {
+        ++lg_small;
+    }
+    const uint64_t compr = big / small;
+    Fr *a = (Fr *)data_;
+    Fr hc[6];
+    ntt::step_domain_consts_host<Fr>(lg_big, small, hc);
+    const Fr g = emu_generator<Fr>(g_);
+    const EmuDomain<Fr> d2(lg_big + 1, g), dbig(lg_big, g);
+    const Fr *T2 = d2.tw.data(); // omega^e, e < big
+    if (op == 4) {
+        std::vector<Fr> zinv(compr);
+        for (uint64_t k = 0; k < compr; ++k) {
+            ntt::step_zinv_body<Fr>(k, hc + 1, zinv.data());
+        }
+        for (uint64_t i = 0; i < m; ++i) {
+            ntt::step_divz_body<Fr>(i, big, compr, zinv.data(), hc + 4, a);
+        }
+        return 0;
+    }
+    std::vector<Fr> dd(big);
+    const auto fold_rows = [&]() {
+        for (uint64_t rows = compr; rows > 1; rows >>= 1) {
+            const uint64_t half = (rows >> 1) * small;
+            for (uint64_t t = 0; t < half; ++t) {
+                ntt::fold_halve_body<Fr>(t, half, dd.data());
+            }
+        }
+    };
+    const auto small_transform = [&](Fr *v, int inverse) {
+        if (lg_small >= 1) {
+            const EmuDomain<Fr> ds(lg_small, g);
+            ds.run(v, inverse, nullptr, nullptr, inverse ? &ds.consts[1] : nullptr);
+        }
+    };
+    const auto fft = [&]() {
+        for (uint64_t i = 0; i < big; ++i) {
+            ntt::step_fft_pre_body<Fr>(i, big, small, T2, a, dd.data());
+        }
+        fold_rows();
+        dbig.run(a, 0, nullptr, nullptr, nullptr);
+        if (lg_small >= 1) {
+            small_transform(dd.data(), 0);
+        }
+        memcpy(a + big, dd.data(), small * sizeof(Fr));
+    };
+    const auto ifft = [&]() {
+        dbig.run(a, 1, nullptr, nullptr, &dbig.consts[1]);
+        small_transform(a + big, 1);
+        for (uint64_t i = 0; i < big; ++i) {
+            ntt::step_ifft_tmp_body<Fr>(i, small, T2, a, dd.data());
+        }
+        fold_rows();
+        for (uint64_t i = 0; i < small; ++i) {
+            ntt::step_ifft_post_body<Fr>(i, big, T2, dd.data(), hc, a);
+        }
+    };
+    std::vector<Fr> table(m);
+    switch (op) {
+    case 0: fft(); break;
+    case 1: ifft(); break;
+    case 2: // g^i, i < m, from the size-2big domain's powers of g (step_coset_tables)
+        for (uint64_t e = 0; e < m; ++e) {
+            ntt::pow_table_body<Fr>(e, d2.pg.data(), lg_big + 1, nullptr, table.data());
+        }
+        for (uint64_t i = 0; i < m; ++i) {
+            ntt::mul_table_body<Fr>(i, a, table.data());
+        }
+        fft();
+        break;
+    case 3:
+        ifft();
+        for (uint64_t e = 0; e < m; ++e) {
+            ntt::pow_table_body<Fr>(e, d2.pgi.data(), lg_big + 1, nullptr, table.data());
+        }
+        for (uint64_t i = 0; i < m; ++i) {
+            ntt::mul_table_body<Fr>(i, a, table.data());
+        }
+        break;
+    }
+    return 0;
+}
+
+extern "C" int emu_step_ntt(int curve, int op, void *data, size_t m, const void *g)
+{
+    switch (curve) {
+    case 0: return emu_step_ntt_t<alt_bn128_fr>(op, data, m, g);
+    case 1: return emu_step_ntt_t<bls12_377_fr>(op, data, m, g);
+    case 2: return emu_step_ntt_t<bw6_761_fr>(op, data, m, g);
+    }
+    return -1;
+}
 extern "C" int emu_ntt(int curve, int op, void *data, size_t m, const void *g)
 {
     switch (curve) {

@@ -49,6 +49,7 @@ def emu():
     L.emu_msm_shared.argtypes = [i, i, vp, sz, vp, i, i, C.c_long, vp]
     L.emu_ntt.argtypes = [i, i, vp, sz, vp]
     L.emu_ext_ntt.argtypes = [i, i, vp, sz, vp]
+    L.emu_step_ntt.argtypes = [i, i, vp, sz, vp]
     return L
 
 
@@ -372,3 +373,19 @@ def test_emulated_extended_domain(emu, curve):
             out = np.array(a, dtype=np.uint64, order="C", copy=True)
             assert emu.emu_ext_ntt(CURVES[curve], op, _p(out), out.shape[0], _p(np.ascontiguousarray(coset))) == 0
             assert np.array_equal(out, g[f"{curve}.s{s}.{name}"]), (s, name)
+
+
+@pytest.mark.parametrize("curve", list(CURVES))
+def test_emulated_step_domain(emu, curve):
+    """The device formulation of step_radix2_domain (ntt.cuh: step_fft_pre_body / fold_halve_body / step_ifft_tmp_body /
+    step_ifft_post_body / step_zinv_body / step_divz_body, constants from step_domain_consts_host, the emulated radix-2
+    transforms of sizes big and small) == the vectors the unmodified reference produced through get_evaluation_domain
+    (tests/golden/step.npz): all five operations at m = 3 ... 288, incl. small = 1 and small = big / 2."""
+    g = np.load(os.path.join(GOLD, "step.npz"))
+    coset = np.ascontiguousarray(g[f"{curve}.generator"])
+    for m in [3, 6, 24, 80, 288]:
+        a = g[f"{curve}.m{m}.in"]
+        for op, name in [(0, "fft"), (1, "ifft"), (2, "coset_fft"), (3, "icoset_fft"), (4, "div_z")]:
+            out = np.array(a, dtype=np.uint64, order="C", copy=True)
+            assert emu.emu_step_ntt(CURVES[curve], op, _p(out), m, _p(coset)) == 0
+            assert np.array_equal(out, g[f"{curve}.m{m}.{name}"]), (m, name)
