@@ -971,17 +971,7 @@ int r1cs_upload(R1csSet &r, const uint32_t *row_ptr, const uint32_t *col, const 
     B200_CUDA_CHECK(cudaMemcpyAsync(r.row_ptr, row_ptr, rows * 4, cudaMemcpyHostToDevice, s));
     std::vector<uint32_t> long_rows, seg_ptr;
     std::vector<ntt::LongSeg> segs;
-    for (size_t i = 0; i + 1 < rows; ++i) {
-        if (row_ptr[i + 1] - row_ptr[i] > ntt::R1CS_LONG_ROW) {
-            seg_ptr.push_back((uint32_t)segs.size());
-            for (uint32_t e = row_ptr[i]; e < row_ptr[i + 1]; e += ntt::R1CS_LONG_SEG) {
-                const uint32_t e1 = std::min<uint32_t>(e + ntt::R1CS_LONG_SEG, row_ptr[i + 1]);
-                segs.push_back(ntt::LongSeg{(uint32_t)i, e, e1, (uint32_t)long_rows.size()});
-            }
-            long_rows.push_back((uint32_t)i);
-        }
-    }
-    seg_ptr.push_back((uint32_t)segs.size());
+    ntt::r1cs_long_plan(row_ptr, rows - 1, long_rows, seg_ptr, segs);
     r.num_long = long_rows.size();
     r.num_segs = segs.size();
     if (r.num_long) {

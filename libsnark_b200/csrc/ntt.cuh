@@ -25,6 +25,8 @@
 // shared-memory exchanges. Coset scaling (a[i] *= g^i) and the 1/m of the inverse are
 // fused into the first pass's loads / the last pass's stores from precomputed tables.
 #pragma once
+#include <vector>
+
 #include "curves.cuh"
 
 namespace b200
@@ -313,6 +315,57 @@ template<class Fr> HD void domain_consts_body(int lgn, const Fr *g_in, Fr *const
     gstore(consts + 3, gi);
     gstore(consts + 4, z.is_zero() ? z : z.inverse());
     gstore(consts + 5, Fr::one());
+}
+
+// ---- sparse R1CS evaluation: the row body and the host-side plan for long rows (kernels further down) -------------------
+constexpr uint32_t R1CS_LONG_ROW = 64;
+constexpr int R1CS_LONG_THREADS = 256;
+constexpr uint32_t R1CS_LONG_SEG = 2048; // terms per CTA of the long-row kernel
+// Rows with more than R1CS_LONG_ROW terms (a sum over all variables is a common last constraint) are cut into segments
+// of R1CS_LONG_SEG terms: one CTA per segment writes a partial; a second launch adds the partials of each row.
+struct LongSeg {
+    uint32_t row, e0, e1, slot; // slot: index of the row in the long-row list
+};
+// rows = 3 nc (the a-, b-, c-combinations); seg_ptr[k] .. seg_ptr[k+1]: the segments of long row k
+inline void r1cs_long_plan(const uint32_t *row_ptr, size_t rows, std::vector<uint32_t> &long_rows, std::vector<uint32_t> &seg_ptr,
+                           std::vector<LongSeg> &segs)
+{
+    for (size_t i = 0; i < rows; ++i) {
+        if (row_ptr[i + 1] - row_ptr[i] > R1CS_LONG_ROW) {
+            seg_ptr.push_back((uint32_t)segs.size());
+            for (uint32_t e = row_ptr[i]; e < row_ptr[i + 1]; e += R1CS_LONG_SEG) {
+                const uint32_t e1 = e + R1CS_LONG_SEG < row_ptr[i + 1] ? e + R1CS_LONG_SEG : row_ptr[i + 1];
+                segs.push_back(LongSeg{(uint32_t)i, e, e1, (uint32_t)long_rows.size()});
+            }
+            long_rows.push_back((uint32_t)i);
+        }
+    }
+    seg_ptr.push_back((uint32_t)segs.size());
+}
+// Element t of the 3 m outputs (r1cs_to_qap.tcc:236-248, :293-296; linear_combination::evaluate, variable.tcc:288-299):
+// rows [0, nc) of A, [nc, 2nc) of B, [2nc, 3nc) of C in one CSR; column 0 is the constant 1, column k the k-th variable,
+// so w = (1 | primary | auxiliary) is indexed directly. Also the input-consistency rows aA[nc + i] = w[i], i <= num_inputs
+// (:240-243) and the zero padding up to m. A long row is left to the segment kernels.
+template<class Fr>
+HD void r1cs_eval_body(uint64_t t, uint64_t nc, uint64_t ni, uint64_t m, const uint32_t *row_ptr, const uint32_t *col, const Fr *val,
+                       const Fr *w, Fr *aA, Fr *aB, Fr *aC)
+{
+    const uint64_t mat = t / m, i = t - mat * m;
+    Fr *dst = mat == 0 ? aA : (mat == 1 ? aB : aC);
+    Fr acc = Fr::zero();
+    if (i < nc) {
+        const uint64_t row = mat * nc + i;
+        const uint32_t e0 = row_ptr[row], e1 = row_ptr[row + 1];
+        if (e1 - e0 > R1CS_LONG_ROW) {
+            return; // the segment kernels own this row
+        }
+        for (uint32_t e = e0; e < e1; ++e) {
+            acc = acc + gload(val + e) * gload(w + col[e]);
+        }
+    } else if (mat == 0 && i - nc <= ni) {
+        acc = gload(w + (i - nc));
+    }
+    gstore(dst + i, acc);
 }
 
 // ---- step_radix2_domain: element-wise steps and host-side constants (kernels further down) ------------------------------
@@ -675,47 +728,18 @@ template<class Fr> __global__ void k_coeff_fixups(CoeffFixups<Fr> f, Fr *h)
     }
 }
 
-constexpr uint32_t R1CS_LONG_ROW = 64;
-constexpr int R1CS_LONG_THREADS = 256;
-constexpr uint32_t R1CS_LONG_SEG = 2048; // terms per CTA of the long-row kernel
-
-// Sparse R1CS evaluation (r1cs_to_qap.tcc:236-248, :293-296; linear_combination::evaluate,
-// variable.tcc:288-299): rows [0, nc) of A, [nc, 2nc) of B, [2nc, 3nc) of C in one CSR.
-// Column 0 is the constant 1, column k the k-th variable, so w = (1 | primary | auxiliary) is indexed
-// directly. One thread per row; rows of R1CS matrices hold a handful of terms. Also writes the
-// input-consistency rows aA[nc + i] = w[i], i <= num_inputs (:240-243) and zeroes the padding up to m.
+// Sparse R1CS evaluation: one thread per output element (r1cs_eval_body above); rows of R1CS matrices hold a handful of terms.
 template<class Fr>
 __global__ void k_r1cs_eval(uint64_t nc, uint64_t ni, uint64_t m, const uint32_t *row_ptr, const uint32_t *col,
                             const Fr *val, const Fr *w, Fr *aA, Fr *aB, Fr *aC)
 {
     const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= 3 * m) {
-        return;
+    if (t < 3 * m) {
+        r1cs_eval_body<Fr>(t, nc, ni, m, row_ptr, col, val, w, aA, aB, aC);
     }
-    const uint64_t mat = t / m, i = t - mat * m;
-    Fr *dst = mat == 0 ? aA : (mat == 1 ? aB : aC);
-    Fr acc = Fr::zero();
-    if (i < nc) {
-        const uint64_t row = mat * nc + i;
-        const uint32_t e0 = row_ptr[row], e1 = row_ptr[row + 1];
-        if (e1 - e0 > R1CS_LONG_ROW) {
-            return; // k_r1cs_eval_long owns this row
-        }
-        for (uint32_t e = e0; e < e1; ++e) {
-            acc = acc + gload(val + e) * gload(w + col[e]);
-        }
-    } else if (mat == 0 && i - nc <= ni) {
-        acc = gload(w + (i - nc));
-    }
-    gstore(dst + i, acc);
 }
 
-// Rows with more than R1CS_LONG_ROW terms (a sum over all variables is a common last constraint) are
-// cut into segments of R1CS_LONG_SEG terms: one CTA per segment (strided partial sums, shared-memory
-// tree) writes a partial; a second launch adds the partials of each row (one CTA per row).
-struct LongSeg {
-    uint32_t row, e0, e1, slot; // slot: index of the row in the long-row list
-};
+// Long rows: one CTA per segment (strided partial sums, shared-memory tree), then one CTA per row over its partials.
 template<class Fr> __device__ Fr cta_tree_sum(Fr acc, Fr *part)
 {
     part[threadIdx.x] = acc;

@@ -707,6 +707,53 @@ template<class Fr> static int emu_step_ntt_t(int op, void *data_, size_t m, cons
     return 0;
 }
 
+// The sparse R1CS evaluation (r1cs_eval_launch of ntt.cu): the row body for every output element, then the long rows
+// by the launcher's own segment plan — per segment a sum of its terms (k_r1cs_eval_long), per row a sum of its partials
+// (k_r1cs_long_finish); the CTA trees of those kernels are sums, and field addition is exact.
+template<class Fr>
+static int emu_r1cs_t(size_t nc, size_t ni, size_t m, const uint32_t *row_ptr, const uint32_t *col, const void *val_, const void *w_,
+                      void *aA_, void *aB_, void *aC_)
+{
+    if (m < nc + ni + 1) {
+        return -2;
+    }
+    const Fr *val = (const Fr *)val_, *w = (const Fr *)w_;
+    Fr *aA = (Fr *)aA_, *aB = (Fr *)aB_, *aC = (Fr *)aC_;
+    for (uint64_t t = 0; t < 3 * m; ++t) {
+        ntt::r1cs_eval_body<Fr>(t, nc, ni, m, row_ptr, col, val, w, aA, aB, aC);
+    }
+    std::vector<uint32_t> long_rows, seg_ptr;
+    std::vector<ntt::LongSeg> segs;
+    ntt::r1cs_long_plan(row_ptr, 3 * nc, long_rows, seg_ptr, segs);
+    std::vector<Fr> partials(segs.size() + 1);
+    for (size_t k = 0; k < segs.size(); ++k) {
+        Fr acc = Fr::zero();
+        for (uint32_t e = segs[k].e0; e < segs[k].e1; ++e) {
+            acc = acc + val[e] * w[col[e]];
+        }
+        partials[k] = acc;
+    }
+    for (size_t r = 0; r < long_rows.size(); ++r) {
+        Fr acc = Fr::zero();
+        for (uint32_t k = seg_ptr[r]; k < seg_ptr[r + 1]; ++k) {
+            acc = acc + partials[k];
+        }
+        const uint64_t row = long_rows[r], mat = row / nc, i = row - mat * nc;
+        (mat == 0 ? aA : (mat == 1 ? aB : aC))[i] = acc;
+    }
+    return (int)long_rows.size();
+}
+extern "C" int emu_r1cs_evaluate(int curve, size_t nc, size_t ni, size_t m, const uint32_t *row_ptr, const uint32_t *col,
+                                 const void *val, const void *w, void *aA, void *aB, void *aC)
+{
+    switch (curve) {
+    case 0: return emu_r1cs_t<alt_bn128_fr>(nc, ni, m, row_ptr, col, val, w, aA, aB, aC);
+    case 1: return emu_r1cs_t<bls12_377_fr>(nc, ni, m, row_ptr, col, val, w, aA, aB, aC);
+    case 2: return emu_r1cs_t<bw6_761_fr>(nc, ni, m, row_ptr, col, val, w, aA, aB, aC);
+    }
+    return -1;
+}
+
 extern "C" int emu_step_ntt(int curve, int op, void *data, size_t m, const void *g)
 {
     switch (curve) {

@@ -50,6 +50,7 @@ def emu():
     L.emu_ntt.argtypes = [i, i, vp, sz, vp]
     L.emu_ext_ntt.argtypes = [i, i, vp, sz, vp]
     L.emu_step_ntt.argtypes = [i, i, vp, sz, vp]
+    L.emu_r1cs_evaluate.argtypes = [i, sz, sz, sz, vp, vp, vp, vp, vp, vp, vp]
     return L
 
 
@@ -389,3 +390,27 @@ def test_emulated_step_domain(emu, curve):
             out = np.array(a, dtype=np.uint64, order="C", copy=True)
             assert emu.emu_step_ntt(CURVES[curve], op, _p(out), m, _p(coset)) == 0
             assert np.array_equal(out, g[f"{curve}.m{m}.{name}"]), (m, name)
+
+
+def test_emulated_r1cs_evaluation(emu):
+    """The device's sparse R1CS evaluation (ntt.cuh r1cs_eval_body for every output element, the long rows cut by
+    r1cs_long_plan and summed per segment and per row as the two long-row kernels do) == the aA, aB, aC the unmodified
+    reference built (r1cs_to_qap.tcc:236-248, :293-296) for the committed circuits — each of which closes with a constraint
+    over all variables, i.e. a long row — on all three fields, incl. the zero padding and the input-consistency rows."""
+    cases = [("step.npz", "alt_bn128", "witness")]
+    z = np.load(os.path.join(GOLD, "zk.npz"))
+    for ci, nc, _s, _m in z["cases"]:
+        cases.append(("zk.npz", list(CURVES)[int(ci)], f"{list(CURVES)[int(ci)]}.nc{int(nc)}"))
+    for fname, curve, k in cases:
+        g = np.load(os.path.join(GOLD, fname))
+        n_c, ni, nv, m = [int(x) for x in g[k + ".sizes"]]
+        row_ptr = np.ascontiguousarray(g[k + ".row_ptr"], dtype=np.uint32)
+        col = np.ascontiguousarray(g[k + ".col"], dtype=np.uint32)
+        val = np.ascontiguousarray(g[k + ".val"], dtype=np.uint64)
+        w = np.ascontiguousarray(g[k + ".w"], dtype=np.uint64)
+        assert w.shape[0] == nv + 1 and row_ptr.shape[0] == 3 * n_c + 1
+        out = [np.full((m, w.shape[1]), 0xAB, dtype=np.uint64) for _ in range(3)]   # garbage: every element must be written
+        nlong = emu.emu_r1cs_evaluate(CURVES[curve], n_c, ni, m, _p(row_ptr), _p(col), _p(val), _p(w), *[_p(o) for o in out])
+        assert nlong >= (1 if nv > 70 else 0), (k, nlong)   # the closing constraint sums every variable
+        for got, name in zip(out, ["aA", "aB", "aC"]):
+            assert np.array_equal(got, g[f"{k}.{name}"]), (k, name)
