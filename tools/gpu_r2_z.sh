@@ -1,4 +1,5 @@
 #!/bin/bash
-# Round 2, call Z17: R1CS evaluation after the body / plan refactor: witness-map and prover tests.
+# Round 2, closing run on the final tree: smoke() and the whole gpu suite.
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_ntt_gpu.py tests/test_groth16_gpu.py -q -m gpu -x -k "r1cs or witness or golden or c_abi_prover or zk_patch" 2>&1 | tail -2
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -1
+(time timeout 1500 python -m pytest tests -q -m gpu -x 2>&1 | grep -v "^\*\|^  \*\|^(\|^$" | tail -3) 2>&1 | tee gpurun_out/r2s6_pytest.log
