@@ -22,9 +22,14 @@
  *               FFT / iFFT / cosetFFT / icosetFFT / divide_by_Z_on_coset  basic_radix2_domain.tcc:54-126
  *   step FFT  : step_radix2_domain FFT / iFFT / cosetFFT / icosetFFT / divide_by_Z_on_coset
  *               libfqfft/evaluation_domain/domains/step_radix2_domain.tcc:20-279 (sizes 2^k + 2^r)
+ *   ext FFT   : extended_radix2_domain FFT / iFFT / cosetFFT / icosetFFT / divide_by_Z_on_coset
+ *               libfqfft/evaluation_domain/domains/extended_radix2_domain.tcc:21-236 (size 2^(s+1); s as the factory sees it
+ *               is settable, port_set_two_adicity, the way libff's mutable FieldT::s is: pinned to vectors the reference
+ *               produced with s lowered, tests/golden/extended.npz)
  *   R1CS eval : aA, aB, aC incl. the input-consistency rows  libsnark/reductions/r1cs_to_qap/r1cs_to_qap.tcc:236-248,
  *               :293-296; linear_combination::evaluate  libsnark/relations/variable.tcc:288-299
- *   H chain   : libsnark/reductions/r1cs_to_qap/r1cs_to_qap.tcc:252-330 (d1 = d2 = d3 = 0), over either domain kind
+ *   H chain   : libsnark/reductions/r1cs_to_qap/r1cs_to_qap.tcc:252-330 (d1 = d2 = d3 = 0), over the three domain kinds;
+ *               with the ZK patch (:262-271, :327-333) and add_poly_Z of each kind: port_witness_map_h_zk (tests/golden/zk.npz)
  *   key gen   : get_window_table / windowed_exp / batch_exp / batch_exp_with_coeff / batch_to_special
  *               libff/algebra/scalar_multiplication/multiexp.tcc:808-974
  *   prover    : the orchestration r1cs_gg_ppzksnark.tcc:460-603 is composed from these in oracle/port.py::groth16_prove
