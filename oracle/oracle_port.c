@@ -30,6 +30,8 @@
  *               :293-296; linear_combination::evaluate  libsnark/relations/variable.tcc:288-299
  *   H chain   : libsnark/reductions/r1cs_to_qap/r1cs_to_qap.tcc:252-330 (d1 = d2 = d3 = 0), over the three domain kinds;
  *               with the ZK patch (:262-271, :327-333) and add_poly_Z of each kind: port_witness_map_h_zk (tests/golden/zk.npz)
+ *   SAP map   : r1cs_to_sap_witness_map  libsnark/reductions/r1cs_to_sap/r1cs_to_sap.tcc:297-481 (port_sap_witness_map;
+ *               the witness map of r1cs_se_ppzksnark; tests/golden/zk.npz)
  *   key gen   : get_window_table / windowed_exp / batch_exp / batch_exp_with_coeff / batch_to_special
  *               libff/algebra/scalar_multiplication/multiexp.tcc:808-974
  *   prover    : the orchestration r1cs_gg_ppzksnark.tcc:460-603 is composed from these in oracle/port.py::groth16_prove
@@ -1172,6 +1174,89 @@ static int add_poly_z(fp_t *H, size_t m, const fp_t *coeff)
     fp_sub(&H[small], &H[small], coeff);
     fp_add(&H[0], &H[0], &u);
     return 0;
+}
+
+/* r1cs_to_sap_witness_map (libsnark/reductions/r1cs_to_sap/r1cs_to_sap.tcc:297-481; the witness map of
+ * r1cs_se_ppzksnark), in the reference's order. ea, eb, ec: the values <a_i, w>, <b_i, w>, <c_i, w> of the nc constraints
+ * (port_r1cs_evaluate rows [0, nc)); w = (1 | primary | auxiliary); d12 = d1, d2. out_H: m + 1 coefficients with
+ * m = the SAP domain size (get_evaluation_domain(2 nc + 2 ni + 1), passed in); out_extra: the nc + ni extra variables. */
+API int port_sap_witness_map(int curve, size_t nc, size_t ni, size_t nv, const void *ea_, const void *eb_, const void *ec_,
+                             const void *w_, size_t m, const void *d12, void *out_H, void *out_extra)
+{
+    if (curve < 0 || curve > 2 || m < 2 * nc + 2 * ni + 1) return -1;
+    g_f = &curve_table[curve].fr;
+    const int nr = g_f->n;
+    fp_t gen, d[2], one, t, u;
+    fp_zero(&gen);
+    memcpy(gen.v, g_f->generator, 8 * nr);
+    fp_one(&one);
+    for (int k = 0; k < 2; ++k) {
+        fp_zero(&d[k]);
+        memcpy(d[k].v, (const uint64_t *)d12 + k * nr, 8 * nr);
+    }
+    fp_t *ea = load_frs((const uint64_t *)ea_, nc), *eb = load_frs((const uint64_t *)eb_, nc), *ec = load_frs((const uint64_t *)ec_, nc);
+    fp_t *w = load_frs((const uint64_t *)w_, nv + 1); /* w[i] = full_variable_assignment[i - 1] */
+    fp_t *extra = (fp_t *)calloc(nc + ni + 1, sizeof(fp_t));
+    for (size_t i = 0; i < nc; ++i) { /* :330-341: (a - b)^2 */
+        fp_sub(&t, &ea[i], &eb[i]);
+        fp_sqr(&extra[i], &t);
+    }
+    for (size_t i = 1; i <= ni; ++i) { /* :342-351: (x_i - 1)^2 */
+        fp_sub(&t, &w[i], &one);
+        fp_sqr(&extra[nc + i - 1], &t);
+    }
+    fp_t *A = (fp_t *)calloc(m, sizeof(fp_t)), *Cc = (fp_t *)calloc(m, sizeof(fp_t)), *H = (fp_t *)calloc(m + 1, sizeof(fp_t));
+    const size_t off = 2 * nc;
+    for (size_t i = 0; i < nc; ++i) { /* :357-363, :414-420 */
+        fp_add(&A[2 * i], &ea[i], &eb[i]);
+        fp_sub(&A[2 * i + 1], &ea[i], &eb[i]);
+        fp_add(&t, &ec[i], &ec[i]);
+        fp_add(&t, &t, &t); /* times_four */
+        fp_add(&Cc[2 * i], &t, &extra[i]);
+        Cc[2 * i + 1] = extra[i];
+    }
+    A[off] = one; /* :367, :423 */
+    Cc[off] = one;
+    for (size_t i = 1; i <= ni; ++i) { /* :369-375, :425-433 */
+        fp_add(&A[off + 2 * i - 1], &w[i], &one);
+        fp_sub(&A[off + 2 * i], &w[i], &one);
+        fp_add(&t, &w[i], &w[i]);
+        fp_add(&t, &t, &t);
+        fp_add(&Cc[off + 2 * i - 1], &t, &extra[nc + i - 1]);
+        Cc[off + 2 * i] = extra[nc + i - 1];
+    }
+    int rc = domain_inplace(A, m, 1, &gen); /* :380 */
+    if (!rc) {
+        for (size_t i = 0; i < m; ++i) { /* :388-391: 2 d1 A */
+            fp_mul(&t, &d[0], &A[i]);
+            fp_add(&H[i], &t, &t);
+        }
+        fp_sub(&H[0], &H[0], &d[1]);
+        fp_mul(&t, &d[0], &d[0]);
+        rc = add_poly_z(H, m, &t);
+    }
+    if (!rc) {
+        domain_inplace(A, m, 2, &gen);
+        for (size_t i = 0; i < m; ++i) fp_sqr(&A[i], &A[i]);
+        domain_inplace(Cc, m, 1, &gen);
+        domain_inplace(Cc, m, 2, &gen);
+        for (size_t i = 0; i < m; ++i) fp_sub(&A[i], &A[i], &Cc[i]);
+        domain_inplace(A, m, 4, &gen);
+        domain_inplace(A, m, 3, &gen);
+        for (size_t i = 0; i < m; ++i) fp_add(&H[i], &H[i], &A[i]);
+        store_frs((uint64_t *)out_H, H, m + 1);
+        store_frs((uint64_t *)out_extra, extra, nc + ni);
+    }
+    (void)u;
+    free(ea);
+    free(eb);
+    free(ec);
+    free(w);
+    free(extra);
+    free(A);
+    free(Cc);
+    free(H);
+    return rc;
 }
 
 /* r1cs_to_qap_witness_map with its ZK patch, in the reference's order (r1cs_to_qap.tcc:252-333): d123 = d1, d2, d3. */

@@ -36,6 +36,7 @@ class OraclePort:
         L.port_fft.argtypes = [i, i, vp, sz, vp]
         L.port_witness_map_h.argtypes = [i, vp, vp, vp, sz, vp]
         L.port_witness_map_h_zk.argtypes = [i, vp, vp, vp, sz, vp, vp]
+        L.port_sap_witness_map.argtypes = [i, sz, sz, sz, vp, vp, vp, vp, sz, vp, vp, vp]
         L.port_field_op.argtypes = [i, i, i, vp, vp, vp, sz]
         L.port_group_op.argtypes = [i, i, i, vp, vp, vp, sz]
         L.port_batch_exp.argtypes = [i, i, vp, vp, vp, sz, sz, vp]
@@ -154,6 +155,17 @@ class OraclePort:
         out = np.zeros((m + 1, aA.shape[1]), dtype=np.uint64)
         assert self.lib.port_witness_map_h_zk(_cid(curve), _p(aA), _p(aB), _p(aC), m, _p(d), _p(out)) == 0
         return out
+
+    def sap_witness_map(self, curve, nc, ni, nv, ea, eb, ec, w, m, d1, d2):
+        """(coefficients_for_H (m + 1), the nc + ni extra variables) of r1cs_to_sap_witness_map (r1cs_to_sap.tcc:297-481);
+        ea, eb, ec = the first nc rows of r1cs_evaluate, m = the SAP domain size."""
+        ea, eb, ec, w = (np.ascontiguousarray(x, dtype=np.uint64) for x in (ea, eb, ec, w))
+        d = np.ascontiguousarray(np.stack([np.asarray(x, dtype=np.uint64).reshape(-1) for x in (d1, d2)]))
+        H = np.zeros((m + 1, w.shape[1]), dtype=np.uint64)
+        extra = np.zeros((nc + ni, w.shape[1]), dtype=np.uint64)
+        rc = self.lib.port_sap_witness_map(_cid(curve), nc, ni, nv, _p(ea), _p(eb), _p(ec), _p(w), m, _p(d), _p(H), _p(extra))
+        assert rc == 0, rc
+        return H, extra
 
     def field_op(self, curve, field, op, a, b=None):
         a = np.ascontiguousarray(a, dtype=np.uint64)

@@ -260,6 +260,22 @@ def test_witness_map_with_zk_patch_golden(P, curve, nc, s, m):
             P.set_two_adicity(curve, 0)
 
 
+@pytest.mark.parametrize("curve,nc,s,m", [c for c in ZK_CASES if c[2] == 0])
+def test_sap_witness_map_golden(P, curve, nc, s, m):
+    """r1cs_to_sap_witness_map (r1cs_to_sap.tcc:297-481; the witness map of r1cs_se_ppzksnark, which the overlay specialises)
+    restated in the C oracle == every coefficient of H and every extra variable the reference computed, d1 and d2 random."""
+    g = np.load(os.path.join(GOLD, "zk.npz"))
+    k = f"{curve}.nc{nc}"
+    n_c, ni, nv, _ = [int(x) for x in g[k + ".sizes"]]
+    msap = g[k + ".sap_H"].shape[0] - 1
+    assert msap >= 2 * n_c + 2 * ni + 1
+    ea, eb, ec = P.r1cs_evaluate(curve, n_c, ni, g[k + ".row_ptr"], g[k + ".col"], g[k + ".val"], g[k + ".w"], n_c + ni + 1)
+    d = g[k + ".d"]
+    H, extra = P.sap_witness_map(curve, n_c, ni, nv, ea[:n_c], eb[:n_c], ec[:n_c], g[k + ".w"], msap, d[0], d[1])
+    assert np.array_equal(extra, g[k + ".sap_extra"])
+    assert np.array_equal(H, g[k + ".sap_H"])
+
+
 def test_r1cs_evaluation_golden(P):
     """The sparse evaluation <a_i, w>, <b_i, w>, <c_i, w> with the input-consistency rows (r1cs_to_qap.tcc:236-248,
     :293-296; linear_combination::evaluate, variable.tcc:288-299) restated over the CSR the device path uploads ==
